@@ -1,0 +1,279 @@
+// core.cu — context, HBM allocation, Arrow C Data Interface import/export.
+#include <cstdlib>
+#include <cstring>
+
+#include "core.h"
+
+namespace b2 {
+
+DevBuf::DevBuf(Ctx* c, size_t n) : ctx(c), bytes(n) {
+  if (n == 0) return;
+  cudaError_t e = cudaMallocAsync(&ptr, n, c->pool, c->stream);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    fail(e == cudaErrorMemoryAllocation ? B2_ERR_OOM : B2_ERR_CUDA,
+         "cudaMallocAsync(" + std::to_string(n) + " B): " + cudaGetErrorString(e));
+  }
+}
+DevBuf::~DevBuf() {
+  if (ptr) cudaFreeAsync(ptr, ctx->stream);
+}
+BufPtr dev_alloc(Ctx* ctx, size_t bytes) { return std::make_shared<DevBuf>(ctx, bytes); }
+BufPtr dev_alloc_zero(Ctx* ctx, size_t bytes) {
+  auto b = dev_alloc(ctx, bytes);
+  if (bytes) B2_CUDA(cudaMemsetAsync(b->ptr, 0, bytes, ctx->stream));
+  return b;
+}
+
+const char* dtype_name(int dt) {
+  switch (dt) {
+    case B2_BOOL: return "Boolean";
+    case B2_INT32: return "Int32";
+    case B2_INT64: return "Int64";
+    case B2_UINT64: return "UInt64";
+    case B2_FLOAT64: return "Float64";
+    case B2_DATE32: return "Date32";
+    case B2_UTF8: return "Utf8";
+    case B2_UINT8: return "UInt8";
+    default: return "?";
+  }
+}
+
+static int dtype_from_format(const char* f) {
+  if (!strcmp(f, "b")) return B2_BOOL;
+  if (!strcmp(f, "i")) return B2_INT32;
+  if (!strcmp(f, "l")) return B2_INT64;
+  if (!strcmp(f, "L")) return B2_UINT64;
+  if (!strcmp(f, "g")) return B2_FLOAT64;
+  if (!strcmp(f, "tdD")) return B2_DATE32;
+  if (!strcmp(f, "u")) return B2_UTF8;
+  if (!strcmp(f, "C")) return B2_UINT8;
+  fail(B2_ERR_NOT_IMPLEMENTED, std::string("Arrow format '") + f + "' is not supported on the GPU path");
+}
+static const char* format_from_dtype(int dt) {
+  switch (dt) {
+    case B2_BOOL: return "b";
+    case B2_INT32: return "i";
+    case B2_INT64: return "l";
+    case B2_UINT64: return "L";
+    case B2_FLOAT64: return "g";
+    case B2_DATE32: return "tdD";
+    case B2_UTF8: return "u";
+    case B2_UINT8: return "C";
+  }
+  fail(B2_ERR_INVALID_ARG, "bad dtype");
+}
+
+Schema schema_from_arrow(const ArrowSchema* s) {
+  if (!s || !s->format) fail(B2_ERR_INVALID_ARG, "null ArrowSchema");
+  if (strcmp(s->format, "+s") != 0) fail(B2_ERR_ARROW, "schema must be a struct ('+s')");
+  Schema out;
+  for (int64_t i = 0; i < s->n_children; ++i) {
+    const ArrowSchema* c = s->children[i];
+    Field f;
+    f.name = c->name ? c->name : "";
+    f.dtype = dtype_from_format(c->format);
+    f.nullable = (c->flags & ARROW_FLAG_NULLABLE) != 0;
+    out.fields.push_back(f);
+  }
+  return out;
+}
+
+// ---- schema export ----
+struct SchemaPriv {
+  std::string format, name;
+  std::vector<ArrowSchema> child_store;
+  std::vector<ArrowSchema*> child_ptrs;
+};
+static void release_schema(ArrowSchema* s) {
+  if (!s || !s->release) return;
+  for (int64_t i = 0; i < s->n_children; ++i)
+    if (s->children[i]->release) s->children[i]->release(s->children[i]);
+  delete static_cast<SchemaPriv*>(s->private_data);
+  s->release = nullptr;
+}
+static void fill_schema(ArrowSchema* out, const std::string& fmt, const std::string& name, bool nullable,
+                        size_t n_children) {
+  auto* p = new SchemaPriv;
+  p->format = fmt;
+  p->name = name;
+  p->child_store.resize(n_children);
+  for (auto& c : p->child_store) p->child_ptrs.push_back(&c);
+  memset(out, 0, sizeof(*out));
+  out->format = p->format.c_str();
+  out->name = p->name.c_str();
+  out->flags = nullable ? ARROW_FLAG_NULLABLE : 0;
+  out->n_children = (int64_t)n_children;
+  out->children = n_children ? p->child_ptrs.data() : nullptr;
+  out->release = release_schema;
+  out->private_data = p;
+}
+void schema_to_arrow(const Schema& s, ArrowSchema* out) {
+  fill_schema(out, "+s", "", false, s.fields.size());
+  for (size_t i = 0; i < s.fields.size(); ++i)
+    fill_schema(out->children[i], format_from_dtype(s.fields[i].dtype), s.fields[i].name,
+                s.fields[i].nullable, 0);
+}
+
+// ---- array import ----
+__global__ void rebase_offsets_kernel(int32_t* off, int64_t n, int32_t base) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) off[i] -= base;
+}
+
+BatchPtr batch_from_arrow(Ctx* ctx, const Schema& schema, ArrowArray* arr, cudaStream_t stream) {
+  if (!arr) fail(B2_ERR_INVALID_ARG, "null ArrowArray");
+  if ((size_t)arr->n_children != schema.fields.size())
+    fail(B2_ERR_ARROW, "RecordBatch has " + std::to_string(arr->n_children) + " columns, schema has " +
+                           std::to_string(schema.fields.size()));
+  if (arr->null_count > 0) fail(B2_ERR_NOT_IMPLEMENTED, "null struct rows");
+  cudaStream_t st = stream ? stream : ctx->stream;
+  auto b = std::make_shared<Batch>();
+  b->ctx = ctx;
+  b->schema = schema;
+  b->num_rows = arr->length;
+  for (int64_t ci = 0; ci < arr->n_children; ++ci) {
+    const ArrowArray* c = arr->children[ci];
+    const Field& f = schema.fields[ci];
+    int64_t off = c->offset + arr->offset;
+    int64_t len = arr->length;
+    if (c->length < arr->offset + arr->length) fail(B2_ERR_ARROW, "child array shorter than batch");
+    // validity bitmaps: accepted only when they mark nothing null
+    if (c->null_count > 0)
+      fail(B2_ERR_NOT_IMPLEMENTED, "column '" + f.name + "' contains nulls; the TPC-H path is non-nullable");
+    Column col;
+    col.dtype = f.dtype;
+    col.length = len;
+    if (f.dtype == B2_UTF8) {
+      const int32_t* ho = static_cast<const int32_t*>(c->buffers[1]);
+      const char* hd = static_cast<const char*>(c->buffers[2]);
+      col.data = dev_alloc(ctx, (size_t)(len + 1) * 4);
+      int32_t base = 0, end = 0;
+      if (len > 0 || ho) {
+        base = ho ? ho[off] : 0;
+        end = ho ? ho[off + len] : 0;
+      }
+      if (ho)
+        B2_CUDA(cudaMemcpyAsync(col.data->ptr, ho + off, (size_t)(len + 1) * 4, cudaMemcpyHostToDevice, st));
+      else
+        B2_CUDA(cudaMemsetAsync(col.data->ptr, 0, 4, st));
+      col.chars_len = end - base;
+      col.chars = dev_alloc(ctx, (size_t)col.chars_len + 16);
+      if (col.chars_len)
+        B2_CUDA(cudaMemcpyAsync(col.chars->ptr, hd + base, (size_t)col.chars_len, cudaMemcpyHostToDevice, st));
+      if (base != 0) {
+        rebase_offsets_kernel<<<grid_for(ctx, 4, len + 1, 256), 256, 0, st>>>(col.data->as<int32_t>(), len + 1,
+                                                                             base);
+        B2_LAUNCHED(ctx);
+      }
+    } else if (f.dtype == B2_BOOL) {
+      // Arrow booleans are bit-packed; device BOOL columns are one byte per row
+      std::vector<uint8_t> tmp((size_t)len);
+      const uint8_t* bits = static_cast<const uint8_t*>(c->buffers[1]);
+      for (int64_t i = 0; i < len; ++i) tmp[(size_t)i] = (bits[(off + i) >> 3] >> ((off + i) & 7)) & 1;
+      col.data = dev_alloc(ctx, (size_t)len + 16);
+      if (len) {
+        B2_CUDA(cudaMemcpyAsync(col.data->ptr, tmp.data(), (size_t)len, cudaMemcpyHostToDevice, st));
+        B2_CUDA(cudaStreamSynchronize(st));
+      }
+    } else {
+      size_t w = dtype_width(f.dtype);
+      col.data = dev_alloc(ctx, (size_t)len * w + 16);
+      if (len)
+        B2_CUDA(cudaMemcpyAsync(col.data->ptr, static_cast<const char*>(c->buffers[1]) + (size_t)off * w,
+                                (size_t)len * w, cudaMemcpyHostToDevice, st));
+    }
+    b->cols.push_back(std::move(col));
+  }
+  return b;
+}
+
+// ---- array export ----
+struct ArrayPriv {
+  std::vector<void*> owned;  // malloc'ed host buffers
+  std::vector<const void*> buffers;
+  std::vector<ArrowArray> child_store;
+  std::vector<ArrowArray*> child_ptrs;
+};
+static void release_array(ArrowArray* a) {
+  if (!a || !a->release) return;
+  for (int64_t i = 0; i < a->n_children; ++i)
+    if (a->children[i]->release) a->children[i]->release(a->children[i]);
+  auto* p = static_cast<ArrayPriv*>(a->private_data);
+  for (void* q : p->owned) free(q);
+  delete p;
+  a->release = nullptr;
+}
+static void* host_buf(ArrayPriv* p, size_t n) {
+  void* q = malloc(n ? n : 1);
+  if (!q) fail(B2_ERR_OOM, "host malloc failed");
+  p->owned.push_back(q);
+  return q;
+}
+
+void batch_to_arrow(const Batch& b, ArrowArray* out) {
+  Ctx* ctx = b.ctx;
+  auto* top = new ArrayPriv;
+  top->child_store.resize(b.cols.size());
+  for (auto& c : top->child_store) {
+    memset(&c, 0, sizeof(c));
+    top->child_ptrs.push_back(&c);
+  }
+  top->buffers.push_back(nullptr);
+  memset(out, 0, sizeof(*out));
+  out->length = b.num_rows;
+  out->n_buffers = 1;
+  out->buffers = top->buffers.data();
+  out->n_children = (int64_t)b.cols.size();
+  out->children = top->child_ptrs.data();
+  out->release = release_array;
+  out->private_data = top;
+  try {
+    std::vector<std::pair<size_t, std::vector<uint8_t>>> bools;  // bit-pack after the sync
+    for (size_t ci = 0; ci < b.cols.size(); ++ci) {
+      const Column& col = b.cols[ci];
+      auto* p = new ArrayPriv;
+      ArrowArray* a = &top->child_store[ci];
+      a->length = col.length;
+      a->release = release_array;
+      a->private_data = p;
+      if (col.dtype == B2_UTF8) {
+        void* ho = host_buf(p, (size_t)(col.length + 1) * 4);
+        void* hd = host_buf(p, (size_t)col.chars_len);
+        B2_CUDA(cudaMemcpyAsync(ho, col.data->ptr, (size_t)(col.length + 1) * 4, cudaMemcpyDeviceToHost,
+                                ctx->stream));
+        if (col.chars_len)
+          B2_CUDA(cudaMemcpyAsync(hd, col.chars->ptr, (size_t)col.chars_len, cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+        p->buffers = {nullptr, ho, hd};
+      } else if (col.dtype == B2_BOOL) {
+        bools.emplace_back(ci, std::vector<uint8_t>((size_t)col.length));
+        if (col.length)
+          B2_CUDA(cudaMemcpyAsync(bools.back().second.data(), col.data->ptr, (size_t)col.length,
+                                  cudaMemcpyDeviceToHost, ctx->stream));
+        void* hb = host_buf(p, (size_t)(col.length + 7) / 8);
+        memset(hb, 0, (size_t)(col.length + 7) / 8);
+        p->buffers = {nullptr, hb};
+      } else {
+        size_t nb = (size_t)col.length * dtype_width(col.dtype);
+        void* hv = host_buf(p, nb);
+        if (nb) B2_CUDA(cudaMemcpyAsync(hv, col.data->ptr, nb, cudaMemcpyDeviceToHost, ctx->stream));
+        p->buffers = {nullptr, hv};
+      }
+      a->n_buffers = (int64_t)p->buffers.size();
+      a->buffers = p->buffers.data();
+    }
+    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (auto& pr : bools) {
+      auto* p = static_cast<ArrayPriv*>(top->child_store[pr.first].private_data);
+      uint8_t* bits = static_cast<uint8_t*>(const_cast<void*>(p->buffers[1]));
+      for (size_t i = 0; i < pr.second.size(); ++i)
+        if (pr.second[i]) bits[i >> 3] |= (uint8_t)(1u << (i & 7));
+    }
+  } catch (...) {
+    release_array(out);
+    throw;
+  }
+}
+
+}  // namespace b2

@@ -1,0 +1,137 @@
+// core.h — internal types of libballista_b200: context, HBM buffers, columns, batches, schemas.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/ballista_b200.h"
+
+namespace b2 {
+
+// ---- errors: thrown inside the library, converted to status codes at the C ABI ----
+struct Error : std::runtime_error {
+  int code;
+  Error(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+[[noreturn]] inline void fail(int code, const std::string& m) { throw Error(code, m); }
+
+#define B2_CUDA(expr)                                                                              \
+  do {                                                                                             \
+    cudaError_t _e = (expr);                                                                       \
+    if (_e != cudaSuccess)                                                                         \
+      ::b2::fail(_e == cudaErrorMemoryAllocation ? B2_ERR_OOM : B2_ERR_CUDA,                       \
+                 std::string(#expr) + ": " + cudaGetErrorString(_e));                              \
+  } while (0)
+
+struct Comm;  // comm.cu
+
+struct Ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;  // H2D prefetch of the next host batch
+  cudaMemPool_t pool = nullptr;
+  int64_t launches = 0;
+  Comm* comm = nullptr;
+  int rank = 0, nranks = 1;
+  int64_t bytes_sent = 0;
+  void activate() const { B2_CUDA(cudaSetDevice(device)); }
+};
+
+// count + check a kernel launch
+#define B2_LAUNCHED(ctx)                      \
+  do {                                        \
+    (ctx)->launches++;                        \
+    B2_CUDA(cudaGetLastError());              \
+  } while (0)
+
+// stream-ordered HBM allocation
+struct DevBuf {
+  Ctx* ctx;
+  void* ptr = nullptr;
+  size_t bytes = 0;
+  DevBuf(Ctx* c, size_t n);
+  ~DevBuf();
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  template <class T> T* as() const { return reinterpret_cast<T*>(ptr); }
+};
+using BufPtr = std::shared_ptr<DevBuf>;
+BufPtr dev_alloc(Ctx* ctx, size_t bytes);
+BufPtr dev_alloc_zero(Ctx* ctx, size_t bytes);
+
+inline size_t dtype_width(int dt) {
+  switch (dt) {
+    case B2_BOOL: case B2_UINT8: return 1;  // device BOOL columns are one byte per row
+    case B2_INT32: case B2_DATE32: return 4;
+    case B2_INT64: case B2_UINT64: case B2_FLOAT64: return 8;
+    default: return 0;
+  }
+}
+const char* dtype_name(int dt);
+
+struct Field {
+  std::string name;
+  int dtype = 0;
+  bool nullable = false;
+};
+struct Schema {
+  std::vector<Field> fields;
+  int index_of(const std::string& name) const {
+    for (size_t i = 0; i < fields.size(); ++i)
+      if (fields[i].name == name) return (int)i;
+    return -1;
+  }
+};
+
+// One column resident in HBM.  Fixed width: `data` = values.  Utf8: `data` = int32 offsets[length+1]
+// (starting at 0), `chars` = bytes.  All columns are non-null (TPC-H schema, main.rs:267-360); batches
+// with nulls are rejected at import.
+struct Column {
+  int dtype = 0;
+  int64_t length = 0;
+  BufPtr data;
+  BufPtr chars;
+  int64_t chars_len = 0;
+  template <class T> const T* values() const { return data ? data->as<T>() : nullptr; }
+  int64_t num_bytes() const {
+    if (dtype == B2_UTF8) return (length + 1) * 4 + chars_len;
+    return length * (int64_t)dtype_width(dtype);
+  }
+};
+
+struct Batch {
+  Ctx* ctx = nullptr;
+  Schema schema;
+  std::vector<Column> cols;
+  int64_t num_rows = 0;
+  int64_t num_bytes() const {
+    int64_t b = 0;
+    for (auto& c : cols) b += c.num_bytes();
+    return b;
+  }
+};
+using BatchPtr = std::shared_ptr<Batch>;
+
+// Arrow C Data import / export (core.cu)
+Schema schema_from_arrow(const ArrowSchema* s);
+void schema_to_arrow(const Schema& s, ArrowSchema* out);
+// host Arrow struct array -> HBM (async on ctx->stream unless `stream` given); releases `arr`
+BatchPtr batch_from_arrow(Ctx* ctx, const Schema& schema, ArrowArray* arr, cudaStream_t stream = nullptr);
+void batch_to_arrow(const Batch& b, ArrowArray* out);
+
+inline int grid_for(const Ctx* ctx, int ctas_per_sm, int64_t work_items, int per_cta) {
+  int64_t need = (work_items + per_cta - 1) / per_cta;
+  int64_t cap = (int64_t)ctx->sm_count * ctas_per_sm;
+  if (need < 1) need = 1;
+  return (int)(need < cap ? need : cap);
+}
+
+}  // namespace b2
+
+// opaque C handles
+struct b2_ctx { b2::Ctx c; };
+struct b2_batch { b2::BatchPtr b; };

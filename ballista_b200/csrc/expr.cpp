@@ -1,0 +1,344 @@
+// expr.cpp — decode / type / coerce / fold / canonicalise expressions.
+#include "expr.h"
+
+#include <cstdio>
+#include <cstring>
+
+namespace b2 {
+
+static bool is_int(int dt) { return dt == B2_INT32 || dt == B2_INT64 || dt == B2_UINT64 || dt == B2_UINT8; }
+static bool is_num(int dt) { return is_int(dt) || dt == B2_FLOAT64; }
+static int num_rank(int dt) {
+  switch (dt) {
+    case B2_UINT8: return 1;
+    case B2_INT32: return 2;
+    case B2_INT64: return 3;
+    case B2_UINT64: return 3;
+    case B2_FLOAT64: return 4;
+  }
+  return 0;
+}
+
+int32_t parse_date32(const std::string& s) {
+  int y, m, d;
+  if (sscanf(s.c_str(), "%d-%d-%d", &y, &m, &d) != 3)
+    fail(B2_ERR_EXECUTION, "cannot cast '" + s + "' to Date32");
+  // days from civil (proleptic Gregorian)
+  y -= m <= 2;
+  int era = (y >= 0 ? y : y - 399) / 400;
+  unsigned yoe = (unsigned)(y - era * 400);
+  unsigned doy = (153 * (m + (m > 2 ? -3 : 9)) + 2) / 5 + d - 1;
+  unsigned doe = yoe * 365 + yoe / 4 - yoe / 100 + doy;
+  return era * 146097 + (int)doe - 719468;
+}
+
+static ExprPtr mk_lit_i(int dt, int64_t v) {
+  auto e = std::make_shared<Expr>();
+  e->kind = B2_EXPR_LITERAL;
+  e->dtype = dt;
+  e->i = v;
+  e->f = (double)v;
+  return e;
+}
+static ExprPtr mk_lit_f(double v) {
+  auto e = std::make_shared<Expr>();
+  e->kind = B2_EXPR_LITERAL;
+  e->dtype = B2_FLOAT64;
+  e->f = v;
+  return e;
+}
+
+static ExprPtr make_cast(ExprPtr c, int target) {
+  if (c->dtype == target) return c;
+  if (c->is_literal()) {
+    if (c->dtype == B2_UTF8 && target == B2_DATE32) return mk_lit_i(B2_DATE32, parse_date32(c->s));
+    if (is_int(c->dtype) && target == B2_FLOAT64) return mk_lit_f((double)c->i);
+    if (is_int(c->dtype) && (is_int(target) || target == B2_DATE32)) return mk_lit_i(target, c->i);
+    if (c->dtype == B2_DATE32 && is_int(target)) return mk_lit_i(target, c->i);
+    if (c->dtype == B2_FLOAT64 && is_int(target)) return mk_lit_i(target, (int64_t)c->f);
+    fail(B2_ERR_NOT_IMPLEMENTED,
+         std::string("CAST of ") + dtype_name(c->dtype) + " literal to " + dtype_name(target));
+  }
+  bool ok = (c->dtype == B2_INT32 && (target == B2_INT64 || target == B2_FLOAT64)) ||
+            (c->dtype == B2_INT64 && target == B2_FLOAT64) || (c->dtype == B2_DATE32 && target == B2_INT32) ||
+            (c->dtype == B2_INT32 && target == B2_DATE32) || (c->dtype == B2_UINT8 && target == B2_INT64);
+  if (!ok)
+    fail(B2_ERR_NOT_IMPLEMENTED, std::string("CAST ") + dtype_name(c->dtype) + " -> " + dtype_name(target));
+  auto e = std::make_shared<Expr>();
+  e->kind = B2_EXPR_CAST;
+  e->dtype = target;
+  e->ch = {c};
+  return e;
+}
+
+static ExprPtr make_binary(int op, ExprPtr a, ExprPtr b);
+
+static ExprPtr fold_binary(int op, const ExprPtr& a, const ExprPtr& b, int t) {
+  // both literals of common type t
+  bool cmp = op >= B2_OP_EQ && op <= B2_OP_GTEQ;
+  if (t == B2_FLOAT64) {
+    double x = a->f, y = b->f;
+    switch (op) {
+      case B2_OP_PLUS: return mk_lit_f(x + y);
+      case B2_OP_MINUS: return mk_lit_f(x - y);
+      case B2_OP_MULTIPLY: return mk_lit_f(x * y);
+      case B2_OP_DIVIDE: return mk_lit_f(x / y);
+      case B2_OP_EQ: return mk_lit_i(B2_BOOL, x == y);
+      case B2_OP_NOTEQ: return mk_lit_i(B2_BOOL, x != y);
+      case B2_OP_LT: return mk_lit_i(B2_BOOL, x < y);
+      case B2_OP_LTEQ: return mk_lit_i(B2_BOOL, x <= y);
+      case B2_OP_GT: return mk_lit_i(B2_BOOL, x > y);
+      case B2_OP_GTEQ: return mk_lit_i(B2_BOOL, x >= y);
+    }
+  } else if (t == B2_UTF8) {
+    int c = a->s.compare(b->s);
+    switch (op) {
+      case B2_OP_EQ: return mk_lit_i(B2_BOOL, c == 0);
+      case B2_OP_NOTEQ: return mk_lit_i(B2_BOOL, c != 0);
+    }
+  } else if (t == B2_BOOL) {
+    switch (op) {
+      case B2_OP_AND: return mk_lit_i(B2_BOOL, a->i && b->i);
+      case B2_OP_OR: return mk_lit_i(B2_BOOL, a->i || b->i);
+    }
+  } else {
+    int64_t x = a->i, y = b->i;
+    switch (op) {
+      case B2_OP_PLUS: return mk_lit_i(t, (int64_t)((uint64_t)x + (uint64_t)y));
+      case B2_OP_MINUS: return mk_lit_i(t, (int64_t)((uint64_t)x - (uint64_t)y));
+      case B2_OP_MULTIPLY: return mk_lit_i(t, (int64_t)((uint64_t)x * (uint64_t)y));
+      case B2_OP_DIVIDE:
+        if (y == 0) fail(B2_ERR_EXECUTION, "Divide by zero");
+        return mk_lit_i(t, x / y);
+      case B2_OP_EQ: return mk_lit_i(B2_BOOL, x == y);
+      case B2_OP_NOTEQ: return mk_lit_i(B2_BOOL, x != y);
+      case B2_OP_LT: return mk_lit_i(B2_BOOL, x < y);
+      case B2_OP_LTEQ: return mk_lit_i(B2_BOOL, x <= y);
+      case B2_OP_GT: return mk_lit_i(B2_BOOL, x > y);
+      case B2_OP_GTEQ: return mk_lit_i(B2_BOOL, x >= y);
+    }
+  }
+  (void)cmp;
+  return nullptr;
+}
+
+static ExprPtr make_binary(int op, ExprPtr a, ExprPtr b) {
+  auto e = std::make_shared<Expr>();
+  e->kind = B2_EXPR_BINARY;
+  e->op = op;
+  bool logical = op == B2_OP_AND || op == B2_OP_OR;
+  bool cmp = op >= B2_OP_EQ && op <= B2_OP_GTEQ;
+  bool arith = op >= B2_OP_PLUS && op <= B2_OP_DIVIDE;
+  int t = 0;
+  if (logical) {
+    if (a->dtype != B2_BOOL || b->dtype != B2_BOOL)
+      fail(B2_ERR_EXECUTION, "AND/OR need Boolean operands");
+    t = B2_BOOL;
+    e->dtype = B2_BOOL;
+  } else if (cmp || arith) {
+    if (is_num(a->dtype) && is_num(b->dtype)) {
+      t = num_rank(a->dtype) >= num_rank(b->dtype) ? a->dtype : b->dtype;
+      if (t == B2_UINT8) t = B2_INT64;
+      // an integer literal against an Int32 column stays Int32 when it fits (the reference coerces the
+      // literal's side with a CAST; the comparison result is identical)
+      if (t == B2_INT64) {
+        const ExprPtr& lit = a->is_literal() ? a : b;
+        const ExprPtr& other = a->is_literal() ? b : a;
+        if (lit->is_literal() && !other->is_literal() && other->dtype == B2_INT32 && cmp &&
+            lit->i >= INT32_MIN && lit->i <= INT32_MAX)
+          t = B2_INT32;
+      }
+    } else if (a->dtype == B2_DATE32 || b->dtype == B2_DATE32) {
+      if (arith) fail(B2_ERR_NOT_IMPLEMENTED, "arithmetic on Date32");
+      t = B2_DATE32;
+    } else if (a->dtype == B2_UTF8 && b->dtype == B2_UTF8) {
+      if (!(op == B2_OP_EQ || op == B2_OP_NOTEQ))
+        fail(B2_ERR_NOT_IMPLEMENTED, "only = and <> are implemented on Utf8");
+      t = B2_UTF8;
+    } else if (a->dtype == B2_BOOL && b->dtype == B2_BOOL && (op == B2_OP_EQ || op == B2_OP_NOTEQ)) {
+      fail(B2_ERR_NOT_IMPLEMENTED, "Boolean equality");
+    } else {
+      fail(B2_ERR_EXECUTION, std::string("cannot coerce ") + dtype_name(a->dtype) + " and " +
+                                 dtype_name(b->dtype) + " for a binary operator");
+    }
+    a = make_cast(a, t);
+    b = make_cast(b, t);
+    e->dtype = cmp ? B2_BOOL : t;
+  } else {
+    fail(B2_ERR_NOT_IMPLEMENTED, "binary operator " + std::to_string(op) + " (LIKE etc.)");
+  }
+  if (a->is_literal() && b->is_literal()) {
+    if (auto f = fold_binary(op, a, b, t)) return f;
+  }
+  e->ch = {a, b};
+  return e;
+}
+
+static ExprPtr make_not(ExprPtr c) {
+  if (c->dtype != B2_BOOL) fail(B2_ERR_EXECUTION, "NOT needs a Boolean operand");
+  if (c->is_literal()) return mk_lit_i(B2_BOOL, !c->i);
+  auto e = std::make_shared<Expr>();
+  e->kind = B2_EXPR_NOT;
+  e->dtype = B2_BOOL;
+  e->ch = {c};
+  return e;
+}
+
+ExprPtr decode_expr(const b2_expr* ex, const Schema& input) {
+  if (!ex || !ex->nodes || ex->n_nodes <= 0) fail(B2_ERR_INVALID_ARG, "empty expression");
+  std::vector<ExprPtr> st;
+  auto pop = [&]() {
+    if (st.empty()) fail(B2_ERR_INVALID_ARG, "malformed expression (stack underflow)");
+    ExprPtr e = st.back();
+    st.pop_back();
+    return e;
+  };
+  for (int k = 0; k < ex->n_nodes; ++k) {
+    const b2_expr_node& n = ex->nodes[k];
+    switch (n.kind) {
+      case B2_EXPR_COLUMN: {
+        if (n.col < 0 || n.col >= (int)input.fields.size())
+          fail(B2_ERR_INVALID_ARG, "column index " + std::to_string(n.col) + " out of range");
+        auto e = std::make_shared<Expr>();
+        e->kind = B2_EXPR_COLUMN;
+        e->col = n.col;
+        e->dtype = input.fields[n.col].dtype;
+        st.push_back(e);
+        break;
+      }
+      case B2_EXPR_LITERAL: {
+        auto e = std::make_shared<Expr>();
+        e->kind = B2_EXPR_LITERAL;
+        e->dtype = n.dtype;
+        switch (n.dtype) {
+          case B2_FLOAT64: e->f = n.f; break;
+          case B2_UTF8: e->s = n.s ? n.s : ""; break;
+          case B2_INT32: case B2_INT64: case B2_UINT64: case B2_DATE32: case B2_BOOL: case B2_UINT8:
+            e->i = n.i;
+            e->f = (double)n.i;
+            break;
+          default: fail(B2_ERR_NOT_IMPLEMENTED, "literal type " + std::to_string(n.dtype));
+        }
+        st.push_back(e);
+        break;
+      }
+      case B2_EXPR_BINARY: {
+        ExprPtr b = pop(), a = pop();
+        st.push_back(make_binary(n.op, a, b));
+        break;
+      }
+      case B2_EXPR_NOT: st.push_back(make_not(pop())); break;
+      case B2_EXPR_IS_NULL: pop(); st.push_back(mk_lit_i(B2_BOOL, 0)); break;      // inputs are non-null
+      case B2_EXPR_IS_NOT_NULL: pop(); st.push_back(mk_lit_i(B2_BOOL, 1)); break;
+      case B2_EXPR_CAST: st.push_back(make_cast(pop(), n.dtype)); break;
+      case B2_EXPR_NEGATIVE: {
+        ExprPtr c = pop();
+        if (!is_num(c->dtype)) fail(B2_ERR_EXECUTION, "negation of a non-numeric value");
+        if (c->is_literal()) {
+          st.push_back(c->dtype == B2_FLOAT64 ? mk_lit_f(-c->f) : mk_lit_i(c->dtype, -c->i));
+        } else {
+          auto e = std::make_shared<Expr>();
+          e->kind = B2_EXPR_NEGATIVE;
+          e->dtype = c->dtype;
+          e->ch = {c};
+          st.push_back(e);
+        }
+        break;
+      }
+      case B2_EXPR_BETWEEN: {  // x BETWEEN lo AND hi  ==  x >= lo AND x <= hi   
+        ExprPtr hi = pop(), lo = pop(), x = pop();
+        ExprPtr r = make_binary(B2_OP_AND, make_binary(B2_OP_GTEQ, x, lo), make_binary(B2_OP_LTEQ, x, hi));
+        st.push_back(n.op ? make_not(r) : r);
+        break;
+      }
+      case B2_EXPR_IN_LIST: {
+        int nl = n.nchildren - 1;
+        if (nl < 1 || (int)st.size() < n.nchildren) fail(B2_ERR_INVALID_ARG, "malformed IN list");
+        std::vector<ExprPtr> items(nl);
+        for (int q = nl - 1; q >= 0; --q) items[q] = pop();
+        ExprPtr x = pop();
+        ExprPtr r = make_binary(B2_OP_EQ, x, items[0]);
+        for (int q = 1; q < nl; ++q) r = make_binary(B2_OP_OR, r, make_binary(B2_OP_EQ, x, items[q]));
+        st.push_back(n.op ? make_not(r) : r);
+        break;
+      }
+      case B2_EXPR_CASE: fail(B2_ERR_NOT_IMPLEMENTED, "CASE expressions");
+      default: fail(B2_ERR_INVALID_ARG, "unknown expression node kind " + std::to_string(n.kind));
+    }
+  }
+  if (st.size() != 1) fail(B2_ERR_INVALID_ARG, "malformed expression (unbalanced)");
+  ExprPtr top = st[0];
+  if (ex->name) top->name = ex->name;
+  return top;
+}
+
+static const char* op_text(int op) {
+  switch (op) {
+    case B2_OP_AND: return "and";
+    case B2_OP_OR: return "or";
+    case B2_OP_EQ: return "eq";
+    case B2_OP_NOTEQ: return "ne";
+    case B2_OP_LTEQ: return "le";
+    case B2_OP_LT: return "lt";
+    case B2_OP_GT: return "gt";
+    case B2_OP_GTEQ: return "ge";
+    case B2_OP_PLUS: return "add";
+    case B2_OP_MINUS: return "sub";
+    case B2_OP_MULTIPLY: return "mul";
+    case B2_OP_DIVIDE: return "div";
+  }
+  return "?";
+}
+
+std::string expr_to_string(const ExprPtr& e, const Schema& input) {
+  char buf[64];
+  switch (e->kind) {
+    case B2_EXPR_COLUMN: return input.fields[e->col].name;
+    case B2_EXPR_LITERAL:
+      if (e->dtype == B2_FLOAT64) { snprintf(buf, sizeof buf, "%.17g", e->f); return buf; }
+      if (e->dtype == B2_UTF8) return "'" + e->s + "'";
+      return std::to_string(e->i);
+    case B2_EXPR_BINARY:
+      return std::string(op_text(e->op)) + "(" + expr_to_string(e->ch[0], input) + "," +
+             expr_to_string(e->ch[1], input) + ")";
+    case B2_EXPR_NOT: return "not(" + expr_to_string(e->ch[0], input) + ")";
+    case B2_EXPR_CAST: return std::string("cast_") + dtype_name(e->dtype) + "(" + expr_to_string(e->ch[0], input) + ")";
+    case B2_EXPR_NEGATIVE: return "neg(" + expr_to_string(e->ch[0], input) + ")";
+  }
+  return "?";
+}
+
+// Signature grammar (must match the sig() of the device expression templates in fused.cuh):
+//   f<k> i<k> s<k>        column slots (Float64 / Int32|Date32 / Utf8)
+//   LF<k> LI<k> LS<k>     literal slots
+//   op(a,b)               binary; and/or chains are kept as nested binaries in source order
+//   not(a) neg(a) f64(a)  unary (f64 = cast of an int slot to Float64)
+std::string expr_signature(const ExprPtr& e, SlotBinder& b) {
+  switch (e->kind) {
+    case B2_EXPR_COLUMN:
+      if (e->dtype == B2_FLOAT64) return "f" + std::to_string(b.slot_for(b.f64_cols, e->col));
+      if (e->dtype == B2_INT32 || e->dtype == B2_DATE32) return "i" + std::to_string(b.slot_for(b.i32_cols, e->col));
+      if (e->dtype == B2_UTF8) return "s" + std::to_string(b.slot_for(b.str_cols, e->col));
+      return "x" + std::to_string(e->dtype);  // no fused support
+    case B2_EXPR_LITERAL:
+      if (e->dtype == B2_FLOAT64) { b.f64_lits.push_back(e->f); return "LF" + std::to_string(b.f64_lits.size() - 1); }
+      if (e->dtype == B2_UTF8) { b.str_lits.push_back(e->s); return "LS" + std::to_string(b.str_lits.size() - 1); }
+      b.i64_lits.push_back(e->i);
+      return "LI" + std::to_string(b.i64_lits.size() - 1);
+    case B2_EXPR_BINARY:
+      {
+        std::string l = expr_signature(e->ch[0], b);
+        std::string r = expr_signature(e->ch[1], b);
+        return std::string(op_text(e->op)) + "(" + l + "," + r + ")";
+      }
+    case B2_EXPR_NOT: return "not(" + expr_signature(e->ch[0], b) + ")";
+    case B2_EXPR_NEGATIVE: return "neg(" + expr_signature(e->ch[0], b) + ")";
+    case B2_EXPR_CAST:
+      if (e->dtype == B2_FLOAT64) return "f64(" + expr_signature(e->ch[0], b) + ")";
+      if (e->dtype == B2_INT32 || e->dtype == B2_DATE32) return expr_signature(e->ch[0], b);  // reinterpret
+      return "cast" + std::to_string(e->dtype) + "(" + expr_signature(e->ch[0], b) + ")";
+  }
+  return "?";
+}
+
+}  // namespace b2

@@ -1,0 +1,312 @@
+// agg.cu — group table management, kernel registry, strategy runner and emit kernels for
+// HashAggregateExec (constructed at rust/core/src/serde/physical_plan/from_proto.rs:173-252).
+#include "agg.h"
+
+#include <cstring>
+
+#include "agg_kernels.cuh"
+
+namespace b2 {
+
+// ------------------------------------------------------------------------------------------------------
+// key layout
+// ------------------------------------------------------------------------------------------------------
+KeyLayout make_key_layout(const std::vector<int>& dtypes) {
+  int int_bytes = 0, n_str = 0;
+  for (int dt : dtypes) {
+    if (dt == B2_INT32 || dt == B2_DATE32) int_bytes += 4;
+    else if (dt == B2_INT64) int_bytes += 8;
+    else if (dt == B2_UTF8) n_str++;
+    else fail(B2_ERR_NOT_IMPLEMENTED, std::string("group/join key of type ") + dtype_name(dt));
+  }
+  int sb = 0;
+  if (n_str) {
+    sb = (15 - int_bytes) / n_str;
+    if (sb > 15) sb = 15;
+    if (sb < 2) fail(B2_ERR_NOT_IMPLEMENTED, "key wider than 15 packed bytes");
+  }
+  if (int_bytes > 15) fail(B2_ERR_NOT_IMPLEMENTED, "key wider than 15 packed bytes");
+  KeyLayout l;
+  int off = 0;
+  for (int dt : dtypes) {
+    int b = dt == B2_UTF8 ? sb : (dt == B2_INT64 ? 8 : 4);
+    l.parts.push_back(KeyPart{dt, off, b});
+    off += b;
+  }
+  return l;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// group table
+// ------------------------------------------------------------------------------------------------------
+std::shared_ptr<GroupTable> make_group_table(Ctx* ctx, u64 cap, int na, int nc) {
+  auto t = std::make_shared<GroupTable>();
+  t->ctx = ctx;
+  t->cap = cap;
+  t->na = na;
+  t->nc = nc;
+  t->keys = dev_alloc(ctx, cap * sizeof(Key128));
+  t->acc = dev_alloc(ctx, cap * sizeof(double) * (size_t)(na ? na : 1));
+  t->cnt = dev_alloc(ctx, cap * sizeof(u64) * (size_t)(nc ? nc : 1));
+  t->n_groups = dev_alloc(ctx, 16);
+  reset_group_table(*t);
+  return t;
+}
+void reset_group_table(GroupTable& t) {
+  B2_CUDA(cudaMemsetAsync(t.keys->ptr, 0xFF, t.keys->bytes, t.ctx->stream));
+  B2_CUDA(cudaMemsetAsync(t.acc->ptr, 0, t.acc->bytes, t.ctx->stream));
+  B2_CUDA(cudaMemsetAsync(t.cnt->ptr, 0, t.cnt->bytes, t.ctx->stream));
+  B2_CUDA(cudaMemsetAsync(t.n_groups->ptr, 0, 16, t.ctx->stream));
+}
+
+__global__ void table_merge_kernel(TableRef src, TableRef dst, int na, int nc, int* status) {
+  u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x;
+  for (; i < src.cap; i += (u64)gridDim.x * blockDim.x) {
+    Key128 k = src.keys[i];
+    if (k.lo == KEY_EMPTY && k.hi == KEY_EMPTY) continue;
+    u64 slot = table_upsert(dst, k);
+    if (slot == ~0ull) {
+      atomicExch(status, AGG_TABLE_FULL);
+      continue;
+    }
+    for (int a = 0; a < na; ++a) red_add_f64(&dst.acc[(u64)a * dst.cap + slot], src.acc[(u64)a * src.cap + i]);
+    for (int a = 0; a < nc; ++a) red_add_u64(&dst.cnt[(u64)a * dst.cap + slot], src.cnt[(u64)a * src.cap + i]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// runner
+// ------------------------------------------------------------------------------------------------------
+static u64 next_pow2(u64 x) {
+  u64 p = 16;
+  while (p < x) p <<= 1;
+  return p;
+}
+constexpr u64 DELTA_CAP = 65536;
+constexpr int64_t GLOBAL_CHUNK_ROWS = 32ll << 20;  // multiple of TILE_ROWS
+
+AggRunner::AggRunner(Ctx* c, int na_, int nc_, bool keyed_) : ctx(c), na(na_), nc(nc_), keyed(keyed_) {
+  status = dev_alloc_zero(ctx, 16);
+  main = make_group_table(ctx, keyed ? 1024 : 16, na, nc);
+}
+
+void AggRunner::check_status(int st) {
+  if (st == AGG_KEY_TOO_WIDE)
+    fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 group key value is longer than the packed-key budget (15 bytes per key)");
+  if (st == AGG_TABLE_FULL) fail(B2_ERR_EXECUTION, "internal: group table full");
+}
+
+void AggRunner::ensure_main(int64_t extra) {
+  u64 need = next_pow2(2 * (u64)(group_bound + extra) + 16);
+  if (need <= main->cap) return;
+  auto bigger = make_group_table(ctx, need, na, nc);
+  table_merge_kernel<<<grid_for(ctx, 8, (int64_t)main->cap, 256), 256, 0, ctx->stream>>>(
+      main->ref(), bigger->ref(), na, nc, status->as<int>());
+  B2_LAUNCHED(ctx);
+  main = bigger;
+}
+
+void AggRunner::consume(const AggLaunch& l, int64_t n) {
+  if (n <= 0) return;
+  int host[4] = {0, 0, 0, 0};
+  if (!force_global) {
+    if (!delta) delta = make_group_table(ctx, keyed ? DELTA_CAP : 16, na, nc);
+    else reset_group_table(*delta);
+    B2_CUDA(cudaMemsetAsync(status->ptr, 0, 16, ctx->stream));
+    l.small(n, delta->ref(), status->as<int>());
+    B2_CUDA(cudaMemcpyAsync(&host[0], status->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(cudaMemcpyAsync(&host[1], delta->n_groups->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (host[0] == AGG_OK) {
+      ensure_main(host[1]);
+      table_merge_kernel<<<grid_for(ctx, 8, (int64_t)delta->cap, 256), 256, 0, ctx->stream>>>(
+          delta->ref(), main->ref(), na, nc, status->as<int>());
+      B2_LAUNCHED(ctx);
+      group_bound += host[1];
+      if (path.empty()) path = "small";
+      return;
+    }
+    if (host[0] == AGG_KEY_TOO_WIDE) check_status(host[0]);
+    // too many groups for the per-CTA tables: redo this batch (and all later ones) on the HBM table
+    force_global = true;
+    delta.reset();
+  }
+  path = "global";
+  for (int64_t b = 0; b < n; b += GLOBAL_CHUNK_ROWS) {
+    int64_t e = b + GLOBAL_CHUNK_ROWS < n ? b + GLOBAL_CHUNK_ROWS : n;
+    ensure_main(keyed ? e - b : 1);
+    B2_CUDA(cudaMemsetAsync(status->ptr, 0, 16, ctx->stream));
+    l.global(b, e, n, main->ref(), status->as<int>());
+    B2_CUDA(cudaMemcpyAsync(&host[0], status->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(cudaMemcpyAsync(&host[1], main->n_groups->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    check_status(host[0]);
+    group_bound = host[1];
+  }
+}
+
+__global__ void table_compact_kernel(const Key128* keys, u64 cap, uint32_t* slots, int* counter) {
+  u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x;
+  for (; i < cap; i += (u64)gridDim.x * blockDim.x) {
+    Key128 k = keys[i];
+    if (k.lo == KEY_EMPTY && k.hi == KEY_EMPTY) continue;
+    int pos = atomicAdd(counter, 1);
+    slots[pos] = (uint32_t)i;
+  }
+}
+
+int64_t AggRunner::finish(BufPtr* slots_out) {
+  int host[2] = {0, 0};
+  B2_CUDA(cudaMemcpyAsync(&host[0], main->n_groups->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  B2_CUDA(cudaMemcpyAsync(&host[1], status->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  B2_CUDA(cudaStreamSynchronize(ctx->stream));
+  check_status(host[1]);
+  int64_t ng = host[0];
+  if (main->cap > (1ull << 32)) fail(B2_ERR_NOT_IMPLEMENTED, "group table beyond 2^32 slots");
+  auto slots = dev_alloc(ctx, (size_t)(ng + 1) * 4);
+  auto counter = dev_alloc_zero(ctx, 16);
+  if (ng > 0) {
+    table_compact_kernel<<<grid_for(ctx, 8, (int64_t)main->cap, 256), 256, 0, ctx->stream>>>(
+        main->keys->as<Key128>(), main->cap, slots->as<uint32_t>(), counter->as<int>());
+    B2_LAUNCHED(ctx);
+  }
+  *slots_out = slots;
+  return ng;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// emit kernels
+// ------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ u128 key_bits(const Key128& k) { return ((u128)k.hi << 64) | k.lo; }
+
+__global__ void emit_key_i32_kernel(const Key128* keys, const uint32_t* slots, int64_t ng, int byte_off, int32_t* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) out[i] = (int32_t)(uint32_t)(key_bits(keys[slots[i]]) >> (8 * byte_off));
+}
+__global__ void emit_key_i64_kernel(const Key128* keys, const uint32_t* slots, int64_t ng, int byte_off, int64_t* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) out[i] = (int64_t)(u64)(key_bits(keys[slots[i]]) >> (8 * byte_off));
+}
+// Utf8 keys: one CTA scans lengths chunk by chunk (group counts with Utf8 keys are small), then writes bytes
+__global__ void emit_key_str_kernel(const Key128* keys, const uint32_t* slots, int64_t ng, int byte_off,
+                                    int32_t* off, uint8_t* chr) {
+  __shared__ int32_t warp_sums[32];
+  __shared__ int32_t carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (int64_t base = 0; base < ng; base += blockDim.x) {
+    int64_t i = base + threadIdx.x;
+    u128 bits = 0;
+    int len = 0;
+    if (i < ng) {
+      bits = key_bits(keys[slots[i]]) >> (8 * byte_off);
+      len = (int)(uint8_t)bits;
+    }
+    int v = len;
+    for (int d = 1; d < 32; d <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, v, d);
+      if (lane >= d) v += t;
+    }
+    if (lane == 31) warp_sums[warp] = v;
+    __syncthreads();
+    int woff = 0, total = 0;
+    for (int w = 0; w < nwarps; ++w) {
+      if (w < warp) woff += warp_sums[w];
+      total += warp_sums[w];
+    }
+    int carry = carry_s;
+    int excl = carry + woff + v - len;
+    if (i < ng) {
+      off[i] = excl;
+      for (int q = 0; q < len; ++q) chr[excl + q] = (uint8_t)(bits >> (8 * (q + 1)));
+      if (i == ng - 1) off[ng] = excl + len;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) carry_s = carry + total;
+    __syncthreads();
+  }
+}
+__global__ void emit_f64_kernel(const double* src, const uint32_t* slots, int64_t ng, double* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) out[i] = src[slots[i]];
+}
+__global__ void emit_u64_kernel(const u64* src, const uint32_t* slots, int64_t ng, u64* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) out[i] = src[slots[i]];
+}
+// AVG evaluate(): sum / count as f64
+__global__ void emit_avg_kernel(const double* sum, const u64* cnt, const uint32_t* slots, int64_t ng, double* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) out[i] = __ddiv_rn(sum[slots[i]], (double)cnt[slots[i]]);
+}
+
+static Column new_fixed(Ctx* ctx, int dtype, int64_t n) {
+  Column c;
+  c.dtype = dtype;
+  c.length = n;
+  c.data = dev_alloc(ctx, (size_t)n * dtype_width(dtype) + 16);
+  return c;
+}
+
+Column emit_key_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, const KeyPart& part) {
+  int grid = grid_for(ctx, 8, ng, 256);
+  const Key128* keys = t.keys->as<Key128>();
+  const uint32_t* sl = slots->as<uint32_t>();
+  if (part.dtype == B2_UTF8) {
+    Column c;
+    c.dtype = B2_UTF8;
+    c.length = ng;
+    c.data = dev_alloc_zero(ctx, (size_t)(ng + 1) * 4);
+    c.chars = dev_alloc(ctx, (size_t)ng * 15 + 16);
+    if (ng) {
+      emit_key_str_kernel<<<1, 1024, 0, ctx->stream>>>(keys, sl, ng, part.byte_off, c.data->as<int32_t>(),
+                                                      c.chars->as<uint8_t>());
+      B2_LAUNCHED(ctx);
+      int32_t total = 0;
+      B2_CUDA(cudaMemcpyAsync(&total, c.data->as<int32_t>() + ng, 4, cudaMemcpyDeviceToHost, ctx->stream));
+      B2_CUDA(cudaStreamSynchronize(ctx->stream));
+      c.chars_len = total;
+    }
+    return c;
+  }
+  Column c = new_fixed(ctx, part.dtype, ng);
+  if (ng) {
+    if (part.bytes == 8)
+      emit_key_i64_kernel<<<grid, 256, 0, ctx->stream>>>(keys, sl, ng, part.byte_off, c.data->as<int64_t>());
+    else
+      emit_key_i32_kernel<<<grid, 256, 0, ctx->stream>>>(keys, sl, ng, part.byte_off, c.data->as<int32_t>());
+    B2_LAUNCHED(ctx);
+  }
+  return c;
+}
+Column emit_sum_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int a) {
+  Column c = new_fixed(ctx, B2_FLOAT64, ng);
+  if (ng) {
+    emit_f64_kernel<<<grid_for(ctx, 8, ng, 256), 256, 0, ctx->stream>>>(t.acc->as<double>() + (u64)a * t.cap,
+                                                                       slots->as<uint32_t>(), ng, c.data->as<double>());
+    B2_LAUNCHED(ctx);
+  }
+  return c;
+}
+Column emit_count_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int a) {
+  Column c = new_fixed(ctx, B2_UINT64, ng);
+  if (ng) {
+    emit_u64_kernel<<<grid_for(ctx, 8, ng, 256), 256, 0, ctx->stream>>>(t.cnt->as<u64>() + (u64)a * t.cap,
+                                                                       slots->as<uint32_t>(), ng, c.data->as<u64>());
+    B2_LAUNCHED(ctx);
+  }
+  return c;
+}
+Column emit_avg_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int a, int cidx) {
+  Column c = new_fixed(ctx, B2_FLOAT64, ng);
+  if (ng) {
+    emit_avg_kernel<<<grid_for(ctx, 8, ng, 256), 256, 0, ctx->stream>>>(
+        t.acc->as<double>() + (u64)a * t.cap, t.cnt->as<u64>() + (u64)cidx * t.cap, slots->as<uint32_t>(), ng,
+        c.data->as<double>());
+    B2_LAUNCHED(ctx);
+  }
+  return c;
+}
+
+}  // namespace b2

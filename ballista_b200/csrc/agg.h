@@ -1,0 +1,90 @@
+// agg.h — host side of the hash aggregate: key layout, HBM group table, fused-kernel registry, runner.
+#pragma once
+#include <functional>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "core.h"
+#include "expr.h"
+#include "table.cuh"
+
+namespace b2 {
+
+// byte layout of a packed key (mirror of fx::PackKey): parts in group-expression order
+struct KeyPart {
+  int dtype;
+  int byte_off;
+  int bytes;  // Int32/Date32: 4, Int64: 8, Utf8: 1 length byte + (bytes-1) chars
+};
+struct KeyLayout {
+  std::vector<KeyPart> parts;
+};
+KeyLayout make_key_layout(const std::vector<int>& dtypes);  // throws NotImplemented when > 15 bytes
+
+struct GroupTable {
+  Ctx* ctx;
+  u64 cap;
+  int na, nc;
+  BufPtr keys, acc, cnt, n_groups;
+  TableRef ref() const {
+    return TableRef{keys->as<Key128>(), acc->as<double>(), cnt->as<u64>(), cap, n_groups->as<int>()};
+  }
+};
+std::shared_ptr<GroupTable> make_group_table(Ctx* ctx, u64 cap, int na, int nc);
+void reset_group_table(GroupTable& t);
+
+// type-erased launchers of the two aggregate kernels for one bound source
+struct AggLaunch {
+  std::function<void(int64_t n, TableRef tbl, int* status)> small;
+  std::function<void(int64_t row_begin, int64_t row_end, int64_t n, TableRef tbl, int* status)> global;
+  int na = 0, nc = 0;
+  bool keyed = false;
+};
+
+// ---- fused-kernel registry: signature text -> instantiated kernels ----
+struct FusedParams;
+struct FusedEntry {
+  std::string sig;
+  int nf, ni, ns, na;
+  bool keyed;
+  std::function<AggLaunch(Ctx*, const FusedParams&)> bind;
+};
+const std::map<std::string, FusedEntry>& fused_registry();
+
+// Try to bind a fused kernel for (predicate?, group exprs, distinct aggregate args) over `batch`.
+// Returns false when the shape is not in the registry (the caller then runs the unfused path).
+bool bind_fused_agg(Ctx* ctx, const ExprPtr& pred, const std::vector<ExprPtr>& groups,
+                    const std::vector<ExprPtr>& args, const Batch& batch, AggLaunch* out, std::string* sig);
+// Materialised source: keys (null = ungrouped), mask (null = all rows), value / count columns.
+AggLaunch bind_column_agg(Ctx* ctx, const Key128* keys, const uint8_t* mask, const std::vector<const double*>& vals,
+                          const std::vector<const u64*>& cnts, bool count_rows);
+// pack evaluated group columns into a Key128 column
+BufPtr pack_keys(Ctx* ctx, const KeyLayout& layout, const std::vector<Column>& cols, int64_t n, int* status_dev);
+
+// Strategy state of one HashAggregateExec execution (one partition)
+struct AggRunner {
+  Ctx* ctx;
+  int na, nc;
+  bool keyed;
+  std::shared_ptr<GroupTable> main, delta;
+  BufPtr status;  // int[2]: status, spare
+  bool force_global = false;
+  int64_t group_bound = 0;  // upper bound on groups in `main`
+  std::string path;         // diagnostics
+  AggRunner(Ctx* c, int na_, int nc_, bool keyed_);
+  void consume(const AggLaunch& l, int64_t n);
+  // compact occupied slots; returns number of groups and the slot index list
+  int64_t finish(BufPtr* slots);
+ private:
+  void ensure_main(int64_t extra_groups);
+  void check_status(int st);
+};
+
+// emit kernels (agg.cu): gather table contents into output columns
+Column emit_key_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, const KeyPart& part);
+Column emit_sum_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int acc_idx);
+Column emit_count_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int cnt_idx);
+Column emit_avg_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int acc_idx, int cnt_idx);
+
+}  // namespace b2

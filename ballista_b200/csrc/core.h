@@ -38,6 +38,20 @@ struct Ctx {
   Comm* comm = nullptr;
   int rank = 0, nranks = 1;
   int64_t bytes_sent = 0;
+  // optional per-launch timing of the dominant (aggregate scan) kernel with CUDA events on `stream`
+  bool profiling = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+  void prof_begin() {
+    if (!profiling) return;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    cudaEventRecord(a, stream);
+    prof_events.emplace_back(a, b);
+  }
+  void prof_end() {
+    if (profiling && !prof_events.empty()) cudaEventRecord(prof_events.back().second, stream);
+  }
   void activate() const { B2_CUDA(cudaSetDevice(device)); }
 };
 

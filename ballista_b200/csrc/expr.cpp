@@ -326,6 +326,25 @@ std::string expr_signature(const ExprPtr& e, SlotBinder& b) {
       b.i64_lits.push_back(e->i);
       return "LI" + std::to_string(b.i64_lits.size() - 1);
     case B2_EXPR_BINARY:
+      if (e->op == B2_OP_AND) {
+        // conjunctions are flattened and re-nested left-associatively so that every association of the
+        // same conjunct sequence maps to one kernel shape
+        std::vector<ExprPtr> leaves;
+        std::vector<ExprPtr> work{e};
+        while (!work.empty()) {
+          ExprPtr x = work.back();
+          work.pop_back();
+          if (x->kind == B2_EXPR_BINARY && x->op == B2_OP_AND) {
+            work.push_back(x->ch[1]);
+            work.push_back(x->ch[0]);
+          } else {
+            leaves.push_back(x);
+          }
+        }
+        std::string acc = expr_signature(leaves[0], b);
+        for (size_t q = 1; q < leaves.size(); ++q) acc = "and(" + acc + "," + expr_signature(leaves[q], b) + ")";
+        return acc;
+      }
       {
         std::string l = expr_signature(e->ch[0], b);
         std::string r = expr_signature(e->ch[1], b);

@@ -1,0 +1,99 @@
+// ops.h — physical operators (the ExecutionPlan trait objects behind b2_op) and the helper entry points
+// of the kernel files.
+#pragma once
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "agg.h"
+#include "core.h"
+#include "expr.h"
+
+namespace b2 {
+
+// ---- kernel-file helpers ----
+BufPtr mask_to_indices(Ctx* ctx, const uint8_t* mask, int64_t n, int64_t* count);        // take.cu
+Column take_column(Ctx* ctx, const Column& c, const uint32_t* idx, int64_t m);            // take.cu
+BatchPtr take_batch(Ctx* ctx, const Batch& b, const uint32_t* idx, int64_t m);            // take.cu
+BatchPtr concat_batches(Ctx* ctx, const Schema& schema, const std::vector<BatchPtr>& b);  // take.cu
+BatchPtr empty_batch(Ctx* ctx, const Schema& schema);                                      // take.cu
+BatchPtr slice_batch(Ctx* ctx, const Batch& b, int64_t begin, int64_t end);               // repartition.cu
+BatchPtr tpch_generate(Ctx* ctx, const std::string& table, double sf, int64_t row_begin, int64_t row_end,
+                       const char* const* columns);                                       // tpch_gen.cu
+int64_t tpch_num_rows(const std::string& table, double sf);
+
+// join.cu
+struct JoinTable {
+  Ctx* ctx;
+  u64 cap = 0;
+  int64_t n_build = 0;
+  BufPtr keys, head, count, next;
+};
+std::shared_ptr<JoinTable> join_build(Ctx* ctx, const Key128* keys, int64_t n);
+// probe: returns number of output pairs; left_idx / right_idx are uint32 row indices in probe order
+int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* probe_keys, int64_t n_probe, BufPtr* left_idx,
+                   BufPtr* right_idx);
+
+// repartition.cu: rows -> destination partition by hash of packed key; returns the stable permutation
+// (destination-major) and fills counts[n_out]
+BufPtr hash_partition_indices(Ctx* ctx, const Key128* keys, int64_t n, int n_out, std::vector<int64_t>* counts);
+
+// comm.cu
+void comm_unique_id(void* id128);
+void comm_init(Ctx* ctx, int rank, int nranks, const void* id128);
+void comm_destroy(Ctx* ctx);
+BatchPtr comm_allgather_batch(Ctx* ctx, const Batch& local);
+// all-to-all of a destination-major permuted batch: slice d (counts[d] rows) goes to rank d
+BatchPtr comm_all_to_all(Ctx* ctx, const Batch& permuted, const std::vector<int64_t>& counts);
+
+// ---- RecordBatchStream ----
+struct Stream {
+  virtual ~Stream() {}
+  virtual BatchPtr next() = 0;  // nullptr at end of stream
+};
+using StreamPtr = std::unique_ptr<Stream>;
+
+// ---- ExecutionPlan ----
+struct Op {
+  Ctx* ctx = nullptr;
+  std::vector<std::shared_ptr<Op>> children;
+  std::string last_path = "unexecuted";
+  virtual ~Op() {}
+  virtual const char* name() const = 0;
+  virtual Schema schema() const = 0;
+  virtual void partitioning(int* scheme, int* n) const {
+    children[0]->partitioning(scheme, n);
+  }
+  virtual StreamPtr execute(int partition) = 0;
+  int n_partitions() const {
+    int s, n;
+    partitioning(&s, &n);
+    return n;
+  }
+};
+using OpPtr = std::shared_ptr<Op>;
+
+struct AggSpec {
+  int fn;
+  ExprPtr arg;
+  std::string name;
+};
+
+OpPtr make_memory_exec(Ctx* ctx, const Schema& schema, int n_partitions);
+void memory_exec_add_host(Op* op, int partition, ArrowArray* batch);
+void memory_exec_add_device(Op* op, int partition, BatchPtr batch);
+void memory_exec_clear(Op* op);
+OpPtr make_filter(Ctx* ctx, OpPtr input, ExprPtr pred);
+OpPtr make_coalesce(Ctx* ctx, OpPtr input, int64_t target);
+OpPtr make_merge(Ctx* ctx, OpPtr input);
+OpPtr make_projection(Ctx* ctx, OpPtr input, std::vector<ExprPtr> exprs);
+OpPtr make_hash_aggregate(Ctx* ctx, OpPtr input, int mode, std::vector<ExprPtr> groups, std::vector<AggSpec> aggs,
+                          const Schema* input_schema);
+OpPtr make_hash_join(Ctx* ctx, OpPtr left, OpPtr right, std::vector<std::string> on_left,
+                     std::vector<std::string> on_right, int join_type);
+OpPtr make_repartition(Ctx* ctx, OpPtr input, int scheme, std::vector<ExprPtr> keys, int n_out);
+
+}  // namespace b2
+
+struct b2_op { b2::OpPtr op; };
+struct b2_stream { b2::StreamPtr s; };

@@ -1,0 +1,274 @@
+// ops_basic.cu — MemoryExec (leaf), FilterExec, CoalesceBatchesExec, MergeExec, ProjectionExec.
+// Constructed where rust/core/src/serde/physical_plan/from_proto.rs:58-132 constructs the DataFusion ones.
+#include "ops.h"
+
+namespace b2 {
+
+// ------------------------------------------------------------------------------------------------------
+// MemoryExec: partitions of host (Arrow) and/or HBM-resident batches
+// ------------------------------------------------------------------------------------------------------
+struct MemItem {
+  BatchPtr dev;            // HBM-resident, or
+  ArrowArray host;         // owned host RecordBatch (release != null)
+  bool is_host = false;
+};
+struct MemoryExec : Op {
+  Schema sch;
+  std::vector<std::vector<std::shared_ptr<MemItem>>> parts;
+  ~MemoryExec() override { clear(); }
+  void clear() {
+    for (auto& p : parts) {
+      for (auto& it : p)
+        if (it->is_host && it->host.release) it->host.release(&it->host);
+      p.clear();
+    }
+  }
+  const char* name() const override { return "MemoryExec"; }
+  Schema schema() const override { return sch; }
+  void partitioning(int* scheme, int* n) const override {
+    *scheme = B2_PART_UNKNOWN;
+    *n = (int)parts.size();
+  }
+  struct S : Stream {
+    MemoryExec* op;
+    int part;
+    size_t pos = 0;
+    BatchPtr next() override {
+      auto& v = op->parts[part];
+      if (pos >= v.size()) return nullptr;
+      auto& it = v[pos++];
+      if (!it->is_host) return it->dev;
+      // host RecordBatch: copy host -> HBM (the ArrowArray stays owned by the MemoryExec)
+      ArrowArray view = it->host;
+      view.release = nullptr;
+      return batch_from_arrow(op->ctx, op->sch, &view);
+    }
+  };
+  StreamPtr execute(int partition) override {
+    if (partition < 0 || partition >= (int)parts.size())
+      fail(B2_ERR_INVALID_ARG, "MemoryExec: partition " + std::to_string(partition) + " out of range");
+    auto s = std::make_unique<S>();
+    s->op = this;
+    s->part = partition;
+    last_path = "source";
+    return s;
+  }
+};
+
+OpPtr make_memory_exec(Ctx* ctx, const Schema& schema, int n_partitions) {
+  if (n_partitions < 1) fail(B2_ERR_INVALID_ARG, "MemoryExec needs at least one partition");
+  auto op = std::make_shared<MemoryExec>();
+  op->ctx = ctx;
+  op->sch = schema;
+  op->parts.resize(n_partitions);
+  return op;
+}
+static MemoryExec* as_mem(Op* op) {
+  auto* m = dynamic_cast<MemoryExec*>(op);
+  if (!m) fail(B2_ERR_INVALID_ARG, "operator is not a MemoryExec");
+  return m;
+}
+void memory_exec_add_host(Op* op, int partition, ArrowArray* batch) {
+  auto* m = as_mem(op);
+  if (partition < 0 || partition >= (int)m->parts.size()) fail(B2_ERR_INVALID_ARG, "partition out of range");
+  if ((size_t)batch->n_children != m->sch.fields.size()) fail(B2_ERR_ARROW, "batch does not match the schema");
+  auto it = std::make_shared<MemItem>();
+  it->is_host = true;
+  it->host = *batch;        // move
+  batch->release = nullptr;
+  m->parts[partition].push_back(it);
+}
+void memory_exec_add_device(Op* op, int partition, BatchPtr batch) {
+  auto* m = as_mem(op);
+  if (partition < 0 || partition >= (int)m->parts.size()) fail(B2_ERR_INVALID_ARG, "partition out of range");
+  if (batch->cols.size() != m->sch.fields.size()) fail(B2_ERR_ARROW, "batch does not match the schema");
+  for (size_t i = 0; i < batch->cols.size(); ++i)
+    if (batch->cols[i].dtype != m->sch.fields[i].dtype) fail(B2_ERR_ARROW, "batch column type mismatch");
+  auto it = std::make_shared<MemItem>();
+  it->dev = batch;
+  m->parts[partition].push_back(it);
+}
+void memory_exec_clear(Op* op) { as_mem(op)->clear(); }
+
+// ------------------------------------------------------------------------------------------------------
+// FilterExec: evaluate the Boolean predicate, compact every column, keep row order
+// ------------------------------------------------------------------------------------------------------
+struct FilterExec : Op {
+  ExprPtr pred;
+  const char* name() const override { return "FilterExec"; }
+  Schema schema() const override { return children[0]->schema(); }
+  struct S : Stream {
+    FilterExec* op;
+    StreamPtr in;
+    BatchPtr next() override {
+      BatchPtr b = in->next();
+      if (!b) return nullptr;
+      Ctx* ctx = op->ctx;
+      if (op->pred->is_literal()) {
+        if (op->pred->i) return b;
+        return take_batch(ctx, *b, nullptr, 0);
+      }
+      Column mask = eval_expr(ctx, op->pred, *b);
+      int64_t m = 0;
+      BufPtr idx = mask_to_indices(ctx, mask.values<uint8_t>(), b->num_rows, &m);
+      return take_batch(ctx, *b, idx->as<uint32_t>(), m);
+    }
+  };
+  StreamPtr execute(int partition) override {
+    auto s = std::make_unique<S>();
+    s->op = this;
+    s->in = children[0]->execute(partition);
+    last_path = "unfused";
+    return s;
+  }
+};
+OpPtr make_filter(Ctx* ctx, OpPtr input, ExprPtr pred) {
+  if (pred->dtype != B2_BOOL)
+    fail(B2_ERR_EXECUTION, "Filter predicate must return boolean values, not " + std::string(dtype_name(pred->dtype)));
+  auto op = std::make_shared<FilterExec>();
+  op->ctx = ctx;
+  op->children = {input};
+  op->pred = pred;
+  return op;
+}
+// used by the aggregate / join to fuse the predicate of a FilterExec child into their scan
+bool op_is_filter(Op* op, ExprPtr* pred) {
+  auto* f = dynamic_cast<FilterExec*>(op);
+  if (!f) return false;
+  *pred = f->pred;
+  return true;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// CoalesceBatchesExec: concatenate small batches up to target_batch_size
+// ------------------------------------------------------------------------------------------------------
+struct CoalesceExec : Op {
+  int64_t target;
+  const char* name() const override { return "CoalesceBatchesExec"; }
+  Schema schema() const override { return children[0]->schema(); }
+  struct S : Stream {
+    CoalesceExec* op;
+    StreamPtr in;
+    bool done = false;
+    BatchPtr next() override {
+      if (done) return nullptr;
+      std::vector<BatchPtr> buf;
+      int64_t rows = 0;
+      while (true) {
+        BatchPtr b = in->next();
+        if (!b) {
+          done = true;
+          break;
+        }
+        if (b->num_rows == 0) continue;
+        if (buf.empty() && b->num_rows >= op->target) return b;
+        buf.push_back(b);
+        rows += b->num_rows;
+        if (rows >= op->target) break;
+      }
+      if (buf.empty()) return nullptr;
+      return concat_batches(op->ctx, op->schema(), buf);
+    }
+  };
+  StreamPtr execute(int partition) override {
+    auto s = std::make_unique<S>();
+    s->op = this;
+    s->in = children[0]->execute(partition);
+    last_path = "passthrough";
+    return s;
+  }
+};
+OpPtr make_coalesce(Ctx* ctx, OpPtr input, int64_t target) {
+  auto op = std::make_shared<CoalesceExec>();
+  op->ctx = ctx;
+  op->children = {input};
+  op->target = target > 0 ? target : 1;
+  return op;
+}
+bool op_is_coalesce(Op* op) { return dynamic_cast<CoalesceExec*>(op) != nullptr; }
+
+// ------------------------------------------------------------------------------------------------------
+// MergeExec: N input partitions -> 1 (partition order; the reference interleaves arbitrarily)
+// ------------------------------------------------------------------------------------------------------
+struct MergeExec : Op {
+  const char* name() const override { return "MergeExec"; }
+  Schema schema() const override { return children[0]->schema(); }
+  void partitioning(int* scheme, int* n) const override {
+    *scheme = B2_PART_UNKNOWN;
+    *n = 1;
+  }
+  struct S : Stream {
+    MergeExec* op;
+    int part = 0, nparts = 0;
+    StreamPtr cur;
+    BatchPtr next() override {
+      while (part < nparts) {
+        if (!cur) cur = op->children[0]->execute(part);
+        BatchPtr b = cur->next();
+        if (b) return b;
+        cur.reset();
+        part++;
+      }
+      return nullptr;
+    }
+  };
+  StreamPtr execute(int partition) override {
+    if (partition != 0) fail(B2_ERR_INVALID_ARG, "MergeExec has a single output partition");
+    auto s = std::make_unique<S>();
+    s->op = this;
+    s->nparts = children[0]->n_partitions();
+    last_path = "passthrough";
+    return s;
+  }
+};
+OpPtr make_merge(Ctx* ctx, OpPtr input) {
+  auto op = std::make_shared<MergeExec>();
+  op->ctx = ctx;
+  op->children = {input};
+  return op;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// ProjectionExec
+// ------------------------------------------------------------------------------------------------------
+struct ProjectionExec : Op {
+  std::vector<ExprPtr> exprs;
+  Schema out;
+  const char* name() const override { return "ProjectionExec"; }
+  Schema schema() const override { return out; }
+  struct S : Stream {
+    ProjectionExec* op;
+    StreamPtr in;
+    BatchPtr next() override {
+      BatchPtr b = in->next();
+      if (!b) return nullptr;
+      auto r = std::make_shared<Batch>();
+      r->ctx = op->ctx;
+      r->schema = op->out;
+      r->num_rows = b->num_rows;
+      for (auto& e : op->exprs) r->cols.push_back(eval_expr(op->ctx, e, *b));
+      return r;
+    }
+  };
+  StreamPtr execute(int partition) override {
+    auto s = std::make_unique<S>();
+    s->op = this;
+    s->in = children[0]->execute(partition);
+    last_path = "unfused";
+    return s;
+  }
+};
+OpPtr make_projection(Ctx* ctx, OpPtr input, std::vector<ExprPtr> exprs) {
+  auto op = std::make_shared<ProjectionExec>();
+  op->ctx = ctx;
+  op->children = {input};
+  Schema in = input->schema();
+  for (size_t i = 0; i < exprs.size(); ++i) {
+    std::string nm = exprs[i]->name.empty() ? expr_to_string(exprs[i], in) : exprs[i]->name;
+    op->out.fields.push_back(Field{nm, exprs[i]->dtype, false});
+  }
+  op->exprs = std::move(exprs);
+  return op;
+}
+
+}  // namespace b2

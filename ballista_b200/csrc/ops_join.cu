@@ -1,0 +1,246 @@
+// ops_join.cu — HashJoinExec (collect-left build + probe) and RepartitionExec (hash / round-robin; with a
+// communicator attached the hash repartition IS the in-box shuffle).  SURVEY §8a rows F, G, H.
+// Constructed where from_proto.rs:253-276 and :133-164 construct the DataFusion operators.
+#include "ops.h"
+
+namespace b2 {
+
+// ------------------------------------------------------------------------------------------------------
+// HashJoinExec
+// ------------------------------------------------------------------------------------------------------
+struct HashJoinExec : Op {
+  std::vector<int> on_left, on_right;  // column indices
+  int join_type = B2_JOIN_INNER;
+  Schema out;
+  std::vector<int> right_keep;  // right columns that survive the duplicate-name rule
+  KeyLayout layout;
+  // build side, collected once (the reference rebuilds it per task; result-neutral)
+  BatchPtr left_batch;
+  std::shared_ptr<JoinTable> table;
+  BufPtr left_keys;
+
+  const char* name() const override { return "HashJoinExec"; }
+  Schema schema() const override { return out; }
+  void partitioning(int* scheme, int* n) const override { children[1]->partitioning(scheme, n); }
+
+  BufPtr pack(const Batch& b, const std::vector<int>& on) {
+    std::vector<Column> kc;
+    for (int c : on) kc.push_back(b.cols[c]);
+    BufPtr st = dev_alloc_zero(ctx, 16);
+    BufPtr keys = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>());
+    int host = 0;
+    B2_CUDA(cudaMemcpyAsync(&host, st->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 join key value is longer than the packed-key budget");
+    return keys;
+  }
+  void build() {
+    if (table) return;
+    Op* l = children[0].get();
+    std::vector<BatchPtr> all;
+    int np = l->n_partitions();
+    for (int p = 0; p < np; ++p) {  // MergeExec(left): all partitions
+      StreamPtr s = l->execute(p);
+      while (BatchPtr b = s->next())
+        if (b->num_rows) all.push_back(b);
+    }
+    if (all.empty()) {
+      left_batch = empty_batch(ctx, l->schema());
+    } else {
+      left_batch = concat_batches(ctx, l->schema(), all);
+    }
+    left_keys = pack(*left_batch, on_left);
+    table = join_build(ctx, left_keys->as<Key128>(), left_batch->num_rows);
+  }
+  struct S : Stream {
+    HashJoinExec* op;
+    StreamPtr in;
+    BatchPtr next() override {
+      BatchPtr r = in->next();
+      if (!r) return nullptr;
+      Ctx* ctx = op->ctx;
+      BufPtr pk = op->pack(*r, op->on_right);
+      BufPtr li, ri;
+      int64_t m = join_probe(ctx, *op->table, pk->as<Key128>(), r->num_rows, &li, &ri);
+      auto o = std::make_shared<Batch>();
+      o->ctx = ctx;
+      o->schema = op->out;
+      o->num_rows = m;
+      for (auto& c : op->left_batch->cols) o->cols.push_back(take_column(ctx, c, li->as<uint32_t>(), m));
+      for (int c : op->right_keep) o->cols.push_back(take_column(ctx, r->cols[c], ri->as<uint32_t>(), m));
+      return o;
+    }
+  };
+  StreamPtr execute(int partition) override {
+    build();
+    auto s = std::make_unique<S>();
+    s->op = this;
+    s->in = children[1]->execute(partition);
+    last_path = "unfused";
+    return s;
+  }
+};
+
+OpPtr make_hash_join(Ctx* ctx, OpPtr left, OpPtr right, std::vector<std::string> on_l, std::vector<std::string> on_r,
+                     int join_type) {
+  if (join_type != B2_JOIN_INNER)
+    fail(B2_ERR_NOT_IMPLEMENTED,
+         "Left/Right outer joins need null-extended rows; only Inner is implemented (all TPC-H Q3/Q5 joins)");
+  if (on_l.empty() || on_l.size() != on_r.size()) fail(B2_ERR_INVALID_ARG, "join needs matching on-column lists");
+  auto op = std::make_shared<HashJoinExec>();
+  op->ctx = ctx;
+  op->children = {left, right};
+  op->join_type = join_type;
+  Schema ls = left->schema(), rs = right->schema();
+  std::vector<int> kd;
+  for (size_t i = 0; i < on_l.size(); ++i) {
+    int a = ls.index_of(on_l[i]), b = rs.index_of(on_r[i]);
+    if (a < 0) fail(B2_ERR_INVALID_ARG, "join column '" + on_l[i] + "' not in the left schema");
+    if (b < 0) fail(B2_ERR_INVALID_ARG, "join column '" + on_r[i] + "' not in the right schema");
+    int ta = ls.fields[a].dtype, tb = rs.fields[b].dtype;
+    bool i32 = (ta == B2_INT32 || ta == B2_DATE32) && (tb == B2_INT32 || tb == B2_DATE32);
+    if (ta != tb && !i32) fail(B2_ERR_EXECUTION, "join key types differ for '" + on_l[i] + "' / '" + on_r[i] + "'");
+    op->on_left.push_back(a);
+    op->on_right.push_back(b);
+    kd.push_back(ta);
+  }
+  op->layout = make_key_layout(kd);
+  // output = left fields ++ right fields minus right on-columns named like their left partner (A.3)
+  op->out = ls;
+  for (size_t c = 0; c < rs.fields.size(); ++c) {
+    bool dup = false;
+    for (size_t i = 0; i < on_l.size(); ++i)
+      if ((int)c == op->on_right[i] && on_l[i] == on_r[i]) dup = true;
+    if (dup) continue;
+    op->right_keep.push_back((int)c);
+    op->out.fields.push_back(rs.fields[c]);
+  }
+  return op;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// RepartitionExec
+// ------------------------------------------------------------------------------------------------------
+struct RepartitionExec : Op {
+  int scheme = B2_PART_HASH;
+  std::vector<ExprPtr> keys;
+  int n_out = 1;
+  KeyLayout layout;
+  bool computed = false;
+  std::vector<std::vector<BatchPtr>> outputs;  // per output partition
+
+  const char* name() const override { return "RepartitionExec"; }
+  Schema schema() const override { return children[0]->schema(); }
+  void partitioning(int* s, int* n) const override {
+    *s = scheme;
+    *n = n_out;
+  }
+  bool exchange_mode() const { return scheme == B2_PART_HASH && ctx->comm && n_out == ctx->nranks; }
+
+  // hash-split one batch: destination-major permuted batch + per-destination counts
+  BatchPtr split(const Batch& b, std::vector<int64_t>* counts) {
+    std::vector<Column> kc;
+    for (auto& k : keys) kc.push_back(eval_expr(ctx, k, b));
+    BufPtr st = dev_alloc_zero(ctx, 16);
+    BufPtr pk = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>());
+    BufPtr perm = hash_partition_indices(ctx, pk->as<Key128>(), b.num_rows, n_out, counts);
+    int host = 0;
+    B2_CUDA(cudaMemcpyAsync(&host, st->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 partitioning key value is longer than the packed-key budget");
+    return take_batch(ctx, b, perm->as<uint32_t>(), b.num_rows);
+  }
+  void compute() {
+    if (computed) return;
+    outputs.assign(n_out, {});
+    Op* in = children[0].get();
+    int np = in->n_partitions();
+    if (exchange_mode()) {
+      // one collective per execution: all local input is concatenated, split, and exchanged once
+      std::vector<BatchPtr> all;
+      for (int p = 0; p < np; ++p) {
+        StreamPtr s = in->execute(p);
+        while (BatchPtr b = s->next())
+          if (b->num_rows) all.push_back(b);
+      }
+      BatchPtr local;
+      if (all.empty()) {
+        local = empty_batch(ctx, schema());
+      } else {
+        local = concat_batches(ctx, schema(), all);
+      }
+      std::vector<int64_t> counts;
+      BatchPtr permuted = split(*local, &counts);
+      outputs[ctx->rank].push_back(comm_all_to_all(ctx, *permuted, counts));
+      last_path = "nccl-all-to-all";
+    } else {
+      int64_t k = 0;
+      for (int p = 0; p < np; ++p) {
+        StreamPtr s = in->execute(p);
+        while (BatchPtr b = s->next()) {
+          if (scheme == B2_PART_ROUND_ROBIN) {
+            outputs[k++ % n_out].push_back(b);
+            continue;
+          }
+          if (!b->num_rows) continue;
+          std::vector<int64_t> counts;
+          BatchPtr permuted = split(*b, &counts);
+          int64_t off = 0;
+          for (int d = 0; d < n_out; ++d) {
+            if (counts[d]) outputs[d].push_back(slice_batch(ctx, *permuted, off, off + counts[d]));
+            off += counts[d];
+          }
+        }
+      }
+      last_path = "local";
+    }
+    computed = true;
+  }
+  struct S : Stream {
+    RepartitionExec* op;
+    int part;
+    size_t pos = 0;
+    BatchPtr next() override {
+      auto& v = op->outputs[part];
+      return pos < v.size() ? v[pos++] : nullptr;
+    }
+  };
+  StreamPtr execute(int partition) override {
+    if (partition < 0 || partition >= n_out) fail(B2_ERR_INVALID_ARG, "RepartitionExec: partition out of range");
+    if (exchange_mode() && partition != ctx->rank)
+      fail(B2_ERR_INVALID_ARG, "with a communicator attached, rank r executes output partition r");
+    compute();
+    auto s = std::make_unique<S>();
+    s->op = this;
+    s->part = partition;
+    return s;
+  }
+};
+
+OpPtr make_repartition(Ctx* ctx, OpPtr input, int scheme, std::vector<ExprPtr> keys, int n_out) {
+  if (n_out < 1) fail(B2_ERR_INVALID_ARG, "RepartitionExec needs n >= 1");
+  if (scheme != B2_PART_HASH && scheme != B2_PART_ROUND_ROBIN)
+    fail(B2_ERR_NOT_IMPLEMENTED, "RepartitionExec supports Hash and RoundRobinBatch partitioning");
+  auto op = std::make_shared<RepartitionExec>();
+  op->ctx = ctx;
+  op->children = {input};
+  op->scheme = scheme;
+  op->n_out = n_out;
+  if (scheme == B2_PART_HASH) {
+    if (keys.empty()) fail(B2_ERR_INVALID_ARG, "hash repartition needs key expressions");
+    std::vector<int> kd;
+    for (auto& k : keys) kd.push_back(k->dtype);
+    op->layout = make_key_layout(kd);
+  }
+  op->keys = std::move(keys);
+  return op;
+}
+
+void repartition_reset(Op* op) {
+  if (auto* r = dynamic_cast<RepartitionExec*>(op)) {
+    r->computed = false;
+    r->outputs.clear();
+  }
+}
+
+}  // namespace b2

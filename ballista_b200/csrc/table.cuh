@@ -1,0 +1,135 @@
+// table.cuh — device-side building blocks shared by the aggregate / join / repartition kernels:
+// 128-bit packed keys, the global open-addressing group table (128-bit CAS claim + red.add accumulate),
+// streaming loads, warp reductions.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2 {
+
+typedef unsigned long long u64;
+typedef unsigned __int128 u128;
+
+// ---- packed group / join keys: 15 payload bytes, byte 15 always 0 so no key equals EMPTY ----
+struct Key128 {
+  u64 lo, hi;
+};
+__host__ __device__ __forceinline__ bool key_eq(const Key128& a, const Key128& b) { return a.lo == b.lo && a.hi == b.hi; }
+constexpr u64 KEY_EMPTY = ~0ull;
+
+__host__ __device__ __forceinline__ u64 mix64(u64 x) {
+  x ^= x >> 33;
+  x *= 0xff51afd7ed558ccdull;
+  x ^= x >> 33;
+  x *= 0xc4ceb9fe1a85ec53ull;
+  x ^= x >> 33;
+  return x;
+}
+__host__ __device__ __forceinline__ u64 key_hash(const Key128& k) { return mix64(k.lo ^ mix64(k.hi + 0x9E3779B97F4A7C15ull)); }
+
+// ---- streaming (read-once) loads: bypass L1 allocation ----
+__device__ __forceinline__ double2 ld_stream_f64x2(const double* p) {
+  double2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ int4 ld_stream_i32x4(const int32_t* p) {
+  int4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+// ---- atomics chosen for Blackwell: 128-bit CAS to claim a slot, result-less red.add to accumulate ----
+__device__ __forceinline__ Key128 atomic_cas_key(Key128* addr, Key128 expect, Key128 desired) {
+  Key128 old;
+  asm volatile(
+      "{\n .reg .b128 e, d, o;\n mov.b128 e, {%2, %3};\n mov.b128 d, {%4, %5};\n"
+      " atom.global.relaxed.gpu.cas.b128 o, [%6], e, d;\n mov.b128 {%0, %1}, o;\n}\n"
+      : "=l"(old.lo), "=l"(old.hi)
+      : "l"(expect.lo), "l"(expect.hi), "l"(desired.lo), "l"(desired.hi), "l"(addr)
+      : "memory");
+  return old;
+}
+__device__ __forceinline__ void red_add_f64(double* p, double v) {
+  asm volatile("red.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_u64(u64* p, u64 v) {
+  asm volatile("red.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ Key128 ld_key_volatile(const Key128* p) {
+  Key128 k;
+  asm volatile("ld.volatile.global.v2.u64 {%0,%1}, [%2];" : "=l"(k.lo), "=l"(k.hi) : "l"(p));
+  return k;
+}
+
+// ---- group table in HBM: keys[cap] (EMPTY-initialised), acc[na][cap] f64 sums, cnt[nc][cap] u64 sums ----
+struct TableRef {
+  Key128* keys;
+  double* acc;
+  u64* cnt;
+  u64 cap;        // power of two
+  int* n_groups;  // number of claimed slots
+};
+
+// find or claim the slot of `key`; returns slot index, or ~0 when the table is full
+__device__ __forceinline__ u64 table_upsert(const TableRef& t, const Key128& key) {
+  u64 mask = t.cap - 1;
+  u64 h = key_hash(key) & mask;
+  const Key128 empty{KEY_EMPTY, KEY_EMPTY};
+  for (u64 probe = 0; probe < t.cap; ++probe) {
+    Key128 cur = ld_key_volatile(&t.keys[h]);
+    if (key_eq(cur, key)) return h;
+    if (key_eq(cur, empty)) {
+      Key128 old = atomic_cas_key(&t.keys[h], empty, key);
+      if (key_eq(old, empty)) {
+        atomicAdd(t.n_groups, 1);
+        return h;
+      }
+      if (key_eq(old, key)) return h;
+    }
+    h = (h + 1) & mask;
+  }
+  return ~0ull;
+}
+// read-only lookup; ~0 when absent
+__device__ __forceinline__ u64 table_find(const Key128* keys, u64 cap, const Key128& key) {
+  u64 mask = cap - 1;
+  u64 h = key_hash(key) & mask;
+  for (u64 probe = 0; probe < cap; ++probe) {
+    Key128 cur = keys[h];
+    if (key_eq(cur, key)) return h;
+    if (cur.lo == KEY_EMPTY && cur.hi == KEY_EMPTY) return ~0ull;
+    h = (h + 1) & mask;
+  }
+  return ~0ull;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  return v;
+}
+__device__ __forceinline__ u64 warp_sum(u64 v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  return v;
+}
+
+// ---- short strings held in registers: first <=15 bytes little-endian + length ----
+struct StrVal {
+  u128 bytes;
+  int len;
+};
+__device__ __forceinline__ StrVal load_str(const int32_t* off, const uint8_t* chr, int64_t row) {
+  int32_t b = off[row], e = off[row + 1];
+  StrVal s;
+  s.len = e - b;
+  s.bytes = 0;
+  int m = s.len < 15 ? s.len : 15;
+  for (int q = 0; q < m; ++q) s.bytes |= (u128)chr[b + q] << (8 * q);
+  return s;
+}
+
+}  // namespace b2

@@ -1,0 +1,158 @@
+// take.cu — selection vectors and gathers: mask -> ordered row indices (stream compaction), and
+// index-driven column gathers (`take`), the building blocks of FilterExec (arrow::compute::filter),
+// HashJoinExec output assembly and RepartitionExec (arrow::compute::take).  SURVEY §8a rows A, F, G.
+#include "ops.h"
+#include "scan.cuh"
+
+namespace b2 {
+
+struct IndexOut {
+  uint32_t* idx;
+  __device__ __forceinline__ void operator()(int64_t i, int v, int64_t pre) const {
+    if (v) idx[pre] = (uint32_t)i;
+  }
+};
+
+// order-preserving compaction of the rows where mask != 0
+BufPtr mask_to_indices(Ctx* ctx, const uint8_t* mask, int64_t n, int64_t* count) {
+  if (n >= (1ll << 32) - 1) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
+  auto idx = dev_alloc(ctx, (size_t)(n + 1) * 4);
+  device_scan(ctx, MaskIn{mask}, n, IndexOut{idx->as<uint32_t>()}, count);
+  return idx;
+}
+
+template <class T> __global__ void gather_kernel(const T* in, const uint32_t* idx, int64_t m, T* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < m; i += (int64_t)gridDim.x * blockDim.x) out[i] = in[idx[i]];
+}
+struct StrOffOut {
+  int32_t* off;
+  int64_t n;
+  __device__ __forceinline__ void operator()(int64_t i, int v, int64_t pre) const {
+    off[i] = (int32_t)pre;
+    if (i == n - 1) off[n] = (int32_t)(pre + v);
+  }
+};
+__global__ void gather_chars_kernel(const int32_t* in_off, const uint8_t* in_chr, const uint32_t* idx, int64_t m,
+                                    const int32_t* out_off, uint8_t* out_chr) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < m; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = idx[i];
+    int32_t b = in_off[r], len = in_off[r + 1] - b, o = out_off[i];
+    for (int q = 0; q < len; ++q) out_chr[o + q] = in_chr[b + q];
+  }
+}
+
+Column take_column(Ctx* ctx, const Column& c, const uint32_t* idx, int64_t m) {
+  Column out;
+  out.dtype = c.dtype;
+  out.length = m;
+  int grid = grid_for(ctx, 8, m, 256);
+  if (c.dtype == B2_UTF8) {
+    out.data = dev_alloc_zero(ctx, (size_t)(m + 1) * 4);
+    int64_t total = 0;
+    device_scan(ctx, StrLenIn{c.values<int32_t>(), idx}, m, StrOffOut{out.data->as<int32_t>(), m}, &total);
+    if (total >= (1ll << 31)) fail(B2_ERR_EXECUTION, "Utf8 column beyond 2 GiB after take");
+    out.chars_len = total;
+    out.chars = dev_alloc(ctx, (size_t)total + 16);
+    if (m) {
+      gather_chars_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), c.chars->as<uint8_t>(), idx, m,
+                                                        out.data->as<int32_t>(), out.chars->as<uint8_t>());
+      B2_LAUNCHED(ctx);
+    }
+    return out;
+  }
+  size_t w = dtype_width(c.dtype);
+  out.data = dev_alloc(ctx, (size_t)m * w + 16);
+  if (m) {
+    switch (w) {
+      case 1: gather_kernel<uint8_t><<<grid, 256, 0, ctx->stream>>>(c.values<uint8_t>(), idx, m, out.data->as<uint8_t>()); break;
+      case 4: gather_kernel<int32_t><<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), idx, m, out.data->as<int32_t>()); break;
+      case 8: gather_kernel<int64_t><<<grid, 256, 0, ctx->stream>>>(c.values<int64_t>(), idx, m, out.data->as<int64_t>()); break;
+      default: fail(B2_ERR_NOT_IMPLEMENTED, "take on this type");
+    }
+    B2_LAUNCHED(ctx);
+  }
+  return out;
+}
+
+BatchPtr take_batch(Ctx* ctx, const Batch& b, const uint32_t* idx, int64_t m) {
+  auto out = std::make_shared<Batch>();
+  out->ctx = ctx;
+  out->schema = b.schema;
+  out->num_rows = m;
+  for (auto& c : b.cols) out->cols.push_back(take_column(ctx, c, idx, m));
+  return out;
+}
+
+BatchPtr empty_batch(Ctx* ctx, const Schema& schema) {
+  auto b = std::make_shared<Batch>();
+  b->ctx = ctx;
+  b->schema = schema;
+  for (auto& f : schema.fields) {
+    Column c;
+    c.dtype = f.dtype;
+    c.data = dev_alloc_zero(ctx, 16);
+    if (f.dtype == B2_UTF8) c.chars = dev_alloc(ctx, 16);
+    b->cols.push_back(c);
+  }
+  return b;
+}
+
+// concatenate batches of one schema (CoalesceBatchesExec / MergeExec collection / join build side)
+__global__ void shift_offsets_kernel(const int32_t* in, int64_t n, int32_t delta, int32_t* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = in[i] + delta;
+}
+
+BatchPtr concat_batches(Ctx* ctx, const Schema& schema, const std::vector<BatchPtr>& batches) {
+  if (batches.size() == 1) return batches[0];
+  auto out = std::make_shared<Batch>();
+  out->ctx = ctx;
+  out->schema = schema;
+  int64_t n = 0;
+  for (auto& b : batches) n += b->num_rows;
+  out->num_rows = n;
+  for (size_t ci = 0; ci < schema.fields.size(); ++ci) {
+    Column c;
+    c.dtype = schema.fields[ci].dtype;
+    c.length = n;
+    if (c.dtype == B2_UTF8) {
+      int64_t chars = 0;
+      for (auto& b : batches) chars += b->cols[ci].chars_len;
+      if (chars >= (1ll << 31)) fail(B2_ERR_EXECUTION, "Utf8 column beyond 2 GiB after concat");
+      c.data = dev_alloc_zero(ctx, (size_t)(n + 1) * 4);
+      c.chars = dev_alloc(ctx, (size_t)chars + 16);
+      c.chars_len = chars;
+      int64_t row = 0, ch = 0;
+      for (auto& b : batches) {
+        const Column& s = b->cols[ci];
+        if (s.length) {
+          shift_offsets_kernel<<<grid_for(ctx, 8, s.length + 1, 256), 256, 0, ctx->stream>>>(
+              s.values<int32_t>(), s.length + 1, (int32_t)ch, c.data->as<int32_t>() + row);
+          B2_LAUNCHED(ctx);
+          if (s.chars_len)
+            B2_CUDA(cudaMemcpyAsync(c.chars->as<uint8_t>() + ch, s.chars->ptr, (size_t)s.chars_len,
+                                    cudaMemcpyDeviceToDevice, ctx->stream));
+        }
+        row += s.length;
+        ch += s.chars_len;
+      }
+    } else {
+      size_t w = dtype_width(c.dtype);
+      c.data = dev_alloc(ctx, (size_t)n * w + 16);
+      int64_t row = 0;
+      for (auto& b : batches) {
+        const Column& s = b->cols[ci];
+        if (s.length)
+          B2_CUDA(cudaMemcpyAsync(c.data->as<char>() + (size_t)row * w, s.data->ptr, (size_t)s.length * w,
+                                  cudaMemcpyDeviceToDevice, ctx->stream));
+        row += s.length;
+      }
+    }
+    out->cols.push_back(std::move(c));
+  }
+  return out;
+}
+
+}  // namespace b2

@@ -10,8 +10,10 @@
 
 #if defined(__CUDACC__)
 #define B2_HD __host__ __device__ __forceinline__
+#define B2_UNROLL _Pragma("unroll")
 #else
 #define B2_HD inline
+#define B2_UNROLL
 #endif
 
 namespace b2spec {
@@ -63,7 +65,7 @@ B2_HD void l_locate(int64_t r, int64_t* order_idx, int32_t* linenumber) {
   int j = (int)(r & 31);
   int rot = (int)(rnd(S_L_COUNTROT, (uint64_t)g) & 7);
   int s = 0, cum = 0;
-#pragma unroll
+B2_UNROLL
   for (int t = 0; t < 8; ++t) {
     int c = base[(t + rot) & 7];
     if (j >= cum + c && t < 7) { cum += c; s = t + 1; }

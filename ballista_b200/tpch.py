@@ -1,0 +1,115 @@
+"""TPC-H query plans as the reference's planner shapes them (SQL in
+rust/benchmarks/tpch/queries/q{1,3,6}.sql), assembled from the operator mirror in plan.py.
+
+Each builder returns (partial_stage_plan, make_final) so that the Partial stage runs per partition / per GPU
+and the Final stage runs over the merged partial states — the two Ballista query stages split at
+rust/scheduler/src/planner.rs:149-169.
+"""
+import pyarrow as pa
+
+from . import _capi as K
+from .expr import avg, col, count, date, lit, sum as sum_
+from .plan import (CoalesceBatchesExec, FilterExec, HashAggregateExec, HashJoinExec, MemoryExec, MergeExec,
+                   RepartitionExec)
+
+Q1_COLUMNS = ["l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_returnflag", "l_linestatus", "l_shipdate"]
+Q6_COLUMNS = ["l_quantity", "l_extendedprice", "l_discount", "l_shipdate"]
+Q3_LINEITEM_COLUMNS = ["l_orderkey", "l_extendedprice", "l_discount", "l_shipdate"]
+Q3_ORDERS_COLUMNS = ["o_orderkey", "o_custkey", "o_orderdate", "o_shippriority"]
+Q3_CUSTOMER_COLUMNS = ["c_custkey", "c_mktsegment"]
+
+# algorithmic bytes per input row
+Q1_BYTES_PER_ROW = 46
+Q6_BYTES_PER_ROW = 28
+
+
+def q1_aggregates():
+    disc_price = col("l_extendedprice") * (lit(1) - col("l_discount"))
+    charge = col("l_extendedprice") * (lit(1) - col("l_discount")) * (lit(1) + col("l_tax"))
+    return [
+        sum_(col("l_quantity")).alias("sum_qty"),
+        sum_(col("l_extendedprice")).alias("sum_base_price"),
+        sum_(disc_price).alias("sum_disc_price"),
+        sum_(charge).alias("sum_charge"),
+        avg(col("l_quantity")).alias("avg_qty"),
+        avg(col("l_extendedprice")).alias("avg_price"),
+        avg(col("l_discount")).alias("avg_disc"),
+        count().alias("count_order"),
+    ]
+
+
+def q1_partial(scan, ship_date="1998-09-02"):
+    """HashAggregateExec(Partial) <- CoalesceBatchesExec <- FilterExec(l_shipdate <= d) <- scan."""
+    filt = CoalesceBatchesExec(FilterExec(col("l_shipdate") <= date(ship_date), scan))
+    groups = [col("l_returnflag"), col("l_linestatus")]
+    return HashAggregateExec("Partial", groups, q1_aggregates(), filt)
+
+
+def q1_final(partial_states, input_schema):
+    """HashAggregateExec(Final) <- MergeExec <- partial states (any plan producing the Partial schema)."""
+    groups = [col("l_returnflag"), col("l_linestatus")]
+    return HashAggregateExec("Final", groups, q1_aggregates(), MergeExec(partial_states), input_schema=input_schema)
+
+
+def q6_predicate():
+    return ((col("l_shipdate") >= date("1994-01-01")) & (col("l_shipdate") < date("1995-01-01"))
+            & col("l_discount").between(lit(0.06) - lit(0.01), lit(0.06) + lit(0.01))
+            & (col("l_quantity") < lit(24)))
+
+
+def q6_aggregates():
+    return [sum_(col("l_extendedprice") * col("l_discount")).alias("revenue")]
+
+
+def q6_partial(scan):
+    filt = CoalesceBatchesExec(FilterExec(q6_predicate(), scan))
+    return HashAggregateExec("Partial", [], q6_aggregates(), filt)
+
+
+def q6_final(partial_states, input_schema):
+    return HashAggregateExec("Final", [], q6_aggregates(), MergeExec(partial_states), input_schema=input_schema)
+
+
+def q3_join_tree(customer, orders, lineitem, segment="BUILDING", cutoff="1995-03-15"):
+    """(customer ⋈ orders) ⋈ lineitem, left-deep, build = left, filters pushed below the joins."""
+    c = CoalesceBatchesExec(FilterExec(col("c_mktsegment") == lit(segment), customer))
+    o = CoalesceBatchesExec(FilterExec(col("o_orderdate") < date(cutoff), orders))
+    l = CoalesceBatchesExec(FilterExec(col("l_shipdate") > date(cutoff), lineitem))
+    j1 = CoalesceBatchesExec(HashJoinExec(c, o, [("c_custkey", "o_custkey")]))
+    j2 = CoalesceBatchesExec(HashJoinExec(j1, l, [("o_orderkey", "l_orderkey")]))
+    return j2
+
+
+def q3_aggregates():
+    return [sum_(col("l_extendedprice") * (lit(1) - col("l_discount"))).alias("revenue")]
+
+
+def q3_groups():
+    return [col("l_orderkey"), col("o_orderdate"), col("o_shippriority")]
+
+
+def q3_partial(customer, orders, lineitem, **kw):
+    return HashAggregateExec("Partial", q3_groups(), q3_aggregates(), q3_join_tree(customer, orders, lineitem, **kw))
+
+
+def q3_final(partial_states, input_schema):
+    return HashAggregateExec("Final", q3_groups(), q3_aggregates(), MergeExec(partial_states),
+                             input_schema=input_schema)
+
+
+def scan(ctx, batches_per_partition, schema=None):
+    """MemoryExec over a list (partitions) of lists of DeviceBatch / pyarrow RecordBatch."""
+    if schema is None:
+        first = next(b for p in batches_per_partition for b in p)
+        schema = first.schema
+    return MemoryExec(ctx, schema, batches_per_partition)
+
+
+def run_two_stage(ctx, partial_plan, make_final, partition=0, merge="local"):
+    """Run the Partial stage on this GPU, merge partial states (all-gather over NVLink when a communicator
+    is attached, replacing the MergeExec stage hop), then the Final stage.  Returns a pyarrow Table."""
+    states = partial_plan.collect_device(partition)
+    if ctx.nranks > 1 and merge != "local":
+        states = [ctx.allgather(s) for s in states]
+    final = make_final(MemoryExec(ctx, partial_plan.schema(), [states]))
+    return final.collect()

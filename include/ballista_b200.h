@@ -91,6 +91,11 @@ void* b2_ctx_cuda_stream(b2_ctx* ctx);
 int b2_ctx_synchronize(b2_ctx* ctx);
 /* number of kernels this ctx has launched so far (bench.py's gpu_launches) */
 int64_t b2_ctx_kernel_launches(b2_ctx* ctx);
+/* Per-launch CUDA-event timing of the aggregate scan kernels (the dominant kernel of Q1/Q6/Q3), recorded
+ * on the ctx stream.  b2_ctx_profile synchronises, returns the summed duration and launch count since the
+ * last call, and resets. */
+int b2_ctx_set_profiling(b2_ctx* ctx, int on);
+int b2_ctx_profile(b2_ctx* ctx, double* ms_total, int64_t* launches);
 /* pinned host memory for Arrow buffers that will be pushed (so H2D runs at PCIe speed) */
 int b2_host_alloc(b2_ctx* ctx, size_t nbytes, void** out);
 int b2_host_free(b2_ctx* ctx, void* p);
@@ -190,7 +195,7 @@ int b2_repartition_create(b2_ctx* ctx, b2_op* input, int scheme, const b2_expr* 
 int b2_op_schema(b2_op* op, struct ArrowSchema* out);                   /* ExecutionPlan::schema              */
 int b2_op_output_partitioning(b2_op* op, int* scheme, int* n_partitions); /* ::output_partitioning            */
 int b2_op_n_children(b2_op* op);
-b2_op* b2_op_child(b2_op* op, int i);                                    /* ::children (borrowed)             */
+b2_op* b2_op_child(b2_op* op, int i); /* ::children — a new handle sharing the node; b2_op_destroy it */
 const char* b2_op_name(b2_op* op);                                       /* the operator's Debug name          */
 /* ::execute(partition)  (called at rust/executor/src/flight_service.rs:117-121) */
 int b2_op_execute(b2_op* op, int partition, b2_stream** out);

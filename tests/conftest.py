@@ -1,0 +1,27 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (runs on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def ctx():
+    import ballista_b200 as b2
+    c = b2.Context(0)  # raises without a GPU: there is no CPU fallback
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="session")
+def O():
+    from oracle import oracle_py
+    oracle_py.lib()
+    return oracle_py

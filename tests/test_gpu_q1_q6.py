@@ -1,0 +1,90 @@
+"""Parity of the fused and unfused scan->filter->aggregate paths (TPC-H Q1, Q6) against the oracle."""
+import os
+
+import numpy as np
+import pytest
+
+from util import assert_rows_match
+
+pytestmark = pytest.mark.gpu
+
+Q1_F = ["sum_qty", "sum_base_price", "sum_disc_price", "sum_charge", "avg_qty", "avg_price", "avg_disc"]
+
+
+def run_q1(ctx, batches, merge_parts=1):
+    from ballista_b200 import tpch
+    scan = tpch.scan(ctx, batches)
+    partial = tpch.q1_partial(scan)
+    states = [s for p in range(len(batches)) for s in partial.collect_device(p)]
+    from ballista_b200 import MemoryExec
+    final = tpch.q1_final(MemoryExec(ctx, partial.schema(), [states]), scan.schema())
+    return final.collect().to_pylist(), partial
+
+
+@pytest.mark.parametrize("n", [1, 5, 1023, 1 << 16, 300_000])
+def test_generator_matches_host(ctx, O, n):
+    sf = 0.05
+    dev = ctx.tpch("lineitem", sf, 7 * 32, 7 * 32 + n).to_arrow()
+    host = O.gen_lineitem(sf, 7 * 32, n)
+    for name in ["l_orderkey", "l_suppkey", "l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_shipdate",
+                 "l_commitdate", "l_receiptdate"]:
+        got = dev.column(name).to_numpy(zero_copy_only=False)
+        if "date" in name:
+            got = dev.column(name).cast("int32").to_numpy()
+        assert np.array_equal(got.view(np.uint8), np.ascontiguousarray(host[name]).view(np.uint8)), name
+    assert dev.column("l_returnflag").to_pylist() == host["l_returnflag"].to_list()
+    assert dev.column("l_linestatus").to_pylist() == host["l_linestatus"].to_list()
+
+
+@pytest.mark.parametrize("n,parts", [(1, 1), (3, 1), (4097, 1), (1 << 16, 1), (300_000, 3)])
+def test_q1_fused_matches_oracle(ctx, O, n, parts):
+    sf = 0.05
+    bounds = [n * p // parts for p in range(parts + 1)]
+    batches = [[ctx.tpch("lineitem", sf, bounds[p], bounds[p + 1])] for p in range(parts)]
+    got, partial = run_q1(ctx, batches)
+    assert partial.last_path().startswith("fused:"), partial.last_path()
+    want = O.q1(O.gen_lineitem(sf, 0, n), n_partitions=parts)
+    assert_rows_match(got, want, ["l_returnflag", "l_linestatus"], exact=["count_order"], approx=Q1_F)
+
+
+def test_q1_unfused_matches_oracle(ctx, O, monkeypatch):
+    monkeypatch.setenv("B2_DISABLE_FUSION", "1")
+    sf, n = 0.05, 100_000
+    got, partial = run_q1(ctx, [[ctx.tpch("lineitem", sf, 0, n)]])
+    assert partial.last_path().startswith("unfused"), partial.last_path()
+    want = O.q1(O.gen_lineitem(sf, 0, n))
+    assert_rows_match(got, want, ["l_returnflag", "l_linestatus"], exact=["count_order"], approx=Q1_F)
+
+
+def test_q1_host_batches_through_arrow(ctx, O):
+    """Host RecordBatches (32,768-row batches like the reference's CsvExec) pushed through the C ABI."""
+    sf, n = 0.05, 150_000
+    cols = O.gen_lineitem(sf, 0, n)
+    from ballista_b200 import tpch
+    rb = O.to_arrow(cols, tpch.Q1_COLUMNS)
+    batches = [[rb.slice(o, 32768) for o in range(0, n, 32768)]]
+    got, partial = run_q1(ctx, batches)
+    want = O.q1(cols)
+    assert_rows_match(got, want, ["l_returnflag", "l_linestatus"], exact=["count_order"], approx=Q1_F)
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_q6_matches_oracle(ctx, O, fused, monkeypatch):
+    if not fused:
+        monkeypatch.setenv("B2_DISABLE_FUSION", "1")
+    from ballista_b200 import MemoryExec, tpch
+    sf, n = 0.1, 600_000
+    li = ctx.tpch("lineitem", sf, 0, n, columns=tpch.Q6_COLUMNS)
+    scan = tpch.scan(ctx, [[li]])
+    partial = tpch.q6_partial(scan)
+    states = partial.collect_device(0)
+    assert partial.last_path().startswith("fused:" if fused else "unfused"), partial.last_path()
+    got = tpch.q6_final(MemoryExec(ctx, partial.schema(), [states]), scan.schema()).collect().to_pylist()
+    rev, passing = O.q6(O.gen_lineitem(sf, 0, n))
+    assert passing > 0
+    assert abs(got[0]["revenue"] - rev) <= 1e-9 * abs(rev)
+    # the f64-folded BETWEEN bounds exclude l_discount == 0.07: count through a COUNT aggregate
+    from ballista_b200 import CoalesceBatchesExec, FilterExec, HashAggregateExec, count
+    cnt = HashAggregateExec("Partial", [], [count().alias("c")],
+                            CoalesceBatchesExec(FilterExec(tpch.q6_predicate(), tpch.scan(ctx, [[li]]))))
+    assert cnt.collect().to_pylist()[0]["c[count]"] == passing  # bit-exact

@@ -23,7 +23,7 @@ def run_q1(ctx, batches, merge_parts=1):
 
 @pytest.mark.parametrize("n", [1, 5, 1023, 1 << 16, 300_000])
 def test_generator_matches_host(ctx, O, n):
-    sf = 0.05
+    sf = 0.1
     dev = ctx.tpch("lineitem", sf, 7 * 32, 7 * 32 + n).to_arrow()
     host = O.gen_lineitem(sf, 7 * 32, n)
     for name in ["l_orderkey", "l_suppkey", "l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_shipdate",

@@ -31,6 +31,7 @@ struct FusedParams {
   const int32_t* i[fx::MAX_I];
   const int32_t* soff[fx::MAX_S];
   const uint8_t* schr[fx::MAX_S];
+  float savg[fx::MAX_S];  // average string bytes per row of each bound Utf8 column (sizes the TMA character window)
   fx::Lits lits;
 };
 
@@ -45,6 +46,9 @@ template <class Pred, class Keys, class Accs> struct FusedSrc {
   static constexpr bool KEYED = Keys::N > 0;
   static constexpr int SB = fx::str_budget(fx::CountStr<Keys>::INTS, fx::CountStr<Keys>::N);
   using Params = FusedParams;
+  using Pred_ = Pred;
+  using Keys_ = Keys;
+  using Accs_ = Accs;
   struct Rows {
     fx::Row r[ROWS_PER_THREAD];
   };

@@ -40,6 +40,7 @@ struct AggLaunch {
   std::function<void(int64_t row_begin, int64_t row_end, int64_t n, TableRef tbl, int* status)> global;
   int na = 0, nc = 0;
   bool keyed = false;
+  bool tma = false;  // `small` is the TMA-fed bandwidth kernel (agg_tma.cuh)
 };
 
 // ---- fused-kernel registry: signature text -> instantiated kernels ----

@@ -3,10 +3,56 @@
 #include <cstring>
 #include <mutex>
 
+#include <cstdlib>
+#include <type_traits>
+
 #include "agg.h"
 #include "agg_kernels.cuh"
+#include "agg_tma.cuh"
 
 namespace b2 {
+
+template <class S> struct is_fused : std::false_type {};
+template <class P, class K, class A> struct is_fused<FusedSrc<P, K, A>> : std::true_type {};
+
+static int align_up(int x, int a) { return (x + a - 1) / a * a; }
+
+// shared-memory ring layout of agg_tma_kernel for one bound source; false when the TMA path cannot be used
+// (a column pointer that is not 16-byte aligned, e.g. a sliced view, or no room for two stages)
+template <class S> static bool build_tma_layout(const FusedParams& p, size_t static_smem, TmaLayout* lay) {
+  memset(lay, 0, sizeof *lay);
+  auto aligned = [](const void* q) { return ((uintptr_t)q & 15u) == 0; };
+  int off = 0;
+  for (int c = 0; c < S::NF; ++c) {
+    if (!aligned(p.f[c])) return false;
+    lay->f_off[c] = off;
+    off += TMA_TILE * 8;
+  }
+  for (int c = 0; c < S::NI; ++c) {
+    if (!aligned(p.i[c])) return false;
+    lay->i_off[c] = off;
+    off += TMA_TILE * 4;
+  }
+  for (int c = 0; c < S::NS; ++c) {
+    if (!aligned(p.soff[c]) || !aligned(p.schr[c])) return false;
+    lay->so_off[c] = off;
+    off += align_up((TMA_TILE + 4) * 4, 128);
+    int cap = (int)(p.savg[c] * 1.5f * TMA_TILE) + 64;
+    if (cap < 256) cap = 256;
+    if (cap > 16 * TMA_TILE) cap = 16 * TMA_TILE;
+    cap = align_up(cap, 128);
+    lay->sc_off[c] = off;
+    lay->sc_cap[c] = cap;
+    off += cap;
+  }
+  lay->stage_bytes = align_up(off > 0 ? off : 128, 128);
+  int budget = 232448 - (int)static_smem - 256;
+  int ns = budget / lay->stage_bytes;
+  if (const char* e = getenv("B2_TMA_STAGES")) ns = std::min(ns, atoi(e));
+  if (ns > TMA_MAX_STAGES) ns = TMA_MAX_STAGES;
+  lay->n_stages = ns;
+  return ns >= 2;
+}
 
 template <class S> static AggLaunch make_launch(Ctx* ctx, const typename S::Params& prm) {
   AggLaunch l;
@@ -25,11 +71,35 @@ template <class S> static AggLaunch make_launch(Ctx* ctx, const typename S::Para
     int64_t tiles = (n + TILE_ROWS - 1) / TILE_ROWS;
     int64_t cap = (int64_t)ps * ctx->sm_count;
     int grid = (int)(tiles < cap ? tiles : cap);
-    ctx->prof_begin();
+    if (is_fused<S>::value) ctx->prof_begin();
     agg_small_kernel<S><<<grid, AGG_THREADS, 0, ctx->stream>>>(prm, n, tbl, status);
-    ctx->prof_end();
+    if (is_fused<S>::value) ctx->prof_end();
     B2_LAUNCHED(ctx);
   };
+  if constexpr (is_fused<S>::value) {
+    // bandwidth path: persistent TMA-fed kernel, one CTA per SM (agg_tma.cuh)
+    static size_t static_smem = 0;
+    if (!static_smem) {
+      cudaFuncAttributes fa;
+      B2_CUDA(cudaFuncGetAttributes(&fa, agg_tma_kernel<S>));
+      static_smem = fa.sharedSizeBytes;
+      B2_CUDA(cudaFuncSetAttribute(agg_tma_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   232448 - (int)static_smem));
+    }
+    TmaLayout lay;
+    if (!getenv("B2_DISABLE_TMA") && build_tma_layout<S>(prm, static_smem, &lay)) {
+      l.small = [ctx, prm, lay](int64_t n, TableRef tbl, int* status) {
+        int64_t tiles = (n + TMA_TILE - 1) / TMA_TILE;
+        int grid = (int)(tiles < ctx->sm_count ? tiles : ctx->sm_count);
+        size_t dyn = (size_t)lay.n_stages * lay.stage_bytes;
+        ctx->prof_begin();
+        agg_tma_kernel<S><<<grid, TMA_THREADS, dyn, ctx->stream>>>(prm, lay, n, tbl, status);
+        ctx->prof_end();
+        B2_LAUNCHED(ctx);
+      };
+      l.tma = true;
+    }
+  }
   l.global = [ctx, prm, pg](int64_t rb, int64_t re, int64_t n, TableRef tbl, int* status) {
     int64_t tiles = (re - rb + TILE_ROWS - 1) / TILE_ROWS;
     int64_t cap = (int64_t)pg * ctx->sm_count;
@@ -117,6 +187,8 @@ bool bind_fused_agg(Ctx* ctx, const ExprPtr& pred, const std::vector<ExprPtr>& g
   for (size_t k = 0; k < b.str_cols.size(); ++k) {
     p.soff[k] = batch.cols[b.str_cols[k]].values<int32_t>();
     p.schr[k] = batch.cols[b.str_cols[k]].chars->as<uint8_t>();
+    const Column& sc = batch.cols[b.str_cols[k]];
+    p.savg[k] = sc.length ? (float)sc.chars_len / (float)sc.length : 0.f;
   }
   for (size_t k = 0; k < b.f64_lits.size(); ++k) p.lits.f[k] = b.f64_lits[k];
   for (size_t k = 0; k < b.i64_lits.size(); ++k) p.lits.i[k] = b.i64_lits[k];

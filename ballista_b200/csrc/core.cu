@@ -8,6 +8,8 @@ namespace b2 {
 
 DevBuf::DevBuf(Ctx* c, size_t n) : ctx(c), bytes(n) {
   if (n == 0) return;
+  // every buffer is padded so that 16-byte vector loads / TMA bulk copies of the last rows stay in bounds
+  n = (n + 32 + 255) & ~(size_t)255;
   cudaError_t e = cudaMallocAsync(&ptr, n, c->pool, c->stream);
   if (e != cudaSuccess) {
     cudaGetLastError();

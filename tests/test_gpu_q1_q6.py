@@ -36,13 +36,18 @@ def test_generator_matches_host(ctx, O, n):
     assert dev.column("l_linestatus").to_pylist() == host["l_linestatus"].to_list()
 
 
-@pytest.mark.parametrize("n,parts", [(1, 1), (3, 1), (4097, 1), (1 << 16, 1), (300_000, 3)])
-def test_q1_fused_matches_oracle(ctx, O, n, parts):
+@pytest.mark.parametrize("tma", [True, False])
+@pytest.mark.parametrize("n,parts", [(1, 1), (3, 1), (959, 1), (960, 1), (961, 1), (4097, 1), (1 << 16, 1), (300_000, 3)])
+def test_q1_fused_matches_oracle(ctx, O, n, parts, tma, monkeypatch):
+    """tma=True: the TMA-fed bandwidth kernel (agg_tma.cuh); False: the register-load kernel it falls back to."""
+    if not tma:
+        monkeypatch.setenv("B2_DISABLE_TMA", "1")
     sf = 0.05
     bounds = [n * p // parts for p in range(parts + 1)]
     batches = [[ctx.tpch("lineitem", sf, bounds[p], bounds[p + 1])] for p in range(parts)]
     got, partial = run_q1(ctx, batches)
     assert partial.last_path().startswith("fused:"), partial.last_path()
+    assert ("[tma]" in partial.last_path()) == tma, partial.last_path()
     want = O.q1(O.gen_lineitem(sf, 0, n), n_partitions=parts)
     assert_rows_match(got, want, ["l_returnflag", "l_linestatus"], exact=["count_order"], approx=Q1_F)
 

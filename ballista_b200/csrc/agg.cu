@@ -110,6 +110,12 @@ void AggRunner::consume(const AggLaunch& l, int64_t n) {
   if (n <= 0) return;
   int host[4] = {0, 0, 0, 0};
   if (!force_global) {
+    if (narrow_overflowed && l.small_wide) {
+      AggLaunch w = l;
+      w.small = l.small_wide;
+      w.small_wide = nullptr;
+      return consume(w, n);
+    }
     if (!delta) delta = make_group_table(ctx, keyed ? DELTA_CAP : 16, na, nc);
     else reset_group_table(*delta);
     B2_CUDA(cudaMemsetAsync(status->ptr, 0, 16, ctx->stream));
@@ -123,8 +129,16 @@ void AggRunner::consume(const AggLaunch& l, int64_t n) {
           delta->ref(), main->ref(), na, nc, status->as<int>());
       B2_LAUNCHED(ctx);
       group_bound += host[1];
-      if (path.empty()) path = "small";
+      if (path.empty() || path == "small") path = narrow_overflowed ? "small+widekeys" : "small";
       return;
+    }
+    if (host[0] == AGG_KEY_TOO_WIDE && l.small_wide) {
+      // a narrow-key kernel met a Utf8 key value of more than its budget: redo the batch with wide keys
+      AggLaunch w = l;
+      w.small = l.small_wide;
+      w.small_wide = nullptr;
+      narrow_overflowed = true;
+      return consume(w, n);
     }
     if (host[0] == AGG_KEY_TOO_WIDE) check_status(host[0]);
     // too many groups for the per-CTA tables: redo this batch (and all later ones) on the HBM table

@@ -32,6 +32,7 @@ struct FusedParams {
   const int32_t* soff[fx::MAX_S];
   const uint8_t* schr[fx::MAX_S];
   float savg[fx::MAX_S];  // average string bytes per row of each bound Utf8 column (sizes the TMA character window)
+  int narrow_lits;        // every Utf8 literal has <= 7 bytes (the narrow kernels can represent them)
   fx::Lits lits;
 };
 
@@ -41,6 +42,7 @@ template <class Pred, class Keys, class Accs> struct FusedSrc {
   static constexpr int NF = fx::cmax(Pred::NF, fx::cmax(KT::NF, AT::NF));
   static constexpr int NI = fx::cmax(Pred::NI, fx::cmax(KT::NI, AT::NI));
   static constexpr int NS = fx::cmax(Pred::NS, fx::cmax(KT::NS, AT::NS));
+  static constexpr int NLS = fx::cmax(Pred::NLS, fx::cmax(KT::NLS, AT::NLS));  // Utf8 literal slots
   static constexpr int NACC = Accs::N;
   static constexpr int NCNT = 1;
   static constexpr bool KEYED = Keys::N > 0;

@@ -40,7 +40,11 @@ struct AggLaunch {
   std::function<void(int64_t row_begin, int64_t row_end, int64_t n, TableRef tbl, int* status)> global;
   int na = 0, nc = 0;
   bool keyed = false;
+  bool narrow = false;
   bool tma = false;  // `small` is the TMA-fed bandwidth kernel (agg_tma.cuh)
+  // when `small` is a narrow-key kernel (8-byte keys, Utf8 values of <= 7 bytes) and reports
+  // AGG_KEY_TOO_WIDE, the batch is redone with this wide (15-byte) variant
+  std::function<void(int64_t n, TableRef tbl, int* status)> small_wide;
 };
 
 // ---- fused-kernel registry: signature text -> instantiated kernels ----
@@ -71,6 +75,7 @@ struct AggRunner {
   std::shared_ptr<GroupTable> main, delta;
   BufPtr status;  // int[2]: status, spare
   bool force_global = false;
+  bool narrow_overflowed = false;  // a narrow-key kernel overflowed once: later batches go straight to wide keys
   int64_t group_bound = 0;  // upper bound on groups in `main`
   std::string path;         // diagnostics
   AggRunner(Ctx* c, int na_, int nc_, bool keyed_);

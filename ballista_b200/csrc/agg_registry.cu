@@ -22,21 +22,13 @@ static int align_up(int x, int a) { return (x + a - 1) / a * a; }
 template <class S> static bool build_tma_layout(const FusedParams& p, size_t static_smem, TmaLayout* lay) {
   memset(lay, 0, sizeof *lay);
   auto aligned = [](const void* q) { return ((uintptr_t)q & 15u) == 0; };
-  int off = 0;
-  for (int c = 0; c < S::NF; ++c) {
+  for (int c = 0; c < S::NF; ++c)
     if (!aligned(p.f[c])) return false;
-    lay->f_off[c] = off;
-    off += TMA_TILE * 8;
-  }
-  for (int c = 0; c < S::NI; ++c) {
+  for (int c = 0; c < S::NI; ++c)
     if (!aligned(p.i[c])) return false;
-    lay->i_off[c] = off;
-    off += TMA_TILE * 4;
-  }
+  int off = TmaStage<S>::SC_OFF;
   for (int c = 0; c < S::NS; ++c) {
     if (!aligned(p.soff[c]) || !aligned(p.schr[c])) return false;
-    lay->so_off[c] = off;
-    off += align_up((TMA_TILE + 4) * 4, 128);
     int cap = (int)(p.savg[c] * 1.5f * TMA_TILE) + 64;
     if (cap < 256) cap = 256;
     if (cap > 16 * TMA_TILE) cap = 16 * TMA_TILE;
@@ -77,38 +69,47 @@ template <class S> static AggLaunch make_launch(Ctx* ctx, const typename S::Para
     B2_LAUNCHED(ctx);
   };
   if constexpr (is_fused<S>::value) {
-    // bandwidth path: persistent TMA-fed kernel, one CTA per SM (agg_tma.cuh)
-    static size_t static_smem = 0;
-    if (!static_smem) {
+    // bandwidth path: persistent TMA-fed kernel, one CTA per SM (agg_tma.cuh).  Narrow variant (8-byte keys,
+    // Utf8 values of <= 7 bytes) when the key shape allows it; the wide variant is its overflow fallback.
+    using KS = fx::CountStr<typename S::Keys_>;
+    constexpr bool NARROW_OK = fx::narrow_key_ok(KS::INTS, KS::N);
+    constexpr bool NEED_WIDE = !NARROW_OK || S::NS > 0;
+    auto tma_launcher = [ctx, prm](auto kernel, std::function<void(int64_t, TableRef, int*)>* out) {
       cudaFuncAttributes fa;
-      B2_CUDA(cudaFuncGetAttributes(&fa, agg_tma_kernel<S>));
-      static_smem = fa.sharedSizeBytes;
-      B2_CUDA(cudaFuncSetAttribute(agg_tma_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   232448 - (int)static_smem));
-    }
-    TmaLayout lay;
-    if (!getenv("B2_DISABLE_TMA") && build_tma_layout<S>(prm, static_smem, &lay)) {
-      l.small = [ctx, prm, lay](int64_t n, TableRef tbl, int* status) {
+      B2_CUDA(cudaFuncGetAttributes(&fa, kernel));
+      B2_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   232448 - (int)fa.sharedSizeBytes));
+      TmaLayout lay;
+      if (!build_tma_layout<S>(prm, fa.sharedSizeBytes, &lay)) return false;
+      *out = [ctx, prm, lay, kernel](int64_t n, TableRef tbl, int* status) {
         int64_t tiles = (n + TMA_TILE - 1) / TMA_TILE;
         int grid = (int)(tiles < ctx->sm_count ? tiles : ctx->sm_count);
         size_t dyn = (size_t)lay.n_stages * lay.stage_bytes;
         ctx->prof_begin();
-        agg_tma_kernel<S><<<grid, TMA_THREADS, dyn, ctx->stream>>>(prm, lay, n, tbl, status);
+        kernel<<<grid, TMA_THREADS, dyn, ctx->stream>>>(prm, lay, n, tbl, status);
         ctx->prof_end();
         B2_LAUNCHED(ctx);
       };
-      l.tma = true;
+      return true;
+    };
+    if (!getenv("B2_DISABLE_TMA")) {
+      std::function<void(int64_t, TableRef, int*)> narrow, wide;
+      bool have_narrow = false, have_wide = false;
+      if constexpr (NARROW_OK) {
+        if (prm.narrow_lits && !getenv("B2_DISABLE_NARROW")) have_narrow = tma_launcher(agg_tma_kernel<S, true>, &narrow);
+      }
+      if constexpr (NEED_WIDE) have_wide = tma_launcher(agg_tma_kernel<S, false>, &wide);
+      if (have_narrow) {
+        l.small_wide = have_wide ? wide : l.small;
+        l.small = narrow;
+        l.tma = true;
+        l.narrow = true;
+      } else if (have_wide) {
+        l.small = wide;
+        l.tma = true;
+      }
     }
   }
-  l.global = [ctx, prm, pg](int64_t rb, int64_t re, int64_t n, TableRef tbl, int* status) {
-    int64_t tiles = (re - rb + TILE_ROWS - 1) / TILE_ROWS;
-    int64_t cap = (int64_t)pg * ctx->sm_count;
-    int grid = (int)(tiles < cap ? tiles : cap);
-    ctx->prof_begin();
-    agg_global_kernel<S><<<grid, AGG_THREADS, 0, ctx->stream>>>(prm, rb, re, n, tbl, status);
-    ctx->prof_end();
-    B2_LAUNCHED(ctx);
-  };
   return l;
 }
 
@@ -134,7 +135,7 @@ template <class S> static void add_entry(std::map<std::string, FusedEntry>& m) {
 //   args qty, price, price*(1-disc), price*(1-disc)*(1+tax), disc
 using Q1Pred = Le<I<0>, LI<0>>;
 using Q1Keys = List<S<0>, S<1>>;
-using Q1Args = List<F<0>, F<1>, Mul<F<1>, Sub<LF<0>, F<2>>>, Mul<Mul<F<1>, Sub<LF<1>, F<2>>>, Add<LF<2>, F<3>>>, F<2>>;
+using Q1Args = List<F<0>, F<1>, Mul<F<1>, Sub<LF<0>, F<2>>>, Mul<Mul<F<1>, Sub<LF<0>, F<2>>>, Add<LF<0>, F<3>>>, F<2>>;
 // TPC-H Q6 (queries/q6.sql): shipdate in [a,b) and discount between lo and hi and quantity < q; sum(price*disc)
 using Q6Pred = And<And<And<And<Ge<I<0>, LI<0>>, Lt<I<0>, LI<1>>>, Ge<F<0>, LF<0>>>, Le<F<0>, LF<1>>>, Lt<F<1>, LF<2>>>;
 using Q6Args = List<Mul<F<2>, F<0>>>;
@@ -190,6 +191,9 @@ bool bind_fused_agg(Ctx* ctx, const ExprPtr& pred, const std::vector<ExprPtr>& g
     const Column& sc = batch.cols[b.str_cols[k]];
     p.savg[k] = sc.length ? (float)sc.chars_len / (float)sc.length : 0.f;
   }
+  p.narrow_lits = 1;
+  for (auto& lit : b.str_lits)
+    if (lit.size() > 7) p.narrow_lits = 0;
   for (size_t k = 0; k < b.f64_lits.size(); ++k) p.lits.f[k] = b.f64_lits[k];
   for (size_t k = 0; k < b.i64_lits.size(); ++k) p.lits.i[k] = b.i64_lits[k];
   for (size_t k = 0; k < b.str_lits.size(); ++k) p.lits.s[k] = pack_literal(b.str_lits[k]);

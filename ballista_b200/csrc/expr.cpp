@@ -321,8 +321,21 @@ std::string expr_signature(const ExprPtr& e, SlotBinder& b) {
       if (e->dtype == B2_UTF8) return "s" + std::to_string(b.slot_for(b.str_cols, e->col));
       return "x" + std::to_string(e->dtype);  // no fused support
     case B2_EXPR_LITERAL:
-      if (e->dtype == B2_FLOAT64) { b.f64_lits.push_back(e->f); return "LF" + std::to_string(b.f64_lits.size() - 1); }
-      if (e->dtype == B2_UTF8) { b.str_lits.push_back(e->s); return "LS" + std::to_string(b.str_lits.size() - 1); }
+      // equal literal values share a slot, so `p*(1-d)` and `p*(1-d)*(1+t)` expose their common subexpression
+      if (e->dtype == B2_FLOAT64) {
+        for (size_t k = 0; k < b.f64_lits.size(); ++k)
+          if (memcmp(&b.f64_lits[k], &e->f, sizeof(double)) == 0) return "LF" + std::to_string(k);
+        b.f64_lits.push_back(e->f);
+        return "LF" + std::to_string(b.f64_lits.size() - 1);
+      }
+      if (e->dtype == B2_UTF8) {
+        for (size_t k = 0; k < b.str_lits.size(); ++k)
+          if (b.str_lits[k] == e->s) return "LS" + std::to_string(k);
+        b.str_lits.push_back(e->s);
+        return "LS" + std::to_string(b.str_lits.size() - 1);
+      }
+      for (size_t k = 0; k < b.i64_lits.size(); ++k)
+        if (b.i64_lits[k] == e->i) return "LI" + std::to_string(k);
       b.i64_lits.push_back(e->i);
       return "LI" + std::to_string(b.i64_lits.size() - 1);
     case B2_EXPR_BINARY:

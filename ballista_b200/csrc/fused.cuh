@@ -18,12 +18,15 @@ namespace fx {
 
 constexpr int MAX_F = 6, MAX_I = 4, MAX_S = 2, MAX_LF = 8, MAX_LI = 8, MAX_LS = 2;
 
-// values of one row's bound slots, in registers
-struct Row {
+// values of one row's bound slots, in registers.  W is the string word: u128 holds the first 15 bytes,
+// u64 the first 7 (narrow kernels; longer key strings raise the overflow flag and the host reruns wide)
+template <class W_> struct RowT {
+  using W = W_;
   double f[MAX_F];
   int32_t i[MAX_I];
-  StrVal s[MAX_S];
+  StrValT<W_> s[MAX_S];
 };
+using Row = RowT<u128>;
 struct Lits {
   double f[MAX_LF];
   int64_t i[MAX_LI];
@@ -34,45 +37,47 @@ constexpr int cmax(int a, int b) { return a > b ? a : b; }
 
 // ---- leaves ----
 template <int K> struct F {  // Float64 column slot
-  static constexpr int NF = K + 1, NI = 0, NS = 0;
-  using type = double;
-  __device__ static double eval(const Row& r, const Lits&) { return r.f[K]; }
+  static constexpr int NF = K + 1, NI = 0, NS = 0, NLS = 0;
+  static constexpr bool IS_STR = false;
+  template <class R> __device__ static double eval(const R& r, const Lits&) { return r.f[K]; }
   static std::string sig() { return "f" + std::to_string(K); }
 };
 template <int K> struct I {  // Int32 / Date32 column slot
-  static constexpr int NF = 0, NI = K + 1, NS = 0;
-  using type = int32_t;
-  __device__ static int32_t eval(const Row& r, const Lits&) { return r.i[K]; }
+  static constexpr int NF = 0, NI = K + 1, NS = 0, NLS = 0;
+  static constexpr bool IS_STR = false;
+  template <class R> __device__ static int32_t eval(const R& r, const Lits&) { return r.i[K]; }
   static std::string sig() { return "i" + std::to_string(K); }
 };
 template <int K> struct S {  // Utf8 column slot
-  static constexpr int NF = 0, NI = 0, NS = K + 1;
-  using type = StrVal;
-  __device__ static StrVal eval(const Row& r, const Lits&) { return r.s[K]; }
+  static constexpr int NF = 0, NI = 0, NS = K + 1, NLS = 0;
+  static constexpr bool IS_STR = true;
+  template <class R> __device__ static StrValT<typename R::W> eval(const R& r, const Lits&) { return r.s[K]; }
   static std::string sig() { return "s" + std::to_string(K); }
 };
 template <int K> struct LF {
-  static constexpr int NF = 0, NI = 0, NS = 0;
-  using type = double;
-  __device__ static double eval(const Row&, const Lits& l) { return l.f[K]; }
+  static constexpr int NF = 0, NI = 0, NS = 0, NLS = 0;
+  static constexpr bool IS_STR = false;
+  template <class R> __device__ static double eval(const R&, const Lits& l) { return l.f[K]; }
   static std::string sig() { return "LF" + std::to_string(K); }
 };
 template <int K> struct LI {
-  static constexpr int NF = 0, NI = 0, NS = 0;
-  using type = int64_t;
-  __device__ static int64_t eval(const Row&, const Lits& l) { return l.i[K]; }
+  static constexpr int NF = 0, NI = 0, NS = 0, NLS = 0;
+  static constexpr bool IS_STR = false;
+  template <class R> __device__ static int64_t eval(const R&, const Lits& l) { return l.i[K]; }
   static std::string sig() { return "LI" + std::to_string(K); }
 };
 template <int K> struct LS {
-  static constexpr int NF = 0, NI = 0, NS = 0;
-  using type = StrVal;
-  __device__ static StrVal eval(const Row&, const Lits& l) { return l.s[K]; }
+  static constexpr int NF = 0, NI = 0, NS = 0, NLS = K + 1;
+  static constexpr bool IS_STR = true;
+  template <class R> __device__ static StrValT<typename R::W> eval(const R&, const Lits& l) {
+    return StrValT<typename R::W>{(typename R::W)l.s[K].bytes, l.s[K].len};
+  }
   static std::string sig() { return "LS" + std::to_string(K); }
 };
 struct True {  // absent predicate
-  static constexpr int NF = 0, NI = 0, NS = 0;
-  using type = bool;
-  __device__ static bool eval(const Row&, const Lits&) { return true; }
+  static constexpr int NF = 0, NI = 0, NS = 0, NLS = 0;
+  static constexpr bool IS_STR = false;
+  template <class R> __device__ static bool eval(const R&, const Lits&) { return true; }
   static std::string sig() { return "true"; }
 };
 
@@ -81,13 +86,15 @@ __device__ __forceinline__ double op_add(double a, double b) { return __dadd_rn(
 __device__ __forceinline__ double op_sub(double a, double b) { return __dsub_rn(a, b); }
 __device__ __forceinline__ double op_mul(double a, double b) { return __dmul_rn(a, b); }
 __device__ __forceinline__ double op_div(double a, double b) { return __ddiv_rn(a, b); }
-__device__ __forceinline__ bool str_eq(const StrVal& a, const StrVal& b) { return a.len == b.len && a.bytes == b.bytes; }
+template <class W> __device__ __forceinline__ bool str_eq(const StrValT<W>& a, const StrValT<W>& b) {
+  return a.len == b.len && a.bytes == b.bytes;
+}
 
 #define B2_FX_BINARY(NAME, TEXT, RET, BODY)                                                   \
   template <class A, class B> struct NAME {                                                   \
-    static constexpr int NF = cmax(A::NF, B::NF), NI = cmax(A::NI, B::NI), NS = cmax(A::NS, B::NS); \
-    using type = RET;                                                                         \
-    __device__ static RET eval(const Row& r, const Lits& l) {                                 \
+    static constexpr int NF = cmax(A::NF, B::NF), NI = cmax(A::NI, B::NI), NS = cmax(A::NS, B::NS), NLS = cmax(A::NLS, B::NLS); \
+    static constexpr bool IS_STR = false;                                                     \
+    template <class R> __device__ static RET eval(const R& r, const Lits& l) {                \
       auto a = A::eval(r, l);                                                                 \
       auto b = B::eval(r, l);                                                                 \
       return BODY;                                                                            \
@@ -111,15 +118,15 @@ B2_FX_BINARY(Or, "or", bool, (a | b))
 #undef B2_FX_BINARY
 
 template <class A> struct Not {
-  static constexpr int NF = A::NF, NI = A::NI, NS = A::NS;
-  using type = bool;
-  __device__ static bool eval(const Row& r, const Lits& l) { return !A::eval(r, l); }
+  static constexpr int NF = A::NF, NI = A::NI, NS = A::NS, NLS = A::NLS;
+  static constexpr bool IS_STR = false;
+  template <class R> __device__ static bool eval(const R& r, const Lits& l) { return !A::eval(r, l); }
   static std::string sig() { return "not(" + A::sig() + ")"; }
 };
 template <class A> struct ToF64 {
-  static constexpr int NF = A::NF, NI = A::NI, NS = A::NS;
-  using type = double;
-  __device__ static double eval(const Row& r, const Lits& l) { return (double)A::eval(r, l); }
+  static constexpr int NF = A::NF, NI = A::NI, NS = A::NS, NLS = A::NLS;
+  static constexpr bool IS_STR = false;
+  template <class R> __device__ static double eval(const R& r, const Lits& l) { return (double)A::eval(r, l); }
   static std::string sig() { return "f64(" + A::sig() + ")"; }
 };
 
@@ -129,22 +136,22 @@ template <class... T> struct List {
 };
 template <class L> struct ListTraits;
 template <> struct ListTraits<List<>> {
-  static constexpr int NF = 0, NI = 0, NS = 0;
+  static constexpr int NF = 0, NI = 0, NS = 0, NLS = 0;
   static std::string sig() { return ""; }
 };
 template <class H, class... T> struct ListTraits<List<H, T...>> {
   using Rest = ListTraits<List<T...>>;
-  static constexpr int NF = cmax(H::NF, Rest::NF), NI = cmax(H::NI, Rest::NI), NS = cmax(H::NS, Rest::NS);
+  static constexpr int NF = cmax(H::NF, Rest::NF), NI = cmax(H::NI, Rest::NI), NS = cmax(H::NS, Rest::NS), NLS = cmax(H::NLS, Rest::NLS);
   static std::string sig() { return H::sig() + (sizeof...(T) ? "," + Rest::sig() : std::string()); }
 };
 
 // evaluate a list of Float64 expressions into out[]
 template <class L> struct EvalF64;
 template <> struct EvalF64<List<>> {
-  __device__ static void run(const Row&, const Lits&, double*) {}
+  template <class R> __device__ static void run(const R&, const Lits&, double*) {}
 };
 template <class H, class... T> struct EvalF64<List<H, T...>> {
-  __device__ static void run(const Row& r, const Lits& l, double* out) {
+  template <class R> __device__ static void run(const R& r, const Lits& l, double* out) {
     out[0] = H::eval(r, l);
     EvalF64<List<T...>>::run(r, l, out + 1);
   }
@@ -152,35 +159,52 @@ template <class H, class... T> struct EvalF64<List<H, T...>> {
 
 // ---- key packing: ints take 4 bytes, each Utf8 key takes `SB` bytes (1 length byte + SB-1 chars),
 //      placed in list order from byte 0; byte 15 stays 0.  Host mirror: KeyLayout in agg.h ----
+// KW = u128 (15 payload bytes) or u64 (8 payload bytes, narrow kernels)
 template <class L, int SB> struct PackKey;
 template <int SB> struct PackKey<List<>, SB> {
-  __device__ static void run(const Row&, const Lits&, u128&, int, bool&) {}
+  template <class R, class KW> __device__ static void run(const R&, const Lits&, KW&, int, bool&) {}
 };
 template <class H, class... T, int SB> struct PackKey<List<H, T...>, SB> {
-  __device__ static void run(const Row& r, const Lits& l, u128& key, int byte_off, bool& overflow) {
+  template <class R, class KW> __device__ static void run(const R& r, const Lits& l, KW& key, int byte_off, bool& overflow) {
     auto v = H::eval(r, l);
     int adv = put(v, key, byte_off, overflow);
     PackKey<List<T...>, SB>::run(r, l, key, byte_off + adv, overflow);
   }
-  __device__ static int put(int32_t v, u128& key, int off, bool&) {
-    key |= (u128)(uint32_t)v << (8 * off);
+  template <class KW> __device__ static int put(int32_t v, KW& key, int off, bool&) {
+    key |= (KW)(uint32_t)v << (8 * off);
     return 4;
   }
-  __device__ static int put(const StrVal& s, u128& key, int off, bool& overflow) {
+  template <class W, class KW> __device__ static int put(const StrValT<W>& s, KW& key, int off, bool& overflow) {
     if (s.len > SB - 1) overflow = true;
-    u128 m = (SB - 1 >= 16) ? ~(u128)0 : (((u128)1 << (8 * (SB - 1))) - 1);
-    key |= ((u128)(uint8_t)s.len | ((s.bytes & m) << 8)) << (8 * off);
+    const W m = (SB - 1 >= (int)sizeof(W)) ? ~(W)0 : (((W)1 << (8 * (SB - 1))) - 1);
+    key |= ((KW)(uint8_t)s.len | ((KW)(s.bytes & m) << 8)) << (8 * off);
     return SB;
+  }
+};
+// re-pack a narrow (u64, string parts of SBN bytes) key into the wide layout (u128, string parts of SBW bytes)
+template <class L, int SBN, int SBW> struct WidenKey;
+template <int SBN, int SBW> struct WidenKey<List<>, SBN, SBW> {
+  __device__ static void run(u64, int, u128&, int) {}
+};
+template <class H, class... T, int SBN, int SBW> struct WidenKey<List<H, T...>, SBN, SBW> {
+  __device__ static void run(u64 nk, int off_n, u128& wk, int off_w) {
+    constexpr int bn = H::IS_STR ? SBN : 4, bw = H::IS_STR ? SBW : 4;
+    const u64 part = bn >= 8 ? nk : ((nk >> (8 * off_n)) & ((1ull << (8 * (bn & 7))) - 1));
+    wk |= (u128)part << (8 * off_w);
+    WidenKey<List<T...>, SBN, SBW>::run(nk, off_n + bn, wk, off_w + bw);
   }
 };
 template <class L> struct CountStr;
 template <> struct CountStr<List<>> { static constexpr int N = 0, INTS = 0; };
 template <class H, class... T> struct CountStr<List<H, T...>> {
-  static constexpr bool is_str = sizeof(typename H::type) == sizeof(StrVal);
+  static constexpr bool is_str = H::IS_STR;
   static constexpr int N = CountStr<List<T...>>::N + (is_str ? 1 : 0);
   static constexpr int INTS = CountStr<List<T...>>::INTS + (is_str ? 0 : 1);
 };
 constexpr int str_budget(int n_int, int n_str) { return n_str ? ((15 - 4 * n_int) / n_str > 15 ? 15 : (15 - 4 * n_int) / n_str) : 0; }
+// narrow keys: 8 bytes in total, strings of at most 7 characters (+ 1 length byte)
+constexpr int str_budget_narrow(int n_int, int n_str) { return n_str ? ((8 - 4 * n_int) / n_str > 8 ? 8 : (8 - 4 * n_int) / n_str) : 0; }
+constexpr bool narrow_key_ok(int n_int, int n_str) { return 4 * n_int <= 8 && (n_str == 0 || str_budget_narrow(n_int, n_str) >= 2); }
 
 }  // namespace fx
 }  // namespace b2

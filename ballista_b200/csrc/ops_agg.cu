@@ -120,7 +120,7 @@ BatchPtr HashAggregateExec::run_partial(int partition) {
     BufPtr keybuf;
     bool fused = !disable_fusion && !getenv("B2_DISABLE_FUSION") && bind_fused_agg(ctx, pred, groups, args, *b, &l, &sig);
     if (fused) {
-      if (path.empty()) path = "fused:" + sig + (l.tma ? "[tma]" : "[ld]");
+      if (path.empty()) path = "fused:" + sig + (l.tma ? (l.narrow ? "[tma,narrow]" : "[tma]") : "[ld]");
     } else {
       if (path.empty()) path = "unfused";
       const uint8_t* mask = nullptr;

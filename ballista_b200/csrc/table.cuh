@@ -118,10 +118,11 @@ __device__ __forceinline__ u64 warp_sum(u64 v) {
 }
 
 // ---- short strings held in registers: first <=15 bytes little-endian + length ----
-struct StrVal {
-  u128 bytes;
+template <class W> struct StrValT {  // W = u128 (<= 15 bytes) or u64 (<= 7 bytes: the narrow fused kernels)
+  W bytes;
   int len;
 };
+using StrVal = StrValT<u128>;
 __device__ __forceinline__ StrVal load_str(const int32_t* off, const uint8_t* chr, int64_t row) {
   int32_t b = off[row], e = off[row + 1];
   StrVal s;

@@ -47,7 +47,7 @@ def test_q1_fused_matches_oracle(ctx, O, n, parts, tma, monkeypatch):
     batches = [[ctx.tpch("lineitem", sf, bounds[p], bounds[p + 1])] for p in range(parts)]
     got, partial = run_q1(ctx, batches)
     assert partial.last_path().startswith("fused:"), partial.last_path()
-    assert ("[tma]" in partial.last_path()) == tma, partial.last_path()
+    assert ("[tma" in partial.last_path()) == tma, partial.last_path()
     want = O.q1(O.gen_lineitem(sf, 0, n), n_partitions=parts)
     assert_rows_match(got, want, ["l_returnflag", "l_linestatus"], exact=["count_order"], approx=Q1_F)
 
@@ -93,3 +93,37 @@ def test_q6_matches_oracle(ctx, O, fused, monkeypatch):
     cnt = HashAggregateExec("Partial", [], [count().alias("c")],
                             CoalesceBatchesExec(FilterExec(tpch.q6_predicate(), tpch.scan(ctx, [[li]]))))
     assert cnt.collect().to_pylist()[0]["c[count]"] == passing  # bit-exact
+
+
+@pytest.mark.parametrize("mapping,expect", [
+    ({"R": "Ret", "A": "Acc", "N": "N"}, "[tma,narrow]/small"),           # <= 3 characters: narrow 8-byte keys
+    ({"R": "Return", "A": "Accept", "N": "N"}, "/small+widekeys"),           # overflow -> redone with 15-byte keys
+])
+def test_q1_long_flag_strings(ctx, O, mapping, expect):
+    """Utf8 group keys of several characters: the narrow-key kernel handles <= 3, longer ones fall back to wide keys."""
+    import pyarrow as pa
+    from ballista_b200 import tpch
+    sf, n = 0.05, 70_000
+    cols = O.gen_lineitem(sf, 0, n)
+    want = O.q1(cols)
+    rb = O.to_arrow(cols, tpch.Q1_COLUMNS)
+    rf = pa.array([mapping[v] for v in rb.column("l_returnflag").to_pylist()], pa.utf8())
+    rb = rb.set_column(rb.schema.get_field_index("l_returnflag"), "l_returnflag", rf)
+    got, partial = run_q1(ctx, [[rb]])
+    assert partial.last_path().endswith(expect), partial.last_path()
+    for r in got:
+        assert r["l_returnflag"] in mapping.values()
+        r["l_returnflag"] = r["l_returnflag"][0]
+    assert_rows_match(got, want, ["l_returnflag", "l_linestatus"], exact=["count_order"], approx=Q1_F)
+
+
+def test_q1_key_strings_beyond_packed_budget_are_rejected(ctx, O):
+    """Two Utf8 keys share 15 packed bytes (6 characters each): longer values are NotImplemented, loudly."""
+    import pyarrow as pa
+    from ballista_b200 import NotImplementedOnGpu, tpch
+    cols = O.gen_lineitem(0.05, 0, 5000)
+    rb = O.to_arrow(cols, tpch.Q1_COLUMNS)
+    rf = pa.array(["Returned!" for _ in range(rb.num_rows)], pa.utf8())
+    rb = rb.set_column(rb.schema.get_field_index("l_returnflag"), "l_returnflag", rf)
+    with pytest.raises(NotImplementedOnGpu):
+        run_q1(ctx, [[rb]])

@@ -230,11 +230,11 @@ def q1(cols, n_partitions=1, date_lit=DATE_1998_09_02):
     return sorted(rows, key=lambda r: (r["l_returnflag"], r["l_linestatus"]))
 
 
-def q6(cols, n_partitions=1):
+def q6(cols, n_partitions=1, date_lo=DATE_1994_01_01, date_hi=DATE_1995_01_01, quantity_lt=24.0):
     n = len(cols["l_quantity"])
     passing = C.c_uint64(0)
     lo, hi = 0.06 - 0.01, 0.06 + 0.01  # folded in IEEE f64 exactly as the reference does at run time
     rev = lib().oracle_q6(C.c_int64(n), _ptr(cols["l_shipdate"]), _ptr(cols["l_discount"]), _ptr(cols["l_quantity"]),
-                          _ptr(cols["l_extendedprice"]), C.c_int32(DATE_1994_01_01), C.c_int32(DATE_1995_01_01),
-                          C.c_double(lo), C.c_double(hi), C.c_double(24.0), n_partitions, C.byref(passing))
+                          _ptr(cols["l_extendedprice"]), C.c_int32(date_lo), C.c_int32(date_hi),
+                          C.c_double(lo), C.c_double(hi), C.c_double(quantity_lt), n_partitions, C.byref(passing))
     return float(rev), int(passing.value)

@@ -24,7 +24,7 @@ __device__ __forceinline__ int smem_group_id(SmallShared<NA, NC>& sh, const Key1
     unsigned st = *(volatile unsigned*)&sh.state[h];
     if (st == 2u) {
       Key128 k = sh.key[h];
-      if (key_eq(k, key)) return (int)sh.gid[h];
+      if (key_eq(k, key)) return sh.gid[h] == 0xFFFF ? -1 : (int)sh.gid[h];  // 0xFFFF: seen after the CTA ran out of ids
       h = (h + 1) & (SMEM_SLOTS - 1);
     } else if (st == 0u) {
       if (atomicCAS(&sh.state[h], 0u, 1u) == 0u) {

@@ -68,6 +68,15 @@ template <class S> static AggLaunch make_launch(Ctx* ctx, const typename S::Para
     if (is_fused<S>::value) ctx->prof_end();
     B2_LAUNCHED(ctx);
   };
+  l.global = [ctx, prm, pg](int64_t rb, int64_t re, int64_t n, TableRef tbl, int* status) {
+    int64_t tiles = (re - rb + TILE_ROWS - 1) / TILE_ROWS;
+    int64_t cap = (int64_t)pg * ctx->sm_count;
+    int grid = (int)(tiles < cap ? tiles : cap);
+    if (is_fused<S>::value) ctx->prof_begin();
+    agg_global_kernel<S><<<grid, AGG_THREADS, 0, ctx->stream>>>(prm, rb, re, n, tbl, status);
+    if (is_fused<S>::value) ctx->prof_end();
+    B2_LAUNCHED(ctx);
+  };
   if constexpr (is_fused<S>::value) {
     // bandwidth path: persistent TMA-fed kernel, one CTA per SM (agg_tma.cuh).  Narrow variant (8-byte keys,
     // Utf8 values of <= 7 bytes) when the key shape allows it; the wide variant is its overflow fallback.

@@ -104,7 +104,7 @@ template <int NA, class KW> __device__ __forceinline__ int tma_group_id(TmaShare
   for (int probe = 0; probe < 4 * SMEM_SLOTS; ++probe) {
     const unsigned m = *(volatile unsigned*)&sh.meta[h];
     if (m > 1u) {
-      if (sh.key[h] == key) return (int)(m >> 8);
+      if (sh.key[h] == key) return (m >> 8) == 0xFFFFu ? -1 : (int)(m >> 8);  // 0xFFFF: CTA ran out of ids
       h = (h + 1) & (SMEM_SLOTS - 1);
     } else if (m == 0u) {
       if (atomicCAS(&sh.meta[h], 0u, 1u) == 0u) {
@@ -135,7 +135,7 @@ template <int NA, class KW> __device__ __forceinline__ int tma_group_id_fast(Tma
   const unsigned h = key_hash32(key);
   const unsigned m = *(volatile unsigned*)&sh.meta[h];
   const KW k = sh.key[h];
-  if (m > 1u && k == key) return (int)(m >> 8);
+  if (m > 1u && k == key && (m >> 8) != 0xFFFFu) return (int)(m >> 8);
   return tma_group_id_slow(&sh, key);
 }
 

@@ -127,3 +127,19 @@ def test_q1_key_strings_beyond_packed_budget_are_rejected(ctx, O):
     rb = rb.set_column(rb.schema.get_field_index("l_returnflag"), "l_returnflag", rf)
     with pytest.raises(NotImplementedOnGpu):
         run_q1(ctx, [[rb]])
+
+
+@pytest.mark.parametrize("n", [3000, 200_000])
+def test_fused_high_cardinality_falls_back_to_global_table(ctx, O, n):
+    """group by l_orderkey: the per-CTA directory overflows (> 128 groups), the launch aborts and the batch is redone
+    on the HBM hash table (agg_global_kernel) — regression for the directory's out-of-ids sentinel."""
+    from ballista_b200 import HashAggregateExec, MemoryExec, col, sum as sum_, tpch
+    sf = 0.05
+    li = ctx.tpch("lineitem", sf, 0, n, columns=["l_orderkey", "l_quantity"])
+    partial = HashAggregateExec("Partial", [col("l_orderkey")], [sum_(col("l_quantity")).alias("q")], tpch.scan(ctx, [[li]]))
+    got = partial.collect().to_pylist()
+    assert partial.last_path().startswith("fused:") and partial.last_path().endswith("/global"), partial.last_path()
+    host = O.gen_lineitem(sf, 0, n)
+    rep, sums, counts = O.hash_aggregate([host["l_orderkey"]], [host["l_quantity"]])
+    want = [{"l_orderkey": int(host["l_orderkey"][r]), "q[sum]": float(sums[g, 0])} for g, r in enumerate(rep)]
+    assert_rows_match(got, want, ["l_orderkey"], approx=["q[sum]"])

@@ -11,7 +11,7 @@ stage hop), HashAggregateExec(Final), and the device->host read of the 4 result 
 
   value    : rows of all ranks / max-over-ranks step time, inputs resident in HBM
   e2e      : same plan through the C ABI fed with HOST (pinned) Arrow RecordBatches, H2D inside the timed region
-  roofline : the fused scan kernel (agg_small_kernel<Q1>) — 46 algorithmic bytes per row over its
+  roofline : the fused scan kernel (agg_tma_kernel<Q1>) — 46 algorithmic bytes per row over its
              mean launch duration, CUDA events on the launching stream, vs the measured HBM copy bandwidth
   cpu_baseline : oracle/ (C++ restatement of the DataFusion plan, one thread per partition) on a bounded sample
 
@@ -39,7 +39,7 @@ Q1_BYTES_PER_ROW = 46  # 4 x f64 + date32 + 2 x (int32 offset + 1
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--sf", type=float, default=100.0, help="scale factor of the per-GPU partition (weak) / table (strong)")
@@ -56,31 +56,68 @@ def parse_args():
 # clocks: sample nvidia-smi while the timed region runs
 # ---------------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons DURING the timed region: NVML every 5 ms (nvidia-smi as a fallback)."""
     BAD = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown")
 
     def __init__(self, gpu_index):
         super().__init__(daemon=True)
         self.idx, self.stop_flag, self.sm, self.reasons, self.sm_max = gpu_index, False, [], set(), None
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(gpu_index))
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nvml = None
 
-    def _query(self, fields):
+    @staticmethod
+    def _physical_index(i):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                return int(vis.split(",")[i])
+            except Exception:
+                pass
+        return i
+
+    def _smi(self, fields):
         out = subprocess.run(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={fields}", "--format=csv,noheader,nounits"],
                              capture_output=True, text=True, timeout=10).stdout.strip()
         return [x.strip() for x in out.split(",")]
 
     def run(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        fields = "clocks.sm," + ",".join("clocks_event_reasons." + n for n in names)
+        if self.nvml is not None:
+            n = self.nvml
+            bits = {"hw_slowdown": n.nvmlClocksThrottleReasonHwSlowdown,
+                    "hw_thermal_slowdown": n.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": n.nvmlClocksThrottleReasonSwThermalSlowdown,
+                    "sw_power_cap": n.nvmlClocksThrottleReasonSwPowerCap}
+            while not self.stop_flag:
+                try:
+                    self.sm.append(float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM)))
+                    r = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    for k, bit in bits.items():
+                        if r & bit:
+                            self.reasons.add(k)
+                except Exception:
+                    pass
+                time.sleep(0.005)
+            return
+        fields = "clocks.sm," + ",".join("clocks_event_reasons." + x for x in names)
         try:
-            self.sm_max = float(self._query("clocks.max.sm")[0])
+            self.sm_max = float(self._smi("clocks.max.sm")[0])
         except Exception:
             pass
         while not self.stop_flag:
             try:
-                v = self._query(fields)
+                v = self._smi(fields)
                 self.sm.append(float(v[0]))
-                for n, flag in zip(names, v[1:]):
+                for k, flag in zip(names, v[1:]):
                     if flag.lower().startswith("active"):
-                        self.reasons.add(n)
+                        self.reasons.add(k)
             except Exception:
                 pass
             time.sleep(0.05)
@@ -89,7 +126,8 @@ class ClockSampler(threading.Thread):
         self.stop_flag = True
         self.join(timeout=15)
         return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max,
-                "reasons": sorted(self.reasons), "samples": len(self.sm)}
+                "reasons": sorted(self.reasons), "samples": len(self.sm),
+                "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def measured_peaks():
@@ -104,7 +142,8 @@ def measured_peaks():
 # host-side helpers
 # ---------------------------------------------------------------------------------------------------------
 def env_rank():
-    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    from ballista_b200 import cluster
+    return cluster.env_rank()
 
 
 def mem_available_bytes():
@@ -165,10 +204,8 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = b2.Context(local_rank)
-    if world > 1:
-        box = [b2.Context.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0)
-        ctx.comm_init(rank, world, box[0])
+    from ballista_b200 import cluster
+    cluster.attach_communicator(ctx, dist, rank, world)
     stream = torch.cuda.ExternalStream(ctx.cuda_stream)
 
     # ---- workload: this rank's lineitem partition, generated in HBM (setup, untimed) ----
@@ -179,7 +216,7 @@ def run_b200(args):
     else:
         table_sf = args.sf
         total = _capi.lib().b2_tpch_num_rows(b"lineitem", float(args.sf))
-        r0, r1 = total * rank // world, total * (rank + 1) // world
+        r0, r1 = cluster.partition_rows(total, world, rank, align=32)
         rows_local = r1 - r0
     rows_total = rows_local * world if args.scaling == "weak" else _capi.lib().b2_tpch_num_rows(b"lineitem", float(args.sf))
     # batches of at most 2^30 rows (Utf8 offsets are int32)
@@ -222,16 +259,13 @@ def run_b200(args):
         if profile:
             ctx.set_profiling(False)
         clocks = sampler.result()
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()), launches, kern, clocks, table, partial
+        return cluster.max_over_ranks(dist, torch, ms, world), launches, kern, clocks, table, partial
 
     # ---- value: inputs resident in HBM ----
     ms, launches, (kern_ms, kern_n), clocks, table, partial = timed(dev_batches, args.steps, args.warmup, True)
     rows = table.to_pylist()
     passed = check_q1_rows(rows, rows_total)
-    assert partial.last_path().startswith("fused:"), partial.last_path()
+    assert partial.last_path().startswith("fused:") and "[tma" in partial.last_path(), partial.last_path()
     value = rows_total * args.steps / (ms / 1e3)
     peaks = measured_peaks()
     peak = peaks.get("hbm_gbs")
@@ -239,7 +273,7 @@ def run_b200(args):
     if not peak:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     achieved = (Q1_BYTES_PER_ROW * rows_local * args.steps / max(kern_n, 1) * 1.0) / (kern_ms / max(kern_n, 1) / 1e3) / 1e9 if kern_n else None
-    roofline = {"bound": "hbm", "kernel": "agg_small_kernel<FusedSrc<Q1>> (scan+filter+expr+partial aggregate)",
+    roofline = {"bound": "hbm", "kernel": "agg_tma_kernel<FusedSrc<Q1>, narrow> (TMA-fed scan + filter + expressions + partial aggregate)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                 "traffic": None, "peak_source": peak_src, "launches": kern_n,
                 "avg_launch_ms": kern_ms / kern_n if kern_n else None,

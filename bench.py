@@ -387,12 +387,20 @@ def run_reference(args):
                     "no-CSE temporaries, byte-key hash aggregate); the Rust reference itself cannot be built here"}
 
 
+def emit(real_stdout, obj):
+    os.write(real_stdout, (json.dumps(obj) + "\n").encode())
+
+
 def main():
     args = parse_args()
+    # stdout carries exactly ONE JSON line: anything libraries print (e.g. NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         out = run_reference(args)
         if out is not None:
-            print(json.dumps(out), flush=True)
+            emit(real_stdout, out)
         return
     ctx, out, dev_batches, timed, env = run_b200(args)
     rank, world, torch = env
@@ -405,7 +413,7 @@ def main():
                                "sample": f"first {n} rows of the SF{args.sf:g} lineitem, one pass of {sec:.2f} s on "
                                          f"{threads} threads (oracle/: C++ restatement of the DataFusion plan)"}
     if rank == 0:
-        print(json.dumps(out), flush=True)
+        emit(real_stdout, out)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()

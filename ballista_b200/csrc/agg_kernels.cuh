@@ -21,6 +21,7 @@ template <int NA, int NC>
 __device__ __forceinline__ int smem_group_id(SmallShared<NA, NC>& sh, const Key128& key) {
   unsigned h = (unsigned)key_hash(key) & (SMEM_SLOTS - 1);
   for (int probe = 0; probe < 4 * SMEM_SLOTS; ++probe) {
+    if (*(volatile int*)&sh.abort) return -1;  // the CTA already ran out of ids: stop probing a full table
     unsigned st = *(volatile unsigned*)&sh.state[h];
     if (st == 2u) {
       Key128 k = sh.key[h];

@@ -102,6 +102,7 @@ __device__ __forceinline__ uint32_t key_hash32(u128 k) {
 template <int NA, class KW> __device__ __forceinline__ int tma_group_id(TmaShared<NA, KW>& sh, const KW key) {
   unsigned h = key_hash32(key);
   for (int probe = 0; probe < 4 * SMEM_SLOTS; ++probe) {
+    if (*(volatile int*)&sh.abort) return -1;  // the CTA already ran out of ids: stop probing a full table
     const unsigned m = *(volatile unsigned*)&sh.meta[h];
     if (m > 1u) {
       if (sh.key[h] == key) return (m >> 8) == 0xFFFFu ? -1 : (int)(m >> 8);  // 0xFFFF: CTA ran out of ids

@@ -234,6 +234,8 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
     std::vector<std::pair<size_t, std::vector<uint8_t>>> bools;  // bit-pack after the sync
     for (size_t ci = 0; ci < b.cols.size(); ++ci) {
       const Column& col = b.cols[ci];
+      if (!col.data) fail(B2_ERR_EXECUTION, "internal: column '" + b.schema.fields[ci].name +
+                                                "' was pruned upstream but is being exported");
       auto* p = new ArrayPriv;
       ArrowArray* a = &top->child_store[ci];
       a->length = col.length;

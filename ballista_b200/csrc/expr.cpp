@@ -373,4 +373,13 @@ std::string expr_signature(const ExprPtr& e, SlotBinder& b) {
   return "?";
 }
 
+void expr_columns(const ExprPtr& e, std::vector<char>& used) {
+  if (!e) return;
+  if (e->kind == B2_EXPR_COLUMN && e->col >= 0) {
+    if ((int)used.size() <= e->col) used.resize(e->col + 1, 0);
+    used[e->col] = 1;
+  }
+  for (auto& c : e->ch) expr_columns(c, used);
+}
+
 }  // namespace b2

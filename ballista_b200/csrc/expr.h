@@ -52,6 +52,9 @@ struct SlotBinder {
 };
 std::string expr_signature(const ExprPtr& e, SlotBinder& b);
 
+// marks used[c] = 1 for every input column the expression reads (used is resized as needed)
+void expr_columns(const ExprPtr& e, std::vector<char>& used);
+
 // column-at-a-time evaluation over an HBM batch (the unfused path; eval.cu)
 Column eval_expr(Ctx* ctx, const ExprPtr& e, const Batch& batch);
 

@@ -28,11 +28,21 @@ struct JoinTable {
   u64 cap = 0;
   int64_t n_build = 0;
   BufPtr keys, head, count, next;
+  // 32-bit-key variant (join_build32): slots[cap] = (key << 32) | head_row; flags = {dup flag, -, count(8 B)}
+  bool k32 = false;
+  BufPtr slots, flags;
+  bool dups_known = false, has_dups = false;
 };
 std::shared_ptr<JoinTable> join_build(Ctx* ctx, const Key128* keys, int64_t n);
 // probe: returns number of output pairs; left_idx / right_idx are uint32 row indices in probe order
 int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* probe_keys, int64_t n_probe, BufPtr* left_idx,
                    BufPtr* right_idx);
+
+// single Int32 / Date32 key: fused filter (mask may be null) + build / probe over the uncompacted key column;
+// row ids are those of the unfiltered batch
+std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const uint8_t* mask, int64_t n);
+int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const uint8_t* mask, int64_t n_probe,
+                     BufPtr* left_idx, BufPtr* right_idx);
 
 // repartition.cu: rows -> destination partition by hash of packed key; returns the stable permutation
 // (destination-major) and fills counts[n_out]
@@ -65,6 +75,10 @@ struct Op {
     children[0]->partitioning(scheme, n);
   }
   virtual StreamPtr execute(int partition) = 0;
+  // Column pruning at execution time: a parent announces which of this operator's output columns it will
+  // read (empty = all).  Operators that assemble their output by gathers (HashJoinExec) leave the others
+  // elided (Column::data == nullptr); the schema is unchanged.  Default: children produce everything.
+  virtual void require(const std::vector<char>& need) { (void)need; }
   int n_partitions() const {
     int s, n;
     partitioning(&s, &n);

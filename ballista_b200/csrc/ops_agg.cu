@@ -92,6 +92,12 @@ BatchPtr HashAggregateExec::emit(AggRunner& r, bool partial, const std::vector<i
 }
 
 BatchPtr HashAggregateExec::run_partial(int partition) {
+  {  // column pruning: tell the input which columns the group / argument expressions read
+    std::vector<char> used(children[0]->schema().fields.size(), 0);
+    for (auto& g : groups) expr_columns(g, used);
+    for (auto& a : args) expr_columns(a, used);
+    children[0]->require(used);
+  }
   // look through CoalesceBatchesExec for a FilterExec whose predicate can ride in the aggregate's scan
   Op* src = children[0].get();
   ExprPtr pred;

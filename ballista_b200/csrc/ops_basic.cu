@@ -97,6 +97,13 @@ struct FilterExec : Op {
   ExprPtr pred;
   const char* name() const override { return "FilterExec"; }
   Schema schema() const override { return children[0]->schema(); }
+  void require(const std::vector<char>& need) override {
+    if (need.empty()) return children[0]->require(need);
+    std::vector<char> n = need;
+    n.resize(children[0]->schema().fields.size(), 0);
+    expr_columns(pred, n);
+    children[0]->require(n);
+  }
   struct S : Stream {
     FilterExec* op;
     StreamPtr in;
@@ -146,6 +153,7 @@ struct CoalesceExec : Op {
   int64_t target;
   const char* name() const override { return "CoalesceBatchesExec"; }
   Schema schema() const override { return children[0]->schema(); }
+  void require(const std::vector<char>& need) override { children[0]->require(need); }
   struct S : Stream {
     CoalesceExec* op;
     StreamPtr in;

@@ -1,6 +1,8 @@
 // ops_join.cu — HashJoinExec (collect-left build + probe) and RepartitionExec (hash / round-robin; with a
 // communicator attached the hash repartition IS the in-box shuffle).  SURVEY §8a rows F, G, H.
 // Constructed where from_proto.rs:253-276 and :133-164 construct the DataFusion operators.
+#include <cstdlib>
+
 #include "ops.h"
 
 namespace b2 {
@@ -8,12 +10,30 @@ namespace b2 {
 // ------------------------------------------------------------------------------------------------------
 // HashJoinExec
 // ------------------------------------------------------------------------------------------------------
+bool op_is_filter(Op* op, ExprPtr* pred);
+bool op_is_coalesce(Op* op);
+
+// FilterExec (optionally under CoalesceBatchesExec) directly below a join side: returns the filter's input
+// and its predicate, so the join evaluates the mask itself and never compacts the side
+static Op* peel_filter(Op* op, ExprPtr* pred) {
+  Op* probe = op;
+  if (op_is_coalesce(probe)) probe = probe->children[0].get();
+  ExprPtr p;
+  if (op_is_filter(probe, &p) && !p->is_literal()) {
+    *pred = p;
+    return probe->children[0].get();
+  }
+  return op;
+}
+
 struct HashJoinExec : Op {
   std::vector<int> on_left, on_right;  // column indices
   int join_type = B2_JOIN_INNER;
   Schema out;
   std::vector<int> right_keep;  // right columns that survive the duplicate-name rule
   KeyLayout layout;
+  bool k32 = false;             // one Int32 / Date32 key per side: 8-byte-slot table, fused filters
+  std::vector<char> need;       // output columns a parent will read (empty = all)
   // build side, collected once (the reference rebuilds it per task; result-neutral)
   BatchPtr left_batch;
   std::shared_ptr<JoinTable> table;
@@ -22,6 +42,21 @@ struct HashJoinExec : Op {
   const char* name() const override { return "HashJoinExec"; }
   Schema schema() const override { return out; }
   void partitioning(int* scheme, int* n) const override { children[1]->partitioning(scheme, n); }
+
+  bool fuse() const { return k32 && !getenv("B2_DISABLE_FUSION"); }
+  bool needed(size_t out_col) const { return need.empty() || (out_col < need.size() && need[out_col]); }
+
+  void require(const std::vector<char>& n) override {
+    need = n;
+    size_t nl = children[0]->schema().fields.size(), nr = children[1]->schema().fields.size();
+    std::vector<char> l(nl, 0), r(nr, 0);
+    for (size_t c = 0; c < nl; ++c) l[c] = needed(c);
+    for (size_t k = 0; k < right_keep.size(); ++k) r[right_keep[k]] = needed(nl + k);
+    for (int c : on_left) l[c] = 1;
+    for (int c : on_right) r[c] = 1;
+    children[0]->require(l);
+    children[1]->require(r);
+  }
 
   BufPtr pack(const Batch& b, const std::vector<int>& on) {
     std::vector<Column> kc;
@@ -37,6 +72,8 @@ struct HashJoinExec : Op {
   void build() {
     if (table) return;
     Op* l = children[0].get();
+    ExprPtr pred;
+    if (fuse()) l = peel_filter(l, &pred);
     std::vector<BatchPtr> all;
     int np = l->n_partitions();
     for (int p = 0; p < np; ++p) {  // MergeExec(left): all partitions
@@ -49,25 +86,55 @@ struct HashJoinExec : Op {
     } else {
       left_batch = concat_batches(ctx, l->schema(), all);
     }
-    left_keys = pack(*left_batch, on_left);
-    table = join_build(ctx, left_keys->as<Key128>(), left_batch->num_rows);
+    if (k32) {
+      Column mask;
+      if (pred && left_batch->num_rows) mask = eval_expr(ctx, pred, *left_batch);
+      table = join_build32(ctx, left_batch->cols[on_left[0]].values<int32_t>(),
+                           mask.data ? mask.values<uint8_t>() : nullptr, left_batch->num_rows);
+      // the mask buffer is freed stream-ordered after the build kernel
+    } else {
+      left_keys = pack(*left_batch, on_left);
+      table = join_build(ctx, left_keys->as<Key128>(), left_batch->num_rows);
+    }
   }
   struct S : Stream {
     HashJoinExec* op;
     StreamPtr in;
+    ExprPtr pred;  // fused right-side FilterExec predicate (k32 path)
     BatchPtr next() override {
       BatchPtr r = in->next();
       if (!r) return nullptr;
       Ctx* ctx = op->ctx;
-      BufPtr pk = op->pack(*r, op->on_right);
       BufPtr li, ri;
-      int64_t m = join_probe(ctx, *op->table, pk->as<Key128>(), r->num_rows, &li, &ri);
+      int64_t m;
+      if (op->k32) {
+        Column mask;
+        if (pred && r->num_rows) mask = eval_expr(ctx, pred, *r);
+        m = join_probe32(ctx, *op->table, r->cols[op->on_right[0]].values<int32_t>(),
+                         mask.data ? mask.values<uint8_t>() : nullptr, r->num_rows, &li, &ri);
+      } else {
+        BufPtr pk = op->pack(*r, op->on_right);
+        m = join_probe(ctx, *op->table, pk->as<Key128>(), r->num_rows, &li, &ri);
+      }
       auto o = std::make_shared<Batch>();
       o->ctx = ctx;
       o->schema = op->out;
       o->num_rows = m;
-      for (auto& c : op->left_batch->cols) o->cols.push_back(take_column(ctx, c, li->as<uint32_t>(), m));
-      for (int c : op->right_keep) o->cols.push_back(take_column(ctx, r->cols[c], ri->as<uint32_t>(), m));
+      size_t oc = 0;
+      auto elided = [&](const Column& c) {
+        Column e;
+        e.dtype = c.dtype;
+        e.length = m;
+        return e;
+      };
+      for (auto& c : op->left_batch->cols) {
+        o->cols.push_back(op->needed(oc) ? take_column(ctx, c, li->as<uint32_t>(), m) : elided(c));
+        ++oc;
+      }
+      for (int c : op->right_keep) {
+        o->cols.push_back(op->needed(oc) ? take_column(ctx, r->cols[c], ri->as<uint32_t>(), m) : elided(r->cols[c]));
+        ++oc;
+      }
       return o;
     }
   };
@@ -75,8 +142,10 @@ struct HashJoinExec : Op {
     build();
     auto s = std::make_unique<S>();
     s->op = this;
-    s->in = children[1]->execute(partition);
-    last_path = "unfused";
+    Op* r = children[1].get();
+    if (fuse()) r = peel_filter(r, &s->pred);
+    s->in = r->execute(partition);
+    last_path = k32 ? (fuse() ? "k32:fused-filter" : "k32") : "key128";
     return s;
   }
 };
@@ -105,6 +174,7 @@ OpPtr make_hash_join(Ctx* ctx, OpPtr left, OpPtr right, std::vector<std::string>
     kd.push_back(ta);
   }
   op->layout = make_key_layout(kd);
+  op->k32 = kd.size() == 1 && (kd[0] == B2_INT32 || kd[0] == B2_DATE32);
   // output = left fields ++ right fields minus right on-columns named like their left partner (A.3)
   op->out = ls;
   for (size_t c = 0; c < rs.fields.size(); ++c) {

@@ -47,6 +47,7 @@ Column take_column(Ctx* ctx, const Column& c, const uint32_t* idx, int64_t m) {
   Column out;
   out.dtype = c.dtype;
   out.length = m;
+  if (!c.data) return out;  // elided by column pruning upstream: stays elided
   int grid = grid_for(ctx, 8, m, 256);
   if (c.dtype == B2_UTF8) {
     out.data = dev_alloc_zero(ctx, (size_t)(m + 1) * 4);
@@ -117,6 +118,10 @@ BatchPtr concat_batches(Ctx* ctx, const Schema& schema, const std::vector<BatchP
     Column c;
     c.dtype = schema.fields[ci].dtype;
     c.length = n;
+    if (!batches[0]->cols[ci].data) {  // elided by column pruning
+      out->cols.push_back(std::move(c));
+      continue;
+    }
     if (c.dtype == B2_UTF8) {
       int64_t chars = 0;
       for (auto& b : batches) chars += b->cols[ci].chars_len;

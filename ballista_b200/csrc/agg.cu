@@ -121,8 +121,7 @@ void AggRunner::consume(const AggLaunch& l, int64_t n) {
     B2_CUDA(cudaMemsetAsync(status->ptr, 0, 16, ctx->stream));
     l.small(n, delta->ref(), status->as<int>());
     B2_CUDA(cudaMemcpyAsync(&host[0], status->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaMemcpyAsync(&host[1], delta->n_groups->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    B2_READBACK(ctx, &host[1], delta->n_groups->ptr, 4);
     if (host[0] == AGG_OK) {
       ensure_main(host[1]);
       table_merge_kernel<<<grid_for(ctx, 8, (int64_t)delta->cap, 256), 256, 0, ctx->stream>>>(
@@ -152,8 +151,7 @@ void AggRunner::consume(const AggLaunch& l, int64_t n) {
     B2_CUDA(cudaMemsetAsync(status->ptr, 0, 16, ctx->stream));
     l.global(b, e, n, main->ref(), status->as<int>());
     B2_CUDA(cudaMemcpyAsync(&host[0], status->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaMemcpyAsync(&host[1], main->n_groups->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    B2_READBACK(ctx, &host[1], main->n_groups->ptr, 4);
     check_status(host[0]);
     group_bound = host[1];
   }
@@ -172,8 +170,7 @@ __global__ void table_compact_kernel(const Key128* keys, u64 cap, uint32_t* slot
 int64_t AggRunner::finish(BufPtr* slots_out) {
   int host[2] = {0, 0};
   B2_CUDA(cudaMemcpyAsync(&host[0], main->n_groups->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-  B2_CUDA(cudaMemcpyAsync(&host[1], status->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-  B2_CUDA(cudaStreamSynchronize(ctx->stream));
+  B2_READBACK(ctx, &host[1], status->ptr, 4);
   check_status(host[1]);
   int64_t ng = host[0];
   if (main->cap > (1ull << 32)) fail(B2_ERR_NOT_IMPLEMENTED, "group table beyond 2^32 slots");
@@ -278,8 +275,7 @@ Column emit_key_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64
                                                       c.chars->as<uint8_t>());
       B2_LAUNCHED(ctx);
       int32_t total = 0;
-      B2_CUDA(cudaMemcpyAsync(&total, c.data->as<int32_t>() + ng, 4, cudaMemcpyDeviceToHost, ctx->stream));
-      B2_CUDA(cudaStreamSynchronize(ctx->stream));
+      B2_READBACK(ctx, &total, c.data->as<int32_t>() + ng, 4);
       c.chars_len = total;
     }
     return c;

@@ -1,5 +1,7 @@
 // capi.cu — the extern "C" surface declared in include/ballista_b200.h.  Every entry point converts
 // internal exceptions into status codes; nothing throws across the ABI.
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -53,6 +55,7 @@ int b2_ctx_create(int device, b2_ctx** out) {
       B2_CUDA(cudaGetDeviceProperties(&prop, device));
       if (prop.major < 10) fail(B2_ERR_CUDA, std::string("device '") + prop.name + "' is not sm_100-class");
       h->c.sm_count = prop.multiProcessorCount;
+      h->c.trace = getenv("B2_TRACE") != nullptr;
       B2_CUDA(cudaStreamCreateWithFlags(&h->c.stream, cudaStreamNonBlocking));
       B2_CUDA(cudaStreamCreateWithFlags(&h->c.copy_stream, cudaStreamNonBlocking));
       B2_CUDA(cudaDeviceGetDefaultMemPool(&h->c.pool, device));
@@ -72,6 +75,12 @@ void b2_ctx_destroy(b2_ctx* ctx) {
     try { comm_destroy(&ctx->c); } catch (...) {}
   }
   cudaStreamSynchronize(ctx->c.stream);
+  if (ctx->c.trace) {
+    fprintf(stderr, "[b2 trace] %-60s %10s %8s\n", "site", "total ms", "calls");
+    for (auto& kv : ctx->c.trace_acc)
+      fprintf(stderr, "[b2 trace] %-60s %10.3f %8lld\n", kv.first.c_str(), kv.second.first * 1e3,
+              (long long)kv.second.second);
+  }
   cudaStreamDestroy(ctx->c.stream);
   cudaStreamDestroy(ctx->c.copy_stream);
   delete ctx;
@@ -87,6 +96,10 @@ int64_t b2_ctx_kernel_launches(b2_ctx* ctx) { return ctx ? ctx->c.launches : 0; 
 int b2_ctx_set_profiling(b2_ctx* ctx, int on) {
   return guard([&] {
     REQUIRE(ctx, "ctx is null");
+    if (on == 2) {  // diagnostics: restart the B2_TRACE accumulators (after warm-up)
+      ctx->c.trace_acc.clear();
+      return;
+    }
     ctx->c.profiling = on != 0;
   });
 }
@@ -272,7 +285,9 @@ const char* b2_op_last_path(b2_op* op) { return (op && op->op) ? op->op->last_pa
 int b2_stream_next_device(b2_stream* s, b2_batch** out, int* eos) {
   return guard([&] {
     REQUIRE(s && s->s && out && eos, "null argument");
+    double t0 = wall_now();
     BatchPtr b = s->s->next();
+    if (b && b->ctx && b->ctx->trace) b->ctx->trace_add("b2_stream_next_device (total host time)", wall_now() - t0);
     if (!b) {
       *eos = 1;
       *out = nullptr;

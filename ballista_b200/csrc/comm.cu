@@ -72,8 +72,7 @@ static std::vector<int64_t> allgather_counts(Ctx* ctx, const std::vector<int64_t
   B2_CUDA(cudaMemcpyAsync(dsend->ptr, mine.data(), len * 8, cudaMemcpyHostToDevice, ctx->stream));
   B2_NCCL(ncclAllGather(dsend->ptr, drecv->ptr, len, ncclInt64, ctx->comm->nccl, ctx->stream));
   std::vector<int64_t> all(len * ctx->nranks);
-  B2_CUDA(cudaMemcpyAsync(all.data(), drecv->ptr, all.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
-  B2_CUDA(cudaStreamSynchronize(ctx->stream));
+  B2_READBACK(ctx, all.data(), drecv->ptr, all.size() * 8);
   return all;
 }
 
@@ -192,9 +191,7 @@ BatchPtr comm_all_to_all(Ctx* ctx, const Batch& b, const std::vector<int64_t>& c
     std::vector<int32_t> tmp(nr + 1, 0);
     if (b.num_rows)
       for (int d = 0; d <= nr; ++d)
-        B2_CUDA(cudaMemcpyAsync(&tmp[d], b.cols[c].values<int32_t>() + send_off[d], 4, cudaMemcpyDeviceToHost,
-                                ctx->stream));
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+        B2_READBACK(ctx, &tmp[d], b.cols[c].values<int32_t>() + send_off[d], 4);
     for (int d = 0; d <= nr; ++d) chr_bounds[c][d] = tmp[d];
   }
   std::vector<int64_t> mine((size_t)nr * (1 + ncol), 0);
@@ -256,7 +253,7 @@ BatchPtr comm_all_to_all(Ctx* ctx, const Batch& b, const std::vector<int64_t>& c
     }
     out->cols.push_back(std::move(o));
   }
-  B2_CUDA(cudaStreamSynchronize(ctx->stream));
+  B2_SYNC(ctx);
   return out;
 }
 

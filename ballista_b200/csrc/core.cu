@@ -10,7 +10,9 @@ DevBuf::DevBuf(Ctx* c, size_t n) : ctx(c), bytes(n) {
   if (n == 0) return;
   // every buffer is padded so that 16-byte vector loads / TMA bulk copies of the last rows stay in bounds
   n = (n + 32 + 255) & ~(size_t)255;
+  double t0 = c->trace ? wall_now() : 0;
   cudaError_t e = cudaMallocAsync(&ptr, n, c->pool, c->stream);
+  if (c->trace) c->trace_add("cudaMallocAsync", wall_now() - t0);
   if (e != cudaSuccess) {
     cudaGetLastError();
     fail(e == cudaErrorMemoryAllocation ? B2_ERR_OOM : B2_ERR_CUDA,
@@ -18,7 +20,10 @@ DevBuf::DevBuf(Ctx* c, size_t n) : ctx(c), bytes(n) {
   }
 }
 DevBuf::~DevBuf() {
-  if (ptr) cudaFreeAsync(ptr, ctx->stream);
+  if (!ptr) return;
+  double t0 = ctx->trace ? wall_now() : 0;
+  cudaFreeAsync(ptr, ctx->stream);
+  if (ctx->trace) ctx->trace_add("cudaFreeAsync", wall_now() - t0);
 }
 BufPtr dev_alloc(Ctx* ctx, size_t bytes) { return std::make_shared<DevBuf>(ctx, bytes); }
 BufPtr dev_alloc_zero(Ctx* ctx, size_t bytes) {
@@ -267,7 +272,7 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
       a->n_buffers = (int64_t)p->buffers.size();
       a->buffers = p->buffers.data();
     }
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    B2_SYNC(ctx);
     for (auto& pr : bools) {
       auto* p = static_cast<ArrayPriv*>(top->child_store[pr.first].private_data);
       uint8_t* bits = static_cast<uint8_t*>(const_cast<void*>(p->buffers[1]));

@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <chrono>
+#include <map>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -53,7 +55,38 @@ struct Ctx {
     if (profiling && !prof_events.empty()) cudaEventRecord(prof_events.back().second, stream);
   }
   void activate() const { B2_CUDA(cudaSetDevice(device)); }
+  // B2_TRACE=1: host wall time per stream synchronisation site and in the allocator, printed at ctx destroy
+  bool trace = false;
+  std::map<std::string, std::pair<double, int64_t>> trace_acc;
+  void trace_add(const std::string& label, double seconds) {
+    auto& e = trace_acc[label];
+    e.first += seconds;
+    e.second++;
+  }
 };
+inline double wall_now() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+inline void sync_stream(Ctx* ctx, const char* where) {
+  if (!ctx->trace) {
+    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    return;
+  }
+  double t0 = wall_now();
+  B2_CUDA(cudaStreamSynchronize(ctx->stream));
+  ctx->trace_add(where, wall_now() - t0);
+}
+// device -> host read of a few bytes followed by a stream sync (the memcpy to pageable memory blocks)
+inline void read_back(Ctx* ctx, void* dst, const void* src, size_t bytes, const char* where) {
+  double t0 = ctx->trace ? wall_now() : 0;
+  B2_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  B2_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (ctx->trace) ctx->trace_add(where, wall_now() - t0);
+}
+#define B2_STR2(x) #x
+#define B2_STR(x) B2_STR2(x)
+#define B2_SYNC(ctx) ::b2::sync_stream((ctx), __FILE__ ":" B2_STR(__LINE__))
+#define B2_READBACK(ctx, dst, src, bytes) ::b2::read_back((ctx), (dst), (src), (bytes), __FILE__ ":" B2_STR(__LINE__))
 
 // count + check a kernel launch
 #define B2_LAUNCHED(ctx)                      \

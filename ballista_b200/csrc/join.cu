@@ -94,8 +94,7 @@ int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* pkeys, int64_t n,
     B2_LAUNCHED(ctx);
     scan_sums_kernel<<<1, SCAN_THREADS, 0, ctx->stream>>>(sums->as<int64_t>(), nb);
     B2_LAUNCHED(ctx);
-    B2_CUDA(cudaMemcpyAsync(&total, sums->as<int64_t>() + nb, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    B2_READBACK(ctx, &total, sums->as<int64_t>() + nb, 8);
   }
   if (total >= (int64_t)NIL) fail(B2_ERR_NOT_IMPLEMENTED, "join output beyond 2^32-2 rows in one batch");
   *left_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
@@ -142,11 +141,85 @@ __device__ __forceinline__ u64 ld_slot_volatile(const u64* p) {
   return v;
 }
 
-__global__ void join_build32_kernel(const int32_t* __restrict__ key, const uint8_t* __restrict__ mask, int64_t n,
-                                    u64* slots, u64 capmask, uint32_t* next, int* flags) {
+// ---- inline FilterExec predicate (RowPred) ----
+template <class T> __device__ __forceinline__ bool cmp_op(int op, T a, T b) {
+  switch (op) {
+    case B2_OP_EQ: return a == b;
+    case B2_OP_NOTEQ: return a != b;
+    case B2_OP_LT: return a < b;
+    case B2_OP_LTEQ: return a <= b;
+    case B2_OP_GT: return a > b;
+    default: return a >= b;
+  }
+}
+__device__ __forceinline__ bool row_pred(const RowPred& p, int64_t i) {
+  bool ok = true;
+  for (int t = 0; t < p.n; ++t) {
+    if (p.is_f64[t])
+      ok = ok && cmp_op<double>(p.op[t], static_cast<const double*>(p.col[t])[i], p.flit[t]);
+    else
+      ok = ok && cmp_op<long long>(p.op[t], (long long)static_cast<const int32_t*>(p.col[t])[i], p.ilit[t]);
+  }
+  return ok;
+}
+
+static bool flatten_and(const ExprPtr& e, std::vector<ExprPtr>* terms) {
+  if (e->kind == B2_EXPR_BINARY && e->op == B2_OP_AND) return flatten_and(e->ch[0], terms) && flatten_and(e->ch[1], terms);
+  terms->push_back(e);
+  return true;
+}
+static int flip_cmp(int op) {
+  switch (op) {
+    case B2_OP_LT: return B2_OP_GT;
+    case B2_OP_LTEQ: return B2_OP_GTEQ;
+    case B2_OP_GT: return B2_OP_LT;
+    case B2_OP_GTEQ: return B2_OP_LTEQ;
+    default: return op;
+  }
+}
+bool compile_row_pred(const ExprPtr& pred, const Batch& batch, RowPred* out) {
+  std::vector<ExprPtr> terms;
+  flatten_and(pred, &terms);
+  if (terms.empty() || terms.size() > 4) return false;
+  RowPred rp;
+  for (auto& t : terms) {
+    if (t->kind != B2_EXPR_BINARY) return false;
+    int op = t->op;
+    if (op != B2_OP_EQ && op != B2_OP_NOTEQ && op != B2_OP_LT && op != B2_OP_LTEQ && op != B2_OP_GT && op != B2_OP_GTEQ)
+      return false;
+    ExprPtr c = t->ch[0], l = t->ch[1];
+    if (c->kind == B2_EXPR_LITERAL && l->kind == B2_EXPR_COLUMN) {
+      std::swap(c, l);
+      op = flip_cmp(op);
+    }
+    if (c->kind != B2_EXPR_COLUMN || l->kind != B2_EXPR_LITERAL) return false;
+    const Column& col = batch.cols[c->col];
+    int k = rp.n++;
+    rp.op[k] = op;
+    rp.col[k] = col.data->ptr;
+    if ((col.dtype == B2_INT32 || col.dtype == B2_DATE32) &&
+        (l->dtype == B2_INT32 || l->dtype == B2_DATE32 || l->dtype == B2_INT64)) {
+      rp.is_f64[k] = 0;
+      rp.ilit[k] = l->i;
+      rp.flit[k] = 0;
+    } else if (col.dtype == B2_FLOAT64 && l->dtype == B2_FLOAT64) {
+      rp.is_f64[k] = 1;
+      rp.flit[k] = l->f;
+      rp.ilit[k] = 0;
+    } else {
+      return false;
+    }
+  }
+  *out = rp;
+  return true;
+}
+
+__global__ void join_build32_kernel(const int32_t* __restrict__ key, RowPred pred, const uint8_t* __restrict__ mask,
+                                    int64_t n, u64* slots, u64 capmask, uint32_t* next, int* flags) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     if (mask && !mask[i]) continue;
+    if (!row_pred(pred, i)) continue;
     uint32_t k = (uint32_t)key[i];
     u64 h = slot_of(k, capmask);
     u64 mine = ((u64)k << 32) | (uint32_t)i;
@@ -177,15 +250,16 @@ __global__ void join_build32_kernel(const int32_t* __restrict__ key, const uint8
   }
 }
 
-__global__ void mask_count_kernel(const uint8_t* __restrict__ mask, int64_t n, unsigned long long* out) {
+__global__ void pass_count_kernel(RowPred pred, const uint8_t* __restrict__ mask, int64_t n, unsigned long long* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   unsigned c = 0;
-  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) c += mask[i] != 0;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) c += (!mask || mask[i]) && row_pred(pred, i);
   for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, (unsigned long long)c);
 }
 
-std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const uint8_t* mask, int64_t n) {
+std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const RowPred& pred, const uint8_t* mask,
+                                        int64_t n) {
   if (n >= (int64_t)NIL) fail(B2_ERR_NOT_IMPLEMENTED, "join build side beyond 2^32-2 rows");
   auto t = std::make_shared<JoinTable>();
   t->ctx = ctx;
@@ -194,13 +268,12 @@ std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const uint
   t->flags = dev_alloc_zero(ctx, 16);
   // size the table for the rows that pass the fused filter, so that a selective build side stays L2-resident
   int64_t n_in = n;
-  if (mask && n > (1 << 18)) {
-    mask_count_kernel<<<grid_for(ctx, 8, n, 1024), 256, 0, ctx->stream>>>(
-        mask, n, reinterpret_cast<unsigned long long*>(t->flags->as<char>() + 8));
+  if ((mask || pred.n) && n > (1 << 18)) {
+    pass_count_kernel<<<grid_for(ctx, 8, n, 1024), 256, 0, ctx->stream>>>(
+        pred, mask, n, reinterpret_cast<unsigned long long*>(t->flags->as<char>() + 8));
     B2_LAUNCHED(ctx);
     unsigned long long c = 0;
-    B2_CUDA(cudaMemcpyAsync(&c, t->flags->as<char>() + 8, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    B2_READBACK(ctx, &c, t->flags->as<char>() + 8, 8);
     n_in = (int64_t)c;
   }
   u64 cap = 64;
@@ -210,8 +283,8 @@ std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const uint
   t->next = dev_alloc(ctx, (size_t)(n + 1) * 4);
   B2_CUDA(cudaMemsetAsync(t->slots->ptr, 0xFF, cap * 8, ctx->stream));
   if (n) {
-    join_build32_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(key, mask, n, t->slots->as<u64>(), cap - 1,
-                                                                         t->next->as<uint32_t>(), t->flags->as<int>());
+    join_build32_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(
+        key, pred, mask, n, t->slots->as<u64>(), cap - 1, t->next->as<uint32_t>(), t->flags->as<int>());
     B2_LAUNCHED(ctx);
   }
   t->dups_known = false;
@@ -219,49 +292,68 @@ std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const uint
 }
 
 constexpr int JP_THREADS = SCAN_THREADS;  // block_exclusive_scan is written for this CTA size
-constexpr int JP_ITEMS = 4;
+constexpr int JP_ITEMS = 8;
 constexpr int JP_TILE = JP_THREADS * JP_ITEMS;
 
-// tile status word of the single-pass ordered compaction: flag (2 bits) | value (62 bits)
-constexpr u64 ST_AGG = 1ull << 62, ST_PREFIX = 2ull << 62, ST_VAL = (1ull << 62) - 1;
-__device__ __forceinline__ void st_status(u64* p, u64 v) {
-  asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+// predicate over the JP_ITEMS consecutive rows of one thread, 128-bit loads (r0 is a multiple of 8)
+__device__ __forceinline__ void row_pred_vec(const RowPred& p, int64_t r0, bool* pass) {
+  for (int t = 0; t < p.n; ++t) {
+    if (p.is_f64[t]) {
+      const double* c = static_cast<const double*>(p.col[t]) + r0;
+#pragma unroll
+      for (int j = 0; j < JP_ITEMS; j += 2) {
+        double2 v = ld_stream_f64x2(c + j);
+        pass[j] = pass[j] && cmp_op<double>(p.op[t], v.x, p.flit[t]);
+        pass[j + 1] = pass[j + 1] && cmp_op<double>(p.op[t], v.y, p.flit[t]);
+      }
+    } else {
+      const int32_t* c = static_cast<const int32_t*>(p.col[t]) + r0;
+#pragma unroll
+      for (int j = 0; j < JP_ITEMS; j += 4) {
+        int4 v = ld_stream_i32x4(c + j);
+        long long lit = p.ilit[t];
+        pass[j] = pass[j] && cmp_op<long long>(p.op[t], v.x, lit);
+        pass[j + 1] = pass[j + 1] && cmp_op<long long>(p.op[t], v.y, lit);
+        pass[j + 2] = pass[j + 2] && cmp_op<long long>(p.op[t], v.z, lit);
+        pass[j + 3] = pass[j + 3] && cmp_op<long long>(p.op[t], v.w, lit);
+      }
+    }
+  }
 }
 
-// One pass over the probe side: filter mask -> table lookup -> (build_row, probe_row) pairs in PROBE ORDER
-// (the reference's output order).  Tiles are handed out by an atomic ticket, so tile t-1 has always started
-// before tile t; each tile publishes its match count, then resolves its output offset with a warp-wide
-// decoupled look-back over its predecessors' status words (no second probe pass, no global scan kernels).
-// COUNT_ONLY sizes the output of a join whose build side has duplicate keys (chains are walked to count).
-template <bool COUNT_ONLY, bool DUPS>
+// Probe-side kernel: filter (inline predicate and / or mask) -> table lookup -> (build_row, probe_row) pairs
+// in PROBE ORDER (the reference's output order).  Three modes, none of which probes a row twice on the
+// primary-key path:
+//   PROBE_STAGE  : pairs of tile t are written, compacted, at [t * JP_TILE, ...) of staging buffers (a tile has
+//                  at most JP_TILE matches when build keys are unique) and tile_cnt[t] = match count; a small
+//                  scan + `join_compact_kernel` then move each tile's run to its final offset.
+//   PROBE_COUNT  : tile_cnt[t] only (build side with duplicate keys: chains are walked to size the output).
+//   PROBE_WRITE  : pairs go straight to tile_cnt[t] (already scanned to offsets) + offset within tile.
+enum { PROBE_STAGE = 0, PROBE_COUNT = 1, PROBE_WRITE = 2 };
+template <int MODE, bool DUPS>
 __global__ void __launch_bounds__(JP_THREADS)
-    join_probe32_kernel(const int32_t* __restrict__ key, const uint8_t* __restrict__ mask, int64_t n, bool vec,
-                        const u64* __restrict__ slots, u64 capmask, const uint32_t* __restrict__ next,
-                        uint32_t* __restrict__ left_idx, uint32_t* __restrict__ right_idx, u64* status,
-                        unsigned long long* ticket, unsigned long long* total_out) {
-  __shared__ unsigned long long base_s, tile_s;
+    join_probe32_kernel(const int32_t* __restrict__ key, RowPred pred, const uint8_t* __restrict__ mask, int64_t n,
+                        bool vec, const u64* __restrict__ slots, u64 capmask, const uint32_t* __restrict__ next,
+                        uint32_t* __restrict__ left_idx, uint32_t* __restrict__ right_idx, int64_t* tile_cnt) {
   const int64_t n_tiles = (n + JP_TILE - 1) / JP_TILE;
-  const int lane = threadIdx.x & 31;
-  while (true) {
-    if (threadIdx.x == 0) tile_s = atomicAdd(ticket, 1ull);
-    __syncthreads();
-    const int64_t tile = (int64_t)tile_s;
-    if (tile >= n_tiles) break;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     int64_t r0 = tile * JP_TILE + (int64_t)threadIdx.x * JP_ITEMS;
     uint32_t k[JP_ITEMS];
     bool pass[JP_ITEMS];
     if (vec && r0 + JP_ITEMS <= n) {
-      int4 v = ld_stream_i32x4(key + r0);
-      k[0] = v.x; k[1] = v.y; k[2] = v.z; k[3] = v.w;
-      uint32_t m = mask ? __ldg(reinterpret_cast<const uint32_t*>(mask + r0)) : 0x01010101u;
+      int4 v0 = ld_stream_i32x4(key + r0), v1 = ld_stream_i32x4(key + r0 + 4);
+      k[0] = v0.x; k[1] = v0.y; k[2] = v0.z; k[3] = v0.w;
+      k[4] = v1.x; k[5] = v1.y; k[6] = v1.z; k[7] = v1.w;
+      u64 m = mask ? __ldg(reinterpret_cast<const u64*>(mask + r0)) : 0x0101010101010101ull;
 #pragma unroll
-      for (int j = 0; j < JP_ITEMS; ++j) pass[j] = ((m >> (8 * j)) & 0xFFu) != 0;
+      for (int j = 0; j < JP_ITEMS; ++j) pass[j] = ((m >> (8 * j)) & 0xFFull) != 0;
+      row_pred_vec(pred, r0, pass);
     } else {
 #pragma unroll
       for (int j = 0; j < JP_ITEMS; ++j) {
         bool in = r0 + j < n;
         k[j] = in ? (uint32_t)key[r0 + j] : 0u;
-        pass[j] = in && (!mask || mask[r0 + j]);
+        pass[j] = in && (!mask || mask[r0 + j]) && row_pred(pred, r0 + j);
       }
     }
     u64 h[JP_ITEMS], cur[JP_ITEMS];
@@ -294,39 +386,10 @@ __global__ void __launch_bounds__(JP_THREADS)
     }
     int total;
     int off = block_exclusive_scan(cnt, &total);
-    if (COUNT_ONLY) {
-      if (threadIdx.x == 0 && total) atomicAdd(total_out, (unsigned long long)total);
-      continue;
-    }
-    if (threadIdx.x < 32) {
-      u64 excl = 0;
-      if (tile == 0) {
-        if (lane == 0) st_status(&status[0], ST_PREFIX | (u64)total);
-      } else {
-        if (lane == 0) st_status(&status[tile], ST_AGG | (u64)total);
-        int64_t look = tile - 1;
-        while (true) {
-          int64_t idx = look - lane;
-          u64 sv = idx >= 0 ? ld_slot_volatile(&status[idx]) : ST_PREFIX;
-          while (__any_sync(0xffffffffu, (sv >> 62) == 0)) {
-            if ((sv >> 62) == 0) sv = ld_slot_volatile(&status[idx]);
-          }
-          unsigned pm = __ballot_sync(0xffffffffu, (sv >> 62) == 2);
-          int first = pm ? __ffs(pm) - 1 : 32;
-          u64 v = lane <= first ? (sv & ST_VAL) : 0ull;
-          excl += warp_sum(v);
-          if (pm) break;
-          look -= 32;
-        }
-        if (lane == 0) st_status(&status[tile], ST_PREFIX | (excl + (u64)total));
-      }
-      if (lane == 0) {
-        base_s = excl;
-        if (tile == n_tiles - 1) *total_out = excl + (u64)total;
-      }
-    }
-    __syncthreads();
-    int64_t o = (int64_t)base_s + off;
+    int64_t base = MODE == PROBE_WRITE ? tile_cnt[tile] : tile * JP_TILE;
+    if (MODE != PROBE_WRITE && threadIdx.x == 0) tile_cnt[tile] = total;
+    if (MODE == PROBE_COUNT || total == 0) continue;
+    int64_t o = base + off;
 #pragma unroll
     for (int j = 0; j < JP_ITEMS; ++j) {
       uint32_t r = head[j];
@@ -341,54 +404,127 @@ __global__ void __launch_bounds__(JP_THREADS)
   }
 }
 
-int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const uint8_t* mask, int64_t n, BufPtr* left_idx,
-                     BufPtr* right_idx) {
+// single CTA: in-place exclusive scan of v[0..n); v[n] = total.  Each thread owns 8 consecutive values per round
+// (all loads in flight at once), so ~30 k tile counts take two rounds.
+constexpr int SC_THREADS = 1024, SC_ITEMS = 8;
+__global__ void __launch_bounds__(SC_THREADS) scan_i64_kernel(int64_t* v, int64_t n) {
+  __shared__ int64_t wsum[SC_THREADS / 32];
+  __shared__ int64_t carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int64_t c0 = 0; c0 < n; c0 += SC_THREADS * SC_ITEMS) {
+    int64_t i0 = c0 + (int64_t)threadIdx.x * SC_ITEMS;
+    int64_t x[SC_ITEMS], s = 0;
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; ++j) {
+      x[j] = i0 + j < n ? v[i0 + j] : 0;
+      s += x[j];
+    }
+    int64_t incl = s;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      int64_t t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    int64_t woff = 0, tot = 0;
+    for (int w = 0; w < SC_THREADS / 32; ++w) {
+      int64_t t = wsum[w];
+      if (w < warp) woff += t;
+      tot += t;
+    }
+    int64_t pre = carry_s + woff + incl - s;
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; ++j) {
+      if (i0 + j < n) v[i0 + j] = pre;
+      pre += x[j];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) carry_s += tot;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) v[n] = carry_s;
+}
+
+// moves each tile's staged run of pairs to its final offset (tile_off = scanned counts)
+__global__ void join_compact_kernel(const uint32_t* __restrict__ stage_l, const uint32_t* __restrict__ stage_r,
+                                    const int64_t* __restrict__ tile_off, int64_t n_tiles, uint32_t* __restrict__ out_l,
+                                    uint32_t* __restrict__ out_r) {
+  const int lane = threadIdx.x & 31;
+  int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t t = w; t < n_tiles; t += nw) {  // one warp per tile: sparse joins have a handful of pairs per tile
+    int64_t o = tile_off[t];
+    int c = (int)(tile_off[t + 1] - o);
+    int64_t src = t * JP_TILE;
+    for (int i = lane; i < c; i += 32) {
+      out_l[o + i] = stage_l[src + i];
+      out_r[o + i] = stage_r[src + i];
+    }
+  }
+}
+
+int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& pred, const uint8_t* mask, int64_t n,
+                     BufPtr* left_idx, BufPtr* right_idx) {
   if (n >= (int64_t)NIL) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
   if (!t.dups_known) {  // one readback per build: does any key occur twice on the build side?
     int f = 0;
-    B2_CUDA(cudaMemcpyAsync(&f, t.flags->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    B2_READBACK(ctx, &f, t.flags->ptr, 4);
     t.has_dups = f != 0;
     t.dups_known = true;
   }
+  int64_t total = 0;
+  if (n == 0) {
+    *left_idx = dev_alloc(ctx, 4);
+    *right_idx = dev_alloc(ctx, 4);
+    return 0;
+  }
   int64_t n_tiles = (n + JP_TILE - 1) / JP_TILE;
-  // [0] ticket, [1] total, [2..] tile status words
-  auto work = dev_alloc_zero(ctx, (size_t)(n_tiles + 4) * 8);
-  auto* ticket = work->as<unsigned long long>();
-  auto* total_dev = ticket + 1;
-  u64* status = work->as<u64>() + 2;
-  bool vec = ((uintptr_t)key & 15) == 0 && ((uintptr_t)mask & 3) == 0;
+  auto tiles = dev_alloc(ctx, (size_t)(n_tiles + 2) * 8);
+  int64_t* tile_cnt = tiles->as<int64_t>();
+  bool vec = ((uintptr_t)key & 15) == 0 && ((uintptr_t)mask & 7) == 0;
+  for (int k = 0; k < pred.n; ++k) vec = vec && ((uintptr_t)pred.col[k] & 15) == 0;
   int grid = grid_for(ctx, 8, n, JP_TILE);
   const u64* slots = t.slots->as<u64>();
   const uint32_t* next = t.next->as<uint32_t>();
-  unsigned long long total = 0;
-  int64_t capacity = n;  // primary-key build: at most one match per probe row
-  if (n > 0 && t.has_dups) {
-    join_probe32_kernel<true, true><<<grid, JP_THREADS, 0, ctx->stream>>>(key, mask, n, vec, slots, t.cap - 1, next,
-                                                                         nullptr, nullptr, status, ticket, total_dev);
+  if (t.has_dups) {
+    join_probe32_kernel<PROBE_COUNT, true><<<grid, JP_THREADS, 0, ctx->stream>>>(key, pred, mask, n, vec, slots,
+                                                                               t.cap - 1, next, nullptr, nullptr, tile_cnt);
     B2_LAUNCHED(ctx);
-    B2_CUDA(cudaMemcpyAsync(&total, total_dev, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (total >= (unsigned long long)NIL) fail(B2_ERR_NOT_IMPLEMENTED, "join output beyond 2^32-2 rows in one batch");
-    capacity = (int64_t)total;
-    B2_CUDA(cudaMemsetAsync(ticket, 0, 16, ctx->stream));
-  }
-  *left_idx = dev_alloc(ctx, (size_t)(capacity + 1) * 4);
-  *right_idx = dev_alloc(ctx, (size_t)(capacity + 1) * 4);
-  if (n > 0 && capacity > 0) {
-    if (t.has_dups)
-      join_probe32_kernel<false, true><<<grid, JP_THREADS, 0, ctx->stream>>>(
-          key, mask, n, vec, slots, t.cap - 1, next, (*left_idx)->as<uint32_t>(), (*right_idx)->as<uint32_t>(), status,
-          ticket, total_dev);
-    else
-      join_probe32_kernel<false, false><<<grid, JP_THREADS, 0, ctx->stream>>>(
-          key, mask, n, vec, slots, t.cap - 1, next, (*left_idx)->as<uint32_t>(), (*right_idx)->as<uint32_t>(), status,
-          ticket, total_dev);
+    scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(tile_cnt, n_tiles);
     B2_LAUNCHED(ctx);
-    B2_CUDA(cudaMemcpyAsync(&total, total_dev, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    B2_READBACK(ctx, &total, tile_cnt + n_tiles, 8);
+    if (total >= (int64_t)NIL) fail(B2_ERR_NOT_IMPLEMENTED, "join output beyond 2^32-2 rows in one batch");
+    *left_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
+    *right_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
+    if (total) {
+      join_probe32_kernel<PROBE_WRITE, true><<<grid, JP_THREADS, 0, ctx->stream>>>(
+          key, pred, mask, n, vec, slots, t.cap - 1, next, (*left_idx)->as<uint32_t>(), (*right_idx)->as<uint32_t>(),
+          tile_cnt);
+      B2_LAUNCHED(ctx);
+    }
+    return total;
   }
-  return (int64_t)total;
+  // primary-key build: one probe pass into tile-local staging runs, then scan + compaction of the runs
+  auto stage_l = dev_alloc(ctx, (size_t)n_tiles * JP_TILE * 4);
+  auto stage_r = dev_alloc(ctx, (size_t)n_tiles * JP_TILE * 4);
+  join_probe32_kernel<PROBE_STAGE, false><<<grid, JP_THREADS, 0, ctx->stream>>>(
+      key, pred, mask, n, vec, slots, t.cap - 1, next, stage_l->as<uint32_t>(), stage_r->as<uint32_t>(), tile_cnt);
+  B2_LAUNCHED(ctx);
+  scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(tile_cnt, n_tiles);
+  B2_LAUNCHED(ctx);
+  B2_READBACK(ctx, &total, tile_cnt + n_tiles, 8);
+  *left_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
+  *right_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
+  if (total) {
+    join_compact_kernel<<<grid_for(ctx, 8, n_tiles * 32, 256), 256, 0, ctx->stream>>>(
+        stage_l->as<uint32_t>(), stage_r->as<uint32_t>(), tile_cnt, n_tiles, (*left_idx)->as<uint32_t>(),
+        (*right_idx)->as<uint32_t>());
+    B2_LAUNCHED(ctx);
+  }
+  return total;
 }
 
 }  // namespace b2

@@ -38,11 +38,24 @@ std::shared_ptr<JoinTable> join_build(Ctx* ctx, const Key128* keys, int64_t n);
 int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* probe_keys, int64_t n_probe, BufPtr* left_idx,
                    BufPtr* right_idx);
 
-// single Int32 / Date32 key: fused filter (mask may be null) + build / probe over the uncompacted key column;
-// row ids are those of the unfiltered batch
-std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const uint8_t* mask, int64_t n);
-int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const uint8_t* mask, int64_t n_probe,
-                     BufPtr* left_idx, BufPtr* right_idx);
+// A FilterExec predicate evaluated inside the join kernels: a conjunction of up to 4 comparisons of an
+// Int32 / Date32 / Float64 column with a literal (every TPC-H date / key / quantity filter).  Anything else is
+// evaluated column-at-a-time into a byte mask first (eval.cu) and passed as `mask`.
+struct RowPred {
+  int n = 0;
+  const void* col[4];
+  int is_f64[4];
+  int op[4];  // b2_binary_op comparison, column on the left
+  long long ilit[4];
+  double flit[4];
+};
+bool compile_row_pred(const ExprPtr& pred, const Batch& batch, RowPred* out);
+// single Int32 / Date32 key: fused filter (RowPred and / or mask, both optional) + build / probe over the
+// uncompacted key column; row ids are those of the unfiltered batch
+std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const RowPred& pred, const uint8_t* mask,
+                                        int64_t n);
+int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& pred, const uint8_t* mask,
+                     int64_t n_probe, BufPtr* left_idx, BufPtr* right_idx);
 
 // repartition.cu: rows -> destination partition by hash of packed key; returns the stable permutation
 // (destination-major) and fills counts[n_out]

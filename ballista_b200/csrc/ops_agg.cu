@@ -146,8 +146,7 @@ BatchPtr HashAggregateExec::run_partial(int partition) {
         for (auto& g : groups) kc.push_back(eval_expr(ctx, g, *b));
         keybuf = pack_keys(ctx, layout, kc, b->num_rows, st->as<int>());
         int host = 0;
-        B2_CUDA(cudaMemcpyAsync(&host, st->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        B2_CUDA(cudaStreamSynchronize(ctx->stream));
+        B2_READBACK(ctx, &host, st->ptr, 4);
         if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 group key value is longer than the packed-key budget");
         keys = keybuf->as<Key128>();
       }

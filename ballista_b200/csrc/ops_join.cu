@@ -64,8 +64,7 @@ struct HashJoinExec : Op {
     BufPtr st = dev_alloc_zero(ctx, 16);
     BufPtr keys = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>());
     int host = 0;
-    B2_CUDA(cudaMemcpyAsync(&host, st->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    B2_READBACK(ctx, &host, st->ptr, 4);
     if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 join key value is longer than the packed-key budget");
     return keys;
   }
@@ -88,8 +87,10 @@ struct HashJoinExec : Op {
     }
     if (k32) {
       Column mask;
-      if (pred && left_batch->num_rows) mask = eval_expr(ctx, pred, *left_batch);
-      table = join_build32(ctx, left_batch->cols[on_left[0]].values<int32_t>(),
+      RowPred rp;
+      if (pred && left_batch->num_rows && !compile_row_pred(pred, *left_batch, &rp))
+        mask = eval_expr(ctx, pred, *left_batch);
+      table = join_build32(ctx, left_batch->cols[on_left[0]].values<int32_t>(), rp,
                            mask.data ? mask.values<uint8_t>() : nullptr, left_batch->num_rows);
       // the mask buffer is freed stream-ordered after the build kernel
     } else {
@@ -109,8 +110,9 @@ struct HashJoinExec : Op {
       int64_t m;
       if (op->k32) {
         Column mask;
-        if (pred && r->num_rows) mask = eval_expr(ctx, pred, *r);
-        m = join_probe32(ctx, *op->table, r->cols[op->on_right[0]].values<int32_t>(),
+        RowPred rp;
+        if (pred && r->num_rows && !compile_row_pred(pred, *r, &rp)) mask = eval_expr(ctx, pred, *r);
+        m = join_probe32(ctx, *op->table, r->cols[op->on_right[0]].values<int32_t>(), rp,
                          mask.data ? mask.values<uint8_t>() : nullptr, r->num_rows, &li, &ri);
       } else {
         BufPtr pk = op->pack(*r, op->on_right);
@@ -215,8 +217,7 @@ struct RepartitionExec : Op {
     BufPtr pk = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>());
     BufPtr perm = hash_partition_indices(ctx, pk->as<Key128>(), b.num_rows, n_out, counts);
     int host = 0;
-    B2_CUDA(cudaMemcpyAsync(&host, st->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    B2_READBACK(ctx, &host, st->ptr, 4);
     if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 partitioning key value is longer than the packed-key budget");
     return take_batch(ctx, b, perm->as<uint32_t>(), b.num_rows);
   }

@@ -61,8 +61,7 @@ BatchPtr slice_batch(Ctx* ctx, const Batch& b, int64_t begin, int64_t end) {
       int32_t ends[2] = {0, 0};
       if (c.length) {
         B2_CUDA(cudaMemcpyAsync(&ends[0], c.values<int32_t>() + begin, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        B2_CUDA(cudaMemcpyAsync(&ends[1], c.values<int32_t>() + end, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        B2_CUDA(cudaStreamSynchronize(ctx->stream));
+        B2_READBACK(ctx, &ends[1], c.values<int32_t>() + end, 4);
       }
       o.data = dev_alloc_zero(ctx, (size_t)(m + 1) * 4);
       o.chars_len = ends[1] - ends[0];

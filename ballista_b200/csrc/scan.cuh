@@ -127,8 +127,7 @@ BufPtr device_scan(Ctx* ctx, In in, int64_t n, Out out, int64_t* total_host) {
   if (total_host) {
     *total_host = 0;
     if (n > 0) {
-      B2_CUDA(cudaMemcpyAsync(total_host, sums->as<int64_t>() + nb, 8, cudaMemcpyDeviceToHost, ctx->stream));
-      B2_CUDA(cudaStreamSynchronize(ctx->stream));
+      B2_READBACK(ctx, total_host, sums->as<int64_t>() + nb, 8);
     }
   }
   return sums;

@@ -190,8 +190,7 @@ BatchPtr tpch_generate(Ctx* ctx, const std::string& table, double sf, int64_t ro
       B2_LAUNCHED(ctx);
       if (seg) {
         int32_t total = 0;
-        B2_CUDA(cudaMemcpyAsync(&total, so + n, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        B2_CUDA(cudaStreamSynchronize(ctx->stream));
+        B2_READBACK(ctx, &total, so + n, 4);
         seg->chars_len = total;
       }
     }

@@ -16,10 +16,13 @@ def step():
     final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
     return final.collect_device(0)
 for _ in range(2): out = step()
-ctx.synchronize(); l0 = ctx.kernel_launches(); t = time.perf_counter()
+ctx.set_profiling(2); ctx.synchronize(); l0 = ctx.kernel_launches(); t = time.perf_counter()
 for _ in range(steps): out = step()
 ctx.synchronize(); dt = (time.perf_counter() - t) / steps
 rows = c.num_rows + o.num_rows + l.num_rows
 scan_bytes = c.num_bytes + o.num_bytes + l.num_bytes
 print(f"Q3 SF{sf:g}: {dt*1e3:.2f} ms/step, {rows/dt/1e9:.3f} G input rows/s, scan-only {scan_bytes/dt/1e9:.1f} GB/s, "
       f"groups {sum(b.num_rows for b in out)}, launches/step {(ctx.kernel_launches()-l0)/steps}")
+del out, c, o, l
+import gc; gc.collect()
+ctx.close()

@@ -4,6 +4,10 @@
 // row is pushed onto its key's chain (head[slot] / next[row]) and the key's match count is bumped, so the
 // probe sizes its output without walking chains.  Probe is two-pass (count -> scan -> write) and emits
 // (build_row, probe_row) pairs in probe order, which is the reference's output order.
+#include <algorithm>
+#include <cmath>
+#include <limits>
+
 #include "ops.h"
 #include "scan.cuh"
 
@@ -113,12 +117,14 @@ int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* pkeys, int64_t n,
 // ------------------------------------------------------------------------------------------------------
 // 32-bit-key join (every TPC-H join: one Int32 / Date32 key column per side).
 //
-// The table is ONE array of 8-byte slots, (key << 32) | head_row, so a probe costs a single 8-byte load and
-// a build insert a single 64-bit CAS; EMPTY is all ones (a claimed slot always has head_row != NIL).  Build
-// rows with equal keys are chained through next[] (head swap by CAS) and raise flags[0]; for primary-key
-// builds (flags[0] == 0) next[] is never read.  The slot index keeps the low 3 key bits and mixes the rest:
-// eight neighbouring keys share one 64-byte line, so a probe side clustered on the key (lineitem by
-// l_orderkey) walks the table with L1/L2 locality instead of one DRAM sector per row.
+// The table is ONE array of 8-byte slots, (key << 32) | head_row, grouped in buckets of 4 slots = one 32-byte
+// sector.  A probe loads its key's whole bucket with two 16-byte loads of the same sector and is finished
+// unless the bucket is full without a match (rare below 50 % load), so neither hits nor misses walk a
+// divergent linear-probing chain; a build insert is one 64-bit CAS on the first empty slot of the bucket
+// (slots of a bucket fill in order, so the first EMPTY slot ends a lookup).  EMPTY is all ones (a claimed slot
+// always has head_row != NIL).  Build rows with equal keys are chained through next[] (head swap by CAS) and
+// raise flags[0]; for primary-key builds (flags[0] == 0) next[] is never read.  The table is sized for the
+// rows that pass the fused filter, so a selective build side stays L2-resident.
 //
 // Both kernels take the FilterExec mask of their input (or null) and the ORIGINAL, uncompacted key column:
 // the filter is never materialised, row ids are those of the unfiltered batch, and output columns are
@@ -132,41 +138,35 @@ __host__ __device__ __forceinline__ uint32_t fmix32(uint32_t h) {
   h ^= h >> 16;
   return h;
 }
-__device__ __forceinline__ u64 slot_of(uint32_t k, u64 capmask) {
-  return (((u64)fmix32(k >> 3) << 3) + (k & 7u)) & capmask;
-}
+constexpr int BUCKET = 4;  // slots per bucket (one 32-byte sector)
+__device__ __forceinline__ u64 bucket_of(uint32_t k, u64 bmask) { return (u64)fmix32(k) & bmask; }
 __device__ __forceinline__ u64 ld_slot_volatile(const u64* p) {
   u64 v;
   asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
   return v;
 }
 
-// ---- inline FilterExec predicate (RowPred) ----
-template <class T> __device__ __forceinline__ bool cmp_op(int op, T a, T b) {
-  switch (op) {
-    case B2_OP_EQ: return a == b;
-    case B2_OP_NOTEQ: return a != b;
-    case B2_OP_LT: return a < b;
-    case B2_OP_LTEQ: return a <= b;
-    case B2_OP_GT: return a > b;
-    default: return a >= b;
-  }
-}
+// ---- inline FilterExec predicate (RowPred): closed range tests, two instructions per Int32 row ----
+__device__ __forceinline__ bool in_range_i32(int32_t x, int lo, unsigned width) { return (unsigned)(x - lo) <= width; }
+__device__ __forceinline__ bool in_range_f64(double x, double lo, double hi) { return x >= lo && x <= hi; }
 __device__ __forceinline__ bool row_pred(const RowPred& p, int64_t i) {
   bool ok = true;
   for (int t = 0; t < p.n; ++t) {
     if (p.is_f64[t])
-      ok = ok && cmp_op<double>(p.op[t], static_cast<const double*>(p.col[t])[i], p.flit[t]);
+      ok = ok && in_range_f64(static_cast<const double*>(p.col[t])[i], p.flo[t], p.fhi[t]);
     else
-      ok = ok && cmp_op<long long>(p.op[t], (long long)static_cast<const int32_t*>(p.col[t])[i], p.ilit[t]);
+      ok = ok && in_range_i32(static_cast<const int32_t*>(p.col[t])[i], p.ilo[t], p.iwidth[t]);
   }
   return ok;
 }
 
-static bool flatten_and(const ExprPtr& e, std::vector<ExprPtr>* terms) {
-  if (e->kind == B2_EXPR_BINARY && e->op == B2_OP_AND) return flatten_and(e->ch[0], terms) && flatten_and(e->ch[1], terms);
+static void flatten_and(const ExprPtr& e, std::vector<ExprPtr>* terms) {
+  if (e->kind == B2_EXPR_BINARY && e->op == B2_OP_AND) {
+    flatten_and(e->ch[0], terms);
+    flatten_and(e->ch[1], terms);
+    return;
+  }
   terms->push_back(e);
-  return true;
 }
 static int flip_cmp(int op) {
   switch (op) {
@@ -185,8 +185,7 @@ bool compile_row_pred(const ExprPtr& pred, const Batch& batch, RowPred* out) {
   for (auto& t : terms) {
     if (t->kind != B2_EXPR_BINARY) return false;
     int op = t->op;
-    if (op != B2_OP_EQ && op != B2_OP_NOTEQ && op != B2_OP_LT && op != B2_OP_LTEQ && op != B2_OP_GT && op != B2_OP_GTEQ)
-      return false;
+    if (op != B2_OP_EQ && op != B2_OP_LT && op != B2_OP_LTEQ && op != B2_OP_GT && op != B2_OP_GTEQ) return false;
     ExprPtr c = t->ch[0], l = t->ch[1];
     if (c->kind == B2_EXPR_LITERAL && l->kind == B2_EXPR_COLUMN) {
       std::swap(c, l);
@@ -195,17 +194,41 @@ bool compile_row_pred(const ExprPtr& pred, const Batch& batch, RowPred* out) {
     if (c->kind != B2_EXPR_COLUMN || l->kind != B2_EXPR_LITERAL) return false;
     const Column& col = batch.cols[c->col];
     int k = rp.n++;
-    rp.op[k] = op;
     rp.col[k] = col.data->ptr;
+    rp.ilo[k] = 0;
+    rp.iwidth[k] = 0;
+    rp.flo[k] = rp.fhi[k] = 0;
     if ((col.dtype == B2_INT32 || col.dtype == B2_DATE32) &&
         (l->dtype == B2_INT32 || l->dtype == B2_DATE32 || l->dtype == B2_INT64)) {
+      const long long MIN = INT32_MIN, MAX = INT32_MAX;
+      long long lo = MIN, hi = MAX, v = l->i;
+      switch (op) {
+        case B2_OP_EQ: lo = hi = v; break;
+        case B2_OP_LT: hi = v - 1; break;
+        case B2_OP_LTEQ: hi = v; break;
+        case B2_OP_GT: lo = v + 1; break;
+        default: lo = v; break;
+      }
+      lo = std::max(lo, MIN);
+      hi = std::min(hi, MAX);
       rp.is_f64[k] = 0;
-      rp.ilit[k] = l->i;
-      rp.flit[k] = 0;
+      if (lo > hi) return false;  // constant-false comparison: rare, the generic mask path handles it
+      rp.ilo[k] = (int)lo;
+      rp.iwidth[k] = (unsigned)(hi - lo);
     } else if (col.dtype == B2_FLOAT64 && l->dtype == B2_FLOAT64) {
+      double v = l->f, inf = std::numeric_limits<double>::infinity();
+      if (v != v) return false;  // NaN literal
+      double lo = -inf, hi = inf;
+      switch (op) {
+        case B2_OP_EQ: lo = hi = v; break;
+        case B2_OP_LT: hi = std::nextafter(v, -inf); break;
+        case B2_OP_LTEQ: hi = v; break;
+        case B2_OP_GT: lo = std::nextafter(v, inf); break;
+        default: lo = v; break;
+      }
       rp.is_f64[k] = 1;
-      rp.flit[k] = l->f;
-      rp.ilit[k] = 0;
+      rp.flo[k] = lo;
+      rp.fhi[k] = hi;
     } else {
       return false;
     }
@@ -215,37 +238,40 @@ bool compile_row_pred(const ExprPtr& pred, const Batch& batch, RowPred* out) {
 }
 
 __global__ void join_build32_kernel(const int32_t* __restrict__ key, RowPred pred, const uint8_t* __restrict__ mask,
-                                    int64_t n, u64* slots, u64 capmask, uint32_t* next, int* flags) {
+                                    int64_t n, u64* slots, u64 bmask, uint32_t* next, int* flags) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     if (mask && !mask[i]) continue;
     if (!row_pred(pred, i)) continue;
     uint32_t k = (uint32_t)key[i];
-    u64 h = slot_of(k, capmask);
+    u64 b = bucket_of(k, bmask);
     u64 mine = ((u64)k << 32) | (uint32_t)i;
-    for (u64 probe = 0; probe <= capmask; ++probe) {
-      u64 cur = ld_slot_volatile(&slots[h]);
-      if (cur == KEY_EMPTY) {
-        u64 old = atomicCAS((unsigned long long*)&slots[h], (unsigned long long)KEY_EMPTY, (unsigned long long)mine);
-        if (old == KEY_EMPTY) {
-          next[i] = NIL;
-          break;
+    bool placed = false;
+    for (u64 probe = 0; probe <= bmask && !placed; ++probe) {
+      u64* bs = slots + b * BUCKET;
+      for (int sidx = 0; sidx < BUCKET && !placed; ++sidx) {
+        u64 cur = ld_slot_volatile(bs + sidx);
+        if (cur == KEY_EMPTY) {
+          u64 old = atomicCAS((unsigned long long*)(bs + sidx), (unsigned long long)KEY_EMPTY, (unsigned long long)mine);
+          if (old == KEY_EMPTY) {
+            next[i] = NIL;
+            placed = true;
+            break;
+          }
+          cur = old;
         }
-        cur = old;
-      }
-      bool placed = false;
-      while ((uint32_t)(cur >> 32) == k) {  // equal key: push this row onto the chain
-        u64 old = atomicCAS((unsigned long long*)&slots[h], (unsigned long long)cur, (unsigned long long)mine);
-        if (old == cur) {
-          next[i] = (uint32_t)cur;
-          flags[0] = 1;
-          placed = true;
-          break;
+        while ((uint32_t)(cur >> 32) == k) {  // equal key: push this row onto the chain
+          u64 old = atomicCAS((unsigned long long*)(bs + sidx), (unsigned long long)cur, (unsigned long long)mine);
+          if (old == cur) {
+            next[i] = (uint32_t)cur;
+            flags[0] = 1;
+            placed = true;
+            break;
+          }
+          cur = old;
         }
-        cur = old;
       }
-      if (placed) break;
-      h = (h + 1) & capmask;
+      b = (b + 1) & bmask;
     }
   }
 }
@@ -276,7 +302,7 @@ std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const RowP
     B2_READBACK(ctx, &c, t->flags->as<char>() + 8, 8);
     n_in = (int64_t)c;
   }
-  u64 cap = 64;
+  u64 cap = 64;  // slots; load factor <= 0.5, BUCKET slots per bucket
   while (cap < 2 * (u64)n_in + 16) cap <<= 1;
   t->cap = cap;
   t->slots = dev_alloc(ctx, cap * 8);
@@ -284,7 +310,7 @@ std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const RowP
   B2_CUDA(cudaMemsetAsync(t->slots->ptr, 0xFF, cap * 8, ctx->stream));
   if (n) {
     join_build32_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(
-        key, pred, mask, n, t->slots->as<u64>(), cap - 1, t->next->as<uint32_t>(), t->flags->as<int>());
+        key, pred, mask, n, t->slots->as<u64>(), cap / BUCKET - 1, t->next->as<uint32_t>(), t->flags->as<int>());
     B2_LAUNCHED(ctx);
   }
   t->dups_known = false;
@@ -300,22 +326,24 @@ __device__ __forceinline__ void row_pred_vec(const RowPred& p, int64_t r0, bool*
   for (int t = 0; t < p.n; ++t) {
     if (p.is_f64[t]) {
       const double* c = static_cast<const double*>(p.col[t]) + r0;
+      const double lo = p.flo[t], hi = p.fhi[t];
 #pragma unroll
       for (int j = 0; j < JP_ITEMS; j += 2) {
         double2 v = ld_stream_f64x2(c + j);
-        pass[j] = pass[j] && cmp_op<double>(p.op[t], v.x, p.flit[t]);
-        pass[j + 1] = pass[j + 1] && cmp_op<double>(p.op[t], v.y, p.flit[t]);
+        pass[j] = pass[j] && in_range_f64(v.x, lo, hi);
+        pass[j + 1] = pass[j + 1] && in_range_f64(v.y, lo, hi);
       }
     } else {
       const int32_t* c = static_cast<const int32_t*>(p.col[t]) + r0;
+      const int lo = p.ilo[t];
+      const unsigned w = p.iwidth[t];
 #pragma unroll
       for (int j = 0; j < JP_ITEMS; j += 4) {
         int4 v = ld_stream_i32x4(c + j);
-        long long lit = p.ilit[t];
-        pass[j] = pass[j] && cmp_op<long long>(p.op[t], v.x, lit);
-        pass[j + 1] = pass[j + 1] && cmp_op<long long>(p.op[t], v.y, lit);
-        pass[j + 2] = pass[j + 2] && cmp_op<long long>(p.op[t], v.z, lit);
-        pass[j + 3] = pass[j + 3] && cmp_op<long long>(p.op[t], v.w, lit);
+        pass[j] = pass[j] && in_range_i32(v.x, lo, w);
+        pass[j + 1] = pass[j + 1] && in_range_i32(v.y, lo, w);
+        pass[j + 2] = pass[j + 2] && in_range_i32(v.z, lo, w);
+        pass[j + 3] = pass[j + 3] && in_range_i32(v.w, lo, w);
       }
     }
   }
@@ -333,7 +361,7 @@ enum { PROBE_STAGE = 0, PROBE_COUNT = 1, PROBE_WRITE = 2 };
 template <int MODE, bool DUPS>
 __global__ void __launch_bounds__(JP_THREADS)
     join_probe32_kernel(const int32_t* __restrict__ key, RowPred pred, const uint8_t* __restrict__ mask, int64_t n,
-                        bool vec, const u64* __restrict__ slots, u64 capmask, const uint32_t* __restrict__ next,
+                        bool vec, const u64* __restrict__ slots, u64 bmask, const uint32_t* __restrict__ next,
                         uint32_t* __restrict__ left_idx, uint32_t* __restrict__ right_idx, int64_t* tile_cnt) {
   const int64_t n_tiles = (n + JP_TILE - 1) / JP_TILE;
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -356,31 +384,48 @@ __global__ void __launch_bounds__(JP_THREADS)
         pass[j] = in && (!mask || mask[r0 + j]) && row_pred(pred, r0 + j);
       }
     }
-    u64 h[JP_ITEMS], cur[JP_ITEMS];
-#pragma unroll
-    for (int j = 0; j < JP_ITEMS; ++j) {  // all first-probe loads in flight before any is used
-      h[j] = slot_of(k[j], capmask);
-      cur[j] = pass[j] ? __ldg(&slots[h[j]]) : KEY_EMPTY;
-    }
     uint32_t head[JP_ITEMS];
     int cnt = 0;
 #pragma unroll
-    for (int j = 0; j < JP_ITEMS; ++j) {
-      head[j] = NIL;
-      u64 c = cur[j], hh = h[j];
-      while (c != KEY_EMPTY) {
-        if ((uint32_t)(c >> 32) == k[j]) {
-          head[j] = (uint32_t)c;
-          break;
-        }
-        hh = (hh + 1) & capmask;
-        c = __ldg(&slots[hh]);
-      }
-      if (head[j] != NIL) {
-        if (DUPS) {
-          for (uint32_t r = head[j]; r != NIL; r = next[r]) ++cnt;
+    for (int g = 0; g < JP_ITEMS; g += 4) {  // four bucket loads (8 x 16 B) in flight per thread
+      ulonglong2 lo[4], hi[4];
+      u64 b[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        b[j] = bucket_of(k[g + j], bmask);
+        const ulonglong2* bp = reinterpret_cast<const ulonglong2*>(slots + b[j] * BUCKET);
+        if (pass[g + j]) {
+          lo[j] = __ldg(bp);
+          hi[j] = __ldg(bp + 1);
         } else {
-          ++cnt;
+          lo[j] = make_ulonglong2(KEY_EMPTY, KEY_EMPTY);
+          hi[j] = lo[j];
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t kk = k[g + j];
+        uint32_t hd = NIL;
+        ulonglong2 x = lo[j], y = hi[j];
+        u64 bb = b[j];
+        while (true) {
+          if ((uint32_t)(x.x >> 32) == kk && x.x != KEY_EMPTY) hd = (uint32_t)x.x;
+          if ((uint32_t)(x.y >> 32) == kk && x.y != KEY_EMPTY) hd = (uint32_t)x.y;
+          if ((uint32_t)(y.x >> 32) == kk && y.x != KEY_EMPTY) hd = (uint32_t)y.x;
+          if ((uint32_t)(y.y >> 32) == kk && y.y != KEY_EMPTY) hd = (uint32_t)y.y;
+          if (hd != NIL || y.y == KEY_EMPTY) break;  // found, or the bucket has a free slot: key absent
+          bb = (bb + 1) & bmask;                      // full bucket without a match: overflow into the next one
+          const ulonglong2* bp = reinterpret_cast<const ulonglong2*>(slots + bb * BUCKET);
+          x = __ldg(bp);
+          y = __ldg(bp + 1);
+        }
+        head[g + j] = hd;
+        if (hd != NIL) {
+          if (DUPS) {
+            for (uint32_t r = hd; r != NIL; r = next[r]) ++cnt;
+          } else {
+            ++cnt;
+          }
         }
       }
     }
@@ -486,12 +531,18 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
   int64_t* tile_cnt = tiles->as<int64_t>();
   bool vec = ((uintptr_t)key & 15) == 0 && ((uintptr_t)mask & 7) == 0;
   for (int k = 0; k < pred.n; ++k) vec = vec && ((uintptr_t)pred.col[k] & 15) == 0;
-  int grid = grid_for(ctx, 8, n, JP_TILE);
+  // persistent grid = exactly the co-resident CTAs, so the static tile striding has no ragged second wave
+  static int per_sm = 0;
+  if (!per_sm) {
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, join_probe32_kernel<PROBE_STAGE, false>, JP_THREADS, 0));
+    if (per_sm < 1) per_sm = 1;
+  }
+  int grid = grid_for(ctx, per_sm, n, JP_TILE);
   const u64* slots = t.slots->as<u64>();
   const uint32_t* next = t.next->as<uint32_t>();
   if (t.has_dups) {
     join_probe32_kernel<PROBE_COUNT, true><<<grid, JP_THREADS, 0, ctx->stream>>>(key, pred, mask, n, vec, slots,
-                                                                               t.cap - 1, next, nullptr, nullptr, tile_cnt);
+                                                                               t.cap / BUCKET - 1, next, nullptr, nullptr, tile_cnt);
     B2_LAUNCHED(ctx);
     scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(tile_cnt, n_tiles);
     B2_LAUNCHED(ctx);
@@ -501,7 +552,7 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
     *right_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
     if (total) {
       join_probe32_kernel<PROBE_WRITE, true><<<grid, JP_THREADS, 0, ctx->stream>>>(
-          key, pred, mask, n, vec, slots, t.cap - 1, next, (*left_idx)->as<uint32_t>(), (*right_idx)->as<uint32_t>(),
+          key, pred, mask, n, vec, slots, t.cap / BUCKET - 1, next, (*left_idx)->as<uint32_t>(), (*right_idx)->as<uint32_t>(),
           tile_cnt);
       B2_LAUNCHED(ctx);
     }
@@ -511,7 +562,7 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
   auto stage_l = dev_alloc(ctx, (size_t)n_tiles * JP_TILE * 4);
   auto stage_r = dev_alloc(ctx, (size_t)n_tiles * JP_TILE * 4);
   join_probe32_kernel<PROBE_STAGE, false><<<grid, JP_THREADS, 0, ctx->stream>>>(
-      key, pred, mask, n, vec, slots, t.cap - 1, next, stage_l->as<uint32_t>(), stage_r->as<uint32_t>(), tile_cnt);
+      key, pred, mask, n, vec, slots, t.cap / BUCKET - 1, next, stage_l->as<uint32_t>(), stage_r->as<uint32_t>(), tile_cnt);
   B2_LAUNCHED(ctx);
   scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(tile_cnt, n_tiles);
   B2_LAUNCHED(ctx);

@@ -41,13 +41,13 @@ int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* probe_keys, int64
 // A FilterExec predicate evaluated inside the join kernels: a conjunction of up to 4 comparisons of an
 // Int32 / Date32 / Float64 column with a literal (every TPC-H date / key / quantity filter).  Anything else is
 // evaluated column-at-a-time into a byte mask first (eval.cu) and passed as `mask`.
-struct RowPred {
+struct RowPred {  // every term is a closed range test lo <= column[i] <= hi (strict bounds are tightened on the host)
   int n = 0;
   const void* col[4];
   int is_f64[4];
-  int op[4];  // b2_binary_op comparison, column on the left
-  long long ilit[4];
-  double flit[4];
+  int ilo[4];            // Int32 / Date32 terms: (uint32)(x - ilo) <= iwidth
+  unsigned iwidth[4];
+  double flo[4], fhi[4];  // Float64 terms
 };
 bool compile_row_pred(const ExprPtr& pred, const Batch& batch, RowPred* out);
 // single Int32 / Date32 key: fused filter (RowPred and / or mask, both optional) + build / probe over the

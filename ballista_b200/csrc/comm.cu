@@ -6,20 +6,11 @@
 
 #include <cstring>
 
+#include "comm.h"
 #include "ops.h"
 #include "scan.cuh"
 
 namespace b2 {
-
-struct Comm {
-  ncclComm_t nccl = nullptr;
-};
-
-#define B2_NCCL(expr)                                                                         \
-  do {                                                                                        \
-    ncclResult_t _r = (expr);                                                                 \
-    if (_r != ncclSuccess) ::b2::fail(B2_ERR_NCCL, std::string(#expr) + ": " + ncclGetErrorString(_r)); \
-  } while (0)
 
 static_assert(sizeof(ncclUniqueId) == 128, "b2_comm_unique_id hands out 128 bytes");
 
@@ -44,6 +35,7 @@ void comm_init(Ctx* ctx, int rank, int nranks, const void* id128) {
 }
 void comm_destroy(Ctx* ctx) {
   if (!ctx->comm) return;
+  shuffle_arena_release(ctx);
   ncclCommDestroy(ctx->comm->nccl);
   delete ctx->comm;
   ctx->comm = nullptr;
@@ -65,7 +57,7 @@ struct OffOut {
 };
 
 // exchange of per-rank int64 vectors (row / byte counts); returns the [nranks][len] matrix on the host
-static std::vector<int64_t> allgather_counts(Ctx* ctx, const std::vector<int64_t>& mine) {
+std::vector<int64_t> allgather_counts(Ctx* ctx, const std::vector<int64_t>& mine) {
   size_t len = mine.size();
   auto dsend = dev_alloc(ctx, len * 8);
   auto drecv = dev_alloc(ctx, len * 8 * ctx->nranks);

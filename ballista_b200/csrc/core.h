@@ -83,6 +83,24 @@ inline void read_back(Ctx* ctx, void* dst, const void* src, size_t bytes, const 
   B2_CUDA(cudaStreamSynchronize(ctx->stream));
   if (ctx->trace) ctx->trace_add(where, wall_now() - t0);
 }
+// B2_TRACE only: synchronise and charge the wall time since the previous mark to `label` (phase timing)
+struct PhaseTimer {
+  Ctx* ctx;
+  double t0;
+  explicit PhaseTimer(Ctx* c) : ctx(c), t0(0) {
+    if (ctx->trace) {
+      cudaStreamSynchronize(ctx->stream);
+      t0 = wall_now();
+    }
+  }
+  void mark(const char* label) {
+    if (!ctx->trace) return;
+    cudaStreamSynchronize(ctx->stream);
+    double t = wall_now();
+    ctx->trace_add(label, t - t0);
+    t0 = t;
+  }
+};
 #define B2_STR2(x) #x
 #define B2_STR(x) B2_STR2(x)
 #define B2_SYNC(ctx) ::b2::sync_stream((ctx), __FILE__ ":" B2_STR(__LINE__))

@@ -449,50 +449,6 @@ __global__ void __launch_bounds__(JP_THREADS)
   }
 }
 
-// single CTA: in-place exclusive scan of v[0..n); v[n] = total.  Each thread owns 8 consecutive values per round
-// (all loads in flight at once), so ~30 k tile counts take two rounds.
-constexpr int SC_THREADS = 1024, SC_ITEMS = 8;
-__global__ void __launch_bounds__(SC_THREADS) scan_i64_kernel(int64_t* v, int64_t n) {
-  __shared__ int64_t wsum[SC_THREADS / 32];
-  __shared__ int64_t carry_s;
-  if (threadIdx.x == 0) carry_s = 0;
-  __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int64_t c0 = 0; c0 < n; c0 += SC_THREADS * SC_ITEMS) {
-    int64_t i0 = c0 + (int64_t)threadIdx.x * SC_ITEMS;
-    int64_t x[SC_ITEMS], s = 0;
-#pragma unroll
-    for (int j = 0; j < SC_ITEMS; ++j) {
-      x[j] = i0 + j < n ? v[i0 + j] : 0;
-      s += x[j];
-    }
-    int64_t incl = s;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      int64_t t = __shfl_up_sync(0xffffffffu, incl, d);
-      if (lane >= d) incl += t;
-    }
-    if (lane == 31) wsum[warp] = incl;
-    __syncthreads();
-    int64_t woff = 0, tot = 0;
-    for (int w = 0; w < SC_THREADS / 32; ++w) {
-      int64_t t = wsum[w];
-      if (w < warp) woff += t;
-      tot += t;
-    }
-    int64_t pre = carry_s + woff + incl - s;
-#pragma unroll
-    for (int j = 0; j < SC_ITEMS; ++j) {
-      if (i0 + j < n) v[i0 + j] = pre;
-      pre += x[j];
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) carry_s += tot;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) v[n] = carry_s;
-}
-
 // moves each tile's staged run of pairs to its final offset (tile_off = scanned counts)
 __global__ void join_compact_kernel(const uint32_t* __restrict__ stage_l, const uint32_t* __restrict__ stage_r,
                                     const int64_t* __restrict__ tile_off, int64_t n_tiles, uint32_t* __restrict__ out_l,

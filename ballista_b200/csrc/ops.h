@@ -59,7 +59,23 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
 
 // repartition.cu: rows -> destination partition by hash of packed key; returns the stable permutation
 // (destination-major) and fills counts[n_out]
-BufPtr hash_partition_indices(Ctx* ctx, const Key128* keys, int64_t n, int n_out, std::vector<int64_t>* counts);
+// `key32` (optional): the single Int32 / Date32 key column, hashed as its packed form without materialising keys
+BufPtr hash_partition_indices(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
+                              std::vector<int64_t>* counts);
+
+// two-phase form used by the shuffle: phase 1 = destination bytes + per-tile histogram + scan (no host sync)
+struct SplitState {
+  BufPtr dest, hist;
+  int64_t n = 0, n_tiles = 0;
+  int n_out = 0;
+};
+SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out);
+void hash_split_starts_device(Ctx* ctx, const SplitState& st, int64_t* out_dev);  // n_out + 1 slice starts
+void hash_split_counts(Ctx* ctx, const SplitState& st, std::vector<int64_t>* counts);
+BufPtr hash_split_perm(Ctx* ctx, const SplitState& st);
+// moves fixed-width columns to dst[c] + base[c * n_out + d] + k * width[c] (k = rank inside destination d's slice)
+void hash_split_move(Ctx* ctx, const SplitState& st, int n_cols, const void* const* src, void* const* dst,
+                     const int* width, const int64_t* base_dev, uint32_t* perm_or_null);
 
 // comm.cu
 void comm_unique_id(void* id128);
@@ -68,6 +84,10 @@ void comm_destroy(Ctx* ctx);
 BatchPtr comm_allgather_batch(Ctx* ctx, const Batch& local);
 // all-to-all of a destination-major permuted batch: slice d (counts[d] rows) goes to rank d
 BatchPtr comm_all_to_all(Ctx* ctx, const Batch& permuted, const std::vector<int64_t>& counts);
+// shuffle.cu: the same exchange over CUDA-IPC peer memory (columns moved into a peer-mapped arena by the split's
+// second phase + one NVLink pull kernel).  Takes the unpermuted batch and phase 1 of its split.
+// nullptr = peer mapping unavailable.
+BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st);
 
 // ---- RecordBatchStream ----
 struct Stream {

@@ -211,15 +211,42 @@ struct RepartitionExec : Op {
 
   // hash-split one batch: destination-major permuted batch + per-destination counts
   BatchPtr split(const Batch& b, std::vector<int64_t>* counts) {
+    BufPtr perm = split_perm(b, counts);
+    return take_batch(ctx, b, perm->as<uint32_t>(), b.num_rows);
+  }
+  // phase 1 of the split (destinations + histogram + scan, no host sync); false = keys need the packed path check
+  bool split_begin(const Batch& b, SplitState* st) {
     std::vector<Column> kc;
     for (auto& k : keys) kc.push_back(eval_expr(ctx, k, b));
-    BufPtr st = dev_alloc_zero(ctx, 16);
-    BufPtr pk = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>());
-    BufPtr perm = hash_partition_indices(ctx, pk->as<Key128>(), b.num_rows, n_out, counts);
+    if (kc.size() == 1 && (kc[0].dtype == B2_INT32 || kc[0].dtype == B2_DATE32)) {
+      *st = hash_split_begin(ctx, nullptr, kc[0].values<int32_t>(), b.num_rows, n_out);
+      return true;
+    }
+    BufPtr stt = dev_alloc_zero(ctx, 16);
+    BufPtr pk = pack_keys(ctx, layout, kc, b.num_rows, stt->as<int>());
+    *st = hash_split_begin(ctx, pk->as<Key128>(), nullptr, b.num_rows, n_out);
     int host = 0;
-    B2_READBACK(ctx, &host, st->ptr, 4);
+    B2_READBACK(ctx, &host, stt->ptr, 4);
     if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 partitioning key value is longer than the packed-key budget");
-    return take_batch(ctx, b, perm->as<uint32_t>(), b.num_rows);
+    return true;
+  }
+  // stable destination-major permutation of the rows of `b` + rows per destination
+  BufPtr split_perm(const Batch& b, std::vector<int64_t>* counts) {
+    std::vector<Column> kc;
+    for (auto& k : keys) kc.push_back(eval_expr(ctx, k, b));
+    BufPtr perm;
+    if (kc.size() == 1 && (kc[0].dtype == B2_INT32 || kc[0].dtype == B2_DATE32) && n_out <= 32) {
+      // one Int32 key: hashed straight from the column (same value as its packed form), nothing materialised
+      perm = hash_partition_indices(ctx, nullptr, kc[0].values<int32_t>(), b.num_rows, n_out, counts);
+    } else {
+      BufPtr st = dev_alloc_zero(ctx, 16);
+      BufPtr pk = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>());
+      perm = hash_partition_indices(ctx, pk->as<Key128>(), nullptr, b.num_rows, n_out, counts);
+      int host = 0;
+      B2_READBACK(ctx, &host, st->ptr, 4);
+      if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 partitioning key value is longer than the packed-key budget");
+    }
+    return perm;
   }
   void compute() {
     if (computed) return;
@@ -240,10 +267,26 @@ struct RepartitionExec : Op {
       } else {
         local = concat_batches(ctx, schema(), all);
       }
-      std::vector<int64_t> counts;
-      BatchPtr permuted = split(*local, &counts);
-      outputs[ctx->rank].push_back(comm_all_to_all(ctx, *permuted, counts));
-      last_path = "nccl-all-to-all";
+      BatchPtr got;
+      SplitState st;
+      bool two_phase = n_out <= 32 && split_begin(*local, &st);
+      if (two_phase) got = comm_shuffle_p2p(ctx, *local, st);
+      if (got) {
+        last_path = "nvlink-peer-pull";
+      } else {
+        std::vector<int64_t> counts;
+        BufPtr perm;
+        if (two_phase) {
+          perm = hash_split_perm(ctx, st);
+          hash_split_counts(ctx, st, &counts);
+        } else {
+          perm = split_perm(*local, &counts);
+        }
+        BatchPtr permuted = take_batch(ctx, *local, perm->as<uint32_t>(), local->num_rows);
+        got = comm_all_to_all(ctx, *permuted, counts);
+        last_path = "nccl-all-to-all";
+      }
+      outputs[ctx->rank].push_back(got);
     } else {
       int64_t k = 0;
       for (int p = 0; p < np; ++p) {

@@ -1,7 +1,10 @@
 // repartition.cu — hash repartition kernels (RepartitionExec(Partitioning::Hash)):
-// destination = hash(packed key) % n_out; a stable, destination-major permutation is built with one
-// compaction scan per destination, so every column is then moved by a single gather and each
-// destination's rows are one contiguous slice (the send segment of the all-to-all).
+// destination = hash(packed key) % n_out; a stable, destination-major permutation is built in two passes over
+// the keys (per-tile histogram -> one scan -> stable scatter of row ids), so every column is then moved by a
+// single gather and each destination's rows are one contiguous slice (the send segment of the all-to-all).
+// Beyond 32 output partitions the permutation falls back to one compaction scan per destination.
+#include <cstring>
+
 #include "ops.h"
 #include "scan.cuh"
 
@@ -23,13 +26,83 @@ struct PermOut {
   }
 };
 
-BufPtr hash_partition_indices(Ctx* ctx, const Key128* keys, int64_t n, int n_out, std::vector<int64_t>* counts) {
-  if (n_out < 1 || n_out > 255) fail(B2_ERR_INVALID_ARG, "hash repartition supports 1..255 output partitions");
-  if (n >= (1ll << 32) - 1) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
+// ---- n_out <= 32: two passes over the keys (histogram, then stable scatter of row ids) ----
+// A tile is RP_ITEMS sub-rows of RP_THREADS consecutive rows (thread t owns rows base + j * RP_THREADS + t, so
+// every load is coalesced); the stable order inside a tile is (j, warp, lane).
+constexpr int RP_THREADS = 256, RP_ITEMS = 8, RP_TILE = RP_THREADS * RP_ITEMS, RP_MAX_OUT = 32;
+constexpr int RP_WARPS = RP_THREADS / 32;
+
+struct KeySrc {  // packed 16-byte keys, or a single Int32 / Date32 key column hashed as its packed form
+  const Key128* k128;
+  const int32_t* k32;
+  __device__ __forceinline__ u64 hash(int64_t i) const {
+    return k128 ? key_hash(k128[i]) : key_hash(Key128{(u64)(uint32_t)k32[i], 0ull});
+  }
+};
+
+// pass 1: destination byte per row + per-tile histogram, stored destination-major (hist[d * n_tiles + tile]) so
+// that ONE exclusive scan of the whole array yields every (destination, tile) output offset
+__global__ void __launch_bounds__(RP_THREADS)
+    rp_hist_kernel(KeySrc keys, int64_t n, int n_out, uint8_t* __restrict__ dest, int64_t* __restrict__ hist,
+                   int64_t n_tiles) {
+  __shared__ int h[RP_MAX_OUT];
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    if (threadIdx.x < RP_MAX_OUT) h[threadIdx.x] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < RP_ITEMS; ++j) {
+      int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
+      int d = r < n ? (int)(keys.hash(r) % (u64)n_out) : -1;
+      if (d >= 0) dest[r] = (uint8_t)d;
+      unsigned peers = __match_any_sync(0xffffffffu, d);
+      if (d >= 0 && (peers & ((1u << (threadIdx.x & 31)) - 1)) == 0) atomicAdd(&h[d], __popc(peers));
+    }
+    __syncthreads();
+    if (threadIdx.x < n_out) hist[(int64_t)threadIdx.x * n_tiles + tile] = h[threadIdx.x];
+    __syncthreads();
+  }
+}
+
+// pass 2: stable rank of every row inside its (destination, tile) run -> perm[offset + rank] = row
+__global__ void __launch_bounds__(RP_THREADS)
+    rp_scatter_kernel(const uint8_t* __restrict__ dest, int64_t n, int n_out, const int64_t* __restrict__ off,
+                      int64_t n_tiles, uint32_t* __restrict__ perm) {
+  __shared__ uint32_t cnt[RP_ITEMS][RP_WARPS][RP_MAX_OUT];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    for (int i = threadIdx.x; i < RP_ITEMS * RP_WARPS * RP_MAX_OUT; i += RP_THREADS) (&cnt[0][0][0])[i] = 0;
+    __syncthreads();
+    int d[RP_ITEMS], rank[RP_ITEMS];
+#pragma unroll
+    for (int j = 0; j < RP_ITEMS; ++j) {
+      int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
+      d[j] = r < n ? (int)dest[r] : -1;
+      unsigned peers = __match_any_sync(0xffffffffu, d[j]);
+      rank[j] = __popc(peers & ((1u << lane) - 1));
+      if (d[j] >= 0 && rank[j] == 0) cnt[j][warp][d[j]] = __popc(peers);
+    }
+    __syncthreads();
+    if (threadIdx.x < n_out) {  // per destination: exclusive scan over (j, warp) from the run's global offset
+      uint32_t run = (uint32_t)off[(int64_t)threadIdx.x * n_tiles + tile];
+      for (int j = 0; j < RP_ITEMS; ++j)
+        for (int w = 0; w < RP_WARPS; ++w) {
+          uint32_t c = cnt[j][w][threadIdx.x];
+          cnt[j][w][threadIdx.x] = run;
+          run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < RP_ITEMS; ++j)
+      if (d[j] >= 0) perm[cnt[j][warp][d[j]] + rank[j]] = (uint32_t)(tile * RP_TILE + j * RP_THREADS + threadIdx.x);
+    __syncthreads();
+  }
+}
+
+static BufPtr partition_indices_scan_per_destination(Ctx* ctx, const Key128* keys, int64_t n, int n_out,
+                                                     std::vector<int64_t>* counts) {
   auto dest = dev_alloc(ctx, (size_t)n + 16);
   auto perm = dev_alloc(ctx, (size_t)(n + 1) * 4);
-  counts->assign(n_out, 0);
-  if (n == 0) return perm;
   dest_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(keys, n, n_out, dest->as<uint8_t>());
   B2_LAUNCHED(ctx);
   int64_t base = 0;
@@ -39,6 +112,167 @@ BufPtr hash_partition_indices(Ctx* ctx, const Key128* keys, int64_t n, int n_out
     (*counts)[d] = c;
     base += c;
   }
+  return perm;
+}
+
+// pass 2': instead of a permutation, move up to 8 fixed-width columns straight to their destination-major
+// position (the shuffle's staging arena): element k of destination d's slice of column c lands at
+// dst[c] + base[c * n_out + d] + k * width[c].  Reads are coalesced; a warp's stores fall into one run per destination.
+struct MoveCols {
+  int n;
+  const char* src[8];
+  char* dst[8];
+  int width[8];
+  const int64_t* base;  // device: [n][n_out] byte offset of slice d inside dst[c]
+};
+__global__ void __launch_bounds__(RP_THREADS)
+    rp_move_kernel(const uint8_t* __restrict__ dest, int64_t n, int n_out, const int64_t* __restrict__ off,
+                   int64_t n_tiles, MoveCols mc, uint32_t* __restrict__ perm) {
+  __shared__ uint32_t cnt[RP_ITEMS][RP_WARPS][RP_MAX_OUT];
+  __shared__ uint32_t start_s[RP_MAX_OUT];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x < n_out) start_s[threadIdx.x] = (uint32_t)off[(int64_t)threadIdx.x * n_tiles];
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    for (int i = threadIdx.x; i < RP_ITEMS * RP_WARPS * RP_MAX_OUT; i += RP_THREADS) (&cnt[0][0][0])[i] = 0;
+    __syncthreads();
+    int d[RP_ITEMS], rank[RP_ITEMS];
+#pragma unroll
+    for (int j = 0; j < RP_ITEMS; ++j) {
+      int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
+      d[j] = r < n ? (int)dest[r] : -1;
+      unsigned peers = __match_any_sync(0xffffffffu, d[j]);
+      rank[j] = __popc(peers & ((1u << lane) - 1));
+      if (d[j] >= 0 && rank[j] == 0) cnt[j][warp][d[j]] = __popc(peers);
+    }
+    __syncthreads();
+    if (threadIdx.x < n_out) {
+      uint32_t run = (uint32_t)off[(int64_t)threadIdx.x * n_tiles + tile];
+      for (int j = 0; j < RP_ITEMS; ++j)
+        for (int w = 0; w < RP_WARPS; ++w) {
+          uint32_t c = cnt[j][w][threadIdx.x];
+          cnt[j][w][threadIdx.x] = run;
+          run += c;
+        }
+    }
+    __syncthreads();
+    uint32_t pos[RP_ITEMS];  // destination-major global position
+#pragma unroll
+    for (int j = 0; j < RP_ITEMS; ++j) pos[j] = d[j] >= 0 ? cnt[j][warp][d[j]] + rank[j] : 0u;
+    if (perm) {
+#pragma unroll
+      for (int j = 0; j < RP_ITEMS; ++j)
+        if (d[j] >= 0) perm[pos[j]] = (uint32_t)(tile * RP_TILE + j * RP_THREADS + threadIdx.x);
+    }
+    for (int c = 0; c < mc.n; ++c) {
+      const int w = mc.width[c];
+      if (w == 8) {
+        int64_t v[RP_ITEMS];
+#pragma unroll
+        for (int j = 0; j < RP_ITEMS; ++j)
+          if (d[j] >= 0) v[j] = reinterpret_cast<const int64_t*>(mc.src[c])[tile * RP_TILE + j * RP_THREADS + threadIdx.x];
+#pragma unroll
+        for (int j = 0; j < RP_ITEMS; ++j)
+          if (d[j] >= 0)
+            *reinterpret_cast<int64_t*>(mc.dst[c] + mc.base[c * n_out + d[j]] + (int64_t)(pos[j] - start_s[d[j]]) * 8) = v[j];
+      } else if (w == 4) {
+        int32_t v[RP_ITEMS];
+#pragma unroll
+        for (int j = 0; j < RP_ITEMS; ++j)
+          if (d[j] >= 0) v[j] = reinterpret_cast<const int32_t*>(mc.src[c])[tile * RP_TILE + j * RP_THREADS + threadIdx.x];
+#pragma unroll
+        for (int j = 0; j < RP_ITEMS; ++j)
+          if (d[j] >= 0)
+            *reinterpret_cast<int32_t*>(mc.dst[c] + mc.base[c * n_out + d[j]] + (int64_t)(pos[j] - start_s[d[j]]) * 4) = v[j];
+      } else {
+#pragma unroll
+        for (int j = 0; j < RP_ITEMS; ++j)
+          if (d[j] >= 0)
+            mc.dst[c][mc.base[c * n_out + d[j]] + (int64_t)(pos[j] - start_s[d[j]])] =
+                mc.src[c][tile * RP_TILE + j * RP_THREADS + threadIdx.x];
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- host side: phase 1 (destinations, histogram, scan: no host sync), then counts / permutation / column move ----
+SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out) {
+  if (n_out < 1 || n_out > RP_MAX_OUT) fail(B2_ERR_INVALID_ARG, "hash_split_begin supports 1..32 output partitions");
+  if (n >= (1ll << 32) - 1) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
+  SplitState st;
+  st.n = n;
+  st.n_out = n_out;
+  st.n_tiles = (n + RP_TILE - 1) / RP_TILE;
+  st.dest = dev_alloc(ctx, (size_t)n + 16);
+  st.hist = dev_alloc_zero(ctx, (size_t)(st.n_tiles * n_out + 2) * 8);
+  if (n == 0) return st;
+  int grid = grid_for(ctx, 8, n, RP_TILE);
+  rp_hist_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(KeySrc{keys, key32}, n, n_out, st.dest->as<uint8_t>(),
+                                                       st.hist->as<int64_t>(), st.n_tiles);
+  B2_LAUNCHED(ctx);
+  scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(st.hist->as<int64_t>(), st.n_tiles * n_out);
+  B2_LAUNCHED(ctx);
+  return st;
+}
+// start offset of every destination = scanned hist[d * n_tiles]: gathers the n_out + 1 starts into `out` (device)
+__global__ void rp_starts_kernel(const int64_t* __restrict__ off, int64_t n_tiles, int n_out, int64_t n,
+                                 int64_t* __restrict__ out) {
+  int d = threadIdx.x;
+  if (d < n_out) out[d] = n ? off[(int64_t)d * n_tiles] : 0;
+  if (d == n_out) out[d] = n;
+}
+void hash_split_starts_device(Ctx* ctx, const SplitState& st, int64_t* out_dev) {
+  rp_starts_kernel<<<1, 64, 0, ctx->stream>>>(st.hist->as<int64_t>(), st.n_tiles, st.n_out, st.n, out_dev);
+  B2_LAUNCHED(ctx);
+}
+void hash_split_counts(Ctx* ctx, const SplitState& st, std::vector<int64_t>* counts) {
+  counts->assign(st.n_out, 0);
+  if (st.n == 0) return;
+  auto tmp = dev_alloc(ctx, (size_t)(st.n_out + 1) * 8);
+  hash_split_starts_device(ctx, st, tmp->as<int64_t>());
+  std::vector<int64_t> starts(st.n_out + 1, 0);
+  B2_READBACK(ctx, starts.data(), tmp->ptr, starts.size() * 8);
+  for (int d = 0; d < st.n_out; ++d) (*counts)[d] = starts[d + 1] - starts[d];
+}
+BufPtr hash_split_perm(Ctx* ctx, const SplitState& st) {
+  auto perm = dev_alloc(ctx, (size_t)(st.n + 1) * 4);
+  if (st.n == 0) return perm;
+  rp_scatter_kernel<<<grid_for(ctx, 8, st.n, RP_TILE), RP_THREADS, 0, ctx->stream>>>(
+      st.dest->as<uint8_t>(), st.n, st.n_out, st.hist->as<int64_t>(), st.n_tiles, perm->as<uint32_t>());
+  B2_LAUNCHED(ctx);
+  return perm;
+}
+void hash_split_move(Ctx* ctx, const SplitState& st, int n_cols, const void* const* src, void* const* dst,
+                     const int* width, const int64_t* base_dev, uint32_t* perm_or_null) {
+  if (st.n == 0) return;
+  if (n_cols > 8) fail(B2_ERR_EXECUTION, "internal: hash_split_move handles 8 columns per launch");
+  MoveCols mc;
+  memset(&mc, 0, sizeof mc);
+  mc.n = n_cols;
+  for (int c = 0; c < n_cols; ++c) {
+    mc.src[c] = static_cast<const char*>(src[c]);
+    mc.dst[c] = static_cast<char*>(dst[c]);
+    mc.width[c] = width[c];
+  }
+  mc.base = base_dev;
+  rp_move_kernel<<<grid_for(ctx, 8, st.n, RP_TILE), RP_THREADS, 0, ctx->stream>>>(
+      st.dest->as<uint8_t>(), st.n, st.n_out, st.hist->as<int64_t>(), st.n_tiles, mc, perm_or_null);
+  B2_LAUNCHED(ctx);
+}
+
+BufPtr hash_partition_indices(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
+                              std::vector<int64_t>* counts) {
+  if (n_out < 1 || n_out > 255) fail(B2_ERR_INVALID_ARG, "hash repartition supports 1..255 output partitions");
+  if (n >= (1ll << 32) - 1) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
+  counts->assign(n_out, 0);
+  if (n == 0) return dev_alloc(ctx, 4);
+  if (n_out > RP_MAX_OUT) {
+    if (!keys) fail(B2_ERR_EXECUTION, "internal: packed keys required beyond 32 output partitions");
+    return partition_indices_scan_per_destination(ctx, keys, n, n_out, counts);
+  }
+  SplitState st = hash_split_begin(ctx, keys, key32, n, n_out);
+  BufPtr perm = hash_split_perm(ctx, st);
+  hash_split_counts(ctx, st, counts);
   return perm;
 }
 

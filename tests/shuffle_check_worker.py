@@ -1,0 +1,70 @@
+"""N-rank correctness check of the in-box shuffle (torchrun): the multiset of full rows is preserved bit-exactly,
+equal keys land on one rank, row order inside (source, destination) is kept.  Runs both exchange paths.
+
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 scratch/shuffle_check.py
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+import ballista_b200 as b2
+from ballista_b200 import RepartitionExec, cluster, col, tpch
+
+rank, local_rank, world = cluster.env_rank()
+torch.cuda.set_device(local_rank)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+ctx = b2.Context(local_rank)
+cluster.attach_communicator(ctx, dist, rank, world)
+cols = ["l_orderkey", "l_extendedprice", "l_returnflag", "l_shipdate"]
+
+
+def rows_of(table):
+    return list(zip(*[table[c].to_pylist() for c in cols]))
+
+
+def run(sf, rows_per_rank, mode):
+    if mode == "nccl":
+        os.environ["B2_SHUFFLE"] = "nccl"
+    else:
+        os.environ.pop("B2_SHUFFLE", None)
+    # uneven partitions; the last rank also gets an empty second batch
+    n = rows_per_rank + 1000 * rank
+    r0 = rank * (rows_per_rank + 5000)
+    part = ctx.tpch("lineitem", sf, r0, r0 + n, columns=cols)
+    import pyarrow as pa
+    mine = rows_of(pa.Table.from_batches([part.to_arrow()]))
+    rep = RepartitionExec(tpch.scan(ctx, [[part]]), "Hash", world, [col("l_orderkey")])
+    got = rep.collect(rank)
+    path = rep.last_path()
+    got_rows = rows_of(got)
+    gathered_in, gathered_out = [None] * world, [None] * world
+    dist.all_gather_object(gathered_in, mine)
+    dist.all_gather_object(gathered_out, got_rows)
+    if rank == 0:
+        all_in = sorted(r for p in gathered_in for r in p)
+        all_out = sorted(r for p in gathered_out for r in p)
+        assert all_in == all_out, f"{mode}: multiset of rows changed ({len(all_in)} vs {len(all_out)})"
+        owner = {}
+        for p, rows in enumerate(gathered_out):
+            for r in rows:
+                assert owner.setdefault(r[0], p) == p, f"{mode}: key {r[0]} on two ranks"
+        # order: inside one destination, rows of one source keep their source order and sources arrive in rank order
+        for p, rows in enumerate(gathered_out):
+            want = [r for s in range(world) for r in gathered_in[s] if owner[r[0]] == p]
+            assert rows == want, f"{mode}: row order inside partition {p} differs"
+        print(f"ok [{mode}] path={path} sf={sf} rows_in={len(all_in)} parts={[len(p) for p in gathered_out]}", flush=True)
+    if mode == "p2p":
+        assert path == "nvlink-peer-pull", path
+    dist.barrier()
+
+
+for mode in ("p2p", "nccl", "p2p"):
+    run(0.01, 20_000, mode)
+run(0.1, 150_000, "p2p")   # arena regrow
+run(0.01, 3_000, "p2p")     # smaller again: arena reused
+ctx.synchronize()
+if rank == 0:
+    print("shuffle_check: all ok")

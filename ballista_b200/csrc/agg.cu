@@ -190,68 +190,6 @@ int64_t AggRunner::finish(BufPtr* slots_out) {
 // ------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ u128 key_bits(const Key128& k) { return ((u128)k.hi << 64) | k.lo; }
 
-__global__ void emit_key_i32_kernel(const Key128* keys, const uint32_t* slots, int64_t ng, int byte_off, int32_t* out) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) out[i] = (int32_t)(uint32_t)(key_bits(keys[slots[i]]) >> (8 * byte_off));
-}
-__global__ void emit_key_i64_kernel(const Key128* keys, const uint32_t* slots, int64_t ng, int byte_off, int64_t* out) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) out[i] = (int64_t)(u64)(key_bits(keys[slots[i]]) >> (8 * byte_off));
-}
-// Utf8 keys: one CTA scans lengths chunk by chunk (group counts with Utf8 keys are small), then writes bytes
-__global__ void emit_key_str_kernel(const Key128* keys, const uint32_t* slots, int64_t ng, int byte_off,
-                                    int32_t* off, uint8_t* chr) {
-  __shared__ int32_t warp_sums[32];
-  __shared__ int32_t carry_s;
-  if (threadIdx.x == 0) carry_s = 0;
-  __syncthreads();
-  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  for (int64_t base = 0; base < ng; base += blockDim.x) {
-    int64_t i = base + threadIdx.x;
-    u128 bits = 0;
-    int len = 0;
-    if (i < ng) {
-      bits = key_bits(keys[slots[i]]) >> (8 * byte_off);
-      len = (int)(uint8_t)bits;
-    }
-    int v = len;
-    for (int d = 1; d < 32; d <<= 1) {
-      int t = __shfl_up_sync(0xffffffffu, v, d);
-      if (lane >= d) v += t;
-    }
-    if (lane == 31) warp_sums[warp] = v;
-    __syncthreads();
-    int woff = 0, total = 0;
-    for (int w = 0; w < nwarps; ++w) {
-      if (w < warp) woff += warp_sums[w];
-      total += warp_sums[w];
-    }
-    int carry = carry_s;
-    int excl = carry + woff + v - len;
-    if (i < ng) {
-      off[i] = excl;
-      for (int q = 0; q < len; ++q) chr[excl + q] = (uint8_t)(bits >> (8 * (q + 1)));
-      if (i == ng - 1) off[ng] = excl + len;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) carry_s = carry + total;
-    __syncthreads();
-  }
-}
-__global__ void emit_f64_kernel(const double* src, const uint32_t* slots, int64_t ng, double* out) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) out[i] = src[slots[i]];
-}
-__global__ void emit_u64_kernel(const u64* src, const uint32_t* slots, int64_t ng, u64* out) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) out[i] = src[slots[i]];
-}
-// AVG evaluate(): sum / count as f64
-__global__ void emit_avg_kernel(const double* sum, const u64* cnt, const uint32_t* slots, int64_t ng, double* out) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) out[i] = __ddiv_rn(sum[slots[i]], (double)cnt[slots[i]]);
-}
-
 static Column new_fixed(Ctx* ctx, int dtype, int64_t n) {
   Column c;
   c.dtype = dtype;
@@ -260,63 +198,138 @@ static Column new_fixed(Ctx* ctx, int dtype, int64_t n) {
   return c;
 }
 
-Column emit_key_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, const KeyPart& part) {
-  int grid = grid_for(ctx, 8, ng, 256);
-  const Key128* keys = t.keys->as<Key128>();
-  const uint32_t* sl = slots->as<uint32_t>();
+// ---- all output columns of one aggregate in ONE launch: blockIdx.y selects the column ----
+enum { EMIT_KEY_I32 = 0, EMIT_KEY_I64, EMIT_KEY_STR, EMIT_F64, EMIT_U64, EMIT_AVG };
+struct EmitCol {
+  int kind;
+  int byte_off;      // key columns: byte offset of the part inside the packed key
+  const void* src;   // EMIT_F64 / EMIT_AVG: sums; EMIT_U64: counts
+  const void* src2;  // EMIT_AVG: counts
+  void* out;         // values (Utf8: int32 offsets)
+  uint8_t* chr;      // Utf8 characters
+};
+constexpr int EMIT_MAX_COLS = 24;
+struct EmitArgs {
+  int n;
+  EmitCol c[EMIT_MAX_COLS];
+};
+__global__ void __launch_bounds__(256) emit_all_kernel(EmitArgs args, const Key128* __restrict__ keys,
+                                                       const uint32_t* __restrict__ slots, int64_t ng) {
+  const EmitCol& col = args.c[blockIdx.y];
+  if (col.kind == EMIT_KEY_STR) {
+    // one CTA scans the lengths chunk by chunk (group counts with Utf8 keys are small), then writes the bytes
+    if (blockIdx.x != 0) return;
+    __shared__ int32_t warp_sums[32];
+    __shared__ int32_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    int32_t* off = static_cast<int32_t*>(col.out);
+    for (int64_t base = 0; base < ng; base += blockDim.x) {
+      int64_t i = base + threadIdx.x;
+      u128 bits = 0;
+      int len = 0;
+      if (i < ng) {
+        bits = key_bits(keys[slots[i]]) >> (8 * col.byte_off);
+        len = (int)(uint8_t)bits;
+      }
+      int v = len;
+      for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += t;
+      }
+      if (lane == 31) warp_sums[warp] = v;
+      __syncthreads();
+      int woff = 0, total = 0;
+      for (int w = 0; w < nwarps; ++w) {
+        if (w < warp) woff += warp_sums[w];
+        total += warp_sums[w];
+      }
+      int carry = carry_s;
+      int excl = carry + woff + v - len;
+      if (i < ng) {
+        off[i] = excl;
+        for (int q = 0; q < len; ++q) col.chr[excl + q] = (uint8_t)(bits >> (8 * (q + 1)));
+        if (i == ng - 1) off[ng] = excl + len;
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) carry_s = carry + total;
+      __syncthreads();
+    }
+    return;
+  }
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < ng; i += (int64_t)gridDim.x * blockDim.x) {
+    uint32_t sl = slots[i];
+    switch (col.kind) {
+      case EMIT_KEY_I32:
+        static_cast<int32_t*>(col.out)[i] = (int32_t)(uint32_t)(key_bits(keys[sl]) >> (8 * col.byte_off));
+        break;
+      case EMIT_KEY_I64:
+        static_cast<int64_t*>(col.out)[i] = (int64_t)(u64)(key_bits(keys[sl]) >> (8 * col.byte_off));
+        break;
+      case EMIT_F64: static_cast<double*>(col.out)[i] = static_cast<const double*>(col.src)[sl]; break;
+      case EMIT_U64: static_cast<u64*>(col.out)[i] = static_cast<const u64*>(col.src)[sl]; break;
+      default:  // AVG evaluate(): sum / count as f64
+        static_cast<double*>(col.out)[i] =
+            __ddiv_rn(static_cast<const double*>(col.src)[sl], (double)static_cast<const u64*>(col.src2)[sl]);
+        break;
+    }
+  }
+}
+
+EmitPlan::EmitPlan(Ctx* c, const GroupTable& t, const BufPtr& s, int64_t n) : ctx(c), table(t), slots(s), ng(n) {}
+void EmitPlan::push(int kind, int byte_off, const void* src, const void* src2, Column col) {
+  descs.push_back(EmitDesc{kind, byte_off, src, src2});
+  cols.push_back(std::move(col));
+}
+void EmitPlan::key(const KeyPart& part) {
   if (part.dtype == B2_UTF8) {
     Column c;
     c.dtype = B2_UTF8;
     c.length = ng;
     c.data = dev_alloc_zero(ctx, (size_t)(ng + 1) * 4);
     c.chars = dev_alloc(ctx, (size_t)ng * 15 + 16);
-    if (ng) {
-      emit_key_str_kernel<<<1, 1024, 0, ctx->stream>>>(keys, sl, ng, part.byte_off, c.data->as<int32_t>(),
-                                                      c.chars->as<uint8_t>());
-      B2_LAUNCHED(ctx);
-      int32_t total = 0;
-      B2_READBACK(ctx, &total, c.data->as<int32_t>() + ng, 4);
-      c.chars_len = total;
+    push(EMIT_KEY_STR, part.byte_off, nullptr, nullptr, std::move(c));
+    return;
+  }
+  push(part.bytes == 8 ? EMIT_KEY_I64 : EMIT_KEY_I32, part.byte_off, nullptr, nullptr, new_fixed(ctx, part.dtype, ng));
+}
+void EmitPlan::sum(int a) {
+  push(EMIT_F64, 0, table.acc->as<double>() + (u64)a * table.cap, nullptr, new_fixed(ctx, B2_FLOAT64, ng));
+}
+void EmitPlan::count(int a) {
+  push(EMIT_U64, 0, table.cnt->as<u64>() + (u64)a * table.cap, nullptr, new_fixed(ctx, B2_UINT64, ng));
+}
+void EmitPlan::avg(int a, int cidx) {
+  push(EMIT_AVG, 0, table.acc->as<double>() + (u64)a * table.cap, table.cnt->as<u64>() + (u64)cidx * table.cap,
+       new_fixed(ctx, B2_FLOAT64, ng));
+}
+std::vector<Column> EmitPlan::run() {
+  if (ng == 0) return std::move(cols);
+  std::vector<size_t> strs;
+  for (size_t b = 0; b < cols.size(); b += EMIT_MAX_COLS) {
+    EmitArgs args;
+    memset(&args, 0, sizeof args);
+    args.n = (int)std::min<size_t>(EMIT_MAX_COLS, cols.size() - b);
+    for (int k = 0; k < args.n; ++k) {
+      const EmitDesc& d = descs[b + k];
+      Column& c = cols[b + k];
+      args.c[k] = EmitCol{d.kind, d.byte_off, d.src, d.src2, c.data->ptr, c.chars ? c.chars->as<uint8_t>() : nullptr};
+      if (d.kind == EMIT_KEY_STR) strs.push_back(b + k);
     }
-    return c;
-  }
-  Column c = new_fixed(ctx, part.dtype, ng);
-  if (ng) {
-    if (part.bytes == 8)
-      emit_key_i64_kernel<<<grid, 256, 0, ctx->stream>>>(keys, sl, ng, part.byte_off, c.data->as<int64_t>());
-    else
-      emit_key_i32_kernel<<<grid, 256, 0, ctx->stream>>>(keys, sl, ng, part.byte_off, c.data->as<int32_t>());
+    dim3 grid((unsigned)grid_for(ctx, 8, ng, 256), (unsigned)args.n);
+    emit_all_kernel<<<grid, 256, 0, ctx->stream>>>(args, table.keys->as<Key128>(), slots->as<uint32_t>(), ng);
     B2_LAUNCHED(ctx);
   }
-  return c;
-}
-Column emit_sum_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int a) {
-  Column c = new_fixed(ctx, B2_FLOAT64, ng);
-  if (ng) {
-    emit_f64_kernel<<<grid_for(ctx, 8, ng, 256), 256, 0, ctx->stream>>>(t.acc->as<double>() + (u64)a * t.cap,
-                                                                       slots->as<uint32_t>(), ng, c.data->as<double>());
-    B2_LAUNCHED(ctx);
+  if (!strs.empty()) {  // one readback for the character totals of all Utf8 key columns
+    std::vector<int32_t> totals(strs.size(), 0);
+    for (size_t k = 0; k < strs.size(); ++k)
+      B2_CUDA(cudaMemcpyAsync(&totals[k], cols[strs[k]].data->as<int32_t>() + ng, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_SYNC(ctx);
+    for (size_t k = 0; k < strs.size(); ++k) cols[strs[k]].chars_len = totals[k];
   }
-  return c;
-}
-Column emit_count_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int a) {
-  Column c = new_fixed(ctx, B2_UINT64, ng);
-  if (ng) {
-    emit_u64_kernel<<<grid_for(ctx, 8, ng, 256), 256, 0, ctx->stream>>>(t.cnt->as<u64>() + (u64)a * t.cap,
-                                                                       slots->as<uint32_t>(), ng, c.data->as<u64>());
-    B2_LAUNCHED(ctx);
-  }
-  return c;
-}
-Column emit_avg_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int a, int cidx) {
-  Column c = new_fixed(ctx, B2_FLOAT64, ng);
-  if (ng) {
-    emit_avg_kernel<<<grid_for(ctx, 8, ng, 256), 256, 0, ctx->stream>>>(
-        t.acc->as<double>() + (u64)a * t.cap, t.cnt->as<u64>() + (u64)cidx * t.cap, slots->as<uint32_t>(), ng,
-        c.data->as<double>());
-    B2_LAUNCHED(ctx);
-  }
-  return c;
+  return std::move(cols);
 }
 
 }  // namespace b2

@@ -87,10 +87,27 @@ struct AggRunner {
   void check_status(int st);
 };
 
-// emit kernels (agg.cu): gather table contents into output columns
-Column emit_key_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, const KeyPart& part);
-Column emit_sum_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int acc_idx);
-Column emit_count_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int cnt_idx);
-Column emit_avg_column(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng, int acc_idx, int cnt_idx);
+// Output assembly (agg.cu): every output column of one aggregate is gathered from the table by ONE launch
+// (blockIdx.y = column) and the character totals of all Utf8 key columns come back in one readback.
+struct EmitPlan {
+  struct EmitDesc {
+    int kind, byte_off;
+    const void *src, *src2;
+  };
+  Ctx* ctx;
+  const GroupTable& table;
+  BufPtr slots;
+  int64_t ng;
+  std::vector<EmitDesc> descs;
+  std::vector<Column> cols;
+  EmitPlan(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng);
+  void key(const KeyPart& part);
+  void sum(int acc_idx);
+  void count(int cnt_idx);
+  void avg(int acc_idx, int cnt_idx);
+  std::vector<Column> run();  // columns in the order they were requested
+ private:
+  void push(int kind, int byte_off, const void* src, const void* src2, Column col);
+};
 
 }  // namespace b2

@@ -81,6 +81,7 @@ void b2_ctx_destroy(b2_ctx* ctx) {
       fprintf(stderr, "[b2 trace] %-60s %10.3f %8lld\n", kv.first.c_str(), kv.second.first * 1e3,
               (long long)kv.second.second);
   }
+  if (ctx->c.pinned_stage) cudaFreeHost(ctx->c.pinned_stage);
   cudaStreamDestroy(ctx->c.stream);
   cudaStreamDestroy(ctx->c.copy_stream);
   delete ctx;

@@ -218,6 +218,50 @@ static void* host_buf(ArrayPriv* p, size_t n) {
   return q;
 }
 
+// Device -> host copies of one exported batch.  Small results (the usual case: aggregate outputs) go through
+// the context's pinned staging buffer: every copy is truly asynchronous and ONE synchronisation serves them all,
+// instead of one blocking pageable copy per buffer.  Large batches are copied directly.
+struct D2HStager {
+  struct Item {
+    void* dst;
+    const void* src;
+    size_t bytes;
+  };
+  Ctx* ctx;
+  std::vector<Item> items;
+  explicit D2HStager(Ctx* c) : ctx(c) {}
+  void add(void* dst, const void* src, size_t bytes) { items.push_back(Item{dst, src, bytes}); }
+  void flush() {
+    constexpr size_t CAP = 4u << 20;
+    size_t total = 0;
+    for (auto& it : items) total += (it.bytes + 15) & ~(size_t)15;
+    if (total <= CAP && !ctx->pinned_stage) {
+      if (cudaHostAlloc(&ctx->pinned_stage, CAP, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        ctx->pinned_stage = nullptr;
+      }
+    }
+    if (total <= CAP && ctx->pinned_stage) {
+      char* base = static_cast<char*>(ctx->pinned_stage);
+      size_t off = 0;
+      for (auto& it : items) {
+        B2_CUDA(cudaMemcpyAsync(base + off, it.src, it.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        off += (it.bytes + 15) & ~(size_t)15;
+      }
+      B2_SYNC(ctx);
+      off = 0;
+      for (auto& it : items) {
+        memcpy(it.dst, base + off, it.bytes);
+        off += (it.bytes + 15) & ~(size_t)15;
+      }
+    } else {
+      for (auto& it : items) B2_CUDA(cudaMemcpyAsync(it.dst, it.src, it.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+      B2_SYNC(ctx);
+    }
+    items.clear();
+  }
+};
+
 void batch_to_arrow(const Batch& b, ArrowArray* out) {
   Ctx* ctx = b.ctx;
   auto* top = new ArrayPriv;
@@ -237,6 +281,8 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
   out->private_data = top;
   try {
     std::vector<std::pair<size_t, std::vector<uint8_t>>> bools;  // bit-pack after the sync
+    bools.reserve(b.cols.size());  // element addresses are handed to the stager
+    D2HStager stage(ctx);
     for (size_t ci = 0; ci < b.cols.size(); ++ci) {
       const Column& col = b.cols[ci];
       if (!col.data) fail(B2_ERR_EXECUTION, "internal: column '" + b.schema.fields[ci].name +
@@ -249,30 +295,25 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
       if (col.dtype == B2_UTF8) {
         void* ho = host_buf(p, (size_t)(col.length + 1) * 4);
         void* hd = host_buf(p, (size_t)col.chars_len);
-        B2_CUDA(cudaMemcpyAsync(ho, col.data->ptr, (size_t)(col.length + 1) * 4, cudaMemcpyDeviceToHost,
-                                ctx->stream));
-        if (col.chars_len)
-          B2_CUDA(cudaMemcpyAsync(hd, col.chars->ptr, (size_t)col.chars_len, cudaMemcpyDeviceToHost,
-                                  ctx->stream));
+        stage.add(ho, col.data->ptr, (size_t)(col.length + 1) * 4);
+        if (col.chars_len) stage.add(hd, col.chars->ptr, (size_t)col.chars_len);
         p->buffers = {nullptr, ho, hd};
       } else if (col.dtype == B2_BOOL) {
         bools.emplace_back(ci, std::vector<uint8_t>((size_t)col.length));
-        if (col.length)
-          B2_CUDA(cudaMemcpyAsync(bools.back().second.data(), col.data->ptr, (size_t)col.length,
-                                  cudaMemcpyDeviceToHost, ctx->stream));
+        if (col.length) stage.add(bools.back().second.data(), col.data->ptr, (size_t)col.length);
         void* hb = host_buf(p, (size_t)(col.length + 7) / 8);
         memset(hb, 0, (size_t)(col.length + 7) / 8);
         p->buffers = {nullptr, hb};
       } else {
         size_t nb = (size_t)col.length * dtype_width(col.dtype);
         void* hv = host_buf(p, nb);
-        if (nb) B2_CUDA(cudaMemcpyAsync(hv, col.data->ptr, nb, cudaMemcpyDeviceToHost, ctx->stream));
+        if (nb) stage.add(hv, col.data->ptr, nb);
         p->buffers = {nullptr, hv};
       }
       a->n_buffers = (int64_t)p->buffers.size();
       a->buffers = p->buffers.data();
     }
-    B2_SYNC(ctx);
+    stage.flush();
     for (auto& pr : bools) {
       auto* p = static_cast<ArrayPriv*>(top->child_store[pr.first].private_data);
       uint8_t* bits = static_cast<uint8_t*>(const_cast<void*>(p->buffers[1]));

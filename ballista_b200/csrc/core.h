@@ -40,6 +40,7 @@ struct Ctx {
   Comm* comm = nullptr;
   int rank = 0, nranks = 1;
   int64_t bytes_sent = 0;
+  void* pinned_stage = nullptr;  // 4 MiB pinned host buffer for the D2H of small result batches (core.cu)
   // optional per-launch timing of the dominant (aggregate scan) kernel with CUDA events on `stream`
   bool profiling = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;

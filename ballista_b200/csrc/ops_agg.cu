@@ -73,21 +73,23 @@ BatchPtr HashAggregateExec::emit(AggRunner& r, bool partial, const std::vector<i
     return b;
   }
   b->num_rows = ng;
-  for (size_t g = 0; g < groups.size(); ++g) b->cols.push_back(emit_key_column(ctx, *r.main, slots, ng, layout.parts[g]));
+  EmitPlan ep(ctx, *r.main, slots, ng);
+  for (size_t g = 0; g < groups.size(); ++g) ep.key(layout.parts[g]);
   for (size_t a = 0; a < aggs.size(); ++a) {
     switch (aggs[a].fn) {
-      case B2_AGG_SUM: b->cols.push_back(emit_sum_column(ctx, *r.main, slots, ng, sum_idx[a])); break;
-      case B2_AGG_COUNT: b->cols.push_back(emit_count_column(ctx, *r.main, slots, ng, cnt_idx[a])); break;
+      case B2_AGG_SUM: ep.sum(sum_idx[a]); break;
+      case B2_AGG_COUNT: ep.count(cnt_idx[a]); break;
       case B2_AGG_AVG:
         if (partial) {
-          b->cols.push_back(emit_count_column(ctx, *r.main, slots, ng, cnt_idx[a]));
-          b->cols.push_back(emit_sum_column(ctx, *r.main, slots, ng, sum_idx[a]));
+          ep.count(cnt_idx[a]);
+          ep.sum(sum_idx[a]);
         } else {
-          b->cols.push_back(emit_avg_column(ctx, *r.main, slots, ng, sum_idx[a], cnt_idx[a]));
+          ep.avg(sum_idx[a], cnt_idx[a]);
         }
         break;
     }
   }
+  b->cols = ep.run();
   return b;
 }
 

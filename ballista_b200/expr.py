@@ -15,6 +15,7 @@ class Expr:
         self.children = list(children)
         self.kw = kw
         self.alias_name = None
+        self._lowered = {}  # (column names, default name) -> (IR struct, keep-alive objects); expressions are immutable
 
     # ---- naming ----
     def alias(self, name):
@@ -91,18 +92,23 @@ class Expr:
         out.append(n)
 
     def lower(self, names, keep, default_name=None):
-        """-> _capi.Expr against the column `names`; `keep` receives objects that must outlive the call."""
-        nodes = []
-        self._emit(list(names), nodes, keep)
-        arr = (K.ExprNode * len(nodes))(*nodes)
-        keep.append(arr)
+        """-> _capi.Expr against the column `names`; `keep` receives objects that must outlive the call.
+        The lowered IR is cached on the expression (the library copies it at operator construction)."""
+        key = (tuple(names), default_name)
+        hit = self._lowered.get(key)
+        if hit is None:
+            mine, nodes = [], []
+            self._emit(list(names), nodes, mine)
+            arr = (K.ExprNode * len(nodes))(*nodes)
+            mine.append(arr)
+            nm = self.alias_name or default_name or self.display()
+            b = nm.encode("utf-8")
+            mine.append(b)
+            hit = (C.cast(arr, C.POINTER(K.ExprNode)), len(nodes), b, mine)
+            self._lowered[key] = hit
         e = K.Expr()
-        e.nodes = C.cast(arr, C.POINTER(K.ExprNode))
-        e.n_nodes = len(nodes)
-        nm = self.alias_name or default_name or self.display()
-        b = nm.encode("utf-8")
-        keep.append(b)
-        e.name = b
+        e.nodes, e.n_nodes, e.name = hit[0], hit[1], hit[2]
+        keep.append(hit[3])
         return e
 
     def display(self):

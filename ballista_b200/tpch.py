@@ -5,6 +5,8 @@ Each builder returns (partial_stage_plan, make_final) so that the Partial stage 
 and the Final stage runs over the merged partial states — the two Ballista query stages split at
 rust/scheduler/src/planner.rs:149-169.
 """
+import functools
+
 import pyarrow as pa
 
 from . import _capi as K
@@ -23,6 +25,7 @@ Q1_BYTES_PER_ROW = 46
 Q6_BYTES_PER_ROW = 28
 
 
+@functools.lru_cache(maxsize=None)
 def q1_aggregates():
     disc_price = col("l_extendedprice") * (lit(1) - col("l_discount"))
     charge = col("l_extendedprice") * (lit(1) - col("l_discount")) * (lit(1) + col("l_tax"))
@@ -38,25 +41,35 @@ def q1_aggregates():
     ]
 
 
+@functools.lru_cache(maxsize=None)
+def _q1_groups():
+    return (col("l_returnflag"), col("l_linestatus"))
+
+
+@functools.lru_cache(maxsize=64)
+def _q1_predicate(ship_date):
+    return col("l_shipdate") <= date(ship_date)
+
+
 def q1_partial(scan, ship_date="1998-09-02"):
     """HashAggregateExec(Partial) <- CoalesceBatchesExec <- FilterExec(l_shipdate <= d) <- scan."""
-    filt = CoalesceBatchesExec(FilterExec(col("l_shipdate") <= date(ship_date), scan))
-    groups = [col("l_returnflag"), col("l_linestatus")]
-    return HashAggregateExec("Partial", groups, q1_aggregates(), filt)
+    filt = CoalesceBatchesExec(FilterExec(_q1_predicate(ship_date), scan))
+    return HashAggregateExec("Partial", _q1_groups(), q1_aggregates(), filt)
 
 
 def q1_final(partial_states, input_schema):
     """HashAggregateExec(Final) <- MergeExec <- partial states (any plan producing the Partial schema)."""
-    groups = [col("l_returnflag"), col("l_linestatus")]
-    return HashAggregateExec("Final", groups, q1_aggregates(), MergeExec(partial_states), input_schema=input_schema)
+    return HashAggregateExec("Final", _q1_groups(), q1_aggregates(), MergeExec(partial_states), input_schema=input_schema)
 
 
+@functools.lru_cache(maxsize=None)
 def q6_predicate():
     return ((col("l_shipdate") >= date("1994-01-01")) & (col("l_shipdate") < date("1995-01-01"))
             & col("l_discount").between(lit(0.06) - lit(0.01), lit(0.06) + lit(0.01))
             & (col("l_quantity") < lit(24)))
 
 
+@functools.lru_cache(maxsize=None)
 def q6_aggregates():
     return [sum_(col("l_extendedprice") * col("l_discount")).alias("revenue")]
 
@@ -70,20 +83,28 @@ def q6_final(partial_states, input_schema):
     return HashAggregateExec("Final", [], q6_aggregates(), MergeExec(partial_states), input_schema=input_schema)
 
 
+@functools.lru_cache(maxsize=64)
+def _q3_predicates(segment, cutoff):
+    return (col("c_mktsegment") == lit(segment), col("o_orderdate") < date(cutoff), col("l_shipdate") > date(cutoff))
+
+
 def q3_join_tree(customer, orders, lineitem, segment="BUILDING", cutoff="1995-03-15"):
     """(customer ⋈ orders) ⋈ lineitem, left-deep, build = left, filters pushed below the joins."""
-    c = CoalesceBatchesExec(FilterExec(col("c_mktsegment") == lit(segment), customer))
-    o = CoalesceBatchesExec(FilterExec(col("o_orderdate") < date(cutoff), orders))
-    l = CoalesceBatchesExec(FilterExec(col("l_shipdate") > date(cutoff), lineitem))
+    pc, po, pl = _q3_predicates(segment, cutoff)
+    c = CoalesceBatchesExec(FilterExec(pc, customer))
+    o = CoalesceBatchesExec(FilterExec(po, orders))
+    l = CoalesceBatchesExec(FilterExec(pl, lineitem))
     j1 = CoalesceBatchesExec(HashJoinExec(c, o, [("c_custkey", "o_custkey")]))
     j2 = CoalesceBatchesExec(HashJoinExec(j1, l, [("o_orderkey", "l_orderkey")]))
     return j2
 
 
+@functools.lru_cache(maxsize=None)
 def q3_aggregates():
     return [sum_(col("l_extendedprice") * (lit(1) - col("l_discount"))).alias("revenue")]
 
 
+@functools.lru_cache(maxsize=None)
 def q3_groups():
     return [col("l_orderkey"), col("o_orderdate"), col("o_shippriority")]
 

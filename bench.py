@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-other", action="store_true", help="skip the other BASELINE configs (Q6 / Q3 at SF10, shuffle)")
+    ap.add_argument("--other-sf", type=float, default=10.0)
     ap.add_argument("--cpu-seconds", type=float, default=3.0, help="wall-clock target of the cpu_baseline sample")
     return ap.parse_args()
 
@@ -387,6 +389,97 @@ def run_reference(args):
                     "no-CSE temporaries, byte-key hash aggregate); the Rust reference itself cannot be built here"}
 
 
+def run_other_configs(args, ctx, env):
+    """The other BASELINE.json configs, timed the same way (CUDA events on the library's stream, max over ranks)
+    and reported under "other_configs": Q6 and Q3 at SF10 on one GPU's partition, and at N > 1 the hash-repartition
+    shuffle of the Q3 lineitem side (l_orderkey, l_extendedprice, l_discount = 20 B/row) over NVLink."""
+    import torch.distributed as dist
+    from ballista_b200 import MemoryExec, RepartitionExec, _capi, cluster, col, tpch
+    rank, world, torch = env
+    stream = torch.cuda.ExternalStream(ctx.cuda_stream)
+    sf = args.other_sf
+    peak = measured_peaks().get("hbm_gbs") or 6650.0
+
+    def timeit(fn, steps=10, warmup=3):
+        for _ in range(warmup):
+            fn()
+        if world > 1:
+            dist.barrier()
+        ctx.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = ctx.kernel_launches()
+        e0.record(stream)
+        for _ in range(steps):
+            r = fn()
+        e1.record(stream)
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        return cluster.max_over_ranks(dist, torch, e0.elapsed_time(e1) / steps, world), (ctx.kernel_launches() - l0) / steps, r
+
+    out = {}
+    nrows = lambda t: _capi.lib().b2_tpch_num_rows(t.encode(), float(sf))
+    # ---- Q6 @ SF10: filter + global SUM over this rank's lineitem (28 B/row) ----
+    li6 = ctx.tpch("lineitem", sf * world, rank * nrows("lineitem"), (rank + 1) * nrows("lineitem"), columns=tpch.Q6_COLUMNS)
+
+    def q6():
+        scan = tpch.scan(ctx, [[li6]])
+        part = tpch.q6_partial(scan)
+        return tpch.run_two_stage(ctx, part, lambda s: tpch.q6_final(s, scan.schema()), merge="allgather"), part
+    ms, launches, (tab, part) = timeit(q6)
+    n = li6.num_rows
+    out["q6"] = {"workload": f"TPC-H Q6, SF{sf:g} lineitem per GPU ({n} rows x 28 B)", "ms_per_step": ms,
+                 "rows_per_s": n * world / (ms / 1e3), "GB_per_s_per_gpu": n * 28 / (ms / 1e3) / 1e9,
+                 "frac_of_hbm_peak": n * 28 / (ms / 1e3) / 1e9 / peak, "launches_per_step": launches,
+                 "path": part.last_path(), "revenue": tab.to_pylist()[0]["revenue"]}
+    del li6
+    # ---- Q3 @ SF10: customer |x| orders |x| lineitem + group-by (this rank's partition of all three) ----
+    cu = ctx.tpch("customer", sf, columns=tpch.Q3_CUSTOMER_COLUMNS)
+    od = ctx.tpch("orders", sf, columns=tpch.Q3_ORDERS_COLUMNS)
+    li = ctx.tpch("lineitem", sf, columns=tpch.Q3_LINEITEM_COLUMNS)
+
+    def q3():
+        c, o, l = (tpch.scan(ctx, [[x]]) for x in (cu, od, li))
+        partial = tpch.q3_partial(c, o, l)
+        states = partial.collect_device(0)
+        final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
+        return sum(b.num_rows for b in final.collect_device(0))
+    ms, launches, groups = timeit(q3)
+    rows = cu.num_rows + od.num_rows + li.num_rows
+    scan_bytes = cu.num_bytes + od.num_bytes + li.num_bytes
+    out["q3"] = {"workload": f"TPC-H Q3, SF{sf:g} on each GPU (customer {cu.num_rows} + orders {od.num_rows} + "
+                             f"lineitem {li.num_rows} rows; {scan_bytes / 1e9:.3f} GB of scanned columns)",
+                 "ms_per_step": ms, "input_rows_per_s": rows * world / (ms / 1e3),
+                 "scan_GB_per_s_per_gpu": scan_bytes / (ms / 1e3) / 1e9, "groups": groups, "launches_per_step": launches,
+                 "note": "late materialisation reads only the key / predicate columns of non-matching rows, so "
+                         "scan GB/s is algorithmic bytes / time, not DRAM traffic"}
+    del cu, od
+    # ---- shuffle: RepartitionExec(Hash(l_orderkey), N) with the communicator attached (N > 1) ----
+    if world > 1:
+        cols = ["l_orderkey", "l_extendedprice", "l_discount"]
+        n = nrows("lineitem")
+        part = ctx.tpch("lineitem", sf * world, rank * n, (rank + 1) * n, columns=cols)
+        path = [None]
+
+        def shuffle():
+            rep = RepartitionExec(tpch.scan(ctx, [[part]]), "Hash", world, [col("l_orderkey")])
+            got = rep.collect_device(rank)
+            path[0] = rep.last_path()
+            return sum(b.num_rows for b in got)
+        sent0 = ctx.comm_bytes_sent()
+        ms, launches, _ = timeit(shuffle, steps=10, warmup=3)
+        sent = (ctx.comm_bytes_sent() - sent0) / 13.0
+        out["shuffle"] = {"workload": f"hash repartition of lineitem SF{sf:g} per GPU ({n} rows x 20 B) into {world} "
+                                      "partitions, exchanged over NVLink", "path": path[0], "ms_per_step": ms,
+                          "rows_per_s": n * world / (ms / 1e3), "egress_bytes_per_gpu": sent,
+                          "egress_GB_per_s_per_gpu": sent / (ms / 1e3) / 1e9,
+                          "frac_of_nvlink_900GBps": sent / (ms / 1e3) / 1e9 / 900.0, "launches_per_step": launches,
+                          "note": "whole operator (split + metadata + exchange); the pull step alone is in profiles/"}
+        del part
+    del li
+    return out
+
+
+
 def emit(real_stdout, obj):
     os.write(real_stdout, (json.dumps(obj) + "\n").encode())
 
@@ -406,6 +499,8 @@ def main():
     rank, world, torch = env
     if not args.no_e2e:
         out["e2e"] = run_e2e(args, ctx, dev_batches, timed, env)
+    if not args.no_other:
+        out["other_configs"] = run_other_configs(args, ctx, env)
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
         v, n, sec = cpu_q1(args.sf, args.cpu_seconds, threads)

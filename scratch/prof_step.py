@@ -10,7 +10,7 @@ def tick(name, t0):
     ctx.synchronize(); T[name] = T.get(name, 0) + time.perf_counter() - t0
 N = 20
 for it in range(N + 3):
-    if it == 3: T.clear()
+    if it == 3: T.clear(); ctx.set_profiling(2)
     t = time.perf_counter(); scan = tpch.scan(ctx, [[li]]); partial = tpch.q1_partial(scan); tick("build partial plan", t)
     t = time.perf_counter(); states = partial.collect_device(0); tick("partial execute", t)
     t = time.perf_counter(); final = tpch.q1_final(MemoryExec(ctx, partial.schema(), [states]), scan.schema()); tick("build final plan", t)
@@ -18,3 +18,7 @@ for it in range(N + 3):
     t = time.perf_counter(); del scan, partial, states, final; tick("teardown", t)
 for k, v in T.items(): print(f"{k:24s} {v / N * 1e3:8.3f} ms")
 print("launches/step", ctx.kernel_launches() / (N + 3))
+
+del li
+import gc; gc.collect()
+ctx.close()

@@ -178,7 +178,7 @@ BatchPtr comm_all_to_all(Ctx* ctx, const Batch& b, const std::vector<int64_t>& c
   for (int d = 0; d < nr; ++d) send_off[d + 1] = send_off[d] + counts[d];
   std::vector<std::vector<int64_t>> chr_bounds(ncol);  // char offset at each slice boundary
   for (size_t c = 0; c < ncol; ++c) {
-    if (b.cols[c].dtype != B2_UTF8) continue;
+    if (b.cols[c].dtype != B2_UTF8 || !b.cols[c].data) continue;
     chr_bounds[c].assign(nr + 1, 0);
     std::vector<int32_t> tmp(nr + 1, 0);
     if (b.num_rows)
@@ -190,7 +190,8 @@ BatchPtr comm_all_to_all(Ctx* ctx, const Batch& b, const std::vector<int64_t>& c
   for (int d = 0; d < nr; ++d) {
     mine[(size_t)d * (1 + ncol)] = counts[d];
     for (size_t c = 0; c < ncol; ++c)
-      if (b.cols[c].dtype == B2_UTF8) mine[(size_t)d * (1 + ncol) + 1 + c] = chr_bounds[c][d + 1] - chr_bounds[c][d];
+      if (b.cols[c].dtype == B2_UTF8 && b.cols[c].data)
+        mine[(size_t)d * (1 + ncol) + 1 + c] = chr_bounds[c][d + 1] - chr_bounds[c][d];
   }
   std::vector<int64_t> all = allgather_counts(ctx, mine);
   // what rank s sends to me
@@ -220,6 +221,10 @@ BatchPtr comm_all_to_all(Ctx* ctx, const Batch& b, const std::vector<int64_t>& c
     Column o;
     o.dtype = col.dtype;
     o.length = total;
+    if (!col.data) {  // elided by column pruning: nothing to move
+      out->cols.push_back(std::move(o));
+      continue;
+    }
     if (col.dtype == B2_UTF8) {
       auto lens = dev_alloc(ctx, (size_t)(b.num_rows + 1) * 4);
       if (b.num_rows) {

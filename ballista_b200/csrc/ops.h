@@ -60,8 +60,10 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
 // repartition.cu: rows -> destination partition by hash of packed key; returns the stable permutation
 // (destination-major) and fills counts[n_out]
 // `key32` (optional): the single Int32 / Date32 key column, hashed as its packed form without materialising keys
+// `pred` / `mask` (optional, n_out <= 32 only): a fused FilterExec; rejected rows appear in no destination
 BufPtr hash_partition_indices(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
-                              std::vector<int64_t>* counts);
+                              std::vector<int64_t>* counts, const RowPred* pred = nullptr,
+                              const uint8_t* mask = nullptr);
 
 // two-phase form used by the shuffle: phase 1 = destination bytes + per-tile histogram + scan (no host sync)
 struct SplitState {
@@ -69,7 +71,8 @@ struct SplitState {
   int64_t n = 0, n_tiles = 0;
   int n_out = 0;
 };
-SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out);
+SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
+                            const RowPred* pred = nullptr, const uint8_t* mask = nullptr);
 void hash_split_starts_device(Ctx* ctx, const SplitState& st, int64_t* out_dev);  // n_out + 1 slice starts
 void hash_split_counts(Ctx* ctx, const SplitState& st, std::vector<int64_t>* counts);
 BufPtr hash_split_perm(Ctx* ctx, const SplitState& st);
@@ -112,6 +115,9 @@ struct Op {
   // read (empty = all).  Operators that assemble their output by gathers (HashJoinExec) leave the others
   // elided (Column::data == nullptr); the schema is unchanged.  Default: children produce everything.
   virtual void require(const std::vector<char>& need) { (void)need; }
+  // true when output partition r exists only on rank r (the plan sits above an exchange): consumers then
+  // execute their own rank's partition instead of iterating over all of them
+  virtual bool per_rank_partitions() const { return !children.empty() && children[0]->per_rank_partitions(); }
   int n_partitions() const {
     int s, n;
     partitioning(&s, &n);

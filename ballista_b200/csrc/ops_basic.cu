@@ -200,6 +200,7 @@ bool op_is_coalesce(Op* op) { return dynamic_cast<CoalesceExec*>(op) != nullptr;
 // ------------------------------------------------------------------------------------------------------
 struct MergeExec : Op {
   const char* name() const override { return "MergeExec"; }
+  bool per_rank_partitions() const override { return false; }
   Schema schema() const override { return children[0]->schema(); }
   void partitioning(int* scheme, int* n) const override {
     *scheme = B2_PART_UNKNOWN;
@@ -208,9 +209,14 @@ struct MergeExec : Op {
   struct S : Stream {
     MergeExec* op;
     int part = 0, nparts = 0;
+    bool own_only = false;
     StreamPtr cur;
     BatchPtr next() override {
       while (part < nparts) {
+        if (own_only && part != op->ctx->rank) {  // above an exchange: the other partitions live on other ranks
+          part++;
+          continue;
+        }
         if (!cur) cur = op->children[0]->execute(part);
         BatchPtr b = cur->next();
         if (b) return b;
@@ -225,6 +231,7 @@ struct MergeExec : Op {
     auto s = std::make_unique<S>();
     s->op = this;
     s->nparts = children[0]->n_partitions();
+    s->own_only = children[0]->per_rank_partitions();
     last_path = "passthrough";
     return s;
   }

@@ -12,6 +12,7 @@ namespace b2 {
 // ------------------------------------------------------------------------------------------------------
 bool op_is_filter(Op* op, ExprPtr* pred);
 bool op_is_coalesce(Op* op);
+bool op_is_exchange(Op* op);  // RepartitionExec whose output partitions live one per rank (communicator attached)
 
 // FilterExec (optionally under CoalesceBatchesExec) directly below a join side: returns the filter's input
 // and its predicate, so the join evaluates the mask itself and never compacts the side
@@ -42,6 +43,7 @@ struct HashJoinExec : Op {
   const char* name() const override { return "HashJoinExec"; }
   Schema schema() const override { return out; }
   void partitioning(int* scheme, int* n) const override { children[1]->partitioning(scheme, n); }
+  bool per_rank_partitions() const override { return children[1]->per_rank_partitions(); }
 
   bool fuse() const { return k32 && !getenv("B2_DISABLE_FUSION"); }
   bool needed(size_t out_col) const { return need.empty() || (out_col < need.size() && need[out_col]); }
@@ -68,14 +70,19 @@ struct HashJoinExec : Op {
     if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 join key value is longer than the packed-key budget");
     return keys;
   }
-  void build() {
+  void build(int partition) {
     if (table) return;
     Op* l = children[0].get();
     ExprPtr pred;
     if (fuse()) l = peel_filter(l, &pred);
     std::vector<BatchPtr> all;
     int np = l->n_partitions();
-    for (int p = 0; p < np; ++p) {  // MergeExec(left): all partitions
+    // Partitioned join: when the build side arrives through an exchange (a hash repartition whose output partition
+    // r lives on rank r), only this rank's partition is built - the probe side was shuffled on the same key.
+    // Otherwise collect-left, as the reference: MergeExec(left) over all partitions.
+    bool partitioned = l->per_rank_partitions();
+    for (int p = 0; p < np; ++p) {
+      if (partitioned && p != partition) continue;
       StreamPtr s = l->execute(p);
       while (BatchPtr b = s->next())
         if (b->num_rows) all.push_back(b);
@@ -141,7 +148,7 @@ struct HashJoinExec : Op {
     }
   };
   StreamPtr execute(int partition) override {
-    build();
+    build(partition);
     auto s = std::make_unique<S>();
     s->op = this;
     Op* r = children[1].get();
@@ -200,6 +207,7 @@ struct RepartitionExec : Op {
   KeyLayout layout;
   bool computed = false;
   std::vector<std::vector<BatchPtr>> outputs;  // per output partition
+  std::vector<char> need;                      // output columns a parent will read (empty = all)
 
   const char* name() const override { return "RepartitionExec"; }
   Schema schema() const override { return children[0]->schema(); }
@@ -208,55 +216,83 @@ struct RepartitionExec : Op {
     *n = n_out;
   }
   bool exchange_mode() const { return scheme == B2_PART_HASH && ctx->comm && n_out == ctx->nranks; }
+  bool per_rank_partitions() const override { return exchange_mode(); }
+  // a FilterExec below a hash repartition rides in the split kernels (rows it rejects get no destination)
+  bool fuse() const { return scheme == B2_PART_HASH && n_out <= 32 && !getenv("B2_DISABLE_FUSION"); }
 
-  // hash-split one batch: destination-major permuted batch + per-destination counts
-  BatchPtr split(const Batch& b, std::vector<int64_t>* counts) {
-    BufPtr perm = split_perm(b, counts);
-    return take_batch(ctx, b, perm->as<uint32_t>(), b.num_rows);
+  void require(const std::vector<char>& n) override {
+    need = n;
+    if (n.empty()) return children[0]->require(n);
+    std::vector<char> c = n;
+    c.resize(schema().fields.size(), 0);
+    for (auto& k : keys) expr_columns(k, c);
+    children[0]->require(c);
   }
-  // phase 1 of the split (destinations + histogram + scan, no host sync); false = keys need the packed path check
-  bool split_begin(const Batch& b, SplitState* st) {
+  // columns nobody reads downstream are not moved: they stay elided in the output
+  BatchPtr prune(const BatchPtr& b) const {
+    if (need.empty()) return b;
+    auto o = std::make_shared<Batch>(*b);
+    for (size_t c = 0; c < o->cols.size(); ++c)
+      if (!(c < need.size() && need[c])) {
+        Column e;
+        e.dtype = o->cols[c].dtype;
+        e.length = o->cols[c].length;
+        o->cols[c] = e;
+      }
+    return o;
+  }
+
+  // phase 1 of the hash split of `b` under the optional fused predicate (destinations + histogram + scan)
+  SplitState split_begin(const Batch& b, const ExprPtr& pred) {
     std::vector<Column> kc;
     for (auto& k : keys) kc.push_back(eval_expr(ctx, k, b));
+    Column mask;
+    RowPred rp;
+    if (pred && b.num_rows && !compile_row_pred(pred, b, &rp)) mask = eval_expr(ctx, pred, b);
+    const uint8_t* m = mask.data ? mask.values<uint8_t>() : nullptr;
     if (kc.size() == 1 && (kc[0].dtype == B2_INT32 || kc[0].dtype == B2_DATE32)) {
-      *st = hash_split_begin(ctx, nullptr, kc[0].values<int32_t>(), b.num_rows, n_out);
-      return true;
+      // one Int32 key: hashed straight from the column (same value as its packed form), nothing materialised
+      return hash_split_begin(ctx, nullptr, kc[0].values<int32_t>(), b.num_rows, n_out, &rp, m);
     }
     BufPtr stt = dev_alloc_zero(ctx, 16);
     BufPtr pk = pack_keys(ctx, layout, kc, b.num_rows, stt->as<int>());
-    *st = hash_split_begin(ctx, pk->as<Key128>(), nullptr, b.num_rows, n_out);
+    SplitState st = hash_split_begin(ctx, pk->as<Key128>(), nullptr, b.num_rows, n_out, &rp, m);
     int host = 0;
     B2_READBACK(ctx, &host, stt->ptr, 4);
     if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 partitioning key value is longer than the packed-key budget");
-    return true;
+    return st;
   }
-  // stable destination-major permutation of the rows of `b` + rows per destination
-  BufPtr split_perm(const Batch& b, std::vector<int64_t>* counts) {
+  // stable destination-major permutation of the surviving rows of `b` + rows per destination
+  BufPtr split_perm(const Batch& b, const ExprPtr& pred, std::vector<int64_t>* counts) {
+    if (n_out <= 32) {
+      SplitState st = split_begin(b, pred);
+      BufPtr perm = hash_split_perm(ctx, st);
+      hash_split_counts(ctx, st, counts);
+      return perm;
+    }
     std::vector<Column> kc;
     for (auto& k : keys) kc.push_back(eval_expr(ctx, k, b));
-    BufPtr perm;
-    if (kc.size() == 1 && (kc[0].dtype == B2_INT32 || kc[0].dtype == B2_DATE32) && n_out <= 32) {
-      // one Int32 key: hashed straight from the column (same value as its packed form), nothing materialised
-      perm = hash_partition_indices(ctx, nullptr, kc[0].values<int32_t>(), b.num_rows, n_out, counts);
-    } else {
-      BufPtr st = dev_alloc_zero(ctx, 16);
-      BufPtr pk = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>());
-      perm = hash_partition_indices(ctx, pk->as<Key128>(), nullptr, b.num_rows, n_out, counts);
-      int host = 0;
-      B2_READBACK(ctx, &host, st->ptr, 4);
-      if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 partitioning key value is longer than the packed-key budget");
-    }
+    BufPtr st = dev_alloc_zero(ctx, 16);
+    BufPtr pk = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>());
+    BufPtr perm = hash_partition_indices(ctx, pk->as<Key128>(), nullptr, b.num_rows, n_out, counts);
+    int host = 0;
+    B2_READBACK(ctx, &host, st->ptr, 4);
+    if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 partitioning key value is longer than the packed-key budget");
     return perm;
   }
   void compute() {
     if (computed) return;
     outputs.assign(n_out, {});
     Op* in = children[0].get();
+    ExprPtr pred;
+    if (fuse()) in = peel_filter(in, &pred);
     int np = in->n_partitions();
+    const bool own_only = in->per_rank_partitions();  // input sits above another exchange: only partition `rank` is here
     if (exchange_mode()) {
       // one collective per execution: all local input is concatenated, split, and exchanged once
       std::vector<BatchPtr> all;
       for (int p = 0; p < np; ++p) {
+        if (own_only && p != ctx->rank) continue;
         StreamPtr s = in->execute(p);
         while (BatchPtr b = s->next())
           if (b->num_rows) all.push_back(b);
@@ -267,22 +303,27 @@ struct RepartitionExec : Op {
       } else {
         local = concat_batches(ctx, schema(), all);
       }
+      BatchPtr moved = prune(local);  // predicate / key columns are still read from `local`
       BatchPtr got;
-      SplitState st;
-      bool two_phase = n_out <= 32 && split_begin(*local, &st);
-      if (two_phase) got = comm_shuffle_p2p(ctx, *local, st);
-      if (got) {
-        last_path = "nvlink-peer-pull";
+      if (n_out <= 32) {
+        SplitState st = split_begin(*local, pred);
+        got = comm_shuffle_p2p(ctx, *moved, st);
+        if (got) {
+          last_path = pred ? "nvlink-peer-pull+fused-filter" : "nvlink-peer-pull";
+        } else {
+          std::vector<int64_t> counts;
+          BufPtr perm = hash_split_perm(ctx, st);
+          hash_split_counts(ctx, st, &counts);
+          int64_t m = 0;
+          for (int64_t c : counts) m += c;
+          BatchPtr permuted = take_batch(ctx, *moved, perm->as<uint32_t>(), m);
+          got = comm_all_to_all(ctx, *permuted, counts);
+          last_path = "nccl-all-to-all";
+        }
       } else {
         std::vector<int64_t> counts;
-        BufPtr perm;
-        if (two_phase) {
-          perm = hash_split_perm(ctx, st);
-          hash_split_counts(ctx, st, &counts);
-        } else {
-          perm = split_perm(*local, &counts);
-        }
-        BatchPtr permuted = take_batch(ctx, *local, perm->as<uint32_t>(), local->num_rows);
+        BufPtr perm = split_perm(*local, pred, &counts);
+        BatchPtr permuted = take_batch(ctx, *moved, perm->as<uint32_t>(), local->num_rows);
         got = comm_all_to_all(ctx, *permuted, counts);
         last_path = "nccl-all-to-all";
       }
@@ -290,6 +331,7 @@ struct RepartitionExec : Op {
     } else {
       int64_t k = 0;
       for (int p = 0; p < np; ++p) {
+        if (own_only && p != ctx->rank) continue;
         StreamPtr s = in->execute(p);
         while (BatchPtr b = s->next()) {
           if (scheme == B2_PART_ROUND_ROBIN) {
@@ -298,7 +340,10 @@ struct RepartitionExec : Op {
           }
           if (!b->num_rows) continue;
           std::vector<int64_t> counts;
-          BatchPtr permuted = split(*b, &counts);
+          BufPtr perm = split_perm(*b, pred, &counts);
+          int64_t m = 0;
+          for (int64_t c : counts) m += c;
+          BatchPtr permuted = take_batch(ctx, *prune(b), perm->as<uint32_t>(), m);
           int64_t off = 0;
           for (int d = 0; d < n_out; ++d) {
             if (counts[d]) outputs[d].push_back(slice_batch(ctx, *permuted, off, off + counts[d]));
@@ -306,7 +351,7 @@ struct RepartitionExec : Op {
           }
         }
       }
-      last_path = "local";
+      last_path = pred ? "local+fused-filter" : "local";
     }
     computed = true;
   }
@@ -348,6 +393,11 @@ OpPtr make_repartition(Ctx* ctx, OpPtr input, int scheme, std::vector<ExprPtr> k
   }
   op->keys = std::move(keys);
   return op;
+}
+
+bool op_is_exchange(Op* op) {
+  auto* r = dynamic_cast<RepartitionExec*>(op);
+  return r && r->exchange_mode();
 }
 
 void repartition_reset(Op* op) {

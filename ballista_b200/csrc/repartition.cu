@@ -6,6 +6,7 @@
 #include <cstring>
 
 #include "ops.h"
+#include "rowpred.cuh"
 #include "scan.cuh"
 
 namespace b2 {
@@ -31,6 +32,7 @@ struct PermOut {
 // every load is coalesced); the stable order inside a tile is (j, warp, lane).
 constexpr int RP_THREADS = 256, RP_ITEMS = 8, RP_TILE = RP_THREADS * RP_ITEMS, RP_MAX_OUT = 32;
 constexpr int RP_WARPS = RP_THREADS / 32;
+constexpr uint8_t RP_DROPPED = 255;  // destination byte of a row the fused filter rejected
 
 struct KeySrc {  // packed 16-byte keys, or a single Int32 / Date32 key column hashed as its packed form
   const Key128* k128;
@@ -43,8 +45,8 @@ struct KeySrc {  // packed 16-byte keys, or a single Int32 / Date32 key column h
 // pass 1: destination byte per row + per-tile histogram, stored destination-major (hist[d * n_tiles + tile]) so
 // that ONE exclusive scan of the whole array yields every (destination, tile) output offset
 __global__ void __launch_bounds__(RP_THREADS)
-    rp_hist_kernel(KeySrc keys, int64_t n, int n_out, uint8_t* __restrict__ dest, int64_t* __restrict__ hist,
-                   int64_t n_tiles) {
+    rp_hist_kernel(KeySrc keys, RowPred pred, const uint8_t* __restrict__ mask, int64_t n, int n_out,
+                   uint8_t* __restrict__ dest, int64_t* __restrict__ hist, int64_t n_tiles) {
   __shared__ int h[RP_MAX_OUT];
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     if (threadIdx.x < RP_MAX_OUT) h[threadIdx.x] = 0;
@@ -52,8 +54,10 @@ __global__ void __launch_bounds__(RP_THREADS)
 #pragma unroll
     for (int j = 0; j < RP_ITEMS; ++j) {
       int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
-      int d = r < n ? (int)(keys.hash(r) % (u64)n_out) : -1;
-      if (d >= 0) dest[r] = (uint8_t)d;
+      // rows rejected by the fused FilterExec (byte mask and / or inline predicate) get no destination
+      bool live = r < n && (!mask || mask[r]) && row_pred(pred, r);
+      int d = live ? (int)(keys.hash(r) % (u64)n_out) : -1;
+      if (r < n) dest[r] = live ? (uint8_t)d : RP_DROPPED;
       unsigned peers = __match_any_sync(0xffffffffu, d);
       if (d >= 0 && (peers & ((1u << (threadIdx.x & 31)) - 1)) == 0) atomicAdd(&h[d], __popc(peers));
     }
@@ -77,6 +81,7 @@ __global__ void __launch_bounds__(RP_THREADS)
     for (int j = 0; j < RP_ITEMS; ++j) {
       int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
       d[j] = r < n ? (int)dest[r] : -1;
+      if (d[j] == RP_DROPPED) d[j] = -1;
       unsigned peers = __match_any_sync(0xffffffffu, d[j]);
       rank[j] = __popc(peers & ((1u << lane) - 1));
       if (d[j] >= 0 && rank[j] == 0) cnt[j][warp][d[j]] = __popc(peers);
@@ -140,6 +145,7 @@ __global__ void __launch_bounds__(RP_THREADS)
     for (int j = 0; j < RP_ITEMS; ++j) {
       int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
       d[j] = r < n ? (int)dest[r] : -1;
+      if (d[j] == RP_DROPPED) d[j] = -1;
       unsigned peers = __match_any_sync(0xffffffffu, d[j]);
       rank[j] = __popc(peers & ((1u << lane) - 1));
       if (d[j] >= 0 && rank[j] == 0) cnt[j][warp][d[j]] = __popc(peers);
@@ -196,7 +202,8 @@ __global__ void __launch_bounds__(RP_THREADS)
 }
 
 // ---- host side: phase 1 (destinations, histogram, scan: no host sync), then counts / permutation / column move ----
-SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out) {
+SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
+                            const RowPred* pred, const uint8_t* mask) {
   if (n_out < 1 || n_out > RP_MAX_OUT) fail(B2_ERR_INVALID_ARG, "hash_split_begin supports 1..32 output partitions");
   if (n >= (1ll << 32) - 1) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
   SplitState st;
@@ -207,8 +214,8 @@ SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, 
   st.hist = dev_alloc_zero(ctx, (size_t)(st.n_tiles * n_out + 2) * 8);
   if (n == 0) return st;
   int grid = grid_for(ctx, 8, n, RP_TILE);
-  rp_hist_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(KeySrc{keys, key32}, n, n_out, st.dest->as<uint8_t>(),
-                                                       st.hist->as<int64_t>(), st.n_tiles);
+  rp_hist_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(KeySrc{keys, key32}, pred ? *pred : RowPred(), mask, n, n_out,
+                                                       st.dest->as<uint8_t>(), st.hist->as<int64_t>(), st.n_tiles);
   B2_LAUNCHED(ctx);
   scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(st.hist->as<int64_t>(), st.n_tiles * n_out);
   B2_LAUNCHED(ctx);
@@ -218,8 +225,7 @@ SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, 
 __global__ void rp_starts_kernel(const int64_t* __restrict__ off, int64_t n_tiles, int n_out, int64_t n,
                                  int64_t* __restrict__ out) {
   int d = threadIdx.x;
-  if (d < n_out) out[d] = n ? off[(int64_t)d * n_tiles] : 0;
-  if (d == n_out) out[d] = n;
+  if (d <= n_out) out[d] = n ? off[(int64_t)d * n_tiles] : 0;  // off[n_out * n_tiles] = rows that passed the filter
 }
 void hash_split_starts_device(Ctx* ctx, const SplitState& st, int64_t* out_dev) {
   rp_starts_kernel<<<1, 64, 0, ctx->stream>>>(st.hist->as<int64_t>(), st.n_tiles, st.n_out, st.n, out_dev);
@@ -261,16 +267,16 @@ void hash_split_move(Ctx* ctx, const SplitState& st, int n_cols, const void* con
 }
 
 BufPtr hash_partition_indices(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
-                              std::vector<int64_t>* counts) {
+                              std::vector<int64_t>* counts, const RowPred* pred, const uint8_t* mask) {
   if (n_out < 1 || n_out > 255) fail(B2_ERR_INVALID_ARG, "hash repartition supports 1..255 output partitions");
   if (n >= (1ll << 32) - 1) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
   counts->assign(n_out, 0);
   if (n == 0) return dev_alloc(ctx, 4);
   if (n_out > RP_MAX_OUT) {
-    if (!keys) fail(B2_ERR_EXECUTION, "internal: packed keys required beyond 32 output partitions");
+    if (!keys || pred || mask) fail(B2_ERR_EXECUTION, "internal: packed keys / no fused filter beyond 32 output partitions");
     return partition_indices_scan_per_destination(ctx, keys, n, n_out, counts);
   }
-  SplitState st = hash_split_begin(ctx, keys, key32, n, n_out);
+  SplitState st = hash_split_begin(ctx, keys, key32, n, n_out, pred, mask);
   BufPtr perm = hash_split_perm(ctx, st);
   hash_split_counts(ctx, st, counts);
   return perm;
@@ -291,6 +297,10 @@ BatchPtr slice_batch(Ctx* ctx, const Batch& b, int64_t begin, int64_t end) {
     Column o;
     o.dtype = c.dtype;
     o.length = m;
+    if (!c.data) {  // elided by column pruning
+      out->cols.push_back(std::move(o));
+      continue;
+    }
     if (c.dtype == B2_UTF8) {
       int32_t ends[2] = {0, 0};
       if (c.length) {

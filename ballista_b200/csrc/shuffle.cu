@@ -226,10 +226,8 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
   // Utf8 columns (rare on shuffled sides) go through the permutation + generic take; their per-destination
   // character counts join the metadata message
   bool has_utf8 = false;
-  for (size_t c = 0; c < ncol; ++c) {
-    if (!local.cols[c].data) fail(B2_ERR_EXECUTION, "internal: pruned column reached the shuffle");
-    has_utf8 = has_utf8 || local.cols[c].dtype == B2_UTF8;
-  }
+  for (size_t c = 0; c < ncol; ++c) has_utf8 = has_utf8 || (local.cols[c].data && local.cols[c].dtype == B2_UTF8);
+  auto elided = [&](size_t c) { return !local.cols[c].data; };  // pruned upstream: not moved, stays elided
   std::vector<Column> taken(ncol);
   std::vector<std::vector<int64_t>> chr_bounds(ncol);
   std::vector<int64_t> my_chars(ncol, 0), my_send_off(nr + 1, 0);
@@ -239,8 +237,8 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
     for (int d = 0; d < nr; ++d) my_send_off[d + 1] = my_send_off[d] + counts[d];
     BufPtr perm = hash_split_perm(ctx, st);
     for (size_t c = 0; c < ncol; ++c) {
-      if (local.cols[c].dtype != B2_UTF8) continue;
-      taken[c] = take_column(ctx, local.cols[c], perm->as<uint32_t>(), n);
+      if (local.cols[c].dtype != B2_UTF8 || elided(c)) continue;
+      taken[c] = take_column(ctx, local.cols[c], perm->as<uint32_t>(), my_send_off[nr]);
       my_chars[c] = taken[c].chars_len;
       chr_bounds[c].assign(nr + 1, 0);
       if (n) {
@@ -277,6 +275,8 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
   std::vector<ArenaMsg> msgs(nr);
   for (int r = 0; r < nr; ++r) memcpy(&msgs[r], all.data() + (size_t)r * L, sizeof(ArenaMsg));
   if (!arena_map_peers(ctx, msgs, retired)) return nullptr;
+  // my staged rows = the rows that passed the fused filter: the layout every peer derives for me
+  arena_layout(local.schema, all[(size_t)me * L + AW + nr], my_chars, nr, &my_regions);
   auto cnt = [&](int s, int d) { return all[(size_t)s * L + AW + d + 1] - all[(size_t)s * L + AW + d]; };
   auto chars = [&](int s, int d, size_t c) { return all[(size_t)s * L + AW + nr + 1 + (size_t)d * ncol + c]; };
   // R[d][s]: row offset, inside destination d's output, of the rows coming from source s (CR: characters)
@@ -285,7 +285,7 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
   for (int d = 0; d < nr; ++d)
     for (int s = 0; s < nr; ++s) R[d][s + 1] = R[d][s] + cnt(s, d);
   for (size_t c = 0; c < ncol; ++c) {
-    if (local.cols[c].dtype != B2_UTF8) continue;
+    if (local.cols[c].dtype != B2_UTF8 || elided(c)) continue;
     CR[c].assign(nr, std::vector<int64_t>(nr + 1, 0));
     for (int d = 0; d < nr; ++d)
       for (int s = 0; s < nr; ++s) CR[c][d][s + 1] = CR[c][d][s] + chars(s, d, c);
@@ -314,6 +314,7 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
     for (size_t c = 0; c < ncol; ++c) {
       const Column& col = local.cols[c];
       std::vector<int64_t> base;
+      if (elided(c)) continue;
       if (col.dtype == B2_UTF8) {
         if (!n) continue;
         bases_of(me, c, false, &base);
@@ -366,6 +367,10 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
     Column o;
     o.dtype = local.cols[c].dtype;
     o.length = total;
+    if (elided(c)) {
+      out->cols.push_back(std::move(o));
+      continue;
+    }
     if (o.dtype == B2_UTF8) {
       if (CR[c][me][nr] >= (1ll << 31)) fail(B2_ERR_EXECUTION, "Utf8 column beyond 2 GiB after the shuffle");
       o.chars_len = CR[c][me][nr];
@@ -392,6 +397,7 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
     for (size_t c = 0; c < ncol; ++c) {
       int dt = local.cols[c].dtype;
       std::vector<int64_t> base;
+      if (elided(c)) continue;
       bases_of(s, c, false, &base);
       if (dt == B2_UTF8) {
         segs.push_back(PullSeg{base_ptr + reg[c].val_off + base[me], lens_bufs[c]->as<char>() + R[me][s] * 4,
@@ -421,7 +427,7 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
   }
   pt.mark("shuffle 5: pull over NVLink");
   for (size_t c = 0; c < ncol; ++c)
-    if (local.cols[c].dtype == B2_UTF8 && total)
+    if (local.cols[c].dtype == B2_UTF8 && total && !elided(c))
       device_scan(ctx, I32In{lens_bufs[c]->as<int32_t>()}, total, LensToOff{out->cols[c].data->as<int32_t>(), total},
                   (int64_t*)nullptr);
   return out;

@@ -99,6 +99,26 @@ def q3_join_tree(customer, orders, lineitem, segment="BUILDING", cutoff="1995-03
     return j2
 
 
+def q3_distributed_join_tree(customer, orders, lineitem, nranks, segment="BUILDING", cutoff="1995-03-15"):
+    """Q3 over row-range partitions (one per GPU): both inputs of each join are hash-repartitioned on the join key
+    into one partition per rank (the ShuffleWriter -> ShuffleReaderExec hop, here an exchange over NVLink), so each
+    rank joins only its own key range.  Filters sit directly below the repartitions and ride in the split kernels."""
+    pc, po, pl = _q3_predicates(segment, cutoff)
+    c = RepartitionExec(CoalesceBatchesExec(FilterExec(pc, customer)), "Hash", nranks, [col("c_custkey")])
+    o = RepartitionExec(CoalesceBatchesExec(FilterExec(po, orders)), "Hash", nranks, [col("o_custkey")])
+    j1 = CoalesceBatchesExec(HashJoinExec(c, o, [("c_custkey", "o_custkey")]))
+    j1s = RepartitionExec(j1, "Hash", nranks, [col("o_orderkey")])
+    l = RepartitionExec(CoalesceBatchesExec(FilterExec(pl, lineitem)), "Hash", nranks, [col("l_orderkey")])
+    return CoalesceBatchesExec(HashJoinExec(j1s, l, [("o_orderkey", "l_orderkey")]))
+
+
+def q3_distributed_partial(customer, orders, lineitem, nranks, **kw):
+    """Partial aggregate over the partitioned join.  Groups are keyed by l_orderkey, the last shuffle key, so the
+    states of different ranks hold disjoint groups and each rank finalises its own (no further exchange)."""
+    return HashAggregateExec("Partial", q3_groups(), q3_aggregates(),
+                             q3_distributed_join_tree(customer, orders, lineitem, nranks, **kw))
+
+
 @functools.lru_cache(maxsize=None)
 def q3_aggregates():
     return [sum_(col("l_extendedprice") * (lit(1) - col("l_discount"))).alias("revenue")]

@@ -68,12 +68,183 @@ std::vector<int64_t> allgather_counts(Ctx* ctx, const std::vector<int64_t>& mine
   return all;
 }
 
+
 static size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
-// All-gather of a small batch (the Partial -> Final merge hop).  One NCCL all-gather of a packed staging
-// buffer: per column a region of max_rows values (Utf8: lengths + a chars region of max_chars bytes).
+// ---- small-batch all-gather: the Partial -> Final hop of an aggregate (a handful of group rows per rank) ----
+// Every rank packs header + columns into a slot whose size depends only on the schema, so ONE ncclAllGather moves
+// everything and ONE readback (the headers) sizes the output; one kernel packs, one unpacks.  A rank whose batch
+// does not fit its slot says so in the header and everybody falls back to the general, two-round protocol below.
+constexpr int SMALL_ROWS = 256, SMALL_CHARS = 4096, SMALL_MAX_COLS = 24, SMALL_MAX_RANKS = 64, SMALL_MAX_STR = 4;
+struct SmallCol {
+  const void* src;       // pack: values (Utf8: int32 offsets); unpack: unused
+  const uint8_t* chars;  // pack: Utf8 characters
+  void* dst;             // unpack: values (Utf8: int32 offsets)
+  uint8_t* dst_chars;    // unpack: Utf8 characters
+  int width;             // bytes per value (Utf8: 4, the staged lengths)
+  int utf8;              // index into the char-prefix table, -1 for fixed width
+  int64_t val_off, chr_off;  // offsets inside a slot
+};
+struct SmallArgs {
+  int ncol, nr;
+  int64_t stride, rows, header_bytes;
+  SmallCol c[SMALL_MAX_COLS];
+  int64_t chars[SMALL_MAX_COLS];                         // pack: my character counts
+  int64_t row_prefix[SMALL_MAX_RANKS + 1];               // unpack
+  int64_t chr_prefix[SMALL_MAX_STR][SMALL_MAX_RANKS + 1];
+};
+__global__ void pack_small_kernel(SmallArgs a, char* slot, int fits) {
+  const SmallCol& c = a.c[blockIdx.y];
+  if (blockIdx.y == 0 && threadIdx.x == 0) {
+    int64_t* h = reinterpret_cast<int64_t*>(slot);
+    h[0] = fits ? a.rows : -1;
+    for (int k = 0; k < a.ncol; ++k) h[1 + k] = a.chars[k];
+  }
+  if (!fits) return;
+  char* base = slot + c.val_off;
+  for (int64_t i = threadIdx.x; i < a.rows; i += blockDim.x) {
+    if (c.utf8 >= 0) {
+      const int32_t* off = static_cast<const int32_t*>(c.src);
+      reinterpret_cast<int32_t*>(base)[i] = off[i + 1] - off[i];
+    } else if (c.width == 8) {
+      reinterpret_cast<int64_t*>(base)[i] = static_cast<const int64_t*>(c.src)[i];
+    } else if (c.width == 4) {
+      reinterpret_cast<int32_t*>(base)[i] = static_cast<const int32_t*>(c.src)[i];
+    } else {
+      base[i] = static_cast<const char*>(c.src)[i];
+    }
+  }
+  if (c.utf8 >= 0)
+    for (int64_t k = threadIdx.x; k < a.chars[blockIdx.y]; k += blockDim.x) slot[c.chr_off + k] = (char)c.chars[k];
+}
+__global__ void unpack_small_kernel(SmallArgs a, const char* recv) {
+  const SmallCol& c = a.c[blockIdx.y];
+  const int64_t total = a.row_prefix[a.nr];
+  for (int64_t i = threadIdx.x; i < total; i += blockDim.x) {
+    int r = 0;
+    while (a.row_prefix[r + 1] <= i) ++r;
+    int64_t j = i - a.row_prefix[r];
+    const char* base = recv + (int64_t)r * a.stride + c.val_off;
+    if (c.utf8 >= 0) {
+      const int32_t* lens = reinterpret_cast<const int32_t*>(base);
+      int64_t o = a.chr_prefix[c.utf8][r];
+      for (int64_t t = 0; t < j; ++t) o += lens[t];
+      static_cast<int32_t*>(c.dst)[i] = (int32_t)o;
+      if (i == total - 1) static_cast<int32_t*>(c.dst)[total] = (int32_t)a.chr_prefix[c.utf8][a.nr];
+    } else if (c.width == 8) {
+      static_cast<int64_t*>(c.dst)[i] = reinterpret_cast<const int64_t*>(base)[j];
+    } else if (c.width == 4) {
+      static_cast<int32_t*>(c.dst)[i] = reinterpret_cast<const int32_t*>(base)[j];
+    } else {
+      static_cast<char*>(c.dst)[i] = base[j];
+    }
+  }
+  if (c.utf8 >= 0) {
+    const int64_t tc = a.chr_prefix[c.utf8][a.nr];
+    for (int64_t k = threadIdx.x; k < tc; k += blockDim.x) {
+      int r = 0;
+      while (a.chr_prefix[c.utf8][r + 1] <= k) ++r;
+      c.dst_chars[k] = (uint8_t)recv[(int64_t)r * a.stride + c.chr_off + (k - a.chr_prefix[c.utf8][r])];
+    }
+  }
+}
+
+static BatchPtr allgather_general(Ctx* ctx, const Batch& local);
+
+// Returns nullptr when the schema is outside the small protocol or some rank's batch did not fit its slot.
+static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
+  const int nr = ctx->nranks;
+  const size_t ncol = local.cols.size();
+  if (ncol > SMALL_MAX_COLS || nr > SMALL_MAX_RANKS || ncol == 0) return nullptr;
+  SmallArgs a;
+  memset(&a, 0, sizeof a);
+  a.ncol = (int)ncol;
+  a.nr = nr;
+  a.rows = local.num_rows;
+  a.header_bytes = (int64_t)align16((1 + ncol) * 8);
+  int64_t off = a.header_bytes;
+  int n_str = 0;
+  bool fits = local.num_rows <= SMALL_ROWS;
+  for (size_t c = 0; c < ncol; ++c) {
+    const Column& col = local.cols[c];
+    if (!col.data) return nullptr;
+    SmallCol& sc = a.c[c];
+    sc.src = col.data->ptr;
+    sc.utf8 = -1;
+    sc.width = col.dtype == B2_UTF8 ? 4 : (int)dtype_width(col.dtype);
+    sc.val_off = off;
+    off += (int64_t)align16((size_t)SMALL_ROWS * sc.width);
+    if (col.dtype == B2_UTF8) {
+      if (n_str == SMALL_MAX_STR) return nullptr;
+      sc.utf8 = n_str++;
+      sc.chars = col.chars ? col.chars->as<uint8_t>() : nullptr;
+      sc.chr_off = off;
+      off += SMALL_CHARS;
+      a.chars[c] = col.chars_len;
+      fits = fits && col.chars_len <= SMALL_CHARS;
+    }
+  }
+  a.stride = off;
+  auto send = dev_alloc(ctx, (size_t)a.stride);
+  auto recv = dev_alloc(ctx, (size_t)a.stride * nr);
+  pack_small_kernel<<<dim3(1, (unsigned)ncol), 256, 0, ctx->stream>>>(a, send->as<char>(), fits ? 1 : 0);
+  B2_LAUNCHED(ctx);
+  B2_NCCL(ncclAllGather(send->ptr, recv->ptr, (size_t)a.stride, ncclChar, ctx->comm->nccl, ctx->stream));
+  ctx->bytes_sent += a.stride * (nr - 1);
+  // one strided readback: the header of every slot
+  std::vector<int64_t> heads((size_t)nr * (1 + ncol));
+  {
+    double t0 = ctx->trace ? wall_now() : 0;
+    B2_CUDA(cudaMemcpy2DAsync(heads.data(), (1 + ncol) * 8, recv->ptr, (size_t)a.stride, (1 + ncol) * 8, (size_t)nr,
+                              cudaMemcpyDeviceToHost, ctx->stream));
+    B2_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->trace) ctx->trace_add("comm.cu:allgather_small headers", wall_now() - t0);
+  }
+  for (int r = 0; r < nr; ++r)
+    if (heads[(size_t)r * (1 + ncol)] < 0) return nullptr;  // somebody did not fit: general protocol (all ranks agree)
+  for (int r = 0; r < nr; ++r) {
+    a.row_prefix[r + 1] = a.row_prefix[r] + heads[(size_t)r * (1 + ncol)];
+    for (size_t c = 0; c < ncol; ++c)
+      if (a.c[c].utf8 >= 0)
+        a.chr_prefix[a.c[c].utf8][r + 1] = a.chr_prefix[a.c[c].utf8][r] + heads[(size_t)r * (1 + ncol) + 1 + c];
+  }
+  int64_t total = a.row_prefix[nr];
+  auto out = std::make_shared<Batch>();
+  out->ctx = ctx;
+  out->schema = local.schema;
+  out->num_rows = total;
+  for (size_t c = 0; c < ncol; ++c) {
+    Column o;
+    o.dtype = local.cols[c].dtype;
+    o.length = total;
+    if (o.dtype == B2_UTF8) {
+      o.data = dev_alloc_zero(ctx, (size_t)(total + 1) * 4);
+      o.chars_len = a.chr_prefix[a.c[c].utf8][nr];
+      o.chars = dev_alloc(ctx, (size_t)o.chars_len + 16);
+      a.c[c].dst_chars = o.chars->as<uint8_t>();
+    } else {
+      o.data = dev_alloc(ctx, (size_t)total * dtype_width(o.dtype) + 16);
+    }
+    a.c[c].dst = o.data->ptr;
+    out->cols.push_back(std::move(o));
+  }
+  if (total) {
+    unpack_small_kernel<<<dim3(1, (unsigned)ncol), 256, 0, ctx->stream>>>(a, recv->as<char>());
+    B2_LAUNCHED(ctx);
+  }
+  return out;
+}
+
 BatchPtr comm_allgather_batch(Ctx* ctx, const Batch& local) {
   if (!ctx->comm) fail(B2_ERR_INVALID_ARG, "no communicator (call b2_comm_init)");
+  if (BatchPtr b = allgather_small(ctx, local)) return b;
+  return allgather_general(ctx, local);
+}
+
+// General all-gather of a batch: counts first, then one NCCL all-gather of a packed staging
+
+// buffer: per column a region of max_rows values (Utf8: lengths + a chars region of max_chars bytes).
+static BatchPtr allgather_general(Ctx* ctx, const Batch& local) {
   int nr = ctx->nranks;
   size_t ncol = local.cols.size();
   std::vector<int64_t> mine(1 + ncol, 0);

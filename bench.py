@@ -475,6 +475,31 @@ def run_other_configs(args, ctx, env):
                           "frac_of_nvlink_900GBps": sent / (ms / 1e3) / 1e9 / 900.0, "launches_per_step": launches,
                           "note": "whole operator (split + metadata + exchange); the pull step alone is in profiles/"}
         del part
+        # ---- Q3 with the shuffle: row-range partitions of an SF(10 x N) database, both join inputs exchanged ----
+        dsf = sf * world
+        def tpart(table, columns, align=1):
+            total = _capi.lib().b2_tpch_num_rows(table.encode(), float(dsf))
+            r0, r1 = cluster.partition_rows(total, world, rank, align=align)
+            return ctx.tpch(table, dsf, r0, r1, columns=columns)
+        dcu, dod = tpart("customer", tpch.Q3_CUSTOMER_COLUMNS), tpart("orders", tpch.Q3_ORDERS_COLUMNS)
+        dli = tpart("lineitem", tpch.Q3_LINEITEM_COLUMNS, align=32)
+        paths = [None]
+
+        def q3d():
+            scans = [tpch.scan(ctx, [[x]]) for x in (dcu, dod, dli)]
+            partial = tpch.q3_distributed_partial(*scans, world)
+            states = partial.collect_device(rank)
+            final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
+            return sum(b.num_rows for b in final.collect_device(0))
+        sent0 = ctx.comm_bytes_sent()
+        ms, launches, groups = timeit(q3d, steps=10, warmup=3)
+        sent = (ctx.comm_bytes_sent() - sent0) / 13.0
+        rows_all = sum(_capi.lib().b2_tpch_num_rows(t.encode(), float(dsf)) for t in ("customer", "orders", "lineitem"))
+        out["q3_distributed"] = {"workload": f"TPC-H Q3 over an SF{dsf:g} database in {world} row-range partitions, both join "
+                                             "inputs hash-repartitioned over NVLink (filters fused into the split)",
+                                 "ms_per_step": ms, "input_rows_per_s": rows_all / (ms / 1e3), "groups_rank0": groups,
+                                 "egress_bytes_per_gpu": sent, "launches_per_step": launches}
+        del dcu, dod, dli
     del li
     return out
 

@@ -61,10 +61,29 @@ def run(sf, rows_per_rank, mode):
     dist.barrier()
 
 
+def check_allgather(sf, n):
+    """b2_comm_allgather_batch: rank-ordered concatenation, small-slot protocol (n <= 256) and general protocol."""
+    import pyarrow as pa
+    part = ctx.tpch("lineitem", sf, rank * n, rank * n + n + rank, columns=cols)
+    mine = rows_of(pa.Table.from_batches([part.to_arrow()]))
+    got = rows_of(pa.Table.from_batches([ctx.allgather(part).to_arrow()]))
+    gathered = [None] * world
+    dist.all_gather_object(gathered, mine)
+    want = [r for p in gathered for r in p]
+    assert got == want, f"allgather({n}) differs on rank {rank}"
+    if rank == 0:
+        print(f"ok [allgather] rows/rank~{n} total={len(got)}", flush=True)
+    dist.barrier()
+
+
+sf0 = 0.01 * world  # 60 k lineitem rows per rank
 for mode in ("p2p", "nccl", "p2p"):
-    run(0.01, 20_000, mode)
-run(0.1, 150_000, "p2p")   # arena regrow
-run(0.01, 3_000, "p2p")     # smaller again: arena reused
+    run(sf0, 20_000, mode)
+run(0.1 * world, 150_000, "p2p")   # arena regrow
+run(sf0, 3_000, "p2p")             # smaller again: arena reused
+check_allgather(sf0, 4)
+check_allgather(sf0, 256 - world)
+check_allgather(sf0, 3000)
 ctx.synchronize()
 if rank == 0:
     print("shuffle_check: all ok")

@@ -9,10 +9,10 @@ from ._capi import BallistaError, NotImplementedOnGpu
 from .expr import Expr, AggExpr, col, lit, date, sum, avg, count  # noqa: A004
 from .plan import (Context, DeviceBatch, ExecutionPlan, RecordBatchStream, MemoryExec, FilterExec,
                    CoalesceBatchesExec, MergeExec, ProjectionExec, HashAggregateExec, HashJoinExec,
-                   RepartitionExec)
+                   RepartitionExec, SortExec, GlobalLimitExec, LocalLimitExec)
 from . import tpch
 
 __all__ = ["BallistaError", "NotImplementedOnGpu", "Expr", "AggExpr", "col", "lit", "date", "sum", "avg", "count",
            "Context", "DeviceBatch", "ExecutionPlan", "RecordBatchStream", "MemoryExec", "FilterExec",
            "CoalesceBatchesExec", "MergeExec", "ProjectionExec", "HashAggregateExec", "HashJoinExec",
-           "RepartitionExec", "tpch"]
+           "RepartitionExec", "SortExec", "GlobalLimitExec", "LocalLimitExec", "tpch"]

@@ -107,6 +107,8 @@ def lib():
         "b2_coalesce_batches_create": (i32, [vp, vp, i64, P(vp)]),
         "b2_merge_create": (i32, [vp, vp, P(vp)]),
         "b2_projection_create": (i32, [vp, vp, P(Expr), i32, P(vp)]),
+        "b2_sort_create": (i32, [vp, vp, P(Expr), P(C.c_int), P(C.c_int), i32, P(vp)]),
+        "b2_limit_create": (i32, [vp, vp, C.c_int64, i32, P(vp)]),
         "b2_hash_aggregate_create": (i32, [vp, vp, i32, P(Expr), i32, P(Agg), i32, P(ArrowSchema), P(vp)]),
         "b2_hash_join_create": (i32, [vp, vp, vp, P(C.c_char_p), P(C.c_char_p), i32, i32, P(vp)]),
         "b2_repartition_create": (i32, [vp, vp, i32, P(Expr), i32, i32, P(vp)]),

@@ -197,6 +197,28 @@ int b2_projection_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, int n_
     *out = wrap(make_projection(&ctx->c, in, std::move(ev)));
   });
 }
+int b2_sort_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, const int* descending, const int* nulls_first,
+                   int n_exprs, b2_op** out) {
+  return guard([&] {
+    REQUIRE(ctx && exprs && descending && out && n_exprs > 0, "null argument");
+    (void)nulls_first;
+    OpPtr in = op_of(input);
+    Schema s = in->schema();
+    std::vector<ExprPtr> es;
+    std::vector<char> desc;
+    for (int i = 0; i < n_exprs; ++i) {
+      es.push_back(decode_expr(&exprs[i], s));
+      desc.push_back(descending[i] != 0);
+    }
+    *out = wrap(make_sort(&ctx->c, in, std::move(es), std::move(desc)));
+  });
+}
+int b2_limit_create(b2_ctx* ctx, b2_op* input, int64_t limit, int global, b2_op** out) {
+  return guard([&] {
+    REQUIRE(ctx && out, "null argument");
+    *out = wrap(make_limit(&ctx->c, op_of(input), limit, global != 0));
+  });
+}
 int b2_hash_aggregate_create(b2_ctx* ctx, b2_op* input, int mode, const b2_expr* group_exprs, int n_groups,
                              const b2_agg* aggs, int n_aggs, const struct ArrowSchema* input_schema, b2_op** out) {
   return guard([&] {

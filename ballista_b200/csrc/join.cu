@@ -373,6 +373,12 @@ __global__ void __launch_bounds__(JP_THREADS)
     }
     uint32_t head[JP_ITEMS];
     int cnt = 0;
+    // a probe side clustered on the key (lineitem: ~4 rows per order) repeats keys in consecutive rows: a row whose
+    // predecessor passed the filter with the same key inherits its result instead of looking the bucket up again
+    bool need[JP_ITEMS];
+    need[0] = pass[0];
+#pragma unroll
+    for (int j = 1; j < JP_ITEMS; ++j) need[j] = pass[j] && !(pass[j - 1] && k[j] == k[j - 1]);
 #pragma unroll
     for (int g = 0; g < JP_ITEMS; g += 4) {  // four bucket loads (8 x 16 B) in flight per thread
       ulonglong2 lo[4], hi[4];
@@ -381,7 +387,7 @@ __global__ void __launch_bounds__(JP_THREADS)
       for (int j = 0; j < 4; ++j) {
         b[j] = bucket_of(k[g + j], bmask);
         const ulonglong2* bp = reinterpret_cast<const ulonglong2*>(slots + b[j] * BUCKET);
-        if (pass[g + j]) {
+        if (need[g + j]) {
           lo[j] = __ldg(bp);
           hi[j] = __ldg(bp + 1);
         } else {
@@ -395,6 +401,9 @@ __global__ void __launch_bounds__(JP_THREADS)
         uint32_t hd = NIL;
         ulonglong2 x = lo[j], y = hi[j];
         u64 bb = b[j];
+        if (!need[g + j]) {
+          hd = (pass[g + j] && g + j > 0) ? head[g + j > 0 ? g + j - 1 : 0] : NIL;
+        } else
         while (true) {
           if ((uint32_t)(x.x >> 32) == kk && x.x != KEY_EMPTY) hd = (uint32_t)x.x;
           if ((uint32_t)(x.y >> 32) == kk && x.y != KEY_EMPTY) hd = (uint32_t)x.y;

@@ -80,6 +80,11 @@ BufPtr hash_split_perm(Ctx* ctx, const SplitState& st);
 void hash_split_move(Ctx* ctx, const SplitState& st, int n_cols, const void* const* src, void* const* dst,
                      const int* width, const int64_t* base_dev, uint32_t* perm_or_null);
 
+// SortExec support (repartition.cu): order-preserving 64-bit key words per sort column, stable LSD radix sort
+void sort_key_words(Ctx* ctx, const Column& c, bool descending, std::vector<BufPtr>* words, std::vector<int>* bits,
+                    int* status_dev);
+BufPtr radix_sort_order(Ctx* ctx, const std::vector<const u64*>& words, const std::vector<int>& bits, int64_t n);
+
 // comm.cu
 void comm_unique_id(void* id128);
 void comm_init(Ctx* ctx, int rank, int nranks, const void* id128);
@@ -140,6 +145,8 @@ OpPtr make_filter(Ctx* ctx, OpPtr input, ExprPtr pred);
 OpPtr make_coalesce(Ctx* ctx, OpPtr input, int64_t target);
 OpPtr make_merge(Ctx* ctx, OpPtr input);
 OpPtr make_projection(Ctx* ctx, OpPtr input, std::vector<ExprPtr> exprs);
+OpPtr make_sort(Ctx* ctx, OpPtr input, std::vector<ExprPtr> exprs, std::vector<char> descending);
+OpPtr make_limit(Ctx* ctx, OpPtr input, int64_t limit, bool global);
 OpPtr make_hash_aggregate(Ctx* ctx, OpPtr input, int mode, std::vector<ExprPtr> groups, std::vector<AggSpec> aggs,
                           const Schema* input_schema);
 OpPtr make_hash_join(Ctx* ctx, OpPtr left, OpPtr right, std::vector<std::string> on_left,

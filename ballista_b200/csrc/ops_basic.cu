@@ -286,4 +286,116 @@ OpPtr make_projection(Ctx* ctx, OpPtr input, std::vector<ExprPtr> exprs) {
   return op;
 }
 
+// ------------------------------------------------------------------------------------------------------
+// SortExec (from_proto.rs:291-330: SortExec::try_new(Vec<PhysicalSortExpr{expr, SortOptions}>, input)) and
+// GlobalLimitExec / LocalLimitExec (from_proto.rs:165-171): the operators that follow the final aggregate in the
+// benchmark queries (q1.sql:17-21 ORDER BY flags; q3.sql:20-23 ORDER BY revenue DESC, o_orderdate LIMIT 10).
+// Like the reference's, SortExec needs a single input partition and emits one sorted batch; the sort is stable
+// (ties keep input order), nulls do not occur on this path.
+// ------------------------------------------------------------------------------------------------------
+struct SortExec : Op {
+  std::vector<ExprPtr> exprs;
+  std::vector<char> descending;
+  const char* name() const override { return "SortExec"; }
+  Schema schema() const override { return children[0]->schema(); }
+  void partitioning(int* scheme, int* n) const override {
+    *scheme = B2_PART_UNKNOWN;
+    *n = 1;
+  }
+  bool per_rank_partitions() const override { return false; }
+  struct S : Stream {
+    SortExec* op;
+    bool done = false;
+    BatchPtr next() override {
+      if (done) return nullptr;
+      done = true;
+      Ctx* ctx = op->ctx;
+      Op* in = op->children[0].get();
+      if (in->n_partitions() != 1)
+        fail(B2_ERR_EXECUTION, "SortExec requires a single input partition (put a MergeExec below it)");
+      std::vector<BatchPtr> all;
+      StreamPtr s = in->execute(0);
+      while (BatchPtr b = s->next())
+        if (b->num_rows) all.push_back(b);
+      if (all.empty()) return empty_batch(ctx, op->schema());
+      BatchPtr b = concat_batches(ctx, op->schema(), all);
+      std::vector<BufPtr> words;
+      std::vector<int> bits;
+      std::vector<Column> keep;
+      BufPtr st = dev_alloc_zero(ctx, 16);
+      for (size_t k = 0; k < op->exprs.size(); ++k) {
+        keep.push_back(eval_expr(ctx, op->exprs[k], *b));
+        sort_key_words(ctx, keep.back(), op->descending[k] != 0, &words, &bits, st->as<int>());
+      }
+      std::vector<const u64*> w;
+      for (auto& x : words) w.push_back(x->as<u64>());
+      BufPtr order = radix_sort_order(ctx, w, bits, b->num_rows);
+      int host = 0;
+      B2_READBACK(ctx, &host, st->ptr, 4);
+      if (host) fail(B2_ERR_NOT_IMPLEMENTED, "sort key strings longer than 16 bytes");
+      return take_batch(ctx, *b, order->as<uint32_t>(), b->num_rows);
+    }
+  };
+  StreamPtr execute(int partition) override {
+    if (partition != 0) fail(B2_ERR_INVALID_ARG, "SortExec has a single output partition");
+    auto s = std::make_unique<S>();
+    s->op = this;
+    last_path = "radix";
+    return s;
+  }
+};
+OpPtr make_sort(Ctx* ctx, OpPtr input, std::vector<ExprPtr> exprs, std::vector<char> descending) {
+  if (exprs.empty() || exprs.size() != descending.size()) fail(B2_ERR_INVALID_ARG, "SortExec needs sort expressions");
+  auto op = std::make_shared<SortExec>();
+  op->ctx = ctx;
+  op->children = {input};
+  op->exprs = std::move(exprs);
+  op->descending = std::move(descending);
+  return op;
+}
+
+struct LimitExec : Op {
+  int64_t limit = 0;
+  bool global = true;
+  const char* name() const override { return global ? "GlobalLimitExec" : "LocalLimitExec"; }
+  Schema schema() const override { return children[0]->schema(); }
+  void require(const std::vector<char>& need) override { children[0]->require(need); }
+  struct S : Stream {
+    LimitExec* op;
+    StreamPtr in;
+    int64_t left;
+    BatchPtr next() override {
+      if (left <= 0) return nullptr;
+      BatchPtr b = in->next();
+      if (!b) return nullptr;
+      if (b->num_rows <= left) {
+        left -= b->num_rows;
+        return b;
+      }
+      BatchPtr cut = slice_batch(op->ctx, *b, 0, left);
+      left = 0;
+      return cut;
+    }
+  };
+  StreamPtr execute(int partition) override {
+    if (global && children[0]->n_partitions() != 1)
+      fail(B2_ERR_EXECUTION, "GlobalLimitExec requires a single input partition");
+    auto s = std::make_unique<S>();
+    s->op = this;
+    s->in = children[0]->execute(partition);
+    s->left = limit;
+    last_path = "slice";
+    return s;
+  }
+};
+OpPtr make_limit(Ctx* ctx, OpPtr input, int64_t limit, bool global) {
+  if (limit < 0) fail(B2_ERR_INVALID_ARG, "negative limit");
+  auto op = std::make_shared<LimitExec>();
+  op->ctx = ctx;
+  op->children = {input};
+  op->limit = limit;
+  op->global = global;
+  return op;
+}
+
 }  // namespace b2

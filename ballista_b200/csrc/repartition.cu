@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(RP_THREADS)
 // pass 2: stable rank of every row inside its (destination, tile) run -> perm[offset + rank] = row
 __global__ void __launch_bounds__(RP_THREADS)
     rp_scatter_kernel(const uint8_t* __restrict__ dest, int64_t n, int n_out, const int64_t* __restrict__ off,
-                      int64_t n_tiles, uint32_t* __restrict__ perm) {
+                      int64_t n_tiles, uint32_t* __restrict__ perm, const uint32_t* __restrict__ remap = nullptr) {
   __shared__ uint32_t cnt[RP_ITEMS][RP_WARPS][RP_MAX_OUT];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -99,7 +99,10 @@ __global__ void __launch_bounds__(RP_THREADS)
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < RP_ITEMS; ++j)
-      if (d[j] >= 0) perm[cnt[j][warp][d[j]] + rank[j]] = (uint32_t)(tile * RP_TILE + j * RP_THREADS + threadIdx.x);
+      if (d[j] >= 0) {
+        int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
+        perm[cnt[j][warp][d[j]] + rank[j]] = remap ? remap[r] : (uint32_t)r;  // remap: the radix sort's current order
+      }
     __syncthreads();
   }
 }
@@ -280,6 +283,146 @@ BufPtr hash_partition_indices(Ctx* ctx, const Key128* keys, const int32_t* key32
   BufPtr perm = hash_split_perm(ctx, st);
   hash_split_counts(ctx, st, counts);
   return perm;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// SortExec support: stable LSD radix sort of row ids over order-preserving 64-bit key words, 5 bits per pass,
+// reusing the split machinery above (a pass IS a stable 32-way split of the current order by one digit).
+// ------------------------------------------------------------------------------------------------------
+// key words: unsigned integers whose order is the column's sort order (descending = complement)
+__global__ void sort_word_i32_kernel(const int32_t* __restrict__ v, int64_t n, bool desc, u64* __restrict__ w) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    u64 x = (u64)((uint32_t)v[i] ^ 0x80000000u);
+    w[i] = desc ? (~x & 0xFFFFFFFFull) : x;
+  }
+}
+__global__ void sort_word_i64_kernel(const int64_t* __restrict__ v, int64_t n, bool desc, bool is_unsigned,
+                                     u64* __restrict__ w) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    u64 x = (u64)v[i] ^ (is_unsigned ? 0ull : 0x8000000000000000ull);
+    w[i] = desc ? ~x : x;
+  }
+}
+// IEEE total order with NaN last in ascending order (arrow's sort places NaN after all numbers)
+__global__ void sort_word_f64_kernel(const double* __restrict__ v, int64_t n, bool desc, u64* __restrict__ w) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    double d = v[i];
+    u64 b = (u64)__double_as_longlong(d);
+    u64 x = (d != d) ? ~0ull : ((b >> 63) ? ~b : (b | 0x8000000000000000ull));
+    w[i] = desc ? ~x : x;
+  }
+}
+// Utf8: bytes [8 * word, 8 * word + 8) big-endian, zero padded (byte strings of at most 16 bytes; longer ones raise
+// status so the host can refuse instead of mis-sorting)
+__global__ void sort_word_str_kernel(const int32_t* __restrict__ off, const uint8_t* __restrict__ chr, int64_t n, int word,
+                                     bool desc, u64* __restrict__ w, int* status) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int32_t b = off[i], len = off[i + 1] - b;
+    if (len > 16) *status = 1;
+    u64 x = 0;
+    for (int q = 0; q < 8; ++q) {
+      int p = word * 8 + q;
+      x = (x << 8) | (p < len ? (u64)chr[b + p] : 0ull);
+    }
+    w[i] = desc ? ~x : x;
+  }
+}
+// digit of the current order's key + per-tile histogram (destination-major, like rp_hist_kernel)
+__global__ void __launch_bounds__(RP_THREADS)
+    sort_digit_kernel(const u64* __restrict__ word, const uint32_t* __restrict__ order, int64_t n, int shift,
+                      uint8_t* __restrict__ dest, int64_t* __restrict__ hist, int64_t n_tiles) {
+  __shared__ int h[RP_MAX_OUT];
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    if (threadIdx.x < RP_MAX_OUT) h[threadIdx.x] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < RP_ITEMS; ++j) {
+      int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
+      int d = r < n ? (int)((word[order[r]] >> shift) & 31ull) : -1;
+      if (d >= 0) dest[r] = (uint8_t)d;
+      unsigned peers = __match_any_sync(0xffffffffu, d);
+      if (d >= 0 && (peers & ((1u << (threadIdx.x & 31)) - 1)) == 0) atomicAdd(&h[d], __popc(peers));
+    }
+    __syncthreads();
+    if (threadIdx.x < RP_MAX_OUT) hist[(int64_t)threadIdx.x * n_tiles + tile] = h[threadIdx.x];
+    __syncthreads();
+  }
+}
+__global__ void iota_kernel(uint32_t* v, int64_t n) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) v[i] = (uint32_t)i;
+}
+
+// words[k] / bits[k]: key words from the MOST significant (first sort column) to the least; returns the sorted
+// order of row ids (stable: equal keys keep their input order)
+BufPtr radix_sort_order(Ctx* ctx, const std::vector<const u64*>& words, const std::vector<int>& bits, int64_t n) {
+  if (n >= (1ll << 32) - 1) fail(B2_ERR_NOT_IMPLEMENTED, "sort beyond 2^32-2 rows");
+  auto a = dev_alloc(ctx, (size_t)(n + 1) * 4), b = dev_alloc(ctx, (size_t)(n + 1) * 4);
+  if (n == 0) return a;
+  int grid = grid_for(ctx, 8, n, RP_TILE);
+  iota_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(a->as<uint32_t>(), n);
+  B2_LAUNCHED(ctx);
+  int64_t n_tiles = (n + RP_TILE - 1) / RP_TILE;
+  auto dest = dev_alloc(ctx, (size_t)n + 16);
+  auto hist = dev_alloc(ctx, (size_t)(n_tiles * RP_MAX_OUT + 2) * 8);
+  for (int k = (int)words.size() - 1; k >= 0; --k) {
+    for (int shift = 0; shift < bits[k]; shift += 5) {
+      sort_digit_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(words[k], a->as<uint32_t>(), n, shift, dest->as<uint8_t>(),
+                                                              hist->as<int64_t>(), n_tiles);
+      B2_LAUNCHED(ctx);
+      scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(hist->as<int64_t>(), n_tiles * RP_MAX_OUT);
+      B2_LAUNCHED(ctx);
+      rp_scatter_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(dest->as<uint8_t>(), n, RP_MAX_OUT, hist->as<int64_t>(),
+                                                              n_tiles, b->as<uint32_t>(), a->as<uint32_t>());
+      B2_LAUNCHED(ctx);
+      std::swap(a, b);
+    }
+  }
+  return a;
+}
+
+// order-preserving key words of one sort column (1 word; Utf8: 2)
+void sort_key_words(Ctx* ctx, const Column& c, bool desc, std::vector<BufPtr>* words, std::vector<int>* bits, int* status_dev) {
+  int64_t n = c.length;
+  int grid = grid_for(ctx, 8, n, 256);
+  auto alloc = [&]() { return dev_alloc(ctx, (size_t)(n + 1) * 8); };
+  switch (c.dtype) {
+    case B2_INT32: case B2_DATE32: {
+      auto w = alloc();
+      if (n) { sort_word_i32_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), n, desc, w->as<u64>()); B2_LAUNCHED(ctx); }
+      words->push_back(w); bits->push_back(32);
+      break;
+    }
+    case B2_INT64: case B2_UINT64: {
+      auto w = alloc();
+      if (n) { sort_word_i64_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<int64_t>(), n, desc, c.dtype == B2_UINT64, w->as<u64>()); B2_LAUNCHED(ctx); }
+      words->push_back(w); bits->push_back(64);
+      break;
+    }
+    case B2_FLOAT64: {
+      auto w = alloc();
+      if (n) { sort_word_f64_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<double>(), n, desc, w->as<u64>()); B2_LAUNCHED(ctx); }
+      words->push_back(w); bits->push_back(64);
+      break;
+    }
+    case B2_UTF8: {
+      for (int word = 0; word < 2; ++word) {
+        auto w = alloc();
+        if (n) {
+          sort_word_str_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), c.chars->as<uint8_t>(), n, word, desc,
+                                                              w->as<u64>(), status_dev);
+          B2_LAUNCHED(ctx);
+        }
+        words->push_back(w); bits->push_back(64);
+      }
+      break;
+    }
+    default: fail(B2_ERR_NOT_IMPLEMENTED, std::string("sort key of type ") + dtype_name(c.dtype));
+  }
 }
 
 // rows [begin, end) of a batch as a new batch (device-to-device copies; Utf8 offsets rebased)

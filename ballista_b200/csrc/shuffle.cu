@@ -175,8 +175,9 @@ struct PullSeg {
   int64_t bytes;
 };
 constexpr int PULL_UNROLL = 4;
-__global__ void __launch_bounds__(256) pull_kernel(const PullSeg* __restrict__ segs) {
-  PullSeg s = segs[blockIdx.y];
+template <int PULL_UNROLL>
+__global__ void __launch_bounds__(256) pull_kernel(const PullSeg* __restrict__ segs, int seg0) {
+  PullSeg s = segs[seg0 + blockIdx.y];
   if (s.bytes <= 0) return;
   const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
   if ((((uintptr_t)s.src ^ (uintptr_t)s.dst) & 15) != 0) {  // not congruent (never on the planned path): bytes
@@ -422,8 +423,29 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
     int64_t want = (max_seg / 16 + 256 * PULL_UNROLL - 1) / (256 * PULL_UNROLL);
     int64_t cap = std::max<int64_t>(1, (int64_t)ctx->sm_count * 8 / (int64_t)segs.size());
     dim3 g((unsigned)std::max<int64_t>(1, std::min(want, cap)), (unsigned)segs.size());
-    pull_kernel<<<g, 256, 0, ctx->stream>>>(dsegs->as<PullSeg>());
-    B2_LAUNCHED(ctx);
+    // experiment knobs (defaults = the measured best): B2_PULL_UNROLL 4|8, B2_PULL_CTAS_PER_SM, B2_PULL_SPLIT=1
+    // launches the local slice (the first ncol-ish descriptors) separately from the peer slices
+    int unroll = getenv("B2_PULL_UNROLL") ? atoi(getenv("B2_PULL_UNROLL")) : 4;
+    int per_sm = getenv("B2_PULL_CTAS_PER_SM") ? atoi(getenv("B2_PULL_CTAS_PER_SM")) : 8;
+    cap = std::max<int64_t>(1, (int64_t)ctx->sm_count * per_sm / (int64_t)segs.size());
+    g.x = (unsigned)std::max<int64_t>(1, std::min(want, cap));
+    size_t n_local = segs.size() / (size_t)nr;  // descriptors of the local slice come first
+    auto launch = [&](size_t first, size_t count) {
+      if (!count) return;
+      dim3 gg(g.x, (unsigned)count);
+      if (unroll == 8)
+        pull_kernel<8><<<gg, 256, 0, ctx->stream>>>(dsegs->as<PullSeg>(), (int)first);
+      else
+        pull_kernel<4><<<gg, 256, 0, ctx->stream>>>(dsegs->as<PullSeg>(), (int)first);
+      B2_LAUNCHED(ctx);
+    };
+    if (getenv("B2_PULL_SPLIT")) {
+      launch(0, n_local);
+      pt.mark("shuffle 5a: local slice copy");
+      launch(n_local, segs.size() - n_local);
+    } else {
+      launch(0, segs.size());
+    }
   }
   pt.mark("shuffle 5: pull over NVLink");
   for (size_t c = 0; c < ncol; ++c)

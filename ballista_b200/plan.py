@@ -312,6 +312,35 @@ class ProjectionExec(ExecutionPlan):
         super().__init__(input.ctx, h, [input])
 
 
+class SortExec(ExecutionPlan):
+    """SortExec::try_new(exprs, input); `exprs` = [expr | (expr, ascending)] (from_proto.rs:291-330)."""
+
+    def __init__(self, exprs, input):
+        keep, h = [], C.c_void_p()
+        names = _names(input)
+        pairs = [(e, True) if isinstance(e, Expr) else (e[0], bool(e[1])) for e in exprs]
+        lowered = [e.lower(names, keep) for e, _ in pairs]
+        arr = (K.Expr * len(lowered))(*lowered)
+        desc = (C.c_int * len(pairs))(*[0 if asc else 1 for _, asc in pairs])
+        nulls = (C.c_int * len(pairs))(*[0] * len(pairs))
+        K.check(K.lib().b2_sort_create(input.ctx._h, input._h, arr, desc, nulls, len(lowered), C.byref(h)))
+        super().__init__(input.ctx, h, [input])
+
+
+class GlobalLimitExec(ExecutionPlan):
+    def __init__(self, input, limit):
+        h = C.c_void_p()
+        K.check(K.lib().b2_limit_create(input.ctx._h, input._h, int(limit), 1, C.byref(h)))
+        super().__init__(input.ctx, h, [input])
+
+
+class LocalLimitExec(ExecutionPlan):
+    def __init__(self, input, limit):
+        h = C.c_void_p()
+        K.check(K.lib().b2_limit_create(input.ctx._h, input._h, int(limit), 0, C.byref(h)))
+        super().__init__(input.ctx, h, [input])
+
+
 class HashAggregateExec(ExecutionPlan):
     """HashAggregateExec::try_new(mode, group_expr, aggr_expr, input, input_schema)."""
 

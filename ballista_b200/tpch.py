@@ -11,8 +11,8 @@ import pyarrow as pa
 
 from . import _capi as K
 from .expr import avg, col, count, date, lit, sum as sum_
-from .plan import (CoalesceBatchesExec, FilterExec, HashAggregateExec, HashJoinExec, MemoryExec, MergeExec,
-                   RepartitionExec)
+from .plan import (CoalesceBatchesExec, FilterExec, GlobalLimitExec, HashAggregateExec, HashJoinExec, MemoryExec,
+                   MergeExec, RepartitionExec, SortExec)
 
 Q1_COLUMNS = ["l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_returnflag", "l_linestatus", "l_shipdate"]
 Q6_COLUMNS = ["l_quantity", "l_extendedprice", "l_discount", "l_shipdate"]
@@ -136,6 +136,16 @@ def q3_partial(customer, orders, lineitem, **kw):
 def q3_final(partial_states, input_schema):
     return HashAggregateExec("Final", q3_groups(), q3_aggregates(), MergeExec(partial_states),
                              input_schema=input_schema)
+
+
+def q1_sorted(final):
+    """ORDER BY l_returnflag, l_linestatus (q1.sql:17-21) over the Final aggregate."""
+    return SortExec([col("l_returnflag"), col("l_linestatus")], final)
+
+
+def q3_top(final, limit=10):
+    """ORDER BY revenue DESC, o_orderdate LIMIT 10 (q3.sql:20-23) over the Final aggregate."""
+    return GlobalLimitExec(SortExec([(col("revenue"), False), (col("o_orderdate"), True)], final), limit)
 
 
 def scan(ctx, batches_per_partition, schema=None):

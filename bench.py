@@ -425,11 +425,19 @@ def run_other_configs(args, ctx, env):
         scan = tpch.scan(ctx, [[li6]])
         part = tpch.q6_partial(scan)
         return tpch.run_two_stage(ctx, part, lambda s: tpch.q6_final(s, scan.schema()), merge="allgather"), part
+    ctx.set_profiling(True)
+    ctx.profile()
     ms, launches, (tab, part) = timeit(q6)
+    k_ms, k_n = ctx.profile()  # CUDA events around every fused-scan launch since the reset (warm-up included)
+    ctx.set_profiling(False)
     n = li6.num_rows
     out["q6"] = {"workload": f"TPC-H Q6, SF{sf:g} lineitem per GPU ({n} rows x 28 B)", "ms_per_step": ms,
                  "rows_per_s": n * world / (ms / 1e3), "GB_per_s_per_gpu": n * 28 / (ms / 1e3) / 1e9,
                  "frac_of_hbm_peak": n * 28 / (ms / 1e3) / 1e9 / peak, "launches_per_step": launches,
+                 "scan_kernel": {"avg_launch_ms": k_ms / k_n if k_n else None,
+                                 "GB_per_s": n * 28 / (k_ms / k_n / 1e3) / 1e9 if k_n else None,
+                                 "frac_of_hbm_peak": n * 28 / (k_ms / k_n / 1e3) / 1e9 / peak if k_n else None,
+                                 "note": "the fused scan kernel alone; the rest of the step is fixed per-step overhead"},
                  "path": part.last_path(), "revenue": tab.to_pylist()[0]["revenue"]}
     del li6
     # ---- Q3 @ SF10: customer |x| orders |x| lineitem + group-by (this rank's partition of all three) ----

@@ -174,6 +174,13 @@ int b2_coalesce_batches_create(b2_ctx* ctx, b2_op* input, int64_t target_batch_s
 int b2_merge_create(b2_ctx* ctx, b2_op* input, b2_op** out);
 /* ProjectionExec::try_new(exprs, input)                       from_proto.rs:60-80 */
 int b2_projection_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, int n_exprs, b2_op** out);
+/* SortExec::try_new(Vec<PhysicalSortExpr{expr, SortOptions{descending, nulls_first}}>, input)  from_proto.rs:291-330.
+ * Single input partition, one sorted output batch, stable.  `descending[i]` != 0 sorts expression i descending;
+ * nulls_first is accepted for interface parity (columns on this path are non-null). */
+int b2_sort_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, const int* descending, const int* nulls_first,
+                   int n_exprs, b2_op** out);
+/* GlobalLimitExec::new(input, limit) (global != 0) / LocalLimitExec::new(input, limit)   from_proto.rs:165-171 */
+int b2_limit_create(b2_ctx* ctx, b2_op* input, int64_t limit, int global, b2_op** out);
 /* HashAggregateExec::try_new(mode, group_expr, aggr_expr, input, input_schema)  from_proto.rs:173-252.
  * Partial emits accumulator-state columns "<name>[sum]" / "<name>[count]" (SURVEY Appendix A.2);
  * Final reads them positionally after the group columns and needs `input_schema` = the schema of the

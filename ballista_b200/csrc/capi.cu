@@ -56,6 +56,7 @@ int b2_ctx_create(int device, b2_ctx** out) {
       if (prop.major < 10) fail(B2_ERR_CUDA, std::string("device '") + prop.name + "' is not sm_100-class");
       h->c.sm_count = prop.multiProcessorCount;
       h->c.trace = getenv("B2_TRACE") != nullptr;
+      h->c.cache_off = getenv("B2_DISABLE_ALLOC_CACHE") != nullptr;
       B2_CUDA(cudaStreamCreateWithFlags(&h->c.stream, cudaStreamNonBlocking));
       B2_CUDA(cudaStreamCreateWithFlags(&h->c.copy_stream, cudaStreamNonBlocking));
       B2_CUDA(cudaDeviceGetDefaultMemPool(&h->c.pool, device));
@@ -81,6 +82,7 @@ void b2_ctx_destroy(b2_ctx* ctx) {
       fprintf(stderr, "[b2 trace] %-60s %10.3f %8lld\n", kv.first.c_str(), kv.second.first * 1e3,
               (long long)kv.second.second);
   }
+  ctx_trim_cache(&ctx->c);
   if (ctx->c.pinned_stage) cudaFreeHost(ctx->c.pinned_stage);
   cudaStreamDestroy(ctx->c.stream);
   cudaStreamDestroy(ctx->c.copy_stream);

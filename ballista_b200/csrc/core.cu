@@ -6,12 +6,41 @@
 
 namespace b2 {
 
-DevBuf::DevBuf(Ctx* c, size_t n) : ctx(c), bytes(n) {
-  if (n == 0) return;
+// Size-class cache in front of the stream-ordered pool.  Every buffer of a context is produced and consumed on
+// the context's stream (the H2D prefetch stream is joined by an event before its buffers are read), so a block
+// released by the host can be handed to the next request at once: work already enqueued on it precedes, in stream
+// order, anything the new owner will enqueue.  cudaMallocAsync costs ~4 us a call and an operator pipeline makes
+// ~70 allocations per Q3 step; a cache hit costs a map lookup.
+static size_t size_class(size_t n) {
   // every buffer is padded so that 16-byte vector loads / TMA bulk copies of the last rows stay in bounds
   n = (n + 32 + 255) & ~(size_t)255;
+  if (n <= (1u << 20)) {
+    size_t p = 256;
+    while (p < n) p <<= 1;
+    return p;
+  }
+  return (n + (1u << 20) - 1) & ~(size_t)((1u << 20) - 1);
+}
+DevBuf::DevBuf(Ctx* c, size_t n) : ctx(c), bytes(n) {
+  if (n == 0) return;
+  n = size_class(n);
+  {
+    std::lock_guard<std::mutex> g(c->cache_mu);
+    auto it = c->cache.find(n);
+    if (it != c->cache.end() && !it->second.empty()) {
+      ptr = it->second.back();
+      it->second.pop_back();
+      c->cache_bytes -= n;
+      return;
+    }
+  }
   double t0 = c->trace ? wall_now() : 0;
   cudaError_t e = cudaMallocAsync(&ptr, n, c->pool, c->stream);
+  if (e == cudaErrorMemoryAllocation) {  // give the cached blocks back and retry once
+    cudaGetLastError();
+    ctx_trim_cache(c);
+    e = cudaMallocAsync(&ptr, n, c->pool, c->stream);
+  }
   if (c->trace) c->trace_add("cudaMallocAsync", wall_now() - t0);
   if (e != cudaSuccess) {
     cudaGetLastError();
@@ -21,9 +50,25 @@ DevBuf::DevBuf(Ctx* c, size_t n) : ctx(c), bytes(n) {
 }
 DevBuf::~DevBuf() {
   if (!ptr) return;
+  size_t n = size_class(bytes);
+  {
+    std::lock_guard<std::mutex> g(ctx->cache_mu);
+    if (!ctx->cache_off && ctx->cache_bytes + n <= ctx->cache_limit) {
+      ctx->cache[n].push_back(ptr);
+      ctx->cache_bytes += n;
+      return;
+    }
+  }
   double t0 = ctx->trace ? wall_now() : 0;
   cudaFreeAsync(ptr, ctx->stream);
   if (ctx->trace) ctx->trace_add("cudaFreeAsync", wall_now() - t0);
+}
+void ctx_trim_cache(Ctx* c) {
+  std::lock_guard<std::mutex> g(c->cache_mu);
+  for (auto& kv : c->cache)
+    for (void* p : kv.second) cudaFreeAsync(p, c->stream);
+  c->cache.clear();
+  c->cache_bytes = 0;
 }
 BufPtr dev_alloc(Ctx* ctx, size_t bytes) { return std::make_shared<DevBuf>(ctx, bytes); }
 BufPtr dev_alloc_zero(Ctx* ctx, size_t bytes) {

@@ -5,6 +5,7 @@
 #include <chrono>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -40,6 +41,11 @@ struct Ctx {
   Comm* comm = nullptr;
   int rank = 0, nranks = 1;
   int64_t bytes_sent = 0;
+  // size-class cache of released HBM blocks (core.cu); B2_DISABLE_ALLOC_CACHE=1 turns it off
+  std::mutex cache_mu;
+  std::map<size_t, std::vector<void*>> cache;
+  size_t cache_bytes = 0, cache_limit = (size_t)48 << 30;
+  bool cache_off = false;
   void* pinned_stage = nullptr;  // 4 MiB pinned host buffer for the D2H of small result batches (core.cu)
   // optional per-launch timing of the dominant (aggregate scan) kernel with CUDA events on `stream`
   bool profiling = false;
@@ -126,6 +132,7 @@ struct DevBuf {
   template <class T> T* as() const { return reinterpret_cast<T*>(ptr); }
 };
 using BufPtr = std::shared_ptr<DevBuf>;
+void ctx_trim_cache(Ctx* ctx);  // returns every cached block to the stream-ordered pool
 BufPtr dev_alloc(Ctx* ctx, size_t bytes);
 BufPtr dev_alloc_zero(Ctx* ctx, size_t bytes);
 

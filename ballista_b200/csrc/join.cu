@@ -466,12 +466,8 @@ __global__ void join_compact_kernel(const uint32_t* __restrict__ stage_l, const 
 int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& pred, const uint8_t* mask, int64_t n,
                      BufPtr* left_idx, BufPtr* right_idx) {
   if (n >= (int64_t)NIL) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
-  if (!t.dups_known) {  // one readback per build: does any key occur twice on the build side?
-    int f = 0;
-    B2_READBACK(ctx, &f, t.flags->ptr, 4);
-    t.has_dups = f != 0;
-    t.dups_known = true;
-  }
+  // Whether any key occurs twice on the build side is learnt with the first probe's own readback: that probe runs
+  // the primary-key path speculatively and is redone through the chain-walking path if the flag turns out set.
   int64_t total = 0;
   if (n == 0) {
     *left_idx = dev_alloc(ctx, 4);
@@ -492,7 +488,7 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
   int grid = grid_for(ctx, per_sm, n, JP_TILE);
   const u64* slots = t.slots->as<u64>();
   const uint32_t* next = t.next->as<uint32_t>();
-  if (t.has_dups) {
+  if (t.dups_known && t.has_dups) {
     join_probe32_kernel<PROBE_COUNT, true><<<grid, JP_THREADS, 0, ctx->stream>>>(key, pred, mask, n, vec, slots,
                                                                                t.cap / BUCKET - 1, next, nullptr, nullptr, tile_cnt);
     B2_LAUNCHED(ctx);
@@ -518,7 +514,16 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
   B2_LAUNCHED(ctx);
   scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(tile_cnt, n_tiles);
   B2_LAUNCHED(ctx);
-  B2_READBACK(ctx, &total, tile_cnt + n_tiles, 8);
+  if (!t.dups_known) {
+    int f = 0;
+    B2_CUDA(cudaMemcpyAsync(&f, t.flags->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_READBACK(ctx, &total, tile_cnt + n_tiles, 8);
+    t.dups_known = true;
+    t.has_dups = f != 0;
+    if (t.has_dups) return join_probe32(ctx, t, key, pred, mask, n, left_idx, right_idx);  // speculation failed
+  } else {
+    B2_READBACK(ctx, &total, tile_cnt + n_tiles, 8);
+  }
   *left_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
   *right_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
   if (total) {

@@ -212,6 +212,9 @@ BatchPtr HashAggregateExec::run_final(int partition) {
     }
     AggLaunch l = bind_column_agg(ctx, keys, nullptr, vals, cnts, /*count_rows=*/false);
     if (!runner) runner = std::make_unique<AggRunner>(ctx, l.na, l.nc, l.keyed);
+    // partial states carry one row per group of their partition: a large state batch means more groups than the
+    // per-CTA tables of the low-cardinality kernel hold, so go straight to the HBM table
+    if (ng && b->num_rows > 16384) runner->force_global = true;
     runner->consume(l, b->num_rows);
   }
   if (!runner) runner = std::make_unique<AggRunner>(ctx, n_sum ? n_sum : 1, n_cnt ? n_cnt : 1, ng > 0);

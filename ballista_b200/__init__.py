@@ -9,10 +9,11 @@ from ._capi import BallistaError, NotImplementedOnGpu
 from .expr import Expr, AggExpr, col, lit, date, sum, avg, count  # noqa: A004
 from .plan import (Context, DeviceBatch, ExecutionPlan, RecordBatchStream, MemoryExec, FilterExec,
                    CoalesceBatchesExec, MergeExec, ProjectionExec, HashAggregateExec, HashJoinExec,
-                   RepartitionExec, SortExec, GlobalLimitExec, LocalLimitExec)
+                   RepartitionExec, SortExec, GlobalLimitExec, LocalLimitExec, plan_from_proto, describe_plan_proto)
 from . import tpch
 
 __all__ = ["BallistaError", "NotImplementedOnGpu", "Expr", "AggExpr", "col", "lit", "date", "sum", "avg", "count",
            "Context", "DeviceBatch", "ExecutionPlan", "RecordBatchStream", "MemoryExec", "FilterExec",
            "CoalesceBatchesExec", "MergeExec", "ProjectionExec", "HashAggregateExec", "HashJoinExec",
-           "RepartitionExec", "SortExec", "GlobalLimitExec", "LocalLimitExec", "tpch"]
+           "RepartitionExec", "SortExec", "GlobalLimitExec", "LocalLimitExec", "plan_from_proto",
+           "describe_plan_proto", "tpch"]

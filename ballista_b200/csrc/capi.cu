@@ -199,6 +199,23 @@ int b2_projection_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, int n_
     *out = wrap(make_projection(&ctx->c, in, std::move(ev)));
   });
 }
+int b2_plan_from_proto(b2_ctx* ctx, const uint8_t* buf, size_t len, b2_op* const* leaves, int n_leaves, b2_op** out) {
+  return guard([&] {
+    REQUIRE(ctx && buf && out && n_leaves >= 0 && (leaves || n_leaves == 0), "null argument");
+    std::vector<OpPtr> ops;
+    for (int i = 0; i < n_leaves; ++i) ops.push_back(op_of(leaves[i]));
+    *out = wrap(plan_from_proto(&ctx->c, buf, len, ops));
+  });
+}
+int b2_plan_proto_describe(const uint8_t* buf, size_t len, char* out, size_t cap, int* n_leaves) {
+  return guard([&] {
+    REQUIRE(buf && out && cap > 0, "null argument");
+    std::string t = plan_proto_describe(buf, len, n_leaves);
+    size_t n = t.size() < cap - 1 ? t.size() : cap - 1;
+    memcpy(out, t.data(), n);
+    out[n] = 0;
+  });
+}
 int b2_sort_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, const int* descending, const int* nulls_first,
                    int n_exprs, b2_op** out) {
   return guard([&] {

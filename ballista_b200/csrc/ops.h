@@ -153,6 +153,10 @@ OpPtr make_hash_join(Ctx* ctx, OpPtr left, OpPtr right, std::vector<std::string>
                      std::vector<std::string> on_right, int join_type);
 OpPtr make_repartition(Ctx* ctx, OpPtr input, int scheme, std::vector<ExprPtr> keys, int n_out);
 
+// proto.cpp: serialized PhysicalPlanNode (ballista.proto:294-422) -> operator tree; leaves bound in pre-order
+OpPtr plan_from_proto(Ctx* ctx, const uint8_t* buf, size_t len, const std::vector<OpPtr>& leaves);
+std::string plan_proto_describe(const uint8_t* buf, size_t len, int* n_leaves);
+
 }  // namespace b2
 
 struct b2_op { b2::OpPtr op; };

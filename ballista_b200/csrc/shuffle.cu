@@ -439,6 +439,7 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
         pull_kernel<4><<<gg, 256, 0, ctx->stream>>>(dsegs->as<PullSeg>(), (int)first);
       B2_LAUNCHED(ctx);
     };
+    ctx->prof_begin();  // b2_ctx_set_profiling: CUDA events around the exchange step (bench.py's NVLink roofline)
     if (getenv("B2_PULL_SPLIT")) {
       launch(0, n_local);
       pt.mark("shuffle 5a: local slice copy");
@@ -446,6 +447,7 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
     } else {
       launch(0, segs.size());
     }
+    ctx->prof_end();
   }
   pt.mark("shuffle 5: pull over NVLink");
   for (size_t c = 0; c < ncol; ++c)

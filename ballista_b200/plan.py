@@ -312,6 +312,22 @@ class ProjectionExec(ExecutionPlan):
         super().__init__(input.ctx, h, [input])
 
 
+def plan_from_proto(ctx, data, leaves):
+    """Serialized `PhysicalPlanNode` (ballista.proto:294-422) -> ExecutionPlan, as the executor rebuilds a task's plan
+    in from_proto.rs:58-346.  `leaves`: the operators bound, in pre-order, to the plan's scan / shuffle-reader nodes."""
+    h = C.c_void_p()
+    arr = (C.c_void_p * max(len(leaves), 1))(*[l._h for l in leaves])
+    K.check(K.lib().b2_plan_from_proto(ctx._h, bytes(data), len(data), arr, len(leaves), C.byref(h)))
+    return ExecutionPlan(ctx, h, list(leaves))
+
+
+def describe_plan_proto(data):
+    """(pre-order operator names, number of leaf nodes) of a serialized PhysicalPlanNode; needs no GPU."""
+    buf, n = C.create_string_buffer(1 << 16), C.c_int(0)
+    K.check(K.lib().b2_plan_proto_describe(bytes(data), len(data), buf, len(buf), C.byref(n)))
+    return [l.strip() for l in buf.value.decode().splitlines()], n.value
+
+
 class SortExec(ExecutionPlan):
     """SortExec::try_new(exprs, input); `exprs` = [expr | (expr, ascending)] (from_proto.rs:291-330)."""
 

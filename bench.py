@@ -474,14 +474,24 @@ def run_other_configs(args, ctx, env):
             path[0] = rep.last_path()
             return sum(b.num_rows for b in got)
         sent0 = ctx.comm_bytes_sent()
+        ctx.set_profiling(True)
+        ctx.profile()
         ms, launches, _ = timeit(shuffle, steps=10, warmup=3)
+        pull_ms, pull_n = ctx.profile()  # CUDA events around the pull kernel of every exchange (warm-up included)
+        ctx.set_profiling(False)
+        pull_ms = cluster.max_over_ranks(dist, torch, pull_ms / max(pull_n, 1), world)
         sent = (ctx.comm_bytes_sent() - sent0) / 13.0
         out["shuffle"] = {"workload": f"hash repartition of lineitem SF{sf:g} per GPU ({n} rows x 20 B) into {world} "
                                       "partitions, exchanged over NVLink", "path": path[0], "ms_per_step": ms,
                           "rows_per_s": n * world / (ms / 1e3), "egress_bytes_per_gpu": sent,
                           "egress_GB_per_s_per_gpu": sent / (ms / 1e3) / 1e9,
                           "frac_of_nvlink_900GBps": sent / (ms / 1e3) / 1e9 / 900.0, "launches_per_step": launches,
-                          "note": "whole operator (split + metadata + exchange); the pull step alone is in profiles/"}
+                          "exchange_step": {"kernel": "pull_kernel (every rank reads its slices from all peer arenas; "
+                                                      "also copies the local slice)", "ms": pull_ms,
+                                            "egress_GB_per_s_per_gpu": sent / (pull_ms / 1e3) / 1e9 if pull_ms else None,
+                                            "frac_of_nvlink_900GBps": sent / (pull_ms / 1e3) / 1e9 / 900.0 if pull_ms else None,
+                                            "frac_of_measured_peer_copy_770GBps": sent / (pull_ms / 1e3) / 1e9 / 770.0 if pull_ms else None},
+                          "note": "ms_per_step is the whole operator (split + metadata + move into the arena + exchange)"}
         del part
         # ---- Q3 with the shuffle: row-range partitions of an SF(10 x N) database, both join inputs exchanged ----
         dsf = sf * world

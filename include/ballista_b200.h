@@ -174,6 +174,16 @@ int b2_coalesce_batches_create(b2_ctx* ctx, b2_op* input, int64_t target_batch_s
 int b2_merge_create(b2_ctx* ctx, b2_op* input, b2_op** out);
 /* ProjectionExec::try_new(exprs, input)                       from_proto.rs:60-80 */
 int b2_projection_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, int n_exprs, b2_op** out);
+/* Wire compatibility: a serialized `PhysicalPlanNode` (rust/core/proto/ballista.proto:294-422, as the scheduler
+ * stores it, rust/scheduler/src/state/mod.rs:149-162) decoded into the operator tree the way the executor does in
+ * rust/core/src/serde/physical_plan/from_proto.rs:58-346.  Leaf nodes (CsvScan, ParquetScan, ShuffleReader,
+ * UnresolvedShuffle, Empty) are not turned into readers: the i-th leaf in pre-order is bound to leaves[i]
+ * (a MemoryExec fed by the CPU reader or by the previous stage).  The handles in `leaves` stay owned by the caller. */
+int b2_plan_from_proto(b2_ctx* ctx, const uint8_t* buf, size_t len, b2_op* const* leaves, int n_leaves, b2_op** out);
+/* The same decoder without a device: writes the pre-order operator list (one node per line, indented) into `out`
+ * (NUL-terminated, truncated to `cap`) and the number of leaf nodes into *n_leaves.  For diagnostics and for
+ * sizing the `leaves` array. */
+int b2_plan_proto_describe(const uint8_t* buf, size_t len, char* out, size_t cap, int* n_leaves);
 /* SortExec::try_new(Vec<PhysicalSortExpr{expr, SortOptions{descending, nulls_first}}>, input)  from_proto.rs:291-330.
  * Single input partition, one sorted output batch, stable.  `descending[i]` != 0 sorts expression i descending;
  * nulls_first is accepted for interface parity (columns on this path are non-null). */

@@ -1,0 +1,122 @@
+"""GPU: edge cases of the fused join / repartition / sort paths (empty and ragged inputs, filters that reject everything,
+extreme key values, duplicate build keys under a fused filter, fused vs unfused agreement)."""
+import os
+
+import numpy as np
+import pyarrow as pa
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def rb(**cols):
+    return pa.RecordBatch.from_arrays([pa.array(v) for v in cols.values()], names=list(cols))
+
+
+def join_rows(ctx, left, right, on, lpred=None, rpred=None):
+    from ballista_b200 import CoalesceBatchesExec, FilterExec, HashJoinExec, tpch
+    l = tpch.scan(ctx, left)
+    r = tpch.scan(ctx, right)
+    if lpred is not None:
+        l = CoalesceBatchesExec(FilterExec(lpred, l))
+    if rpred is not None:
+        r = CoalesceBatchesExec(FilterExec(rpred, r))
+    j = HashJoinExec(l, r, on)
+    out = []
+    for p in range(j.output_partitioning()[1]):
+        t = j.collect(p)
+        out += list(zip(*[t[c].to_pylist() for c in t.schema.names]))
+    return sorted(out), j
+
+
+def test_join_extreme_keys_empty_sides_and_ragged_batches(ctx):
+    from ballista_b200 import col, lit
+    i32 = np.int32
+    lk = np.array([-1, -2**31, 2**31 - 1, 0, 7, 7, -1], dtype=i32)  # -1 = 0xFFFFFFFF (the table's EMPTY key bits), dups
+    rk = np.array([7, -1, 5, -2**31, 2**31 - 1, 0, 0, 9], dtype=i32)
+    left = rb(k=lk, lv=np.arange(len(lk), dtype=np.int64))
+    right = rb(k2=rk, rv=np.arange(len(rk), dtype=np.int64))
+    want = sorted((int(a), i, int(b), j) for i, a in enumerate(lk) for j, b in enumerate(rk) if a == b)
+    got, j = join_rows(ctx, [[left]], [[right.slice(0, 3), right.slice(3, 0)], [right.slice(3)]], [("k", "k2")])
+    assert got == want and "k32" in j.last_path()
+    # empty build side, empty probe side
+    got, _ = join_rows(ctx, [[left.slice(0, 0)]], [[right]], [("k", "k2")])
+    assert got == []
+    got, _ = join_rows(ctx, [[left]], [[right.slice(0, 0)]], [("k", "k2")])
+    assert got == []
+    # fused filters: reject everything on either side, then a selective one with duplicate build keys
+    got, _ = join_rows(ctx, [[left]], [[right]], [("k", "k2")], lpred=col("lv") < lit(0))
+    assert got == []
+    got, _ = join_rows(ctx, [[left]], [[right]], [("k", "k2")], rpred=col("rv") > lit(100))
+    assert got == []
+    got, j = join_rows(ctx, [[left]], [[right]], [("k", "k2")], lpred=col("lv") >= lit(4), rpred=col("rv") <= lit(1))
+    want = sorted((int(a), i, int(b), jx) for i, a in enumerate(lk) for jx, b in enumerate(rk) if a == b and i >= 4 and jx <= 1)
+    assert got == want and len(got) == 3 and "fused" in j.last_path()
+
+
+def test_join_fused_equals_unfused_on_random_data(ctx):
+    from ballista_b200 import col, lit
+    rng = np.random.default_rng(3)
+    n_l, n_r = 50_000, 300_001
+    left = rb(k=rng.integers(0, 40_000, n_l).astype(np.int32), a=rng.random(n_l))
+    right = rb(k2=rng.integers(0, 60_000, n_r).astype(np.int32), b=rng.integers(0, 100, n_r).astype(np.int32),
+               s=pa.array([["x", "yy", "BUILDING"][i % 3] for i in range(n_r)]))
+    parts = [[right.slice(0, 100_000), right.slice(100_000, 7)], [right.slice(100_007)]]
+    args = dict(lpred=col("a") < lit(0.5), rpred=(col("b") >= lit(10)) & (col("b") < lit(60)))
+    fused, j = join_rows(ctx, [[left]], parts, [("k", "k2")], **args)
+    assert "fused" in j.last_path()
+    os.environ["B2_DISABLE_FUSION"] = "1"
+    try:
+        plain, j2 = join_rows(ctx, [[left]], parts, [("k", "k2")], **args)
+    finally:
+        del os.environ["B2_DISABLE_FUSION"]
+    assert "fused" not in j2.last_path()
+    assert fused == plain and len(fused) > 10_000
+    # a string-equality predicate is evaluated as a byte mask and still fused
+    m1, j3 = join_rows(ctx, [[left]], parts, [("k", "k2")], rpred=col("s") == lit("BUILDING"))
+    lk, la = left["k"].to_numpy(), left["a"].to_numpy()
+    rkk = right["k2"].to_numpy()
+    from collections import defaultdict
+    idx = defaultdict(list)
+    for i, k in enumerate(lk):
+        idx[int(k)].append(i)
+    want = sum(len(idx.get(int(k), ())) for i, k in enumerate(rkk) if i % 3 == 2)
+    assert len(m1) == want
+
+
+def test_repartition_fused_filter_empty_and_all_rejected(ctx):
+    from ballista_b200 import CoalesceBatchesExec, FilterExec, RepartitionExec, col, lit, tpch
+    n = 100_003
+    rng = np.random.default_rng(9)
+    b = rb(k=rng.integers(-1000, 1000, n).astype(np.int32), v=rng.random(n), s=pa.array([str(i % 11) for i in range(n)]))
+    def run(pred, batches):
+        src = tpch.scan(ctx, batches)
+        if pred is not None:
+            src = CoalesceBatchesExec(FilterExec(pred, src))
+        rep = RepartitionExec(src, "Hash", 5, [col("k")])
+        rows, owner = [], {}
+        for p in range(5):
+            t = rep.collect(p)
+            for r in zip(t["k"].to_pylist(), t["v"].to_pylist(), t["s"].to_pylist()):
+                assert owner.setdefault(r[0], p) == p
+                rows.append(r)
+        return sorted(rows), rep
+    allrows = sorted(zip(b["k"].to_pylist(), b["v"].to_pylist(), b["s"].to_pylist()))
+    got, rep = run(None, [[b.slice(0, 40_000)], [b.slice(40_000, 0), b.slice(40_000)]])
+    assert got == allrows
+    got, rep = run(col("v") < lit(0.25), [[b]])
+    assert got == [r for r in allrows if r[1] < 0.25] and "fused-filter" in rep.last_path()
+    got, _ = run(col("v") < lit(-1.0), [[b]])
+    assert got == []
+    got, _ = run(None, [[b.slice(0, 0)]])
+    assert got == []
+
+
+def test_sort_empty_single_row_and_presorted(ctx):
+    from ballista_b200 import SortExec, col, tpch
+    b = rb(x=np.array([3, 1, 2], dtype=np.int32), y=np.array([0.5, -0.5, 0.0]))
+    assert SortExec([col("x")], tpch.scan(ctx, [[b.slice(0, 0)]])).collect().num_rows == 0
+    assert SortExec([col("x")], tpch.scan(ctx, [[b.slice(1, 1)]])).collect()["x"].to_pylist() == [1]
+    assert SortExec([(col("y"), False)], tpch.scan(ctx, [[b]])).collect()["x"].to_pylist() == [3, 2, 1]
+    big = rb(x=np.arange(300_000, dtype=np.int32))
+    assert SortExec([(col("x"), False)], tpch.scan(ctx, [[big]])).collect()["x"].to_pylist() == list(range(299_999, -1, -1))

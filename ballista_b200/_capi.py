@@ -107,6 +107,7 @@ def lib():
         "b2_coalesce_batches_create": (i32, [vp, vp, i64, P(vp)]),
         "b2_merge_create": (i32, [vp, vp, P(vp)]),
         "b2_projection_create": (i32, [vp, vp, P(Expr), i32, P(vp)]),
+        "b2_csv_decode": (i32, [vp, P(ArrowSchema), P(C.c_int), i32, C.c_char, i32, C.c_char_p, C.c_size_t, P(vp)]),
         "b2_plan_from_proto": (i32, [vp, C.c_char_p, C.c_size_t, P(vp), i32, P(vp)]),
         "b2_plan_proto_describe": (i32, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, P(i32)]),
         "b2_sort_create": (i32, [vp, vp, P(Expr), P(C.c_int), P(C.c_int), i32, P(vp)]),

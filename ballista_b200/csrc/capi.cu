@@ -199,6 +199,21 @@ int b2_projection_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, int n_
     *out = wrap(make_projection(&ctx->c, in, std::move(ev)));
   });
 }
+int b2_csv_decode(b2_ctx* ctx, const struct ArrowSchema* file_schema, const int* projection, int n_projection,
+                  char delimiter, int has_header, const char* text, size_t len, b2_batch** out) {
+  return guard([&] {
+    REQUIRE(ctx && file_schema && out && (text || len == 0) && n_projection >= 0 && (projection || n_projection == 0),
+            "null argument");
+    ctx->c.activate();
+    Schema fs = schema_from_arrow(file_schema);
+    std::vector<int> proj(projection, projection + n_projection);
+    if (proj.empty())
+      for (size_t i = 0; i < fs.fields.size(); ++i) proj.push_back((int)i);
+    auto* h = new b2_batch;
+    h->b = csv_decode(&ctx->c, fs, proj, delimiter, has_header != 0, text, len);
+    *out = h;
+  });
+}
 int b2_plan_from_proto(b2_ctx* ctx, const uint8_t* buf, size_t len, b2_op* const* leaves, int n_leaves, b2_op** out) {
   return guard([&] {
     REQUIRE(ctx && buf && out && n_leaves >= 0 && (leaves || n_leaves == 0), "null argument");

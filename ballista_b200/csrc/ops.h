@@ -153,6 +153,9 @@ OpPtr make_hash_join(Ctx* ctx, OpPtr left, OpPtr right, std::vector<std::string>
                      std::vector<std::string> on_right, int join_type);
 OpPtr make_repartition(Ctx* ctx, OpPtr input, int scheme, std::vector<ExprPtr> keys, int n_out);
 
+// csv.cu: delimiter-separated text (dbgen .tbl) -> projected columns in HBM; `text` holds whole rows
+BatchPtr csv_decode(Ctx* ctx, const Schema& file_schema, const std::vector<int>& projection, char delimiter,
+                    bool has_header, const char* host_text, size_t len);
 // proto.cpp: serialized PhysicalPlanNode (ballista.proto:294-422) -> operator tree; leaves bound in pre-order
 OpPtr plan_from_proto(Ctx* ctx, const uint8_t* buf, size_t len, const std::vector<OpPtr>& leaves);
 std::string plan_proto_describe(const uint8_t* buf, size_t len, int* n_leaves);

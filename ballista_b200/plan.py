@@ -58,6 +58,22 @@ class Context:
         K.check(K.lib().b2_ctx_profile(self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def read_csv(self, text, schema, projection=None, delimiter="|", has_header=False):
+        """Decode delimiter-separated text (bytes of whole rows, e.g. one dbgen .tbl partition file) on the GPU into a
+        DeviceBatch of the projected columns: the CsvExec leaf's decode (from_proto.rs:93-110)."""
+        sch = _export_schema(schema)
+        proj = list(projection) if projection is not None else list(range(len(schema.names)))
+        proj = [schema.names.index(p) if isinstance(p, str) else int(p) for p in proj]
+        arr = (C.c_int * max(len(proj), 1))(*proj)
+        h = C.c_void_p()
+        data = bytes(text)
+        try:
+            K.check(K.lib().b2_csv_decode(self._h, C.byref(sch), arr, len(proj), delimiter.encode()[:1], int(has_header),
+                                          data, len(data), C.byref(h)))
+        finally:
+            _release_schema(sch)
+        return DeviceBatch(self, h)
+
     # ---- HBM-resident batches ----
     def upload(self, batch):
         """pyarrow RecordBatch (or Table with one chunk) -> DeviceBatch."""

@@ -174,6 +174,13 @@ int b2_coalesce_batches_create(b2_ctx* ctx, b2_op* input, int64_t target_batch_s
 int b2_merge_create(b2_ctx* ctx, b2_op* input, b2_op** out);
 /* ProjectionExec::try_new(exprs, input)                       from_proto.rs:60-80 */
 int b2_projection_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, int n_exprs, b2_op** out);
+/* Column decode of the CsvExec leaf (from_proto.rs:93-110: CsvReadOptions{has_header, delimiter, schema} + projection)
+ * on the GPU: `text` = `len` bytes of whole rows of a delimiter-separated file (dbgen .tbl: '|', no quoting, trailing
+ * delimiter allowed) in host memory; the result holds the projected columns of `file_schema` in HBM.  Int32, Int64,
+ * Float64 (plain decimals of <= 15 significant digits, converted with one correctly rounded division), Date32
+ * (YYYY-MM-DD) and Utf8 columns; malformed input is B2_ERR_ARROW with the line number. */
+int b2_csv_decode(b2_ctx* ctx, const struct ArrowSchema* file_schema, const int* projection, int n_projection,
+                  char delimiter, int has_header, const char* text, size_t len, b2_batch** out);
 /* Wire compatibility: a serialized `PhysicalPlanNode` (rust/core/proto/ballista.proto:294-422, as the scheduler
  * stores it, rust/scheduler/src/state/mod.rs:149-162) decoded into the operator tree the way the executor does in
  * rust/core/src/serde/physical_plan/from_proto.rs:58-346.  Leaf nodes (CsvScan, ParquetScan, ShuffleReader,

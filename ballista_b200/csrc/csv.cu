@@ -216,8 +216,7 @@ BatchPtr csv_decode(Ctx* ctx, const Schema& file_schema, const std::vector<int>&
     auto tiles = dev_alloc(ctx, (size_t)(n_tiles + 2) * 8);
     csv_count_kernel<<<(unsigned)n_tiles, 256, 0, ctx->stream>>>(text->as<char>(), n, tiles->as<int64_t>());
     B2_LAUNCHED(ctx);
-    scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(tiles->as<int64_t>(), n_tiles);
-    B2_LAUNCHED(ctx);
+    scan_i64(ctx, tiles->as<int64_t>(), n_tiles);
     B2_READBACK(ctx, &n_lines, tiles->as<int64_t>() + n_tiles, 8);
     row_end = dev_alloc(ctx, (size_t)(n_lines + 1) * 8);
     if (n_lines) {

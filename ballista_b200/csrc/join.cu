@@ -141,6 +141,15 @@ __host__ __device__ __forceinline__ uint32_t fmix32(uint32_t h) {
 }
 constexpr int BUCKET = 4;  // slots per bucket (one 32-byte sector)
 __device__ __forceinline__ u64 bucket_of(uint32_t k, u64 bmask) { return (u64)fmix32(k) & bmask; }
+// Bloom word for a key: blocked filter, one 32-bit word per key, 3 bits chosen by a second multiplicative hash so
+// that they are independent of the word index (the low bits of the bucket hash).  Sized at >= 16 bits per build key
+// it stays L2-resident where the 8-byte-slot table (16 B per key at load 0.5) does not, and a probe that misses it
+// (most rows of a selective join: Q3's lineitem side matches ~1%) never touches the table.
+__device__ __forceinline__ uint32_t bloom_bits(uint32_t h) {
+  uint32_t g = h * 0x9E3779B1u;
+  return (1u << (g >> 27)) | (1u << ((g >> 22) & 31u)) | (1u << ((g >> 17) & 31u));
+}
+
 __device__ __forceinline__ u64 ld_slot_volatile(const u64* p) {
   u64 v;
   asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
@@ -231,7 +240,8 @@ __global__ void join_build32_kernel(const int32_t* __restrict__ key, RowPred pre
     if (mask && !mask[i]) continue;
     if (!row_pred(pred, i)) continue;
     uint32_t k = (uint32_t)key[i];
-    u64 b = bucket_of(k, bmask);
+    const uint32_t h = fmix32(k);
+    u64 b = (u64)h & bmask;
     u64 mine = ((u64)k << 32) | (uint32_t)i;
     bool placed = false;
     for (u64 probe = 0; probe <= bmask && !placed; ++probe) {
@@ -260,6 +270,19 @@ __global__ void join_build32_kernel(const int32_t* __restrict__ key, RowPred pre
       }
       b = (b + 1) & bmask;
     }
+  }
+}
+
+// Bloom filter over the build keys, as its own pass before the table build: the filter (<= 4 B per key) stays in L2
+// under the reductions, which it does not when they are interleaved with the table's random 32-byte sector traffic
+__global__ void bloom_build_kernel(const int32_t* __restrict__ key, RowPred pred, const uint8_t* __restrict__ mask, int64_t n,
+                                   uint32_t* bloom, uint32_t wmask) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    if (mask && !mask[i]) continue;
+    if (!row_pred(pred, i)) continue;
+    const uint32_t h = fmix32((uint32_t)key[i]);
+    atomicOr(bloom + (h & wmask), bloom_bits(h));
   }
 }
 
@@ -295,7 +318,15 @@ std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const RowP
   t->slots = dev_alloc(ctx, cap * 8);
   t->next = dev_alloc(ctx, (size_t)(n + 1) * 4);
   B2_CUDA(cudaMemsetAsync(t->slots->ptr, 0xFF, cap * 8, ctx->stream));
+  u64 words = 1024;  // Bloom filter: >= 16 bits per build key, 32-bit blocks
+  while (words * 2 < (u64)n_in) words <<= 1;
+  t->bloom_words = words;
+  t->bloom = dev_alloc(ctx, words * 4);
+  B2_CUDA(cudaMemsetAsync(t->bloom->ptr, 0, words * 4, ctx->stream));
   if (n) {
+    bloom_build_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(key, pred, mask, n, t->bloom->as<uint32_t>(),
+                                                                        (uint32_t)(words - 1));
+    B2_LAUNCHED(ctx);
     join_build32_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(
         key, pred, mask, n, t->slots->as<u64>(), cap / BUCKET - 1, t->next->as<uint32_t>(), t->flags->as<int>());
     B2_LAUNCHED(ctx);
@@ -336,23 +367,41 @@ __device__ __forceinline__ void row_pred_vec(const RowPred& p, int64_t r0, bool*
   }
 }
 
-// Probe-side kernel: filter (inline predicate and / or mask) -> table lookup -> (build_row, probe_row) pairs
-// in PROBE ORDER (the reference's output order).  Three modes, none of which probes a row twice on the
-// primary-key path:
-//   PROBE_STAGE  : pairs of tile t are written, compacted, at [t * JP_TILE, ...) of staging buffers (a tile has
-//                  at most JP_TILE matches when build keys are unique) and tile_cnt[t] = match count; a small
-//                  scan + `join_compact_kernel` then move each tile's run to its final offset.
+// Probe-side kernel: filter (inline predicate and / or mask) -> Bloom test -> table lookup -> (build_row,
+// probe_row) pairs in PROBE ORDER (the reference's output order).  The unit of work is a WARP TILE of JP_WTILE = 256
+// consecutive rows and warps never synchronise with each other:
+//   (1) every lane tests its 8 consecutive rows against the predicate (128-bit loads) and keeps the rows that need a
+//       lookup: a probe side clustered on the key (lineitem: ~4 rows per order) repeats keys in consecutive rows, so a
+//       passing row whose predecessor passed with the same key joins that row's RUN instead of being looked up;
+//   (2) the run heads are compacted, in row order, into the warp's slice of shared memory (one shuffle scan);
+//   (3) the warp walks the compacted heads 32 at a time: Bloom word, and only on a Bloom hit the table bucket; the
+//       matches of a chunk are placed by a second shuffle scan and each lane writes its run.
+// Only the rows that survive a stage pay for the next one: the hash / Bloom arithmetic runs over the compacted
+// heads (13% of lineitem's rows in Q3), the bucket walk over the Bloom hits (~1%).  Three modes, none of which
+// probes a row twice on the primary-key path:
+//   PROBE_STAGE  : pairs of warp tile t are written, compacted, at [t * JP_WTILE, ...) of staging buffers (a tile has
+//                  at most JP_WTILE matches when build keys are unique) and tile_cnt[t] = match count; a scan +
+//                  `join_compact_kernel` then move each tile's run to its final offset.
 //   PROBE_COUNT  : tile_cnt[t] only (build side with duplicate keys: chains are walked to size the output).
 //   PROBE_WRITE  : pairs go straight to tile_cnt[t] (already scanned to offsets) + offset within tile.
 enum { PROBE_STAGE = 0, PROBE_COUNT = 1, PROBE_WRITE = 2 };
+constexpr int JP_WTILE = 32 * JP_ITEMS;
 template <int MODE, bool DUPS>
-__global__ void __launch_bounds__(JP_THREADS)
+__global__ void __launch_bounds__(JP_THREADS, 4)
     join_probe32_kernel(const int32_t* __restrict__ key, RowPred pred, const uint8_t* __restrict__ mask, int64_t n,
-                        bool vec, const u64* __restrict__ slots, u64 bmask, const uint32_t* __restrict__ next,
-                        uint32_t* __restrict__ left_idx, uint32_t* __restrict__ right_idx, int64_t* tile_cnt) {
-  const int64_t n_tiles = (n + JP_TILE - 1) / JP_TILE;
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    int64_t r0 = tile * JP_TILE + (int64_t)threadIdx.x * JP_ITEMS;
+                        bool vec, const u64* __restrict__ slots, u64 bmask, const uint32_t* __restrict__ bloom,
+                        uint32_t wmask, const uint32_t* __restrict__ next, uint32_t* __restrict__ left_idx,
+                        uint32_t* __restrict__ right_idx, int64_t* tile_cnt) {
+  __shared__ uint32_t s_key[JP_TILE];   // run-head keys, row order, one JP_WTILE slice per warp
+  __shared__ uint16_t s_info[JP_TILE];  // run head's row within the warp tile (8 bits) | (run length - 1) << 8
+  const int lane = threadIdx.x & 31;
+  uint32_t* wkey = s_key + (threadIdx.x >> 5) * JP_WTILE;
+  uint16_t* winfo = s_info + (threadIdx.x >> 5) * JP_WTILE;
+  const int64_t n_tiles = (n + JP_WTILE - 1) / JP_WTILE;
+  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t tile = warp0; tile < n_tiles; tile += n_warps) {
+    const int64_t r0 = tile * JP_WTILE + (int64_t)lane * JP_ITEMS;
     uint32_t k[JP_ITEMS];
     bool pass[JP_ITEMS];
     if (vec && r0 + JP_ITEMS <= n) {
@@ -371,77 +420,96 @@ __global__ void __launch_bounds__(JP_THREADS)
         pass[j] = in && (!mask || mask[r0 + j]) && row_pred(pred, r0 + j);
       }
     }
-    uint32_t head[JP_ITEMS];
-    int cnt = 0;
-    // a probe side clustered on the key (lineitem: ~4 rows per order) repeats keys in consecutive rows: a row whose
-    // predecessor passed the filter with the same key inherits its result instead of looking the bucket up again
-    bool need[JP_ITEMS];
-    need[0] = pass[0];
+    // run heads and run lengths within the lane's 8 rows (runs do not continue across lanes: the first row of a lane
+    // is always a head, which costs one extra lookup per lane at most)
+    bool head[JP_ITEMS];
+    int len[JP_ITEMS];
+    head[0] = pass[0];
 #pragma unroll
-    for (int j = 1; j < JP_ITEMS; ++j) need[j] = pass[j] && !(pass[j - 1] && k[j] == k[j - 1]);
+    for (int j = 1; j < JP_ITEMS; ++j) head[j] = pass[j] && !(pass[j - 1] && k[j] == k[j - 1]);
+    len[JP_ITEMS - 1] = 1;
 #pragma unroll
-    for (int g = 0; g < JP_ITEMS; g += 4) {  // four bucket loads (8 x 16 B) in flight per thread
-      ulonglong2 lo[4], hi[4];
-      u64 b[4];
+    for (int j = JP_ITEMS - 2; j >= 0; --j) len[j] = (pass[j + 1] && !head[j + 1]) ? len[j + 1] + 1 : 1;
+    int nh = 0;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        b[j] = bucket_of(k[g + j], bmask);
-        const ulonglong2* bp = reinterpret_cast<const ulonglong2*>(slots + b[j] * BUCKET);
-        if (need[g + j]) {
-          lo[j] = __ldg(bp);
-          hi[j] = __ldg(bp + 1);
-        } else {
-          lo[j] = make_ulonglong2(KEY_EMPTY, KEY_EMPTY);
-          hi[j] = lo[j];
-        }
+    for (int j = 0; j < JP_ITEMS; ++j) nh += head[j];
+    int incl = nh;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    const int n_heads = __shfl_sync(0xffffffffu, incl, 31);
+    int off = incl - nh;
+#pragma unroll
+    for (int j = 0; j < JP_ITEMS; ++j)
+      if (head[j]) {
+        wkey[off] = k[j];
+        winfo[off] = (uint16_t)((lane * JP_ITEMS + j) | ((len[j] - 1) << 8));
+        ++off;
       }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const uint32_t kk = k[g + j];
-        uint32_t hd = NIL;
-        ulonglong2 x = lo[j], y = hi[j];
-        u64 bb = b[j];
-        if (!need[g + j]) {
-          hd = (pass[g + j] && g + j > 0) ? head[g + j > 0 ? g + j - 1 : 0] : NIL;
-        } else
+    __syncwarp();
+    const int64_t base = MODE == PROBE_WRITE ? tile_cnt[tile] : tile * JP_WTILE;
+    int64_t done = 0;  // matches of the chunks before this one
+    for (int c0 = 0; c0 < n_heads; c0 += 32) {
+      const int c = c0 + lane;
+      const bool active = c < n_heads;
+      const uint32_t kk = active ? wkey[c] : 0u;
+      const uint32_t info = active ? winfo[c] : 0u;
+      const uint32_t h = fmix32(kk);
+      const uint32_t bits = bloom_bits(h);
+      const uint32_t word = active ? __ldg(bloom + (h & wmask)) : 0u;
+      uint32_t hd = NIL;
+      if ((word & bits) == bits) {  // inactive lanes: word == 0, never true
+        u64 bb = (u64)h & bmask;
         while (true) {
+          const ulonglong2* bp = reinterpret_cast<const ulonglong2*>(slots + bb * BUCKET);
+          const ulonglong2 x = __ldg(bp), y = __ldg(bp + 1);
           if ((uint32_t)(x.x >> 32) == kk && x.x != KEY_EMPTY) hd = (uint32_t)x.x;
           if ((uint32_t)(x.y >> 32) == kk && x.y != KEY_EMPTY) hd = (uint32_t)x.y;
           if ((uint32_t)(y.x >> 32) == kk && y.x != KEY_EMPTY) hd = (uint32_t)y.x;
           if ((uint32_t)(y.y >> 32) == kk && y.y != KEY_EMPTY) hd = (uint32_t)y.y;
           if (hd != NIL || y.y == KEY_EMPTY) break;  // found, or the bucket has a free slot: key absent
           bb = (bb + 1) & bmask;                      // full bucket without a match: overflow into the next one
-          const ulonglong2* bp = reinterpret_cast<const ulonglong2*>(slots + bb * BUCKET);
-          x = __ldg(bp);
-          y = __ldg(bp + 1);
-        }
-        head[g + j] = hd;
-        if (hd != NIL) {
-          if (DUPS) {
-            for (uint32_t r = hd; r != NIL; r = next[r]) ++cnt;
-          } else {
-            ++cnt;
-          }
         }
       }
-    }
-    int total;
-    int off = block_exclusive_scan(cnt, &total);
-    int64_t base = MODE == PROBE_WRITE ? tile_cnt[tile] : tile * JP_TILE;
-    if (MODE != PROBE_WRITE && threadIdx.x == 0) tile_cnt[tile] = total;
-    if (MODE == PROBE_COUNT || total == 0) continue;
-    int64_t o = base + off;
+      const int run = (int)(info >> 8) + 1;
+      int cnt = 0;
+      if (hd != NIL) {
+        if (DUPS) {
+          int chain = 0;
+          for (uint32_t r = hd; r != NIL; r = next[r]) ++chain;
+          cnt = chain * run;
+        } else {
+          cnt = run;
+        }
+      }
+      if (__ballot_sync(0xffffffffu, cnt != 0) == 0) continue;
+      int inc2 = cnt;
 #pragma unroll
-    for (int j = 0; j < JP_ITEMS; ++j) {
-      uint32_t r = head[j];
-      while (r != NIL) {
-        left_idx[o] = r;
-        right_idx[o] = (uint32_t)(r0 + j);
-        ++o;
-        if (!DUPS) break;
-        r = next[r];
+      for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, inc2, d);
+        if (lane >= d) inc2 += t;
       }
+      const int chunk_total = __shfl_sync(0xffffffffu, inc2, 31);
+      if (MODE != PROBE_COUNT && cnt) {
+        int64_t o = base + done + (inc2 - cnt);
+        const uint32_t row = (uint32_t)(tile * JP_WTILE + (info & 0xFFu));
+        for (int i = 0; i < run; ++i) {  // probe-row major, chain order within a row
+          uint32_t r = hd;
+          do {
+            left_idx[o] = r;
+            right_idx[o] = row + i;
+            ++o;
+            if (!DUPS) break;
+            r = next[r];
+          } while (r != NIL);
+        }
+      }
+      done += chunk_total;
     }
+    if (MODE != PROBE_WRITE && lane == 0) tile_cnt[tile] = done;
+    __syncwarp();  // the warp's slice is rewritten by its next tile
   }
 }
 
@@ -455,7 +523,7 @@ __global__ void join_compact_kernel(const uint32_t* __restrict__ stage_l, const 
   for (int64_t t = w; t < n_tiles; t += nw) {  // one warp per tile: sparse joins have a handful of pairs per tile
     int64_t o = tile_off[t];
     int c = (int)(tile_off[t + 1] - o);
-    int64_t src = t * JP_TILE;
+    int64_t src = t * JP_WTILE;
     for (int i = lane; i < c; i += 32) {
       out_l[o + i] = stage_l[src + i];
       out_r[o + i] = stage_r[src + i];
@@ -474,7 +542,7 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
     *right_idx = dev_alloc(ctx, 4);
     return 0;
   }
-  int64_t n_tiles = (n + JP_TILE - 1) / JP_TILE;
+  int64_t n_tiles = (n + JP_WTILE - 1) / JP_WTILE;
   auto tiles = dev_alloc(ctx, (size_t)(n_tiles + 2) * 8);
   int64_t* tile_cnt = tiles->as<int64_t>();
   bool vec = ((uintptr_t)key & 15) == 0 && ((uintptr_t)mask & 7) == 0;
@@ -488,32 +556,33 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
   int grid = grid_for(ctx, per_sm, n, JP_TILE);
   const u64* slots = t.slots->as<u64>();
   const uint32_t* next = t.next->as<uint32_t>();
+  const uint32_t* bloom = t.bloom->as<uint32_t>();
+  const uint32_t wmask = (uint32_t)(t.bloom_words - 1);
   if (t.dups_known && t.has_dups) {
     join_probe32_kernel<PROBE_COUNT, true><<<grid, JP_THREADS, 0, ctx->stream>>>(key, pred, mask, n, vec, slots,
-                                                                               t.cap / BUCKET - 1, next, nullptr, nullptr, tile_cnt);
+                                                                               t.cap / BUCKET - 1, bloom, wmask, next, nullptr, nullptr, tile_cnt);
     B2_LAUNCHED(ctx);
-    scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(tile_cnt, n_tiles);
-    B2_LAUNCHED(ctx);
+    scan_i64(ctx, tile_cnt, n_tiles);
     B2_READBACK(ctx, &total, tile_cnt + n_tiles, 8);
     if (total >= (int64_t)NIL) fail(B2_ERR_NOT_IMPLEMENTED, "join output beyond 2^32-2 rows in one batch");
     *left_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
     *right_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
     if (total) {
       join_probe32_kernel<PROBE_WRITE, true><<<grid, JP_THREADS, 0, ctx->stream>>>(
-          key, pred, mask, n, vec, slots, t.cap / BUCKET - 1, next, (*left_idx)->as<uint32_t>(), (*right_idx)->as<uint32_t>(),
-          tile_cnt);
+          key, pred, mask, n, vec, slots, t.cap / BUCKET - 1, bloom, wmask, next, (*left_idx)->as<uint32_t>(),
+          (*right_idx)->as<uint32_t>(), tile_cnt);
       B2_LAUNCHED(ctx);
     }
     return total;
   }
   // primary-key build: one probe pass into tile-local staging runs, then scan + compaction of the runs
-  auto stage_l = dev_alloc(ctx, (size_t)n_tiles * JP_TILE * 4);
-  auto stage_r = dev_alloc(ctx, (size_t)n_tiles * JP_TILE * 4);
+  auto stage_l = dev_alloc(ctx, (size_t)n_tiles * JP_WTILE * 4);
+  auto stage_r = dev_alloc(ctx, (size_t)n_tiles * JP_WTILE * 4);
   join_probe32_kernel<PROBE_STAGE, false><<<grid, JP_THREADS, 0, ctx->stream>>>(
-      key, pred, mask, n, vec, slots, t.cap / BUCKET - 1, next, stage_l->as<uint32_t>(), stage_r->as<uint32_t>(), tile_cnt);
+      key, pred, mask, n, vec, slots, t.cap / BUCKET - 1, bloom, wmask, next, stage_l->as<uint32_t>(),
+      stage_r->as<uint32_t>(), tile_cnt);
   B2_LAUNCHED(ctx);
-  scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(tile_cnt, n_tiles);
-  B2_LAUNCHED(ctx);
+  scan_i64(ctx, tile_cnt, n_tiles);
   if (!t.dups_known) {
     int f = 0;
     B2_CUDA(cudaMemcpyAsync(&f, t.flags->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));

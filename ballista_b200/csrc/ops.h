@@ -30,9 +30,12 @@ struct JoinTable {
   BufPtr keys, head, count, next;
   // 32-bit-key variant (join_build32): slots[cap] = (key << 32) | head_row; flags = {dup flag, -, count(8 B)}
   bool k32 = false;
-  BufPtr slots, flags;
+  BufPtr slots, flags, bloom;  // bloom: blocked Bloom filter over the build keys (32-bit words, 3 bits per key)
+  u64 bloom_words = 0;
   bool dups_known = false, has_dups = false;
 };
+// in-place exclusive scan of v[0..n) on the context's stream; v[n] = total (single CTA for short inputs, chunked above)
+void scan_i64(Ctx* ctx, int64_t* v, int64_t n);
 std::shared_ptr<JoinTable> join_build(Ctx* ctx, const Key128* keys, int64_t n);
 // probe: returns number of output pairs; left_idx / right_idx are uint32 row indices in probe order
 int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* probe_keys, int64_t n_probe, BufPtr* left_idx,

@@ -11,6 +11,22 @@
 
 namespace b2 {
 
+void scan_i64(Ctx* ctx, int64_t* v, int64_t n) {
+  if (n <= 4 * SC_CHUNK) {
+    scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(v, n);
+    B2_LAUNCHED(ctx);
+    return;
+  }
+  const int64_t n_chunks = (n + SC_CHUNK - 1) / SC_CHUNK;
+  auto sums = dev_alloc(ctx, (size_t)(n_chunks + 1) * 8);
+  scan_i64_chunk_kernel<<<(unsigned)n_chunks, SC_THREADS, 0, ctx->stream>>>(v, n, sums->as<int64_t>());
+  B2_LAUNCHED(ctx);
+  scan_i64(ctx, sums->as<int64_t>(), n_chunks);
+  scan_i64_add_kernel<<<(unsigned)n_chunks, SC_THREADS, 0, ctx->stream>>>(v, n, sums->as<int64_t>(), n_chunks);
+  B2_LAUNCHED(ctx);
+}
+
+
 __global__ void dest_kernel(const Key128* keys, int64_t n, int n_out, uint8_t* dest) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   for (; i < n; i += (int64_t)gridDim.x * blockDim.x) dest[i] = (uint8_t)(key_hash(keys[i]) % (u64)n_out);
@@ -220,8 +236,7 @@ SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, 
   rp_hist_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(KeySrc{keys, key32}, pred ? *pred : RowPred(), mask, n, n_out,
                                                        st.dest->as<uint8_t>(), st.hist->as<int64_t>(), st.n_tiles);
   B2_LAUNCHED(ctx);
-  scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(st.hist->as<int64_t>(), st.n_tiles * n_out);
-  B2_LAUNCHED(ctx);
+  scan_i64(ctx, st.hist->as<int64_t>(), st.n_tiles * n_out);
   return st;
 }
 // start offset of every destination = scanned hist[d * n_tiles]: gathers the n_out + 1 starts into `out` (device)
@@ -374,8 +389,7 @@ BufPtr radix_sort_order(Ctx* ctx, const std::vector<const u64*>& words, const st
       sort_digit_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(words[k], a->as<uint32_t>(), n, shift, dest->as<uint8_t>(),
                                                               hist->as<int64_t>(), n_tiles);
       B2_LAUNCHED(ctx);
-      scan_i64_kernel<<<1, SC_THREADS, 0, ctx->stream>>>(hist->as<int64_t>(), n_tiles * RP_MAX_OUT);
-      B2_LAUNCHED(ctx);
+      scan_i64(ctx, hist->as<int64_t>(), n_tiles * RP_MAX_OUT);
       rp_scatter_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(dest->as<uint8_t>(), n, RP_MAX_OUT, hist->as<int64_t>(),
                                                               n_tiles, b->as<uint32_t>(), a->as<uint32_t>());
       B2_LAUNCHED(ctx);

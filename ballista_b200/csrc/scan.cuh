@@ -134,6 +134,53 @@ static __global__ void __launch_bounds__(SC_THREADS) scan_i64_kernel(int64_t* v,
   if (threadIdx.x == 0) v[n] = carry_s;
 }
 
+// Multi-CTA form for long inputs (one count per 256-row warp tile of a 600 M-row probe side = 2.3 M values, which the
+// single CTA above would walk in ~290 dependent rounds): CTA b scans chunk b of SC_CHUNK values in place, exclusive and
+// chunk-local, and stores the chunk total in sums[b]; `scan_i64_kernel` then scans the totals, and the add kernel folds
+// each chunk's offset back in and writes v[n] = grand total.  See `scan_i64` (repartition.cu) for the host side.
+constexpr int64_t SC_CHUNK = (int64_t)SC_THREADS * SC_ITEMS;
+static __global__ void __launch_bounds__(SC_THREADS) scan_i64_chunk_kernel(int64_t* v, int64_t n, int64_t* sums) {
+  __shared__ int64_t wsum[SC_THREADS / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int64_t i0 = blockIdx.x * SC_CHUNK + (int64_t)threadIdx.x * SC_ITEMS;
+  int64_t x[SC_ITEMS], s = 0;
+#pragma unroll
+  for (int j = 0; j < SC_ITEMS; ++j) {
+    x[j] = i0 + j < n ? v[i0 + j] : 0;
+    s += x[j];
+  }
+  int64_t incl = s;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    int64_t t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  if (lane == 31) wsum[warp] = incl;
+  __syncthreads();
+  int64_t woff = 0, tot = 0;
+  for (int w = 0; w < SC_THREADS / 32; ++w) {
+    int64_t t = wsum[w];
+    if (w < warp) woff += t;
+    tot += t;
+  }
+  int64_t pre = woff + incl - s;
+#pragma unroll
+  for (int j = 0; j < SC_ITEMS; ++j) {
+    if (i0 + j < n) v[i0 + j] = pre;
+    pre += x[j];
+  }
+  if (threadIdx.x == 0) sums[blockIdx.x] = tot;
+}
+static __global__ void __launch_bounds__(SC_THREADS) scan_i64_add_kernel(int64_t* v, int64_t n, const int64_t* __restrict__ sums,
+                                                                        int64_t n_chunks) {
+  const int64_t add = sums[blockIdx.x];
+  int64_t i0 = blockIdx.x * SC_CHUNK + (int64_t)threadIdx.x * SC_ITEMS;
+#pragma unroll
+  for (int j = 0; j < SC_ITEMS; ++j)
+    if (i0 + j < n) v[i0 + j] += add;
+  if (blockIdx.x == 0 && threadIdx.x == 0) v[n] = sums[n_chunks];
+}
+
 // Out functor receives (i, value, exclusive_prefix)
 template <class In, class Out>
 __global__ void scan_apply_kernel(In in, int64_t n, const int64_t* block_sums, Out out) {

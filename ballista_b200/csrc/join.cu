@@ -131,14 +131,6 @@ int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* pkeys, int64_t n,
 // the filter is never materialised, row ids are those of the unfiltered batch, and output columns are
 // gathered once, for matching rows only (late materialisation).
 // ------------------------------------------------------------------------------------------------------
-__host__ __device__ __forceinline__ uint32_t fmix32(uint32_t h) {
-  h ^= h >> 16;
-  h *= 0x85ebca6bu;
-  h ^= h >> 13;
-  h *= 0xc2b2ae35u;
-  h ^= h >> 16;
-  return h;
-}
 constexpr int BUCKET = 4;  // slots per bucket (one 32-byte sector)
 __device__ __forceinline__ u64 bucket_of(uint32_t k, u64 bmask) { return (u64)fmix32(k) & bmask; }
 // Bloom word for a key: blocked filter, one 32-bit word per key, 3 bits chosen by a second multiplicative hash so

@@ -1,5 +1,5 @@
 // repartition.cu — hash repartition kernels (RepartitionExec(Partitioning::Hash)):
-// destination = hash(packed key) % n_out; a stable, destination-major permutation is built in two passes over
+// destination = part_dest(part_hash(packed key), n_out) (table.cuh); a stable, destination-major permutation is built in two passes over
 // the keys (per-tile histogram -> one scan -> stable scatter of row ids), so every column is then moved by a
 // single gather and each destination's rows are one contiguous slice (the send segment of the all-to-all).
 // Beyond 32 output partitions the permutation falls back to one compaction scan per destination.
@@ -29,7 +29,7 @@ void scan_i64(Ctx* ctx, int64_t* v, int64_t n) {
 
 __global__ void dest_kernel(const Key128* keys, int64_t n, int n_out, uint8_t* dest) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) dest[i] = (uint8_t)(key_hash(keys[i]) % (u64)n_out);
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) dest[i] = (uint8_t)part_dest(part_hash(keys[i]), n_out);
 }
 struct DestIn {
   const uint8_t* dest;
@@ -53,9 +53,7 @@ constexpr uint8_t RP_DROPPED = 255;  // destination byte of a row the fused filt
 struct KeySrc {  // packed 16-byte keys, or a single Int32 / Date32 key column hashed as its packed form
   const Key128* k128;
   const int32_t* k32;
-  __device__ __forceinline__ u64 hash(int64_t i) const {
-    return k128 ? key_hash(k128[i]) : key_hash(Key128{(u64)(uint32_t)k32[i], 0ull});
-  }
+  __device__ __forceinline__ uint32_t hash(int64_t i) const { return k128 ? part_hash(k128[i]) : part_hash((uint32_t)k32[i]); }
 };
 
 // pass 1: destination byte per row + per-tile histogram, stored destination-major (hist[d * n_tiles + tile]) so
@@ -72,7 +70,7 @@ __global__ void __launch_bounds__(RP_THREADS)
       int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
       // rows rejected by the fused FilterExec (byte mask and / or inline predicate) get no destination
       bool live = r < n && (!mask || mask[r]) && row_pred(pred, r);
-      int d = live ? (int)(keys.hash(r) % (u64)n_out) : -1;
+      int d = live ? part_dest(keys.hash(r), n_out) : -1;
       if (r < n) dest[r] = live ? (uint8_t)d : RP_DROPPED;
       unsigned peers = __match_any_sync(0xffffffffu, d);
       if (d >= 0 && (peers & ((1u << (threadIdx.x & 31)) - 1)) == 0) atomicAdd(&h[d], __popc(peers));

@@ -27,6 +27,27 @@ __host__ __device__ __forceinline__ u64 mix64(u64 x) {
 }
 __host__ __device__ __forceinline__ u64 key_hash(const Key128& k) { return mix64(k.lo ^ mix64(k.hi + 0x9E3779B97F4A7C15ull)); }
 
+// 32-bit finaliser (murmur3): the join table's bucket / Bloom hash, and the hash partitioner's
+__host__ __device__ __forceinline__ uint32_t fmix32(uint32_t h) {
+  h ^= h >> 16;
+  h *= 0x85ebca6bu;
+  h ^= h >> 13;
+  h *= 0xc2b2ae35u;
+  h ^= h >> 16;
+  return h;
+}
+// Hash partitioning (RepartitionExec): 32-bit hash and multiply-shift range reduction, 7 integer instructions per row
+// where `key_hash(k) % n` costs two 64-bit mixes and a 64-bit division.  An Int32 / Date32 key column and its packed
+// Key128 form (lo = zero-extended key, hi = 0) hash alike, so both sides of a join co-locate whichever path packed
+// them.  The destination uses the HIGH bits of the hash; the join table built behind the exchange indexes with the
+// low bits, so the keys of one partition still spread over all its buckets.
+__host__ __device__ __forceinline__ uint32_t part_hash(uint32_t k) { return fmix32(k); }
+__host__ __device__ __forceinline__ uint32_t part_hash(const Key128& k) {
+  return fmix32((uint32_t)k.lo ^ (uint32_t)(k.lo >> 32) * 0x85EBCA6Bu ^ (uint32_t)k.hi * 0xC2B2AE35u ^
+                (uint32_t)(k.hi >> 32) * 0x27D4EB2Fu);
+}
+__host__ __device__ __forceinline__ int part_dest(uint32_t h, int n_out) { return (int)(((u64)h * (u64)(uint32_t)n_out) >> 32); }
+
 // ---- streaming (read-once) loads: bypass L1 allocation ----
 __device__ __forceinline__ double2 ld_stream_f64x2(const double* p) {
   double2 r;

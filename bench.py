@@ -50,6 +50,8 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-other", action="store_true", help="skip the other BASELINE configs (Q6 / Q3 at SF10, shuffle)")
     ap.add_argument("--other-sf", type=float, default=10.0)
+    ap.add_argument("--q3-sf", type=float, default=100.0, help="Q3 at the metric's scale: one GPU's own copy at N=1, "
+                    "row-range partitions of one database of this scale (strong scaling) at N>1")
     ap.add_argument("--cpu-seconds", type=float, default=3.0, help="wall-clock target of the cpu_baseline sample")
     return ap.parse_args()
 
@@ -391,7 +393,7 @@ def run_reference(args):
 
 def run_other_configs(args, ctx, env):
     """The other BASELINE.json configs, timed the same way (CUDA events on the library's stream, max over ranks)
-    and reported under "other_configs": Q6 and Q3 at SF10 on one GPU's partition, and at N > 1 the hash-repartition
+    and reported under "other_configs": Q6 and Q3 at SF10 on one GPU's partition, Q3 at SF100 (one GPU's own copy at N = 1), and at N > 1 the hash-repartition
     shuffle of the Q3 lineitem side (l_orderkey, l_extendedprice, l_discount = 20 B/row) over NVLink."""
     import torch.distributed as dist
     from ballista_b200 import MemoryExec, RepartitionExec, _capi, cluster, col, tpch
@@ -440,27 +442,31 @@ def run_other_configs(args, ctx, env):
                                  "note": "the fused scan kernel alone; the rest of the step is fixed per-step overhead"},
                  "path": part.last_path(), "revenue": tab.to_pylist()[0]["revenue"]}
     del li6
-    # ---- Q3 @ SF10: customer |x| orders |x| lineitem + group-by (this rank's partition of all three) ----
-    cu = ctx.tpch("customer", sf, columns=tpch.Q3_CUSTOMER_COLUMNS)
-    od = ctx.tpch("orders", sf, columns=tpch.Q3_ORDERS_COLUMNS)
-    li = ctx.tpch("lineitem", sf, columns=tpch.Q3_LINEITEM_COLUMNS)
+    # ---- Q3 @ SF10 (and, on one GPU, the metric's SF100): customer |x| orders |x| lineitem + group-by over this
+    # rank's own copy of all three tables ----
+    def q3_local(qsf):
+        cu = ctx.tpch("customer", qsf, columns=tpch.Q3_CUSTOMER_COLUMNS)
+        od = ctx.tpch("orders", qsf, columns=tpch.Q3_ORDERS_COLUMNS)
+        li = ctx.tpch("lineitem", qsf, columns=tpch.Q3_LINEITEM_COLUMNS)
 
-    def q3():
-        c, o, l = (tpch.scan(ctx, [[x]]) for x in (cu, od, li))
-        partial = tpch.q3_partial(c, o, l)
-        states = partial.collect_device(0)
-        final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
-        return sum(b.num_rows for b in final.collect_device(0))
-    ms, launches, groups = timeit(q3)
-    rows = cu.num_rows + od.num_rows + li.num_rows
-    scan_bytes = cu.num_bytes + od.num_bytes + li.num_bytes
-    out["q3"] = {"workload": f"TPC-H Q3, SF{sf:g} on each GPU (customer {cu.num_rows} + orders {od.num_rows} + "
-                             f"lineitem {li.num_rows} rows; {scan_bytes / 1e9:.3f} GB of scanned columns)",
-                 "ms_per_step": ms, "input_rows_per_s": rows * world / (ms / 1e3),
-                 "scan_GB_per_s_per_gpu": scan_bytes / (ms / 1e3) / 1e9, "groups": groups, "launches_per_step": launches,
-                 "note": "late materialisation reads only the key / predicate columns of non-matching rows, so "
-                         "scan GB/s is algorithmic bytes / time, not DRAM traffic"}
-    del cu, od
+        def q3():
+            c, o, l = (tpch.scan(ctx, [[x]]) for x in (cu, od, li))
+            partial = tpch.q3_partial(c, o, l)
+            states = partial.collect_device(0)
+            final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
+            return sum(b.num_rows for b in final.collect_device(0))
+        ms, launches, groups = timeit(q3)
+        rows = cu.num_rows + od.num_rows + li.num_rows
+        scan_bytes = cu.num_bytes + od.num_bytes + li.num_bytes
+        return {"workload": f"TPC-H Q3, SF{qsf:g} on each GPU (customer {cu.num_rows} + orders {od.num_rows} + "
+                            f"lineitem {li.num_rows} rows; {scan_bytes / 1e9:.3f} GB of scanned columns)",
+                "ms_per_step": ms, "input_rows_per_s": rows * world / (ms / 1e3),
+                "scan_GB_per_s_per_gpu": scan_bytes / (ms / 1e3) / 1e9, "groups": groups, "launches_per_step": launches,
+                "note": "late materialisation reads only the key / predicate columns of non-matching rows, so "
+                        "scan GB/s is algorithmic bytes / time, not DRAM traffic"}
+    out["q3"] = q3_local(sf)
+    if world == 1 and args.q3_sf > sf:
+        out[f"q3_sf{args.q3_sf:g}"] = q3_local(args.q3_sf)
     # ---- shuffle: RepartitionExec(Hash(l_orderkey), N) with the communicator attached (N > 1) ----
     if world > 1:
         cols = ["l_orderkey", "l_extendedprice", "l_discount"]
@@ -493,8 +499,8 @@ def run_other_configs(args, ctx, env):
                                             "frac_of_measured_peer_copy_770GBps": sent / (pull_ms / 1e3) / 1e9 / 770.0 if pull_ms else None},
                           "note": "ms_per_step is the whole operator (split + metadata + move into the arena + exchange)"}
         del part
-        # ---- Q3 with the shuffle: row-range partitions of an SF(10 x N) database, both join inputs exchanged ----
-        dsf = sf * world
+        # ---- Q3 with the shuffle: row-range partitions of the metric's SF100 database, both join inputs exchanged ----
+        dsf = args.q3_sf
         def tpart(table, columns, align=1):
             total = _capi.lib().b2_tpch_num_rows(table.encode(), float(dsf))
             r0, r1 = cluster.partition_rows(total, world, rank, align=align)
@@ -518,7 +524,6 @@ def run_other_configs(args, ctx, env):
                                  "ms_per_step": ms, "input_rows_per_s": rows_all / (ms / 1e3), "groups_rank0": groups,
                                  "egress_bytes_per_gpu": sent, "launches_per_step": launches}
         del dcu, dod, dli
-    del li
     return out
 
 

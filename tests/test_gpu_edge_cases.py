@@ -120,3 +120,41 @@ def test_sort_empty_single_row_and_presorted(ctx):
     assert SortExec([(col("y"), False)], tpch.scan(ctx, [[b]])).collect()["x"].to_pylist() == [3, 2, 1]
     big = rb(x=np.arange(300_000, dtype=np.int32))
     assert SortExec([(col("x"), False)], tpch.scan(ctx, [[big]])).collect()["x"].to_pylist() == list(range(299_999, -1, -1))
+
+
+@pytest.mark.parametrize("dups", [False, True])
+def test_join_long_clustered_probe_side_against_numpy(ctx, dups):
+    """9 M probe rows clustered on the key in runs of 1..7 (the lineitem shape): more warp tiles than the single-CTA
+    scan takes (chunked scan), runs that inherit their head's lookup, Bloom false positives that the table rejects, and
+    with `dups` a build side whose keys repeat (chain walk, count + write passes).  Checked against a numpy join:
+    same pairs, probe order kept."""
+    from ballista_b200 import HashJoinExec, tpch
+    rng = np.random.default_rng(11 + dups)
+    n_keys = 2_300_000
+    runs = rng.integers(1, 8, n_keys)
+    pk = np.repeat(np.arange(n_keys, dtype=np.int32) * 3 + 1, runs)[:9_000_000]
+    bk = rng.choice(np.arange(n_keys, dtype=np.int32) * 3 + 1, 40_000, replace=False)
+    if dups:
+        bk = np.concatenate([bk, bk[:5000], bk[:50]])
+    bk = np.concatenate([bk, np.array([2, 5, 8], dtype=np.int32)])  # keys the probe side never has
+    left = rb(k=bk, lrow=np.arange(len(bk), dtype=np.int64))
+    right = rb(k2=pk, rrow=np.arange(len(pk), dtype=np.int64))
+    j = HashJoinExec(tpch.scan(ctx, [[left]]), tpch.scan(ctx, [[right]]), [("k", "k2")])
+    t = j.collect(0)
+    lrow, rrow = t["lrow"].to_numpy(), t["rrow"].to_numpy()
+    # numpy statement of the same join: for every probe row in order, every build row with that key
+    order = np.argsort(bk, kind="stable")
+    sk = bk[order]
+    lo, hi = np.searchsorted(sk, pk, "left"), np.searchsorted(sk, pk, "right")
+    cnt = hi - lo
+    assert len(rrow) == int(cnt.sum())
+    want_r = np.repeat(np.arange(len(pk), dtype=np.int64), cnt)
+    assert np.array_equal(rrow, want_r)  # probe order, every row as often as its key occurs on the build side
+    assert np.array_equal(bk[lrow], pk[rrow])
+    # each (probe row, build row) pair exactly once
+    starts = np.repeat(lo, cnt)
+    within = np.arange(len(want_r)) - np.repeat(np.cumsum(cnt) - cnt, cnt)
+    want_l = np.sort((order[starts + within]).reshape(-1))
+    assert np.array_equal(np.sort(lrow), want_l)
+    pair = rrow * (len(bk) + 1) + lrow
+    assert len(np.unique(pair)) == len(pair)

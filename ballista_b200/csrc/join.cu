@@ -379,16 +379,16 @@ __device__ __forceinline__ void row_pred_vec(const RowPred& p, int64_t r0, bool*
 enum { PROBE_STAGE = 0, PROBE_COUNT = 1, PROBE_WRITE = 2 };
 constexpr int JP_WTILE = 32 * JP_ITEMS;
 template <int MODE, bool DUPS>
-__global__ void __launch_bounds__(JP_THREADS, 4)
+__global__ void __launch_bounds__(JP_THREADS, 5)
     join_probe32_kernel(const int32_t* __restrict__ key, RowPred pred, const uint8_t* __restrict__ mask, int64_t n,
                         bool vec, const u64* __restrict__ slots, u64 bmask, const uint32_t* __restrict__ bloom,
                         uint32_t wmask, const uint32_t* __restrict__ next, uint32_t* __restrict__ left_idx,
                         uint32_t* __restrict__ right_idx, int64_t* tile_cnt) {
-  __shared__ uint32_t s_key[JP_TILE];   // run-head keys, row order, one JP_WTILE slice per warp
-  __shared__ uint16_t s_info[JP_TILE];  // run head's row within the warp tile (8 bits) | (run length - 1) << 8
+  // run heads of the warp's tile in row order: key | (row within the tile | (run length - 1) << 8) << 32; rewritten in
+  // place by the hits of step (3): build row | the same info word
+  __shared__ u64 s_ent[JP_TILE];
   const int lane = threadIdx.x & 31;
-  uint32_t* wkey = s_key + (threadIdx.x >> 5) * JP_WTILE;
-  uint16_t* winfo = s_info + (threadIdx.x >> 5) * JP_WTILE;
+  u64* went = s_ent + (threadIdx.x >> 5) * JP_WTILE;
   const int64_t n_tiles = (n + JP_WTILE - 1) / JP_WTILE;
   const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -435,24 +435,18 @@ __global__ void __launch_bounds__(JP_THREADS, 4)
     int off = incl - nh;
 #pragma unroll
     for (int j = 0; j < JP_ITEMS; ++j)
-      if (head[j]) {
-        wkey[off] = k[j];
-        winfo[off] = (uint16_t)((lane * JP_ITEMS + j) | ((len[j] - 1) << 8));
-        ++off;
-      }
+      if (head[j]) went[off++] = (u64)k[j] | ((u64)(uint32_t)((lane * JP_ITEMS + j) | ((len[j] - 1) << 8)) << 32);
     __syncwarp();
-    const int64_t base = MODE == PROBE_WRITE ? tile_cnt[tile] : tile * JP_WTILE;
-    int64_t done = 0;  // matches of the chunks before this one
+    // (3a) Bloom word, then the bucket, for 32 heads at a time; the hits are compacted in place, in row order
+    int n_hits = 0;
     for (int c0 = 0; c0 < n_heads; c0 += 32) {
-      const int c = c0 + lane;
-      const bool active = c < n_heads;
-      const uint32_t kk = active ? wkey[c] : 0u;
-      const uint32_t info = active ? winfo[c] : 0u;
+      const u64 e = c0 + lane < n_heads ? went[c0 + lane] : ~0ull;
+      const uint32_t kk = (uint32_t)e;
       const uint32_t h = fmix32(kk);
       const uint32_t bits = bloom_bits(h);
-      const uint32_t word = active ? __ldg(bloom + (h & wmask)) : 0u;
+      const uint32_t word = c0 + lane < n_heads ? __ldg(bloom + (h & wmask)) : 0u;
       uint32_t hd = NIL;
-      if ((word & bits) == bits) {  // inactive lanes: word == 0, never true
+      if ((word & bits) == bits) {  // lanes past the last head: word == 0, never true
         u64 bb = (u64)h & bmask;
         while (true) {
           const ulonglong2* bp = reinterpret_cast<const ulonglong2*>(slots + bb * BUCKET);
@@ -465,9 +459,22 @@ __global__ void __launch_bounds__(JP_THREADS, 4)
           bb = (bb + 1) & bmask;                      // full bucket without a match: overflow into the next one
         }
       }
+      const unsigned found = __ballot_sync(0xffffffffu, hd != NIL);
+      __syncwarp();  // every lane holds its entry: slots below c0 + 32 may be overwritten
+      if (hd != NIL) went[n_hits + __popc(found & ((1u << lane) - 1u))] = (e & 0xFFFFFFFF00000000ull) | hd;
+      n_hits += __popc(found);
+    }
+    __syncwarp();
+    // (3b) output: 32 hits at a time, placed by a shuffle scan over (run length x chain length)
+    const int64_t base = MODE == PROBE_WRITE ? tile_cnt[tile] : tile * JP_WTILE;
+    int64_t done = 0;  // matches of the chunks before this one
+    for (int c0 = 0; c0 < n_hits; c0 += 32) {
+      const bool active = c0 + lane < n_hits;
+      const u64 e = active ? went[c0 + lane] : 0ull;
+      const uint32_t hd = (uint32_t)e, info = (uint32_t)(e >> 32);
       const int run = (int)(info >> 8) + 1;
       int cnt = 0;
-      if (hd != NIL) {
+      if (active) {
         if (DUPS) {
           int chain = 0;
           for (uint32_t r = hd; r != NIL; r = next[r]) ++chain;
@@ -476,7 +483,6 @@ __global__ void __launch_bounds__(JP_THREADS, 4)
           cnt = run;
         }
       }
-      if (__ballot_sync(0xffffffffu, cnt != 0) == 0) continue;
       int inc2 = cnt;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
@@ -484,7 +490,7 @@ __global__ void __launch_bounds__(JP_THREADS, 4)
         if (lane >= d) inc2 += t;
       }
       const int chunk_total = __shfl_sync(0xffffffffu, inc2, 31);
-      if (MODE != PROBE_COUNT && cnt) {
+      if (MODE != PROBE_COUNT && active) {
         int64_t o = base + done + (inc2 - cnt);
         const uint32_t row = (uint32_t)(tile * JP_WTILE + (info & 0xFFu));
         for (int i = 0; i < run; ++i) {  // probe-row major, chain order within a row

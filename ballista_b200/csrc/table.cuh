@@ -105,7 +105,9 @@ __device__ __forceinline__ u64 table_upsert(const TableRef& t, const Key128& key
     if (key_eq(cur, empty)) {
       Key128 old = atomic_cas_key(&t.keys[h], empty, key);
       if (key_eq(old, empty)) {
-        atomicAdd(t.n_groups, 1);
+        // one counter update per group of lanes that claimed together, not one same-address reduction per claim
+        const unsigned together = __activemask();
+        if ((threadIdx.x & 31) == __ffs(together) - 1) atomicAdd(t.n_groups, __popc(together));
         return h;
       }
       if (key_eq(old, key)) return h;

@@ -266,6 +266,11 @@ struct ProjectionExec : Op {
     }
   };
   StreamPtr execute(int partition) override {
+    // execution-time column pruning: the input materialises only the columns the expressions read (whatever the
+    // parent needs of this operator's output, every expression is evaluated, so `require` from above is not forwarded)
+    std::vector<char> need(children[0]->schema().fields.size(), 0);
+    for (auto& e : exprs) expr_columns(e, need);
+    children[0]->require(need);
     auto s = std::make_unique<S>();
     s->op = this;
     s->in = children[0]->execute(partition);

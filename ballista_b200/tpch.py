@@ -12,7 +12,7 @@ import pyarrow as pa
 from . import _capi as K
 from .expr import avg, col, count, date, lit, sum as sum_
 from .plan import (CoalesceBatchesExec, FilterExec, GlobalLimitExec, HashAggregateExec, HashJoinExec, MemoryExec,
-                   MergeExec, RepartitionExec, SortExec)
+                   MergeExec, ProjectionExec, RepartitionExec, SortExec)
 
 Q1_COLUMNS = ["l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_returnflag", "l_linestatus", "l_shipdate"]
 Q6_COLUMNS = ["l_quantity", "l_extendedprice", "l_discount", "l_shipdate"]
@@ -117,6 +117,40 @@ def q3_distributed_partial(customer, orders, lineitem, nranks, **kw):
     states of different ranks hold disjoint groups and each rank finalises its own (no further exchange)."""
     return HashAggregateExec("Partial", q3_groups(), q3_aggregates(),
                              q3_distributed_join_tree(customer, orders, lineitem, nranks, **kw))
+
+
+def q3_broadcast_stages(ctx, customer, orders, lineitem, nranks, segment="BUILDING", cutoff="1995-03-15"):
+    """Q3 over row-range partitions with BROADCAST build sides: the reference's own join is collect-left
+    (`HashJoinExec` builds over `MergeExec(left)`), which across ranks is an all-gather of the filtered
+    build side; the probe side (orders, then lineitem: 98 % of the bytes) never leaves its GPU.  Run as Ballista runs
+    stages, each stage's output materialised and handed to the next:
+      1  Filter(customer) -> c_custkey                                   -> all-gather
+      2  HashJoin(stage 1, Filter(orders)) -> order key / date / priority -> all-gather
+      3  HashJoin(stage 2, Filter(lineitem)) -> Partial aggregate -> Repartition(Hash(group keys), N)
+      4  Final aggregate of this rank's groups (the caller: `q3_final`)
+    Returns (partial_states_op, input_schema_for_final): the states of this rank's partition of the groups."""
+    pc, po, pl = _q3_predicates(segment, cutoff)
+    rank = ctx.rank if nranks > 1 else 0
+
+    def gather(plan):
+        got = CoalesceBatchesExec(plan, (1 << 31) - 2).collect_device(0)
+        if len(got) > 1:
+            raise RuntimeError("a broadcast stage produced more than one batch")
+        if not got:  # every rank joins the collective, with an empty batch if it has no rows
+            got = [ctx.upload(pa.RecordBatch.from_pylist([], schema=plan.schema()))]
+        if nranks > 1:
+            got = [ctx.allgather(got[0])]
+        return MemoryExec(ctx, plan.schema(), [got])
+    s1 = gather(ProjectionExec([col("c_custkey")], CoalesceBatchesExec(FilterExec(pc, customer))))
+    j1 = HashJoinExec(s1, CoalesceBatchesExec(FilterExec(po, orders)), [("c_custkey", "o_custkey")])
+    s2 = gather(ProjectionExec([col("o_orderkey"), col("o_orderdate"), col("o_shippriority")], CoalesceBatchesExec(j1)))
+    j2 = CoalesceBatchesExec(HashJoinExec(s2, CoalesceBatchesExec(FilterExec(pl, lineitem)), [("o_orderkey", "l_orderkey")]))
+    partial = HashAggregateExec("Partial", q3_groups(), q3_aggregates(), j2)
+    if nranks == 1:
+        return partial, j2.schema(), 0
+    # a group (one order) can straddle two lineitem row ranges: co-locate the states by group key before the Final
+    names = [f.name for f in partial.schema()]
+    return RepartitionExec(partial, "Hash", nranks, [col(names[0])]), j2.schema(), rank
 
 
 @functools.lru_cache(maxsize=None)

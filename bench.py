@@ -523,6 +523,22 @@ def run_other_configs(args, ctx, env):
                                              "inputs hash-repartitioned over NVLink (filters fused into the split)",
                                  "ms_per_step": ms, "input_rows_per_s": rows_all / (ms / 1e3), "groups_rank0": groups,
                                  "egress_bytes_per_gpu": sent, "launches_per_step": launches}
+        # ---- the same query and partitions with BROADCAST build sides (the reference's collect-left join across
+        # ranks): filtered customers and the first join's output are all-gathered, lineitem / orders never move,
+        # partial states are exchanged by group key ----
+        def q3b():
+            scans = [tpch.scan(ctx, [[x]]) for x in (dcu, dod, dli)]
+            partial, in_schema, p = tpch.q3_broadcast_stages(ctx, *scans, world)
+            states = partial.collect_device(p)
+            final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), in_schema)
+            return sum(b.num_rows for b in final.collect_device(0))
+        sent0 = ctx.comm_bytes_sent()
+        ms, launches, groups = timeit(q3b, steps=10, warmup=3)
+        sent = (ctx.comm_bytes_sent() - sent0) / 13.0
+        out["q3_broadcast"] = {"workload": f"TPC-H Q3 over an SF{dsf:g} database in {world} row-range partitions, build sides "
+                                           "all-gathered (collect-left), probe sides local, partial states exchanged by group key",
+                               "ms_per_step": ms, "input_rows_per_s": rows_all / (ms / 1e3), "groups_rank0": groups,
+                               "egress_bytes_per_gpu": sent, "launches_per_step": launches}
         del dcu, dod, dli
     return out
 

@@ -12,6 +12,7 @@ ctx = b2.Context(local_rank)
 cluster.attach_communicator(ctx, dist, rank, world)
 sf = float(sys.argv[1]) if len(sys.argv) > 1 else 20.0
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 10
+mode = sys.argv[3] if len(sys.argv) > 3 else "repartition"
 def part(table, columns, align=1):
     n = b2._capi.lib().b2_tpch_num_rows(table.encode(), sf)
     r0, r1 = cluster.partition_rows(n, world, rank, align=align)
@@ -19,9 +20,14 @@ def part(table, columns, align=1):
 cu, od, li = part("customer", tpch.Q3_CUSTOMER_COLUMNS), part("orders", tpch.Q3_ORDERS_COLUMNS), part("lineitem", tpch.Q3_LINEITEM_COLUMNS, 32)
 def step():
     scans = [tpch.scan(ctx, [[x]]) for x in (cu, od, li)]
-    partial = tpch.q3_distributed_partial(*scans, world)
-    states = partial.collect_device(rank)
-    final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
+    if mode == "broadcast":
+        partial, in_schema, p = tpch.q3_broadcast_stages(ctx, *scans, world)
+        states = partial.collect_device(p)
+        final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), in_schema)
+    else:
+        partial = tpch.q3_distributed_partial(*scans, world)
+        states = partial.collect_device(rank)
+        final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
     return sum(b.num_rows for b in final.collect_device(0))
 for _ in range(3): g = step()
 dist.barrier(); ctx.synchronize()
@@ -31,7 +37,7 @@ for _ in range(steps): g = step()
 ctx.synchronize(); dt = (time.perf_counter() - t) / steps
 dist.barrier()
 if rank == 0:
-    print(f"Q3 distributed SF{sf:g} on {world} GPUs: {dt*1e3:.2f} ms/step, groups(rank0) {g}, launches/step {(ctx.kernel_launches()-l0)/steps}", flush=True)
+    print(f"Q3 distributed [{mode}] SF{sf:g} on {world} GPUs: {dt*1e3:.2f} ms/step, groups(rank0) {g}, launches/step {(ctx.kernel_launches()-l0)/steps}", flush=True)
 del cu, od, li; gc.collect()
 ctx.close()
 dist.destroy_process_group()

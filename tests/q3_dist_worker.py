@@ -37,9 +37,14 @@ def run(sf, mode):
     od = part("orders", sf, tpch.Q3_ORDERS_COLUMNS)
     li = part("lineitem", sf, tpch.Q3_LINEITEM_COLUMNS, align=32)
     scans = [tpch.scan(ctx, [[x]]) for x in (cu, od, li)]
-    partial = tpch.q3_distributed_partial(*scans, world)
-    states = partial.collect_device(rank)
-    final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
+    if mode == "broadcast":  # collect-left build sides all-gathered, probe sides stay put, states exchanged by group key
+        partial, in_schema, p = tpch.q3_broadcast_stages(ctx, *scans, world)
+        states = partial.collect_device(p)
+        final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), in_schema)
+    else:
+        partial = tpch.q3_distributed_partial(*scans, world)
+        states = partial.collect_device(rank)
+        final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
     got = final.collect().to_pylist()
     for r in got:
         r["o_orderdate"] = (r["o_orderdate"] - datetime.date(1970, 1, 1)).days
@@ -62,6 +67,8 @@ def run(sf, mode):
 run(0.02, "p2p")
 run(0.02, "nccl")
 run(0.2, "p2p")
+run(0.02, "broadcast")
+run(0.2, "broadcast")
 ctx.synchronize()
 if rank == 0:
     print("q3_dist: all ok")

@@ -133,15 +133,6 @@ int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* pkeys, int64_t n,
 // ------------------------------------------------------------------------------------------------------
 constexpr int BUCKET = 4;  // slots per bucket (one 32-byte sector)
 __device__ __forceinline__ u64 bucket_of(uint32_t k, u64 bmask) { return (u64)fmix32(k) & bmask; }
-// Bloom word for a key: blocked filter, one 32-bit word per key, 3 bits chosen by a second multiplicative hash so
-// that they are independent of the word index (the low bits of the bucket hash).  Sized at >= 16 bits per build key
-// it stays L2-resident where the 8-byte-slot table (16 B per key at load 0.5) does not, and a probe that misses it
-// (most rows of a selective join: Q3's lineitem side matches ~1%) never touches the table.
-__device__ __forceinline__ uint32_t bloom_bits(uint32_t h) {
-  uint32_t g = h * 0x9E3779B1u;
-  return (1u << (g >> 27)) | (1u << ((g >> 22) & 31u)) | (1u << ((g >> 17) & 31u));
-}
-
 __device__ __forceinline__ u64 ld_slot_volatile(const u64* p) {
   u64 v;
   asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));

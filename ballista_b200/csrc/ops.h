@@ -23,6 +23,17 @@ BatchPtr tpch_generate(Ctx* ctx, const std::string& table, double sf, int64_t ro
 int64_t tpch_num_rows(const std::string& table, double sf);
 
 // join.cu
+// Bloom filters of a partitioned join's build keys, one per destination rank (filter d covers the build keys that
+// live on rank d; word = fmix32(key) & wmask[d], bits = bloom_bits).  The probe side's hash split tests every row
+// against the filter of its destination and gives the row no destination on a miss: rows that cannot match never
+// cross NVLink (Q3: ~98 % of the lineitem rows that pass the date filter).
+struct SemiFilter {
+  BufPtr words;          // n filters, `stride` 32-bit words apart
+  uint32_t stride = 0;
+  uint32_t wmask[32] = {0};
+  int n = 0;
+};
+
 struct JoinTable {
   Ctx* ctx;
   u64 cap = 0;
@@ -75,7 +86,8 @@ struct SplitState {
   int n_out = 0;
 };
 SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
-                            const RowPred* pred = nullptr, const uint8_t* mask = nullptr);
+                            const RowPred* pred = nullptr, const uint8_t* mask = nullptr,
+                            const SemiFilter* semi = nullptr);
 void hash_split_starts_device(Ctx* ctx, const SplitState& st, int64_t* out_dev);  // n_out + 1 slice starts
 void hash_split_counts(Ctx* ctx, const SplitState& st, std::vector<int64_t>* counts);
 BufPtr hash_split_perm(Ctx* ctx, const SplitState& st);
@@ -123,6 +135,10 @@ struct Op {
   // read (empty = all).  Operators that assemble their output by gathers (HashJoinExec) leave the others
   // elided (Column::data == nullptr); the schema is unchanged.  Default: children produce everything.
   virtual void require(const std::vector<char>& need) { (void)need; }
+  // Semi-join reduction across an exchange (see SemiFilter): a partitioned hash join offers the Bloom filters of
+  // its build partitions to its probe-side child; only a hash RepartitionExec on exactly that key column accepts
+  virtual bool accepts_semi_filter(int key_col) const { (void)key_col; return false; }
+  virtual void set_semi_filter(std::shared_ptr<SemiFilter> f) { (void)f; }
   // true when output partition r exists only on rank r (the plan sits above an exchange): consumers then
   // execute their own rank's partition instead of iterating over all of them
   virtual bool per_rank_partitions() const { return !children.empty() && children[0]->per_rank_partitions(); }

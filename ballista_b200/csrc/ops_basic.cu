@@ -154,6 +154,8 @@ struct CoalesceExec : Op {
   const char* name() const override { return "CoalesceBatchesExec"; }
   Schema schema() const override { return children[0]->schema(); }
   void require(const std::vector<char>& need) override { children[0]->require(need); }
+  bool accepts_semi_filter(int key_col) const override { return children[0]->accepts_semi_filter(key_col); }
+  void set_semi_filter(std::shared_ptr<SemiFilter> f) override { children[0]->set_semi_filter(std::move(f)); }
   struct S : Stream {
     CoalesceExec* op;
     StreamPtr in;

@@ -3,6 +3,7 @@
 // Constructed where from_proto.rs:253-276 and :133-164 construct the DataFusion operators.
 #include <cstdlib>
 
+#include "comm.h"
 #include "ops.h"
 
 namespace b2 {
@@ -39,6 +40,7 @@ struct HashJoinExec : Op {
   BatchPtr left_batch;
   std::shared_ptr<JoinTable> table;
   BufPtr left_keys;
+  bool semi_offered = false;
 
   const char* name() const override { return "HashJoinExec"; }
   Schema schema() const override { return out; }
@@ -147,8 +149,38 @@ struct HashJoinExec : Op {
       return o;
     }
   };
+  // Partitioned join over an exchange: publish the Bloom filter of this rank's build partition to every rank, so the
+  // probe side's split drops, before the exchange, the rows whose destination cannot hold their key.  Collective:
+  // every rank runs the same plan and takes the same branch.
+  void offer_semi_filter() {
+    if (semi_offered || !k32 || !table || !ctx->comm || ctx->nranks < 2 || getenv("B2_DISABLE_SEMI_FILTER")) return;
+    semi_offered = true;
+    Op* l = children[0].get();
+    ExprPtr unused;
+    if (fuse()) l = peel_filter(l, &unused);
+    if (!l->per_rank_partitions() || !children[1]->accepts_semi_filter(on_right[0])) return;
+    const int nr = ctx->nranks;
+    std::vector<int64_t> words = allgather_counts(ctx, std::vector<int64_t>{(int64_t)table->bloom_words});
+    int64_t stride = 0;
+    for (int64_t w : words) stride = std::max(stride, w);
+    auto f = std::make_shared<SemiFilter>();
+    f->n = nr;
+    f->stride = (uint32_t)stride;
+    for (int r = 0; r < nr; ++r) f->wmask[r] = (uint32_t)(words[r] - 1);
+    BufPtr send = table->bloom;
+    if ((int64_t)table->bloom_words < stride) {
+      send = dev_alloc_zero(ctx, (size_t)stride * 4);
+      B2_CUDA(cudaMemcpyAsync(send->ptr, table->bloom->ptr, (size_t)table->bloom_words * 4, cudaMemcpyDeviceToDevice,
+                              ctx->stream));
+    }
+    f->words = dev_alloc(ctx, (size_t)stride * 4 * nr);
+    B2_NCCL(ncclAllGather(send->ptr, f->words->ptr, (size_t)stride, ncclUint32, ctx->comm->nccl, ctx->stream));
+    ctx->bytes_sent += stride * 4 * (nr - 1);
+    children[1]->set_semi_filter(f);
+  }
   StreamPtr execute(int partition) override {
     build(partition);
+    offer_semi_filter();
     auto s = std::make_unique<S>();
     s->op = this;
     Op* r = children[1].get();
@@ -215,7 +247,14 @@ struct RepartitionExec : Op {
     *s = scheme;
     *n = n_out;
   }
+  std::shared_ptr<SemiFilter> semi;            // Bloom filters of the join this exchange feeds (probe side), or null
   bool exchange_mode() const { return scheme == B2_PART_HASH && ctx->comm && n_out == ctx->nranks; }
+  bool accepts_semi_filter(int key_col) const override {
+    if (computed || !exchange_mode() || n_out > 32 || keys.size() != 1) return false;
+    const Expr& k = *keys[0];
+    return k.kind == B2_EXPR_COLUMN && k.col == key_col && (k.dtype == B2_INT32 || k.dtype == B2_DATE32);
+  }
+  void set_semi_filter(std::shared_ptr<SemiFilter> f) override { semi = std::move(f); }
   bool per_rank_partitions() const override { return exchange_mode(); }
   // a FilterExec below a hash repartition rides in the split kernels (rows it rejects get no destination)
   bool fuse() const { return scheme == B2_PART_HASH && n_out <= 32 && !getenv("B2_DISABLE_FUSION"); }
@@ -252,7 +291,7 @@ struct RepartitionExec : Op {
     const uint8_t* m = mask.data ? mask.values<uint8_t>() : nullptr;
     if (kc.size() == 1 && (kc[0].dtype == B2_INT32 || kc[0].dtype == B2_DATE32)) {
       // one Int32 key: hashed straight from the column (same value as its packed form), nothing materialised
-      return hash_split_begin(ctx, nullptr, kc[0].values<int32_t>(), b.num_rows, n_out, &rp, m);
+      return hash_split_begin(ctx, nullptr, kc[0].values<int32_t>(), b.num_rows, n_out, &rp, m, semi.get());
     }
     BufPtr stt = dev_alloc_zero(ctx, 16);
     BufPtr pk = pack_keys(ctx, layout, kc, b.num_rows, stt->as<int>());

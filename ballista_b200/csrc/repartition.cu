@@ -58,8 +58,13 @@ struct KeySrc {  // packed 16-byte keys, or a single Int32 / Date32 key column h
 
 // pass 1: destination byte per row + per-tile histogram, stored destination-major (hist[d * n_tiles + tile]) so
 // that ONE exclusive scan of the whole array yields every (destination, tile) output offset
+struct SemiArgs {  // device view of a SemiFilter (ops.h); words == nullptr: no filter
+  const uint32_t* words;
+  uint32_t stride;
+  uint32_t wmask[RP_MAX_OUT];
+};
 __global__ void __launch_bounds__(RP_THREADS)
-    rp_hist_kernel(KeySrc keys, RowPred pred, const uint8_t* __restrict__ mask, int64_t n, int n_out,
+    rp_hist_kernel(KeySrc keys, RowPred pred, const uint8_t* __restrict__ mask, SemiArgs semi, int64_t n, int n_out,
                    uint8_t* __restrict__ dest, int64_t* __restrict__ hist, int64_t n_tiles) {
   __shared__ int h[RP_MAX_OUT];
   for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -70,7 +75,18 @@ __global__ void __launch_bounds__(RP_THREADS)
       int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
       // rows rejected by the fused FilterExec (byte mask and / or inline predicate) get no destination
       bool live = r < n && (!mask || mask[r]) && row_pred(pred, r);
-      int d = live ? part_dest(keys.hash(r), n_out) : -1;
+      int d = -1;
+      if (live) {
+        const uint32_t h = keys.hash(r);
+        d = part_dest(h, n_out);
+        if (semi.words) {  // semi-join reduction: the destination's build side cannot hold this key
+          const uint32_t bits = bloom_bits(h);
+          if ((__ldg(semi.words + (size_t)d * semi.stride + (h & semi.wmask[d])) & bits) != bits) {
+            d = -1;
+            live = false;
+          }
+        }
+      }
       if (r < n) dest[r] = live ? (uint8_t)d : RP_DROPPED;
       unsigned peers = __match_any_sync(0xffffffffu, d);
       if (d >= 0 && (peers & ((1u << (threadIdx.x & 31)) - 1)) == 0) atomicAdd(&h[d], __popc(peers));
@@ -220,7 +236,7 @@ __global__ void __launch_bounds__(RP_THREADS)
 
 // ---- host side: phase 1 (destinations, histogram, scan: no host sync), then counts / permutation / column move ----
 SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
-                            const RowPred* pred, const uint8_t* mask) {
+                            const RowPred* pred, const uint8_t* mask, const SemiFilter* semi) {
   if (n_out < 1 || n_out > RP_MAX_OUT) fail(B2_ERR_INVALID_ARG, "hash_split_begin supports 1..32 output partitions");
   if (n >= (1ll << 32) - 1) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
   SplitState st;
@@ -231,7 +247,14 @@ SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, 
   st.hist = dev_alloc_zero(ctx, (size_t)(st.n_tiles * n_out + 2) * 8);
   if (n == 0) return st;
   int grid = grid_for(ctx, 8, n, RP_TILE);
-  rp_hist_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(KeySrc{keys, key32}, pred ? *pred : RowPred(), mask, n, n_out,
+  SemiArgs sa{nullptr, 0, {0}};
+  if (semi) {
+    if (semi->n != n_out) fail(B2_ERR_EXECUTION, "internal: semi-join filter does not match the exchange width");
+    sa.words = semi->words->as<uint32_t>();
+    sa.stride = semi->stride;
+    for (int d = 0; d < n_out; ++d) sa.wmask[d] = semi->wmask[d];
+  }
+  rp_hist_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(KeySrc{keys, key32}, pred ? *pred : RowPred(), mask, sa, n, n_out,
                                                        st.dest->as<uint8_t>(), st.hist->as<int64_t>(), st.n_tiles);
   B2_LAUNCHED(ctx);
   scan_i64(ctx, st.hist->as<int64_t>(), st.n_tiles * n_out);

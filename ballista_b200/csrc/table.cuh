@@ -36,6 +36,15 @@ __host__ __device__ __forceinline__ uint32_t fmix32(uint32_t h) {
   h ^= h >> 16;
   return h;
 }
+// Bloom word for a key: blocked filter, one 32-bit word per key, 3 bits chosen by a second multiplicative hash so
+// that they are independent of the word index (the low bits of the bucket hash).  Sized at >= 16 bits per build key
+// it stays L2-resident where the 8-byte-slot table (16 B per key at load 0.5) does not, and a probe that misses it
+// (most rows of a selective join: Q3's lineitem side matches ~1%) never touches the table.
+__device__ __forceinline__ uint32_t bloom_bits(uint32_t h) {
+  uint32_t g = h * 0x9E3779B1u;
+  return (1u << (g >> 27)) | (1u << ((g >> 22) & 31u)) | (1u << ((g >> 17) & 31u));
+}
+
 // Hash partitioning (RepartitionExec): 32-bit hash and multiply-shift range reduction, 7 integer instructions per row
 // where `key_hash(k) % n` costs two 64-bit mixes and a 64-bit division.  An Int32 / Date32 key column and its packed
 // Key128 form (lo = zero-extended key, hi = 0) hash alike, so both sides of a join co-locate whichever path packed

@@ -93,7 +93,7 @@ void hash_split_counts(Ctx* ctx, const SplitState& st, std::vector<int64_t>* cou
 BufPtr hash_split_perm(Ctx* ctx, const SplitState& st);
 // moves fixed-width columns to dst[c] + base[c * n_out + d] + k * width[c] (k = rank inside destination d's slice)
 void hash_split_move(Ctx* ctx, const SplitState& st, int n_cols, const void* const* src, void* const* dst,
-                     const int* width, const int64_t* base_dev, uint32_t* perm_or_null);
+                     const int* width, const int64_t* base_dev, uint32_t* perm_or_null, int64_t n_live = -1);
 
 // SortExec support (repartition.cu): order-preserving 64-bit key words per sort column, stable LSD radix sort
 void sort_key_words(Ctx* ctx, const Column& c, bool descending, std::vector<BufPtr>* words, std::vector<int>* bits,

@@ -346,7 +346,7 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
       for (size_t g = 0; g < src.size(); g += 8) {
         int k = (int)std::min<size_t>(8, src.size() - g);
         hash_split_move(ctx, st, k, src.data() + g, dst.data() + g, width.data() + g, dbase->as<int64_t>() + g * nr,
-                        nullptr);
+                        nullptr, all[(size_t)me * L + AW + nr]);  // my surviving rows: picks the sparse move kernel
       }
     }
   }

@@ -61,6 +61,41 @@ def run(sf, rows_per_rank, mode):
     dist.barrier()
 
 
+def run_filtered(sf, rows_per_rank, cutoff, label):
+    """A FilterExec directly below the repartition rides in the split kernels.  `cutoff` picks the density of the
+    survivors: most rows (dense move kernel) or under one in eight (sparse move kernel); same contract either way."""
+    import datetime
+    import pyarrow as pa
+    from ballista_b200 import CoalesceBatchesExec, FilterExec, date
+    os.environ.pop("B2_SHUFFLE", None)
+    n = rows_per_rank + 777 * rank
+    r0 = rank * (rows_per_rank + 5000)
+    part = ctx.tpch("lineitem", sf, r0, r0 + n, columns=cols)
+    day = (datetime.date.fromisoformat(cutoff) - datetime.date(1970, 1, 1)).days
+    mine = [r for r in rows_of(pa.Table.from_batches([part.to_arrow()]))
+            if (r[3] - datetime.date(1970, 1, 1)).days > day]
+    rep = RepartitionExec(CoalesceBatchesExec(FilterExec(col("l_shipdate") > date(cutoff), tpch.scan(ctx, [[part]]))),
+                          "Hash", world, [col("l_orderkey")])
+    got_rows = rows_of(rep.collect(rank))
+    path = rep.last_path()
+    gathered_in, gathered_out = [None] * world, [None] * world
+    dist.all_gather_object(gathered_in, mine)
+    dist.all_gather_object(gathered_out, got_rows)
+    if rank == 0:
+        owner = {}
+        for q, rows in enumerate(gathered_out):
+            for r in rows:
+                assert owner.setdefault(r[0], q) == q, f"{label}: key {r[0]} on two ranks"
+        assert sorted(r for q in gathered_in for r in q) == sorted(r for q in gathered_out for r in q), label
+        for q, rows in enumerate(gathered_out):
+            want = [r for s in range(world) for r in gathered_in[s] if owner[r[0]] == q]
+            assert rows == want, f"{label}: row order inside partition {q} differs"
+        kept = sum(len(q) for q in gathered_in)
+        print(f"ok [filtered:{label}] path={path} kept {kept} of ~{world * n} rows", flush=True)
+    assert path == "nvlink-peer-pull+fused-filter", path
+    dist.barrier()
+
+
 def check_allgather(sf, n):
     """b2_comm_allgather_batch: rank-ordered concatenation, small-slot protocol (n <= 256) and general protocol."""
     import pyarrow as pa
@@ -81,6 +116,9 @@ for mode in ("p2p", "nccl", "p2p"):
     run(sf0, 20_000, mode)
 run(0.1 * world, 150_000, "p2p")   # arena regrow
 run(sf0, 3_000, "p2p")             # smaller again: arena reused
+run_filtered(sf0, 20_000, "1993-01-01", "dense")    # ~85 % of the rows survive
+run_filtered(sf0, 20_000, "1998-06-01", "sparse")   # ~7 %: the sparse move kernel
+run_filtered(sf0, 20_000, "1999-01-01", "none")     # nothing survives
 check_allgather(sf0, 4)
 check_allgather(sf0, 256 - world)
 check_allgather(sf0, 3000)

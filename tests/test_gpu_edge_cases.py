@@ -158,3 +158,42 @@ def test_join_long_clustered_probe_side_against_numpy(ctx, dups):
     assert np.array_equal(np.sort(lrow), want_l)
     pair = rrow * (len(bk) + 1) + lrow
     assert len(np.unique(pair)) == len(pair)
+
+
+def test_join_two_column_and_string_keys_general_path(ctx):
+    """The packed-key join (any key shape that is not one Int32 column): Q5's two-column key
+    (l_suppkey = s_suppkey AND c_nationkey = s_nationkey, q5.sql:11-12), an Int64 key and a Utf8 key, with duplicate
+    build keys; pairs and probe order against a dictionary join."""
+    from ballista_b200 import HashJoinExec, tpch
+    rng = np.random.default_rng(23)
+    nb, npr = 3_000, 40_000
+    b_supp = rng.integers(0, 500, nb).astype(np.int32)
+    b_nat = rng.integers(0, 25, nb).astype(np.int32)
+    p_supp = rng.integers(0, 600, npr).astype(np.int32)
+    p_nat = rng.integers(0, 25, npr).astype(np.int32)
+
+    def check(left, right, on, lkey, rkey):
+        j = HashJoinExec(tpch.scan(ctx, [[left]]), tpch.scan(ctx, [[right.slice(0, 17_001), right.slice(17_001)]]), on)
+        assert "key128" in (j.collect_device(0) and j.last_path())
+        t = j.collect(0)
+        build = {}
+        for i, k in enumerate(lkey):
+            build.setdefault(k, []).append(i)
+        want = [(i, r) for r, k in enumerate(rkey) for i in build.get(k, [])]
+        got = list(zip(t["lrow"].to_pylist(), t["rrow"].to_pylist()))
+        assert [r for _, r in got] == [r for _, r in want]          # probe order
+        assert sorted(got) == sorted(want)                            # every pair exactly once
+
+    left = rb(s_suppkey=b_supp, s_nationkey=b_nat, lrow=np.arange(nb, dtype=np.int64))
+    right = rb(l_suppkey=p_supp, c_nationkey=p_nat, rrow=np.arange(npr, dtype=np.int64))
+    check(left, right, [("s_suppkey", "l_suppkey"), ("s_nationkey", "c_nationkey")],
+          list(zip(b_supp.tolist(), b_nat.tolist())), list(zip(p_supp.tolist(), p_nat.tolist())))
+    # Int64 key with values beyond 32 bits
+    b64 = (b_supp.astype(np.int64) << 33) + b_nat
+    p64 = (p_supp.astype(np.int64) << 33) + p_nat
+    check(rb(k=b64, lrow=np.arange(nb, dtype=np.int64)), rb(k2=p64, rrow=np.arange(npr, dtype=np.int64)), [("k", "k2")],
+          b64.tolist(), p64.tolist())
+    # Utf8 key
+    bs = [f"n{a}-{b}" for a, b in zip(b_supp.tolist(), b_nat.tolist())]
+    ps = [f"n{a}-{b}" for a, b in zip(p_supp.tolist(), p_nat.tolist())]
+    check(rb(k=bs, lrow=np.arange(nb, dtype=np.int64)), rb(k2=ps, rrow=np.arange(npr, dtype=np.int64)), [("k", "k2")], bs, ps)

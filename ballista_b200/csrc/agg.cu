@@ -108,6 +108,7 @@ void AggRunner::ensure_main(int64_t extra) {
 
 void AggRunner::consume(const AggLaunch& l, int64_t n) {
   if (n <= 0) return;
+  groups_exact = false;
   int host[4] = {0, 0, 0, 0};
   if (!force_global) {
     if (narrow_overflowed && l.small_wide) {
@@ -154,6 +155,7 @@ void AggRunner::consume(const AggLaunch& l, int64_t n) {
     B2_READBACK(ctx, &host[1], main->n_groups->ptr, 4);
     check_status(host[0]);
     group_bound = host[1];
+    groups_exact = true;  // status checked and the count read after the last kernel on the table
   }
 }
 
@@ -169,10 +171,13 @@ __global__ void table_compact_kernel(const Key128* keys, u64 cap, uint32_t* slot
 
 int64_t AggRunner::finish(BufPtr* slots_out) {
   int host[2] = {0, 0};
-  B2_CUDA(cudaMemcpyAsync(&host[0], main->n_groups->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-  B2_READBACK(ctx, &host[1], status->ptr, 4);
-  check_status(host[1]);
-  int64_t ng = host[0];
+  int64_t ng = group_bound;
+  if (!groups_exact) {
+    B2_CUDA(cudaMemcpyAsync(&host[0], main->n_groups->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    B2_READBACK(ctx, &host[1], status->ptr, 4);
+    check_status(host[1]);
+    ng = host[0];
+  }
   if (main->cap > (1ull << 32)) fail(B2_ERR_NOT_IMPLEMENTED, "group table beyond 2^32 slots");
   auto slots = dev_alloc(ctx, (size_t)(ng + 1) * 4);
   auto counter = dev_alloc_zero(ctx, 16);

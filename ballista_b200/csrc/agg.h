@@ -21,6 +21,12 @@ struct KeyLayout {
   std::vector<KeyPart> parts;
 };
 KeyLayout make_key_layout(const std::vector<int>& dtypes);  // throws NotImplemented when > 15 bytes
+// only a Utf8 part can overflow its budget: integer-only keys need no status readback after pack_keys
+inline bool layout_has_utf8(const KeyLayout& l) {
+  for (auto& p : l.parts)
+    if (p.dtype == B2_UTF8) return true;
+  return false;
+}
 
 struct GroupTable {
   Ctx* ctx;
@@ -77,6 +83,7 @@ struct AggRunner {
   bool force_global = false;
   bool narrow_overflowed = false;  // a narrow-key kernel overflowed once: later batches go straight to wide keys
   int64_t group_bound = 0;  // upper bound on groups in `main`
+  bool groups_exact = false;  // group_bound is main's exact group count and nothing ran on the table since (finish() skips its readback)
   std::string path;         // diagnostics
   AggRunner(Ctx* c, int na_, int nc_, bool keyed_);
   void consume(const AggLaunch& l, int64_t n);

@@ -148,7 +148,7 @@ BatchPtr HashAggregateExec::run_partial(int partition) {
         for (auto& g : groups) kc.push_back(eval_expr(ctx, g, *b));
         keybuf = pack_keys(ctx, layout, kc, b->num_rows, st->as<int>());
         int host = 0;
-        B2_READBACK(ctx, &host, st->ptr, 4);
+        if (layout_has_utf8(layout)) B2_READBACK(ctx, &host, st->ptr, 4);
         if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 group key value is longer than the packed-key budget");
         keys = keybuf->as<Key128>();
       }

@@ -68,7 +68,7 @@ struct HashJoinExec : Op {
     BufPtr st = dev_alloc_zero(ctx, 16);
     BufPtr keys = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>());
     int host = 0;
-    B2_READBACK(ctx, &host, st->ptr, 4);
+    if (layout_has_utf8(layout)) B2_READBACK(ctx, &host, st->ptr, 4);
     if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 join key value is longer than the packed-key budget");
     return keys;
   }
@@ -297,7 +297,7 @@ struct RepartitionExec : Op {
     BufPtr pk = pack_keys(ctx, layout, kc, b.num_rows, stt->as<int>());
     SplitState st = hash_split_begin(ctx, pk->as<Key128>(), nullptr, b.num_rows, n_out, &rp, m);
     int host = 0;
-    B2_READBACK(ctx, &host, stt->ptr, 4);
+    if (layout_has_utf8(layout)) B2_READBACK(ctx, &host, stt->ptr, 4);
     if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 partitioning key value is longer than the packed-key budget");
     return st;
   }

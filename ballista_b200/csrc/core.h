@@ -181,6 +181,9 @@ struct Batch {
   Schema schema;
   std::vector<Column> cols;
   int64_t num_rows = 0;
+  // >= 0: this batch is the complete output of one Partial aggregate whose first `unique_key_cols` columns are its
+  // group keys, so no key occurs twice in it.  Any operator that builds a new batch leaves the default.
+  int unique_key_cols = -1;
   int64_t num_bytes() const {
     int64_t b = 0;
     for (auto& c : cols) b += c.num_bytes();

@@ -90,6 +90,7 @@ BatchPtr HashAggregateExec::emit(AggRunner& r, bool partial, const std::vector<i
     }
   }
   b->cols = ep.run();
+  if (partial && !groups.empty()) b->unique_key_cols = (int)groups.size();
   return b;
 }
 
@@ -184,8 +185,38 @@ BatchPtr HashAggregateExec::run_final(int partition) {
   if ((int)in_schema.fields.size() != col)
     fail(B2_ERR_EXECUTION, "Final aggregate: input has " + std::to_string(in_schema.fields.size()) +
                                " columns, expected " + std::to_string(col) + " (groups + accumulator state)");
+  // The whole input is ONE Partial output over these group keys (a stage with a single partition, or states that an
+  // exchange already co-located and a Partial re-aggregated): every key occurs once, so the merge is the identity and
+  // SUM / COUNT states are the results.  AVG (a division) and computed group expressions take the general path.
+  auto next_nonempty = [&]() {
+    BatchPtr b;
+    while ((b = in->next()) && b->num_rows == 0) {}
+    return b;
+  };
+  BatchPtr first = next_nonempty(), second = first ? next_nonempty() : nullptr;
+  bool identity = first && !second && ng > 0 && first->unique_key_cols == (int)ng && !getenv("B2_DISABLE_FUSION");
+  for (size_t g = 0; g < ng && identity; ++g) identity = groups[g]->kind == B2_EXPR_COLUMN && groups[g]->col == (int)g;
+  for (size_t a = 0; a < aggs.size() && identity; ++a) identity = aggs[a].fn != B2_AGG_AVG;
+  if (identity) {
+    auto o = std::make_shared<Batch>();
+    o->ctx = ctx;
+    o->schema = out;
+    o->num_rows = first->num_rows;
+    for (size_t g = 0; g < ng; ++g) o->cols.push_back(first->cols[g]);
+    for (size_t a = 0; a < aggs.size(); ++a) o->cols.push_back(first->cols[sum_col[a] >= 0 ? sum_col[a] : cnt_col[a]]);
+    last_path = "identity(unique partial states)";
+    return o;
+  }
   std::unique_ptr<AggRunner> runner;
-  while (BatchPtr b = in->next()) {
+  std::vector<BatchPtr> head;
+  if (first) head.push_back(first);
+  if (second) head.push_back(second);
+  size_t head_i = 0;
+  auto next_batch = [&]() -> BatchPtr {
+    if (head_i < head.size()) return head[head_i++];
+    return in->next();
+  };
+  while (BatchPtr b = next_batch()) {
     if (b->num_rows == 0) continue;
     std::vector<const double*> vals;
     std::vector<const u64*> cnts;

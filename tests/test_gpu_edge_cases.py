@@ -197,3 +197,45 @@ def test_join_two_column_and_string_keys_general_path(ctx):
     bs = [f"n{a}-{b}" for a, b in zip(b_supp.tolist(), b_nat.tolist())]
     ps = [f"n{a}-{b}" for a, b in zip(p_supp.tolist(), p_nat.tolist())]
     check(rb(k=bs, lrow=np.arange(nb, dtype=np.int64)), rb(k2=ps, rrow=np.arange(npr, dtype=np.int64)), [("k", "k2")], bs, ps)
+
+
+def test_final_over_one_unique_partial_output_is_the_identity(ctx):
+    """A Final aggregate whose whole input is one Partial output (every key once) returns the states unchanged; two
+    Partial outputs with overlapping keys, or an AVG, take the merging path.  Same rows either way."""
+    from ballista_b200 import HashAggregateExec, MemoryExec, MergeExec, avg, col, sum as sum_, tpch
+    rng = np.random.default_rng(3)
+    n = 50_000
+    b = rb(k=rng.integers(0, 20_000, n).astype(np.int32), d=rng.integers(0, 3, n).astype(np.int32),
+           v=rng.random(n))
+    groups = [col("k"), col("d")]
+
+    def run(aggs, parts):
+        states, schema = [], None
+        for p in parts:
+            partial = HashAggregateExec("Partial", groups, aggs, tpch.scan(ctx, [[p]]))
+            states += partial.collect_device(0)
+            schema = partial.schema()
+        final = HashAggregateExec("Final", groups, aggs, MergeExec(MemoryExec(ctx, schema, [states])),
+                                  input_schema=b.schema)
+        t = final.collect()
+        rows = sorted(zip(*[t[c].to_pylist() for c in t.schema.names]))
+        return rows, final.last_path()
+
+    want = {}
+    for k, d, v in zip(b["k"].to_pylist(), b["d"].to_pylist(), b["v"].to_pylist()):
+        want.setdefault((k, d), []).append(v)
+    one, path1 = run([sum_(col("v")).alias("s")], [b])
+    assert path1.startswith("identity"), path1
+    two, path2 = run([sum_(col("v")).alias("s")], [b.slice(0, n // 2), b.slice(n // 2)])
+    assert not path2.startswith("identity"), path2
+    withavg, path3 = run([sum_(col("v")).alias("s"), avg(col("v")).alias("a")], [b])
+    assert not path3.startswith("identity"), path3
+    for rows in (one, two):
+        assert [r[:2] for r in rows] == sorted(want)
+        for r in rows:
+            assert abs(r[2] - sum(want[r[:2]])) <= 1e-9 * abs(sum(want[r[:2]]))
+    assert [r[:3] for r in withavg] == [tuple(r) for r in one] or all(
+        abs(x[2] - y[2]) <= 1e-12 * abs(y[2]) for x, y in zip(withavg, one))
+    for r in withavg:
+        vs = want[r[:2]]
+        assert abs(r[3] - sum(vs) / len(vs)) <= 1e-9 * abs(sum(vs) / len(vs))

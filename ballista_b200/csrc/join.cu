@@ -127,6 +127,10 @@ int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* pkeys, int64_t n,
 // raise flags[0]; for primary-key builds (flags[0] == 0) next[] is never read.  The table is sized for the
 // rows that pass the fused filter, so a selective build side stays L2-resident.
 //
+// Beside the slots the build keeps a blocked Bloom filter of its keys (table.cuh: `bloom_bits`; one 32-bit word
+// per key, >= 16 bits per key): the probe tests it before touching the table, and a partitioned join across ranks
+// publishes it so that the probe side's exchange drops non-matching rows before they move (ops_join.cu).
+//
 // Both kernels take the FilterExec mask of their input (or null) and the ORIGINAL, uncompacted key column:
 // the filter is never materialised, row ids are those of the unfiltered batch, and output columns are
 // gathered once, for matching rows only (late materialisation).

@@ -6,13 +6,13 @@ is the host-side mirror of the reference's operator interface.  There is no CPU 
 """
 from . import _capi
 from ._capi import BallistaError, NotImplementedOnGpu
-from .expr import Expr, AggExpr, col, lit, date, sum, avg, count  # noqa: A004
+from .expr import Expr, AggExpr, col, lit, date, case, scalar_fn, sum, avg, count  # noqa: A004
 from .plan import (Context, DeviceBatch, ExecutionPlan, RecordBatchStream, MemoryExec, FilterExec,
                    CoalesceBatchesExec, MergeExec, ProjectionExec, HashAggregateExec, HashJoinExec,
                    RepartitionExec, SortExec, GlobalLimitExec, LocalLimitExec, plan_from_proto, describe_plan_proto)
 from . import tpch
 
-__all__ = ["BallistaError", "NotImplementedOnGpu", "Expr", "AggExpr", "col", "lit", "date", "sum", "avg", "count",
+__all__ = ["BallistaError", "NotImplementedOnGpu", "Expr", "AggExpr", "col", "lit", "date", "case", "scalar_fn", "sum", "avg", "count",
            "Context", "DeviceBatch", "ExecutionPlan", "RecordBatchStream", "MemoryExec", "FilterExec",
            "CoalesceBatchesExec", "MergeExec", "ProjectionExec", "HashAggregateExec", "HashJoinExec",
            "RepartitionExec", "SortExec", "GlobalLimitExec", "LocalLimitExec", "plan_from_proto",

@@ -13,9 +13,13 @@ LIB_PATH = os.path.join(_HERE, "libballista_b200.so")
 OK, ERR_INVALID_ARG, ERR_NOT_IMPLEMENTED, ERR_EXECUTION, ERR_ARROW, ERR_CUDA, ERR_NCCL, ERR_OOM = 0, -1, -2, -3, -4, -5, -6, -7
 
 # b2_expr_kind / b2_binary_op / b2_dtype / misc enums
-EXPR_COLUMN, EXPR_LITERAL, EXPR_BINARY, EXPR_NOT, EXPR_IS_NULL, EXPR_IS_NOT_NULL, EXPR_CAST, EXPR_NEGATIVE, EXPR_BETWEEN, EXPR_IN_LIST, EXPR_CASE = range(1, 12)
+EXPR_COLUMN, EXPR_LITERAL, EXPR_BINARY, EXPR_NOT, EXPR_IS_NULL, EXPR_IS_NOT_NULL, EXPR_CAST, EXPR_NEGATIVE, EXPR_BETWEEN, EXPR_IN_LIST, EXPR_CASE, EXPR_SCALAR_FN = range(1, 13)
 OP_AND, OP_OR, OP_EQ, OP_NOTEQ, OP_LTEQ, OP_LT, OP_GT, OP_GTEQ, OP_PLUS, OP_MINUS, OP_MULTIPLY, OP_DIVIDE, OP_LIKE = range(1, 14)
 BOOL, INT32, INT64, UINT64, FLOAT64, DATE32, UTF8, UINT8 = range(1, 9)
+# ScalarFunction (rust/core/proto/ballista.proto:80-114)
+SCALAR_FUNCTIONS = ["sqrt", "sin", "cos", "tan", "asin", "acos", "atan", "exp", "log", "log2", "log10", "floor", "ceil",
+                    "round", "trunc", "abs", "signum", "octetlength", "concat", "lower", "upper", "trim", "ltrim",
+                    "rtrim", "totimestamp", "array", "nullif", "datetrunc", "md5", "sha224", "sha256", "sha384", "sha512"]
 AGG_SUM, AGG_AVG, AGG_COUNT = 1, 2, 3
 AGG_PARTIAL, AGG_FINAL = 0, 1
 JOIN_INNER, JOIN_LEFT, JOIN_RIGHT = 0, 1, 2

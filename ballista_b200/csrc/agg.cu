@@ -40,6 +40,7 @@ KeyLayout make_key_layout(const std::vector<int>& dtypes) {
 // group table
 // ------------------------------------------------------------------------------------------------------
 std::shared_ptr<GroupTable> make_group_table(Ctx* ctx, u64 cap, int na, int nc) {
+  if (cap > (1ull << 32)) fail(B2_ERR_NOT_IMPLEMENTED, "group table beyond 2^32 slots");
   auto t = std::make_shared<GroupTable>();
   t->ctx = ctx;
   t->cap = cap;
@@ -49,6 +50,7 @@ std::shared_ptr<GroupTable> make_group_table(Ctx* ctx, u64 cap, int na, int nc) 
   t->acc = dev_alloc(ctx, cap * sizeof(double) * (size_t)(na ? na : 1));
   t->cnt = dev_alloc(ctx, cap * sizeof(u64) * (size_t)(nc ? nc : 1));
   t->n_groups = dev_alloc(ctx, 16);
+  t->slot_list = dev_alloc(ctx, cap * 4 + 16);  // written before it is read: no initialisation
   reset_group_table(*t);
   return t;
 }
@@ -59,11 +61,13 @@ void reset_group_table(GroupTable& t) {
   B2_CUDA(cudaMemsetAsync(t.n_groups->ptr, 0, 16, t.ctx->stream));
 }
 
+// walks the source's slot list (its claimed groups), not its whole capacity
 __global__ void table_merge_kernel(TableRef src, TableRef dst, int na, int nc, int* status) {
-  u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x;
-  for (; i < src.cap; i += (u64)gridDim.x * blockDim.x) {
+  const u64 ng = (u64)*src.n_groups;
+  u64 g = blockIdx.x * (u64)blockDim.x + threadIdx.x;
+  for (; g < ng; g += (u64)gridDim.x * blockDim.x) {
+    const u64 i = src.slot_list[g];
     Key128 k = src.keys[i];
-    if (k.lo == KEY_EMPTY && k.hi == KEY_EMPTY) continue;
     u64 slot = table_upsert(dst, k);
     if (slot == ~0ull) {
       atomicExch(status, AGG_TABLE_FULL);
@@ -87,7 +91,15 @@ constexpr int64_t GLOBAL_CHUNK_ROWS = 32ll << 20;  // multiple of TILE_ROWS
 
 AggRunner::AggRunner(Ctx* c, int na_, int nc_, bool keyed_) : ctx(c), na(na_), nc(nc_), keyed(keyed_) {
   status = dev_alloc_zero(ctx, 16);
-  main = make_group_table(ctx, keyed ? 1024 : 16, na, nc);
+}
+void AggRunner::reset() {
+  main.reset();
+  delta.reset();
+  group_bound = 0;
+  groups_exact = false;
+  speculative = false;
+  path.clear();
+  B2_CUDA(cudaMemsetAsync(status->ptr, 0, 16, ctx->stream));
 }
 
 void AggRunner::check_status(int st) {
@@ -102,12 +114,28 @@ void AggRunner::ensure_main(int64_t extra) {
   // footprint (each new group's first touch misses L2): beyond 2 M slots size for a worst-case load of 0.75 rather
   // than 0.5.  Linear probing stays short because real inputs repeat keys (Q3: 2.6 rows per group => load 0.27).
   if (need > (1ull << 21)) need = std::max<u64>(1ull << 21, next_pow2((u64)(group_bound + extra) * 4 / 3 + 16));
+  if (!main) {
+    main = make_group_table(ctx, std::max<u64>(need, keyed ? 1024 : 16), na, nc);
+    return;
+  }
   if (need <= main->cap) return;
   auto bigger = make_group_table(ctx, need, na, nc);
-  table_merge_kernel<<<grid_for(ctx, 8, (int64_t)main->cap, 256), 256, 0, ctx->stream>>>(
-      main->ref(), bigger->ref(), na, nc, status->as<int>());
+  int64_t walk = group_bound > 0 ? group_bound : 1;
+  table_merge_kernel<<<grid_for(ctx, 8, walk, 256), 256, 0, ctx->stream>>>(main->ref(), bigger->ref(), na, nc,
+                                                                         status->as<int>());
   B2_LAUNCHED(ctx);
   main = bigger;
+}
+
+bool AggRunner::consume_unchecked(const AggLaunch& l, int64_t n) {
+  if (force_global || main || n <= 0) return false;
+  main = make_group_table(ctx, keyed ? DELTA_CAP : 16, na, nc);
+  // the status word was zeroed at construction / reset(); the key-packing kernel of the unfused path may already
+  // have raised AGG_KEY_TOO_WIDE in it, which the emit's readback reports like a status of the scan itself
+  l.small(n, main->ref(), status->as<int>());
+  speculative = true;
+  path = "small";
+  return true;
 }
 
 void AggRunner::consume(const AggLaunch& l, int64_t n) {
@@ -123,19 +151,21 @@ void AggRunner::consume(const AggLaunch& l, int64_t n) {
     }
     if (!delta) delta = make_group_table(ctx, keyed ? DELTA_CAP : 16, na, nc);
     else reset_group_table(*delta);
-    B2_CUDA(cudaMemsetAsync(status->ptr, 0, 16, ctx->stream));
     l.small(n, delta->ref(), status->as<int>());
     B2_CUDA(cudaMemcpyAsync(&host[0], status->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
     B2_READBACK(ctx, &host[1], delta->n_groups->ptr, 4);
     if (host[0] == AGG_OK) {
       ensure_main(host[1]);
-      table_merge_kernel<<<grid_for(ctx, 8, (int64_t)delta->cap, 256), 256, 0, ctx->stream>>>(
-          delta->ref(), main->ref(), na, nc, status->as<int>());
-      B2_LAUNCHED(ctx);
+      if (host[1] > 0) {
+        table_merge_kernel<<<grid_for(ctx, 8, host[1], 256), 256, 0, ctx->stream>>>(delta->ref(), main->ref(), na, nc,
+                                                                                  status->as<int>());
+        B2_LAUNCHED(ctx);
+      }
       group_bound += host[1];
       if (path.empty() || path == "small") path = narrow_overflowed ? "small+widekeys" : "small";
       return;
     }
+    B2_CUDA(cudaMemsetAsync(status->ptr, 0, 16, ctx->stream));
     if (host[0] == AGG_KEY_TOO_WIDE && l.small_wide) {
       // a narrow-key kernel met a Utf8 key value of more than its budget: redo the batch with wide keys
       AggLaunch w = l;
@@ -144,7 +174,7 @@ void AggRunner::consume(const AggLaunch& l, int64_t n) {
       narrow_overflowed = true;
       return consume(w, n);
     }
-    if (host[0] == AGG_KEY_TOO_WIDE) check_status(host[0]);
+    check_status(host[0]);
     // too many groups for the per-CTA tables: redo this batch (and all later ones) on the HBM table
     force_global = true;
     delta.reset();
@@ -153,7 +183,6 @@ void AggRunner::consume(const AggLaunch& l, int64_t n) {
   for (int64_t b = 0; b < n; b += GLOBAL_CHUNK_ROWS) {
     int64_t e = b + GLOBAL_CHUNK_ROWS < n ? b + GLOBAL_CHUNK_ROWS : n;
     ensure_main(keyed ? e - b : 1);
-    B2_CUDA(cudaMemsetAsync(status->ptr, 0, 16, ctx->stream));
     l.global(b, e, n, main->ref(), status->as<int>());
     B2_CUDA(cudaMemcpyAsync(&host[0], status->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
     B2_READBACK(ctx, &host[1], main->n_groups->ptr, 4);
@@ -163,35 +192,20 @@ void AggRunner::consume(const AggLaunch& l, int64_t n) {
   }
 }
 
-__global__ void table_compact_kernel(const Key128* keys, u64 cap, uint32_t* slots, int* counter) {
-  u64 i = blockIdx.x * (u64)blockDim.x + threadIdx.x;
-  for (; i < cap; i += (u64)gridDim.x * blockDim.x) {
-    Key128 k = keys[i];
-    if (k.lo == KEY_EMPTY && k.hi == KEY_EMPTY) continue;
-    int pos = atomicAdd(counter, 1);
-    slots[pos] = (uint32_t)i;
+int64_t AggRunner::finish() {
+  if (!main) {
+    ensure_main(0);
+    groups_exact = true;
+    group_bound = 0;
   }
-}
-
-int64_t AggRunner::finish(BufPtr* slots_out) {
+  if (groups_exact) return group_bound;
   int host[2] = {0, 0};
-  int64_t ng = group_bound;
-  if (!groups_exact) {
-    B2_CUDA(cudaMemcpyAsync(&host[0], main->n_groups->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_READBACK(ctx, &host[1], status->ptr, 4);
-    check_status(host[1]);
-    ng = host[0];
-  }
-  if (main->cap > (1ull << 32)) fail(B2_ERR_NOT_IMPLEMENTED, "group table beyond 2^32 slots");
-  auto slots = dev_alloc(ctx, (size_t)(ng + 1) * 4);
-  auto counter = dev_alloc_zero(ctx, 16);
-  if (ng > 0) {
-    table_compact_kernel<<<grid_for(ctx, 8, (int64_t)main->cap, 256), 256, 0, ctx->stream>>>(
-        main->keys->as<Key128>(), main->cap, slots->as<uint32_t>(), counter->as<int>());
-    B2_LAUNCHED(ctx);
-  }
-  *slots_out = slots;
-  return ng;
+  B2_CUDA(cudaMemcpyAsync(&host[0], main->n_groups->ptr, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  B2_READBACK(ctx, &host[1], status->ptr, 4);
+  check_status(host[1]);
+  group_bound = host[0];
+  groups_exact = true;
+  return group_bound;
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -214,17 +228,28 @@ struct EmitCol {
   int byte_off;      // key columns: byte offset of the part inside the packed key
   const void* src;   // EMIT_F64 / EMIT_AVG: sums; EMIT_U64: counts
   const void* src2;  // EMIT_AVG: counts
+  const u64* vsrc;   // validity source (count of non-null inputs), or null
   void* out;         // values (Utf8: int32 offsets)
   uint8_t* chr;      // Utf8 characters
+  uint8_t* vout;     // validity bytes
 };
 constexpr int EMIT_MAX_COLS = 24;
 struct EmitArgs {
   int n;
   EmitCol c[EMIT_MAX_COLS];
 };
+// hdr (int64): [0] = status word, [1] = group count, [2 + y] = character total of column y (Utf8 key columns).
+// ng_dev == null: the host knows the group count (`bound`).
 __global__ void __launch_bounds__(256) emit_all_kernel(EmitArgs args, const Key128* __restrict__ keys,
-                                                       const uint32_t* __restrict__ slots, int64_t ng) {
+                                                       const uint32_t* __restrict__ slots, int64_t bound,
+                                                       const int* ng_dev, const int* status, int64_t* hdr) {
   const EmitCol& col = args.c[blockIdx.y];
+  int64_t ng = ng_dev ? (int64_t)*ng_dev : bound;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && hdr) {
+    hdr[0] = status ? (int64_t)*status : 0;
+    hdr[1] = ng;
+  }
+  if (ng > bound) return;  // speculation failed: the host sees hdr[1] > bound and redoes the batch
   if (col.kind == EMIT_KEY_STR) {
     // one CTA scans the lengths chunk by chunk (group counts with Utf8 keys are small), then writes the bytes
     if (blockIdx.x != 0) return;
@@ -234,6 +259,7 @@ __global__ void __launch_bounds__(256) emit_all_kernel(EmitArgs args, const Key1
     __syncthreads();
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     int32_t* off = static_cast<int32_t*>(col.out);
+    if (ng == 0 && threadIdx.x == 0) off[0] = 0;
     for (int64_t base = 0; base < ng; base += blockDim.x) {
       int64_t i = base + threadIdx.x;
       u128 bits = 0;
@@ -265,6 +291,7 @@ __global__ void __launch_bounds__(256) emit_all_kernel(EmitArgs args, const Key1
       if (threadIdx.x == 0) carry_s = carry + total;
       __syncthreads();
     }
+    if (threadIdx.x == 0 && hdr) hdr[2 + blockIdx.y] = carry_s;
     return;
   }
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -279,66 +306,98 @@ __global__ void __launch_bounds__(256) emit_all_kernel(EmitArgs args, const Key1
         break;
       case EMIT_F64: static_cast<double*>(col.out)[i] = static_cast<const double*>(col.src)[sl]; break;
       case EMIT_U64: static_cast<u64*>(col.out)[i] = static_cast<const u64*>(col.src)[sl]; break;
-      default:  // AVG evaluate(): sum / count as f64
-        static_cast<double*>(col.out)[i] =
-            __ddiv_rn(static_cast<const double*>(col.src)[sl], (double)static_cast<const u64*>(col.src2)[sl]);
+      default: {  // AVG evaluate(): sum / count as f64; NULL when nothing was counted
+        const u64 c = static_cast<const u64*>(col.src2)[sl];
+        static_cast<double*>(col.out)[i] = c ? __ddiv_rn(static_cast<const double*>(col.src)[sl], (double)c) : 0.0;
         break;
+      }
     }
+    if (col.vout) col.vout[i] = col.vsrc[sl] > 0;
   }
 }
 
-EmitPlan::EmitPlan(Ctx* c, const GroupTable& t, const BufPtr& s, int64_t n) : ctx(c), table(t), slots(s), ng(n) {}
-void EmitPlan::push(int kind, int byte_off, const void* src, const void* src2, Column col) {
-  descs.push_back(EmitDesc{kind, byte_off, src, src2});
+EmitPlan::EmitPlan(Ctx* c, const GroupTable& t, int64_t b) : ctx(c), table(t), bound(b) {}
+void EmitPlan::push(int kind, int byte_off, const void* src, const void* src2, const u64* vsrc, Column col) {
+  if (vsrc) col.valid = dev_alloc(ctx, (size_t)bound + 16);
+  descs.push_back(EmitDesc{kind, byte_off, src, src2, vsrc});
   cols.push_back(std::move(col));
 }
 void EmitPlan::key(const KeyPart& part) {
   if (part.dtype == B2_UTF8) {
     Column c;
     c.dtype = B2_UTF8;
-    c.length = ng;
-    c.data = dev_alloc_zero(ctx, (size_t)(ng + 1) * 4);
-    c.chars = dev_alloc(ctx, (size_t)ng * 15 + 16);
-    push(EMIT_KEY_STR, part.byte_off, nullptr, nullptr, std::move(c));
+    c.length = bound;
+    c.data = dev_alloc(ctx, (size_t)(bound + 1) * 4 + 16);
+    c.chars = dev_alloc(ctx, (size_t)bound * 15 + 16);
+    push(EMIT_KEY_STR, part.byte_off, nullptr, nullptr, nullptr, std::move(c));
     return;
   }
-  push(part.bytes == 8 ? EMIT_KEY_I64 : EMIT_KEY_I32, part.byte_off, nullptr, nullptr, new_fixed(ctx, part.dtype, ng));
+  push(part.bytes == 8 ? EMIT_KEY_I64 : EMIT_KEY_I32, part.byte_off, nullptr, nullptr, nullptr,
+       new_fixed(ctx, part.dtype, bound));
 }
-void EmitPlan::sum(int a) {
-  push(EMIT_F64, 0, table.acc->as<double>() + (u64)a * table.cap, nullptr, new_fixed(ctx, B2_FLOAT64, ng));
+void EmitPlan::sum(int a, int v) {
+  push(EMIT_F64, 0, table.acc->as<double>() + (u64)a * table.cap, nullptr,
+       v >= 0 ? table.cnt->as<u64>() + (u64)v * table.cap : nullptr, new_fixed(ctx, B2_FLOAT64, bound));
+}
+void EmitPlan::isum(int a, int dtype, int v) {
+  push(EMIT_U64, 0, table.cnt->as<u64>() + (u64)a * table.cap, nullptr,
+       v >= 0 ? table.cnt->as<u64>() + (u64)v * table.cap : nullptr, new_fixed(ctx, dtype, bound));
 }
 void EmitPlan::count(int a) {
-  push(EMIT_U64, 0, table.cnt->as<u64>() + (u64)a * table.cap, nullptr, new_fixed(ctx, B2_UINT64, ng));
+  push(EMIT_U64, 0, table.cnt->as<u64>() + (u64)a * table.cap, nullptr, nullptr, new_fixed(ctx, B2_UINT64, bound));
 }
-void EmitPlan::avg(int a, int cidx) {
-  push(EMIT_AVG, 0, table.acc->as<double>() + (u64)a * table.cap, table.cnt->as<u64>() + (u64)cidx * table.cap,
-       new_fixed(ctx, B2_FLOAT64, ng));
+void EmitPlan::avg(int a, int cidx, bool track_null) {
+  const u64* counts = table.cnt->as<u64>() + (u64)cidx * table.cap;
+  push(EMIT_AVG, 0, table.acc->as<double>() + (u64)a * table.cap, counts, track_null ? counts : nullptr,
+       new_fixed(ctx, B2_FLOAT64, bound));
 }
-std::vector<Column> EmitPlan::run() {
-  if (ng == 0) return std::move(cols);
-  std::vector<size_t> strs;
-  for (size_t b = 0; b < cols.size(); b += EMIT_MAX_COLS) {
-    EmitArgs args;
-    memset(&args, 0, sizeof args);
-    args.n = (int)std::min<size_t>(EMIT_MAX_COLS, cols.size() - b);
-    for (int k = 0; k < args.n; ++k) {
-      const EmitDesc& d = descs[b + k];
-      Column& c = cols[b + k];
-      args.c[k] = EmitCol{d.kind, d.byte_off, d.src, d.src2, c.data->ptr, c.chars ? c.chars->as<uint8_t>() : nullptr};
-      if (d.kind == EMIT_KEY_STR) strs.push_back(b + k);
+bool EmitPlan::run(int64_t exact_ng, const int* status_dev, int64_t* ng_out, int* status_out) {
+  if (cols.size() > EMIT_MAX_COLS) fail(B2_ERR_NOT_IMPLEMENTED, "aggregate with more than 24 output columns");
+  const bool spec = exact_ng < 0;
+  if (status_out) *status_out = 0;
+  if (!spec && exact_ng == 0) {
+    for (auto& c : cols) {
+      c.length = 0;
+      if (c.dtype == B2_UTF8) B2_CUDA(cudaMemsetAsync(c.data->ptr, 0, 4, ctx->stream));
     }
-    dim3 grid((unsigned)grid_for(ctx, 8, ng, 256), (unsigned)args.n);
-    emit_all_kernel<<<grid, 256, 0, ctx->stream>>>(args, table.keys->as<Key128>(), slots->as<uint32_t>(), ng);
-    B2_LAUNCHED(ctx);
+    *ng_out = 0;
+    return true;
   }
-  if (!strs.empty()) {  // one readback for the character totals of all Utf8 key columns
-    std::vector<int32_t> totals(strs.size(), 0);
-    for (size_t k = 0; k < strs.size(); ++k)
-      B2_CUDA(cudaMemcpyAsync(&totals[k], cols[strs[k]].data->as<int32_t>() + ng, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    B2_SYNC(ctx);
-    for (size_t k = 0; k < strs.size(); ++k) cols[strs[k]].chars_len = totals[k];
+  EmitArgs args;
+  memset(&args, 0, sizeof args);
+  args.n = (int)cols.size();
+  bool any_str = false;
+  for (int k = 0; k < args.n; ++k) {
+    const EmitDesc& d = descs[k];
+    Column& c = cols[k];
+    args.c[k] = EmitCol{d.kind, d.byte_off, d.src, d.src2, d.vsrc, c.data->ptr, c.chars ? c.chars->as<uint8_t>() : nullptr,
+                        c.valid ? c.valid->as<uint8_t>() : nullptr};
+    any_str |= d.kind == EMIT_KEY_STR;
   }
-  return std::move(cols);
+  const int64_t rows = spec ? bound : exact_ng;
+  BufPtr hdr;
+  if (spec || any_str) hdr = dev_alloc_zero(ctx, (size_t)(2 + EMIT_MAX_COLS) * 8);
+  dim3 grid((unsigned)grid_for(ctx, 8, rows, 256), (unsigned)args.n);
+  emit_all_kernel<<<grid, 256, 0, ctx->stream>>>(args, table.keys->as<Key128>(), table.slot_list->as<uint32_t>(), rows,
+                                                 spec ? table.n_groups->as<int>() : nullptr, status_dev,
+                                                 hdr ? hdr->as<int64_t>() : nullptr);
+  B2_LAUNCHED(ctx);
+  int64_t ng = exact_ng;
+  int64_t h[2 + EMIT_MAX_COLS] = {0};
+  if (hdr) {  // ONE readback: status, group count, character totals
+    B2_READBACK(ctx, h, hdr->ptr, sizeof h);
+    if (spec) {
+      ng = h[1];
+      if (status_out) *status_out = (int)h[0];
+      if (h[0] != AGG_OK || ng > bound) return false;
+    }
+  }
+  for (int k = 0; k < args.n; ++k) {
+    cols[k].length = ng;
+    if (descs[k].kind == EMIT_KEY_STR) cols[k].chars_len = h[2 + k];
+  }
+  *ng_out = ng;
+  return true;
 }
 
 }  // namespace b2

@@ -21,7 +21,6 @@ constexpr int SMEM_SLOTS = 512;   // per-CTA key table
 constexpr int SMEM_GROUPS = 128;  // max dense group ids per CTA
 constexpr int REG_GROUPS = 4;     // group ids accumulated in registers
 
-enum { AGG_OK = 0, AGG_ABORT_CARDINALITY = 1, AGG_KEY_TOO_WIDE = 2, AGG_TABLE_FULL = 3 };
 
 // ------------------------------------------------------------------------------------------------------
 // fused source: columns bound to slots, predicate / keys / aggregate arguments evaluated in registers

@@ -32,9 +32,10 @@ struct GroupTable {
   Ctx* ctx;
   u64 cap;
   int na, nc;
-  BufPtr keys, acc, cnt, n_groups;
+  BufPtr keys, acc, cnt, n_groups, slot_list;
   TableRef ref() const {
-    return TableRef{keys->as<Key128>(), acc->as<double>(), cnt->as<u64>(), cap, n_groups->as<int>()};
+    return TableRef{keys->as<Key128>(), acc->as<double>(), cnt->as<u64>(), cap, n_groups->as<int>(),
+                    slot_list->as<uint32_t>()};
   }
 };
 std::shared_ptr<GroupTable> make_group_table(Ctx* ctx, u64 cap, int na, int nc);
@@ -68,10 +69,17 @@ const std::map<std::string, FusedEntry>& fused_registry();
 bool bind_fused_agg(Ctx* ctx, const ExprPtr& pred, const std::vector<ExprPtr>& groups,
                     const std::vector<ExprPtr>& args, const Batch& batch, AggLaunch* out, std::string* sig);
 // Materialised source: keys (null = ungrouped), mask (null = all rows), value / count columns.
+// `cnts`: one u64 column per count accumulator; a null entry counts 1 per row (COUNT(*), Partial mode).
 AggLaunch bind_column_agg(Ctx* ctx, const Key128* keys, const uint8_t* mask, const std::vector<const double*>& vals,
-                          const std::vector<const u64*>& cnts, bool count_rows);
+                          const std::vector<const u64*>& cnts);
+// accumulator counts of the instantiated materialised-source kernels (what bind_column_agg pads a request to)
+inline int agg_padded_na(int n) { return n <= 1 ? 1 : n <= 2 ? 2 : n <= 4 ? 4 : 8; }
+inline int agg_padded_nc(int n) { return n <= 1 ? 1 : n <= 4 ? 4 : 12; }
 // pack evaluated group columns into a Key128 column
-BufPtr pack_keys(Ctx* ctx, const KeyLayout& layout, const std::vector<Column>& cols, int64_t n, int* status_dev);
+// null_tag: byte 15 of the key of a row with a NULL key part (joins give each side its own tag, so that null keys
+// match nothing); 0 = NULL key parts are refused (group / partition keys)
+BufPtr pack_keys(Ctx* ctx, const KeyLayout& layout, const std::vector<Column>& cols, int64_t n, int* status_dev,
+                 int null_tag = 0);
 
 // Strategy state of one HashAggregateExec execution (one partition)
 struct AggRunner {
@@ -79,42 +87,53 @@ struct AggRunner {
   int na, nc;
   bool keyed;
   std::shared_ptr<GroupTable> main, delta;
-  BufPtr status;  // int[2]: status, spare
+  BufPtr status;  // int[4]: status, spare
   bool force_global = false;
   bool narrow_overflowed = false;  // a narrow-key kernel overflowed once: later batches go straight to wide keys
   int64_t group_bound = 0;  // upper bound on groups in `main`
   bool groups_exact = false;  // group_bound is main's exact group count and nothing ran on the table since (finish() skips its readback)
+  bool speculative = false;   // consume_unchecked() ran: status / group count are still on the device
   std::string path;         // diagnostics
   AggRunner(Ctx* c, int na_, int nc_, bool keyed_);
   void consume(const AggLaunch& l, int64_t n);
-  // compact occupied slots; returns number of groups and the slot index list
-  int64_t finish(BufPtr* slots);
+  // The whole input is ONE batch: the low-cardinality kernel writes straight into `main` and nothing is read back;
+  // the emit step returns status and group count with its own (single) readback, and the caller redoes the batch
+  // through consume() when the status says so.  False when this runner cannot speculate (global path forced).
+  bool consume_unchecked(const AggLaunch& l, int64_t n);
+  void reset();  // forget everything accumulated so far (after a failed speculation)
+  // number of groups in `main` (synchronises unless already known)
+  int64_t finish();
+  void check_status(int st);
  private:
   void ensure_main(int64_t extra_groups);
-  void check_status(int st);
 };
 
 // Output assembly (agg.cu): every output column of one aggregate is gathered from the table by ONE launch
-// (blockIdx.y = column) and the character totals of all Utf8 key columns come back in one readback.
+// (blockIdx.y = column) through the table's slot list; status, group count and the character totals of all Utf8 key
+// columns come back in ONE readback.
 struct EmitPlan {
   struct EmitDesc {
     int kind, byte_off;
     const void *src, *src2;
+    const u64* vsrc;  // validity = (vsrc[slot] > 0), or null: always valid
   };
   Ctx* ctx;
   const GroupTable& table;
-  BufPtr slots;
-  int64_t ng;
+  int64_t bound;  // rows the output columns are allocated for (>= the group count, or the emit reports failure)
   std::vector<EmitDesc> descs;
   std::vector<Column> cols;
-  EmitPlan(Ctx* ctx, const GroupTable& t, const BufPtr& slots, int64_t ng);
+  EmitPlan(Ctx* ctx, const GroupTable& t, int64_t bound);
   void key(const KeyPart& part);
-  void sum(int acc_idx);
+  void sum(int acc_idx, int vcnt_idx = -1);
+  void isum(int cnt_idx, int dtype, int vcnt_idx = -1);  // Int64 / UInt64 sums live in the count accumulators
   void count(int cnt_idx);
-  void avg(int acc_idx, int cnt_idx);
-  std::vector<Column> run();  // columns in the order they were requested
+  void avg(int acc_idx, int cnt_idx, bool track_null);
+  // Runs the emit.  exact_ng >= 0: the host already knows the group count (no status to check).  Otherwise the count
+  // and `status_dev` are read back with the Utf8 totals; returns false (and *status_out) when the speculation
+  // failed: bad status or more groups than `bound`.  On success *ng_out rows are valid in every column.
+  bool run(int64_t exact_ng, const int* status_dev, int64_t* ng_out, int* status_out);
  private:
-  void push(int kind, int byte_off, const void* src, const void* src2, Column col);
+  void push(int kind, int byte_off, const void* src, const void* src2, const u64* vsrc, Column col);
 };
 
 }  // namespace b2

@@ -215,40 +215,39 @@ bool bind_fused_agg(Ctx* ctx, const ExprPtr& pred, const std::vector<ExprPtr>& g
 // ------------------------------------------------------------------------------------------------------
 template <int NA, int NC, bool K>
 static AggLaunch bind_cols(Ctx* ctx, const Key128* keys, const uint8_t* mask, const std::vector<const double*>& vals,
-                           const std::vector<const u64*>& cnts, bool count_rows) {
+                           const std::vector<const u64*>& cnts) {
   ColumnParams<NA, NC> p;
   memset(&p, 0, sizeof p);
   p.keys = keys;
   p.mask = mask;
   for (size_t a = 0; a < vals.size(); ++a) p.val[a] = vals[a];
-  if (count_rows) {
-    p.cnt_default[0] = 1;
-  } else {
-    for (size_t a = 0; a < cnts.size(); ++a) p.cnt[a] = cnts[a];
+  for (size_t a = 0; a < cnts.size(); ++a) {
+    p.cnt[a] = cnts[a];
+    p.cnt_default[a] = 1;  // a null entry counts rows; padding slots beyond cnts.size() keep 0
   }
   return make_launch<ColumnSrc<NA, NC, K>>(ctx, p);
 }
 template <int NA, int NC>
 static AggLaunch bind_cols_k(Ctx* ctx, const Key128* keys, const uint8_t* mask, const std::vector<const double*>& vals,
-                             const std::vector<const u64*>& cnts, bool count_rows) {
-  return keys ? bind_cols<NA, NC, true>(ctx, keys, mask, vals, cnts, count_rows)
-              : bind_cols<NA, NC, false>(ctx, keys, mask, vals, cnts, count_rows);
+                             const std::vector<const u64*>& cnts) {
+  return keys ? bind_cols<NA, NC, true>(ctx, keys, mask, vals, cnts) : bind_cols<NA, NC, false>(ctx, keys, mask, vals, cnts);
 }
 template <int NA>
 static AggLaunch bind_cols_c(Ctx* ctx, const Key128* keys, const uint8_t* mask, const std::vector<const double*>& vals,
-                             const std::vector<const u64*>& cnts, bool count_rows) {
-  size_t nc = count_rows ? 1 : cnts.size();
-  if (nc <= 1) return bind_cols_k<NA, 1>(ctx, keys, mask, vals, cnts, count_rows);
-  if (nc <= 4) return bind_cols_k<NA, 4>(ctx, keys, mask, vals, cnts, count_rows);
-  fail(B2_ERR_NOT_IMPLEMENTED, "more than 4 count accumulators in one aggregate");
+                             const std::vector<const u64*>& cnts) {
+  size_t nc = cnts.size();
+  if (nc <= 1) return bind_cols_k<NA, 1>(ctx, keys, mask, vals, cnts);
+  if (nc <= 4) return bind_cols_k<NA, 4>(ctx, keys, mask, vals, cnts);
+  if (nc <= 12) return bind_cols_k<NA, 12>(ctx, keys, mask, vals, cnts);
+  fail(B2_ERR_NOT_IMPLEMENTED, "more than 12 count / integer-sum accumulators in one aggregate");
 }
 AggLaunch bind_column_agg(Ctx* ctx, const Key128* keys, const uint8_t* mask, const std::vector<const double*>& vals,
-                          const std::vector<const u64*>& cnts, bool count_rows) {
+                          const std::vector<const u64*>& cnts) {
   size_t na = vals.size();
-  if (na <= 1) return bind_cols_c<1>(ctx, keys, mask, vals, cnts, count_rows);
-  if (na <= 2) return bind_cols_c<2>(ctx, keys, mask, vals, cnts, count_rows);
-  if (na <= 4) return bind_cols_c<4>(ctx, keys, mask, vals, cnts, count_rows);
-  if (na <= 8) return bind_cols_c<8>(ctx, keys, mask, vals, cnts, count_rows);
+  if (na <= 1) return bind_cols_c<1>(ctx, keys, mask, vals, cnts);
+  if (na <= 2) return bind_cols_c<2>(ctx, keys, mask, vals, cnts);
+  if (na <= 4) return bind_cols_c<4>(ctx, keys, mask, vals, cnts);
+  if (na <= 8) return bind_cols_c<8>(ctx, keys, mask, vals, cnts);
   fail(B2_ERR_NOT_IMPLEMENTED, "more than 8 distinct Float64 accumulators in one aggregate");
 }
 
@@ -259,18 +258,24 @@ struct PackPart {
   int dtype, byte_off, bytes;
   const void* data;
   const uint8_t* chars;
+  const uint8_t* valid;
 };
 struct PackArgs {
   PackPart part[8];
   int n;
 };
-__global__ void pack_keys_kernel(PackArgs a, int64_t n, Key128* out, int* status) {
+__global__ void pack_keys_kernel(PackArgs a, int64_t n, Key128* out, int* status, int null_tag) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   bool overflow = false;
   for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     u128 key = 0;
+    bool is_null = false;
     for (int p = 0; p < a.n; ++p) {
       const PackPart& pp = a.part[p];
+      if (pp.valid && !pp.valid[i]) {
+        is_null = true;
+        continue;
+      }
       if (pp.dtype == B2_UTF8) {
         StrVal s = load_str((const int32_t*)pp.data, pp.chars, i);
         if (s.len > pp.bytes - 1) overflow = true;
@@ -282,13 +287,17 @@ __global__ void pack_keys_kernel(PackArgs a, int64_t n, Key128* out, int* status
         key |= (u128)(uint32_t)((const int32_t*)pp.data)[i] << (8 * pp.byte_off);
       }
     }
-    out[i] = Key128{(u64)key, (u64)(key >> 64)};
+    out[i] = is_null ? Key128{0, (u64)null_tag << 56} : Key128{(u64)key, (u64)(key >> 64)};
   }
   if (overflow) atomicExch(status, AGG_KEY_TOO_WIDE);
 }
 
-BufPtr pack_keys(Ctx* ctx, const KeyLayout& layout, const std::vector<Column>& cols, int64_t n, int* status_dev) {
+BufPtr pack_keys(Ctx* ctx, const KeyLayout& layout, const std::vector<Column>& cols, int64_t n, int* status_dev,
+                 int null_tag) {
   if (layout.parts.size() > 8) fail(B2_ERR_NOT_IMPLEMENTED, "more than 8 key columns");
+  if (!null_tag)
+    for (auto& c : cols)
+      if (c.valid) fail(B2_ERR_NOT_IMPLEMENTED, "NULLs in a group / partitioning key column");
   PackArgs a;
   memset(&a, 0, sizeof a);
   a.n = (int)layout.parts.size();
@@ -298,10 +307,11 @@ BufPtr pack_keys(Ctx* ctx, const KeyLayout& layout, const std::vector<Column>& c
     a.part[p].bytes = layout.parts[p].bytes;
     a.part[p].data = cols[p].data->ptr;
     a.part[p].chars = cols[p].chars ? cols[p].chars->as<uint8_t>() : nullptr;
+    a.part[p].valid = cols[p].validity();
   }
   auto out = dev_alloc(ctx, (size_t)(n + 1) * sizeof(Key128));
   if (n) {
-    pack_keys_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(a, n, out->as<Key128>(), status_dev);
+    pack_keys_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(a, n, out->as<Key128>(), status_dev, null_tag);
     B2_LAUNCHED(ctx);
   }
   return out;

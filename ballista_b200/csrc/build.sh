@@ -7,7 +7,7 @@ OBJ=build
 mkdir -p $OBJ
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-ffp-contract=off -diag-suppress 550"
-SRCS="core.cu tpch_gen.cu agg.cu agg_registry.cu eval.cu take.cu join.cu repartition.cu comm.cu shuffle.cu csv.cu ops_basic.cu ops_agg.cu ops_join.cu capi.cu expr.cpp proto.cpp"
+SRCS="core.cu validity.cu tpch_gen.cu agg.cu agg_registry.cu eval.cu take.cu join.cu repartition.cu comm.cu shuffle.cu csv.cu ops_basic.cu ops_agg.cu ops_join.cu capi.cu expr.cpp proto.cpp"
 pids=()
 for f in $SRCS; do
   o=$OBJ/${f%.*}.o

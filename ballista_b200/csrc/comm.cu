@@ -78,6 +78,9 @@ static size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 constexpr int SMALL_ROWS = 256, SMALL_CHARS = 4096, SMALL_MAX_COLS = 24, SMALL_MAX_RANKS = 64, SMALL_MAX_STR = 4;
 struct SmallCol {
   const void* src;       // pack: values (Utf8: int32 offsets); unpack: unused
+  const uint8_t* valid;  // pack: validity bytes, or null (all rows valid)
+  uint8_t* dst_valid;    // unpack: validity bytes of the gathered column, or null (no rank sent a NULL)
+  int64_t valid_off;     // SMALL_ROWS validity bytes inside a slot
   const uint8_t* chars;  // pack: Utf8 characters
   void* dst;             // unpack: values (Utf8: int32 offsets)
   uint8_t* dst_chars;    // unpack: Utf8 characters
@@ -98,11 +101,15 @@ __global__ void pack_small_kernel(SmallArgs a, char* slot, int fits) {
   if (blockIdx.y == 0 && threadIdx.x == 0) {
     int64_t* h = reinterpret_cast<int64_t*>(slot);
     h[0] = fits ? a.rows : -1;
-    for (int k = 0; k < a.ncol; ++k) h[1 + k] = a.chars[k];
+    for (int k = 0; k < a.ncol; ++k) {
+      h[1 + k] = a.chars[k];
+      h[1 + a.ncol + k] = a.c[k].valid != nullptr;  // this rank's column may hold NULLs
+    }
   }
   if (!fits) return;
   char* base = slot + c.val_off;
   for (int64_t i = threadIdx.x; i < a.rows; i += blockDim.x) {
+    slot[c.valid_off + i] = c.valid ? (char)c.valid[i] : (char)1;
     if (c.utf8 >= 0) {
       const int32_t* off = static_cast<const int32_t*>(c.src);
       reinterpret_cast<int32_t*>(base)[i] = off[i + 1] - off[i];
@@ -125,6 +132,7 @@ __global__ void unpack_small_kernel(SmallArgs a, const char* recv) {
     while (a.row_prefix[r + 1] <= i) ++r;
     int64_t j = i - a.row_prefix[r];
     const char* base = recv + (int64_t)r * a.stride + c.val_off;
+    if (c.dst_valid) c.dst_valid[i] = (uint8_t)recv[(int64_t)r * a.stride + c.valid_off + j];
     if (c.utf8 >= 0) {
       const int32_t* lens = reinterpret_cast<const int32_t*>(base);
       int64_t o = a.chr_prefix[c.utf8][r];
@@ -161,7 +169,8 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
   a.ncol = (int)ncol;
   a.nr = nr;
   a.rows = local.num_rows;
-  a.header_bytes = (int64_t)align16((1 + ncol) * 8);
+  const size_t hdr_words = 1 + 2 * ncol;  // rows, character count per column, may-hold-NULLs flag per column
+  a.header_bytes = (int64_t)align16(hdr_words * 8);
   int64_t off = a.header_bytes;
   int n_str = 0;
   bool fits = local.num_rows <= SMALL_ROWS;
@@ -170,6 +179,9 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
     if (!col.data) return nullptr;
     SmallCol& sc = a.c[c];
     sc.src = col.data->ptr;
+    sc.valid = col.validity();
+    sc.valid_off = off;
+    off += SMALL_ROWS;
     sc.utf8 = -1;
     sc.width = col.dtype == B2_UTF8 ? 4 : (int)dtype_width(col.dtype);
     sc.val_off = off;
@@ -192,21 +204,24 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
   B2_NCCL(ncclAllGather(send->ptr, recv->ptr, (size_t)a.stride, ncclChar, ctx->comm->nccl, ctx->stream));
   ctx->bytes_sent += a.stride * (nr - 1);
   // one strided readback: the header of every slot
-  std::vector<int64_t> heads((size_t)nr * (1 + ncol));
+  std::vector<int64_t> heads((size_t)nr * hdr_words);
   {
     double t0 = ctx->trace ? wall_now() : 0;
-    B2_CUDA(cudaMemcpy2DAsync(heads.data(), (1 + ncol) * 8, recv->ptr, (size_t)a.stride, (1 + ncol) * 8, (size_t)nr,
+    B2_CUDA(cudaMemcpy2DAsync(heads.data(), hdr_words * 8, recv->ptr, (size_t)a.stride, hdr_words * 8, (size_t)nr,
                               cudaMemcpyDeviceToHost, ctx->stream));
     B2_CUDA(cudaStreamSynchronize(ctx->stream));
     if (ctx->trace) ctx->trace_add("comm.cu:allgather_small headers", wall_now() - t0);
   }
   for (int r = 0; r < nr; ++r)
-    if (heads[(size_t)r * (1 + ncol)] < 0) return nullptr;  // somebody did not fit: general protocol (all ranks agree)
+    if (heads[(size_t)r * hdr_words] < 0) return nullptr;  // somebody did not fit: general protocol (all ranks agree)
+  std::vector<char> any_null(ncol, 0);
   for (int r = 0; r < nr; ++r) {
-    a.row_prefix[r + 1] = a.row_prefix[r] + heads[(size_t)r * (1 + ncol)];
-    for (size_t c = 0; c < ncol; ++c)
+    a.row_prefix[r + 1] = a.row_prefix[r] + heads[(size_t)r * hdr_words];
+    for (size_t c = 0; c < ncol; ++c) {
       if (a.c[c].utf8 >= 0)
-        a.chr_prefix[a.c[c].utf8][r + 1] = a.chr_prefix[a.c[c].utf8][r] + heads[(size_t)r * (1 + ncol) + 1 + c];
+        a.chr_prefix[a.c[c].utf8][r + 1] = a.chr_prefix[a.c[c].utf8][r] + heads[(size_t)r * hdr_words + 1 + c];
+      any_null[c] |= heads[(size_t)r * hdr_words + 1 + ncol + c] != 0;
+    }
   }
   int64_t total = a.row_prefix[nr];
   auto out = std::make_shared<Batch>();
@@ -226,6 +241,11 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
       o.data = dev_alloc(ctx, (size_t)total * dtype_width(o.dtype) + 16);
     }
     a.c[c].dst = o.data->ptr;
+    a.c[c].dst_valid = nullptr;
+    if (any_null[c]) {  // some rank's column carried validity (e.g. the NULL sum state of an empty partition)
+      o.valid = dev_alloc(ctx, (size_t)total + 16);
+      a.c[c].dst_valid = o.valid->as<uint8_t>();
+    }
     out->cols.push_back(std::move(o));
   }
   if (total) {
@@ -237,7 +257,8 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
 
 BatchPtr comm_allgather_batch(Ctx* ctx, const Batch& local) {
   if (!ctx->comm) fail(B2_ERR_INVALID_ARG, "no communicator (call b2_comm_init)");
-  if (BatchPtr b = allgather_small(ctx, local)) return b;
+  if (BatchPtr b = allgather_small(ctx, local)) return b;  // carries validity
+  require_no_nulls(local, "all-gather of a large batch");
   return allgather_general(ctx, local);
 }
 
@@ -340,6 +361,7 @@ static BatchPtr allgather_general(Ctx* ctx, const Batch& local) {
 // All-to-all of a destination-major permuted batch: rows of slice d go to rank d.  Fixed-width columns
 // are sent as they are; Utf8 columns travel as a lengths column plus a chars byte stream.
 BatchPtr comm_all_to_all(Ctx* ctx, const Batch& b, const std::vector<int64_t>& counts) {
+  require_no_nulls(b, "exchange over NVLink");
   if (!ctx->comm) fail(B2_ERR_INVALID_ARG, "no communicator (call b2_comm_init)");
   int nr = ctx->nranks, me = ctx->rank;
   if ((int)counts.size() != nr) fail(B2_ERR_INVALID_ARG, "all-to-all needs one slice per rank");

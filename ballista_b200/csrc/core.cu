@@ -178,7 +178,14 @@ BatchPtr batch_from_arrow(Ctx* ctx, const Schema& schema, ArrowArray* arr, cudaS
   if ((size_t)arr->n_children != schema.fields.size())
     fail(B2_ERR_ARROW, "RecordBatch has " + std::to_string(arr->n_children) + " columns, schema has " +
                            std::to_string(schema.fields.size()));
-  if (arr->null_count > 0) fail(B2_ERR_NOT_IMPLEMENTED, "null struct rows");
+  // null_count == -1 means "not computed" (Arrow C Data Interface): a struct-level bitmap is then looked at
+  if (arr->null_count != 0 && arr->n_buffers > 0 && arr->buffers && arr->buffers[0]) {
+    const uint8_t* sb = static_cast<const uint8_t*>(arr->buffers[0]);
+    for (int64_t i = 0; i < arr->length; ++i) {
+      int64_t bit = arr->offset + i;
+      if (!((sb[bit >> 3] >> (bit & 7)) & 1)) fail(B2_ERR_NOT_IMPLEMENTED, "null struct rows (a RecordBatch has none)");
+    }
+  }
   cudaStream_t st = stream ? stream : ctx->stream;
   auto b = std::make_shared<Batch>();
   b->ctx = ctx;
@@ -190,12 +197,12 @@ BatchPtr batch_from_arrow(Ctx* ctx, const Schema& schema, ArrowArray* arr, cudaS
     int64_t off = c->offset + arr->offset;
     int64_t len = arr->length;
     if (c->length < arr->offset + arr->length) fail(B2_ERR_ARROW, "child array shorter than batch");
-    // validity bitmaps: accepted only when they mark nothing null
-    if (c->null_count > 0)
-      fail(B2_ERR_NOT_IMPLEMENTED, "column '" + f.name + "' contains nulls; the TPC-H path is non-nullable");
     Column col;
     col.dtype = f.dtype;
     col.length = len;
+    // validity bitmap -> one byte per row in HBM.  null_count == -1 ("not computed") is treated as "may hold nulls".
+    if (c->null_count != 0 && c->n_buffers > 0 && c->buffers[0] && len > 0)
+      col.valid = valid_from_bitmap(ctx, static_cast<const uint8_t*>(c->buffers[0]), off, len, st);
     if (f.dtype == B2_UTF8) {
       const int32_t* ho = static_cast<const int32_t*>(c->buffers[1]);
       const char* hd = static_cast<const char*>(c->buffers[2]);
@@ -328,6 +335,8 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
     std::vector<std::pair<size_t, std::vector<uint8_t>>> bools;  // bit-pack after the sync
     bools.reserve(b.cols.size());  // element addresses are handed to the stager
     D2HStager stage(ctx);
+    std::vector<BufPtr> keep;  // packed bitmaps / null counters live until the flush
+    std::vector<int64_t> null_counts(b.cols.size(), 0);
     for (size_t ci = 0; ci < b.cols.size(); ++ci) {
       const Column& col = b.cols[ci];
       if (!col.data) fail(B2_ERR_EXECUTION, "internal: column '" + b.schema.fields[ci].name +
@@ -355,10 +364,21 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
         if (nb) stage.add(hv, col.data->ptr, nb);
         p->buffers = {nullptr, hv};
       }
+      if (col.valid && col.length) {
+        auto counter = dev_alloc(ctx, 16);
+        auto bits = valid_to_bitmap(ctx, col.valid->as<uint8_t>(), col.length, counter->as<int64_t>());
+        void* hb = host_buf(p, (size_t)((col.length + 7) >> 3));
+        stage.add(hb, bits->ptr, (size_t)((col.length + 7) >> 3));
+        stage.add(&null_counts[ci], counter->ptr, 8);
+        p->buffers[0] = hb;
+        keep.push_back(bits);
+        keep.push_back(counter);
+      }
       a->n_buffers = (int64_t)p->buffers.size();
       a->buffers = p->buffers.data();
     }
     stage.flush();
+    for (size_t ci = 0; ci < b.cols.size(); ++ci) top->child_store[ci].null_count = null_counts[ci];
     for (auto& pr : bools) {
       auto* p = static_cast<ArrayPriv*>(top->child_store[pr.first].private_data);
       uint8_t* bits = static_cast<uint8_t*>(const_cast<void*>(p->buffers[1]));

@@ -161,14 +161,17 @@ struct Schema {
 };
 
 // One column resident in HBM.  Fixed width: `data` = values.  Utf8: `data` = int32 offsets[length+1]
-// (starting at 0), `chars` = bytes.  All columns are non-null (TPC-H schema, main.rs:267-360); batches
-// with nulls are rejected at import.
+// (starting at 0), `chars` = bytes.  `valid` (optional) = one byte per row, 1 = value present, 0 = NULL; absent
+// means every row is valid (the TPC-H schema is non-nullable, main.rs:267-360, so the hot kernels never see it).
+// Arrow's bit-packed validity bitmaps are expanded at import and packed again at export (validity.cu).
 struct Column {
   int dtype = 0;
   int64_t length = 0;
   BufPtr data;
   BufPtr chars;
   int64_t chars_len = 0;
+  BufPtr valid;
+  const uint8_t* validity() const { return valid ? valid->as<uint8_t>() : nullptr; }
   template <class T> const T* values() const { return data ? data->as<T>() : nullptr; }
   int64_t num_bytes() const {
     if (dtype == B2_UTF8) return (length + 1) * 4 + chars_len;
@@ -191,6 +194,12 @@ struct Batch {
   }
 };
 using BatchPtr = std::shared_ptr<Batch>;
+// paths that move raw value buffers only (the exchange) refuse nullable data loudly instead of dropping the validity
+inline void require_no_nulls(const Batch& b, const char* where) {
+  for (size_t c = 0; c < b.cols.size(); ++c)
+    if (b.cols[c].valid)
+      fail(B2_ERR_NOT_IMPLEMENTED, std::string(where) + ": column '" + b.schema.fields[c].name + "' holds NULLs");
+}
 
 // Arrow C Data import / export (core.cu)
 Schema schema_from_arrow(const ArrowSchema* s);
@@ -198,6 +207,16 @@ void schema_to_arrow(const Schema& s, ArrowSchema* out);
 // host Arrow struct array -> HBM (async on ctx->stream unless `stream` given); releases `arr`
 BatchPtr batch_from_arrow(Ctx* ctx, const Schema& schema, ArrowArray* arr, cudaStream_t stream = nullptr);
 void batch_to_arrow(const Batch& b, ArrowArray* out);
+
+// validity.cu — null handling shared by the operators (a null predicate is false, SUM / AVG /
+// COUNT skip nulls, null join keys never match)
+BufPtr valid_and(Ctx* ctx, const BufPtr& a, const BufPtr& b, int64_t n);             // null when both are absent
+BufPtr valid_from_bitmap(Ctx* ctx, const uint8_t* host_bits, int64_t bit_off, int64_t n, cudaStream_t st);
+// packs byte validity into an Arrow bitmap in HBM; *nulls_dev (int64 in HBM) receives the null count
+BufPtr valid_to_bitmap(Ctx* ctx, const uint8_t* valid, int64_t n, int64_t* nulls_dev);
+BufPtr valid_gather(Ctx* ctx, const uint8_t* valid, const uint32_t* idx, int64_t m);  // idx 0xFFFFFFFF -> NULL
+BufPtr valid_not(Ctx* ctx, const uint8_t* valid_or_null, int64_t n);                 // IS NULL as a Boolean column
+BufPtr valid_copy(Ctx* ctx, const uint8_t* valid_or_null, int64_t n);                // IS NOT NULL as a Boolean column
 
 inline int grid_for(const Ctx* ctx, int ctas_per_sm, int64_t work_items, int per_cta) {
   int64_t need = (work_items + per_cta - 1) / per_cta;

@@ -1,6 +1,18 @@
 // eval.cu — column-at-a-time expression evaluation over an HBM batch: the unfused path, with the same
 // execution model as DataFusion's PhysicalExpr::evaluate: every node produces a full
 // column; literals are broadcast as scalars.  Arithmetic is IEEE with one rounding per operation.
+//
+// Vocabulary = LogicalExprNode (rust/core/proto/ballista.proto:14-45) with the operator table of
+// rust/core/src/serde/logical_plan/from_proto.rs:937-957: column, literal, And Or Eq NotEq Lt LtEq Gt GtEq Plus Minus
+// Multiply Divide Like, Not, IsNull / IsNotNull, Between / InList (lowered at decode), Case, Cast, Negative, and the
+// numeric / length / case-mapping scalar functions of ballista.proto:80-114.
+//
+// NULLs: a result row is NULL when any operand row is (arrow 4.0's arithmetic / comparison / `and` / `or` kernels,
+// which DataFusion@46161d2 calls, are not Kleene); IS [NOT] NULL reads the validity; CASE treats a NULL condition as
+// false and yields NULL when no branch fires and there is no ELSE.
+#include <limits>
+#include <type_traits>
+
 #include "expr.h"
 #include "table.cuh"
 
@@ -15,11 +27,9 @@ template <class T> struct Operand {
 struct OpAdd { template <class T> __device__ static T run(T a, T b) { return a + b; } };
 struct OpSub { template <class T> __device__ static T run(T a, T b) { return a - b; } };
 struct OpMul { template <class T> __device__ static T run(T a, T b) { return a * b; } };
-struct OpDiv { template <class T> __device__ static T run(T a, T b) { return b == 0 ? 0 : a / b; } };
 template <> __device__ double OpAdd::run<double>(double a, double b) { return __dadd_rn(a, b); }
 template <> __device__ double OpSub::run<double>(double a, double b) { return __dsub_rn(a, b); }
 template <> __device__ double OpMul::run<double>(double a, double b) { return __dmul_rn(a, b); }
-template <> __device__ double OpDiv::run<double>(double a, double b) { return __ddiv_rn(a, b); }
 struct OpLt { template <class T> __device__ static uint8_t run(T a, T b) { return a < b; } };
 struct OpLe { template <class T> __device__ static uint8_t run(T a, T b) { return a <= b; } };
 struct OpGt { template <class T> __device__ static uint8_t run(T a, T b) { return a > b; } };
@@ -34,9 +44,45 @@ __global__ void binary_kernel(Operand<T> a, Operand<T> b, int64_t n, TO* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = (TO)OP::run(a.get(i), b.get(i));
 }
+__global__ void fdiv_kernel(Operand<double> a, Operand<double> b, int64_t n, double* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = __ddiv_rn(a.get(i), b.get(i));
+}
+// Integer division fails the query on a zero divisor (arrow's `divide` kernel returns ArrowError::DivideByZero) and on
+// MIN / -1; rows that are NULL on either side are not looked at.  status: 1 = zero divisor, 2 = overflow.
+template <class T>
+__global__ void idiv_kernel(Operand<T> a, Operand<T> b, const uint8_t* valid, int64_t n, T* out, int* status) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int bad = 0;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    T x = a.get(i), y = b.get(i);
+    if (valid && !valid[i]) {
+      out[i] = 0;
+      continue;
+    }
+    if (y == 0) {
+      bad |= 1;
+      out[i] = 0;
+    } else if (y == (T)-1) {
+      if (x == (T)((T)1 << (8 * sizeof(T) - 1))) bad |= 2;
+      out[i] = (T)(0 - (typename std::make_unsigned<T>::type)x);
+    } else {
+      out[i] = x / y;
+    }
+  }
+  if (bad) atomicOr(status, bad);
+}
 template <class TI, class TO> __global__ void cast_kernel(const TI* in, int64_t n, TO* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = (TO)in[i];
+}
+// Float64 -> integer casts saturate and map NaN to 0 (Rust `as`, which arrow's cast kernel uses)
+template <class TO> __global__ void cast_f64_int_kernel(const double* in, int64_t n, TO* out, double lo, double hi, TO top) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    double v = in[i];
+    out[i] = v != v ? (TO)0 : (v <= lo ? (TO)lo : (v >= hi ? top : (TO)v));
+  }
 }
 template <class T> __global__ void neg_kernel(const T* in, int64_t n, T* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -50,25 +96,143 @@ template <class T> __global__ void fill_kernel(T v, int64_t n, T* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = v;
 }
-// Utf8 equality: column vs literal, or column vs column
-__global__ void str_eq_lit_kernel(const int32_t* off, const uint8_t* chr, int64_t n, const uint8_t* lit, int lit_len,
-                                  bool negate, uint8_t* out) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    int32_t b = off[i], e = off[i + 1];
-    bool eq = (e - b) == lit_len;
-    for (int q = 0; eq && q < lit_len; ++q) eq = chr[b + q] == lit[q];
-    out[i] = eq != negate;
+
+// ---- Utf8 comparisons: = <> < <= > >= by unsigned byte order (Rust str ordering), column vs literal / column ----
+__device__ __forceinline__ bool apply_cmp(int op, int c) {
+  switch (op) {
+    case B2_OP_EQ: return c == 0;
+    case B2_OP_NOTEQ: return c != 0;
+    case B2_OP_LT: return c < 0;
+    case B2_OP_LTEQ: return c <= 0;
+    case B2_OP_GT: return c > 0;
+    default: return c >= 0;
   }
 }
-__global__ void str_eq_col_kernel(const int32_t* off_a, const uint8_t* chr_a, const int32_t* off_b,
-                                  const uint8_t* chr_b, int64_t n, bool negate, uint8_t* out) {
+__device__ __forceinline__ int bytes_cmp(const uint8_t* a, int la, const uint8_t* b, int lb) {
+  int m = la < lb ? la : lb;
+  for (int q = 0; q < m; ++q)
+    if (a[q] != b[q]) return a[q] < b[q] ? -1 : 1;
+  return la == lb ? 0 : (la < lb ? -1 : 1);
+}
+// b_off == nullptr: the right side is the literal (b_chr, lit_len); `swap`: the literal was the LEFT operand
+__global__ void str_cmp_kernel(const int32_t* a_off, const uint8_t* a_chr, const int32_t* b_off, const uint8_t* b_chr,
+                               int lit_len, int op, bool swap, int64_t n, uint8_t* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    int32_t ba = off_a[i], la = off_a[i + 1] - ba, bb = off_b[i], lb = off_b[i + 1] - bb;
-    bool eq = la == lb;
-    for (int q = 0; eq && q < la; ++q) eq = chr_a[ba + q] == chr_b[bb + q];
-    out[i] = eq != negate;
+    int32_t ab = a_off[i], la = a_off[i + 1] - ab;
+    int c;
+    if (b_off) {
+      int32_t bb = b_off[i];
+      c = bytes_cmp(a_chr + ab, la, b_chr + bb, b_off[i + 1] - bb);
+    } else {
+      c = bytes_cmp(a_chr + ab, la, b_chr, lit_len);
+    }
+    out[i] = apply_cmp(op, swap ? -c : c);
+  }
+}
+// SQL LIKE against a literal pattern: % = any run of characters, _ = exactly one character (one UTF-8 code point);
+// no escape character (arrow 4.0's like_utf8_scalar knows none either)
+__global__ void str_like_kernel(const int32_t* off, const uint8_t* chr, const uint8_t* pat, int pl, int64_t n,
+                                uint8_t* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint8_t* s = chr + off[i];
+    const int sl = off[i + 1] - off[i];
+    int si = 0, pi = 0, star = -1, mark = 0;
+    bool ok = true;
+    while (si < sl) {
+      if (pi < pl && pat[pi] == '%') {
+        star = pi++;
+        mark = si;
+      } else if (pi < pl && pat[pi] == '_') {
+        ++si;
+        while (si < sl && (s[si] & 0xC0) == 0x80) ++si;  // rest of a multi-byte code point
+        ++pi;
+      } else if (pi < pl && pat[pi] == s[si]) {
+        ++si;
+        ++pi;
+      } else if (star >= 0) {
+        pi = star + 1;
+        ++mark;
+        while (mark < sl && (s[mark] & 0xC0) == 0x80) ++mark;
+        si = mark;
+      } else {
+        ok = false;
+        break;
+      }
+    }
+    while (ok && pi < pl && pat[pi] == '%') ++pi;
+    out[i] = ok && pi == pl;
+  }
+}
+__global__ void str_len_kernel(const int32_t* off, int64_t n, int32_t* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = off[i + 1] - off[i];
+}
+__global__ void str_case_kernel(const uint8_t* in, int64_t nbytes, bool upper, uint8_t* out, int* status) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  bool non_ascii = false;
+  for (; i < nbytes; i += (int64_t)gridDim.x * blockDim.x) {
+    uint8_t c = in[i];
+    non_ascii |= c >= 0x80;
+    if (upper) out[i] = (c >= 'a' && c <= 'z') ? c - 32 : c;
+    else out[i] = (c >= 'A' && c <= 'Z') ? c + 32 : c;
+  }
+  if (non_ascii) atomicOr(status, 4);
+}
+// a Utf8 literal broadcast to a column (CASE branches, projections)
+__global__ void str_fill_kernel(const uint8_t* lit, int len, int64_t n, int32_t* off, uint8_t* chr) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    off[i] = (int32_t)(i * len);
+    for (int q = 0; q < len; ++q) chr[i * len + q] = lit[q];
+    if (i == n - 1) off[n] = (int32_t)(n * len);
+  }
+}
+
+// ---- scalar functions on Float64 (ScalarFunction, ballista.proto:80-114) ----
+enum {
+  FN_SQRT = 0, FN_SIN, FN_COS, FN_TAN, FN_ASIN, FN_ACOS, FN_ATAN, FN_EXP, FN_LOG, FN_LOG2, FN_LOG10, FN_FLOOR, FN_CEIL,
+  FN_ROUND, FN_TRUNC, FN_ABS, FN_SIGNUM, FN_OCTETLENGTH, FN_CONCAT, FN_LOWER, FN_UPPER
+};
+__global__ void math_kernel(int fn, const double* in, int64_t n, double* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    double x = in[i], r;
+    switch (fn) {
+      case FN_SQRT: r = sqrt(x); break;
+      case FN_SIN: r = sin(x); break;
+      case FN_COS: r = cos(x); break;
+      case FN_TAN: r = tan(x); break;
+      case FN_ASIN: r = asin(x); break;
+      case FN_ACOS: r = acos(x); break;
+      case FN_ATAN: r = atan(x); break;
+      case FN_EXP: r = exp(x); break;
+      case FN_LOG: r = log(x); break;
+      case FN_LOG2: r = log2(x); break;
+      case FN_LOG10: r = log10(x); break;
+      case FN_FLOOR: r = floor(x); break;
+      case FN_CEIL: r = ceil(x); break;
+      case FN_ROUND: r = round(x); break;  // half away from zero, as f64::round
+      case FN_TRUNC: r = trunc(x); break;
+      case FN_ABS: r = fabs(x); break;
+      default: r = x != x ? x : (signbit(x) ? -1.0 : 1.0); break;  // f64::signum: +-0.0 -> +-1.0, NaN -> NaN
+    }
+    out[i] = r;
+  }
+}
+
+// ---- CASE: out = cond (true and not NULL) ? a : b, validity likewise ----
+template <class T>
+__global__ void select_kernel(const uint8_t* cond, const uint8_t* cond_valid, Operand<T> a, const uint8_t* a_valid,
+                              bool a_null, Operand<T> b, const uint8_t* b_valid, bool b_null, int64_t n, T* out,
+                              uint8_t* out_valid) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    bool c = cond[i] != 0 && (!cond_valid || cond_valid[i]);
+    bool v = c ? (!a_null && (!a_valid || a_valid[i])) : (!b_null && (!b_valid || b_valid[i]));
+    out[i] = v ? (c ? a.get(i) : b.get(i)) : T();
+    if (out_valid) out_valid[i] = v;
   }
 }
 
@@ -99,9 +263,17 @@ template <class T> static Operand<T> operand_of(const ExprPtr& e, const Column& 
   return o;
 }
 
+static void check_eval_status(Ctx* ctx, const BufPtr& st) {
+  int host = 0;
+  B2_READBACK(ctx, &host, st->ptr, 4);
+  if (host & 1) fail(B2_ERR_EXECUTION, "Divide by zero");
+  if (host & 2) fail(B2_ERR_EXECUTION, "integer overflow in division");
+  if (host & 4) fail(B2_ERR_NOT_IMPLEMENTED, "lower() / upper() on non-ASCII text");
+}
+
 template <class T>
 static Column eval_binary_typed(Ctx* ctx, int op, const ExprPtr& ea, const Column& ca, const ExprPtr& eb,
-                                const Column& cb, int64_t n, int arith_dtype) {
+                                const Column& cb, int64_t n, int arith_dtype, const BufPtr& valid) {
   Operand<T> a = operand_of<T>(ea, ca), b = operand_of<T>(eb, cb);
   bool cmp = op >= B2_OP_EQ && op <= B2_OP_GTEQ;
   if (cmp) {
@@ -123,19 +295,60 @@ static Column eval_binary_typed(Ctx* ctx, int op, const ExprPtr& ea, const Colum
     case B2_OP_PLUS: launch_binary<T, T, OpAdd>(ctx, a, b, n, o); break;
     case B2_OP_MINUS: launch_binary<T, T, OpSub>(ctx, a, b, n, o); break;
     case B2_OP_MULTIPLY: launch_binary<T, T, OpMul>(ctx, a, b, n, o); break;
-    case B2_OP_DIVIDE: launch_binary<T, T, OpDiv>(ctx, a, b, n, o); break;
+    case B2_OP_DIVIDE:
+      if (!n) break;
+      if constexpr (std::is_same<T, double>::value) {
+        fdiv_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(a, b, n, o);
+        B2_LAUNCHED(ctx);
+      } else {
+        BufPtr st = dev_alloc_zero(ctx, 16);
+        idiv_kernel<T><<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(a, b, valid ? valid->as<uint8_t>() : nullptr, n,
+                                                                         o, st->as<int>());
+        B2_LAUNCHED(ctx);
+        check_eval_status(ctx, st);
+      }
+      break;
     default: fail(B2_ERR_NOT_IMPLEMENTED, "binary operator");
   }
   return out;
 }
 
+static BufPtr upload_bytes(Ctx* ctx, const std::string& s) {
+  auto d = dev_alloc(ctx, s.size() + 16);
+  // the literal's bytes live in the expression node, which outlives the asynchronous copy
+  if (!s.empty()) B2_CUDA(cudaMemcpyAsync(d->ptr, s.data(), s.size(), cudaMemcpyHostToDevice, ctx->stream));
+  return d;
+}
+
+static Column eval_case(Ctx* ctx, const ExprPtr& e, const Batch& batch);
+static Column eval_scalar_fn(Ctx* ctx, const ExprPtr& e, const Batch& batch);
+
 Column eval_expr(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
   int64_t n = batch.num_rows;
   int grid = grid_for(ctx, 8, n, 256);
   switch (e->kind) {
-    case B2_EXPR_COLUMN: return batch.cols[e->col];
+    case B2_EXPR_COLUMN:
+      if (!batch.cols[e->col].data)
+        fail(B2_ERR_EXECUTION, "internal: column '" + batch.schema.fields[e->col].name + "' was pruned upstream");
+      return batch.cols[e->col];
     case B2_EXPR_LITERAL: {
-      if (e->dtype == B2_UTF8) fail(B2_ERR_NOT_IMPLEMENTED, "materialising a Utf8 literal column");
+      if (e->dtype == B2_UTF8) {
+        Column out;
+        out.dtype = B2_UTF8;
+        out.length = n;
+        int64_t total = n * (int64_t)e->s.size();
+        if (total >= (1ll << 31)) fail(B2_ERR_EXECUTION, "Utf8 literal column beyond 2 GiB");
+        out.data = dev_alloc_zero(ctx, (size_t)(n + 1) * 4);
+        out.chars = dev_alloc(ctx, (size_t)total + 16);
+        out.chars_len = total;
+        if (n) {
+          BufPtr lit = upload_bytes(ctx, e->s);
+          str_fill_kernel<<<grid, 256, 0, ctx->stream>>>(lit->as<uint8_t>(), (int)e->s.size(), n,
+                                                        out.data->as<int32_t>(), out.chars->as<uint8_t>());
+          B2_LAUNCHED(ctx);
+        }
+        return out;
+      }
       Column out = new_col(ctx, e->dtype, n);
       if (n) {
         switch (dtype_width(e->dtype)) {
@@ -149,9 +362,19 @@ Column eval_expr(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
       }
       return out;
     }
+    case B2_EXPR_IS_NULL:
+    case B2_EXPR_IS_NOT_NULL: {
+      Column c = eval_expr(ctx, e->ch[0], batch);
+      Column out;
+      out.dtype = B2_BOOL;
+      out.length = n;
+      out.data = e->kind == B2_EXPR_IS_NULL ? valid_not(ctx, c.validity(), n) : valid_copy(ctx, c.validity(), n);
+      return out;
+    }
     case B2_EXPR_NOT: {
       Column c = eval_expr(ctx, e->ch[0], batch);
       Column out = new_col(ctx, B2_BOOL, n);
+      out.valid = c.valid;
       if (n) {
         not_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<uint8_t>(), n, out.data->as<uint8_t>());
         B2_LAUNCHED(ctx);
@@ -161,6 +384,7 @@ Column eval_expr(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
     case B2_EXPR_NEGATIVE: {
       Column c = eval_expr(ctx, e->ch[0], batch);
       Column out = new_col(ctx, e->dtype, n);
+      out.valid = c.valid;
       if (n) {
         if (e->dtype == B2_FLOAT64) neg_kernel<double><<<grid, 256, 0, ctx->stream>>>(c.values<double>(), n, out.data->as<double>());
         else if (e->dtype == B2_INT32) neg_kernel<int32_t><<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), n, out.data->as<int32_t>());
@@ -172,65 +396,223 @@ Column eval_expr(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
     case B2_EXPR_CAST: {
       Column c = eval_expr(ctx, e->ch[0], batch);
       int from = c.dtype, to = e->dtype;
-      if ((from == B2_DATE32 && to == B2_INT32) || (from == B2_INT32 && to == B2_DATE32)) {
-        c.dtype = to;
+      if (from == to) return c;
+      if ((from == B2_DATE32 && to == B2_INT32) || (from == B2_INT32 && to == B2_DATE32) ||
+          (from == B2_INT64 && to == B2_UINT64) || (from == B2_UINT64 && to == B2_INT64) ||
+          (from == B2_BOOL && to == B2_UINT8)) {
+        c.dtype = to;  // same bits
         return c;
       }
       Column out = new_col(ctx, to, n);
+      out.valid = c.valid;
       if (n) {
-        if (from == B2_INT32 && to == B2_INT64) cast_kernel<int32_t, int64_t><<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), n, out.data->as<int64_t>());
-        else if (from == B2_INT32 && to == B2_FLOAT64) cast_kernel<int32_t, double><<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), n, out.data->as<double>());
-        else if (from == B2_INT64 && to == B2_FLOAT64) cast_kernel<int64_t, double><<<grid, 256, 0, ctx->stream>>>(c.values<int64_t>(), n, out.data->as<double>());
-        else if (from == B2_UINT8 && to == B2_INT64) cast_kernel<uint8_t, int64_t><<<grid, 256, 0, ctx->stream>>>(c.values<uint8_t>(), n, out.data->as<int64_t>());
-        else fail(B2_ERR_NOT_IMPLEMENTED, "runtime CAST");
+#define B2_CAST(FROM, TFROM, TO, TTO)                                                                             \
+  if (from == FROM && to == TO) {                                                                                 \
+    cast_kernel<TFROM, TTO><<<grid, 256, 0, ctx->stream>>>(c.values<TFROM>(), n, out.data->as<TTO>());            \
+    done = true;                                                                                                  \
+  }
+        bool done = false;
+        B2_CAST(B2_INT32, int32_t, B2_INT64, int64_t)
+        B2_CAST(B2_INT32, int32_t, B2_UINT64, u64)
+        B2_CAST(B2_INT32, int32_t, B2_FLOAT64, double)
+        B2_CAST(B2_DATE32, int32_t, B2_INT64, int64_t)
+        B2_CAST(B2_INT64, int64_t, B2_FLOAT64, double)
+        B2_CAST(B2_INT64, int64_t, B2_INT32, int32_t)
+        B2_CAST(B2_INT64, int64_t, B2_DATE32, int32_t)
+        B2_CAST(B2_UINT64, u64, B2_FLOAT64, double)
+        B2_CAST(B2_UINT64, u64, B2_INT32, int32_t)
+        B2_CAST(B2_UINT8, uint8_t, B2_INT64, int64_t)
+        B2_CAST(B2_UINT8, uint8_t, B2_INT32, int32_t)
+        B2_CAST(B2_UINT8, uint8_t, B2_UINT64, u64)
+        B2_CAST(B2_UINT8, uint8_t, B2_FLOAT64, double)
+        B2_CAST(B2_BOOL, uint8_t, B2_INT32, int32_t)
+        B2_CAST(B2_BOOL, uint8_t, B2_INT64, int64_t)
+        B2_CAST(B2_BOOL, uint8_t, B2_UINT64, u64)
+        B2_CAST(B2_BOOL, uint8_t, B2_FLOAT64, double)
+#undef B2_CAST
+        if (!done && from == B2_FLOAT64 && to == B2_INT64) {
+          cast_f64_int_kernel<int64_t><<<grid, 256, 0, ctx->stream>>>(c.values<double>(), n, out.data->as<int64_t>(),
+                                                                     -9223372036854775808.0, 9223372036854775808.0, INT64_MAX);
+          done = true;
+        }
+        if (!done && from == B2_FLOAT64 && to == B2_INT32) {
+          cast_f64_int_kernel<int32_t><<<grid, 256, 0, ctx->stream>>>(c.values<double>(), n, out.data->as<int32_t>(),
+                                                                     -2147483648.0, 2147483647.0, INT32_MAX);
+          done = true;
+        }
+        if (!done)
+          fail(B2_ERR_NOT_IMPLEMENTED, std::string("runtime CAST ") + dtype_name(from) + " -> " + dtype_name(to));
         B2_LAUNCHED(ctx);
       }
       return out;
     }
+    case B2_EXPR_CASE: return eval_case(ctx, e, batch);
+    case B2_EXPR_SCALAR_FN: return eval_scalar_fn(ctx, e, batch);
     case B2_EXPR_BINARY: {
       const ExprPtr &ea = e->ch[0], &eb = e->ch[1];
       int t = ea->dtype;  // operands were coerced to a common type at decode
       if (t == B2_UTF8) {
-        bool neg = e->op == B2_OP_NOTEQ;
         Column out = new_col(ctx, B2_BOOL, n);
-        if (!n) return out;
+        if (e->op == B2_OP_LIKE) {
+          if (!eb->is_literal()) fail(B2_ERR_NOT_IMPLEMENTED, "LIKE with a non-literal pattern");
+          Column c = eval_expr(ctx, ea, batch);
+          out.valid = c.valid;
+          if (n) {
+            BufPtr pat = upload_bytes(ctx, eb->s);
+            str_like_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), c.chars->as<uint8_t>(),
+                                                          pat->as<uint8_t>(), (int)eb->s.size(), n, out.data->as<uint8_t>());
+            B2_LAUNCHED(ctx);
+          }
+          return out;
+        }
         if (ea->is_literal() || eb->is_literal()) {
-          const ExprPtr& lit = ea->is_literal() ? ea : eb;
-          Column c = eval_expr(ctx, ea->is_literal() ? eb : ea, batch);
-          auto dlit = dev_alloc(ctx, lit->s.size() + 16);
-          // literal bytes must outlive the async copy: keep them in the expression node
-          B2_CUDA(cudaMemcpyAsync(dlit->ptr, lit->s.data(), lit->s.size(), cudaMemcpyHostToDevice, ctx->stream));
-          str_eq_lit_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), c.chars->as<uint8_t>(), n,
-                                                          dlit->as<uint8_t>(), (int)lit->s.size(), neg,
-                                                          out.data->as<uint8_t>());
+          const bool swap = ea->is_literal();
+          const ExprPtr& lit = swap ? ea : eb;
+          Column c = eval_expr(ctx, swap ? eb : ea, batch);
+          out.valid = c.valid;
+          if (n) {
+            BufPtr dlit = upload_bytes(ctx, lit->s);
+            str_cmp_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), c.chars->as<uint8_t>(), nullptr,
+                                                         dlit->as<uint8_t>(), (int)lit->s.size(), e->op, swap, n,
+                                                         out.data->as<uint8_t>());
+            B2_LAUNCHED(ctx);
+          }
         } else {
           Column a = eval_expr(ctx, ea, batch), b = eval_expr(ctx, eb, batch);
-          str_eq_col_kernel<<<grid, 256, 0, ctx->stream>>>(a.values<int32_t>(), a.chars->as<uint8_t>(),
-                                                          b.values<int32_t>(), b.chars->as<uint8_t>(), n, neg,
-                                                          out.data->as<uint8_t>());
+          out.valid = valid_and(ctx, a.valid, b.valid, n);
+          if (n) {
+            str_cmp_kernel<<<grid, 256, 0, ctx->stream>>>(a.values<int32_t>(), a.chars->as<uint8_t>(),
+                                                         b.values<int32_t>(), b.chars->as<uint8_t>(), 0, e->op, false, n,
+                                                         out.data->as<uint8_t>());
+            B2_LAUNCHED(ctx);
+          }
         }
-        B2_LAUNCHED(ctx);
         return out;
       }
       Column ca, cb;
       if (!ea->is_literal()) ca = eval_expr(ctx, ea, batch);
       if (!eb->is_literal()) cb = eval_expr(ctx, eb, batch);
+      BufPtr valid = valid_and(ctx, ca.valid, cb.valid, n);
+      Column out;
       if (e->op == B2_OP_AND || e->op == B2_OP_OR) {
-        Column out = new_col(ctx, B2_BOOL, n);
+        out = new_col(ctx, B2_BOOL, n);
         Operand<uint8_t> a = operand_of<uint8_t>(ea, ca), b = operand_of<uint8_t>(eb, cb);
         if (e->op == B2_OP_AND) launch_binary<uint8_t, uint8_t, OpAnd>(ctx, a, b, n, out.data->as<uint8_t>());
         else launch_binary<uint8_t, uint8_t, OpOr>(ctx, a, b, n, out.data->as<uint8_t>());
-        return out;
+      } else {
+        switch (t) {
+          case B2_INT32: case B2_DATE32: out = eval_binary_typed<int32_t>(ctx, e->op, ea, ca, eb, cb, n, e->dtype, valid); break;
+          case B2_INT64: out = eval_binary_typed<int64_t>(ctx, e->op, ea, ca, eb, cb, n, e->dtype, valid); break;
+          case B2_FLOAT64: out = eval_binary_typed<double>(ctx, e->op, ea, ca, eb, cb, n, e->dtype, valid); break;
+          default: fail(B2_ERR_NOT_IMPLEMENTED, std::string("binary operator on ") + dtype_name(t));
+        }
       }
-      switch (t) {
-        case B2_INT32: case B2_DATE32: return eval_binary_typed<int32_t>(ctx, e->op, ea, ca, eb, cb, n, e->dtype);
-        case B2_INT64: return eval_binary_typed<int64_t>(ctx, e->op, ea, ca, eb, cb, n, e->dtype);
-        case B2_FLOAT64: return eval_binary_typed<double>(ctx, e->op, ea, ca, eb, cb, n, e->dtype);
-        default: fail(B2_ERR_NOT_IMPLEMENTED, std::string("binary operator on ") + dtype_name(t));
-      }
+      out.valid = valid;
+      return out;
     }
   }
   fail(B2_ERR_NOT_IMPLEMENTED, "expression kind " + std::to_string(e->kind));
+}
+
+// A Boolean predicate as a filter mask: NULL counts as false (FilterExec), so the result has no validity
+Column eval_predicate(Ctx* ctx, const ExprPtr& pred, const Batch& batch) {
+  Column m = eval_expr(ctx, pred, batch);
+  if (m.valid) {
+    m.data = valid_and(ctx, m.data, m.valid, batch.num_rows);
+    m.valid = nullptr;
+  }
+  return m;
+}
+
+// CASE [base] WHEN w1 THEN t1 ... [ELSE e] END.  children: [base?] (when, then)* [else?]; op bit 0 = base present,
+// bit 1 = ELSE present.  With a base the WHEN values were rewritten to `base = when` at decode.  Branches are folded
+// from the last to the first: out = when_k ? then_k : out.
+template <class T>
+static Column case_typed(Ctx* ctx, const ExprPtr& e, const Batch& batch, size_t first, size_t n_when, bool has_else) {
+  const int64_t n = batch.num_rows;
+  Column acc;  // value so far (else branch, or NULL)
+  bool acc_null = true, acc_lit = false;
+  ExprPtr acc_e;
+  if (has_else) {
+    acc_e = e->ch.back();
+    acc_null = false;
+    if (acc_e->is_literal()) acc_lit = true;
+    else acc = eval_expr(ctx, acc_e, batch);
+  }
+  for (size_t k = n_when; k-- > 0;) {
+    const ExprPtr& w = e->ch[first + 2 * k];
+    const ExprPtr& t = e->ch[first + 2 * k + 1];
+    Column cond = eval_expr(ctx, w, batch);
+    Column tv;
+    if (!t->is_literal()) tv = eval_expr(ctx, t, batch);
+    Operand<T> a = operand_of<T>(t, tv);
+    Operand<T> b;
+    if (acc_null) b = Operand<T>{nullptr, T()};
+    else if (acc_lit) b = operand_of<T>(acc_e, acc);
+    else b = Operand<T>{acc.values<T>(), T()};
+    Column out = new_col(ctx, e->dtype, n);
+    const bool need_valid = acc_null || acc.valid || tv.valid;
+    if (need_valid) out.valid = dev_alloc(ctx, (size_t)n + 16);
+    if (n) {
+      select_kernel<T><<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(
+          cond.values<uint8_t>(), cond.validity(), a, tv.validity(), false, b, acc_null ? nullptr : acc.validity(),
+          acc_null, n, out.data->as<T>(), need_valid ? out.valid->as<uint8_t>() : nullptr);
+      B2_LAUNCHED(ctx);
+    }
+    acc = out;
+    acc_null = false;
+    acc_lit = false;
+  }
+  return acc;
+}
+static Column eval_case(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
+  const bool has_base = e->op & 1, has_else = e->op & 2;
+  (void)has_base;  // folded into the WHEN conditions at decode
+  size_t n_when = (e->ch.size() - (has_else ? 1 : 0)) / 2;
+  switch (e->dtype) {
+    case B2_INT32: case B2_DATE32: return case_typed<int32_t>(ctx, e, batch, 0, n_when, has_else);
+    case B2_INT64: case B2_UINT64: return case_typed<int64_t>(ctx, e, batch, 0, n_when, has_else);
+    case B2_FLOAT64: return case_typed<double>(ctx, e, batch, 0, n_when, has_else);
+    case B2_BOOL: case B2_UINT8: return case_typed<uint8_t>(ctx, e, batch, 0, n_when, has_else);
+  }
+  fail(B2_ERR_NOT_IMPLEMENTED, std::string("CASE producing ") + dtype_name(e->dtype));
+}
+
+static Column eval_scalar_fn(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
+  const int64_t n = batch.num_rows;
+  const int grid = grid_for(ctx, 8, n, 256);
+  Column c = eval_expr(ctx, e->ch[0], batch);
+  if (e->op <= FN_SIGNUM) {
+    Column out = new_col(ctx, B2_FLOAT64, n);
+    out.valid = c.valid;
+    if (n) {
+      math_kernel<<<grid, 256, 0, ctx->stream>>>(e->op, c.values<double>(), n, out.data->as<double>());
+      B2_LAUNCHED(ctx);
+    }
+    return out;
+  }
+  if (e->op == FN_OCTETLENGTH) {
+    Column out = new_col(ctx, B2_INT32, n);
+    out.valid = c.valid;
+    if (n) {
+      str_len_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), n, out.data->as<int32_t>());
+      B2_LAUNCHED(ctx);
+    }
+    return out;
+  }
+  if (e->op == FN_LOWER || e->op == FN_UPPER) {
+    Column out = c;  // same offsets
+    out.chars = dev_alloc(ctx, (size_t)c.chars_len + 16);
+    if (c.chars_len) {
+      BufPtr st = dev_alloc_zero(ctx, 16);
+      str_case_kernel<<<grid_for(ctx, 8, c.chars_len, 256), 256, 0, ctx->stream>>>(
+          c.chars->as<uint8_t>(), c.chars_len, e->op == FN_UPPER, out.chars->as<uint8_t>(), st->as<int>());
+      B2_LAUNCHED(ctx);
+      check_eval_status(ctx, st);
+    }
+    return out;
+  }
+  fail(B2_ERR_NOT_IMPLEMENTED, "scalar function " + std::to_string(e->op));
 }
 
 }  // namespace b2

@@ -59,9 +59,21 @@ static ExprPtr make_cast(ExprPtr c, int target) {
     fail(B2_ERR_NOT_IMPLEMENTED,
          std::string("CAST of ") + dtype_name(c->dtype) + " literal to " + dtype_name(target));
   }
-  bool ok = (c->dtype == B2_INT32 && (target == B2_INT64 || target == B2_FLOAT64)) ||
-            (c->dtype == B2_INT64 && target == B2_FLOAT64) || (c->dtype == B2_DATE32 && target == B2_INT32) ||
-            (c->dtype == B2_INT32 && target == B2_DATE32) || (c->dtype == B2_UINT8 && target == B2_INT64);
+  auto in = [&](std::initializer_list<int> l) {
+    for (int t : l)
+      if (t == target) return true;
+    return false;
+  };
+  bool ok = false;  // the pairs eval.cu has a kernel (or a reinterpretation) for
+  switch (c->dtype) {
+    case B2_INT32: ok = in({B2_INT64, B2_UINT64, B2_FLOAT64, B2_DATE32}); break;
+    case B2_DATE32: ok = in({B2_INT32, B2_INT64}); break;
+    case B2_INT64: ok = in({B2_FLOAT64, B2_INT32, B2_DATE32, B2_UINT64}); break;
+    case B2_UINT64: ok = in({B2_FLOAT64, B2_INT32, B2_INT64}); break;
+    case B2_UINT8: ok = in({B2_INT64, B2_INT32, B2_UINT64, B2_FLOAT64}); break;
+    case B2_BOOL: ok = in({B2_INT32, B2_INT64, B2_UINT64, B2_FLOAT64, B2_UINT8}); break;
+    case B2_FLOAT64: ok = in({B2_INT64, B2_INT32}); break;
+  }
   if (!ok)
     fail(B2_ERR_NOT_IMPLEMENTED, std::string("CAST ") + dtype_name(c->dtype) + " -> " + dtype_name(target));
   auto e = std::make_shared<Expr>();
@@ -95,6 +107,10 @@ static ExprPtr fold_binary(int op, const ExprPtr& a, const ExprPtr& b, int t) {
     switch (op) {
       case B2_OP_EQ: return mk_lit_i(B2_BOOL, c == 0);
       case B2_OP_NOTEQ: return mk_lit_i(B2_BOOL, c != 0);
+      case B2_OP_LT: return mk_lit_i(B2_BOOL, c < 0);
+      case B2_OP_LTEQ: return mk_lit_i(B2_BOOL, c <= 0);
+      case B2_OP_GT: return mk_lit_i(B2_BOOL, c > 0);
+      case B2_OP_GTEQ: return mk_lit_i(B2_BOOL, c >= 0);
     }
   } else if (t == B2_BOOL) {
     switch (op) {
@@ -130,6 +146,14 @@ static ExprPtr make_binary(int op, ExprPtr a, ExprPtr b) {
   bool cmp = op >= B2_OP_EQ && op <= B2_OP_GTEQ;
   bool arith = op >= B2_OP_PLUS && op <= B2_OP_DIVIDE;
   int t = 0;
+  if (op == B2_OP_LIKE) {
+    if (a->dtype != B2_UTF8 || b->dtype != B2_UTF8) fail(B2_ERR_EXECUTION, "LIKE needs Utf8 operands");
+    if (!b->is_literal()) fail(B2_ERR_NOT_IMPLEMENTED, "LIKE with a non-literal pattern");
+    if (a->is_literal()) fail(B2_ERR_NOT_IMPLEMENTED, "LIKE over a literal value");
+    e->dtype = B2_BOOL;
+    e->ch = {a, b};
+    return e;
+  }
   if (logical) {
     if (a->dtype != B2_BOOL || b->dtype != B2_BOOL)
       fail(B2_ERR_EXECUTION, "AND/OR need Boolean operands");
@@ -149,12 +173,12 @@ static ExprPtr make_binary(int op, ExprPtr a, ExprPtr b) {
           t = B2_INT32;
       }
     } else if (a->dtype == B2_DATE32 || b->dtype == B2_DATE32) {
+      // the reference has none either: DataFusion@46161d2's binary coercion accepts numeric operands only
       if (arith) fail(B2_ERR_NOT_IMPLEMENTED, "arithmetic on Date32");
       t = B2_DATE32;
     } else if (a->dtype == B2_UTF8 && b->dtype == B2_UTF8) {
-      if (!(op == B2_OP_EQ || op == B2_OP_NOTEQ))
-        fail(B2_ERR_NOT_IMPLEMENTED, "only = and <> are implemented on Utf8");
-      t = B2_UTF8;
+      if (!cmp) fail(B2_ERR_EXECUTION, "arithmetic on Utf8");
+      t = B2_UTF8;  // byte-wise ordering (Rust str comparison)
     } else if (a->dtype == B2_BOOL && b->dtype == B2_BOOL && (op == B2_OP_EQ || op == B2_OP_NOTEQ)) {
       fail(B2_ERR_NOT_IMPLEMENTED, "Boolean equality");
     } else {
@@ -228,8 +252,20 @@ ExprPtr decode_expr(const b2_expr* ex, const Schema& input) {
         break;
       }
       case B2_EXPR_NOT: st.push_back(make_not(pop())); break;
-      case B2_EXPR_IS_NULL: pop(); st.push_back(mk_lit_i(B2_BOOL, 0)); break;      // inputs are non-null
-      case B2_EXPR_IS_NOT_NULL: pop(); st.push_back(mk_lit_i(B2_BOOL, 1)); break;
+      case B2_EXPR_IS_NULL:
+      case B2_EXPR_IS_NOT_NULL: {
+        ExprPtr c = pop();
+        if (c->is_literal()) {  // literals on this path are never NULL
+          st.push_back(mk_lit_i(B2_BOOL, n.kind == B2_EXPR_IS_NOT_NULL));
+          break;
+        }
+        auto e = std::make_shared<Expr>();
+        e->kind = n.kind;
+        e->dtype = B2_BOOL;
+        e->ch = {c};
+        st.push_back(e);
+        break;
+      }
       case B2_EXPR_CAST: st.push_back(make_cast(pop(), n.dtype)); break;
       case B2_EXPR_NEGATIVE: {
         ExprPtr c = pop();
@@ -262,7 +298,72 @@ ExprPtr decode_expr(const b2_expr* ex, const Schema& input) {
         st.push_back(n.op ? make_not(r) : r);
         break;
       }
-      case B2_EXPR_CASE: fail(B2_ERR_NOT_IMPLEMENTED, "CASE expressions");
+      case B2_EXPR_CASE: {
+        // children: [base] (when, then)* [else]   (CaseNode, ballista.proto:141-150)
+        const bool has_base = n.op & 1, has_else = n.op & 2;
+        int nc = n.nchildren;
+        int pairs = nc - (has_base ? 1 : 0) - (has_else ? 1 : 0);
+        if (pairs < 2 || (pairs & 1) || (int)st.size() < nc) fail(B2_ERR_INVALID_ARG, "malformed CASE expression");
+        std::vector<ExprPtr> items(nc);
+        for (int q = nc - 1; q >= 0; --q) items[q] = pop();
+        size_t first = has_base ? 1 : 0;
+        auto e = std::make_shared<Expr>();
+        e->kind = B2_EXPR_CASE;
+        e->op = has_else ? 2 : 0;
+        // result type: the common type of the THEN / ELSE values
+        int t = 0;
+        auto widen = [&](const ExprPtr& v) {
+          if (v->dtype == B2_UTF8) fail(B2_ERR_NOT_IMPLEMENTED, "CASE producing Utf8");
+          if (!t) t = v->dtype;
+          else if (t != v->dtype) {
+            if (!is_num(t) || !is_num(v->dtype))
+              fail(B2_ERR_EXECUTION, std::string("CASE branches of types ") + dtype_name(t) + " and " + dtype_name(v->dtype));
+            t = num_rank(t) >= num_rank(v->dtype) ? t : v->dtype;
+          }
+        };
+        for (int q = 0; q < pairs / 2; ++q) widen(items[first + 2 * q + 1]);
+        if (has_else) widen(items.back());
+        if (t == B2_UINT8) t = B2_INT64;
+        for (int q = 0; q < pairs / 2; ++q) {
+          ExprPtr w = items[first + 2 * q];
+          if (has_base) w = make_binary(B2_OP_EQ, items[0], w);  // CASE x WHEN v  ==  CASE WHEN x = v
+          if (w->dtype != B2_BOOL) fail(B2_ERR_EXECUTION, "CASE WHEN needs a Boolean condition");
+          e->ch.push_back(w);
+          e->ch.push_back(make_cast(items[first + 2 * q + 1], t));
+        }
+        if (has_else) e->ch.push_back(make_cast(items.back(), t));
+        e->dtype = t;
+        st.push_back(e);
+        break;
+      }
+      case B2_EXPR_SCALAR_FN: {
+        if (n.nchildren != 1 || st.empty())
+          fail(B2_ERR_NOT_IMPLEMENTED, "scalar function " + std::to_string(n.op) + " with " + std::to_string(n.nchildren) +
+                                           " arguments");
+        ExprPtr c = pop();
+        auto e = std::make_shared<Expr>();
+        e->kind = B2_EXPR_SCALAR_FN;
+        e->op = n.op;
+        if (n.op >= 0 && n.op <= 16) {  // SQRT .. SIGNUM: Float64 in, Float64 out (math_unary_function)
+          if (!is_num(c->dtype)) fail(B2_ERR_EXECUTION, "math function over a non-numeric value");
+          c = make_cast(c, B2_FLOAT64);
+          e->dtype = B2_FLOAT64;
+        } else if (n.op == 17) {  // OCTETLENGTH
+          if (c->dtype != B2_UTF8) fail(B2_ERR_EXECUTION, "octet_length needs a Utf8 argument");
+          e->dtype = B2_INT32;
+        } else if (n.op == 19 || n.op == 20) {  // LOWER / UPPER
+          if (c->dtype != B2_UTF8) fail(B2_ERR_EXECUTION, "lower / upper need a Utf8 argument");
+          e->dtype = B2_UTF8;
+        } else {
+          fail(B2_ERR_NOT_IMPLEMENTED, "scalar function " + std::to_string(n.op) +
+                                           " (implemented: sqrt sin cos tan asin acos atan exp ln log2 log10 floor ceil "
+                                           "round trunc abs signum octet_length lower upper)");
+        }
+        if (c->is_literal() && c->dtype != B2_FLOAT64) fail(B2_ERR_NOT_IMPLEMENTED, "scalar function over a literal");
+        e->ch = {c};
+        st.push_back(e);
+        break;
+      }
       default: fail(B2_ERR_INVALID_ARG, "unknown expression node kind " + std::to_string(n.kind));
     }
   }
@@ -286,6 +387,7 @@ static const char* op_text(int op) {
     case B2_OP_MINUS: return "sub";
     case B2_OP_MULTIPLY: return "mul";
     case B2_OP_DIVIDE: return "div";
+    case B2_OP_LIKE: return "like";
   }
   return "?";
 }
@@ -304,6 +406,14 @@ std::string expr_to_string(const ExprPtr& e, const Schema& input) {
     case B2_EXPR_NOT: return "not(" + expr_to_string(e->ch[0], input) + ")";
     case B2_EXPR_CAST: return std::string("cast_") + dtype_name(e->dtype) + "(" + expr_to_string(e->ch[0], input) + ")";
     case B2_EXPR_NEGATIVE: return "neg(" + expr_to_string(e->ch[0], input) + ")";
+    case B2_EXPR_IS_NULL: return "isnull(" + expr_to_string(e->ch[0], input) + ")";
+    case B2_EXPR_IS_NOT_NULL: return "isnotnull(" + expr_to_string(e->ch[0], input) + ")";
+    case B2_EXPR_CASE:
+    case B2_EXPR_SCALAR_FN: {
+      std::string t = e->kind == B2_EXPR_CASE ? "case" + std::to_string(e->op) + "(" : "fn" + std::to_string(e->op) + "(";
+      for (size_t k = 0; k < e->ch.size(); ++k) t += (k ? "," : "") + expr_to_string(e->ch[k], input);
+      return t + ")";
+    }
   }
   return "?";
 }
@@ -369,6 +479,11 @@ std::string expr_signature(const ExprPtr& e, SlotBinder& b) {
       if (e->dtype == B2_FLOAT64) return "f64(" + expr_signature(e->ch[0], b) + ")";
       if (e->dtype == B2_INT32 || e->dtype == B2_DATE32) return expr_signature(e->ch[0], b);  // reinterpret
       return "cast" + std::to_string(e->dtype) + "(" + expr_signature(e->ch[0], b) + ")";
+    default: {  // IS [NOT] NULL, CASE, scalar functions: no fused form
+      std::string t = "x" + std::to_string(e->kind) + "_" + std::to_string(e->op) + "(";
+      for (size_t k = 0; k < e->ch.size(); ++k) t += (k ? "," : "") + expr_signature(e->ch[k], b);
+      return t + ")";
+    }
   }
   return "?";
 }

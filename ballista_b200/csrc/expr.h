@@ -57,5 +57,7 @@ void expr_columns(const ExprPtr& e, std::vector<char>& used);
 
 // column-at-a-time evaluation over an HBM batch (the unfused path; eval.cu)
 Column eval_expr(Ctx* ctx, const ExprPtr& e, const Batch& batch);
+// a Boolean predicate as a filter mask (one byte per row, NULL -> 0)
+Column eval_predicate(Ctx* ctx, const ExprPtr& pred, const Batch& batch);
 
 }  // namespace b2

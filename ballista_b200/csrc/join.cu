@@ -176,6 +176,7 @@ bool compile_row_pred(const ExprPtr& pred, const Batch& batch, RowPred* out) {
     }
     if (c->kind != B2_EXPR_COLUMN || l->kind != B2_EXPR_LITERAL) return false;
     const Column& col = batch.cols[c->col];
+    if (col.valid) return false;  // NULLs: the generic mask path folds them to false
     int k = rp.n++;
     rp.col[k] = col.data->ptr;
     rp.ilo[k] = 0;

@@ -13,7 +13,9 @@ namespace b2 {
 
 // ---- kernel-file helpers ----
 BufPtr mask_to_indices(Ctx* ctx, const uint8_t* mask, int64_t n, int64_t* count);        // take.cu
-Column take_column(Ctx* ctx, const Column& c, const uint32_t* idx, int64_t m);            // take.cu
+// idx 0xFFFFFFFF = null-extended row (outer joins); pass null_extended when the index vector may hold such entries
+Column take_column(Ctx* ctx, const Column& c, const uint32_t* idx, int64_t m, bool null_extended = false);  // take.cu
+Column null_column(Ctx* ctx, int dtype, int64_t n);                                       // take.cu
 BatchPtr take_batch(Ctx* ctx, const Batch& b, const uint32_t* idx, int64_t m);            // take.cu
 BatchPtr concat_batches(Ctx* ctx, const Schema& schema, const std::vector<BatchPtr>& b);  // take.cu
 BatchPtr empty_batch(Ctx* ctx, const Schema& schema);                                      // take.cu
@@ -142,6 +144,21 @@ struct Op {
   // true when output partition r exists only on rank r (the plan sits above an exchange): consumers then
   // execute their own rank's partition instead of iterating over all of them
   virtual bool per_rank_partitions() const { return !children.empty() && children[0]->per_rank_partitions(); }
+  // When this operator's output partitions are those of a hash exchange over plain columns (a communicator-attached
+  // RepartitionExec, seen through operators that neither move rows nor renumber columns): the key columns and the
+  // partition count.  A HashJoinExec joins partition-wise only when BOTH inputs report exchanges on its own keys.
+  virtual bool exchange_on(std::vector<int>* key_cols, int* n_out) const {
+    (void)key_cols;
+    (void)n_out;
+    return false;
+  }
+  // Changes whenever the data a leaf holds changes (MemoryExec: add / clear); operators that cache work across
+  // execute() calls (join build table, repartition outputs) recompute when their subtree's version moved.
+  virtual uint64_t version() const {
+    uint64_t v = 1469598103934665603ull;
+    for (auto& c : children) v = (v ^ c->version()) * 1099511628211ull;
+    return v;
+  }
   int n_partitions() const {
     int s, n;
     partitioning(&s, &n);

@@ -15,15 +15,49 @@ namespace b2 {
 bool op_is_filter(Op* op, ExprPtr* pred);
 bool op_is_coalesce(Op* op);
 
+// values with their NULL rows zeroed (so that they add nothing) and validity widened to a count column
+__global__ void zero_nulls_kernel(const u64* in, const uint8_t* valid, int64_t n, u64* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = valid[i] ? in[i] : 0ull;
+}
+__global__ void valid_to_u64_kernel(const uint8_t* valid, int64_t n, u64* out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = valid[i] != 0;
+}
+static BufPtr zero_nulls(Ctx* ctx, const Column& c) {  // 8-byte values
+  auto out = dev_alloc(ctx, (size_t)c.length * 8 + 16);
+  if (c.length) {
+    zero_nulls_kernel<<<grid_for(ctx, 8, c.length, 256), 256, 0, ctx->stream>>>(c.values<u64>(), c.validity(), c.length,
+                                                                               out->as<u64>());
+    B2_LAUNCHED(ctx);
+  }
+  return out;
+}
+static BufPtr valid_to_u64(Ctx* ctx, const Column& c) {
+  auto out = dev_alloc(ctx, (size_t)c.length * 8 + 16);
+  if (c.length) {
+    valid_to_u64_kernel<<<grid_for(ctx, 8, c.length, 256), 256, 0, ctx->stream>>>(c.validity(), c.length, out->as<u64>());
+    B2_LAUNCHED(ctx);
+  }
+  return out;
+}
+
 struct HashAggregateExec : Op {
   int mode = B2_AGG_PARTIAL;
   std::vector<ExprPtr> groups;
   std::vector<AggSpec> aggs;
   Schema out;
   KeyLayout layout;
-  // Partial: distinct argument expressions (CSE across aggregates) and each aggregate's accumulator index
+  // Partial: distinct argument expressions (CSE across aggregates).  Float64 arguments of SUM / AVG accumulate in the
+  // table's f64 accumulators, Int64 arguments of SUM in its u64 accumulators (two's complement: the same addition),
+  // COUNT(x) arguments only contribute their validity.
+  enum { ARG_F64 = 0, ARG_I64 = 1, ARG_COUNT = 2 };
   std::vector<ExprPtr> args;
-  std::vector<int> agg_acc;  // per aggregate: index into args (SUM/AVG), -1 for COUNT
+  std::vector<int> arg_kind;
+  std::vector<int> agg_arg;  // per aggregate: index into args, -1 for COUNT(literal)
+  // the argument reads a column its schema declares nullable: the column-at-a-time path then always counts the
+  // argument's non-null rows, whichever batch the first NULL arrives in
+  std::vector<char> arg_nullable;
   bool disable_fusion = false;
 
   const char* name() const override { return "HashAggregateExec"; }
@@ -46,50 +80,79 @@ struct HashAggregateExec : Op {
     return s;
   }
 
-  BatchPtr emit(AggRunner& r, bool partial, const std::vector<int>& sum_idx, const std::vector<int>& cnt_idx);
+  // where each aggregate's state lives in the group table
+  struct Slots {
+    int acc = -1;    // f64 accumulator (SUM / AVG over Float64)
+    int isum = -1;   // u64 accumulator holding an integer SUM
+    int cnt = -1;    // u64 accumulator: COUNT result / AVG divisor
+    int vcnt = -1;   // u64 accumulator: non-null inputs seen (validity of a SUM; -1 = never NULL)
+    bool avg_null = false;  // AVG: NULL when cnt == 0
+  };
+  BatchPtr null_row();
+  // speculative = the runner ran consume_unchecked(): returns null when the batch has to be redone
+  BatchPtr emit(AggRunner& r, bool partial, const std::vector<Slots>& sl, bool speculative, int* status_out);
   BatchPtr run_partial(int partition);
   BatchPtr run_final(int partition);
 };
 
-// ---- output assembly shared by both modes.  sum_idx / cnt_idx: per aggregate accumulator indices ----
-BatchPtr HashAggregateExec::emit(AggRunner& r, bool partial, const std::vector<int>& sum_idx,
-                                 const std::vector<int>& cnt_idx) {
-  BufPtr slots;
-  int64_t ng = r.finish(&slots);
+// An ungrouped aggregate over no rows still yields one row: COUNT = 0, SUM / AVG = NULL (DataFusion's
+// accumulators start as ScalarValue::Float64(None)).  Partial mode: the AVG state is (count 0, sum NULL).
+BatchPtr HashAggregateExec::null_row() {
   auto b = std::make_shared<Batch>();
   b->ctx = ctx;
   b->schema = out;
-  if (groups.empty() && ng == 0) {
-    // ungrouped aggregate over empty input still yields one row; sums are 0, counts 0
-    // (the reference yields NULL sums; this path has no validity bitmaps)
-    b->num_rows = 1;
-    for (auto& f : out.fields) {
-      Column c;
-      c.dtype = f.dtype;
-      c.length = 1;
-      c.data = dev_alloc_zero(ctx, 16);
-      b->cols.push_back(c);
+  b->num_rows = 1;
+  for (auto& f : out.fields) {
+    Column c;
+    c.dtype = f.dtype;
+    c.length = 1;
+    c.data = dev_alloc_zero(ctx, 16);
+    const bool is_count = f.dtype == B2_UINT64 && f.name.size() >= 7 && f.name.compare(f.name.size() - 7, 7, "[count]") == 0;
+    bool counts = mode == B2_AGG_PARTIAL ? is_count : false;
+    if (mode == B2_AGG_FINAL) {
+      size_t a = &f - &out.fields[0];
+      counts = aggs[a].fn == B2_AGG_COUNT;
     }
-    return b;
+    if (!counts) c.valid = dev_alloc_zero(ctx, 16);  // one NULL
+    b->cols.push_back(c);
   }
-  b->num_rows = ng;
-  EmitPlan ep(ctx, *r.main, slots, ng);
+  return b;
+}
+
+// ---- output assembly shared by both modes ----
+BatchPtr HashAggregateExec::emit(AggRunner& r, bool partial, const std::vector<Slots>& sl, bool speculative,
+                                 int* status_out) {
+  int64_t exact = speculative ? -1 : r.finish();
+  if (!speculative && groups.empty() && exact == 0) return null_row();
+  const int64_t bound = speculative ? std::min<int64_t>((int64_t)r.main->cap, 32768) : exact;
+  EmitPlan ep(ctx, *r.main, bound);
   for (size_t g = 0; g < groups.size(); ++g) ep.key(layout.parts[g]);
   for (size_t a = 0; a < aggs.size(); ++a) {
+    const Slots& s = sl[a];
     switch (aggs[a].fn) {
-      case B2_AGG_SUM: ep.sum(sum_idx[a]); break;
-      case B2_AGG_COUNT: ep.count(cnt_idx[a]); break;
+      case B2_AGG_SUM:
+        if (s.isum >= 0) ep.isum(s.isum, out.fields[ep.cols.size()].dtype, s.vcnt);
+        else ep.sum(s.acc, s.vcnt);
+        break;
+      case B2_AGG_COUNT: ep.count(s.cnt); break;
       case B2_AGG_AVG:
         if (partial) {
-          ep.count(cnt_idx[a]);
-          ep.sum(sum_idx[a]);
+          ep.count(s.cnt);
+          ep.sum(s.acc, s.avg_null ? s.cnt : -1);
         } else {
-          ep.avg(sum_idx[a], cnt_idx[a]);
+          ep.avg(s.acc, s.cnt, s.avg_null);
         }
         break;
     }
   }
-  b->cols = ep.run();
+  int64_t ng = 0;
+  if (!ep.run(exact, r.status->as<int>(), &ng, status_out)) return nullptr;
+  if (groups.empty() && ng == 0) return null_row();
+  auto b = std::make_shared<Batch>();
+  b->ctx = ctx;
+  b->schema = out;
+  b->num_rows = ng;
+  b->cols = std::move(ep.cols);
   if (partial && !groups.empty()) b->unique_key_cols = (int)groups.size();
   return b;
 }
@@ -113,58 +176,165 @@ BatchPtr HashAggregateExec::run_partial(int partition) {
       src = probe->children[0].get();
     }
   }
+  bool reject_all = false;
   if (pred && pred->is_literal()) {
-    if (!pred->i) fail(B2_ERR_NOT_IMPLEMENTED, "constant-false filter under an aggregate");
+    reject_all = !pred->i;  // constant-false filter: no row reaches the aggregate
     pred = nullptr;
   }
+  // fused kernels take Float64 SUM / AVG arguments and count rows; anything else goes column-at-a-time
+  std::vector<ExprPtr> fargs;
+  bool fusable_shape = !disable_fusion && !getenv("B2_DISABLE_FUSION");
+  for (size_t k = 0; k < args.size(); ++k) {
+    if (arg_kind[k] == ARG_F64) fargs.push_back(args[k]);
+    else if (arg_kind[k] == ARG_I64) fusable_shape = false;
+  }
+  std::vector<char> touched;  // input columns whose NULLs would change the result
+  if (pred) expr_columns(pred, touched);
+  for (auto& g : groups) expr_columns(g, touched);
+  for (auto& a : args) expr_columns(a, touched);
+
+  // slot layout of the unfused path, fixed by the first batch: cnt[0] = rows; then one valid-count per argument whose
+  // column holds NULLs, one integer-sum slot per Int64 argument
+  std::vector<int> f_acc(args.size(), -1), vcnt(args.size(), -1), isum(args.size(), -1);
+  int n_acc = 0, n_cnt = 1;
+  bool layout_fixed = false, fused_run = false;
+
   StreamPtr in = src->execute(partition);
   std::unique_ptr<AggRunner> runner;
   std::string path;
-  std::vector<BatchPtr> keep_alive;  // kernels are asynchronous: inputs must outlive them
-  while (BatchPtr b = in->next()) {
-    if (b->num_rows == 0) continue;
-    AggLaunch l;
+  // one batch of look-ahead: a stream of exactly one batch (a partition resident in HBM) takes the speculative path
+  auto next_nonempty = [&]() {
+    BatchPtr b;
+    while ((b = in->next()) && (b->num_rows == 0 || reject_all)) {}
+    return b;
+  };
+  BatchPtr cur = next_nonempty(), ahead = cur ? next_nonempty() : nullptr;
+  const bool single = cur && !ahead;
+  bool speculated = false;
+  std::vector<Column> temps;
+  std::vector<BufPtr> tbufs;
+  BufPtr keybuf;
+  auto bind = [&](const BatchPtr& b, AggLaunch* l) {
+    temps.clear();
+    tbufs.clear();
+    keybuf.reset();
     std::string sig;
-    std::vector<Column> temps;
-    BufPtr keybuf;
-    bool fused = !disable_fusion && !getenv("B2_DISABLE_FUSION") && bind_fused_agg(ctx, pred, groups, args, *b, &l, &sig);
+    bool nulls = false;
+    for (size_t c = 0; c < touched.size() && c < b->cols.size(); ++c) nulls |= touched[c] && (bool)b->cols[c].valid;
+    bool fused = fusable_shape && !nulls && (!layout_fixed || fused_run) && bind_fused_agg(ctx, pred, groups, fargs, *b, l, &sig);
     if (fused) {
-      if (path.empty()) path = "fused:" + sig + (l.tma ? (l.narrow ? "[tma,narrow]" : "[tma]") : "[ld]");
-    } else {
-      if (path.empty()) path = "unfused";
-      const uint8_t* mask = nullptr;
-      if (pred) {
-        temps.push_back(eval_expr(ctx, pred, *b));
-        mask = temps.back().values<uint8_t>();
+      if (path.empty()) path = "fused:" + sig + (l->tma ? (l->narrow ? "[tma,narrow]" : "[tma]") : "[ld]");
+      if (!layout_fixed) {
+        layout_fixed = fused_run = true;
+        for (size_t k = 0; k < args.size(); ++k)
+          if (arg_kind[k] == ARG_F64) f_acc[k] = n_acc++;
       }
-      std::vector<const double*> vals;
-      for (auto& a : args) {
-        temps.push_back(eval_expr(ctx, a, *b));
-        vals.push_back(temps.back().values<double>());
-      }
-      const Key128* keys = nullptr;
-      BufPtr st = dev_alloc_zero(ctx, 16);
-      if (!groups.empty()) {
-        std::vector<Column> kc;
-        for (auto& g : groups) kc.push_back(eval_expr(ctx, g, *b));
-        keybuf = pack_keys(ctx, layout, kc, b->num_rows, st->as<int>());
-        int host = 0;
-        if (layout_has_utf8(layout)) B2_READBACK(ctx, &host, st->ptr, 4);
-        if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 group key value is longer than the packed-key budget");
-        keys = keybuf->as<Key128>();
-      }
-      l = bind_column_agg(ctx, keys, mask, vals, {}, /*count_rows=*/true);
+      return;
     }
+    if (layout_fixed && fused_run)
+      fail(B2_ERR_NOT_IMPLEMENTED, "NULLs appear in a later batch of a partition whose first batch had none");
+    if (path.empty()) path = "unfused";
+    const uint8_t* mask = nullptr;
+    if (pred) {
+      temps.push_back(eval_predicate(ctx, pred, *b));
+      mask = temps.back().values<uint8_t>();
+    }
+    std::vector<Column> av;
+    for (auto& a : args) av.push_back(eval_expr(ctx, a, *b));
+    if (!layout_fixed) {
+      layout_fixed = true;
+      for (size_t k = 0; k < args.size(); ++k) {
+        if (arg_kind[k] == ARG_F64) f_acc[k] = n_acc++;
+        if (av[k].valid || arg_nullable[k]) vcnt[k] = n_cnt++;
+      }
+      for (size_t k = 0; k < args.size(); ++k)
+        if (arg_kind[k] == ARG_I64) isum[k] = n_cnt++;
+    }
+    std::vector<const double*> vals(n_acc, nullptr);
+    std::vector<const u64*> cnts(n_cnt, nullptr);
+    for (size_t k = 0; k < args.size(); ++k) {
+      if (av[k].valid && vcnt[k] < 0)
+        fail(B2_ERR_NOT_IMPLEMENTED, "NULLs appear in a later batch of a partition whose first batch had none");
+      const void* data = av[k].data->ptr;
+      if (av[k].valid && arg_kind[k] != ARG_COUNT) {
+        tbufs.push_back(zero_nulls(ctx, av[k]));
+        data = tbufs.back()->ptr;
+      }
+      if (vcnt[k] >= 0) {
+        if (av[k].valid) {
+          tbufs.push_back(valid_to_u64(ctx, av[k]));
+          cnts[vcnt[k]] = tbufs.back()->as<u64>();
+        }  // else: null entry = 1 per row, every value of this batch is present
+      }
+      if (arg_kind[k] == ARG_F64) vals[f_acc[k]] = static_cast<const double*>(data);
+      if (arg_kind[k] == ARG_I64) cnts[isum[k]] = static_cast<const u64*>(data);
+    }
+    temps.insert(temps.end(), av.begin(), av.end());
+    const Key128* keys = nullptr;
+    if (!groups.empty()) {
+      std::vector<Column> kc;
+      for (auto& g : groups) kc.push_back(eval_expr(ctx, g, *b));
+      if (!runner) runner = std::make_unique<AggRunner>(ctx, agg_padded_na(n_acc), agg_padded_nc(n_cnt), true);
+      // an over-long Utf8 key raises AGG_KEY_TOO_WIDE in the runner's status word, read back with the scan's status
+      keybuf = pack_keys(ctx, layout, kc, b->num_rows, runner->status->as<int>());
+      keys = keybuf->as<Key128>();
+    }
+    *l = bind_column_agg(ctx, keys, mask, vals, cnts);
+  };
+  auto slots_now = [&]() {
+    std::vector<Slots> sl(aggs.size());
+    for (size_t a = 0; a < aggs.size(); ++a) {
+      int k = agg_arg[a];
+      Slots& s = sl[a];
+      switch (aggs[a].fn) {
+        case B2_AGG_SUM:
+          if (arg_kind[k] == ARG_I64) s.isum = isum[k];
+          else s.acc = f_acc[k];
+          s.vcnt = vcnt[k];
+          break;
+        case B2_AGG_AVG:
+          s.acc = f_acc[k];
+          s.cnt = vcnt[k] >= 0 ? vcnt[k] : 0;
+          s.avg_null = vcnt[k] >= 0;
+          break;
+        default: s.cnt = (k >= 0 && vcnt[k] >= 0) ? vcnt[k] : 0; break;
+      }
+    }
+    return sl;
+  };
+  while (cur) {
+    AggLaunch l;
+    bind(cur, &l);
     if (!runner) runner = std::make_unique<AggRunner>(ctx, l.na, l.nc, l.keyed);
     if (runner->na != l.na || runner->nc != l.nc)
       fail(B2_ERR_EXECUTION, "internal: aggregate source shape changed between batches");
-    runner->consume(l, b->num_rows);  // synchronises on the status word, so temporaries may go
+    if (single && !getenv("B2_DISABLE_SPECULATION") && runner->consume_unchecked(l, cur->num_rows)) {
+      // nothing read back yet: the emit returns status + group count with its single readback
+      last_path = path + "/small";
+      int st = 0;
+      BatchPtr o = emit(*runner, true, slots_now(), true, &st);
+      if (o) return o;
+      // redo through the checked path: wide keys, or the high-cardinality kernel, or a loud failure
+      runner->reset();
+      if (st == AGG_KEY_TOO_WIDE && l.small_wide) runner->narrow_overflowed = true;
+      else if (st == AGG_KEY_TOO_WIDE) runner->check_status(st);
+      else if (st == AGG_ABORT_CARDINALITY) runner->force_global = true;
+      bind(cur, &l);  // temporaries of the unfused path were released with the first attempt's buffers
+      speculated = true;
+    }
+    runner->consume(l, cur->num_rows);  // synchronises on the status word, so temporaries may go
+    cur = ahead;
+    ahead = cur ? next_nonempty() : nullptr;
   }
-  if (!runner) runner = std::make_unique<AggRunner>(ctx, (int)(args.empty() ? 1 : args.size()), 1, !groups.empty());
+  (void)speculated;
+  if (!runner) {
+    if (!layout_fixed)
+      for (size_t k = 0; k < args.size(); ++k)
+        if (arg_kind[k] == ARG_F64) f_acc[k] = n_acc++;
+    runner = std::make_unique<AggRunner>(ctx, agg_padded_na(n_acc), agg_padded_nc(n_cnt), !groups.empty());
+  }
   last_path = (path.empty() ? std::string("empty") : path) + (runner->path.empty() ? "" : "/" + runner->path);
-  std::vector<int> sum_idx(aggs.size(), 0), cnt_idx(aggs.size(), 0);
-  for (size_t a = 0; a < aggs.size(); ++a) sum_idx[a] = agg_acc[a] < 0 ? 0 : agg_acc[a];
-  return emit(*runner, true, sum_idx, cnt_idx);
+  return emit(*runner, true, slots_now(), false, nullptr);
 }
 
 BatchPtr HashAggregateExec::run_final(int partition) {
@@ -172,13 +342,12 @@ BatchPtr HashAggregateExec::run_final(int partition) {
   StreamPtr in = children[0]->execute(partition);
   size_t ng = groups.size();
   std::vector<int> sum_col(aggs.size(), -1), cnt_col(aggs.size(), -1);
-  std::vector<int> sum_idx(aggs.size(), 0), cnt_idx(aggs.size(), 0);
-  int col = (int)ng, n_sum = 0, n_cnt = 0;
+  int col = (int)ng;
   for (size_t a = 0; a < aggs.size(); ++a) {
     switch (aggs[a].fn) {
-      case B2_AGG_SUM: sum_col[a] = col++; sum_idx[a] = n_sum++; break;
-      case B2_AGG_COUNT: cnt_col[a] = col++; cnt_idx[a] = n_cnt++; break;
-      case B2_AGG_AVG: cnt_col[a] = col++; sum_col[a] = col++; cnt_idx[a] = n_cnt++; sum_idx[a] = n_sum++; break;
+      case B2_AGG_SUM: sum_col[a] = col++; break;
+      case B2_AGG_COUNT: cnt_col[a] = col++; break;
+      case B2_AGG_AVG: cnt_col[a] = col++; sum_col[a] = col++; break;
     }
   }
   Schema in_schema = children[0]->schema();
@@ -193,64 +362,143 @@ BatchPtr HashAggregateExec::run_final(int partition) {
     while ((b = in->next()) && b->num_rows == 0) {}
     return b;
   };
-  BatchPtr first = next_nonempty(), second = first ? next_nonempty() : nullptr;
-  bool identity = first && !second && ng > 0 && first->unique_key_cols == (int)ng && !getenv("B2_DISABLE_FUSION");
+  BatchPtr cur = next_nonempty(), ahead = cur ? next_nonempty() : nullptr;
+  const bool single = cur && !ahead;
+  bool identity = single && ng > 0 && cur->unique_key_cols == (int)ng && !getenv("B2_DISABLE_FUSION");
   for (size_t g = 0; g < ng && identity; ++g) identity = groups[g]->kind == B2_EXPR_COLUMN && groups[g]->col == (int)g;
   for (size_t a = 0; a < aggs.size() && identity; ++a) identity = aggs[a].fn != B2_AGG_AVG;
   if (identity) {
     auto o = std::make_shared<Batch>();
     o->ctx = ctx;
     o->schema = out;
-    o->num_rows = first->num_rows;
-    for (size_t g = 0; g < ng; ++g) o->cols.push_back(first->cols[g]);
-    for (size_t a = 0; a < aggs.size(); ++a) o->cols.push_back(first->cols[sum_col[a] >= 0 ? sum_col[a] : cnt_col[a]]);
+    o->num_rows = cur->num_rows;
+    for (size_t g = 0; g < ng; ++g) o->cols.push_back(cur->cols[g]);
+    for (size_t a = 0; a < aggs.size(); ++a) o->cols.push_back(cur->cols[sum_col[a] >= 0 ? sum_col[a] : cnt_col[a]]);
     last_path = "identity(unique partial states)";
     return o;
   }
+  // slot layout, fixed by the first batch: f64 sums in `acc`; counts, integer sums and the valid-counts of nullable
+  // sum states in `cnt`
+  std::vector<Slots> sl(aggs.size());
+  int n_acc = 0, n_cnt = 0;
+  bool layout_fixed = false;
   std::unique_ptr<AggRunner> runner;
-  std::vector<BatchPtr> head;
-  if (first) head.push_back(first);
-  if (second) head.push_back(second);
-  size_t head_i = 0;
-  auto next_batch = [&]() -> BatchPtr {
-    if (head_i < head.size()) return head[head_i++];
-    return in->next();
-  };
-  while (BatchPtr b = next_batch()) {
-    if (b->num_rows == 0) continue;
-    std::vector<const double*> vals;
-    std::vector<const u64*> cnts;
-    for (size_t a = 0; a < aggs.size(); ++a) {
-      if (sum_col[a] >= 0) {
-        if (b->cols[sum_col[a]].dtype != B2_FLOAT64) fail(B2_ERR_NOT_IMPLEMENTED, "non-Float64 sum state");
-        vals.push_back(b->cols[sum_col[a]].values<double>());
+  std::vector<BufPtr> tbufs;
+  std::vector<Column> kc;
+  BufPtr keybuf;
+  auto bind = [&](const BatchPtr& b, AggLaunch* l) {
+    tbufs.clear();
+    kc.clear();
+    if (!layout_fixed) {
+      layout_fixed = true;
+      for (size_t a = 0; a < aggs.size(); ++a) {
+        Slots& s = sl[a];
+        if (sum_col[a] >= 0) {
+          const Column& sc = b->cols[sum_col[a]];
+          if (sc.dtype == B2_FLOAT64) s.acc = n_acc++;
+          else if (sc.dtype == B2_INT64 || sc.dtype == B2_UINT64) s.isum = n_cnt++;
+          else fail(B2_ERR_NOT_IMPLEMENTED, std::string("sum state of type ") + dtype_name(sc.dtype));
+          // an ungrouped Final always tracks NULL states: the empty partition among its inputs may come second
+          if (aggs[a].fn == B2_AGG_SUM && (sc.valid || ng == 0)) s.vcnt = n_cnt++;
+          if (aggs[a].fn == B2_AGG_AVG) s.avg_null = sc.valid || ng == 0;
+        }
+        if (cnt_col[a] >= 0) s.cnt = n_cnt++;
       }
     }
-    for (size_t a = 0; a < aggs.size(); ++a)
+    std::vector<const double*> vals(n_acc, nullptr);
+    std::vector<const u64*> cnts(n_cnt, nullptr);
+    for (size_t a = 0; a < aggs.size(); ++a) {
+      const Slots& s = sl[a];
+      if (sum_col[a] >= 0) {
+        const Column& sc = b->cols[sum_col[a]];
+        if ((s.acc >= 0) != (sc.dtype == B2_FLOAT64)) fail(B2_ERR_EXECUTION, "sum state type changed between batches");
+        const void* data = sc.data->ptr;
+        if (sc.valid) {
+          if (aggs[a].fn == B2_AGG_SUM && s.vcnt < 0)
+            fail(B2_ERR_NOT_IMPLEMENTED, "NULL sum states appear in a later batch of a partition whose first batch had none");
+          tbufs.push_back(zero_nulls(ctx, sc));
+          data = tbufs.back()->ptr;
+          if (s.vcnt >= 0) {
+            tbufs.push_back(valid_to_u64(ctx, sc));
+            cnts[s.vcnt] = tbufs.back()->as<u64>();
+          }
+        } else if (s.vcnt >= 0) {  // every state of this batch is present: count 1 per row
+          Column ones;
+          ones.length = b->num_rows;
+          ones.valid = valid_copy(ctx, nullptr, b->num_rows);
+          tbufs.push_back(valid_to_u64(ctx, ones));
+          cnts[s.vcnt] = tbufs.back()->as<u64>();
+        }
+        if (s.acc >= 0) vals[s.acc] = static_cast<const double*>(data);
+        else cnts[s.isum] = static_cast<const u64*>(data);
+      }
       if (cnt_col[a] >= 0) {
         if (b->cols[cnt_col[a]].dtype != B2_UINT64) fail(B2_ERR_EXECUTION, "count state must be UInt64");
-        cnts.push_back(b->cols[cnt_col[a]].values<u64>());
+        cnts[s.cnt] = b->cols[cnt_col[a]].values<u64>();
       }
-    // note: vals/cnts were pushed in aggregate order per kind, matching sum_idx / cnt_idx
+    }
+    if (!runner) runner = std::make_unique<AggRunner>(ctx, agg_padded_na(n_acc), agg_padded_nc(n_cnt), ng > 0);
     const Key128* keys = nullptr;
-    BufPtr keybuf;
     if (ng) {
-      std::vector<Column> kc;
       for (auto& g : groups) kc.push_back(eval_expr(ctx, g, *b));
-      BufPtr st = dev_alloc_zero(ctx, 16);
-      keybuf = pack_keys(ctx, layout, kc, b->num_rows, st->as<int>());
+      // an over-long Utf8 key value (states from a CPU executor or a shuffle file) raises AGG_KEY_TOO_WIDE in the
+      // runner's status word: read back with the scan's status and failed loudly, never truncated
+      keybuf = pack_keys(ctx, layout, kc, b->num_rows, runner->status->as<int>());
       keys = keybuf->as<Key128>();
     }
-    AggLaunch l = bind_column_agg(ctx, keys, nullptr, vals, cnts, /*count_rows=*/false);
-    if (!runner) runner = std::make_unique<AggRunner>(ctx, l.na, l.nc, l.keyed);
+    if (cnts.empty()) cnts.push_back(nullptr);
+    *l = bind_column_agg(ctx, keys, nullptr, vals, cnts);
+  };
+  while (cur) {
+    AggLaunch l;
+    bind(cur, &l);
     // partial states carry one row per group of their partition: a large state batch means more groups than the
     // per-CTA tables of the low-cardinality kernel hold, so go straight to the HBM table
-    if (ng && b->num_rows > 16384) runner->force_global = true;
-    runner->consume(l, b->num_rows);
+    if (ng && cur->num_rows > 16384) runner->force_global = true;
+    if (single && !getenv("B2_DISABLE_SPECULATION") && runner->consume_unchecked(l, cur->num_rows)) {
+      last_path = "unfused/small";
+      int st = 0;
+      BatchPtr o = emit(*runner, false, sl, true, &st);
+      if (o) return o;
+      runner->reset();
+      if (st == AGG_KEY_TOO_WIDE) runner->check_status(st);
+      if (st == AGG_ABORT_CARDINALITY) runner->force_global = true;
+      bind(cur, &l);
+    }
+    runner->consume(l, cur->num_rows);
+    cur = ahead;
+    ahead = cur ? next_nonempty() : nullptr;
   }
-  if (!runner) runner = std::make_unique<AggRunner>(ctx, n_sum ? n_sum : 1, n_cnt ? n_cnt : 1, ng > 0);
+  if (!runner) {
+    for (size_t a = 0; a < aggs.size(); ++a) {  // no input at all: layout from the schema
+      Slots& s = sl[a];
+      if (sum_col[a] >= 0) {
+        if (in_schema.fields[sum_col[a]].dtype == B2_FLOAT64) s.acc = n_acc++;
+        else s.isum = n_cnt++;
+      }
+      if (cnt_col[a] >= 0) s.cnt = n_cnt++;
+    }
+    runner = std::make_unique<AggRunner>(ctx, agg_padded_na(n_acc), agg_padded_nc(n_cnt), ng > 0);
+  }
   last_path = "unfused/" + runner->path;
-  return emit(*runner, false, sum_idx, cnt_idx);
+  return emit(*runner, false, sl, false, nullptr);
+}
+
+static int sum_return_type(int dt) {  // DataFusion's sum_return_type
+  switch (dt) {
+    case B2_INT32: case B2_INT64: case B2_UINT8: return B2_INT64;
+    case B2_UINT64: return B2_UINT64;
+    case B2_FLOAT64: return B2_FLOAT64;
+  }
+  fail(B2_ERR_NOT_IMPLEMENTED, std::string("SUM over ") + dtype_name(dt));
+}
+static ExprPtr cast_to(const ExprPtr& arg, int dtype) {
+  if (arg->dtype == dtype) return arg;
+  auto c = std::make_shared<Expr>();
+  c->kind = B2_EXPR_CAST;
+  c->dtype = dtype;
+  c->ch = {arg};
+  return c;
 }
 
 OpPtr make_hash_aggregate(Ctx* ctx, OpPtr input, int mode, std::vector<ExprPtr> groups, std::vector<AggSpec> aggs,
@@ -268,39 +516,48 @@ OpPtr make_hash_aggregate(Ctx* ctx, OpPtr input, int mode, std::vector<ExprPtr> 
   op->layout = make_key_layout(kd);
   const Schema& arg_schema = input_schema ? *input_schema : in;
   for (auto& a : aggs) {
-    int acc = -1;
-    if (a.fn == B2_AGG_SUM || a.fn == B2_AGG_AVG) {
-      ExprPtr arg = a.arg;
-      if (arg->dtype != B2_FLOAT64) {
-        if (a.fn == B2_AGG_SUM)
-          fail(B2_ERR_NOT_IMPLEMENTED, std::string("SUM over ") + dtype_name(arg->dtype) +
-                                           " (only Float64 sums occur on the TPC-H path)");
-        // AVG casts its input to Float64 (avg_return_type is always Float64)
-        auto c = std::make_shared<Expr>();
-        c->kind = B2_EXPR_CAST;
-        c->dtype = B2_FLOAT64;
-        c->ch = {arg};
-        if (!(arg->dtype == B2_INT32 || arg->dtype == B2_INT64))
-          fail(B2_ERR_NOT_IMPLEMENTED, std::string("AVG over ") + dtype_name(arg->dtype));
-        arg = c;
+    int idx = -1, sum_type = B2_FLOAT64;
+    ExprPtr arg = a.arg;
+    int kind = HashAggregateExec::ARG_COUNT;
+    if (a.fn == B2_AGG_SUM) {
+      sum_type = sum_return_type(arg->dtype);
+      if (sum_type == B2_FLOAT64) {
+        kind = HashAggregateExec::ARG_F64;
+      } else {  // integer sums accumulate as 64-bit two's complement words
+        kind = HashAggregateExec::ARG_I64;
+        if (arg->dtype != B2_INT64 && arg->dtype != B2_UINT64) arg = cast_to(arg, B2_INT64);
       }
-      if (mode == B2_AGG_PARTIAL) {
-        std::string text = expr_to_string(arg, arg_schema);
-        for (size_t k = 0; k < op->args.size(); ++k)
-          if (expr_to_string(op->args[k], arg_schema) == text) acc = (int)k;
-        if (acc < 0) {
-          op->args.push_back(arg);
-          acc = (int)op->args.size() - 1;
-        }
-      }
+    } else if (a.fn == B2_AGG_AVG) {
+      // AVG casts its input to Float64 (avg_return_type is always Float64)
+      if (!(arg->dtype == B2_FLOAT64 || arg->dtype == B2_INT32 || arg->dtype == B2_INT64 || arg->dtype == B2_UINT64 ||
+            arg->dtype == B2_UINT8))
+        fail(B2_ERR_NOT_IMPLEMENTED, std::string("AVG over ") + dtype_name(arg->dtype));
+      arg = cast_to(arg, B2_FLOAT64);
+      kind = HashAggregateExec::ARG_F64;
     } else if (a.fn != B2_AGG_COUNT) {
       fail(B2_ERR_NOT_IMPLEMENTED, "aggregate function " + std::to_string(a.fn) +
                                        " (only Sum, Avg, Count cross the Ballista wire, to_proto.rs:352-363)");
     }
-    op->agg_acc.push_back(acc);
+    if (mode == B2_AGG_PARTIAL && !(a.fn == B2_AGG_COUNT && arg->is_literal())) {
+      std::string text = expr_to_string(arg, arg_schema);
+      for (size_t k = 0; k < op->args.size(); ++k)
+        if (op->arg_kind[k] == kind && expr_to_string(op->args[k], arg_schema) == text) idx = (int)k;
+      if (idx < 0) {
+        op->args.push_back(arg);
+        op->arg_kind.push_back(kind);
+        std::vector<char> used;
+        expr_columns(arg, used);
+        bool nullable = false;
+        for (size_t c = 0; c < used.size() && c < arg_schema.fields.size(); ++c)
+          nullable |= used[c] && arg_schema.fields[c].nullable;
+        op->arg_nullable.push_back(nullable);
+        idx = (int)op->args.size() - 1;
+      }
+    }
+    op->agg_arg.push_back(idx);
     if (mode == B2_AGG_PARTIAL) {
       switch (a.fn) {
-        case B2_AGG_SUM: op->out.fields.push_back(Field{a.name + "[sum]", B2_FLOAT64, true}); break;
+        case B2_AGG_SUM: op->out.fields.push_back(Field{a.name + "[sum]", sum_type, true}); break;
         case B2_AGG_COUNT: op->out.fields.push_back(Field{a.name + "[count]", B2_UINT64, true}); break;
         case B2_AGG_AVG:
           op->out.fields.push_back(Field{a.name + "[count]", B2_UINT64, true});
@@ -308,7 +565,7 @@ OpPtr make_hash_aggregate(Ctx* ctx, OpPtr input, int mode, std::vector<ExprPtr> 
           break;
       }
     } else {
-      op->out.fields.push_back(Field{a.name, a.fn == B2_AGG_COUNT ? B2_UINT64 : B2_FLOAT64, true});
+      op->out.fields.push_back(Field{a.name, a.fn == B2_AGG_COUNT ? B2_UINT64 : (a.fn == B2_AGG_SUM ? sum_type : B2_FLOAT64), true});
     }
   }
   op->groups = std::move(groups);

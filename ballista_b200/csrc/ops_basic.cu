@@ -15,8 +15,11 @@ struct MemItem {
 struct MemoryExec : Op {
   Schema sch;
   std::vector<std::vector<std::shared_ptr<MemItem>>> parts;
+  uint64_t ver = 1;
+  uint64_t version() const override { return ver * 0x9E3779B97F4A7C15ull ^ (uint64_t)(uintptr_t)this; }
   ~MemoryExec() override { clear(); }
   void clear() {
+    ++ver;
     for (auto& p : parts) {
       for (auto& it : p)
         if (it->is_host && it->host.release) it->host.release(&it->host);
@@ -77,6 +80,7 @@ void memory_exec_add_host(Op* op, int partition, ArrowArray* batch) {
   it->host = *batch;        // move
   batch->release = nullptr;
   m->parts[partition].push_back(it);
+  ++m->ver;
 }
 void memory_exec_add_device(Op* op, int partition, BatchPtr batch) {
   auto* m = as_mem(op);
@@ -87,6 +91,7 @@ void memory_exec_add_device(Op* op, int partition, BatchPtr batch) {
   auto it = std::make_shared<MemItem>();
   it->dev = batch;
   m->parts[partition].push_back(it);
+  ++m->ver;
 }
 void memory_exec_clear(Op* op) { as_mem(op)->clear(); }
 
@@ -97,6 +102,7 @@ struct FilterExec : Op {
   ExprPtr pred;
   const char* name() const override { return "FilterExec"; }
   Schema schema() const override { return children[0]->schema(); }
+  bool exchange_on(std::vector<int>* k, int* n) const override { return children[0]->exchange_on(k, n); }
   void require(const std::vector<char>& need) override {
     if (need.empty()) return children[0]->require(need);
     std::vector<char> n = need;
@@ -115,7 +121,7 @@ struct FilterExec : Op {
         if (op->pred->i) return b;
         return take_batch(ctx, *b, nullptr, 0);
       }
-      Column mask = eval_expr(ctx, op->pred, *b);
+      Column mask = eval_predicate(ctx, op->pred, *b);
       int64_t m = 0;
       BufPtr idx = mask_to_indices(ctx, mask.values<uint8_t>(), b->num_rows, &m);
       return take_batch(ctx, *b, idx->as<uint32_t>(), m);
@@ -153,6 +159,7 @@ struct CoalesceExec : Op {
   int64_t target;
   const char* name() const override { return "CoalesceBatchesExec"; }
   Schema schema() const override { return children[0]->schema(); }
+  bool exchange_on(std::vector<int>* k, int* n) const override { return children[0]->exchange_on(k, n); }
   void require(const std::vector<char>& need) override { children[0]->require(need); }
   bool accepts_semi_filter(int key_col) const override { return children[0]->accepts_semi_filter(key_col); }
   void set_semi_filter(std::shared_ptr<SemiFilter> f) override { children[0]->set_semi_filter(std::move(f)); }
@@ -332,6 +339,7 @@ struct SortExec : Op {
       BufPtr st = dev_alloc_zero(ctx, 16);
       for (size_t k = 0; k < op->exprs.size(); ++k) {
         keep.push_back(eval_expr(ctx, op->exprs[k], *b));
+        if (keep.back().valid) fail(B2_ERR_NOT_IMPLEMENTED, "SortExec over a key column that holds NULLs");
         sort_key_words(ctx, keep.back(), op->descending[k] != 0, &words, &bits, st->as<int>());
       }
       std::vector<const u64*> w;

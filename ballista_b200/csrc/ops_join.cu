@@ -28,63 +28,122 @@ static Op* peel_filter(Op* op, ExprPtr* pred) {
   return op;
 }
 
+__global__ void mark_rows_kernel(const uint32_t* idx, int64_t m, uint8_t* flags) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < m; i += (int64_t)gridDim.x * blockDim.x) flags[idx[i]] = 1;
+}
+
 struct HashJoinExec : Op {
   std::vector<int> on_left, on_right;  // column indices
   int join_type = B2_JOIN_INNER;
   Schema out;
-  std::vector<int> right_keep;  // right columns that survive the duplicate-name rule
+  // output = kept left columns ++ kept right columns.  Inner / Left drop a right `on` column named like its left
+  // partner, Right drops the left one instead (DataFusion's build_join_schema)
+  std::vector<int> left_keep, right_keep;
   KeyLayout layout;
   bool k32 = false;             // one Int32 / Date32 key per side: 8-byte-slot table, fused filters
   std::vector<char> need;       // output columns a parent will read (empty = all)
-  // build side, collected once (the reference rebuilds it per task; result-neutral)
+  // build side, collected once per version of the left subtree (the reference rebuilds it per task; result-neutral,
+  // SURVEY App. C.10)
   BatchPtr left_batch;
   std::shared_ptr<JoinTable> table;
   BufPtr left_keys;
   bool semi_offered = false;
+  bool partitioned = false;     // both inputs arrive through exchanges on the join keys: partition-wise join
+  uint64_t built_version = 0;
 
   const char* name() const override { return "HashJoinExec"; }
   Schema schema() const override { return out; }
   void partitioning(int* scheme, int* n) const override { children[1]->partitioning(scheme, n); }
   bool per_rank_partitions() const override { return children[1]->per_rank_partitions(); }
+  // rows stay in the partition of their probe-side row: the output is exchanged on the right key columns
+  bool exchange_on(std::vector<int>* key_cols, int* n_out) const override {
+    std::vector<int> rk;
+    if (!children[1]->exchange_on(&rk, n_out)) return false;
+    key_cols->clear();
+    for (int c : rk) {
+      int o = -1;
+      for (size_t k = 0; k < right_keep.size(); ++k)
+        if (right_keep[k] == c) o = (int)(left_keep.size() + k);
+      if (o < 0 && join_type != B2_JOIN_RIGHT)  // dropped as a duplicate of its (equal-valued) left partner
+        for (size_t i = 0; i < on_right.size(); ++i)
+          if (on_right[i] == c)
+            for (size_t k = 0; k < left_keep.size(); ++k)
+              if (left_keep[k] == on_left[i]) o = (int)k;
+      if (o < 0) return false;
+      key_cols->push_back(o);
+    }
+    return true;
+  }
 
-  bool fuse() const { return k32 && !getenv("B2_DISABLE_FUSION"); }
+  // A FilterExec below a side is folded into the build / probe kernels, except on the side whose unmatched rows an
+  // outer join must enumerate (there the filter is materialised, so that "row of the input" means "row that passed")
+  bool fuse_left() const { return k32 && join_type != B2_JOIN_LEFT && !getenv("B2_DISABLE_FUSION"); }
+  bool fuse_right() const { return k32 && join_type != B2_JOIN_RIGHT && !getenv("B2_DISABLE_FUSION"); }
   bool needed(size_t out_col) const { return need.empty() || (out_col < need.size() && need[out_col]); }
 
   void require(const std::vector<char>& n) override {
     need = n;
     size_t nl = children[0]->schema().fields.size(), nr = children[1]->schema().fields.size();
     std::vector<char> l(nl, 0), r(nr, 0);
-    for (size_t c = 0; c < nl; ++c) l[c] = needed(c);
-    for (size_t k = 0; k < right_keep.size(); ++k) r[right_keep[k]] = needed(nl + k);
+    for (size_t k = 0; k < left_keep.size(); ++k) l[left_keep[k]] = needed(k);
+    for (size_t k = 0; k < right_keep.size(); ++k) r[right_keep[k]] = needed(left_keep.size() + k);
     for (int c : on_left) l[c] = 1;
     for (int c : on_right) r[c] = 1;
     children[0]->require(l);
     children[1]->require(r);
   }
 
-  BufPtr pack(const Batch& b, const std::vector<int>& on) {
+  // packed keys of one side; rows with a NULL key part get a per-side tag in byte 15, so they equal no key of the
+  // other side (null keys never match)
+  BufPtr pack(const Batch& b, const std::vector<int>& on, int null_tag) {
     std::vector<Column> kc;
     for (int c : on) kc.push_back(b.cols[c]);
     BufPtr st = dev_alloc_zero(ctx, 16);
-    BufPtr keys = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>());
+    BufPtr keys = pack_keys(ctx, layout, kc, b.num_rows, st->as<int>(), null_tag);
     int host = 0;
     if (layout_has_utf8(layout)) B2_READBACK(ctx, &host, st->ptr, 4);
     if (host) fail(B2_ERR_NOT_IMPLEMENTED, "a Utf8 join key value is longer than the packed-key budget");
     return keys;
   }
+  // fused-filter mask of one side of the 32-bit-key path, with the key column's NULLs folded in
+  Column side_mask(const ExprPtr& pred, const Batch& b, int key_col, RowPred* rp) {
+    Column mask;
+    if (pred && b.num_rows && !compile_row_pred(pred, b, rp)) mask = eval_predicate(ctx, pred, b);
+    const Column& kc = b.cols[key_col];
+    if (kc.valid) {
+      if (mask.data) mask.data = valid_and(ctx, mask.data, kc.valid, b.num_rows);
+      else mask.data = kc.valid;
+    }
+    return mask;
+  }
   void build(int partition) {
-    if (table) return;
+    const uint64_t v = children[0]->version();
+    if (table && built_version == v) return;
+    table.reset();
+    left_batch.reset();
+    left_keys.reset();
+    semi_offered = false;
+    built_version = v;
     Op* l = children[0].get();
     ExprPtr pred;
-    if (fuse()) l = peel_filter(l, &pred);
+    if (fuse_left()) l = peel_filter(l, &pred);
     std::vector<BatchPtr> all;
     int np = l->n_partitions();
-    // Partitioned join: when the build side arrives through an exchange (a hash repartition whose output partition
-    // r lives on rank r), only this rank's partition is built - the probe side was shuffled on the same key.
-    // Otherwise collect-left, as the reference: MergeExec(left) over all partitions.
-    bool partitioned = l->per_rank_partitions();
+    // Partitioned join: when BOTH inputs arrive through exchanges (hash repartitions whose output partition r lives on
+    // rank r) on this join's keys with one partition count, only this rank's build partition is needed - every probe
+    // row was sent to the rank that holds its matches.  A per-rank build side under any other probe side is
+    // all-gathered: collect-left, as the reference's MergeExec(left) over all partitions.
+    const bool per_rank = l->per_rank_partitions();
+    partitioned = false;
+    if (per_rank) {
+      std::vector<int> lk, rk;
+      int ln = 0, rn = 0;
+      partitioned = children[0]->exchange_on(&lk, &ln) && children[1]->exchange_on(&rk, &rn) && ln == rn &&
+                    lk == on_left && rk == on_right;
+    }
     for (int p = 0; p < np; ++p) {
-      if (partitioned && p != partition) continue;
+      if (per_rank && p != partition) continue;
       StreamPtr s = l->execute(p);
       while (BatchPtr b = s->next())
         if (b->num_rows) all.push_back(b);
@@ -94,71 +153,130 @@ struct HashJoinExec : Op {
     } else {
       left_batch = concat_batches(ctx, l->schema(), all);
     }
+    if (per_rank && !partitioned) {
+      if (!ctx->comm) fail(B2_ERR_EXECUTION, "HashJoinExec: per-rank build partitions without a communicator");
+      left_batch = comm_allgather_batch(ctx, *left_batch);
+    }
     if (k32) {
-      Column mask;
       RowPred rp;
-      if (pred && left_batch->num_rows && !compile_row_pred(pred, *left_batch, &rp))
-        mask = eval_expr(ctx, pred, *left_batch);
+      Column mask = side_mask(pred, *left_batch, on_left[0], &rp);
       table = join_build32(ctx, left_batch->cols[on_left[0]].values<int32_t>(), rp,
                            mask.data ? mask.values<uint8_t>() : nullptr, left_batch->num_rows);
       // the mask buffer is freed stream-ordered after the build kernel
     } else {
-      left_keys = pack(*left_batch, on_left);
+      left_keys = pack(*left_batch, on_left, 0x81);
       table = join_build(ctx, left_keys->as<Key128>(), left_batch->num_rows);
     }
   }
   struct S : Stream {
     HashJoinExec* op;
     StreamPtr in;
-    ExprPtr pred;  // fused right-side FilterExec predicate (k32 path)
-    BatchPtr next() override {
-      BatchPtr r = in->next();
-      if (!r) return nullptr;
+    ExprPtr pred;        // fused right-side FilterExec predicate (k32 path)
+    BufPtr left_matched; // Left join: one byte per build row, set by every probe batch of this stream
+    bool tail_done = false;
+
+    BatchPtr assemble(const Batch* r, const BufPtr& li, const BufPtr& ri, int64_t m, bool null_left, bool null_right) {
       Ctx* ctx = op->ctx;
-      BufPtr li, ri;
-      int64_t m;
-      if (op->k32) {
-        Column mask;
-        RowPred rp;
-        if (pred && r->num_rows && !compile_row_pred(pred, *r, &rp)) mask = eval_expr(ctx, pred, *r);
-        m = join_probe32(ctx, *op->table, r->cols[op->on_right[0]].values<int32_t>(), rp,
-                         mask.data ? mask.values<uint8_t>() : nullptr, r->num_rows, &li, &ri);
-      } else {
-        BufPtr pk = op->pack(*r, op->on_right);
-        m = join_probe(ctx, *op->table, pk->as<Key128>(), r->num_rows, &li, &ri);
-      }
       auto o = std::make_shared<Batch>();
       o->ctx = ctx;
       o->schema = op->out;
       o->num_rows = m;
       size_t oc = 0;
-      auto elided = [&](const Column& c) {
+      auto elided = [&](int dtype) {
         Column e;
-        e.dtype = c.dtype;
+        e.dtype = dtype;
         e.length = m;
         return e;
       };
-      for (auto& c : op->left_batch->cols) {
-        o->cols.push_back(op->needed(oc) ? take_column(ctx, c, li->as<uint32_t>(), m) : elided(c));
+      for (int c : op->left_keep) {
+        const Column& col = op->left_batch->cols[c];
+        if (!op->needed(oc)) o->cols.push_back(elided(col.dtype));
+        else if (!li) o->cols.push_back(null_column(ctx, col.dtype, m));
+        else o->cols.push_back(take_column(ctx, col, li->as<uint32_t>(), m, null_left));
         ++oc;
       }
+      Schema rs = op->children[1]->schema();
       for (int c : op->right_keep) {
-        o->cols.push_back(op->needed(oc) ? take_column(ctx, r->cols[c], ri->as<uint32_t>(), m) : elided(r->cols[c]));
+        if (!op->needed(oc)) o->cols.push_back(elided(rs.fields[c].dtype));
+        else if (!ri) o->cols.push_back(null_column(ctx, rs.fields[c].dtype, m));
+        else o->cols.push_back(take_column(ctx, r->cols[c], ri->as<uint32_t>(), m, null_right));
         ++oc;
       }
       return o;
     }
+    BatchPtr next() override {
+      Ctx* ctx = op->ctx;
+      BatchPtr r = in->next();
+      if (!r) {
+        // Left join: build rows no probe batch of this stream matched, null-extended on the right (emitted once, at
+        // the end of the stream; DataFusion@46161d2 emits them per probe batch, which repeats them - SURVEY A.3
+        // states the intended result and that is what is produced here)
+        if (op->join_type == B2_JOIN_LEFT && !tail_done) {
+          tail_done = true;
+          int64_t nb = op->left_batch->num_rows, m = 0;
+          if (!nb) return nullptr;
+          BufPtr un = valid_not(ctx, left_matched ? left_matched->as<uint8_t>() : nullptr, nb);
+          if (!left_matched) B2_CUDA(cudaMemsetAsync(un->ptr, 1, (size_t)nb, ctx->stream));
+          BufPtr idx = mask_to_indices(ctx, un->as<uint8_t>(), nb, &m);
+          if (!m) return nullptr;
+          return assemble(nullptr, idx, nullptr, m, false, false);
+        }
+        return nullptr;
+      }
+      BufPtr li, ri;
+      int64_t m;
+      if (op->k32) {
+        RowPred rp;
+        Column mask = op->side_mask(pred, *r, op->on_right[0], &rp);
+        m = join_probe32(ctx, *op->table, r->cols[op->on_right[0]].values<int32_t>(), rp,
+                         mask.data ? mask.values<uint8_t>() : nullptr, r->num_rows, &li, &ri);
+      } else {
+        BufPtr pk = op->pack(*r, op->on_right, 0x82);
+        m = join_probe(ctx, *op->table, pk->as<Key128>(), r->num_rows, &li, &ri);
+      }
+      if (op->join_type == B2_JOIN_LEFT && op->left_batch->num_rows) {
+        if (!left_matched) left_matched = dev_alloc_zero(ctx, (size_t)op->left_batch->num_rows + 16);
+        if (m) {
+          mark_rows_kernel<<<grid_for(ctx, 8, m, 256), 256, 0, ctx->stream>>>(li->as<uint32_t>(), m,
+                                                                             left_matched->as<uint8_t>());
+          B2_LAUNCHED(ctx);
+        }
+      }
+      bool null_left = false;
+      if (op->join_type == B2_JOIN_RIGHT && r->num_rows) {
+        // probe rows without a match follow the matched pairs of their batch, null-extended on the left
+        BufPtr hit = dev_alloc_zero(ctx, (size_t)r->num_rows + 16);
+        if (m) {
+          mark_rows_kernel<<<grid_for(ctx, 8, m, 256), 256, 0, ctx->stream>>>(ri->as<uint32_t>(), m, hit->as<uint8_t>());
+          B2_LAUNCHED(ctx);
+        }
+        BufPtr un = valid_not(ctx, hit->as<uint8_t>(), r->num_rows);
+        int64_t u = 0;
+        BufPtr uidx = mask_to_indices(ctx, un->as<uint8_t>(), r->num_rows, &u);
+        if (u) {
+          BufPtr li2 = dev_alloc(ctx, (size_t)(m + u + 1) * 4), ri2 = dev_alloc(ctx, (size_t)(m + u + 1) * 4);
+          if (m) {
+            B2_CUDA(cudaMemcpyAsync(li2->ptr, li->ptr, (size_t)m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+            B2_CUDA(cudaMemcpyAsync(ri2->ptr, ri->ptr, (size_t)m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+          }
+          B2_CUDA(cudaMemsetAsync(li2->as<uint32_t>() + m, 0xFF, (size_t)u * 4, ctx->stream));
+          B2_CUDA(cudaMemcpyAsync(ri2->as<uint32_t>() + m, uidx->ptr, (size_t)u * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+          li = li2;
+          ri = ri2;
+          m += u;
+          null_left = true;
+        }
+      }
+      return assemble(r.get(), li, ri, m, null_left, false);
+    }
   };
   // Partitioned join over an exchange: publish the Bloom filter of this rank's build partition to every rank, so the
   // probe side's split drops, before the exchange, the rows whose destination cannot hold their key.  Collective:
-  // every rank runs the same plan and takes the same branch.
+  // every rank runs the same plan and takes the same branch.  Inner joins only (an outer join keeps unmatched rows).
   void offer_semi_filter() {
     if (semi_offered || !k32 || !table || !ctx->comm || ctx->nranks < 2 || getenv("B2_DISABLE_SEMI_FILTER")) return;
     semi_offered = true;
-    Op* l = children[0].get();
-    ExprPtr unused;
-    if (fuse()) l = peel_filter(l, &unused);
-    if (!l->per_rank_partitions() || !children[1]->accepts_semi_filter(on_right[0])) return;
+    if (!partitioned || join_type != B2_JOIN_INNER || !children[1]->accepts_semi_filter(on_right[0])) return;
     const int nr = ctx->nranks;
     std::vector<int64_t> words = allgather_counts(ctx, std::vector<int64_t>{(int64_t)table->bloom_words});
     int64_t stride = 0;
@@ -184,18 +302,18 @@ struct HashJoinExec : Op {
     auto s = std::make_unique<S>();
     s->op = this;
     Op* r = children[1].get();
-    if (fuse()) r = peel_filter(r, &s->pred);
+    if (fuse_right()) r = peel_filter(r, &s->pred);
     s->in = r->execute(partition);
-    last_path = k32 ? (fuse() ? "k32:fused-filter" : "k32") : "key128";
+    last_path = std::string(k32 ? (fuse_left() || fuse_right() ? "k32:fused-filter" : "k32") : "key128") +
+                (partitioned ? "/partitioned" : "");
     return s;
   }
 };
 
 OpPtr make_hash_join(Ctx* ctx, OpPtr left, OpPtr right, std::vector<std::string> on_l, std::vector<std::string> on_r,
                      int join_type) {
-  if (join_type != B2_JOIN_INNER)
-    fail(B2_ERR_NOT_IMPLEMENTED,
-         "Left/Right outer joins need null-extended rows; only Inner is implemented (all TPC-H Q3/Q5 joins)");
+  if (join_type != B2_JOIN_INNER && join_type != B2_JOIN_LEFT && join_type != B2_JOIN_RIGHT)
+    fail(B2_ERR_INVALID_ARG, "unknown JoinType " + std::to_string(join_type));  // ballista.proto:266-270
   if (on_l.empty() || on_l.size() != on_r.size()) fail(B2_ERR_INVALID_ARG, "join needs matching on-column lists");
   auto op = std::make_shared<HashJoinExec>();
   op->ctx = ctx;
@@ -216,15 +334,26 @@ OpPtr make_hash_join(Ctx* ctx, OpPtr left, OpPtr right, std::vector<std::string>
   }
   op->layout = make_key_layout(kd);
   op->k32 = kd.size() == 1 && (kd[0] == B2_INT32 || kd[0] == B2_DATE32);
-  // output = left fields ++ right fields minus right on-columns named like their left partner (A.3)
-  op->out = ls;
-  for (size_t c = 0; c < rs.fields.size(); ++c) {
-    bool dup = false;
+  // output = left fields ++ right fields; an `on` column named like its partner appears once: Inner / Left keep the
+  // left one, Right keeps the right one (A.3).  An outer join makes the null-extended side's fields nullable.
+  auto is_dup = [&](const std::vector<int>& on_side, int c) {
     for (size_t i = 0; i < on_l.size(); ++i)
-      if ((int)c == op->on_right[i] && on_l[i] == on_r[i]) dup = true;
-    if (dup) continue;
+      if (c == on_side[i] && on_l[i] == on_r[i]) return true;
+    return false;
+  };
+  for (size_t c = 0; c < ls.fields.size(); ++c) {
+    if (join_type == B2_JOIN_RIGHT && is_dup(op->on_left, (int)c)) continue;
+    op->left_keep.push_back((int)c);
+    Field f = ls.fields[c];
+    if (join_type == B2_JOIN_RIGHT) f.nullable = true;
+    op->out.fields.push_back(f);
+  }
+  for (size_t c = 0; c < rs.fields.size(); ++c) {
+    if (join_type != B2_JOIN_RIGHT && is_dup(op->on_right, (int)c)) continue;
     op->right_keep.push_back((int)c);
-    op->out.fields.push_back(rs.fields[c]);
+    Field f = rs.fields[c];
+    if (join_type == B2_JOIN_LEFT) f.nullable = true;
+    op->out.fields.push_back(f);
   }
   return op;
 }
@@ -238,6 +367,7 @@ struct RepartitionExec : Op {
   int n_out = 1;
   KeyLayout layout;
   bool computed = false;
+  uint64_t computed_version = 0;               // version of the input subtree the cached outputs were computed from
   std::vector<std::vector<BatchPtr>> outputs;  // per output partition
   std::vector<char> need;                      // output columns a parent will read (empty = all)
 
@@ -250,12 +380,22 @@ struct RepartitionExec : Op {
   std::shared_ptr<SemiFilter> semi;            // Bloom filters of the join this exchange feeds (probe side), or null
   bool exchange_mode() const { return scheme == B2_PART_HASH && ctx->comm && n_out == ctx->nranks; }
   bool accepts_semi_filter(int key_col) const override {
-    if (computed || !exchange_mode() || n_out > 32 || keys.size() != 1) return false;
+    if (!exchange_mode() || n_out > 32 || keys.size() != 1) return false;
     const Expr& k = *keys[0];
     return k.kind == B2_EXPR_COLUMN && k.col == key_col && (k.dtype == B2_INT32 || k.dtype == B2_DATE32);
   }
   void set_semi_filter(std::shared_ptr<SemiFilter> f) override { semi = std::move(f); }
   bool per_rank_partitions() const override { return exchange_mode(); }
+  bool exchange_on(std::vector<int>* key_cols, int* n) const override {
+    if (!exchange_mode()) return false;
+    key_cols->clear();
+    for (auto& k : keys) {
+      if (k->kind != B2_EXPR_COLUMN) return false;
+      key_cols->push_back(k->col);
+    }
+    *n = n_out;
+    return true;
+  }
   // a FilterExec below a hash repartition rides in the split kernels (rows it rejects get no destination)
   bool fuse() const { return scheme == B2_PART_HASH && n_out <= 32 && !getenv("B2_DISABLE_FUSION"); }
 
@@ -287,7 +427,7 @@ struct RepartitionExec : Op {
     for (auto& k : keys) kc.push_back(eval_expr(ctx, k, b));
     Column mask;
     RowPred rp;
-    if (pred && b.num_rows && !compile_row_pred(pred, b, &rp)) mask = eval_expr(ctx, pred, b);
+    if (pred && b.num_rows && !compile_row_pred(pred, b, &rp)) mask = eval_predicate(ctx, pred, b);
     const uint8_t* m = mask.data ? mask.values<uint8_t>() : nullptr;
     if (kc.size() == 1 && (kc[0].dtype == B2_INT32 || kc[0].dtype == B2_DATE32)) {
       // one Int32 key: hashed straight from the column (same value as its packed form), nothing materialised
@@ -320,7 +460,11 @@ struct RepartitionExec : Op {
     return perm;
   }
   void compute() {
-    if (computed) return;
+    // the outputs of one input version are computed once and served partition by partition; re-feeding a leaf
+    // (b2_memory_exec_clear / add) moves the version and the next execute() recomputes, as the reference does per task
+    const uint64_t v = children[0]->version();
+    if (computed && computed_version == v) return;
+    computed_version = v;
     outputs.assign(n_out, {});
     Op* in = children[0].get();
     ExprPtr pred;
@@ -437,13 +581,6 @@ OpPtr make_repartition(Ctx* ctx, OpPtr input, int scheme, std::vector<ExprPtr> k
 bool op_is_exchange(Op* op) {
   auto* r = dynamic_cast<RepartitionExec*>(op);
   return r && r->exchange_mode();
-}
-
-void repartition_reset(Op* op) {
-  if (auto* r = dynamic_cast<RepartitionExec*>(op)) {
-    r->computed = false;
-    r->outputs.clear();
-  }
 }
 
 }  // namespace b2

@@ -255,7 +255,30 @@ struct ExprBuilder {
         nodes.push_back(n);
         break;
       }
-      case 10: fail(B2_ERR_NOT_IMPLEMENTED, "CASE expressions");
+      case 10: {  // CaseNode{expr=1, when_then_expr=2 repeated WhenThen{when_expr=1, then_expr=2}, else_expr=3}
+        Slice m = f.sub;
+        Field g;
+        Slice base, els;
+        bool has_base = false, has_else = false;
+        std::vector<Slice> wt;
+        while (next_field(m, &g)) {
+          if (g.number == 1 && g.wire == 2) { base = g.sub; has_base = true; }
+          if (g.number == 2 && g.wire == 2) wt.push_back(g.sub);
+          if (g.number == 3 && g.wire == 2) { els = g.sub; has_else = true; }
+        }
+        if (wt.empty()) fail(B2_ERR_INVALID_ARG, "CaseNode without WHEN / THEN");
+        if (has_base) emit(base);
+        for (auto& w : wt) {
+          emit(member(w, 1, "WhenThen.when_expr"));
+          emit(member(w, 2, "WhenThen.then_expr"));
+        }
+        if (has_else) emit(els);
+        b2_expr_node n = blank(B2_EXPR_CASE);
+        n.op = (has_base ? 1 : 0) | (has_else ? 2 : 0);
+        n.nchildren = (has_base ? 1 : 0) + 2 * (int)wt.size() + (has_else ? 1 : 0);
+        nodes.push_back(n);
+        break;
+      }
       case 11: {  // CastNode{expr=1, arrow_type=2}
         emit(member(f.sub, 1, "CastNode.expr"));
         b2_expr_node n = blank(B2_EXPR_CAST);
@@ -281,6 +304,22 @@ struct ExprBuilder {
         b2_expr_node n = blank(B2_EXPR_IN_LIST);
         n.nchildren = 1 + (int)list.size();
         n.op = neg;
+        nodes.push_back(n);
+        break;
+      }
+      case 16: {  // ScalarFunctionNode{fun=1 (enum, default SQRT = 0), expr=2 repeated}
+        Slice m = f.sub;
+        Field g;
+        int fun = 0;
+        std::vector<Slice> args;
+        while (next_field(m, &g)) {
+          if (g.number == 1 && g.wire == 0) fun = (int)g.v;
+          if (g.number == 2 && g.wire == 2) args.push_back(g.sub);
+        }
+        for (auto& a : args) emit(a);
+        b2_expr_node n = blank(B2_EXPR_SCALAR_FN);
+        n.op = fun;
+        n.nchildren = (int)args.size();
         nodes.push_back(n);
         break;
       }

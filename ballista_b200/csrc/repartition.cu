@@ -561,6 +561,12 @@ BatchPtr slice_batch(Ctx* ctx, const Batch& b, int64_t begin, int64_t end) {
       out->cols.push_back(std::move(o));
       continue;
     }
+    if (c.valid) {
+      o.valid = dev_alloc(ctx, (size_t)m + 16);
+      if (m)
+        B2_CUDA(cudaMemcpyAsync(o.valid->ptr, c.valid->as<uint8_t>() + begin, (size_t)m, cudaMemcpyDeviceToDevice,
+                                ctx->stream));
+    }
     if (c.dtype == B2_UTF8) {
       int32_t ends[2] = {0, 0};
       if (c.length) {

@@ -214,6 +214,7 @@ struct LensToOff {
 // Shuffle of `local` given phase 1 of its hash split (`st`, n_out == nranks).  Returns this rank's output
 // partition, or nullptr when peer mapping is unavailable (the caller then takes the NCCL send/recv path).
 BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
+  require_no_nulls(local, "exchange over NVLink");
   if (!ctx->comm) fail(B2_ERR_INVALID_ARG, "no communicator (call b2_comm_init)");
   Comm* cm = ctx->comm;
   if (cm->p2p_state < 0) return nullptr;

@@ -7,6 +7,9 @@
 
 namespace b2 {
 
+// status word of an aggregate launch (read back by the host)
+enum { AGG_OK = 0, AGG_ABORT_CARDINALITY = 1, AGG_KEY_TOO_WIDE = 2, AGG_TABLE_FULL = 3 };
+
 typedef unsigned long long u64;
 typedef unsigned __int128 u128;
 
@@ -101,6 +104,8 @@ struct TableRef {
   u64* cnt;
   u64 cap;        // power of two
   int* n_groups;  // number of claimed slots
+  uint32_t* slot_list;  // slot_list[g] = slot of the g-th claimed group (claim order), or null: the emit step reads
+                        // its groups from this list instead of compacting the table
 };
 
 // find or claim the slot of `key`; returns slot index, or ~0 when the table is full
@@ -116,7 +121,11 @@ __device__ __forceinline__ u64 table_upsert(const TableRef& t, const Key128& key
       if (key_eq(old, empty)) {
         // one counter update per group of lanes that claimed together, not one same-address reduction per claim
         const unsigned together = __activemask();
-        if ((threadIdx.x & 31) == __ffs(together) - 1) atomicAdd(t.n_groups, __popc(together));
+        const int leader = __ffs(together) - 1, lane = threadIdx.x & 31;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(t.n_groups, __popc(together));
+        base = __shfl_sync(together, base, leader);
+        if (t.slot_list) t.slot_list[base + __popc(together & ((1u << lane) - 1u))] = (uint32_t)h;
         return h;
       }
       if (key_eq(old, key)) return h;

@@ -21,9 +21,13 @@ BufPtr mask_to_indices(Ctx* ctx, const uint8_t* mask, int64_t n, int64_t* count)
   return idx;
 }
 
+// idx == 0xFFFFFFFF marks a null-extended row (outer joins): its value slot is zero and its validity byte 0
 template <class T> __global__ void gather_kernel(const T* in, const uint32_t* idx, int64_t m, T* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  for (; i < m; i += (int64_t)gridDim.x * blockDim.x) out[i] = in[idx[i]];
+  for (; i < m; i += (int64_t)gridDim.x * blockDim.x) {
+    uint32_t r = idx[i];
+    out[i] = r == 0xFFFFFFFFu ? T() : in[r];
+  }
 }
 struct StrOffOut {
   int32_t* off;
@@ -38,16 +42,18 @@ __global__ void gather_chars_kernel(const int32_t* in_off, const uint8_t* in_chr
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   for (; i < m; i += (int64_t)gridDim.x * blockDim.x) {
     int64_t r = idx[i];
+    if (r == 0xFFFFFFFFll) continue;
     int32_t b = in_off[r], len = in_off[r + 1] - b, o = out_off[i];
     for (int q = 0; q < len; ++q) out_chr[o + q] = in_chr[b + q];
   }
 }
 
-Column take_column(Ctx* ctx, const Column& c, const uint32_t* idx, int64_t m) {
+Column take_column(Ctx* ctx, const Column& c, const uint32_t* idx, int64_t m, bool null_extended) {
   Column out;
   out.dtype = c.dtype;
   out.length = m;
   if (!c.data) return out;  // elided by column pruning upstream: stays elided
+  if (c.valid || null_extended) out.valid = valid_gather(ctx, c.validity(), idx, m);
   int grid = grid_for(ctx, 8, m, 256);
   if (c.dtype == B2_UTF8) {
     out.data = dev_alloc_zero(ctx, (size_t)(m + 1) * 4);
@@ -86,6 +92,18 @@ BatchPtr take_batch(Ctx* ctx, const Batch& b, const uint32_t* idx, int64_t m) {
   return out;
 }
 
+// a column of `n` NULLs (the absent side of an outer join's unmatched rows)
+Column null_column(Ctx* ctx, int dtype, int64_t n) {
+  Column c;
+  c.dtype = dtype;
+  c.length = n;
+  size_t w = dtype == B2_UTF8 ? 4 : dtype_width(dtype);
+  c.data = dev_alloc_zero(ctx, (size_t)(n + 1) * w + 16);
+  if (dtype == B2_UTF8) c.chars = dev_alloc(ctx, 16);
+  c.valid = dev_alloc_zero(ctx, (size_t)n + 16);
+  return c;
+}
+
 BatchPtr empty_batch(Ctx* ctx, const Schema& schema) {
   auto b = std::make_shared<Batch>();
   b->ctx = ctx;
@@ -121,6 +139,23 @@ BatchPtr concat_batches(Ctx* ctx, const Schema& schema, const std::vector<BatchP
     if (!batches[0]->cols[ci].data) {  // elided by column pruning
       out->cols.push_back(std::move(c));
       continue;
+    }
+    bool any_valid = false;
+    for (auto& b : batches) any_valid |= (bool)b->cols[ci].valid;
+    if (any_valid) {
+      c.valid = dev_alloc(ctx, (size_t)n + 16);
+      int64_t row = 0;
+      for (auto& b : batches) {
+        const Column& s = b->cols[ci];
+        if (s.length) {
+          if (s.valid)
+            B2_CUDA(cudaMemcpyAsync(c.valid->as<uint8_t>() + row, s.valid->ptr, (size_t)s.length, cudaMemcpyDeviceToDevice,
+                                    ctx->stream));
+          else
+            B2_CUDA(cudaMemsetAsync(c.valid->as<uint8_t>() + row, 1, (size_t)s.length, ctx->stream));
+        }
+        row += s.length;
+      }
     }
     if (c.dtype == B2_UTF8) {
       int64_t chars = 0;

@@ -61,6 +61,10 @@ class Expr:
     def cast(self, dtype):
         return Expr(K.EXPR_CAST, [self], dtype=dtype)
 
+    def like(self, pattern):
+        """SQL LIKE (% and _ wildcards) against a literal pattern (BinaryExprNode op "Like")."""
+        return self._bin(K.OP_LIKE, pattern)
+
     def is_null(self): return Expr(K.EXPR_IS_NULL, [self])
     def is_not_null(self): return Expr(K.EXPR_IS_NOT_NULL, [self])
 
@@ -136,6 +140,25 @@ def lit(value, dtype=None):
         else:
             raise TypeError(f"unsupported literal {value!r}")
     return Expr(K.EXPR_LITERAL, value=value, dtype=dtype)
+
+
+def case(when_then, otherwise=None, base=None):
+    """CASE [base] WHEN w THEN t ... [ELSE otherwise] END (CaseNode, ballista.proto:141-150).
+    `when_then` = [(when, then), ...]."""
+    wrap = lambda v: v if isinstance(v, Expr) else lit(v)
+    children = [wrap(base)] if base is not None else []
+    for w, t in when_then:
+        children += [wrap(w), wrap(t)]
+    if otherwise is not None:
+        children.append(wrap(otherwise))
+    return Expr(K.EXPR_CASE, children, op=(1 if base is not None else 0) | (2 if otherwise is not None else 0))
+
+
+def scalar_fn(name, *args):
+    """ScalarFunctionNode (ballista.proto:80-119): sqrt, sin, ..., floor, ceil, round, trunc, abs, signum,
+    octetlength, lower, upper."""
+    return Expr(K.EXPR_SCALAR_FN, [a if isinstance(a, Expr) else lit(a) for a in args],
+                op=K.SCALAR_FUNCTIONS.index(name.lower()))
 
 
 def date(s):

@@ -114,7 +114,10 @@ enum b2_expr_kind {
   B2_EXPR_NEGATIVE = 8, /* NegativeNode      : 1 child                                                    */
   B2_EXPR_BETWEEN = 9,  /* BetweenNode       : 3 children (expr, low, high); op!=0 => NOT BETWEEN         */
   B2_EXPR_IN_LIST = 10, /* InListNode        : nchildren = 1 + list length; op!=0 => NOT IN               */
-  B2_EXPR_CASE = 11     /* CaseNode          : not implemented (B2_ERR_NOT_IMPLEMENTED)                   */
+  B2_EXPR_CASE = 11,    /* CaseNode          : nchildren children = [base] (when, then)* [else];
+                                               op bit 0 = base expression present, bit 1 = ELSE present        */
+  B2_EXPR_SCALAR_FN = 12 /* ScalarFunctionNode: op = ScalarFunction enum value (ballista.proto:80-114),
+                                               nchildren arguments                                             */
 };
 enum b2_binary_op {
   B2_OP_AND = 1, B2_OP_OR, B2_OP_EQ, B2_OP_NOTEQ, B2_OP_LTEQ, B2_OP_LT, B2_OP_GT, B2_OP_GTEQ,
@@ -129,7 +132,7 @@ typedef struct b2_expr_node {
   int32_t op;        /* b2_binary_op / negation flag      */
   int32_t dtype;     /* b2_dtype for LITERAL and CAST     */
   int32_t col;       /* COLUMN: input-schema index        */
-  int32_t nchildren; /* IN_LIST only; others are implied  */
+  int32_t nchildren; /* IN_LIST / CASE / SCALAR_FN; others are implied */
   int32_t reserved;
   int64_t i;         /* integer / date32 literal          */
   double f;          /* Float64 literal                   */

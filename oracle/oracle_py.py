@@ -141,6 +141,39 @@ def hash_join(left_keys, right_keys):
     return li, ri
 
 
+def hash_join_outer(left_keys, right_keys, how, left_valid=None, right_valid=None):
+    """A.3 Inner / Left / Right join over keys that may be NULL (`*_valid`: boolean array, False = some key part NULL).
+    Null keys never match.  Returns (left_idx, right_idx) with -1 marking the null-extended side: the matched pairs in
+    probe order, then (Left) the build rows nothing matched, or (Right) each probe row without a match."""
+    nl, nr = len(left_keys[0]), len(right_keys[0])
+    lv = np.ones(nl, bool) if left_valid is None else np.asarray(left_valid, bool)
+    rv = np.ones(nr, bool) if right_valid is None else np.asarray(right_valid, bool)
+    lrows, rrows = np.nonzero(lv)[0], np.nonzero(rv)[0]
+    li, ri = hash_join([take(k, lrows) for k in left_keys], [take(k, rrows) for k in right_keys])
+    li, ri = lrows[li], rrows[ri]
+    if how == "Left":
+        un = np.setdiff1d(np.arange(nl), li)
+        li, ri = np.concatenate([li, un]), np.concatenate([ri, np.full(len(un), -1)])
+    elif how == "Right":
+        un = np.setdiff1d(np.arange(nr), ri)
+        li, ri = np.concatenate([li, np.full(len(un), -1)]), np.concatenate([ri, un])
+    elif how != "Inner":
+        raise ValueError(how)
+    return li.astype(np.int64), ri.astype(np.int64)
+
+
+def aggregate_skip_nulls(keys, values, valid):
+    """A.2 with NULL inputs: per group (dict key -> (count_rows, count_valid, sum or None)): SUM / AVG / COUNT(x) skip
+    NULLs, SUM of nothing is NULL.  Sequential left-to-right f64 sums, as DataFusion's accumulators."""
+    out = {}
+    for k, v, ok in zip(keys, values, valid):
+        rows, cnt, tot = out.get(k, (0, 0, None))
+        if ok:
+            cnt, tot = cnt + 1, (v if tot is None else tot + v)
+        out[k] = (rows + 1, cnt, tot)
+    return out
+
+
 def hash_partition(key_cols, n_out):
     """A.4: destination partition of every row (equal keys co-locate; which partition is unobservable)."""
     L = lib()
@@ -237,4 +270,5 @@ def q6(cols, n_partitions=1, date_lo=DATE_1994_01_01, date_hi=DATE_1995_01_01, q
     rev = lib().oracle_q6(C.c_int64(n), _ptr(cols["l_shipdate"]), _ptr(cols["l_discount"]), _ptr(cols["l_quantity"]),
                           _ptr(cols["l_extendedprice"]), C.c_int32(date_lo), C.c_int32(date_hi),
                           C.c_double(lo), C.c_double(hi), C.c_double(quantity_lt), n_partitions, C.byref(passing))
-    return float(rev), int(passing.value)
+    # an ungrouped SUM over no rows is NULL, not 0.0 (the accumulator starts as Float64(None))
+    return (float(rev) if passing.value else None), int(passing.value)

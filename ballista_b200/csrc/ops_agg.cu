@@ -210,6 +210,14 @@ BatchPtr HashAggregateExec::run_partial(int partition) {
   };
   BatchPtr cur = next_nonempty(), ahead = cur ? next_nonempty() : nullptr;
   const bool single = cur && !ahead;
+  if (!single) {
+    // Several batches: the accumulator layout is fixed by the first one, so the fused kernels (which do not count
+    // NULLs) are taken only when the schema promises that no column they read holds any.  A single batch is judged by
+    // its own validity buffers.
+    Schema ss = src->schema();
+    for (size_t c = 0; c < touched.size() && c < ss.fields.size(); ++c)
+      if (touched[c] && ss.fields[c].nullable) fusable_shape = false;
+  }
   bool speculated = false;
   std::vector<Column> temps;
   std::vector<BufPtr> tbufs;

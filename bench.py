@@ -13,7 +13,10 @@ stage hop), HashAggregateExec(Final), and the device->host read of the 4 result 
   e2e      : same plan through the C ABI fed with HOST (pinned) Arrow RecordBatches, H2D inside the timed region
   roofline : the fused scan kernel (agg_tma_kernel<Q1>) — 46 algorithmic bytes per row over its
              mean launch duration, CUDA events on the launching stream, vs the measured HBM copy bandwidth
-  cpu_baseline : oracle/ (C++ restatement of the DataFusion plan, one thread per partition) on a bounded sample
+  cpu_baseline : oracle/ (C++ restatement of the DataFusion plan, one thread per partition) on a bounded sample;
+             cpu_baseline_b = pyarrow Acero on the same sample (a production CPU engine as a sanity anchor)
+  parity   : the result of the timed plan over ALL its rows against the oracle over the same rows (counts bit-exact,
+             Float64 sums <= 1e-9 relative); every other config carries its own verdict; a mismatch fails the run
 
 Weak scaling: every rank holds one SF100-sized partition (`--sf` x 6M rows) of an SF(100*N) lineitem;
 `--scaling strong` instead splits one SF100 table across the N ranks (BASELINE.json config 3, literally).
@@ -53,6 +56,8 @@ def parse_args():
     ap.add_argument("--q3-sf", type=float, default=100.0, help="Q3 at the metric's scale: one GPU's own copy at N=1, "
                     "row-range partitions of one database of this scale (strong scaling) at N>1")
     ap.add_argument("--cpu-seconds", type=float, default=3.0, help="wall-clock target of the cpu_baseline sample")
+    ap.add_argument("--no-parity", action="store_true", help="skip the full-size oracle comparisons (untimed)")
+    ap.add_argument("--parity-chunk-rows", type=int, default=1 << 26)
     return ap.parse_args()
 
 
@@ -180,8 +185,10 @@ def unpin(torch, addrs):
         rt.cudaHostUnregister(a)
 
 
+
+
 def check_q1_rows(rows, n_rows_total):
-    """Cheap invariants of the Q1 result (full parity is tests/; this guards the timed path)."""
+    """Cheap invariants of the Q1 result (the parity block compares every value with the oracle)."""
     assert 1 <= len(rows) <= 4, rows
     keys = sorted((r["l_returnflag"], r["l_linestatus"]) for r in rows)
     assert keys == sorted(set(keys)), keys
@@ -192,128 +199,320 @@ def check_q1_rows(rows, n_rows_total):
     return total
 
 
+def workload_config(sf, scaling, world, rows_per_gpu, rows_total):
+    """`config` of the JSON line: the SAME object in this repo's arm and in the reference arm of one run."""
+    return {"workload": f"TPC-H Q1 over synthetic SF{sf:g} lineitem: filter l_shipdate <= 1998-09-02, group by "
+                        "(l_returnflag, l_linestatus), 4 x SUM + 3 x AVG + COUNT (rust/benchmarks/tpch/queries/q1.sql)",
+            "query": "q1", "sf": sf, "scaling": scaling, "n_gpus": world, "rows_per_gpu": int(rows_per_gpu),
+            "rows_total": int(rows_total), "algorithmic_bytes_per_row": Q1_BYTES_PER_ROW,
+            "partitioning": ("one SF%g partition per GPU (weak: an SF%g table over %d GPUs)" % (sf, sf * world, world))
+            if scaling == "weak" else ("one SF%g table in %d row-range partitions" % (sf, world)),
+            "l2": "inputs larger than L2 (no flush needed)" if rows_per_gpu * Q1_BYTES_PER_ROW > 512e6 else
+                  "inputs smaller than L2"}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# parity: the oracle over the SAME rows the timed plan read (untimed).  Rows are regenerated chunk by chunk by the
+# library's counter-based generator, copied to the host and aggregated by oracle/; the first chunk is also compared
+# bit for bit with the oracle's own host generator, so both sides of the comparison see one table.
+# ---------------------------------------------------------------------------------------------------------
+def arrow_to_oracle_cols(O, rb):
+    import numpy as np
+    import pyarrow as pa
+    cols = {}
+    for name, col in zip(rb.schema.names, rb.columns):
+        n = len(col)
+        bufs = col.buffers()
+        if pa.types.is_string(col.type):
+            cols[name] = O.Utf8(np.frombuffer(bufs[1], dtype=np.int32, count=n + 1 + col.offset)[col.offset:],
+                                np.frombuffer(bufs[2], dtype=np.uint8) if bufs[2] is not None else np.zeros(0, np.uint8))
+        elif pa.types.is_date32(col.type) or pa.types.is_int32(col.type):
+            cols[name] = np.frombuffer(bufs[1], dtype=np.int32, count=n + col.offset)[col.offset:]
+        else:
+            cols[name] = col.to_numpy(zero_copy_only=True)
+    return cols
+
+
+def check_generator(O, sf, r0, cols, limit=1 << 20):
+    """the first `limit` rows of a device-generated chunk == the oracle's host generator, bit for bit"""
+    import numpy as np
+    n = min(limit, len(next(iter(cols.values()))))
+    want = O.gen_lineitem(sf, r0, n)
+    for name, c in cols.items():
+        w = want[name]
+        if isinstance(c, O.Utf8):
+            assert np.array_equal(c.offsets[:n + 1] - c.offsets[0], w.offsets) and \
+                np.array_equal(c.chars[c.offsets[0]:c.offsets[n]], w.chars[:w.offsets[n]]), name
+        else:
+            assert np.array_equal(c[:n], w), name
+    return n
+
+
+def oracle_scan_chunks(ctx, O, table_sf, r0, r1, columns, chunk_rows, fn):
+    """fn(oracle columns of one chunk) for every chunk of lineitem rows [r0, r1); -> rows the generators agreed on"""
+    checked = 0
+    for b in range(r0, r1, chunk_rows):
+        e = min(b + chunk_rows, r1)
+        db = ctx.tpch("lineitem", table_sf, b, e, columns=columns)
+        rb = db.to_arrow()
+        del db
+        cols = arrow_to_oracle_cols(O, rb)
+        if b == r0:
+            checked = check_generator(O, table_sf, b, cols)
+        fn(cols)
+        del cols, rb
+    return checked
+
+
+def oracle_q1_partition(ctx, O, table_sf, r0, r1, threads, chunk_rows, columns):
+    """-> ({(flag, status): [sum_qty, sum_base, sum_disc_price, sum_charge, sum_disc, count]}, generator rows checked)"""
+    acc = {}
+
+    def one(cols):
+        for r in O.q1(cols, n_partitions=threads):
+            a = acc.setdefault((r["l_returnflag"], r["l_linestatus"]), [0.0, 0.0, 0.0, 0.0, 0.0, 0])
+            for k, nm in enumerate(("sum_qty", "sum_base_price", "sum_disc_price", "sum_charge")):
+                a[k] += r[nm]
+            a[4] += r["avg_disc"] * r["count_order"]
+            a[5] += r["count_order"]
+    checked = oracle_scan_chunks(ctx, O, table_sf, r0, r1, columns, chunk_rows, one)
+    return acc, checked
+
+
+def merge_q1_acc(accs):
+    out = {}
+    for acc in accs:
+        for k, v in acc.items():
+            a = out.setdefault(k, [0.0, 0.0, 0.0, 0.0, 0.0, 0])
+            for i in range(6):
+                a[i] += v[i]
+    return out
+
+
+def parity_q1(name, gpu_rows, acc, rows, checked):
+    """GPU result rows vs the merged oracle accumulators: group keys and counts bit-exact, sums / averages <= 1e-9."""
+    got = {(r["l_returnflag"], r["l_linestatus"]): r for r in gpu_rows}
+    keys_equal = sorted(got) == sorted(acc)
+    counts_equal = keys_equal and all(got[k]["count_order"] == acc[k][5] for k in acc)
+    worst = 0.0
+    if keys_equal:
+        for k, a in acc.items():
+            g, n = got[k], a[5]
+            want = {"sum_qty": a[0], "sum_base_price": a[1], "sum_disc_price": a[2], "sum_charge": a[3],
+                    "avg_qty": a[0] / n, "avg_price": a[1] / n, "avg_disc": a[4] / n}
+            for nm, w in want.items():
+                worst = max(worst, abs(g[nm] - w) / abs(w))
+    ok = bool(keys_equal and counts_equal and worst <= 1e-9)
+    return {"config": name, "rows": int(rows), "groups": len(got), "keys_equal": bool(keys_equal),
+            "counts_equal": bool(counts_equal), "max_rel_err": worst, "tolerance": 1e-9, "ok": ok,
+            "checker": "oracle/ Q1 over the same rows (chunks regenerated by the library's generator, D2H, aggregated on "
+                       "the host)", "generator_rows_cross_checked": int(checked)}
+
+
+def q3_table_arrays(table):
+    """pa.Table of the Q3 Final -> (orderkey, orderdate days, shippriority, revenue) sorted by orderkey"""
+    import numpy as np
+    import pyarrow as pa
+    ok = table["l_orderkey"].combine_chunks().to_numpy()
+    od = table["o_orderdate"].combine_chunks().cast(pa.int32()).to_numpy()
+    sp = table["o_shippriority"].combine_chunks().to_numpy()
+    rv = table["revenue"].combine_chunks().to_numpy()
+    o = np.argsort(ok, kind="stable")
+    return ok[o], od[o], sp[o], rv[o]
+
+
+def q3_checksum(arrs):
+    """order-independent digest of a set of Q3 groups: (count, 64-bit key checksum, revenue sum)"""
+    import math
+    import numpy as np
+    ok, od, sp, rv = arrs
+    with np.errstate(over="ignore"):
+        h = (ok.astype(np.uint64) * np.uint64(0x9E3779B97F4A7C15) + od.astype(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F)
+             + sp.astype(np.uint64) * np.uint64(0x165667B19E3779F9))
+        h ^= h >> np.uint64(29)
+        return int(len(ok)), int(h.sum(dtype=np.uint64)), math.fsum(rv.tolist())
+
+
+def parity_q3(name, arrs, want, rows):
+    """full comparison with the oracle's Q3: group keys bit-exact, revenue <= 1e-9 relative"""
+    import numpy as np
+    ok, od, sp, rv = arrs
+    keys_equal = (len(ok) == len(want["l_orderkey"]) and np.array_equal(ok, want["l_orderkey"]) and
+                  np.array_equal(od, want["o_orderdate"]) and np.array_equal(sp, want["o_shippriority"]))
+    worst = float(np.max(np.abs(rv - want["revenue"]) / np.abs(want["revenue"]))) if keys_equal and len(ok) else 0.0
+    return {"config": name, "input_rows": int(rows), "groups": int(len(ok)), "keys_equal": bool(keys_equal),
+            "counts_equal": bool(keys_equal), "max_rel_err": worst, "tolerance": 1e-9,
+            "ok": bool(keys_equal and worst <= 1e-9),
+            "checker": "oracle/ Q3 (filters, two collect-left hash joins, group-by) over the oracle's own host tables"}
+
+
 # ---------------------------------------------------------------------------------------------------------
 # this repo's arm
 # ---------------------------------------------------------------------------------------------------------
-def run_b200(args):
+class Env:
+    pass
+
+
+def setup_env(args):
     import torch
     import torch.distributed as dist
     import ballista_b200 as b2
-    from ballista_b200 import tpch, _capi
-
-    rank, local_rank, world = env_rank()
+    from ballista_b200 import cluster
+    env = Env()
+    env.rank, env.local_rank, env.world = env_rank()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (ballista_b200 has no CPU fallback)")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    ctx = b2.Context(local_rank)
-    from ballista_b200 import cluster
-    cluster.attach_communicator(ctx, dist, rank, world)
-    stream = torch.cuda.ExternalStream(ctx.cuda_stream)
+    torch.cuda.set_device(env.local_rank)
+    if env.world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", env.local_rank))
+    env.torch, env.dist, env.cluster = torch, dist, cluster
+    env.ctx = b2.Context(env.local_rank)
+    cluster.attach_communicator(env.ctx, dist, env.rank, env.world)
+    env.stream = torch.cuda.ExternalStream(env.ctx.cuda_stream)
+    env.local_world = int(os.environ.get("LOCAL_WORLD_SIZE", env.world))
+    env.host_threads = max(1, (os.cpu_count() or 1) // max(env.local_world, 1))
+    return env
 
+
+def barrier(env):
+    if env.world > 1:
+        env.dist.barrier()
+    env.torch.cuda.synchronize()
+    env.ctx.synchronize()
+
+
+def time_steps(env, fn, steps, warmup, profile=False, sample_clocks=False):
+    """W untimed + K timed calls of fn(), one CUDA event per step on the library's stream, barrier + synchronize on
+    both sides.  -> dict(ms_total (max over ranks), per-step ms list (this rank), launches, kernel (ms, n), clocks, last)"""
+    torch, ctx = env.torch, env.ctx
+    last = None
+    for _ in range(warmup):
+        last = fn()
+    barrier(env)
+    sampler = None
+    if sample_clocks:
+        sampler = ClockSampler(env.local_rank)
+        sampler.start()
+    if profile:
+        ctx.set_profiling(True)
+        ctx.profile()
+    l0 = ctx.kernel_launches()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    ev[0].record(env.stream)
+    for k in range(steps):
+        last = fn()
+        ev[k + 1].record(env.stream)
+    barrier(env)
+    ms = ev[0].elapsed_time(ev[steps])
+    per_step = [ev[k].elapsed_time(ev[k + 1]) for k in range(steps)]
+    launches = ctx.kernel_launches() - l0
+    kern = ctx.profile() if profile else (0.0, 0)
+    if profile:
+        ctx.set_profiling(False)
+    clocks = sampler.result() if sampler else None
+    return {"ms_total": env.cluster.max_over_ranks(env.dist, torch, ms, env.world), "per_step": per_step,
+            "launches": launches, "kernel": kern, "clocks": clocks, "last": last}
+
+
+def step_stats(per_step):
+    return {"median_ms": statistics.median(per_step), "best_ms": min(per_step), "worst_ms": max(per_step)}
+
+
+def gather_objects(env, obj):
+    if env.world == 1:
+        return [obj]
+    out = [None] * env.world
+    env.dist.all_gather_object(out, obj)
+    return out
+
+
+def run_b200(args, env):
+    from ballista_b200 import tpch, _capi
+    ctx, rank, world, cluster = env.ctx, env.rank, env.world, env.cluster
     # ---- workload: this rank's lineitem partition, generated in HBM (setup, untimed) ----
     if args.scaling == "weak":
         table_sf = args.sf * world
         rows_local = _capi.lib().b2_tpch_num_rows(b"lineitem", float(args.sf))
         r0 = rank * rows_local
+        rows_total = rows_local * world
     else:
         table_sf = args.sf
-        total = _capi.lib().b2_tpch_num_rows(b"lineitem", float(args.sf))
-        r0, r1 = cluster.partition_rows(total, world, rank, align=32)
+        rows_total = _capi.lib().b2_tpch_num_rows(b"lineitem", float(args.sf))
+        r0, r1 = cluster.partition_rows(rows_total, world, rank, align=32)
         rows_local = r1 - r0
-    rows_total = rows_local * world if args.scaling == "weak" else _capi.lib().b2_tpch_num_rows(b"lineitem", float(args.sf))
-    # batches of at most 2^30 rows (Utf8 offsets are int32)
-    max_batch = 1 << 30
+    rows_gpu0 = rows_local if args.scaling == "weak" else cluster.partition_rows(rows_total, world, 0, align=32)[1]
+    max_batch = 1 << 30  # batches of at most 2^30 rows (Utf8 offsets are int32)
     dev_batches = [ctx.tpch("lineitem", table_sf, b, min(b + max_batch, r0 + rows_local), columns=tpch.Q1_COLUMNS)
                    for b in range(r0, r0 + rows_local, max_batch)]
     ctx.synchronize()
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        ctx.synchronize()
-
-    def step(source_batches):
-        scan = tpch.scan(ctx, [source_batches])
-        partial = tpch.q1_partial(scan)
-        table = tpch.run_two_stage(ctx, partial, lambda s: tpch.q1_final(s, scan.schema()), merge="allgather")
-        return table, partial
-
-    def timed(source_batches, steps, warmup, profile):
-        for _ in range(warmup):
-            step(source_batches)
-        barrier()
-        sampler = ClockSampler(local_rank)
-        sampler.start()
-        if profile:
-            ctx.set_profiling(True)
-            ctx.profile()
-        l0 = ctx.kernel_launches()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(steps):
-            table, partial = step(source_batches)
-        e1.record(stream)
-        barrier()
-        ms = e0.elapsed_time(e1)
-        launches = ctx.kernel_launches() - l0
-        kern = ctx.profile() if profile else (0.0, 0)
-        if profile:
-            ctx.set_profiling(False)
-        clocks = sampler.result()
-        return cluster.max_over_ranks(dist, torch, ms, world), launches, kern, clocks, table, partial
+    def make_step(source_batches):
+        def step():
+            scan = tpch.scan(ctx, [source_batches])
+            partial = tpch.q1_partial(scan)
+            table = tpch.run_two_stage(ctx, partial, lambda s: tpch.q1_final(s, scan.schema()), merge="allgather")
+            return table, partial
+        return step
 
     # ---- value: inputs resident in HBM ----
-    ms, launches, (kern_ms, kern_n), clocks, table, partial = timed(dev_batches, args.steps, args.warmup, True)
+    t = time_steps(env, make_step(dev_batches), args.steps, args.warmup, profile=True, sample_clocks=True)
+    table, partial = t["last"]
     rows = table.to_pylist()
     passed = check_q1_rows(rows, rows_total)
     assert partial.last_path().startswith("fused:") and "[tma" in partial.last_path(), partial.last_path()
+    ms, (kern_ms, kern_n) = t["ms_total"], t["kernel"]
     value = rows_total * args.steps / (ms / 1e3)
     peaks = measured_peaks()
     peak = peaks.get("hbm_gbs")
-    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs, copy read+write)"
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs, copy read+write, burst: the kernel is timed alone by its own events)"
     if not peak:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    achieved = (Q1_BYTES_PER_ROW * rows_local * args.steps / max(kern_n, 1) * 1.0) / (kern_ms / max(kern_n, 1) / 1e3) / 1e9 if kern_n else None
+    rows_per_launch = rows_local * args.steps / max(kern_n, 1)
+    achieved = Q1_BYTES_PER_ROW * rows_per_launch / (kern_ms / max(kern_n, 1) / 1e3) / 1e9 if kern_n else None
     roofline = {"bound": "hbm", "kernel": "agg_tma_kernel<FusedSrc<Q1>, narrow> (TMA-fed scan + filter + expressions + partial aggregate)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                 "traffic": None, "peak_source": peak_src, "launches": kern_n,
                 "avg_launch_ms": kern_ms / kern_n if kern_n else None,
-                "algorithmic_bytes_per_row": Q1_BYTES_PER_ROW, "rows_per_launch": rows_local * args.steps / max(kern_n, 1),
-                "kernel_share_of_step": kern_ms / ms if ms else None}
+                "algorithmic_bytes_per_row": Q1_BYTES_PER_ROW, "rows_per_launch": rows_per_launch,
+                "kernel_share_of_step": kern_ms / ms if ms else None,
+                "step_frac_of_peak": Q1_BYTES_PER_ROW * rows_local * args.steps / (ms / 1e3) / 1e9 / peak}
     traffic_file = os.path.join(ROOT, "profiles", "q1_traffic.json")
     if os.path.exists(traffic_file):
         try:
             with open(traffic_file) as f:
                 tj = json.load(f)
-            if tj.get("rows_per_launch") == roofline["rows_per_launch"]:
+            if tj.get("rows_per_launch") == rows_per_launch:
                 roofline["traffic"] = tj.get("dram_bytes_per_launch")
+                roofline["traffic_source"] = "recorded, not measured in this run: " + tj.get("source", "profiles/q1_traffic.json")
         except Exception:
             pass
-
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
            "dtype": "f64", "data": "synthetic (counter-based TPC-H-shaped generator, seed 42, generated in HBM)",
-           "config": {"workload": f"TPC-H Q1, SF{args.sf:g} lineitem ({rows_local} rows x 46 B = "
-                                  f"{rows_local * 46 / 1e9:.2f} GB) per GPU" if args.scaling == "weak" else
-                                  f"TPC-H Q1, one SF{args.sf:g} lineitem split over {world} GPUs",
-                      "rows_per_gpu": rows_local, "rows_total": rows_total, "rows_passing_filter": passed,
-                      "l2": "inputs larger than L2 (no flush needed)" if rows_local * 46 > 512e6 else "inputs smaller than L2!",
-                      "parallelism": f"partition-per-GPU x{world}, partial states all-gathered over NCCL" if world > 1 else "1 partition"},
-           "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
-           "GB_per_s": value * Q1_BYTES_PER_ROW / 1e9}
-    return ctx, out, dev_batches, timed, (rank, world, torch)
+           "config": workload_config(args.sf, args.scaling, world, rows_gpu0, rows_total),
+           "gpu_launches": t["launches"], "clocks": t["clocks"], "roofline": roofline,
+           "GB_per_s": value * Q1_BYTES_PER_ROW / 1e9, "rows_passing_filter": passed,
+           "step_ms": dict(step_stats(t["per_step"]), mean_ms=ms / args.steps,
+                           note="per-step CUDA-event times of rank 0; value uses the max-over-ranks total"),
+           "plan_path": partial.last_path()}
+    # ---- parity at full size: every rank runs the oracle over ITS rows, rank 0 merges and compares ----
+    if not args.no_parity:
+        from oracle import oracle_py as O
+        O.lib()
+        acc, checked = oracle_q1_partition(ctx, O, table_sf, r0, r0 + rows_local, env.host_threads, args.parity_chunk_rows,
+                                           tpch.Q1_COLUMNS)
+        accs = gather_objects(env, acc)
+        out["parity"] = parity_q1(f"q1_sf{args.sf:g}_x{world}_{args.scaling}", rows, merge_q1_acc(accs), rows_total, checked)
+    env.q1 = (dev_batches, make_step, table_sf, r0, rows_local)
+    return out
 
 
-def run_e2e(args, ctx, dev_batches, timed, env):
+def run_e2e(args, env):
     """Same plan fed with HOST RecordBatches (pinned): H2D of every input column inside the timed region."""
-    rank, world, torch = env
-    rows_local = sum(b.num_rows for b in dev_batches)
+    dev_batches, make_step, _, _, rows_local = env.q1
+    torch, world = env.torch, env.world
     need = rows_local * Q1_BYTES_PER_ROW
-    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", world))
-    budget = mem_available_bytes() // max(local_world, 1) // 3
+    budget = mem_available_bytes() // max(env.local_world, 1) // 3
     frac = 1.0
     if need > budget:
         frac = max(budget / need, 0.01)
@@ -330,13 +529,16 @@ def run_e2e(args, ctx, dev_batches, timed, env):
             host_batches.append(rb.slice(o, args.e2e_batch_rows))
         rows_e2e += rb.num_rows
     h2d = rows_e2e * Q1_BYTES_PER_ROW + 8 * len(host_batches)  # Utf8 offsets carry one extra int32 per batch
-    ms, launches, _, clocks, table, _ = timed(host_batches, args.e2e_steps, 1, False)
+    t = time_steps(env, make_step(host_batches), args.e2e_steps, 1)
+    table, _ = t["last"]
+    ms = t["ms_total"]
     d2h = sum(c.nbytes for c in table.columns)
     check_q1_rows(table.to_pylist(), rows_e2e * world)
     unpin(torch, pinned)
     return {"value": rows_e2e * world * args.e2e_steps / (ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "rows_per_gpu": rows_e2e, "steps": args.e2e_steps,
             "ms_per_step": ms / args.e2e_steps, "host_batch_rows": args.e2e_batch_rows,
+            "h2d_GB_per_s_per_gpu": h2d / (ms / args.e2e_steps / 1e3) / 1e9,
             "note": "host Arrow RecordBatches in cudaHostRegister'ed memory pushed through b2_memory_exec_add_batch; "
                     "H2D of all 7 columns + result D2H inside the timed region"
                     + ("" if frac == 1.0 else f"; bounded to {frac:.2f} of the partition by host RAM")}
@@ -344,11 +546,11 @@ def run_e2e(args, ctx, dev_batches, timed, env):
 
 # ---------------------------------------------------------------------------------------------------------
 # the reference's CPU algorithm (oracle/: C++ restatement of the DataFusion plan; the Rust reference cannot be
-# built here — no cargo, DataFusion not vendored)
+# built here — no cargo, DataFusion not vendored), and pyarrow Acero as a second, production-grade CPU engine
 # ---------------------------------------------------------------------------------------------------------
-def cpu_q1(sf, seconds, threads, steps=1, warmup=0):
-    """-> (rows/s, sample description).  A bounded sample of the SF`sf` lineitem: the first `n` rows, n
-    calibrated so that one pass takes about `seconds` of wall clock on `threads` threads."""
+def cpu_q1(sf, seconds, threads, steps=1, warmup=0, with_acero=False):
+    """-> dict(rows/s of the oracle port, sample rows, s per pass, per-pass list, acero rows/s or None).  A bounded
+    sample of the SF`sf` lineitem: the first `n` rows, n calibrated so one pass takes about `seconds` on `threads` threads."""
     from oracle import oracle_py as O
     O.lib()
     total = O.tpch_num_rows("lineitem", sf)
@@ -363,189 +565,373 @@ def cpu_q1(sf, seconds, threads, steps=1, warmup=0):
     cols = O.gen_lineitem(sf, 0, n, threads=threads)
     for _ in range(warmup):
         O.q1(cols, n_partitions=threads)
-    t = time.perf_counter()
+    passes = []
     for _ in range(steps):
+        t = time.perf_counter()
         rows = O.q1(cols, n_partitions=threads)
-    dt = time.perf_counter() - t
+        passes.append(time.perf_counter() - t)
     check_q1_rows(rows, n)
-    return n * steps / dt, n, dt / steps
+    out = {"value": n * steps / sum(passes), "rows": n, "s_per_pass": sum(passes) / steps, "passes": passes, "acero": None}
+    if with_acero:
+        try:
+            out["acero"] = acero_q1(O, cols, rows, n)
+        except Exception as e:  # a sanity anchor, never fatal
+            out["acero"] = {"error": repr(e)}
+    return out
+
+
+def acero_q1(O, cols, oracle_rows, n):
+    """TPC-H Q1 with pyarrow's Acero engine (filter + computed columns + group_by().aggregate) on the same host sample;
+    -> rows/s (best of 3) after checking its counts against the oracle's."""
+    import pyarrow as pa
+    import pyarrow.compute as pc
+    t = pa.Table.from_batches([O.to_arrow(cols, tpch_q1_columns())])
+
+    def run():
+        f = t.filter(pc.less_equal(t["l_shipdate"], pa.scalar(O.DATE_1998_09_02, pa.int32()).cast(pa.date32())))
+        one = pa.scalar(1.0)
+        disc = pc.multiply(f["l_extendedprice"], pc.subtract(one, f["l_discount"]))
+        f = f.append_column("disc_price", disc).append_column("charge", pc.multiply(disc, pc.add(one, f["l_tax"])))
+        return f.group_by(["l_returnflag", "l_linestatus"]).aggregate(
+            [("l_quantity", "sum"), ("l_extendedprice", "sum"), ("disc_price", "sum"), ("charge", "sum"),
+             ("l_quantity", "mean"), ("l_extendedprice", "mean"), ("l_discount", "mean"), ("l_quantity", "count")])
+    best, res = None, None
+    for _ in range(3):
+        t0 = time.perf_counter()
+        res = run()
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    got = {(r["l_returnflag"], r["l_linestatus"]): r["l_quantity_count"] for r in res.to_pylist()}
+    want = {(r["l_returnflag"], r["l_linestatus"]): r["count_order"] for r in oracle_rows}
+    assert got == want, (got, want)
+    return {"value": n / best, "unit": UNIT, "cores": pa.cpu_count(), "kind": "pyarrow Acero " + pa.__version__,
+            "sample": f"the same {n} rows, best of 3 passes ({best:.2f} s); group counts equal the oracle's"}
+
+
+def tpch_q1_columns():
+    return ["l_quantity", "l_extendedprice", "l_discount", "l_tax", "l_returnflag", "l_linestatus", "l_shipdate"]
 
 
 def run_reference(args):
     rank, _, world = env_rank()
     if rank != 0:
         return None
+    from oracle import oracle_py as O
+    from ballista_b200 import cluster
+    O.lib()
     threads = os.cpu_count() or 1
     # each step = one pass over a bounded sample; K + W passes must end within minutes
     per_step = min(20.0, 150.0 / max(args.steps + args.warmup, 1))
-    v, n, sec = cpu_q1(args.sf, per_step, threads, steps=args.steps, warmup=args.warmup)
-    sample = f"first {n} rows of the SF{args.sf:g} synthetic lineitem per step, {threads} partitions (one thread each)"
+    r = cpu_q1(args.sf, per_step, threads, steps=args.steps, warmup=args.warmup)
+    v, n, sec = r["value"], r["rows"], r["s_per_pass"]
+    rows_sf = O.tpch_num_rows("lineitem", args.sf)
+    if args.scaling == "weak":
+        rows_gpu0, rows_total = rows_sf, rows_sf * world
+    else:
+        rows_gpu0, rows_total = cluster.partition_rows(rows_sf, world, 0, align=32)[1], rows_sf
+    sample = (f"first {n} rows of the SF{args.sf:g} synthetic lineitem per step, {threads} partitions (one thread each); "
+              "rows/s of the sample stands for the whole table (the plan is a streaming scan: cost is linear in rows)")
     return {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic (same generator, host copy)",
-            "config": {"workload": f"TPC-H Q1, SF{args.sf:g} lineitem, bounded sample of {n} rows per step"},
+            "config": workload_config(args.sf, args.scaling, world, rows_gpu0, rows_total),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0,
+            "gpu_launches": 0, "step_ms": {"median_ms": statistics.median(r["passes"]) * 1e3, "best_ms": min(r["passes"]) * 1e3},
             "note": "oracle/ C++ restatement of DataFusion@46161d2's Q1 plan (32,768-row batches, FilterExec copy, "
                     "no-CSE temporaries, byte-key hash aggregate); the Rust reference itself cannot be built here"}
 
 
-def run_other_configs(args, ctx, env):
-    """The other BASELINE.json configs, timed the same way (CUDA events on the library's stream, max over ranks)
-    and reported under "other_configs": Q6 and Q3 at SF10 on one GPU's partition, Q3 at SF100 (one GPU's own copy at N = 1), and at N > 1 the hash-repartition
-    shuffle of the Q3 lineitem side (l_orderkey, l_extendedprice, l_discount = 20 B/row) over NVLink."""
-    import torch.distributed as dist
-    from ballista_b200 import MemoryExec, RepartitionExec, _capi, cluster, col, tpch
-    rank, world, torch = env
-    stream = torch.cuda.ExternalStream(ctx.cuda_stream)
+# ---------------------------------------------------------------------------------------------------------
+# the other BASELINE.json configs: each timed the same way and each with its own parity verdict
+# ---------------------------------------------------------------------------------------------------------
+def oracle_q6_partition(ctx, O, table_sf, r0, r1, threads, chunk_rows, columns):
+    tot = [0.0, 0]
+
+    def one(cols):
+        rev, passing = O.q6(cols, n_partitions=threads)
+        tot[0] += rev or 0.0
+        tot[1] += passing
+    checked = oracle_scan_chunks(ctx, O, table_sf, r0, r1, columns, chunk_rows, one)
+    return tot, checked
+
+
+def q3_roofline(scan_bytes, stats, ms, peak):
+    """scan-only GB/s and scan + table GB/s (one 32-byte sector per build insert and per probe)"""
+    out = {"bound": "hbm", "unit": "GB/s", "peak": peak, "scan_bytes": int(scan_bytes),
+           "scan_only": scan_bytes / (ms / 1e3) / 1e9, "frac_scan_only": scan_bytes / (ms / 1e3) / 1e9 / peak,
+           "note": "whole-step figures (all kernels of the plan), not a single kernel's"}
+    if stats:
+        table_bytes = 32 * (stats["build1"] + stats["build2"] + stats["probe1"] + stats["probe2"])
+        out.update({"table_bytes": int(table_bytes), "scan_plus_table": (scan_bytes + table_bytes) / (ms / 1e3) / 1e9,
+                    "frac_scan_plus_table": (scan_bytes + table_bytes) / (ms / 1e3) / 1e9 / peak, "join_rows": stats})
+    return out
+
+
+def run_other_configs(args, env):
+    from ballista_b200 import MemoryExec, RepartitionExec, _capi, col, tpch
+    import numpy as np
+    ctx, rank, world, cluster, dist, torch = env.ctx, env.rank, env.world, env.cluster, env.dist, env.torch
     sf = args.other_sf
     peak = measured_peaks().get("hbm_gbs") or 6650.0
-
-    def timeit(fn, steps=10, warmup=3):
-        for _ in range(warmup):
-            fn()
-        if world > 1:
-            dist.barrier()
-        ctx.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        l0 = ctx.kernel_launches()
-        e0.record(stream)
-        for _ in range(steps):
-            r = fn()
-        e1.record(stream)
-        ctx.synchronize()
-        torch.cuda.synchronize()
-        return cluster.max_over_ranks(dist, torch, e0.elapsed_time(e1) / steps, world), (ctx.kernel_launches() - l0) / steps, r
-
+    O = None
+    if not args.no_parity:
+        from oracle import oracle_py as O
+        O.lib()
     out = {}
-    nrows = lambda t: _capi.lib().b2_tpch_num_rows(t.encode(), float(sf))
+    nrows = lambda t, s=None: _capi.lib().b2_tpch_num_rows(t.encode(), float(sf if s is None else s))
+
+    def timeit(fn, steps=10, warmup=3, profile=False):
+        t = time_steps(env, fn, steps, warmup, profile=profile)
+        return t["ms_total"] / steps, t["launches"] / steps, t["last"], t
+
     # ---- Q6 @ SF10: filter + global SUM over this rank's lineitem (28 B/row) ----
-    li6 = ctx.tpch("lineitem", sf * world, rank * nrows("lineitem"), (rank + 1) * nrows("lineitem"), columns=tpch.Q6_COLUMNS)
+    n6 = nrows("lineitem")
+    li6 = ctx.tpch("lineitem", sf * world, rank * n6, (rank + 1) * n6, columns=tpch.Q6_COLUMNS)
 
     def q6():
         scan = tpch.scan(ctx, [[li6]])
         part = tpch.q6_partial(scan)
         return tpch.run_two_stage(ctx, part, lambda s: tpch.q6_final(s, scan.schema()), merge="allgather"), part
-    ctx.set_profiling(True)
-    ctx.profile()
-    ms, launches, (tab, part) = timeit(q6)
-    k_ms, k_n = ctx.profile()  # CUDA events around every fused-scan launch since the reset (warm-up included)
-    ctx.set_profiling(False)
+    ms, launches, (tab, part), t = timeit(q6, steps=20, profile=True)
+    k_ms, k_n = t["kernel"]
     n = li6.num_rows
+    revenue = tab.to_pylist()[0]["revenue"]
     out["q6"] = {"workload": f"TPC-H Q6, SF{sf:g} lineitem per GPU ({n} rows x 28 B)", "ms_per_step": ms,
+                 "step_ms": step_stats(t["per_step"]),
                  "rows_per_s": n * world / (ms / 1e3), "GB_per_s_per_gpu": n * 28 / (ms / 1e3) / 1e9,
                  "frac_of_hbm_peak": n * 28 / (ms / 1e3) / 1e9 / peak, "launches_per_step": launches,
                  "scan_kernel": {"avg_launch_ms": k_ms / k_n if k_n else None,
                                  "GB_per_s": n * 28 / (k_ms / k_n / 1e3) / 1e9 if k_n else None,
                                  "frac_of_hbm_peak": n * 28 / (k_ms / k_n / 1e3) / 1e9 / peak if k_n else None,
                                  "note": "the fused scan kernel alone; the rest of the step is fixed per-step overhead"},
-                 "path": part.last_path(), "revenue": tab.to_pylist()[0]["revenue"]}
+                 "path": part.last_path(), "revenue": revenue}
+    if O:
+        tot, checked = oracle_q6_partition(ctx, O, sf * world, rank * n6, (rank + 1) * n6, env.host_threads,
+                                           args.parity_chunk_rows, tpch.Q6_COLUMNS)
+        tots = gather_objects(env, tot)
+        want, passing = sum(x[0] for x in tots), sum(x[1] for x in tots)
+        err = abs(revenue - want) / abs(want) if passing and revenue is not None else (0.0 if revenue is None and not passing else 1.0)
+        # counts: COUNT(*) under the same filter, bit-exact
+        from ballista_b200 import CoalesceBatchesExec, FilterExec, HashAggregateExec, count
+        cnt = HashAggregateExec("Partial", [], [count().alias("c")],
+                                CoalesceBatchesExec(FilterExec(tpch.q6_predicate(), tpch.scan(ctx, [[li6]]))))
+        mine = cnt.collect().to_pylist()[0]["c[count]"]
+        got_passing = sum(gather_objects(env, mine))
+        out["q6"]["parity"] = {"config": f"q6_sf{sf:g}_x{world}", "rows": int(n * world), "counts_equal": bool(got_passing == passing),
+                               "rows_passing": int(passing), "max_rel_err": err, "tolerance": 1e-9,
+                               "ok": bool(got_passing == passing and err <= 1e-9), "generator_rows_cross_checked": checked,
+                               "checker": "oracle/ Q6 over the same rows"}
     del li6
-    # ---- Q3 @ SF10 (and, on one GPU, the metric's SF100): customer |x| orders |x| lineitem + group-by over this
-    # rank's own copy of all three tables ----
-    def q3_local(qsf):
+
+    # ---- Q3 on one GPU's own copy of all three tables: SF10, and (N = 1) the metric's SF100 ----
+    def q3_local(qsf, name):
         cu = ctx.tpch("customer", qsf, columns=tpch.Q3_CUSTOMER_COLUMNS)
         od = ctx.tpch("orders", qsf, columns=tpch.Q3_ORDERS_COLUMNS)
         li = ctx.tpch("lineitem", qsf, columns=tpch.Q3_LINEITEM_COLUMNS)
 
-        def q3():
+        def plan():
             c, o, l = (tpch.scan(ctx, [[x]]) for x in (cu, od, li))
             partial = tpch.q3_partial(c, o, l)
             states = partial.collect_device(0)
-            final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
-            return sum(b.num_rows for b in final.collect_device(0))
-        ms, launches, groups = timeit(q3)
+            return tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
+
+        def q3():
+            return sum(b.num_rows for b in plan().collect_device(0))
+        ms, launches, groups, t = timeit(q3)
         rows = cu.num_rows + od.num_rows + li.num_rows
         scan_bytes = cu.num_bytes + od.num_bytes + li.num_bytes
-        return {"workload": f"TPC-H Q3, SF{qsf:g} on each GPU (customer {cu.num_rows} + orders {od.num_rows} + "
-                            f"lineitem {li.num_rows} rows; {scan_bytes / 1e9:.3f} GB of scanned columns)",
-                "ms_per_step": ms, "input_rows_per_s": rows * world / (ms / 1e3),
-                "scan_GB_per_s_per_gpu": scan_bytes / (ms / 1e3) / 1e9, "groups": groups, "launches_per_step": launches,
-                "note": "late materialisation reads only the key / predicate columns of non-matching rows, so "
-                        "scan GB/s is algorithmic bytes / time, not DRAM traffic"}
-    out["q3"] = q3_local(sf)
+        res = {"workload": f"TPC-H Q3, SF{qsf:g} on each GPU (customer {cu.num_rows} + orders {od.num_rows} + "
+                           f"lineitem {li.num_rows} rows; {scan_bytes / 1e9:.3f} GB of scanned columns)",
+               "ms_per_step": ms, "step_ms": step_stats(t["per_step"]), "input_rows_per_s": rows * world / (ms / 1e3),
+               "scan_GB_per_s_per_gpu": scan_bytes / (ms / 1e3) / 1e9, "groups": groups, "launches_per_step": launches,
+               "note": "late materialisation reads only the key / predicate columns of non-matching rows, so "
+                       "scan GB/s is algorithmic bytes / time, not DRAM traffic"}
+        arrs = q3_table_arrays(plan().collect())
+        stats = None
+        if O:
+            want = O.q3(qsf, threads=env.host_threads)
+            stats = want["stats"]
+            res["parity"] = parity_q3(name, arrs, want, rows)
+        res["roofline"] = q3_roofline(scan_bytes, stats, ms, peak)
+        res["digest"] = q3_checksum(arrs)
+        return res
+    out["q3"] = q3_local(sf, f"q3_sf{sf:g}")
     if world == 1 and args.q3_sf > sf:
-        out[f"q3_sf{args.q3_sf:g}"] = q3_local(args.q3_sf)
-    # ---- shuffle: RepartitionExec(Hash(l_orderkey), N) with the communicator attached (N > 1) ----
+        out[f"q3_sf{args.q3_sf:g}"] = q3_local(args.q3_sf, f"q3_sf{args.q3_sf:g}")
     if world > 1:
-        cols = ["l_orderkey", "l_extendedprice", "l_discount"]
-        n = nrows("lineitem")
-        part = ctx.tpch("lineitem", sf * world, rank * n, (rank + 1) * n, columns=cols)
-        path = [None]
-
-        def shuffle():
-            rep = RepartitionExec(tpch.scan(ctx, [[part]]), "Hash", world, [col("l_orderkey")])
-            got = rep.collect_device(rank)
-            path[0] = rep.last_path()
-            return sum(b.num_rows for b in got)
-        sent0 = ctx.comm_bytes_sent()
-        ctx.set_profiling(True)
-        ctx.profile()
-        ms, launches, _ = timeit(shuffle, steps=10, warmup=3)
-        pull_ms, pull_n = ctx.profile()  # CUDA events around the pull kernel of every exchange (warm-up included)
-        ctx.set_profiling(False)
-        pull_ms = cluster.max_over_ranks(dist, torch, pull_ms / max(pull_n, 1), world)
-        sent = (ctx.comm_bytes_sent() - sent0) / 13.0
-        out["shuffle"] = {"workload": f"hash repartition of lineitem SF{sf:g} per GPU ({n} rows x 20 B) into {world} "
-                                      "partitions, exchanged over NVLink", "path": path[0], "ms_per_step": ms,
-                          "rows_per_s": n * world / (ms / 1e3), "egress_bytes_per_gpu": sent,
-                          "egress_GB_per_s_per_gpu": sent / (ms / 1e3) / 1e9,
-                          "frac_of_nvlink_900GBps": sent / (ms / 1e3) / 1e9 / 900.0, "launches_per_step": launches,
-                          "exchange_step": {"kernel": "pull_kernel (every rank reads its slices from all peer arenas; "
-                                                      "also copies the local slice)", "ms": pull_ms,
-                                            "egress_GB_per_s_per_gpu": sent / (pull_ms / 1e3) / 1e9 if pull_ms else None,
-                                            "frac_of_nvlink_900GBps": sent / (pull_ms / 1e3) / 1e9 / 900.0 if pull_ms else None,
-                                            "frac_of_measured_peer_copy_770GBps": sent / (pull_ms / 1e3) / 1e9 / 770.0 if pull_ms else None},
-                          "note": "ms_per_step is the whole operator (split + metadata + move into the arena + exchange)"}
-        del part
-        # ---- Q3 with the shuffle: row-range partitions of the metric's SF100 database, both join inputs exchanged ----
-        dsf = args.q3_sf
-        def tpart(table, columns, align=1):
-            total = _capi.lib().b2_tpch_num_rows(table.encode(), float(dsf))
-            r0, r1 = cluster.partition_rows(total, world, rank, align=align)
-            return ctx.tpch(table, dsf, r0, r1, columns=columns)
-        dcu, dod = tpart("customer", tpch.Q3_CUSTOMER_COLUMNS), tpart("orders", tpch.Q3_ORDERS_COLUMNS)
-        dli = tpart("lineitem", tpch.Q3_LINEITEM_COLUMNS, align=32)
-        paths = [None]
-
-        def q3d():
-            scans = [tpch.scan(ctx, [[x]]) for x in (dcu, dod, dli)]
-            partial = tpch.q3_distributed_partial(*scans, world)
-            states = partial.collect_device(rank)
-            final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
-            return sum(b.num_rows for b in final.collect_device(0))
-        sent0 = ctx.comm_bytes_sent()
-        ms, launches, groups = timeit(q3d, steps=10, warmup=3)
-        sent = (ctx.comm_bytes_sent() - sent0) / 13.0
-        rows_all = sum(_capi.lib().b2_tpch_num_rows(t.encode(), float(dsf)) for t in ("customer", "orders", "lineitem"))
-        out["q3_distributed"] = {"workload": f"TPC-H Q3 over an SF{dsf:g} database in {world} row-range partitions, both join "
-                                             "inputs hash-repartitioned over NVLink (filters fused into the split)",
-                                 "ms_per_step": ms, "input_rows_per_s": rows_all / (ms / 1e3), "groups_rank0": groups,
-                                 "egress_bytes_per_gpu": sent, "launches_per_step": launches}
-        # ---- the same query and partitions with BROADCAST build sides (the reference's collect-left join across
-        # ranks): filtered customers and the first join's output are all-gathered, lineitem / orders never move,
-        # partial states are exchanged by group key ----
-        def q3b():
-            scans = [tpch.scan(ctx, [[x]]) for x in (dcu, dod, dli)]
-            partial, in_schema, p = tpch.q3_broadcast_stages(ctx, *scans, world)
-            states = partial.collect_device(p)
-            final = tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), in_schema)
-            return sum(b.num_rows for b in final.collect_device(0))
-        sent0 = ctx.comm_bytes_sent()
-        ms, launches, groups = timeit(q3b, steps=10, warmup=3)
-        sent = (ctx.comm_bytes_sent() - sent0) / 13.0
-        out["q3_broadcast"] = {"workload": f"TPC-H Q3 over an SF{dsf:g} database in {world} row-range partitions, build sides "
-                                           "all-gathered (collect-left), probe sides local, partial states exchanged by group key",
-                               "ms_per_step": ms, "input_rows_per_s": rows_all / (ms / 1e3), "groups_rank0": groups,
-                               "egress_bytes_per_gpu": sent, "launches_per_step": launches}
-        del dcu, dod, dli
+        out.update(run_multi_gpu_configs(args, env, O, timeit))
     return out
 
+
+def run_multi_gpu_configs(args, env, O, timeit):
+    """N > 1: the shuffle, Q3 over ONE SF100 database in N row-range partitions (both plan shapes) and the strong-scaled
+    Q1.  Every leg checks itself: digests reduced over the ranks against the single-GPU plan over the same database."""
+    from ballista_b200 import MemoryExec, RepartitionExec, _capi, col, tpch
+    import numpy as np
+    ctx, rank, world, cluster = env.ctx, env.rank, env.world, env.cluster
+    sf = args.other_sf
+    out = {}
+    nrows = lambda t, s: _capi.lib().b2_tpch_num_rows(t.encode(), float(s))
+
+    def row_digest(ok, price, disc):
+        with np.errstate(over="ignore"):
+            h = (ok.astype(np.uint64) * np.uint64(0x9E3779B97F4A7C15) ^ price.view(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F)
+                 ^ disc.view(np.uint64) * np.uint64(0x165667B19E3779F9))
+            return int(len(ok)), int(h.sum(dtype=np.uint64))
+
+    # ---- shuffle: RepartitionExec(Hash(l_orderkey), N) with the communicator attached ----
+    cols = ["l_orderkey", "l_extendedprice", "l_discount"]
+    n = nrows("lineitem", sf)
+    part = ctx.tpch("lineitem", sf * world, rank * n, (rank + 1) * n, columns=cols)
+    path = [None]
+
+    def exchange():
+        rep = RepartitionExec(tpch.scan(ctx, [[part]]), "Hash", world, [col("l_orderkey")])
+        got = rep.collect_device(rank)
+        path[0] = rep.last_path()
+        return got
+
+    def shuffle():
+        return sum(b.num_rows for b in exchange())
+    sent0 = ctx.comm_bytes_sent()
+    ms, launches, _, t = timeit(shuffle, steps=10, warmup=3, profile=True)
+    pull_ms, pull_n = t["kernel"]  # CUDA events around the exchange kernel of every timed exchange
+    pull_ms = cluster.max_over_ranks(env.dist, env.torch, pull_ms / max(pull_n, 1), world)
+    sent = (ctx.comm_bytes_sent() - sent0) / 13.0
+    out["shuffle"] = {"workload": f"hash repartition of lineitem SF{sf:g} per GPU ({n} rows x 20 B) into {world} "
+                                  "partitions, exchanged over NVLink", "path": path[0], "ms_per_step": ms,
+                      "step_ms": step_stats(t["per_step"]),
+                      "rows_per_s": n * world / (ms / 1e3), "egress_bytes_per_gpu": sent,
+                      "egress_GB_per_s_per_gpu": sent / (ms / 1e3) / 1e9,
+                      "frac_of_nvlink_900GBps": sent / (ms / 1e3) / 1e9 / 900.0, "launches_per_step": launches,
+                      "exchange_step": {"kernel": "the exchange kernel alone (CUDA events on the library's stream)", "ms": pull_ms,
+                                        "egress_GB_per_s_per_gpu": sent / (pull_ms / 1e3) / 1e9 if pull_ms else None,
+                                        "frac_of_nvlink_900GBps": sent / (pull_ms / 1e3) / 1e9 / 900.0 if pull_ms else None},
+                      "note": "ms_per_step is the whole operator (split + metadata + exchange)"}
+    # parity: nothing lost or invented (row count + 64-bit digest of whole rows, reduced over ranks) and every key
+    # on exactly one rank (distinct keys per rank add up to the table's orders: every order has a line)
+    src = part.to_arrow()
+    d_in = row_digest(*(src[c].to_numpy() for c in cols))
+    got = [b.to_arrow() for b in exchange()]
+    oks = np.concatenate([g["l_orderkey"].to_numpy() for g in got]) if got else np.zeros(0, np.int32)
+    d_out = row_digest(oks, np.concatenate([g["l_extendedprice"].to_numpy() for g in got]),
+                       np.concatenate([g["l_discount"].to_numpy() for g in got]))
+    mine = (d_in, d_out, int(len(np.unique(oks))))
+    alls = gather_objects(env, mine)
+    rows_in, rows_out = sum(a[0][0] for a in alls), sum(a[1][0] for a in alls)
+    dig_in = sum(a[0][1] for a in alls) % (1 << 64)
+    dig_out = sum(a[1][1] for a in alls) % (1 << 64)
+    distinct = sum(a[2] for a in alls)
+    orders = nrows("orders", sf * world)
+    out["shuffle"]["parity"] = {"config": f"shuffle_sf{sf:g}_x{world}", "rows": rows_in, "counts_equal": bool(rows_in == rows_out),
+                                "row_digest_equal": bool(dig_in == dig_out),
+                                "keys_colocated": bool(distinct == orders), "distinct_keys": distinct,
+                                "ok": bool(rows_in == rows_out and dig_in == dig_out and distinct == orders),
+                                "checker": "row count + order-independent 64-bit digest of whole rows before / after the "
+                                           "exchange, reduced over ranks; distinct keys per rank sum to the table's orders"}
+    del part, src, got, oks
+
+    # ---- Q3 over ONE SF100 database in N row-range partitions ----
+    dsf = args.q3_sf
+    def tpart(table, columns, align=1):
+        total = nrows(table, dsf)
+        r0, r1 = cluster.partition_rows(total, world, rank, align=align)
+        return ctx.tpch(table, dsf, r0, r1, columns=columns)
+    # reference digest: the single-GPU plan over the whole database (every rank computes it: no communication)
+    fc, fo, fl = (ctx.tpch(t, dsf, columns=c) for t, c in (("customer", tpch.Q3_CUSTOMER_COLUMNS),
+                                                           ("orders", tpch.Q3_ORDERS_COLUMNS),
+                                                           ("lineitem", tpch.Q3_LINEITEM_COLUMNS)))
+    scans = [tpch.scan(ctx, [[x]]) for x in (fc, fo, fl)]
+    partial = tpch.q3_partial(*scans)
+    states = partial.collect_device(0)
+    ref = q3_checksum(q3_table_arrays(tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]),
+                                                    partial.children()[0].schema()).collect()))
+    del fc, fo, fl, scans, partial, states
+    dcu, dod = tpart("customer", tpch.Q3_CUSTOMER_COLUMNS), tpart("orders", tpch.Q3_ORDERS_COLUMNS)
+    dli = tpart("lineitem", tpch.Q3_LINEITEM_COLUMNS, align=32)
+    rows_all = sum(nrows(t, dsf) for t in ("customer", "orders", "lineitem"))
+
+    def q3d_plan():
+        scans = [tpch.scan(ctx, [[x]]) for x in (dcu, dod, dli)]
+        partial = tpch.q3_distributed_partial(*scans, world)
+        states = partial.collect_device(rank)
+        return tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), partial.children()[0].schema())
+
+    def q3b_plan():
+        scans = [tpch.scan(ctx, [[x]]) for x in (dcu, dod, dli)]
+        partial, in_schema, p = tpch.q3_broadcast_stages(ctx, *scans, world)
+        states = partial.collect_device(p)
+        return tpch.q3_final(MemoryExec(ctx, partial.schema(), [states]), in_schema)
+
+    def digest_parity(name, plan):
+        d = q3_checksum(q3_table_arrays(plan().collect()))
+        alls = gather_objects(env, d)
+        cnt, dig = sum(a[0] for a in alls), sum(a[1] for a in alls) % (1 << 64)
+        rev = math_fsum([a[2] for a in alls])
+        err = abs(rev - ref[2]) / abs(ref[2]) if ref[2] else 0.0
+        return {"config": name, "input_rows": int(rows_all), "groups": cnt, "counts_equal": bool(cnt == ref[0]),
+                "keys_equal": bool(dig == ref[1]), "max_rel_err": err, "tolerance": 1e-9,
+                "ok": bool(cnt == ref[0] and dig == ref[1] and err <= 1e-9),
+                "checker": "group count, 64-bit digest of the group keys and total revenue, reduced over ranks, against the "
+                           "single-GPU plan over the same database (itself compared with oracle/ in the N = 1 run)"}
+    for name, plan, what in (("q3_distributed", q3d_plan, "both join inputs hash-repartitioned over NVLink (filters fused into the split)"),
+                             ("q3_broadcast", q3b_plan, "build sides all-gathered (collect-left), probe sides local, partial states exchanged by group key")):
+        sent0 = ctx.comm_bytes_sent()
+        ms, launches, groups, t = timeit(lambda: sum(b.num_rows for b in plan().collect_device(0)), steps=10, warmup=3)
+        sent = (ctx.comm_bytes_sent() - sent0) / 13.0
+        out[name] = {"workload": f"TPC-H Q3 over an SF{dsf:g} database in {world} row-range partitions, " + what,
+                     "ms_per_step": ms, "step_ms": step_stats(t["per_step"]), "input_rows_per_s": rows_all / (ms / 1e3),
+                     "groups_rank0": groups, "egress_bytes_per_gpu": sent, "launches_per_step": launches,
+                     "parity": digest_parity(f"{name}_sf{dsf:g}_x{world}", plan)}
+    del dcu, dod, dli
+
+    # ---- Q1 strong scaling: ONE SF100 lineitem in N row-range partitions (BASELINE config 3, literally) ----
+    total = nrows("lineitem", args.sf)
+    r0, r1 = cluster.partition_rows(total, world, rank, align=32)
+    li = ctx.tpch("lineitem", args.sf, r0, r1, columns=tpch.Q1_COLUMNS)
+
+    def q1s():
+        scan = tpch.scan(ctx, [[li]])
+        partial = tpch.q1_partial(scan)
+        return tpch.run_two_stage(ctx, partial, lambda s: tpch.q1_final(s, scan.schema()), merge="allgather")
+    ms, launches, tab, t = timeit(q1s, steps=20, warmup=3, profile=True)
+    k_ms, k_n = t["kernel"]
+    peak = measured_peaks().get("hbm_gbs") or 6650.0
+    out["q1_strong"] = {"workload": f"TPC-H Q1, one SF{args.sf:g} lineitem ({total} rows) in {world} row-range partitions",
+                        "ms_per_step": ms, "step_ms": step_stats(t["per_step"]), "rows_per_s": total / (ms / 1e3),
+                        "GB_per_s_per_gpu": (r1 - r0) * Q1_BYTES_PER_ROW / (ms / 1e3) / 1e9,
+                        "frac_of_hbm_peak_per_gpu": (r1 - r0) * Q1_BYTES_PER_ROW / (ms / 1e3) / 1e9 / peak,
+                        "scan_kernel_ms": k_ms / k_n if k_n else None, "launches_per_step": launches}
+    if O:
+        acc, checked = oracle_q1_partition(ctx, O, args.sf, r0, r1, env.host_threads, args.parity_chunk_rows, tpch.Q1_COLUMNS)
+        out["q1_strong"]["parity"] = parity_q1(f"q1_strong_sf{args.sf:g}_x{world}", tab.to_pylist(),
+                                               merge_q1_acc(gather_objects(env, acc)), total, checked)
+    del li
+    return out
+
+
+def math_fsum(xs):
+    import math
+    return math.fsum(xs)
 
 
 def emit(real_stdout, obj):
     os.write(real_stdout, (json.dumps(obj) + "\n").encode())
+
+
+def collect_parity(out):
+    """every parity verdict of the line -> (all ok, list of failing configs)"""
+    bad = []
+    def walk(o):
+        if isinstance(o, dict):
+            p = o.get("parity")
+            if isinstance(p, dict) and not p.get("ok", False):
+                bad.append(p.get("config"))
+            for v in o.values():
+                walk(v)
+    walk(out)
+    return not bad, bad
 
 
 def main():
@@ -559,24 +945,31 @@ def main():
         if out is not None:
             emit(real_stdout, out)
         return
-    ctx, out, dev_batches, timed, env = run_b200(args)
-    rank, world, torch = env
+    env = setup_env(args)
+    out = run_b200(args, env)
+    rank, world = env.rank, env.world
     if not args.no_e2e:
-        out["e2e"] = run_e2e(args, ctx, dev_batches, timed, env)
+        out["e2e"] = run_e2e(args, env)
+    env.q1 = None
     if not args.no_other:
-        out["other_configs"] = run_other_configs(args, ctx, env)
+        out["other_configs"] = run_other_configs(args, env)
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
-        v, n, sec = cpu_q1(args.sf, args.cpu_seconds, threads)
-        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                               "sample": f"first {n} rows of the SF{args.sf:g} lineitem, one pass of {sec:.2f} s on "
+        r = cpu_q1(args.sf, args.cpu_seconds, threads, with_acero=True)
+        out["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": threads, "kind": "port",
+                               "sample": f"first {r['rows']} rows of the SF{args.sf:g} lineitem, one pass of {r['s_per_pass']:.2f} s on "
                                          f"{threads} threads (oracle/: C++ restatement of the DataFusion plan)"}
+        out["cpu_baseline_b"] = r["acero"]
+    ok, bad = collect_parity(out)
+    out["parity_all_ok"] = ok
     if rank == 0:
         emit(real_stdout, out)
     if world > 1:
-        import torch.distributed as dist
-        dist.barrier()
-        dist.destroy_process_group()
+        env.dist.barrier()
+        env.dist.destroy_process_group()
+    if not ok:
+        sys.stderr.write(f"bench.py: PARITY FAILED for {bad}\n")
+        sys.exit(3)
 
 
 if __name__ == "__main__":

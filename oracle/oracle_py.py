@@ -74,7 +74,12 @@ class Utf8:
         return Utf8.from_list([vals[i] for i in idx])
 
     def equals_literal(self, s):
-        return np.array([v == s for v in self.to_list()], dtype=bool)
+        lit = np.frombuffer(s.encode(), dtype=np.uint8)
+        m = np.diff(self.offsets) == len(lit)
+        if len(lit) and m.any():
+            start = self.offsets[:-1][m].astype(np.int64)
+            m[m] = (self.chars[start[:, None] + np.arange(len(lit))] == lit).all(axis=1)
+        return m
 
 
 def _keycols(cols, keep):
@@ -272,3 +277,53 @@ def q6(cols, n_partitions=1, date_lo=DATE_1994_01_01, date_hi=DATE_1995_01_01, q
                           C.c_double(lo), C.c_double(hi), C.c_double(quantity_lt), n_partitions, C.byref(passing))
     # an ungrouped SUM over no rows is NULL, not 0.0 (the accumulator starts as Float64(None))
     return (float(rev) if passing.value else None), int(passing.value)
+
+
+# ---- TPC-H Q3 (rust/benchmarks/tpch/queries/q3.sql) as the reference's plan runs it: filters below the joins,
+#      (customer |x| orders) |x| lineitem with build = left, group by (l_orderkey, o_orderdate, o_shippriority) ----
+def q3_range(sf, o_lo, o_hi, building_custkeys, cutoff=DATE_1995_03_15):
+    """Q3 over the orders rows [o_lo, o_hi) (multiples of 8) and their lineitem rows [4 o_lo, 4 o_hi); every order's
+    lines lie inside its range, so ranges yield disjoint groups.
+    -> (l_orderkey, o_orderdate, o_shippriority, revenue, join statistics)"""
+    o = gen_orders(sf, o_lo, o_hi - o_lo)
+    l = gen_lineitem(sf, 4 * o_lo, 4 * (o_hi - o_lo))
+    om = o["o_orderdate"] < cutoff
+    of = {k: v[om] for k, v in o.items()}
+    _, ri = hash_join([building_custkeys], [of["o_custkey"]])
+    j1 = {k: v[ri] for k, v in of.items()}
+    lm = l["l_shipdate"] > cutoff
+    lf = {k: l[k][lm] for k in ("l_orderkey", "l_extendedprice", "l_discount")}
+    # build rows / probes of the two joins (SURVEY 8d counts one 32-byte sector of table traffic for each)
+    stats = {"probe1": int(om.sum()), "build2": int(len(ri)), "probe2": int(lm.sum())}
+    empty = (np.zeros(0, np.int32),) * 3 + (np.zeros(0), stats)
+    if len(ri) == 0 or not lm.any():
+        return empty
+    li2, ri2 = hash_join([j1["o_orderkey"]], [lf["l_orderkey"]])
+    stats["joined"] = int(len(ri2))
+    if len(ri2) == 0:
+        return empty
+    rev = lf["l_extendedprice"][ri2] * (1.0 - lf["l_discount"][ri2])
+    keys = [lf["l_orderkey"][ri2], j1["o_orderdate"][li2], j1["o_shippriority"][li2]]
+    rep, sums, _ = hash_aggregate(keys, [rev])
+    return keys[0][rep], keys[1][rep], keys[2][rep], sums[:, 0].copy(), stats
+
+
+def q3(sf, segment="BUILDING", cutoff=DATE_1995_03_15, threads=1, range_orders=1 << 21):
+    """The whole query, one task per orders range on `threads` host threads (the C++ primitives release the GIL).
+    -> dict of arrays sorted by l_orderkey."""
+    from concurrent.futures import ThreadPoolExecutor
+    nc, no = tpch_num_rows("customer", sf), tpch_num_rows("orders", sf)
+    c = gen_customer(sf, 0, nc)
+    ck = np.ascontiguousarray(c["c_custkey"][c["c_mktsegment"].equals_literal(segment)])
+    step = max(8, min(range_orders, -(-no // max(threads, 1))) // 8 * 8)
+    ranges = [(a, min(a + step, no)) for a in range(0, no, step)]
+    with ThreadPoolExecutor(max_workers=max(threads, 1)) as ex:
+        parts = list(ex.map(lambda r: q3_range(sf, r[0], r[1], ck, cutoff), ranges))
+    out = [np.concatenate([p[k] for p in parts]) for k in range(4)]
+    order = np.argsort(out[0], kind="stable")
+    stats = {"build1": int(len(ck))}
+    for p in parts:
+        for k, v in p[4].items():
+            stats[k] = stats.get(k, 0) + v
+    return {"l_orderkey": out[0][order], "o_orderdate": out[1][order], "o_shippriority": out[2][order],
+            "revenue": out[3][order], "stats": stats}

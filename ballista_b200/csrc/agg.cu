@@ -39,7 +39,7 @@ KeyLayout make_key_layout(const std::vector<int>& dtypes) {
 // ------------------------------------------------------------------------------------------------------
 // group table
 // ------------------------------------------------------------------------------------------------------
-std::shared_ptr<GroupTable> make_group_table(Ctx* ctx, u64 cap, int na, int nc) {
+std::shared_ptr<GroupTable> make_group_table(Ctx* ctx, u64 cap, int na, int nc, bool init) {
   if (cap > (1ull << 32)) fail(B2_ERR_NOT_IMPLEMENTED, "group table beyond 2^32 slots");
   auto t = std::make_shared<GroupTable>();
   t->ctx = ctx;
@@ -51,7 +51,7 @@ std::shared_ptr<GroupTable> make_group_table(Ctx* ctx, u64 cap, int na, int nc) 
   t->cnt = dev_alloc(ctx, cap * sizeof(u64) * (size_t)(nc ? nc : 1));
   t->n_groups = dev_alloc(ctx, 16);
   t->slot_list = dev_alloc(ctx, cap * 4 + 16);  // written before it is read: no initialisation
-  reset_group_table(*t);
+  if (init) reset_group_table(*t);
   return t;
 }
 void reset_group_table(GroupTable& t) {
@@ -87,6 +87,7 @@ static u64 next_pow2(u64 x) {
   return p;
 }
 constexpr u64 DELTA_CAP = 65536;
+constexpr u64 SPEC_CAP = 4096;  // table of the speculative single-batch path (its emit bound is SPEC_BOUND groups)
 constexpr int64_t GLOBAL_CHUNK_ROWS = 32ll << 20;  // multiple of TILE_ROWS
 
 AggRunner::AggRunner(Ctx* c, int na_, int nc_, bool keyed_) : ctx(c), na(na_), nc(nc_), keyed(keyed_) {
@@ -129,7 +130,7 @@ void AggRunner::ensure_main(int64_t extra) {
 
 bool AggRunner::consume_unchecked(const AggLaunch& l, int64_t n) {
   if (force_global || main || n <= 0) return false;
-  main = make_group_table(ctx, keyed ? DELTA_CAP : 16, na, nc);
+  main = make_group_table(ctx, keyed ? SPEC_CAP : 16, na, nc);
   // the status word was zeroed at construction / reset(); the key-packing kernel of the unfused path may already
   // have raised AGG_KEY_TOO_WIDE in it, which the emit's readback reports like a status of the scan itself
   l.small(n, main->ref(), status->as<int>());
@@ -398,6 +399,111 @@ bool EmitPlan::run(int64_t exact_ng, const int* status_dev, int64_t* ng_out, int
   }
   *ng_out = ng;
   return true;
+}
+
+BufPtr EmitPlan::run_lazy(const int* status_dev) {
+  if (cols.size() > EMIT_MAX_COLS) fail(B2_ERR_NOT_IMPLEMENTED, "aggregate with more than 24 output columns");
+  EmitArgs args;
+  memset(&args, 0, sizeof args);
+  args.n = (int)cols.size();
+  for (int k = 0; k < args.n; ++k) {
+    const EmitDesc& d = descs[k];
+    Column& c = cols[k];
+    args.c[k] = EmitCol{d.kind, d.byte_off, d.src, d.src2, d.vsrc, c.data->ptr, c.chars ? c.chars->as<uint8_t>() : nullptr,
+                        c.valid ? c.valid->as<uint8_t>() : nullptr};
+    c.length = bound;
+  }
+  BufPtr hdr = dev_alloc_zero(ctx, (size_t)(2 + EMIT_MAX_COLS) * 8);
+  dim3 grid((unsigned)grid_for(ctx, 8, bound, 256), (unsigned)args.n);
+  emit_all_kernel<<<grid, 256, 0, ctx->stream>>>(args, table.keys->as<Key128>(), table.slot_list->as<uint32_t>(), bound,
+                                                 table.n_groups->as<int>(), status_dev, hdr->as<int64_t>());
+  B2_LAUNCHED(ctx);
+  return hdr;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// small Final aggregate (see agg.h)
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) final_tiny_kernel(TinyArgs a, TableRef t, int na_tbl, int nc_tbl, int* status) {
+  if (a.init) {  // the table arrives uninitialised
+    for (u64 i = threadIdx.x; i < t.cap; i += blockDim.x) {
+      t.keys[i] = Key128{KEY_EMPTY, KEY_EMPTY};
+      for (int x = 0; x < na_tbl; ++x) t.acc[(u64)x * t.cap + i] = 0.0;
+      for (int x = 0; x < nc_tbl; ++x) t.cnt[(u64)x * t.cap + i] = 0;
+    }
+    if (threadIdx.x == 0) *t.n_groups = 0;
+    __syncthreads();
+  }
+  __shared__ int64_t s_rows[TINY_BATCHES];
+  __shared__ int s_bad;
+  if (threadIdx.x == 0) {
+    int bad = 0;
+    int64_t total = 0;
+    for (int b = 0; b < a.nb; ++b) {
+      const TinyBatch& tb = a.b[b];
+      int64_t n = tb.rows;
+      if (tb.hdr) {
+        n = tb.hdr[1];
+        if (tb.hdr[0] != 0 || n < 0 || n > tb.bound || (tb.redo_if_empty && n == 0)) bad = AGG_INPUT_FAILED;
+      }
+      s_rows[b] = n;
+      total += n;
+    }
+    if (!bad && total > TINY_MAX_ROWS) bad = AGG_TOO_BIG;
+    s_bad = bad;
+    if (bad) atomicExch(status, bad);
+  }
+  __syncthreads();
+  if (s_bad) return;
+  int err = 0;
+  for (int b = 0; b < a.nb; ++b) {
+    const TinyBatch& tb = a.b[b];
+    const int64_t n = s_rows[b];
+    for (int64_t r = threadIdx.x; r < n; r += blockDim.x) {
+      u128 key = 0;
+      for (int p = 0; p < a.nkeys; ++p) {
+        const TinyCol& kc = tb.key[p];
+        if (kc.valid && !kc.valid[r]) {
+          err = AGG_NULL_KEY;
+          continue;
+        }
+        if (a.part_dtype[p] == B2_UTF8) {
+          StrVal sv = load_str((const int32_t*)kc.data, kc.chars, r);
+          if (sv.len > a.part_bytes[p] - 1) err = AGG_KEY_TOO_WIDE;
+          u128 m = (((u128)1 << (8 * (a.part_bytes[p] - 1))) - 1);
+          key |= ((u128)(uint8_t)sv.len | ((sv.bytes & m) << 8)) << (8 * a.part_off[p]);
+        } else if (a.part_bytes[p] == 8) {
+          key |= (u128)(u64)((const int64_t*)kc.data)[r] << (8 * a.part_off[p]);
+        } else {
+          key |= (u128)(uint32_t)((const int32_t*)kc.data)[r] << (8 * a.part_off[p]);
+        }
+      }
+      u64 slot = table_upsert(t, Key128{(u64)key, (u64)(key >> 64)});
+      if (slot == ~0ull) {
+        err = AGG_TABLE_FULL;
+        continue;
+      }
+      for (int x = 0; x < a.na; ++x) {
+        const TinyCol& vc = tb.val[x];
+        if (!vc.data) continue;
+        const bool ok = !vc.valid || vc.valid[r];
+        if (ok) red_add_f64(&t.acc[(u64)x * t.cap + slot], ((const double*)vc.data)[r]);
+        if (a.vslot[x] >= 0 && ok) red_add_u64(&t.cnt[(u64)a.vslot[x] * t.cap + slot], 1ull);
+      }
+      for (int x = 0; x < a.nc; ++x) {
+        const TinyCol& cc = tb.cnt[x];
+        if (!cc.data) continue;
+        const bool ok = !cc.valid || cc.valid[r];
+        if (ok) red_add_u64(&t.cnt[(u64)x * t.cap + slot], ((const u64*)cc.data)[r]);
+        if (a.cvslot[x] >= 0 && ok) red_add_u64(&t.cnt[(u64)a.cvslot[x] * t.cap + slot], 1ull);
+      }
+    }
+  }
+  if (err) atomicExch(status, err);
+}
+void final_tiny_launch(Ctx* ctx, const TinyArgs& a, const GroupTable& t, int* status) {
+  final_tiny_kernel<<<1, 1024, 0, ctx->stream>>>(a, t.ref(), t.na ? t.na : 1, t.nc ? t.nc : 1, status);
+  B2_LAUNCHED(ctx);
 }
 
 }  // namespace b2

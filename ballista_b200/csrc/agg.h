@@ -38,7 +38,7 @@ struct GroupTable {
                     slot_list->as<uint32_t>()};
   }
 };
-std::shared_ptr<GroupTable> make_group_table(Ctx* ctx, u64 cap, int na, int nc);
+std::shared_ptr<GroupTable> make_group_table(Ctx* ctx, u64 cap, int na, int nc, bool init = true);
 void reset_group_table(GroupTable& t);
 
 // type-erased launchers of the two aggregate kernels for one bound source
@@ -132,8 +132,38 @@ struct EmitPlan {
   // and `status_dev` are read back with the Utf8 totals; returns false (and *status_out) when the speculation
   // failed: bad status or more groups than `bound`.  On success *ng_out rows are valid in every column.
   bool run(int64_t exact_ng, const int* status_dev, int64_t* ng_out, int* status_out);
+  // The same launch with nothing read back: columns keep `bound` rows, the returned header (int64 in HBM: status,
+  // group count, character totals by column) is what Batch::lazy carries.
+  BufPtr run_lazy(const int* status_dev);
  private:
   void push(int kind, int byte_off, const void* src, const void* src2, const u64* vsrc, Column col);
 };
+
+// ---- small Final aggregate: partial states of a few rows (one batch per partition or per rank) merged by ONE
+// single-CTA kernel that packs keys, claims groups and accumulates straight from the state columns, reading each
+// batch's row count from its device-side header when the batch is lazy.  (agg.cu) ----
+constexpr int TINY_BATCHES = 4;        // per launch
+constexpr int64_t TINY_MAX_ROWS = 8192;  // all batches together
+constexpr u64 TINY_CAP = 2048;         // slots of the group table (the emit bound is 1024 groups)
+constexpr int64_t SPEC_BOUND = 1024;   // groups a speculative (lazy) aggregate result may hold
+struct TinyCol {
+  const void* data;
+  const uint8_t* valid;
+  const uint8_t* chars;
+};
+struct TinyBatch {
+  const int64_t* hdr;  // lazy input: [0] status, [1] rows; null = `rows` is exact
+  int64_t rows, bound;
+  int redo_if_empty;
+  TinyCol key[8], val[8], cnt[12];
+};
+struct TinyArgs {
+  int nb, nkeys, na, nc, init;
+  int part_dtype[8], part_off[8], part_bytes[8];
+  int vslot[8];    // count slot that receives the number of non-NULL rows of value a, or -1
+  int cvslot[12];  // likewise for an integer-sum column
+  TinyBatch b[TINY_BATCHES];
+};
+void final_tiny_launch(Ctx* ctx, const TinyArgs& a, const GroupTable& t, int* status);
 
 }  // namespace b2

@@ -343,7 +343,7 @@ int b2_stream_next_device(b2_stream* s, b2_batch** out, int* eos) {
   return guard([&] {
     REQUIRE(s && s->s && out && eos, "null argument");
     double t0 = wall_now();
-    BatchPtr b = s->s->next();
+    BatchPtr b = s->s->next_lazy();  // the handle may stand for a batch whose row count is still on the device
     if (b && b->ctx && b->ctx->trace) b->ctx->trace_add("b2_stream_next_device (total host time)", wall_now() - t0);
     if (!b) {
       *eos = 1;
@@ -359,7 +359,7 @@ int b2_stream_next_device(b2_stream* s, b2_batch** out, int* eos) {
 int b2_stream_next(b2_stream* s, struct ArrowArray* out, int* eos) {
   return guard([&] {
     REQUIRE(s && s->s && out && eos, "null argument");
-    BatchPtr b = s->s->next();
+    BatchPtr b = s->s->next_lazy();  // exported with its header: one synchronisation learns the count and copies
     if (!b) {
       *eos = 1;
       return;
@@ -396,8 +396,17 @@ int b2_batch_schema(b2_batch* b, struct ArrowSchema* out) {
     schema_to_arrow(b->b->schema, out);
   });
 }
-int64_t b2_batch_num_rows(b2_batch* b) { return (b && b->b) ? b->b->num_rows : -1; }
-int64_t b2_batch_num_bytes(b2_batch* b) { return (b && b->b) ? b->b->num_bytes() : -1; }
+static bool resolve_handle(b2_batch* b) {
+  if (!b || !b->b) return false;
+  if (b->b->lazy && guard([&] {
+        b->b->ctx->activate();
+        resolve_batch(*b->b);
+      }) != B2_OK)
+    return false;
+  return true;
+}
+int64_t b2_batch_num_rows(b2_batch* b) { return resolve_handle(b) ? b->b->num_rows : -1; }
+int64_t b2_batch_num_bytes(b2_batch* b) { return resolve_handle(b) ? b->b->num_bytes() : -1; }
 void b2_batch_destroy(b2_batch* b) { delete b; }
 
 // ---- workload ----

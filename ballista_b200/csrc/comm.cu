@@ -90,25 +90,44 @@ struct SmallCol {
 };
 struct SmallArgs {
   int ncol, nr;
+  const int64_t* lazy_hdr;  // pack: the batch's device-side header (status, rows, character totals), or null
+  int64_t lazy_bound;
+  int lazy_redo_if_empty;
   int64_t stride, rows, header_bytes;
   SmallCol c[SMALL_MAX_COLS];
   int64_t chars[SMALL_MAX_COLS];                         // pack: my character counts
   int64_t row_prefix[SMALL_MAX_RANKS + 1];               // unpack
   int64_t chr_prefix[SMALL_MAX_STR][SMALL_MAX_RANKS + 1];
 };
+// header word 0: rows, or -1 = does not fit the slot (everybody takes the general protocol), or -2 = this rank's lazy
+// batch has to be redone first (everybody retries)
 __global__ void pack_small_kernel(SmallArgs a, char* slot, int fits) {
   const SmallCol& c = a.c[blockIdx.y];
+  int64_t rows = a.rows;
+  int64_t my_chars = a.chars[blockIdx.y];
+  int64_t verdict = fits ? a.rows : -1;
+  if (a.lazy_hdr) {  // row count and character totals live on the device
+    rows = a.lazy_hdr[1];
+    my_chars = a.lazy_hdr[2 + blockIdx.y];
+    if (a.lazy_hdr[0] != 0 || rows < 0 || rows > a.lazy_bound || (a.lazy_redo_if_empty && rows == 0)) {
+      verdict = -2;
+    } else {
+      verdict = rows <= SMALL_ROWS ? rows : -1;
+      for (int k = 0; k < a.ncol; ++k)
+        if (a.c[k].utf8 >= 0 && a.lazy_hdr[2 + k] > SMALL_CHARS) verdict = -1;
+    }
+  }
   if (blockIdx.y == 0 && threadIdx.x == 0) {
     int64_t* h = reinterpret_cast<int64_t*>(slot);
-    h[0] = fits ? a.rows : -1;
+    h[0] = verdict;
     for (int k = 0; k < a.ncol; ++k) {
-      h[1 + k] = a.chars[k];
+      h[1 + k] = a.lazy_hdr ? (a.c[k].utf8 >= 0 ? a.lazy_hdr[2 + k] : 0) : a.chars[k];
       h[1 + a.ncol + k] = a.c[k].valid != nullptr;  // this rank's column may hold NULLs
     }
   }
-  if (!fits) return;
+  if (verdict < 0) return;
   char* base = slot + c.val_off;
-  for (int64_t i = threadIdx.x; i < a.rows; i += blockDim.x) {
+  for (int64_t i = threadIdx.x; i < rows; i += blockDim.x) {
     slot[c.valid_off + i] = c.valid ? (char)c.valid[i] : (char)1;
     if (c.utf8 >= 0) {
       const int32_t* off = static_cast<const int32_t*>(c.src);
@@ -122,7 +141,7 @@ __global__ void pack_small_kernel(SmallArgs a, char* slot, int fits) {
     }
   }
   if (c.utf8 >= 0)
-    for (int64_t k = threadIdx.x; k < a.chars[blockIdx.y]; k += blockDim.x) slot[c.chr_off + k] = (char)c.chars[k];
+    for (int64_t k = threadIdx.x; k < my_chars; k += blockDim.x) slot[c.chr_off + k] = (char)c.chars[k];
 }
 __global__ void unpack_small_kernel(SmallArgs a, const char* recv) {
   const SmallCol& c = a.c[blockIdx.y];
@@ -159,8 +178,10 @@ __global__ void unpack_small_kernel(SmallArgs a, const char* recv) {
 
 static BatchPtr allgather_general(Ctx* ctx, const Batch& local);
 
-// Returns nullptr when the schema is outside the small protocol or some rank's batch did not fit its slot.
-static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
+// Returns nullptr when the schema is outside the small protocol or some rank's batch did not fit its slot; *retry is
+// set when some rank's lazy batch must be redone first (then every rank resolves and calls again).
+static BatchPtr allgather_small(Ctx* ctx, const Batch& local, bool* retry) {
+  *retry = false;
   const int nr = ctx->nranks;
   const size_t ncol = local.cols.size();
   if (ncol > SMALL_MAX_COLS || nr > SMALL_MAX_RANKS || ncol == 0) return nullptr;
@@ -168,12 +189,17 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
   memset(&a, 0, sizeof a);
   a.ncol = (int)ncol;
   a.nr = nr;
-  a.rows = local.num_rows;
+  a.rows = local.lazy ? 0 : local.num_rows;
+  if (local.lazy) {
+    a.lazy_hdr = local.lazy->hdr->as<int64_t>();
+    a.lazy_bound = local.lazy->bound;
+    a.lazy_redo_if_empty = local.lazy->redo_if_empty;
+  }
   const size_t hdr_words = 1 + 2 * ncol;  // rows, character count per column, may-hold-NULLs flag per column
   a.header_bytes = (int64_t)align16(hdr_words * 8);
   int64_t off = a.header_bytes;
   int n_str = 0;
-  bool fits = local.num_rows <= SMALL_ROWS;
+  bool fits = local.lazy || local.num_rows <= SMALL_ROWS;
   for (size_t c = 0; c < ncol; ++c) {
     const Column& col = local.cols[c];
     if (!col.data) return nullptr;
@@ -192,8 +218,8 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
       sc.chars = col.chars ? col.chars->as<uint8_t>() : nullptr;
       sc.chr_off = off;
       off += SMALL_CHARS;
-      a.chars[c] = col.chars_len;
-      fits = fits && col.chars_len <= SMALL_CHARS;
+      a.chars[c] = local.lazy ? 0 : col.chars_len;
+      fits = fits && (local.lazy || col.chars_len <= SMALL_CHARS);
     }
   }
   a.stride = off;
@@ -212,8 +238,13 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
     B2_CUDA(cudaStreamSynchronize(ctx->stream));
     if (ctx->trace) ctx->trace_add("comm.cu:allgather_small headers", wall_now() - t0);
   }
-  for (int r = 0; r < nr; ++r)
-    if (heads[(size_t)r * hdr_words] < 0) return nullptr;  // somebody did not fit: general protocol (all ranks agree)
+  bool general = false;
+  for (int r = 0; r < nr; ++r) {
+    if (heads[(size_t)r * hdr_words] == -1) general = true;  // somebody did not fit: general protocol (all ranks agree)
+    if (heads[(size_t)r * hdr_words] == -2) *retry = true;   // somebody has to redo a speculative batch first
+  }
+  if (general) *retry = false;
+  if (general || *retry) return nullptr;
   std::vector<char> any_null(ncol, 0);
   for (int r = 0; r < nr; ++r) {
     a.row_prefix[r + 1] = a.row_prefix[r] + heads[(size_t)r * hdr_words];
@@ -255,9 +286,14 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local) {
   return out;
 }
 
-BatchPtr comm_allgather_batch(Ctx* ctx, const Batch& local) {
+BatchPtr comm_allgather_batch(Ctx* ctx, Batch& local) {
   if (!ctx->comm) fail(B2_ERR_INVALID_ARG, "no communicator (call b2_comm_init)");
-  if (BatchPtr b = allgather_small(ctx, local)) return b;  // carries validity
+  bool retry = false;
+  // a lazy batch is packed from its device-side header: the Partial -> Final hop adds no synchronisation of its own
+  if (BatchPtr b = allgather_small(ctx, local, &retry)) return b;  // carries validity
+  if (local.lazy) resolve_batch(local);
+  if (retry)
+    if (BatchPtr b = allgather_small(ctx, local, &retry)) return b;
   require_no_nulls(local, "all-gather of a large batch");
   return allgather_general(ctx, local);
 }

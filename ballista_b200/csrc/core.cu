@@ -1,4 +1,5 @@
 // core.cu — context, HBM allocation, Arrow C Data Interface import/export.
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 
@@ -75,6 +76,30 @@ BufPtr dev_alloc_zero(Ctx* ctx, size_t bytes) {
   auto b = dev_alloc(ctx, bytes);
   if (bytes) B2_CUDA(cudaMemsetAsync(b->ptr, 0, bytes, ctx->stream));
   return b;
+}
+
+void resolve_batch(Batch& b) {
+  auto lz = b.lazy;
+  if (!lz) return;
+  int64_t h[2 + 24] = {0};
+  size_t words = 2 + std::min<size_t>(b.cols.size(), 24);
+  B2_READBACK(b.ctx, h, lz->hdr->ptr, words * 8);
+  b.lazy = nullptr;
+  const bool ok = h[0] == 0 && h[1] >= 0 && h[1] <= lz->bound && !(lz->redo_if_empty && h[1] == 0);
+  if (ok) {
+    b.num_rows = h[1];
+    for (size_t c = 0; c < b.cols.size(); ++c) {
+      b.cols[c].length = h[1];
+      if (b.cols[c].dtype == B2_UTF8) b.cols[c].chars_len = h[2 + c];
+    }
+    return;
+  }
+  if (!lz->redo) fail(B2_ERR_EXECUTION, "internal: a speculative aggregate failed and cannot be redone");
+  BatchPtr r = lz->redo();
+  if (r->lazy) resolve_batch(*r);
+  b.cols = r->cols;
+  b.num_rows = r->num_rows;
+  b.unique_key_cols = r->unique_key_cols;
 }
 
 const char* dtype_name(int dt) {
@@ -314,8 +339,12 @@ struct D2HStager {
   }
 };
 
+// A lazy batch (Batch::lazy) is exported without resolving it first: the header travels with the columns (copied at
+// their allocated bound; aggregate results are a few rows), so the export's one synchronisation is also the one that
+// learns the row count.  If the header then says the speculation failed, the batch is redone and exported again.
 void batch_to_arrow(const Batch& b, ArrowArray* out) {
   Ctx* ctx = b.ctx;
+  const std::shared_ptr<LazyRows> lz = b.lazy;
   auto* top = new ArrayPriv;
   top->child_store.resize(b.cols.size());
   for (auto& c : top->child_store) {
@@ -331,44 +360,51 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
   out->children = top->child_ptrs.data();
   out->release = release_array;
   out->private_data = top;
+  int64_t hdr[2 + 24] = {0};
+  bool redo = false;
   try {
+    if (lz && b.cols.size() > 24) fail(B2_ERR_EXECUTION, "internal: lazy batch with more than 24 columns");
     std::vector<std::pair<size_t, std::vector<uint8_t>>> bools;  // bit-pack after the sync
     bools.reserve(b.cols.size());  // element addresses are handed to the stager
     D2HStager stage(ctx);
     std::vector<BufPtr> keep;  // packed bitmaps / null counters live until the flush
     std::vector<int64_t> null_counts(b.cols.size(), 0);
+    if (lz) stage.add(hdr, lz->hdr->ptr, (2 + b.cols.size()) * 8);
     for (size_t ci = 0; ci < b.cols.size(); ++ci) {
       const Column& col = b.cols[ci];
       if (!col.data) fail(B2_ERR_EXECUTION, "internal: column '" + b.schema.fields[ci].name +
                                                 "' was pruned upstream but is being exported");
+      const int64_t len = lz ? lz->bound : col.length;  // rows copied; the exported length is set after the sync
       auto* p = new ArrayPriv;
       ArrowArray* a = &top->child_store[ci];
-      a->length = col.length;
+      a->length = len;
       a->release = release_array;
       a->private_data = p;
       if (col.dtype == B2_UTF8) {
-        void* ho = host_buf(p, (size_t)(col.length + 1) * 4);
-        void* hd = host_buf(p, (size_t)col.chars_len);
-        stage.add(ho, col.data->ptr, (size_t)(col.length + 1) * 4);
-        if (col.chars_len) stage.add(hd, col.chars->ptr, (size_t)col.chars_len);
+        const size_t nchars = lz ? (col.chars ? col.chars->bytes : 0) : (size_t)col.chars_len;
+        void* ho = host_buf(p, (size_t)(len + 1) * 4);
+        void* hd = host_buf(p, nchars);
+        stage.add(ho, col.data->ptr, (size_t)(len + 1) * 4);
+        if (nchars) stage.add(hd, col.chars->ptr, nchars);
         p->buffers = {nullptr, ho, hd};
       } else if (col.dtype == B2_BOOL) {
-        bools.emplace_back(ci, std::vector<uint8_t>((size_t)col.length));
-        if (col.length) stage.add(bools.back().second.data(), col.data->ptr, (size_t)col.length);
-        void* hb = host_buf(p, (size_t)(col.length + 7) / 8);
-        memset(hb, 0, (size_t)(col.length + 7) / 8);
+        bools.emplace_back(ci, std::vector<uint8_t>((size_t)len));
+        if (len) stage.add(bools.back().second.data(), col.data->ptr, (size_t)len);
+        void* hb = host_buf(p, (size_t)(len + 7) / 8);
+        memset(hb, 0, (size_t)(len + 7) / 8);
         p->buffers = {nullptr, hb};
       } else {
-        size_t nb = (size_t)col.length * dtype_width(col.dtype);
+        size_t nb = (size_t)len * dtype_width(col.dtype);
         void* hv = host_buf(p, nb);
         if (nb) stage.add(hv, col.data->ptr, nb);
         p->buffers = {nullptr, hv};
       }
-      if (col.valid && col.length) {
+      if (col.valid && len) {
         auto counter = dev_alloc(ctx, 16);
-        auto bits = valid_to_bitmap(ctx, col.valid->as<uint8_t>(), col.length, counter->as<int64_t>());
-        void* hb = host_buf(p, (size_t)((col.length + 7) >> 3));
-        stage.add(hb, bits->ptr, (size_t)((col.length + 7) >> 3));
+        auto bits = valid_to_bitmap(ctx, col.valid->as<uint8_t>(), len, counter->as<int64_t>(),
+                                    lz ? lz->hdr->as<int64_t>() + 1 : nullptr);
+        void* hb = host_buf(p, (size_t)((len + 7) >> 3));
+        stage.add(hb, bits->ptr, (size_t)((len + 7) >> 3));
         stage.add(&null_counts[ci], counter->ptr, 8);
         p->buffers[0] = hb;
         keep.push_back(bits);
@@ -378,6 +414,13 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
       a->buffers = p->buffers.data();
     }
     stage.flush();
+    if (lz) {
+      redo = !(hdr[0] == 0 && hdr[1] >= 0 && hdr[1] <= lz->bound && !(lz->redo_if_empty && hdr[1] == 0));
+      if (!redo) {
+        out->length = hdr[1];
+        for (size_t ci = 0; ci < b.cols.size(); ++ci) top->child_store[ci].length = hdr[1];
+      }
+    }
     for (size_t ci = 0; ci < b.cols.size(); ++ci) top->child_store[ci].null_count = null_counts[ci];
     for (auto& pr : bools) {
       auto* p = static_cast<ArrayPriv*>(top->child_store[pr.first].private_data);
@@ -388,6 +431,13 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
   } catch (...) {
     release_array(out);
     throw;
+  }
+  if (redo) {
+    release_array(out);
+    if (!lz->redo) fail(B2_ERR_EXECUTION, "internal: a speculative aggregate failed and cannot be redone");
+    BatchPtr r = lz->redo();
+    if (r->lazy) resolve_batch(*r);
+    batch_to_arrow(*r, out);
   }
 }
 

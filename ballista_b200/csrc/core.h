@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <chrono>
+#include <functional>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -179,11 +180,25 @@ struct Column {
   }
 };
 
+struct Batch;
+using BatchPtr = std::shared_ptr<Batch>;
+// A small aggregate result whose row count is still on the device: the producing kernels ran speculatively and nothing
+// was read back.  Columns are allocated for `bound` rows; `hdr` (int64, in HBM) = [0] status of the producing launches
+// (0 = fine), [1] rows, [2 + c] character total of Utf8 column c.  The consumers that can work from the device-side
+// count (the small Final aggregate, the Partial -> Final all-gather, the host export) do so, and a whole
+// Partial -> Final -> export step synchronises once; everyone else calls resolve_batch() first.
+struct LazyRows {
+  BufPtr hdr;
+  int64_t bound = 0;
+  bool redo_if_empty = false;        // an ungrouped aggregate over no rows is one NULL row, made by the checked path
+  std::function<BatchPtr()> redo;    // recompute through the checked path when the speculation failed
+};
 struct Batch {
   Ctx* ctx = nullptr;
   Schema schema;
   std::vector<Column> cols;
-  int64_t num_rows = 0;
+  int64_t num_rows = 0;  // -1 while `lazy` is set
+  std::shared_ptr<LazyRows> lazy;
   // >= 0: this batch is the complete output of one Partial aggregate whose first `unique_key_cols` columns are its
   // group keys, so no key occurs twice in it.  Any operator that builds a new batch leaves the default.
   int unique_key_cols = -1;
@@ -193,7 +208,12 @@ struct Batch {
     return b;
   }
 };
-using BatchPtr = std::shared_ptr<Batch>;
+// one readback: afterwards b.lazy is null and num_rows / column lengths are exact (core.cu)
+void resolve_batch(Batch& b);
+inline BatchPtr resolved(BatchPtr b) {
+  if (b && b->lazy) resolve_batch(*b);
+  return b;
+}
 // paths that move raw value buffers only (the exchange) refuse nullable data loudly instead of dropping the validity
 inline void require_no_nulls(const Batch& b, const char* where) {
   for (size_t c = 0; c < b.cols.size(); ++c)
@@ -213,7 +233,8 @@ void batch_to_arrow(const Batch& b, ArrowArray* out);
 BufPtr valid_and(Ctx* ctx, const BufPtr& a, const BufPtr& b, int64_t n);             // null when both are absent
 BufPtr valid_from_bitmap(Ctx* ctx, const uint8_t* host_bits, int64_t bit_off, int64_t n, cudaStream_t st);
 // packs byte validity into an Arrow bitmap in HBM; *nulls_dev (int64 in HBM) receives the null count
-BufPtr valid_to_bitmap(Ctx* ctx, const uint8_t* valid, int64_t n, int64_t* nulls_dev);
+// (n_dev: the row count lives on the device; rows at and beyond it are packed but not counted as NULLs)
+BufPtr valid_to_bitmap(Ctx* ctx, const uint8_t* valid, int64_t n, int64_t* nulls_dev, const int64_t* n_dev = nullptr);
 BufPtr valid_gather(Ctx* ctx, const uint8_t* valid, const uint32_t* idx, int64_t m);  // idx 0xFFFFFFFF -> NULL
 BufPtr valid_not(Ctx* ctx, const uint8_t* valid_or_null, int64_t n);                 // IS NULL as a Boolean column
 BufPtr valid_copy(Ctx* ctx, const uint8_t* valid_or_null, int64_t n);                // IS NOT NULL as a Boolean column

@@ -106,7 +106,7 @@ BufPtr radix_sort_order(Ctx* ctx, const std::vector<const u64*>& words, const st
 void comm_unique_id(void* id128);
 void comm_init(Ctx* ctx, int rank, int nranks, const void* id128);
 void comm_destroy(Ctx* ctx);
-BatchPtr comm_allgather_batch(Ctx* ctx, const Batch& local);
+BatchPtr comm_allgather_batch(Ctx* ctx, Batch& local);
 // all-to-all of a destination-major permuted batch: slice d (counts[d] rows) goes to rank d
 BatchPtr comm_all_to_all(Ctx* ctx, const Batch& permuted, const std::vector<int64_t>& counts);
 // shuffle.cu: the same exchange over CUDA-IPC peer memory (columns moved into a peer-mapped arena by the split's
@@ -117,12 +117,15 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st);
 // ---- RecordBatchStream ----
 struct Stream {
   virtual ~Stream() {}
-  virtual BatchPtr next() = 0;  // nullptr at end of stream
+  virtual BatchPtr next() = 0;  // nullptr at end of stream; never a lazy batch
+  // may return a batch whose row count is still on the device (Batch::lazy); only consumers that work from the
+  // device-side count ask for it
+  virtual BatchPtr next_lazy() { return next(); }
 };
 using StreamPtr = std::unique_ptr<Stream>;
 
 // ---- ExecutionPlan ----
-struct Op {
+struct Op : std::enable_shared_from_this<Op> {
   Ctx* ctx = nullptr;
   std::vector<std::shared_ptr<Op>> children;
   std::string last_path = "unexecuted";

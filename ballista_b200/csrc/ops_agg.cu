@@ -7,6 +7,7 @@
 // Otherwise the unfused path evaluates mask / key / argument columns first (eval.cu) and feeds the same
 // aggregate kernels through the materialised source.
 #include <cstdlib>
+#include <cstring>
 
 #include "ops.h"
 
@@ -67,11 +68,13 @@ struct HashAggregateExec : Op {
     HashAggregateExec* op;
     int partition;
     bool done = false;
-    BatchPtr next() override {
+    BatchPtr next_lazy() override {
       if (done) return nullptr;
       done = true;
-      return op->mode == B2_AGG_PARTIAL ? op->run_partial(partition) : op->run_final(partition);
+      const bool spec = !getenv("B2_DISABLE_SPECULATION");
+      return op->mode == B2_AGG_PARTIAL ? op->run_partial(partition, spec) : op->run_final(partition, spec);
     }
+    BatchPtr next() override { return resolved(next_lazy()); }
   };
   StreamPtr execute(int partition) override {
     auto s = std::make_unique<S>();
@@ -90,9 +93,13 @@ struct HashAggregateExec : Op {
   };
   BatchPtr null_row();
   // speculative = the runner ran consume_unchecked(): returns null when the batch has to be redone
-  BatchPtr emit(AggRunner& r, bool partial, const std::vector<Slots>& sl, bool speculative, int* status_out);
-  BatchPtr run_partial(int partition);
-  BatchPtr run_final(int partition);
+  BatchPtr emit(AggRunner& r, bool partial, const std::vector<Slots>& sl);
+  // speculative: nothing is read back; the batch carries its header (Batch::lazy) and `redo` reruns the checked path
+  BatchPtr emit_lazy(const GroupTable& table, const int* status, bool partial, const std::vector<Slots>& sl,
+                     int64_t bound, std::function<BatchPtr()> redo);
+  void plan_emit(EmitPlan& ep, bool partial, const std::vector<Slots>& sl);
+  BatchPtr run_partial(int partition, bool speculate);
+  BatchPtr run_final(int partition, bool speculate);
 };
 
 // An ungrouped aggregate over no rows still yields one row: COUNT = 0, SUM / AVG = NULL (DataFusion's
@@ -120,12 +127,7 @@ BatchPtr HashAggregateExec::null_row() {
 }
 
 // ---- output assembly shared by both modes ----
-BatchPtr HashAggregateExec::emit(AggRunner& r, bool partial, const std::vector<Slots>& sl, bool speculative,
-                                 int* status_out) {
-  int64_t exact = speculative ? -1 : r.finish();
-  if (!speculative && groups.empty() && exact == 0) return null_row();
-  const int64_t bound = speculative ? std::min<int64_t>((int64_t)r.main->cap, 32768) : exact;
-  EmitPlan ep(ctx, *r.main, bound);
+void HashAggregateExec::plan_emit(EmitPlan& ep, bool partial, const std::vector<Slots>& sl) {
   for (size_t g = 0; g < groups.size(); ++g) ep.key(layout.parts[g]);
   for (size_t a = 0; a < aggs.size(); ++a) {
     const Slots& s = sl[a];
@@ -145,9 +147,14 @@ BatchPtr HashAggregateExec::emit(AggRunner& r, bool partial, const std::vector<S
         break;
     }
   }
+}
+BatchPtr HashAggregateExec::emit(AggRunner& r, bool partial, const std::vector<Slots>& sl) {
+  int64_t exact = r.finish();
+  if (groups.empty() && exact == 0) return null_row();
+  EmitPlan ep(ctx, *r.main, exact);
+  plan_emit(ep, partial, sl);
   int64_t ng = 0;
-  if (!ep.run(exact, r.status->as<int>(), &ng, status_out)) return nullptr;
-  if (groups.empty() && ng == 0) return null_row();
+  ep.run(exact, r.status->as<int>(), &ng, nullptr);
   auto b = std::make_shared<Batch>();
   b->ctx = ctx;
   b->schema = out;
@@ -156,8 +163,26 @@ BatchPtr HashAggregateExec::emit(AggRunner& r, bool partial, const std::vector<S
   if (partial && !groups.empty()) b->unique_key_cols = (int)groups.size();
   return b;
 }
+BatchPtr HashAggregateExec::emit_lazy(const GroupTable& table, const int* status, bool partial,
+                                      const std::vector<Slots>& sl, int64_t bound, std::function<BatchPtr()> redo) {
+  EmitPlan ep(ctx, table, bound);
+  plan_emit(ep, partial, sl);
+  auto lz = std::make_shared<LazyRows>();
+  lz->hdr = ep.run_lazy(status);
+  lz->bound = bound;
+  lz->redo_if_empty = groups.empty();
+  lz->redo = std::move(redo);
+  auto b = std::make_shared<Batch>();
+  b->ctx = ctx;
+  b->schema = out;
+  b->num_rows = -1;
+  b->lazy = lz;
+  b->cols = std::move(ep.cols);
+  if (partial && !groups.empty()) b->unique_key_cols = (int)groups.size();
+  return b;
+}
 
-BatchPtr HashAggregateExec::run_partial(int partition) {
+BatchPtr HashAggregateExec::run_partial(int partition, bool speculate) {
   {  // column pruning: tell the input which columns the group / argument expressions read
     std::vector<char> used(children[0]->schema().fields.size(), 0);
     for (auto& g : groups) expr_columns(g, used);
@@ -218,7 +243,6 @@ BatchPtr HashAggregateExec::run_partial(int partition) {
     for (size_t c = 0; c < touched.size() && c < ss.fields.size(); ++c)
       if (touched[c] && ss.fields[c].nullable) fusable_shape = false;
   }
-  bool speculated = false;
   std::vector<Column> temps;
   std::vector<BufPtr> tbufs;
   BufPtr keybuf;
@@ -316,25 +340,20 @@ BatchPtr HashAggregateExec::run_partial(int partition) {
     if (!runner) runner = std::make_unique<AggRunner>(ctx, l.na, l.nc, l.keyed);
     if (runner->na != l.na || runner->nc != l.nc)
       fail(B2_ERR_EXECUTION, "internal: aggregate source shape changed between batches");
-    if (single && !getenv("B2_DISABLE_SPECULATION") && runner->consume_unchecked(l, cur->num_rows)) {
-      // nothing read back yet: the emit returns status + group count with its single readback
+    if (single && speculate && runner->consume_unchecked(l, cur->num_rows)) {
+      // Nothing is read back: the result carries its device-side header.  Whoever needs the row count first (the
+      // small Final, the all-gather, the export) learns with it whether the speculation held; if not - wide keys,
+      // too many groups, an ungrouped aggregate over no rows - the partition is redone through the checked path.
       last_path = path + "/small";
-      int st = 0;
-      BatchPtr o = emit(*runner, true, slots_now(), true, &st);
-      if (o) return o;
-      // redo through the checked path: wide keys, or the high-cardinality kernel, or a loud failure
-      runner->reset();
-      if (st == AGG_KEY_TOO_WIDE && l.small_wide) runner->narrow_overflowed = true;
-      else if (st == AGG_KEY_TOO_WIDE) runner->check_status(st);
-      else if (st == AGG_ABORT_CARDINALITY) runner->force_global = true;
-      bind(cur, &l);  // temporaries of the unfused path were released with the first attempt's buffers
-      speculated = true;
+      auto self = shared_from_this();
+      return emit_lazy(*runner->main, runner->status->as<int>(), true, slots_now(), SPEC_BOUND, [self, partition]() {
+        return static_cast<HashAggregateExec*>(self.get())->run_partial(partition, false);
+      });
     }
     runner->consume(l, cur->num_rows);  // synchronises on the status word, so temporaries may go
     cur = ahead;
     ahead = cur ? next_nonempty() : nullptr;
   }
-  (void)speculated;
   if (!runner) {
     if (!layout_fixed)
       for (size_t k = 0; k < args.size(); ++k)
@@ -342,12 +361,11 @@ BatchPtr HashAggregateExec::run_partial(int partition) {
     runner = std::make_unique<AggRunner>(ctx, agg_padded_na(n_acc), agg_padded_nc(n_cnt), !groups.empty());
   }
   last_path = (path.empty() ? std::string("empty") : path) + (runner->path.empty() ? "" : "/" + runner->path);
-  return emit(*runner, true, slots_now(), false, nullptr);
+  return emit(*runner, true, slots_now());
 }
 
-BatchPtr HashAggregateExec::run_final(int partition) {
+BatchPtr HashAggregateExec::run_final(int partition, bool speculate) {
   // input = partial-state batches: group columns first, then state columns positionally
-  StreamPtr in = children[0]->execute(partition);
   size_t ng = groups.size();
   std::vector<int> sum_col(aggs.size(), -1), cnt_col(aggs.size(), -1);
   int col = (int)ng;
@@ -362,20 +380,25 @@ BatchPtr HashAggregateExec::run_final(int partition) {
   if ((int)in_schema.fields.size() != col)
     fail(B2_ERR_EXECUTION, "Final aggregate: input has " + std::to_string(in_schema.fields.size()) +
                                " columns, expected " + std::to_string(col) + " (groups + accumulator state)");
+  StreamPtr in = children[0]->execute(partition);
+  std::vector<BatchPtr> all;  // partial states are small: collect them (lazy ones keep their count on the device)
+  int64_t bound_rows = 0;
+  while (BatchPtr b = in->next_lazy()) {
+    if (!b->lazy && b->num_rows == 0) continue;
+    bound_rows += b->lazy ? b->lazy->bound : b->num_rows;
+    all.push_back(b);
+  }
+  bool plain_keys = true;
+  for (size_t g = 0; g < ng; ++g) plain_keys = plain_keys && groups[g]->kind == B2_EXPR_COLUMN;
   // The whole input is ONE Partial output over these group keys (a stage with a single partition, or states that an
   // exchange already co-located and a Partial re-aggregated): every key occurs once, so the merge is the identity and
   // SUM / COUNT states are the results.  AVG (a division) and computed group expressions take the general path.
-  auto next_nonempty = [&]() {
-    BatchPtr b;
-    while ((b = in->next()) && b->num_rows == 0) {}
-    return b;
-  };
-  BatchPtr cur = next_nonempty(), ahead = cur ? next_nonempty() : nullptr;
-  const bool single = cur && !ahead;
-  bool identity = single && ng > 0 && cur->unique_key_cols == (int)ng && !getenv("B2_DISABLE_FUSION");
+  const bool single = all.size() == 1;
+  bool identity = single && !all[0]->lazy && ng > 0 && all[0]->unique_key_cols == (int)ng && !getenv("B2_DISABLE_FUSION");
   for (size_t g = 0; g < ng && identity; ++g) identity = groups[g]->kind == B2_EXPR_COLUMN && groups[g]->col == (int)g;
   for (size_t a = 0; a < aggs.size() && identity; ++a) identity = aggs[a].fn != B2_AGG_AVG;
   if (identity) {
+    const BatchPtr& cur = all[0];
     auto o = std::make_shared<Batch>();
     o->ctx = ctx;
     o->schema = out;
@@ -389,29 +412,107 @@ BatchPtr HashAggregateExec::run_final(int partition) {
   // sum states in `cnt`
   std::vector<Slots> sl(aggs.size());
   int n_acc = 0, n_cnt = 0;
-  bool layout_fixed = false;
+  auto fix_layout = [&](const Batch* b) {
+    for (size_t a = 0; a < aggs.size(); ++a) {
+      Slots& s = sl[a];
+      if (sum_col[a] >= 0) {
+        const int dt = b ? b->cols[sum_col[a]].dtype : in_schema.fields[sum_col[a]].dtype;
+        const bool has_valid = b && b->cols[sum_col[a]].valid;
+        if (dt == B2_FLOAT64) s.acc = n_acc++;
+        else if (dt == B2_INT64 || dt == B2_UINT64) s.isum = n_cnt++;
+        else fail(B2_ERR_NOT_IMPLEMENTED, std::string("sum state of type ") + dtype_name(dt));
+        // an ungrouped Final always tracks NULL states: the empty partition among its inputs may come second
+        if (aggs[a].fn == B2_AGG_SUM && (has_valid || ng == 0)) s.vcnt = n_cnt++;
+        if (aggs[a].fn == B2_AGG_AVG) s.avg_null = has_valid || ng == 0;
+      }
+      if (cnt_col[a] >= 0) s.cnt = n_cnt++;
+    }
+  };
+  fix_layout(all.empty() ? nullptr : all[0].get());
+  if (speculate && !all.empty() && plain_keys && bound_rows <= TINY_MAX_ROWS && all.size() <= 64 && n_acc <= 8 && n_cnt <= 12) {
+    // ---- small Final: one single-CTA kernel per four batches + the emit, nothing read back ----
+    auto table = make_group_table(ctx, ng ? TINY_CAP : 16, std::max(n_acc, 1), std::max(n_cnt, 1), /*init=*/false);
+    BufPtr status = dev_alloc_zero(ctx, 16);
+    for (size_t b0 = 0; b0 < all.size(); b0 += TINY_BATCHES) {
+      TinyArgs ta;
+      memset(&ta, 0, sizeof ta);
+      ta.nb = (int)std::min<size_t>(TINY_BATCHES, all.size() - b0);
+      ta.nkeys = (int)ng;
+      ta.na = n_acc;
+      ta.nc = n_cnt;
+      ta.init = b0 == 0;
+      for (size_t g = 0; g < ng; ++g) {
+        ta.part_dtype[g] = layout.parts[g].dtype;
+        ta.part_off[g] = layout.parts[g].byte_off;
+        ta.part_bytes[g] = layout.parts[g].bytes;
+      }
+      for (int x = 0; x < 8; ++x) ta.vslot[x] = -1;
+      for (int x = 0; x < 12; ++x) ta.cvslot[x] = -1;
+      for (int k = 0; k < ta.nb; ++k) {
+        const Batch& b = *all[b0 + k];
+        TinyBatch& tb = ta.b[k];
+        tb.hdr = b.lazy ? b.lazy->hdr->as<int64_t>() : nullptr;
+        tb.rows = b.lazy ? 0 : b.num_rows;
+        tb.bound = b.lazy ? b.lazy->bound : b.num_rows;
+        tb.redo_if_empty = b.lazy && b.lazy->redo_if_empty;
+        auto tcol = [](const Column& c) {
+          return TinyCol{c.data ? c.data->ptr : nullptr, c.validity(), c.chars ? c.chars->as<uint8_t>() : nullptr};
+        };
+        for (size_t g = 0; g < ng; ++g) tb.key[g] = tcol(b.cols[groups[g]->col]);
+        for (size_t a = 0; a < aggs.size(); ++a) {
+          const Slots& s = sl[a];
+          if (sum_col[a] >= 0) {
+            const Column& sc = b.cols[sum_col[a]];
+            if ((s.acc >= 0) != (sc.dtype == B2_FLOAT64)) fail(B2_ERR_EXECUTION, "sum state type changed between batches");
+            if (sc.valid && aggs[a].fn == B2_AGG_SUM && s.vcnt < 0)
+              fail(B2_ERR_NOT_IMPLEMENTED, "NULL sum states appear in a later batch of a partition whose first batch had none");
+            if (s.acc >= 0) {
+              tb.val[s.acc] = tcol(sc);
+              ta.vslot[s.acc] = s.vcnt;
+            } else {
+              tb.cnt[s.isum] = tcol(sc);
+              ta.cvslot[s.isum] = s.vcnt;
+            }
+          }
+          if (cnt_col[a] >= 0) {
+            if (b.cols[cnt_col[a]].dtype != B2_UINT64) fail(B2_ERR_EXECUTION, "count state must be UInt64");
+            tb.cnt[s.cnt] = tcol(b.cols[cnt_col[a]]);
+          }
+        }
+      }
+      final_tiny_launch(ctx, ta, *table, status->as<int>());
+    }
+    last_path = "small-final";
+    auto self = shared_from_this();
+    return emit_lazy(*table, status->as<int>(), false, sl, std::max<int64_t>(1, std::min<int64_t>(SPEC_BOUND, bound_rows)),
+                     [self, partition]() {
+                       return static_cast<HashAggregateExec*>(self.get())->run_final(partition, false);
+                     });
+  }
+  // ---- general path: resolved batches through the aggregate kernels ----
+  {
+    std::vector<BatchPtr> keep;
+    for (auto& b : all) {
+      resolved(b);
+      if (b->num_rows) keep.push_back(b);
+    }
+    all.swap(keep);
+  }
   std::unique_ptr<AggRunner> runner;
   std::vector<BufPtr> tbufs;
   std::vector<Column> kc;
   BufPtr keybuf;
+  bool layout_checked = false;
   auto bind = [&](const BatchPtr& b, AggLaunch* l) {
     tbufs.clear();
     kc.clear();
-    if (!layout_fixed) {
-      layout_fixed = true;
-      for (size_t a = 0; a < aggs.size(); ++a) {
-        Slots& s = sl[a];
-        if (sum_col[a] >= 0) {
-          const Column& sc = b->cols[sum_col[a]];
-          if (sc.dtype == B2_FLOAT64) s.acc = n_acc++;
-          else if (sc.dtype == B2_INT64 || sc.dtype == B2_UINT64) s.isum = n_cnt++;
-          else fail(B2_ERR_NOT_IMPLEMENTED, std::string("sum state of type ") + dtype_name(sc.dtype));
-          // an ungrouped Final always tracks NULL states: the empty partition among its inputs may come second
-          if (aggs[a].fn == B2_AGG_SUM && (sc.valid || ng == 0)) s.vcnt = n_cnt++;
-          if (aggs[a].fn == B2_AGG_AVG) s.avg_null = sc.valid || ng == 0;
-        }
-        if (cnt_col[a] >= 0) s.cnt = n_cnt++;
-      }
+    if (!layout_checked) {
+      layout_checked = true;
+      // the layout came from the first collected batch, which may have been an empty lazy one: re-derive it from the
+      // first batch that actually has rows
+      sl.assign(aggs.size(), Slots());
+      n_acc = n_cnt = 0;
+      fix_layout(b.get());
     }
     std::vector<const double*> vals(n_acc, nullptr);
     std::vector<const u64*> cnts(n_cnt, nullptr);
@@ -457,39 +558,17 @@ BatchPtr HashAggregateExec::run_final(int partition) {
     if (cnts.empty()) cnts.push_back(nullptr);
     *l = bind_column_agg(ctx, keys, nullptr, vals, cnts);
   };
-  while (cur) {
+  for (auto& cur : all) {
     AggLaunch l;
     bind(cur, &l);
     // partial states carry one row per group of their partition: a large state batch means more groups than the
     // per-CTA tables of the low-cardinality kernel hold, so go straight to the HBM table
     if (ng && cur->num_rows > 16384) runner->force_global = true;
-    if (single && !getenv("B2_DISABLE_SPECULATION") && runner->consume_unchecked(l, cur->num_rows)) {
-      last_path = "unfused/small";
-      int st = 0;
-      BatchPtr o = emit(*runner, false, sl, true, &st);
-      if (o) return o;
-      runner->reset();
-      if (st == AGG_KEY_TOO_WIDE) runner->check_status(st);
-      if (st == AGG_ABORT_CARDINALITY) runner->force_global = true;
-      bind(cur, &l);
-    }
     runner->consume(l, cur->num_rows);
-    cur = ahead;
-    ahead = cur ? next_nonempty() : nullptr;
   }
-  if (!runner) {
-    for (size_t a = 0; a < aggs.size(); ++a) {  // no input at all: layout from the schema
-      Slots& s = sl[a];
-      if (sum_col[a] >= 0) {
-        if (in_schema.fields[sum_col[a]].dtype == B2_FLOAT64) s.acc = n_acc++;
-        else s.isum = n_cnt++;
-      }
-      if (cnt_col[a] >= 0) s.cnt = n_cnt++;
-    }
-    runner = std::make_unique<AggRunner>(ctx, agg_padded_na(n_acc), agg_padded_nc(n_cnt), ng > 0);
-  }
+  if (!runner) runner = std::make_unique<AggRunner>(ctx, agg_padded_na(n_acc), agg_padded_nc(n_cnt), ng > 0);
   last_path = "unfused/" + runner->path;
-  return emit(*runner, false, sl, false, nullptr);
+  return emit(*runner, false, sl);
 }
 
 static int sum_return_type(int dt) {  // DataFusion's sum_return_type

@@ -36,7 +36,8 @@ struct MemoryExec : Op {
     MemoryExec* op;
     int part;
     size_t pos = 0;
-    BatchPtr next() override {
+    BatchPtr next() override { return resolved(next_lazy()); }
+    BatchPtr next_lazy() override {
       auto& v = op->parts[part];
       if (pos >= v.size()) return nullptr;
       auto& it = v[pos++];
@@ -86,6 +87,7 @@ void memory_exec_add_device(Op* op, int partition, BatchPtr batch) {
   auto* m = as_mem(op);
   if (partition < 0 || partition >= (int)m->parts.size()) fail(B2_ERR_INVALID_ARG, "partition out of range");
   if (batch->cols.size() != m->sch.fields.size()) fail(B2_ERR_ARROW, "batch does not match the schema");
+  // a lazy batch (device-side row count) is accepted as it is: the stream hands it to consumers that can use it
   for (size_t i = 0; i < batch->cols.size(); ++i)
     if (batch->cols[i].dtype != m->sch.fields[i].dtype) fail(B2_ERR_ARROW, "batch column type mismatch");
   auto it = std::make_shared<MemItem>();
@@ -220,14 +222,15 @@ struct MergeExec : Op {
     int part = 0, nparts = 0;
     bool own_only = false;
     StreamPtr cur;
-    BatchPtr next() override {
+    BatchPtr next() override { return resolved(next_lazy()); }
+    BatchPtr next_lazy() override {
       while (part < nparts) {
         if (own_only && part != op->ctx->rank) {  // above an exchange: the other partitions live on other ranks
           part++;
           continue;
         }
         if (!cur) cur = op->children[0]->execute(part);
-        BatchPtr b = cur->next();
+        BatchPtr b = cur->next_lazy();
         if (b) return b;
         cur.reset();
         part++;

@@ -8,7 +8,9 @@
 namespace b2 {
 
 // status word of an aggregate launch (read back by the host)
-enum { AGG_OK = 0, AGG_ABORT_CARDINALITY = 1, AGG_KEY_TOO_WIDE = 2, AGG_TABLE_FULL = 3 };
+// 4..6: raised by the small Final kernel (its host side redoes the aggregate through the checked path)
+enum { AGG_OK = 0, AGG_ABORT_CARDINALITY = 1, AGG_KEY_TOO_WIDE = 2, AGG_TABLE_FULL = 3, AGG_INPUT_FAILED = 4,
+       AGG_TOO_BIG = 5, AGG_NULL_KEY = 6 };
 
 typedef unsigned long long u64;
 typedef unsigned __int128 u128;

@@ -45,8 +45,10 @@ BufPtr valid_from_bitmap(Ctx* ctx, const uint8_t* host_bits, int64_t bit_off, in
 }
 
 // one thread packs 8 rows into one bitmap byte
-__global__ void bitmap_pack_kernel(const uint8_t* valid, int64_t n, uint8_t* bits, unsigned long long* nulls) {
+__global__ void bitmap_pack_kernel(const uint8_t* valid, int64_t n, uint8_t* bits, unsigned long long* nulls,
+                                   const int64_t* n_dev) {
   int64_t nb = (n + 7) >> 3;
+  const int64_t counted = n_dev ? (*n_dev < n ? *n_dev : n) : n;
   int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   unsigned long long missing = 0;
   for (; j < nb; j += (int64_t)gridDim.x * blockDim.x) {
@@ -55,19 +57,19 @@ __global__ void bitmap_pack_kernel(const uint8_t* valid, int64_t n, uint8_t* bit
       int64_t i = j * 8 + q;
       if (i < n) {
         if (valid[i]) v |= 1u << q;
-        else missing++;
+        else if (i < counted) missing++;
       }
     }
     bits[j] = (uint8_t)v;
   }
   if (missing) atomicAdd(nulls, missing);
 }
-BufPtr valid_to_bitmap(Ctx* ctx, const uint8_t* valid, int64_t n, int64_t* nulls_dev) {
+BufPtr valid_to_bitmap(Ctx* ctx, const uint8_t* valid, int64_t n, int64_t* nulls_dev, const int64_t* n_dev) {
   auto bits = dev_alloc(ctx, (size_t)((n + 7) >> 3) + 16);
   B2_CUDA(cudaMemsetAsync(nulls_dev, 0, 8, ctx->stream));
   if (n) {
     bitmap_pack_kernel<<<grid_for(ctx, 8, (n + 7) >> 3, 256), 256, 0, ctx->stream>>>(
-        valid, n, bits->as<uint8_t>(), reinterpret_cast<unsigned long long*>(nulls_dev));
+        valid, n, bits->as<uint8_t>(), reinterpret_cast<unsigned long long*>(nulls_dev), n_dev);
     B2_LAUNCHED(ctx);
   }
   return bits;

@@ -282,6 +282,11 @@ class MemoryExec(ExecutionPlan):
             for b in batches:
                 self.add(p, b)
 
+    def clear(self):
+        """Drop every batch of every partition (b2_memory_exec_clear): the plans above recompute on their next execute."""
+        K.check(K.lib().b2_memory_exec_clear(self._h))
+        self._keep = []
+
     def add(self, partition, b):
         if isinstance(b, DeviceBatch):
             K.check(K.lib().b2_memory_exec_add_device_batch(self._h, partition, b._h))

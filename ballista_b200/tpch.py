@@ -190,6 +190,28 @@ def scan(ctx, batches_per_partition, schema=None):
     return MemoryExec(ctx, schema, batches_per_partition)
 
 
+class TwoStage:
+    """A Partial stage plan and its Final stage plan, built ONCE and executed per call - what an executor does when it
+    keeps the decoded plan of a stage and runs one task per partition (b2_op_execute is the per-task call,
+    rust/executor/src/flight_service.rs:117-121).  `run()` = Partial task on this GPU -> merge of the partial states
+    (all-gather over NVLink when a communicator is attached, replacing the MergeExec stage hop) -> Final task."""
+
+    def __init__(self, ctx, partial_plan, make_final, partition=0, merge="local"):
+        self.ctx, self.partial, self.partition = ctx, partial_plan, partition
+        self.gather = ctx.nranks > 1 and merge != "local"
+        self.leaf = MemoryExec(ctx, partial_plan.schema(), [[]])
+        self.final = make_final(self.leaf)
+
+    def run(self):
+        states = self.partial.collect_device(self.partition)
+        if self.gather:
+            states = [self.ctx.allgather(s) for s in states]
+        self.leaf.clear()
+        for s in states:
+            self.leaf.add(0, s)
+        return self.final.collect()
+
+
 def run_two_stage(ctx, partial_plan, make_final, partition=0, merge="local"):
     """Run the Partial stage on this GPU, merge partial states (all-gather over NVLink when a communicator
     is attached, replacing the MergeExec stage hop), then the Final stage.  Returns a pyarrow Table."""

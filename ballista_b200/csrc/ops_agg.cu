@@ -394,9 +394,14 @@ BatchPtr HashAggregateExec::run_final(int partition, bool speculate) {
   // exchange already co-located and a Partial re-aggregated): every key occurs once, so the merge is the identity and
   // SUM / COUNT states are the results.  AVG (a division) and computed group expressions take the general path.
   const bool single = all.size() == 1;
-  bool identity = single && !all[0]->lazy && ng > 0 && all[0]->unique_key_cols == (int)ng && !getenv("B2_DISABLE_FUSION");
+  bool identity = single && ng > 0 && all[0]->unique_key_cols == (int)ng && !getenv("B2_DISABLE_FUSION");
   for (size_t g = 0; g < ng && identity; ++g) identity = groups[g]->kind == B2_EXPR_COLUMN && groups[g]->col == (int)g;
   for (size_t a = 0; a < aggs.size() && identity; ++a) identity = aggs[a].fn != B2_AGG_AVG;
+  if (identity) resolved(all[0]);  // (a lazy Partial output: its count is needed now; still cheaper than any merge)
+  if (identity && all[0]->num_rows == 0) {
+    identity = false;
+    all.clear();
+  }
   if (identity) {
     const BatchPtr& cur = all[0];
     auto o = std::make_shared<Batch>();

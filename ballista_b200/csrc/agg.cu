@@ -214,11 +214,23 @@ int64_t AggRunner::finish() {
 // ------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ u128 key_bits(const Key128& k) { return ((u128)k.hi << 64) | k.lo; }
 
-static Column new_fixed(Ctx* ctx, int dtype, int64_t n) {
+constexpr size_t EMIT_ARENA_BYTES = 384 << 10;
+BufPtr EmitPlan::alloc(size_t bytes) {
+  if (arena) {
+    size_t off = (arena_used + 15) & ~(size_t)15;
+    if (off + bytes + 16 <= arena->bytes) {
+      arena_used = off + bytes;
+      return dev_view(arena, off, bytes);
+    }
+    arena = nullptr;  // does not fit: ordinary buffers, the export copies column by column
+  }
+  return dev_alloc(ctx, bytes);
+}
+Column EmitPlan::new_fixed(int dtype) {
   Column c;
   c.dtype = dtype;
-  c.length = n;
-  c.data = dev_alloc(ctx, (size_t)n * dtype_width(dtype) + 16);
+  c.length = bound;
+  c.data = alloc((size_t)bound * dtype_width(dtype) + 16);
   return c;
 }
 
@@ -241,7 +253,7 @@ struct EmitArgs {
 };
 // hdr (int64): [0] = status word, [1] = group count, [2 + y] = character total of column y (Utf8 key columns).
 // ng_dev == null: the host knows the group count (`bound`).
-__global__ void __launch_bounds__(256) emit_all_kernel(EmitArgs args, const Key128* __restrict__ keys,
+__global__ void __launch_bounds__(256) emit_all_kernel(const __grid_constant__ EmitArgs args, const Key128* __restrict__ keys,
                                                        const uint32_t* __restrict__ slots, int64_t bound,
                                                        const int* ng_dev, const int* status, int64_t* hdr) {
   const EmitCol& col = args.c[blockIdx.y];
@@ -317,9 +329,14 @@ __global__ void __launch_bounds__(256) emit_all_kernel(EmitArgs args, const Key1
   }
 }
 
-EmitPlan::EmitPlan(Ctx* c, const GroupTable& t, int64_t b) : ctx(c), table(t), bound(b) {}
+EmitPlan::EmitPlan(Ctx* c, const GroupTable& t, int64_t b, bool use_arena) : ctx(c), table(t), bound(b) {
+  if (use_arena) {
+    arena = dev_alloc(ctx, EMIT_ARENA_BYTES);
+    hdr = alloc((size_t)(2 + 24) * 8);
+  }
+}
 void EmitPlan::push(int kind, int byte_off, const void* src, const void* src2, const u64* vsrc, Column col) {
-  if (vsrc) col.valid = dev_alloc(ctx, (size_t)bound + 16);
+  if (vsrc) col.valid = alloc((size_t)bound + 16);
   descs.push_back(EmitDesc{kind, byte_off, src, src2, vsrc});
   cols.push_back(std::move(col));
 }
@@ -328,29 +345,29 @@ void EmitPlan::key(const KeyPart& part) {
     Column c;
     c.dtype = B2_UTF8;
     c.length = bound;
-    c.data = dev_alloc(ctx, (size_t)(bound + 1) * 4 + 16);
-    c.chars = dev_alloc(ctx, (size_t)bound * 15 + 16);
+    c.data = alloc((size_t)(bound + 1) * 4 + 16);
+    c.chars = alloc((size_t)bound * 15 + 16);
     push(EMIT_KEY_STR, part.byte_off, nullptr, nullptr, nullptr, std::move(c));
     return;
   }
   push(part.bytes == 8 ? EMIT_KEY_I64 : EMIT_KEY_I32, part.byte_off, nullptr, nullptr, nullptr,
-       new_fixed(ctx, part.dtype, bound));
+       new_fixed(part.dtype));
 }
 void EmitPlan::sum(int a, int v) {
   push(EMIT_F64, 0, table.acc->as<double>() + (u64)a * table.cap, nullptr,
-       v >= 0 ? table.cnt->as<u64>() + (u64)v * table.cap : nullptr, new_fixed(ctx, B2_FLOAT64, bound));
+       v >= 0 ? table.cnt->as<u64>() + (u64)v * table.cap : nullptr, new_fixed(B2_FLOAT64));
 }
 void EmitPlan::isum(int a, int dtype, int v) {
   push(EMIT_U64, 0, table.cnt->as<u64>() + (u64)a * table.cap, nullptr,
-       v >= 0 ? table.cnt->as<u64>() + (u64)v * table.cap : nullptr, new_fixed(ctx, dtype, bound));
+       v >= 0 ? table.cnt->as<u64>() + (u64)v * table.cap : nullptr, new_fixed(dtype));
 }
 void EmitPlan::count(int a) {
-  push(EMIT_U64, 0, table.cnt->as<u64>() + (u64)a * table.cap, nullptr, nullptr, new_fixed(ctx, B2_UINT64, bound));
+  push(EMIT_U64, 0, table.cnt->as<u64>() + (u64)a * table.cap, nullptr, nullptr, new_fixed(B2_UINT64));
 }
 void EmitPlan::avg(int a, int cidx, bool track_null) {
   const u64* counts = table.cnt->as<u64>() + (u64)cidx * table.cap;
   push(EMIT_AVG, 0, table.acc->as<double>() + (u64)a * table.cap, counts, track_null ? counts : nullptr,
-       new_fixed(ctx, B2_FLOAT64, bound));
+       new_fixed(B2_FLOAT64));
 }
 bool EmitPlan::run(int64_t exact_ng, const int* status_dev, int64_t* ng_out, int* status_out) {
   if (cols.size() > EMIT_MAX_COLS) fail(B2_ERR_NOT_IMPLEMENTED, "aggregate with more than 24 output columns");
@@ -413,7 +430,8 @@ BufPtr EmitPlan::run_lazy(const int* status_dev) {
                         c.valid ? c.valid->as<uint8_t>() : nullptr};
     c.length = bound;
   }
-  BufPtr hdr = dev_alloc_zero(ctx, (size_t)(2 + EMIT_MAX_COLS) * 8);
+  if (!hdr) hdr = dev_alloc(ctx, (size_t)(2 + EMIT_MAX_COLS) * 8);
+  B2_CUDA(cudaMemsetAsync(hdr->ptr, 0, (size_t)(2 + EMIT_MAX_COLS) * 8, ctx->stream));
   dim3 grid((unsigned)grid_for(ctx, 8, bound, 256), (unsigned)args.n);
   emit_all_kernel<<<grid, 256, 0, ctx->stream>>>(args, table.keys->as<Key128>(), table.slot_list->as<uint32_t>(), bound,
                                                  table.n_groups->as<int>(), status_dev, hdr->as<int64_t>());
@@ -424,7 +442,7 @@ BufPtr EmitPlan::run_lazy(const int* status_dev) {
 // ------------------------------------------------------------------------------------------------------
 // small Final aggregate (see agg.h)
 // ------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) final_tiny_kernel(TinyArgs a, TableRef t, int na_tbl, int nc_tbl, int* status) {
+__global__ void __launch_bounds__(1024) final_tiny_kernel(const __grid_constant__ TinyArgs a, TableRef t, int na_tbl, int nc_tbl, int* status) {
   if (a.init) {  // the table arrives uninitialised
     for (u64 i = threadIdx.x; i < t.cap; i += blockDim.x) {
       t.keys[i] = Key128{KEY_EMPTY, KEY_EMPTY};

@@ -122,7 +122,10 @@ struct EmitPlan {
   int64_t bound;  // rows the output columns are allocated for (>= the group count, or the emit reports failure)
   std::vector<EmitDesc> descs;
   std::vector<Column> cols;
-  EmitPlan(Ctx* ctx, const GroupTable& t, int64_t bound);
+  // lazy results: header + all column buffers are carved out of one arena, so the export copies once
+  BufPtr arena, hdr;
+  size_t arena_used = 0;
+  EmitPlan(Ctx* ctx, const GroupTable& t, int64_t bound, bool use_arena = false);
   void key(const KeyPart& part);
   void sum(int acc_idx, int vcnt_idx = -1);
   void isum(int cnt_idx, int dtype, int vcnt_idx = -1);  // Int64 / UInt64 sums live in the count accumulators
@@ -137,6 +140,8 @@ struct EmitPlan {
   BufPtr run_lazy(const int* status_dev);
  private:
   void push(int kind, int byte_off, const void* src, const void* src2, const u64* vsrc, Column col);
+  BufPtr alloc(size_t bytes);
+  Column new_fixed(int dtype);
 };
 
 // ---- small Final aggregate: partial states of a few rows (one batch per partition or per rank) merged by ONE

@@ -50,7 +50,7 @@ DevBuf::DevBuf(Ctx* c, size_t n) : ctx(c), bytes(n) {
   }
 }
 DevBuf::~DevBuf() {
-  if (!ptr) return;
+  if (!ptr || parent) return;
   size_t n = size_class(bytes);
   {
     std::lock_guard<std::mutex> g(ctx->cache_mu);
@@ -95,7 +95,7 @@ void resolve_batch(Batch& b) {
     return;
   }
   if (!lz->redo) fail(B2_ERR_EXECUTION, "internal: a speculative aggregate failed and cannot be redone");
-  BatchPtr r = lz->redo();
+  BatchPtr r = lz->redo((int)h[0]);
   if (r->lazy) resolve_batch(*r);
   b.cols = r->cols;
   b.num_rows = r->num_rows;
@@ -339,6 +339,50 @@ struct D2HStager {
   }
 };
 
+// Lazy batch whose header and columns are windows of one arena: ONE device -> host copy of the used prefix into one
+// host block; the Arrow buffers point into that block, validity bytes are packed into bitmaps on the host (a lazy
+// result holds at most a few hundred rows).  Returns false when the header says the speculation failed.
+static bool export_arena(const Batch& b, const LazyRows& lz, ArrowArray* out, ArrayPriv* top, int64_t* status) {
+  Ctx* ctx = b.ctx;
+  char* host = static_cast<char*>(host_buf(top, lz.arena_used + 64));
+  const char* dev0 = static_cast<const char*>(lz.arena->ptr);
+  D2HStager stage(ctx);
+  stage.add(host, dev0, lz.arena_used);
+  stage.flush();
+  auto at = [&](const BufPtr& buf) { return host + (static_cast<const char*>(buf->ptr) - dev0); };
+  const int64_t* hdr = reinterpret_cast<const int64_t*>(at(lz.hdr));
+  *status = hdr[0];
+  if (!(hdr[0] == 0 && hdr[1] >= 0 && hdr[1] <= lz.bound && !(lz.redo_if_empty && hdr[1] == 0))) return false;
+  const int64_t n = hdr[1];
+  out->length = n;
+  for (size_t ci = 0; ci < b.cols.size(); ++ci) {
+    const Column& col = b.cols[ci];
+    auto* p = new ArrayPriv;
+    ArrowArray* a = &top->child_store[ci];
+    a->length = n;
+    a->release = release_array;
+    a->private_data = p;
+    if (col.dtype == B2_UTF8) p->buffers = {nullptr, at(col.data), at(col.chars)};
+    else if (col.dtype == B2_BOOL) fail(B2_ERR_EXECUTION, "internal: Boolean column in an aggregate result");
+    else p->buffers = {nullptr, at(col.data)};
+    if (col.valid) {
+      const uint8_t* v = reinterpret_cast<const uint8_t*>(at(col.valid));
+      uint8_t* bits = static_cast<uint8_t*>(host_buf(p, (size_t)((n + 7) >> 3) + 1));
+      memset(bits, 0, (size_t)((n + 7) >> 3) + 1);
+      int64_t nulls = 0;
+      for (int64_t i = 0; i < n; ++i) {
+        if (v[i]) bits[i >> 3] |= (uint8_t)(1u << (i & 7));
+        else ++nulls;
+      }
+      p->buffers[0] = bits;
+      a->null_count = nulls;
+    }
+    a->n_buffers = (int64_t)p->buffers.size();
+    a->buffers = p->buffers.data();
+  }
+  return true;
+}
+
 // A lazy batch (Batch::lazy) is exported without resolving it first: the header travels with the columns (copied at
 // their allocated bound; aggregate results are a few rows), so the export's one synchronisation is also the one that
 // learns the row count.  If the header then says the speculation failed, the batch is redone and exported again.
@@ -364,6 +408,12 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
   bool redo = false;
   try {
     if (lz && b.cols.size() > 24) fail(B2_ERR_EXECUTION, "internal: lazy batch with more than 24 columns");
+    if (lz && lz->arena) {
+      for (size_t ci = 0; ci < b.cols.size(); ++ci)
+        if (!b.cols[ci].data) fail(B2_ERR_EXECUTION, "internal: pruned column in an aggregate result");
+      redo = !export_arena(b, *lz, out, top, &hdr[0]);
+      if (!redo) return;
+    } else {
     std::vector<std::pair<size_t, std::vector<uint8_t>>> bools;  // bit-pack after the sync
     bools.reserve(b.cols.size());  // element addresses are handed to the stager
     D2HStager stage(ctx);
@@ -428,6 +478,7 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
       for (size_t i = 0; i < pr.second.size(); ++i)
         if (pr.second[i]) bits[i >> 3] |= (uint8_t)(1u << (i & 7));
     }
+    }
   } catch (...) {
     release_array(out);
     throw;
@@ -435,7 +486,7 @@ void batch_to_arrow(const Batch& b, ArrowArray* out) {
   if (redo) {
     release_array(out);
     if (!lz->redo) fail(B2_ERR_EXECUTION, "internal: a speculative aggregate failed and cannot be redone");
-    BatchPtr r = lz->redo();
+    BatchPtr r = lz->redo((int)hdr[0]);
     if (r->lazy) resolve_batch(*r);
     batch_to_arrow(*r, out);
   }

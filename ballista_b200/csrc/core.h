@@ -126,7 +126,9 @@ struct DevBuf {
   Ctx* ctx;
   void* ptr = nullptr;
   size_t bytes = 0;
+  std::shared_ptr<DevBuf> parent;  // set: this is a window of `parent`'s allocation (dev_view) and owns nothing
   DevBuf(Ctx* c, size_t n);
+  DevBuf(std::shared_ptr<DevBuf> p, size_t off, size_t n) : ctx(p->ctx), ptr(static_cast<char*>(p->ptr) + off), bytes(n), parent(std::move(p)) {}
   ~DevBuf();
   DevBuf(const DevBuf&) = delete;
   DevBuf& operator=(const DevBuf&) = delete;
@@ -135,6 +137,7 @@ struct DevBuf {
 using BufPtr = std::shared_ptr<DevBuf>;
 void ctx_trim_cache(Ctx* ctx);  // returns every cached block to the stream-ordered pool
 BufPtr dev_alloc(Ctx* ctx, size_t bytes);
+inline BufPtr dev_view(const BufPtr& parent, size_t off, size_t bytes) { return std::make_shared<DevBuf>(parent, off, bytes); }
 BufPtr dev_alloc_zero(Ctx* ctx, size_t bytes);
 
 inline size_t dtype_width(int dt) {
@@ -188,10 +191,14 @@ using BatchPtr = std::shared_ptr<Batch>;
 // count (the small Final aggregate, the Partial -> Final all-gather, the host export) do so, and a whole
 // Partial -> Final -> export step synchronises once; everyone else calls resolve_batch() first.
 struct LazyRows {
+  BufPtr arena;     // when set: header and every column buffer are windows of this one allocation, [0, arena_used),
+  size_t arena_used = 0;  // so the host export is ONE device -> host copy
   BufPtr hdr;
   int64_t bound = 0;
   bool redo_if_empty = false;        // an ungrouped aggregate over no rows is one NULL row, made by the checked path
-  std::function<BatchPtr()> redo;    // recompute through the checked path when the speculation failed
+  // recompute through the checked path when the speculation failed; gets the header's status word (0 when the
+  // failure is the row count itself)
+  std::function<BatchPtr(int)> redo;
 };
 struct Batch {
   Ctx* ctx = nullptr;

@@ -96,9 +96,11 @@ struct HashAggregateExec : Op {
   BatchPtr emit(AggRunner& r, bool partial, const std::vector<Slots>& sl);
   // speculative: nothing is read back; the batch carries its header (Batch::lazy) and `redo` reruns the checked path
   BatchPtr emit_lazy(const GroupTable& table, const int* status, bool partial, const std::vector<Slots>& sl,
-                     int64_t bound, std::function<BatchPtr()> redo);
+                     int64_t bound, std::function<BatchPtr(int)> redo);
   void plan_emit(EmitPlan& ep, bool partial, const std::vector<Slots>& sl);
-  BatchPtr run_partial(int partition, bool speculate);
+  // `only`: aggregate this one batch instead of the input stream (the redo of a failed speculation: the input, e.g. a
+  // join's output, is not recomputed); `hint`: the status the failed attempt ended with
+  BatchPtr run_partial(int partition, bool speculate, BatchPtr only = nullptr, int hint = 0);
   BatchPtr run_final(int partition, bool speculate);
 };
 
@@ -164,11 +166,13 @@ BatchPtr HashAggregateExec::emit(AggRunner& r, bool partial, const std::vector<S
   return b;
 }
 BatchPtr HashAggregateExec::emit_lazy(const GroupTable& table, const int* status, bool partial,
-                                      const std::vector<Slots>& sl, int64_t bound, std::function<BatchPtr()> redo) {
-  EmitPlan ep(ctx, table, bound);
+                                      const std::vector<Slots>& sl, int64_t bound, std::function<BatchPtr(int)> redo) {
+  EmitPlan ep(ctx, table, bound, /*use_arena=*/true);
   plan_emit(ep, partial, sl);
   auto lz = std::make_shared<LazyRows>();
   lz->hdr = ep.run_lazy(status);
+  lz->arena = ep.arena;  // null when the columns did not fit one arena
+  lz->arena_used = ep.arena_used;
   lz->bound = bound;
   lz->redo_if_empty = groups.empty();
   lz->redo = std::move(redo);
@@ -182,7 +186,7 @@ BatchPtr HashAggregateExec::emit_lazy(const GroupTable& table, const int* status
   return b;
 }
 
-BatchPtr HashAggregateExec::run_partial(int partition, bool speculate) {
+BatchPtr HashAggregateExec::run_partial(int partition, bool speculate, BatchPtr only, int hint) {
   {  // column pruning: tell the input which columns the group / argument expressions read
     std::vector<char> used(children[0]->schema().fields.size(), 0);
     for (auto& g : groups) expr_columns(g, used);
@@ -224,16 +228,27 @@ BatchPtr HashAggregateExec::run_partial(int partition, bool speculate) {
   int n_acc = 0, n_cnt = 1;
   bool layout_fixed = false, fused_run = false;
 
-  StreamPtr in = src->execute(partition);
+  StreamPtr in;
+  if (!only) in = src->execute(partition);
   std::unique_ptr<AggRunner> runner;
   std::string path;
+  // A join's output grouped by an integer key (Q3: l_orderkey, the join key itself) has about as many groups as rows:
+  // the low-cardinality kernel would fill its per-CTA tables, abort, and the batch would be done twice.  Such inputs go
+  // straight to the HBM table.  (Joins grouped by a short string - Q5's n_name, q12's l_shipmode - keep the fast path.)
+  bool join_fed_int_key = false;
+  {
+    Op* j = src;
+    if (op_is_coalesce(j)) j = j->children[0].get();
+    if (!strcmp(j->name(), "HashJoinExec"))
+      for (auto& g : groups) join_fed_int_key |= g->dtype == B2_INT32 || g->dtype == B2_INT64 || g->dtype == B2_DATE32;
+  }
   // one batch of look-ahead: a stream of exactly one batch (a partition resident in HBM) takes the speculative path
   auto next_nonempty = [&]() {
     BatchPtr b;
-    while ((b = in->next()) && (b->num_rows == 0 || reject_all)) {}
+    while (in && (b = in->next()) && (b->num_rows == 0 || reject_all)) {}
     return b;
   };
-  BatchPtr cur = next_nonempty(), ahead = cur ? next_nonempty() : nullptr;
+  BatchPtr cur = only ? only : next_nonempty(), ahead = cur ? next_nonempty() : nullptr;
   const bool single = cur && !ahead;
   if (!single) {
     // Several batches: the accumulator layout is fixed by the first one, so the fused kernels (which do not count
@@ -340,16 +355,21 @@ BatchPtr HashAggregateExec::run_partial(int partition, bool speculate) {
     if (!runner) runner = std::make_unique<AggRunner>(ctx, l.na, l.nc, l.keyed);
     if (runner->na != l.na || runner->nc != l.nc)
       fail(B2_ERR_EXECUTION, "internal: aggregate source shape changed between batches");
+    if (join_fed_int_key) runner->force_global = true;
     if (single && speculate && runner->consume_unchecked(l, cur->num_rows)) {
       // Nothing is read back: the result carries its device-side header.  Whoever needs the row count first (the
       // small Final, the all-gather, the export) learns with it whether the speculation held; if not - wide keys,
       // too many groups, an ungrouped aggregate over no rows - the partition is redone through the checked path.
       last_path = path + "/small";
       auto self = shared_from_this();
-      return emit_lazy(*runner->main, runner->status->as<int>(), true, slots_now(), SPEC_BOUND, [self, partition]() {
-        return static_cast<HashAggregateExec*>(self.get())->run_partial(partition, false);
-      });
+      BatchPtr input = cur;  // kept until the result is resolved: a redo aggregates it again, nothing below is re-run
+      return emit_lazy(*runner->main, runner->status->as<int>(), true, slots_now(), SPEC_BOUND,
+                       [self, partition, input](int st) {
+                         return static_cast<HashAggregateExec*>(self.get())->run_partial(partition, false, input, st);
+                       });
     }
+    if (hint == AGG_ABORT_CARDINALITY) runner->force_global = true;  // the failed attempt already learnt this
+    if (hint == AGG_KEY_TOO_WIDE && l.small_wide) runner->narrow_overflowed = true;
     runner->consume(l, cur->num_rows);  // synchronises on the status word, so temporaries may go
     cur = ahead;
     ahead = cur ? next_nonempty() : nullptr;
@@ -490,7 +510,7 @@ BatchPtr HashAggregateExec::run_final(int partition, bool speculate) {
     last_path = "small-final";
     auto self = shared_from_this();
     return emit_lazy(*table, status->as<int>(), false, sl, std::max<int64_t>(1, std::min<int64_t>(SPEC_BOUND, bound_rows)),
-                     [self, partition]() {
+                     [self, partition](int) {
                        return static_cast<HashAggregateExec*>(self.get())->run_final(partition, false);
                      });
   }

@@ -185,14 +185,13 @@ class RecordBatchStream:
 
     def __iter__(self):
         schema = self.plan.schema()
+        lib = K.lib()
         while True:
             arr, eos = K.ArrowArray(), C.c_int(0)
-            K.check(K.lib().b2_stream_next(self._h, C.byref(arr), C.byref(eos)))
+            K.check(lib.b2_stream_next(self._h, C.byref(arr), C.byref(eos)))
             if eos.value:
                 return
-            sch = K.ArrowSchema()
-            schema._export_to_c(_addr(sch))
-            yield pa.RecordBatch._import_from_c(_addr(arr), _addr(sch))
+            yield pa.RecordBatch._import_from_c(_addr(arr), schema)
 
     def device(self):
         while True:
@@ -218,9 +217,13 @@ class ExecutionPlan:
             pass
 
     def schema(self):
-        sch = K.ArrowSchema()
-        K.check(K.lib().b2_op_schema(self._h, C.byref(sch)))
-        return pa.Schema._import_from_c(_addr(sch))
+        # an operator's schema never changes: one trip through the C Data Interface, then the cached object
+        s = getattr(self, "_schema", None)
+        if s is None:
+            sch = K.ArrowSchema()
+            K.check(K.lib().b2_op_schema(self._h, C.byref(sch)))
+            s = self._schema = pa.Schema._import_from_c(_addr(sch))
+        return s
 
     def output_partitioning(self):
         scheme, n = C.c_int(0), C.c_int(0)

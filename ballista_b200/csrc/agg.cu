@@ -213,6 +213,10 @@ int64_t AggRunner::finish() {
 // emit kernels
 // ------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ u128 key_bits(const Key128& k) { return ((u128)k.hi << 64) | k.lo; }
+// byte `idx` (0..15) of a packed key, without 128-bit arithmetic
+__device__ __forceinline__ uint8_t key_byte(const Key128& k, int idx) {
+  return (uint8_t)(idx < 8 ? k.lo >> (8 * idx) : k.hi >> (8 * (idx - 8)));
+}
 
 constexpr size_t EMIT_ARENA_BYTES = 384 << 10;
 BufPtr EmitPlan::alloc(size_t bytes) {
@@ -275,11 +279,11 @@ __global__ void __launch_bounds__(256) emit_all_kernel(const __grid_constant__ E
     if (ng == 0 && threadIdx.x == 0) off[0] = 0;
     for (int64_t base = 0; base < ng; base += blockDim.x) {
       int64_t i = base + threadIdx.x;
-      u128 bits = 0;
+      Key128 kk{0, 0};
       int len = 0;
       if (i < ng) {
-        bits = key_bits(keys[slots[i]]) >> (8 * col.byte_off);
-        len = (int)(uint8_t)bits;
+        kk = keys[slots[i]];
+        len = (int)key_byte(kk, col.byte_off);
       }
       int v = len;
       for (int d = 1; d < 32; d <<= 1) {
@@ -297,7 +301,7 @@ __global__ void __launch_bounds__(256) emit_all_kernel(const __grid_constant__ E
       int excl = carry + woff + v - len;
       if (i < ng) {
         off[i] = excl;
-        for (int q = 0; q < len; ++q) col.chr[excl + q] = (uint8_t)(bits >> (8 * (q + 1)));
+        for (int q = 0; q < len; ++q) col.chr[excl + q] = key_byte(kk, col.byte_off + 1 + q);
         if (i == ng - 1) off[ng] = excl + len;
       }
       __syncthreads();

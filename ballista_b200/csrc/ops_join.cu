@@ -51,6 +51,7 @@ struct HashJoinExec : Op {
   bool semi_offered = false;
   bool partitioned = false;     // both inputs arrive through exchanges on the join keys: partition-wise join
   uint64_t built_version = 0;
+  ExprPtr left_pred;            // FilterExec predicate peeled off the left side (folded into the build / probe kernels)
 
   const char* name() const override { return "HashJoinExec"; }
   Schema schema() const override { return out; }
@@ -119,15 +120,15 @@ struct HashJoinExec : Op {
   }
   void build(int partition) {
     const uint64_t v = children[0]->version();
-    if (table && built_version == v) return;
+    if (left_batch && built_version == v) return;  // (the table itself is built on first use: see ensure_table)
     table.reset();
     left_batch.reset();
     left_keys.reset();
     semi_offered = false;
     built_version = v;
     Op* l = children[0].get();
-    ExprPtr pred;
-    if (fuse_left()) l = peel_filter(l, &pred);
+    left_pred = nullptr;
+    if (fuse_left()) l = peel_filter(l, &left_pred);
     std::vector<BatchPtr> all;
     int np = l->n_partitions();
     // Partitioned join: when BOTH inputs arrive through exchanges (hash repartitions whose output partition r lives on
@@ -157,16 +158,34 @@ struct HashJoinExec : Op {
       if (!ctx->comm) fail(B2_ERR_EXECUTION, "HashJoinExec: per-rank build partitions without a communicator");
       left_batch = comm_allgather_batch(ctx, *left_batch);
     }
+  }
+  // hash table over one side's batch (the collected left side, or - swapped - a small right batch)
+  std::shared_ptr<JoinTable> build_table(const Batch& b, const ExprPtr& pred, const std::vector<int>& on, int null_tag,
+                                         BufPtr* keys_keep) {
     if (k32) {
       RowPred rp;
-      Column mask = side_mask(pred, *left_batch, on_left[0], &rp);
-      table = join_build32(ctx, left_batch->cols[on_left[0]].values<int32_t>(), rp,
-                           mask.data ? mask.values<uint8_t>() : nullptr, left_batch->num_rows);
+      Column mask = side_mask(pred, b, on[0], &rp);
       // the mask buffer is freed stream-ordered after the build kernel
-    } else {
-      left_keys = pack(*left_batch, on_left, 0x81);
-      table = join_build(ctx, left_keys->as<Key128>(), left_batch->num_rows);
+      return join_build32(ctx, b.cols[on[0]].values<int32_t>(), rp, mask.data ? mask.values<uint8_t>() : nullptr,
+                          b.num_rows);
     }
+    *keys_keep = pack(b, on, null_tag);
+    return join_build(ctx, (*keys_keep)->as<Key128>(), b.num_rows);
+  }
+  void ensure_table() {
+    if (!table) table = build_table(*left_batch, left_pred, on_left, 0x81, &left_keys);
+  }
+  // pairs (row of `b`, build row) of one probe batch against `t`
+  int64_t probe_table(JoinTable& t, const Batch& b, const ExprPtr& pred, const std::vector<int>& on, int null_tag,
+                      BufPtr* build_idx, BufPtr* probe_idx) {
+    if (k32) {
+      RowPred rp;
+      Column mask = side_mask(pred, b, on[0], &rp);
+      return join_probe32(ctx, t, b.cols[on[0]].values<int32_t>(), rp, mask.data ? mask.values<uint8_t>() : nullptr,
+                          b.num_rows, build_idx, probe_idx);
+    }
+    BufPtr pk = pack(b, on, null_tag);
+    return join_probe(ctx, t, pk->as<Key128>(), b.num_rows, build_idx, probe_idx);
   }
   struct S : Stream {
     HashJoinExec* op;
@@ -174,6 +193,8 @@ struct HashJoinExec : Op {
     ExprPtr pred;        // fused right-side FilterExec predicate (k32 path)
     BufPtr left_matched; // Left join: one byte per build row, set by every probe batch of this stream
     bool tail_done = false;
+    bool decided = false, swapped_done = false;
+    BatchPtr first, second;  // one batch of look-ahead on the probe side
 
     BatchPtr assemble(const Batch* r, const BufPtr& li, const BufPtr& ri, int64_t m, bool null_left, bool null_right) {
       Ctx* ctx = op->ctx;
@@ -204,9 +225,42 @@ struct HashJoinExec : Op {
       }
       return o;
     }
+    BatchPtr pull() {
+      if (first) {
+        BatchPtr b = first;
+        first = second;
+        second = nullptr;
+        return b;
+      }
+      return in->next();
+    }
     BatchPtr next() override {
       Ctx* ctx = op->ctx;
-      BatchPtr r = in->next();
+      if (!decided) {
+        decided = true;
+        while ((first = in->next()) && first->num_rows == 0) {}
+        if (first)
+          while ((second = in->next()) && second->num_rows == 0) {}
+        // Side selection at run time (inner joins): the reference always builds on the left (collect-left), which in a
+        // left-deep plan is the accumulated join result - Q5 joins millions of rows against the 25 nations and then
+        // against one region, every probe row walking a chain of 10^5 build rows.  When the whole right side is ONE
+        // batch far smaller than the left, the table is built over it and the collected left side probes: the same
+        // row set (order is unobservable), a table that fits L2 and no chains.
+        if (op->join_type == B2_JOIN_INNER && !op->table && first && !second && !getenv("B2_DISABLE_JOIN_SWAP") &&
+            first->num_rows * 4 <= op->left_batch->num_rows) {
+          swapped_done = true;
+          BatchPtr r = first;
+          first = nullptr;
+          BufPtr keep, bi, pi;
+          auto t = op->build_table(*r, pred, op->on_right, 0x82, &keep);
+          int64_t m = op->probe_table(*t, *op->left_batch, op->left_pred, op->on_left, 0x81, &bi, &pi);
+          op->last_path += "/build-right";
+          return assemble(r.get(), pi, bi, m, false, false);
+        }
+        op->ensure_table();
+      }
+      if (swapped_done) return nullptr;
+      BatchPtr r = pull();
       if (!r) {
         // Left join: build rows no probe batch of this stream matched, null-extended on the right (emitted once, at
         // the end of the stream; DataFusion@46161d2 emits them per probe batch, which repeats them - SURVEY A.3
@@ -224,16 +278,7 @@ struct HashJoinExec : Op {
         return nullptr;
       }
       BufPtr li, ri;
-      int64_t m;
-      if (op->k32) {
-        RowPred rp;
-        Column mask = op->side_mask(pred, *r, op->on_right[0], &rp);
-        m = join_probe32(ctx, *op->table, r->cols[op->on_right[0]].values<int32_t>(), rp,
-                         mask.data ? mask.values<uint8_t>() : nullptr, r->num_rows, &li, &ri);
-      } else {
-        BufPtr pk = op->pack(*r, op->on_right, 0x82);
-        m = join_probe(ctx, *op->table, pk->as<Key128>(), r->num_rows, &li, &ri);
-      }
+      int64_t m = op->probe_table(*op->table, *r, pred, op->on_right, 0x82, &li, &ri);
       if (op->join_type == B2_JOIN_LEFT && op->left_batch->num_rows) {
         if (!left_matched) left_matched = dev_alloc_zero(ctx, (size_t)op->left_batch->num_rows + 16);
         if (m) {
@@ -274,9 +319,10 @@ struct HashJoinExec : Op {
   // probe side's split drops, before the exchange, the rows whose destination cannot hold their key.  Collective:
   // every rank runs the same plan and takes the same branch.  Inner joins only (an outer join keeps unmatched rows).
   void offer_semi_filter() {
-    if (semi_offered || !k32 || !table || !ctx->comm || ctx->nranks < 2 || getenv("B2_DISABLE_SEMI_FILTER")) return;
+    if (semi_offered || !k32 || !ctx->comm || ctx->nranks < 2 || getenv("B2_DISABLE_SEMI_FILTER")) return;
     semi_offered = true;
     if (!partitioned || join_type != B2_JOIN_INNER || !children[1]->accepts_semi_filter(on_right[0])) return;
+    ensure_table();  // the filter is the Bloom filter of the left side's table: no side swapping for this join
     const int nr = ctx->nranks;
     std::vector<int64_t> words = allgather_counts(ctx, std::vector<int64_t>{(int64_t)table->bloom_words});
     int64_t stride = 0;

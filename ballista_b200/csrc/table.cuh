@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <type_traits>
+
 namespace b2 {
 
 // status word of an aggregate launch (read back by the host)
@@ -13,7 +15,43 @@ enum { AGG_OK = 0, AGG_ABORT_CARDINALITY = 1, AGG_KEY_TOO_WIDE = 2, AGG_TABLE_FU
        AGG_TOO_BIG = 5, AGG_NULL_KEY = 6 };
 
 typedef unsigned long long u64;
-typedef unsigned __int128 u128;
+
+// 128-bit unsigned integer as two explicit 64-bit words.  The compiler's own `unsigned __int128` is NOT used in device
+// code: nvcc 12.9 drops the carry into the high word in `((x & m) << 8) << (8 * off)` of the key-packing kernel (a
+// character at byte 7 of a string key came back as 0: scratch/cu/pack_test.cu reproduces it), so every shift here is
+// spelled out.
+struct u128 {
+  u64 lo, hi;
+  u128() = default;
+  template <class T, class = typename std::enable_if<std::is_integral<T>::value>::type>
+  __host__ __device__ constexpr u128(T v) : lo((u64)v), hi(0) {}
+  template <class T, class = typename std::enable_if<std::is_integral<T>::value>::type>
+  __host__ __device__ explicit constexpr operator T() const { return (T)lo; }
+};
+__host__ __device__ __forceinline__ constexpr u128 make_u128(u64 lo, u64 hi) {
+  u128 r(lo);
+  r.hi = hi;
+  return r;
+}
+__host__ __device__ __forceinline__ constexpr u128 operator|(u128 a, u128 b) { return make_u128(a.lo | b.lo, a.hi | b.hi); }
+__host__ __device__ __forceinline__ constexpr u128 operator&(u128 a, u128 b) { return make_u128(a.lo & b.lo, a.hi & b.hi); }
+__host__ __device__ __forceinline__ constexpr u128 operator~(u128 a) { return make_u128(~a.lo, ~a.hi); }
+__host__ __device__ __forceinline__ u128& operator|=(u128& a, u128 b) {
+  a.lo |= b.lo;
+  a.hi |= b.hi;
+  return a;
+}
+__host__ __device__ __forceinline__ constexpr bool operator==(u128 a, u128 b) { return a.lo == b.lo && a.hi == b.hi; }
+__host__ __device__ __forceinline__ constexpr bool operator!=(u128 a, u128 b) { return !(a == b); }
+__host__ __device__ __forceinline__ constexpr u128 operator<<(u128 a, int s) {
+  return s <= 0 ? a : s < 64 ? make_u128(a.lo << s, (a.hi << s) | (a.lo >> (64 - s))) : s < 128 ? make_u128(0, a.lo << (s - 64)) : make_u128(0, 0);
+}
+__host__ __device__ __forceinline__ constexpr u128 operator>>(u128 a, int s) {
+  return s <= 0 ? a : s < 64 ? make_u128((a.lo >> s) | (a.hi << (64 - s)), a.hi >> s) : s < 128 ? make_u128(a.hi >> (s - 64), 0) : make_u128(0, 0);
+}
+__host__ __device__ __forceinline__ constexpr u128 operator-(u128 a, u128 b) {
+  return make_u128(a.lo - b.lo, a.hi - b.hi - (a.lo < b.lo ? 1ull : 0ull));
+}
 
 // ---- packed group / join keys: 15 payload bytes, byte 15 always 0 so no key equals EMPTY ----
 struct Key128 {

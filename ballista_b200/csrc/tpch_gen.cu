@@ -112,6 +112,14 @@ static Column utf8_col(Ctx* ctx, int64_t n, int64_t chars) {
   return c;
 }
 
+__global__ void gen_supplier_kernel(int32_t* suppkey, int32_t* nationkey, int64_t r0, int64_t n) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    if (suppkey) suppkey[i] = b2spec::s_suppkey(r0 + i);
+    if (nationkey) nationkey[i] = b2spec::s_nationkey(r0 + i);
+  }
+}
+
 BatchPtr tpch_generate(Ctx* ctx, const std::string& table, double sf, int64_t row_begin, int64_t row_end,
                        const char* const* columns) {
   std::set<std::string> sel;
@@ -194,8 +202,47 @@ BatchPtr tpch_generate(Ctx* ctx, const std::string& table, double sf, int64_t ro
         seg->chars_len = total;
       }
     }
+  } else if (table == "supplier") {
+    if (row_end > b2spec::n_supplier(sf)) fail(B2_ERR_INVALID_ARG, "supplier row range beyond table");
+    b->cols.reserve(4);
+    int32_t *sk = nullptr, *nk = nullptr;
+    if (want(sel, "s_suppkey")) sk = (int32_t*)add("s_suppkey", fixed_col(ctx, B2_INT32, n))->data->ptr;
+    if (want(sel, "s_nationkey")) nk = (int32_t*)add("s_nationkey", fixed_col(ctx, B2_INT32, n))->data->ptr;
+    if (n) {
+      gen_supplier_kernel<<<grid, 256, 0, ctx->stream>>>(sk, nk, row_begin, n);
+      B2_LAUNCHED(ctx);
+    }
+  } else if (table == "nation" || table == "region") {
+    // dbgen's fixed tables (25 / 5 rows): assembled on the host, one upload per column
+    const bool nat = table == "nation";
+    if (row_end > (nat ? b2spec::N_NATION : b2spec::N_REGION)) fail(B2_ERR_INVALID_ARG, table + " row range beyond table");
+    std::vector<int32_t> key((size_t)n), region((size_t)n), off((size_t)n + 1, 0);
+    std::string chars;
+    for (int64_t i = 0; i < n; ++i) {
+      int id = (int)(row_begin + i);
+      key[(size_t)i] = id;
+      region[(size_t)i] = nat ? b2spec::nation_regionkey(id) : 0;
+      chars += nat ? b2spec::nation_name(id) : b2spec::region_name(id);
+      off[(size_t)i + 1] = (int32_t)chars.size();
+    }
+    auto put = [&](const char* name, int dtype, const void* src, size_t bytes) {
+      Column c = fixed_col(ctx, dtype, n);
+      if (bytes) B2_CUDA(cudaMemcpyAsync(c.data->ptr, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+      add(name, std::move(c));
+    };
+    b->cols.reserve(4);
+    if (want(sel, nat ? "n_nationkey" : "r_regionkey")) put(nat ? "n_nationkey" : "r_regionkey", B2_INT32, key.data(), (size_t)n * 4);
+    if (want(sel, nat ? "n_name" : "r_name")) {
+      Column c = utf8_col(ctx, n, (int64_t)chars.size());
+      B2_CUDA(cudaMemcpyAsync(c.data->ptr, off.data(), (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+      if (!chars.empty())
+        B2_CUDA(cudaMemcpyAsync(c.chars->ptr, chars.data(), chars.size(), cudaMemcpyHostToDevice, ctx->stream));
+      add(nat ? "n_name" : "r_name", std::move(c));
+    }
+    if (nat && want(sel, "n_regionkey")) put("n_regionkey", B2_INT32, region.data(), (size_t)n * 4);
+    B2_CUDA(cudaStreamSynchronize(ctx->stream));  // the host vectors go out of scope
   } else {
-    fail(B2_ERR_INVALID_ARG, "unknown TPC-H table '" + table + "' (lineitem | orders | customer)");
+    fail(B2_ERR_INVALID_ARG, "unknown TPC-H table '" + table + "' (lineitem | orders | customer | supplier | nation | region)");
   }
   return b;
 }
@@ -204,6 +251,9 @@ int64_t tpch_num_rows(const std::string& table, double sf) {
   if (table == "lineitem") return b2spec::n_lineitem(sf);
   if (table == "orders") return b2spec::n_orders(sf);
   if (table == "customer") return b2spec::n_customer(sf);
+  if (table == "supplier") return b2spec::n_supplier(sf);
+  if (table == "nation") return b2spec::N_NATION;
+  if (table == "region") return b2spec::N_REGION;
   return -1;
 }
 

@@ -23,7 +23,7 @@ constexpr uint64_t SEED = 42;
 // streams (one per generated attribute)
 enum Stream : uint64_t {
   S_O_CUSTKEY = 1, S_O_ORDERDATE, S_L_COUNTROT, S_L_PARTKEY, S_L_SUPPKEY, S_L_QUANTITY, S_L_DISCOUNT,
-  S_L_TAX, S_L_SHIPDELTA, S_L_COMMITDELTA, S_L_RECEIPTDELTA, S_L_RFLAG, S_C_MKTSEGMENT, S_C_NATIONKEY
+  S_L_TAX, S_L_SHIPDELTA, S_L_COMMITDELTA, S_L_RECEIPTDELTA, S_L_RFLAG, S_C_MKTSEGMENT, S_C_NATIONKEY, S_S_NATIONKEY
 };
 
 B2_HD uint64_t splitmix64(uint64_t x) {
@@ -46,6 +46,11 @@ B2_HD int64_t uniform(uint64_t stream, uint64_t idx, int64_t lo, int64_t hi) {
 B2_HD int64_t n_orders(double sf) { return (int64_t)(1500000.0 * sf + 0.5) & ~7ll; }  // multiple of 8
 B2_HD int64_t n_lineitem(double sf) { return 4 * n_orders(sf); }
 B2_HD int64_t n_customer(double sf) { return (int64_t)(150000.0 * sf + 0.5); }
+B2_HD int64_t n_supplier(double sf) {
+  int64_t n = (int64_t)(10000.0 * sf + 0.5);  // the range l_suppkey is drawn from (lineitem_row)
+  return n < 1 ? 1 : n;
+}
+constexpr int64_t N_NATION = 25, N_REGION = 5;
 
 // ---- orders ----
 B2_HD int32_t o_orderkey(int64_t i) { return (int32_t)(((i >> 3) << 5) + (i & 7) + 1); }
@@ -124,5 +129,24 @@ B2_HD const char* mktsegment_name(int id) {
   }
 }
 B2_HD int mktsegment_len(int id) { return id == 0 ? 10 : (id == 1 ? 8 : 9); }
+
+// ---- supplier / nation / region (TPC-H Q5: rust/benchmarks/tpch/queries/q5.sql; schemas main.rs:267-360) ----
+B2_HD int32_t s_suppkey(int64_t i) { return (int32_t)(i + 1); }
+B2_HD int32_t s_nationkey(int64_t i) { return (int32_t)uniform(S_S_NATIONKEY, (uint64_t)i, 0, 24); }
+// the 25 nations and 5 regions of the TPC-H specification (dbgen's fixed tables)
+B2_HD const char* nation_name(int id) {
+  const char* names[25] = {"ALGERIA", "ARGENTINA", "BRAZIL", "CANADA", "EGYPT", "ETHIOPIA", "FRANCE", "GERMANY", "INDIA",
+                           "INDONESIA", "IRAN", "IRAQ", "JAPAN", "JORDAN", "KENYA", "MOROCCO", "MOZAMBIQUE", "PERU",
+                           "CHINA", "ROMANIA", "SAUDI ARABIA", "VIETNAM", "RUSSIA", "UNITED KINGDOM", "UNITED STATES"};
+  return names[id];
+}
+B2_HD int nation_regionkey(int id) {
+  const int region[25] = {0, 1, 1, 1, 4, 0, 3, 3, 2, 2, 4, 4, 2, 4, 0, 0, 0, 1, 2, 3, 4, 2, 3, 3, 1};
+  return region[id];
+}
+B2_HD const char* region_name(int id) {
+  const char* names[5] = {"AFRICA", "AMERICA", "ASIA", "EUROPE", "MIDDLE EAST"};
+  return names[id];
+}
 
 }  // namespace b2spec

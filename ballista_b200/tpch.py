@@ -20,6 +20,13 @@ Q3_LINEITEM_COLUMNS = ["l_orderkey", "l_extendedprice", "l_discount", "l_shipdat
 Q3_ORDERS_COLUMNS = ["o_orderkey", "o_custkey", "o_orderdate", "o_shippriority"]
 Q3_CUSTOMER_COLUMNS = ["c_custkey", "c_mktsegment"]
 
+Q5_CUSTOMER_COLUMNS = ["c_custkey", "c_nationkey"]
+Q5_ORDERS_COLUMNS = ["o_orderkey", "o_custkey", "o_orderdate"]
+Q5_LINEITEM_COLUMNS = ["l_orderkey", "l_suppkey", "l_extendedprice", "l_discount"]
+Q5_SUPPLIER_COLUMNS = ["s_suppkey", "s_nationkey"]
+Q5_NATION_COLUMNS = ["n_nationkey", "n_name", "n_regionkey"]
+Q5_REGION_COLUMNS = ["r_regionkey", "r_name"]
+
 # algorithmic bytes per input row
 Q1_BYTES_PER_ROW = 46
 Q6_BYTES_PER_ROW = 28
@@ -170,6 +177,50 @@ def q3_partial(customer, orders, lineitem, **kw):
 def q3_final(partial_states, input_schema):
     return HashAggregateExec("Final", q3_groups(), q3_aggregates(), MergeExec(partial_states),
                              input_schema=input_schema)
+
+
+@functools.lru_cache(maxsize=16)
+def _q5_predicates(region, date_lo, date_hi):
+    return (col("r_name") == lit(region), (col("o_orderdate") >= date(date_lo)) & (col("o_orderdate") < date(date_hi)))
+
+
+@functools.lru_cache(maxsize=None)
+def q5_aggregates():
+    return [sum_(col("l_extendedprice") * (lit(1) - col("l_discount"))).alias("revenue")]
+
+
+def q5_join_tree(customer, orders, lineitem, supplier, nation, region, region_name="ASIA", date_lo="1994-01-01",
+                 date_hi="1995-01-01"):
+    """q5.sql as the reference's planner shapes it: comma joins in FROM order, left-deep, build = left,
+    single-table predicates pushed below the joins; `l_suppkey = s_suppkey AND c_nationkey = s_nationkey` is ONE join
+    with a two-column key."""
+    pr, po = _q5_predicates(region_name, date_lo, date_hi)
+    o = CoalesceBatchesExec(FilterExec(po, orders))
+    r = CoalesceBatchesExec(FilterExec(pr, region))
+    j1 = CoalesceBatchesExec(HashJoinExec(customer, o, [("c_custkey", "o_custkey")]))
+    j2 = CoalesceBatchesExec(HashJoinExec(j1, lineitem, [("o_orderkey", "l_orderkey")]))
+    j3 = CoalesceBatchesExec(HashJoinExec(j2, supplier, [("l_suppkey", "s_suppkey"), ("c_nationkey", "s_nationkey")]))
+    j4 = CoalesceBatchesExec(HashJoinExec(j3, nation, [("s_nationkey", "n_nationkey")]))
+    return CoalesceBatchesExec(HashJoinExec(j4, r, [("n_regionkey", "r_regionkey")]))
+
+
+def q5_partial(customer, orders, lineitem, supplier, nation, region, **kw):
+    return HashAggregateExec("Partial", [col("n_name")], q5_aggregates(),
+                             q5_join_tree(customer, orders, lineitem, supplier, nation, region, **kw))
+
+
+def q5_final(partial_states, input_schema):
+    return HashAggregateExec("Final", [col("n_name")], q5_aggregates(), MergeExec(partial_states),
+                             input_schema=input_schema)
+
+
+def q5_sorted(final):
+    """ORDER BY revenue DESC (q5.sql:24)."""
+    return SortExec([(col("revenue"), False)], final)
+
+
+Q5_TABLES = (("customer", Q5_CUSTOMER_COLUMNS), ("orders", Q5_ORDERS_COLUMNS), ("lineitem", Q5_LINEITEM_COLUMNS),
+             ("supplier", Q5_SUPPLIER_COLUMNS), ("nation", Q5_NATION_COLUMNS), ("region", Q5_REGION_COLUMNS))
 
 
 def q1_sorted(final):

@@ -252,10 +252,22 @@ int64_t oracle_gen_customer(double, int64_t r0, int64_t n, int32_t* custkey, int
   if (seg_off) seg_off[n] = (int32_t)pos;
   return pos;
 }
+void oracle_gen_supplier(double, int64_t r0, int64_t n, int32_t* suppkey, int32_t* nationkey) {
+  for (int64_t i = 0; i < n; ++i) {
+    if (suppkey) suppkey[i] = b2spec::s_suppkey(r0 + i);
+    if (nationkey) nationkey[i] = b2spec::s_nationkey(r0 + i);
+  }
+}
+const char* oracle_nation_name(int id) { return b2spec::nation_name(id); }
+int oracle_nation_regionkey(int id) { return b2spec::nation_regionkey(id); }
+const char* oracle_region_name(int id) { return b2spec::region_name(id); }
 int64_t oracle_tpch_num_rows(const char* table, double sf) {
   if (!strcmp(table, "lineitem")) return b2spec::n_lineitem(sf);
   if (!strcmp(table, "orders")) return b2spec::n_orders(sf);
   if (!strcmp(table, "customer")) return b2spec::n_customer(sf);
+  if (!strcmp(table, "supplier")) return b2spec::n_supplier(sf);
+  if (!strcmp(table, "nation")) return b2spec::N_NATION;
+  if (!strcmp(table, "region")) return b2spec::N_REGION;
   return -1;
 }
 

@@ -38,6 +38,9 @@ def lib():
         _LIB.oracle_agg_num_groups.restype = C.c_int64
         _LIB.oracle_hash_join.restype = C.c_int64
         _LIB.oracle_gen_customer.restype = C.c_int64
+        _LIB.oracle_nation_name.restype = C.c_char_p
+        _LIB.oracle_region_name.restype = C.c_char_p
+        _LIB.oracle_nation_regionkey.restype = C.c_int
         _LIB.oracle_tpch_num_rows.restype = C.c_int64
         _LIB.oracle_q6.restype = C.c_double
         _LIB.oracle_q1.restype = C.c_int
@@ -227,6 +230,25 @@ def gen_customer(sf, r0, n):
     return {"c_custkey": ck, "c_nationkey": nk, "c_mktsegment": Utf8(off, chr_[:total])}
 
 
+def gen_supplier(sf, r0, n):
+    sk, nk = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    lib().oracle_gen_supplier(C.c_double(sf), C.c_int64(r0), C.c_int64(n), _ptr(sk), _ptr(nk))
+    return {"s_suppkey": sk, "s_nationkey": nk}
+
+
+def gen_nation():
+    L = lib()
+    return {"n_nationkey": np.arange(25, dtype=np.int32),
+            "n_name": Utf8.from_list([L.oracle_nation_name(i).decode() for i in range(25)]),
+            "n_regionkey": np.array([L.oracle_nation_regionkey(i) for i in range(25)], dtype=np.int32)}
+
+
+def gen_region():
+    L = lib()
+    return {"r_regionkey": np.arange(5, dtype=np.int32),
+            "r_name": Utf8.from_list([L.oracle_region_name(i).decode() for i in range(5)])}
+
+
 def to_arrow(cols, names=None):
     """host columns -> pyarrow RecordBatch (zero-copy for numerics)."""
     import pyarrow as pa
@@ -327,3 +349,53 @@ def q3(sf, segment="BUILDING", cutoff=DATE_1995_03_15, threads=1, range_orders=1
             stats[k] = stats.get(k, 0) + v
     return {"l_orderkey": out[0][order], "o_orderdate": out[1][order], "o_shippriority": out[2][order],
             "revenue": out[3][order], "stats": stats}
+
+
+# ---- TPC-H Q5 (rust/benchmarks/tpch/queries/q5.sql): customer |x| orders |x| lineitem |x| supplier |x| nation |x|
+#      region, left-deep in FROM order with build = left, the two-column key l_suppkey = s_suppkey AND
+#      c_nationkey = s_nationkey, r_name = 'ASIA', o_orderdate in [1994-01-01, 1995-01-01), group by n_name ----
+def q5_range(sf, o_lo, o_hi, cust, supp, nation, region_keys, date_lo=DATE_1994_01_01, date_hi=DATE_1995_01_01):
+    """Q5 over the orders rows [o_lo, o_hi) and their lineitem rows; -> {n_name: revenue} of this range"""
+    o = gen_orders(sf, o_lo, o_hi - o_lo)
+    l = gen_lineitem(sf, 4 * o_lo, 4 * (o_hi - o_lo))
+    om = (o["o_orderdate"] >= date_lo) & (o["o_orderdate"] < date_hi)
+    of = {k: v[om] for k, v in o.items()}
+    if not om.any():
+        return {}
+    li1, ri1 = hash_join([cust["c_custkey"]], [of["o_custkey"]])                      # customer |x| orders
+    j1 = {"c_nationkey": cust["c_nationkey"][li1], "o_orderkey": of["o_orderkey"][ri1]}
+    li2, ri2 = hash_join([j1["o_orderkey"]], [l["l_orderkey"]])                        # ... |x| lineitem
+    j2 = {"c_nationkey": j1["c_nationkey"][li2], "l_suppkey": l["l_suppkey"][ri2],
+          "rev": l["l_extendedprice"][ri2] * (1.0 - l["l_discount"][ri2])}
+    if len(ri2) == 0:
+        return {}
+    li3, ri3 = hash_join([j2["l_suppkey"], j2["c_nationkey"]], [supp["s_suppkey"], supp["s_nationkey"]])  # ... |x| supplier
+    j3 = {"s_nationkey": supp["s_nationkey"][ri3], "rev": j2["rev"][li3]}
+    if len(ri3) == 0:
+        return {}
+    li4, ri4 = hash_join([j3["s_nationkey"]], [nation["n_nationkey"]])                 # ... |x| nation
+    j4 = {"n_regionkey": nation["n_regionkey"][ri4], "n_name_id": ri4, "rev": j3["rev"][li4]}
+    li5, ri5 = hash_join([j4["n_regionkey"]], [region_keys])                           # ... |x| region (r_name = 'ASIA')
+    if len(li5) == 0:
+        return {}
+    names = nation["n_name"].to_list()
+    ids, rev = j4["n_name_id"][li5], j4["rev"][li5]
+    rep, sums, _ = hash_aggregate([ids.astype(np.int32)], [rev])
+    return {names[int(ids[r])]: float(sums[g, 0]) for g, r in enumerate(rep)}
+
+
+def q5(sf, region="ASIA", threads=1, range_orders=1 << 21):
+    """-> {n_name: revenue}; one task per orders range on `threads` host threads"""
+    from concurrent.futures import ThreadPoolExecutor
+    nc, no, ns = tpch_num_rows("customer", sf), tpch_num_rows("orders", sf), tpch_num_rows("supplier", sf)
+    cust, supp, nation, reg = gen_customer(sf, 0, nc), gen_supplier(sf, 0, ns), gen_nation(), gen_region()
+    rk = np.ascontiguousarray(reg["r_regionkey"][reg["r_name"].equals_literal(region)])
+    step = max(8, min(range_orders, -(-no // max(threads, 1))) // 8 * 8)
+    ranges = [(a, min(a + step, no)) for a in range(0, no, step)]
+    with ThreadPoolExecutor(max_workers=max(threads, 1)) as ex:
+        parts = list(ex.map(lambda r: q5_range(sf, r[0], r[1], cust, supp, nation, rk), ranges))
+    out = {}
+    for p in parts:
+        for k, v in p.items():
+            out[k] = out.get(k, 0.0) + v
+    return out

@@ -392,3 +392,30 @@ def test_final_aggregate_rejects_overlong_utf8_key(ctx):
                             scan(ctx, [[states.rename_columns(["g", "s[sum]"])]]), input_schema=in_schema)
     with pytest.raises(NotImplementedOnGpu, match="packed-key budget"):
         fin.collect()
+
+
+def test_group_keys_of_eight_to_fourteen_characters(ctx):
+    """a character at byte 7 of a packed string key sits at the 64-bit word boundary of the 128-bit key (regression:
+    nvcc's __int128 lost it); through the unfused Partial, the small Final and the general Final"""
+    import os
+    from ballista_b200 import HashAggregateExec, MemoryExec, col, count, sum
+    names = ["INDONESIA", "UNITED KINGDOM", "ABCDEFGH", "ABCDEFGI", "X", "", "SAUDI ARABIA", "ABCDEFG"]
+    n = 4000
+    s = [names[i % len(names)] for i in range(n)]
+    b = rb(s=pa.array(s), v=np.arange(n, dtype=np.float64))
+    want = {}
+    for k, v in zip(s, range(n)):
+        c, t = want.get(k, (0, 0.0))
+        want[k] = (c + 1, t + v)
+    aggs = [sum(col("v")).alias("t"), count().alias("c")]
+    for env in ({}, {"B2_DISABLE_SPECULATION": "1"}):
+        os.environ.update(env)
+        try:
+            p = HashAggregateExec("Partial", [col("s")], aggs, scan(ctx, [[b.slice(0, 1500)], [b.slice(1500)]]))
+            states = [x for q in range(2) for x in p.collect_device(q)]
+            f = HashAggregateExec("Final", [col("s")], aggs, MemoryExec(ctx, p.schema(), [states]), input_schema=b.schema)
+            got = {r["s"]: (r["c"], r["t"]) for r in f.collect().to_pylist()}
+        finally:
+            for k in env:
+                del os.environ[k]
+        assert got == want, (env, f.last_path())

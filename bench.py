@@ -774,6 +774,55 @@ def run_other_configs(args, env):
     out["q3"] = q3_local(sf, f"q3_sf{sf:g}")
     if world == 1 and args.q3_sf > sf:
         out[f"q3_sf{args.q3_sf:g}"] = q3_local(args.q3_sf, f"q3_sf{args.q3_sf:g}")
+    # ---- Q5: six tables, five joins (one on a two-column key), group by n_name.  Orders / lineitem are row-range
+    # partitions of ONE database (one per GPU); customer, supplier, nation and region are replicated, as the reference's
+    # collect-left join reads its whole build side in every task.  An order's lines lie in its own partition, so every
+    # join is local and only the 5-row partial states cross NVLink (all-gather). ----
+    def q5_run(qsf, name):
+        no = nrows("orders", qsf)
+        o0, o1 = cluster.partition_rows(no, world, rank, align=8)
+        batches = []
+        for table, cols_ in tpch.Q5_TABLES:
+            if table == "orders":
+                batches.append(ctx.tpch(table, qsf, o0, o1, columns=cols_))
+            elif table == "lineitem":
+                batches.append(ctx.tpch(table, qsf, 4 * o0, 4 * o1, columns=cols_))
+            else:
+                batches.append(ctx.tpch(table, qsf, columns=cols_))
+        scans = [tpch.scan(ctx, [[b_]]) for b_ in batches]
+        partial = tpch.q5_partial(*scans)
+        query = tpch.TwoStage(ctx, partial, lambda s_: tpch.q5_final(s_, partial.children()[0].schema()), merge="allgather")
+
+        def q5():
+            for leaf_scan, batch in zip(scans, batches):  # the joins rebuild their tables in every step (see Q3)
+                leaf_scan.clear()
+                leaf_scan.add(0, batch)
+            return query.run()
+        ms, launches, tab, t = timeit(q5)
+        rows_all = sum(nrows(tb, qsf) for tb, _ in tpch.Q5_TABLES)
+        scan_bytes = sum(b_.num_bytes for b_ in batches)
+        res = {"workload": f"TPC-H Q5 over an SF{qsf:g} database: orders / lineitem in {world} row-range partition(s), "
+                           "customer / supplier / nation / region replicated", "ms_per_step": ms,
+               "step_ms": step_stats(t["per_step"]), "input_rows_per_s": rows_all / (ms / 1e3),
+               "scan_GB_per_s_per_gpu": scan_bytes / (ms / 1e3) / 1e9, "launches_per_step": launches,
+               "revenue": {r_["n_name"]: r_["revenue"] for r_ in tab.to_pylist()}}
+        if O:
+            mine = O.q5(qsf, threads=env.host_threads, orders_range=(o0, o1))
+            want = {}
+            for part_ in gather_objects(env, mine):
+                for k_, v_ in part_.items():
+                    want[k_] = want.get(k_, 0.0) + v_
+            got = res["revenue"]
+            keys_equal = sorted(got) == sorted(want)
+            err = max(abs(got[k_] - want[k_]) / abs(want[k_]) for k_ in want) if keys_equal and want else 0.0
+            res["parity"] = {"config": f"{name}_x{world}", "input_rows": int(rows_all), "groups": len(got),
+                             "keys_equal": bool(keys_equal), "counts_equal": bool(keys_equal), "max_rel_err": err,
+                             "tolerance": 1e-9, "ok": bool(keys_equal and err <= 1e-9),
+                             "checker": "oracle/ Q5 (five collect-left hash joins in FROM order + group-by) over the oracle's own host tables"}
+        return res
+    out["q5"] = q5_run(sf, f"q5_sf{sf:g}")
+    if args.q3_sf > sf:
+        out[f"q5_sf{args.q3_sf:g}"] = q5_run(args.q3_sf, f"q5_sf{args.q3_sf:g}")
     if world > 1:
         out.update(run_multi_gpu_configs(args, env, O, timeit))
     return out

@@ -181,6 +181,122 @@ int64_t oracle_hash_join(int64_t n_left, int n_keys, const KeyCol* lkeys, int64_
   return m;
 }
 
+// The same join, one pass: the pairs are kept inside a handle and fetched once their number is known (the two-call
+// protocol above joins twice).  Keys of fixed-width columns totalling <= 16 bytes - every TPC-H join - go through an
+// open-addressing table of (key -> first / last build row) with a `next` chain per build row, which is the same
+// structure (hash of the key -> build row indices in insertion order, probe rows in order) without a heap allocation
+// per key; anything else falls back to the byte-string map.
+struct JoinResult {
+  std::vector<int64_t> l, r;
+};
+static inline uint64_t mix64_(uint64_t x) {
+  x ^= x >> 33;
+  x *= 0xff51afd7ed558ccdull;
+  x ^= x >> 33;
+  x *= 0xc4ceb9fe1a85ec53ull;
+  x ^= x >> 33;
+  return x;
+}
+static int fixed_key_bytes(int n_keys, const KeyCol* keys) {
+  int total = 0;
+  for (int k = 0; k < n_keys; ++k) {
+    switch (keys[k].dtype) {
+      case T_INT32: case T_DATE32: total += 4; break;
+      case T_INT64: case T_UINT64: case T_FLOAT64: total += 8; break;
+      default: return -1;
+    }
+  }
+  return total;
+}
+static inline void fixed_key(int n_keys, const KeyCol* keys, int64_t row, uint64_t out[2]) {
+  unsigned char buf[16] = {0};
+  int off = 0;
+  for (int k = 0; k < n_keys; ++k) {
+    if (keys[k].dtype == T_INT32 || keys[k].dtype == T_DATE32) {
+      memcpy(buf + off, (const int32_t*)keys[k].data + row, 4);
+      off += 4;
+    } else {
+      memcpy(buf + off, (const int64_t*)keys[k].data + row, 8);
+      off += 8;
+    }
+  }
+  memcpy(out, buf, 16);
+}
+void* oracle_hash_join_run(int64_t n_left, int n_keys, const KeyCol* lkeys, int64_t n_right, const KeyCol* rkeys) {
+  auto* res = new JoinResult;
+  int kb = fixed_key_bytes(n_keys, lkeys);
+  if (kb < 0 || kb > 16 || fixed_key_bytes(n_keys, rkeys) != kb) {
+    std::unordered_map<std::string, std::vector<int64_t>> map;
+    std::string key;
+    for (int64_t r = 0; r < n_left; ++r) {
+      key.clear();
+      for (int k = 0; k < n_keys; ++k) append_key(key, lkeys[k], r);
+      map[key].push_back(r);
+    }
+    for (int64_t r = 0; r < n_right; ++r) {
+      key.clear();
+      for (int k = 0; k < n_keys; ++k) append_key(key, rkeys[k], r);
+      auto it = map.find(key);
+      if (it == map.end()) continue;
+      for (int64_t l : it->second) {
+        res->l.push_back(l);
+        res->r.push_back(r);
+      }
+    }
+    return res;
+  }
+  struct Slot {
+    uint64_t k0, k1;
+    int64_t first, last;
+  };
+  uint64_t cap = 16;
+  while (cap < 2 * (uint64_t)n_left + 16) cap <<= 1;
+  std::vector<Slot> slots(cap, Slot{0, 0, -1, -1});
+  std::vector<int64_t> next((size_t)n_left, -1);
+  uint64_t key[2];
+  for (int64_t r = 0; r < n_left; ++r) {
+    fixed_key(n_keys, lkeys, r, key);
+    uint64_t h = mix64_(key[0] ^ mix64_(key[1] + 0x9E3779B97F4A7C15ull)) & (cap - 1);
+    while (true) {
+      Slot& sl = slots[h];
+      if (sl.first < 0) {
+        sl = Slot{key[0], key[1], r, r};
+        break;
+      }
+      if (sl.k0 == key[0] && sl.k1 == key[1]) {
+        next[(size_t)sl.last] = r;  // insertion order
+        sl.last = r;
+        break;
+      }
+      h = (h + 1) & (cap - 1);
+    }
+  }
+  for (int64_t r = 0; r < n_right; ++r) {
+    fixed_key(n_keys, rkeys, r, key);
+    uint64_t h = mix64_(key[0] ^ mix64_(key[1] + 0x9E3779B97F4A7C15ull)) & (cap - 1);
+    while (true) {
+      const Slot& sl = slots[h];
+      if (sl.first < 0) break;
+      if (sl.k0 == key[0] && sl.k1 == key[1]) {
+        for (int64_t l = sl.first; l >= 0; l = next[(size_t)l]) {
+          res->l.push_back(l);
+          res->r.push_back(r);
+        }
+        break;
+      }
+      h = (h + 1) & (cap - 1);
+    }
+  }
+  return res;
+}
+int64_t oracle_join_size(void* h) { return (int64_t)((JoinResult*)h)->l.size(); }
+void oracle_join_fetch(void* h, int64_t* left_idx, int64_t* right_idx) {
+  auto* res = (JoinResult*)h;
+  std::copy(res->l.begin(), res->l.end(), left_idx);
+  std::copy(res->r.begin(), res->r.end(), right_idx);
+  delete res;
+}
+
 // A.4: destination of every row.  The reference hashes with ahash (seeds fixed); no consumer observes which
 // partition a key lands in, only that equal keys co-locate, so the oracle uses FNV-1a.
 void oracle_hash_partition(int64_t n, int n_keys, const KeyCol* keys, int n_out, int32_t* dest) {

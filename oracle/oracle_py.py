@@ -37,6 +37,8 @@ def lib():
         _LIB.oracle_agg_create.restype = C.c_void_p
         _LIB.oracle_agg_num_groups.restype = C.c_int64
         _LIB.oracle_hash_join.restype = C.c_int64
+        _LIB.oracle_hash_join_run.restype = C.c_void_p
+        _LIB.oracle_join_size.restype = C.c_int64
         _LIB.oracle_gen_customer.restype = C.c_int64
         _LIB.oracle_nation_name.restype = C.c_char_p
         _LIB.oracle_region_name.restype = C.c_char_p
@@ -143,9 +145,10 @@ def hash_join(left_keys, right_keys):
     keep = []
     nl, nr = len(left_keys[0]), len(right_keys[0])
     lk, rk = _keycols(left_keys, keep), _keycols(right_keys, keep)
-    m = L.oracle_hash_join(C.c_int64(nl), len(left_keys), lk, C.c_int64(nr), rk, None, None, C.c_int64(0))
+    h = C.c_void_p(L.oracle_hash_join_run(C.c_int64(nl), len(left_keys), lk, C.c_int64(nr), rk))
+    m = L.oracle_join_size(h)
     li, ri = np.zeros(m, dtype=np.int64), np.zeros(m, dtype=np.int64)
-    L.oracle_hash_join(C.c_int64(nl), len(left_keys), lk, C.c_int64(nr), rk, _ptr(li), _ptr(ri), C.c_int64(m))
+    L.oracle_join_fetch(h, _ptr(li), _ptr(ri))
     return li, ri
 
 
@@ -384,14 +387,16 @@ def q5_range(sf, o_lo, o_hi, cust, supp, nation, region_keys, date_lo=DATE_1994_
     return {names[int(ids[r])]: float(sums[g, 0]) for g, r in enumerate(rep)}
 
 
-def q5(sf, region="ASIA", threads=1, range_orders=1 << 21):
-    """-> {n_name: revenue}; one task per orders range on `threads` host threads"""
+def q5(sf, region="ASIA", threads=1, range_orders=1 << 21, orders_range=None):
+    """-> {n_name: revenue}; one task per orders range on `threads` host threads.  `orders_range` = (lo, hi) restricts
+    the query to those orders rows and their lineitem rows (one rank's partition; partial sums add up over ranks)."""
     from concurrent.futures import ThreadPoolExecutor
     nc, no, ns = tpch_num_rows("customer", sf), tpch_num_rows("orders", sf), tpch_num_rows("supplier", sf)
     cust, supp, nation, reg = gen_customer(sf, 0, nc), gen_supplier(sf, 0, ns), gen_nation(), gen_region()
     rk = np.ascontiguousarray(reg["r_regionkey"][reg["r_name"].equals_literal(region)])
-    step = max(8, min(range_orders, -(-no // max(threads, 1))) // 8 * 8)
-    ranges = [(a, min(a + step, no)) for a in range(0, no, step)]
+    o_lo, o_hi = orders_range if orders_range is not None else (0, no)
+    step = max(8, min(range_orders, -(-(o_hi - o_lo) // max(threads, 1))) // 8 * 8)
+    ranges = [(a, min(a + step, o_hi)) for a in range(o_lo, o_hi, step)]
     with ThreadPoolExecutor(max_workers=max(threads, 1)) as ex:
         parts = list(ex.map(lambda r: q5_range(sf, r[0], r[1], cust, supp, nation, rk), ranges))
     out = {}

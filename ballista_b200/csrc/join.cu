@@ -327,8 +327,9 @@ constexpr int JP_THREADS = SCAN_THREADS;  // block_exclusive_scan is written for
 constexpr int JP_ITEMS = 8;
 constexpr int JP_TILE = JP_THREADS * JP_ITEMS;
 
-// predicate over the JP_ITEMS consecutive rows of one thread, 128-bit loads (r0 is a multiple of 8)
-__device__ __forceinline__ void row_pred_vec(const RowPred& p, int64_t r0, bool* pass) {
+// predicate over the JP_ITEMS consecutive rows of one thread as a BIT MASK (bit j = row r0 + j passes), 128-bit loads
+// (r0 is a multiple of 8): three instructions per Int32 row (subtract, unsigned compare, select into the mask)
+__device__ __forceinline__ unsigned row_pred_bits(const RowPred& p, int64_t r0, unsigned pm) {
   for (int t = 0; t < p.n; ++t) {
     if (p.is_f64[t]) {
       const double* c = static_cast<const double*>(p.col[t]) + r0;
@@ -336,37 +337,41 @@ __device__ __forceinline__ void row_pred_vec(const RowPred& p, int64_t r0, bool*
 #pragma unroll
       for (int j = 0; j < JP_ITEMS; j += 2) {
         double2 v = ld_stream_f64x2(c + j);
-        pass[j] = pass[j] && in_range_f64(v.x, lo, hi);
-        pass[j + 1] = pass[j + 1] && in_range_f64(v.y, lo, hi);
+        if (!in_range_f64(v.x, lo, hi)) pm &= ~(1u << j);
+        if (!in_range_f64(v.y, lo, hi)) pm &= ~(2u << j);
       }
     } else {
       const int32_t* c = static_cast<const int32_t*>(p.col[t]) + r0;
       const int lo = p.ilo[t];
       const unsigned w = p.iwidth[t];
-#pragma unroll
-      for (int j = 0; j < JP_ITEMS; j += 4) {
-        int4 v = ld_stream_i32x4(c + j);
-        pass[j] = pass[j] && in_range_i32(v.x, lo, w);
-        pass[j + 1] = pass[j + 1] && in_range_i32(v.y, lo, w);
-        pass[j + 2] = pass[j + 2] && in_range_i32(v.z, lo, w);
-        pass[j + 3] = pass[j + 3] && in_range_i32(v.w, lo, w);
-      }
+      int4 v0 = ld_stream_i32x4(c), v1 = ld_stream_i32x4(c + 4);
+      if (!in_range_i32(v0.x, lo, w)) pm &= ~1u;
+      if (!in_range_i32(v0.y, lo, w)) pm &= ~2u;
+      if (!in_range_i32(v0.z, lo, w)) pm &= ~4u;
+      if (!in_range_i32(v0.w, lo, w)) pm &= ~8u;
+      if (!in_range_i32(v1.x, lo, w)) pm &= ~16u;
+      if (!in_range_i32(v1.y, lo, w)) pm &= ~32u;
+      if (!in_range_i32(v1.z, lo, w)) pm &= ~64u;
+      if (!in_range_i32(v1.w, lo, w)) pm &= ~128u;
     }
   }
+  return pm;
 }
 
 // Probe-side kernel: filter (inline predicate and / or mask) -> Bloom test -> table lookup -> (build_row,
 // probe_row) pairs in PROBE ORDER (the reference's output order).  The unit of work is a WARP TILE of JP_WTILE = 256
 // consecutive rows and warps never synchronise with each other:
-//   (1) every lane tests its 8 consecutive rows against the predicate (128-bit loads) and keeps the rows that need a
-//       lookup: a probe side clustered on the key (lineitem: ~4 rows per order) repeats keys in consecutive rows, so a
-//       passing row whose predecessor passed with the same key joins that row's RUN instead of being looked up;
+//   (1) every lane tests its 8 consecutive rows against the predicate (128-bit loads) into an 8-bit pass mask.  A probe
+//       side clustered on the key (lineitem: ~4 rows per order) repeats keys in consecutive rows, so a passing row
+//       whose predecessor passed with the same key CONTINUES that row's run instead of being looked up: a second 8-bit
+//       mask; run heads = pass & ~continues.  Both masks stay in shared memory for step (3b);
 //   (2) the run heads are compacted, in row order, into the warp's slice of shared memory (one shuffle scan);
 //   (3) the warp walks the compacted heads 32 at a time: Bloom word, and only on a Bloom hit the table bucket; the
-//       matches of a chunk are placed by a second shuffle scan and each lane writes its run.
+//       hits of a chunk are compacted in place by ballot, and the output of the hits (run length from the owner lane's
+//       masks: the zeros of `continues` after the head's bit) is placed by a second shuffle scan.
 // Only the rows that survive a stage pay for the next one: the hash / Bloom arithmetic runs over the compacted
-// heads (13% of lineitem's rows in Q3), the bucket walk over the Bloom hits (~1%).  Three modes, none of which
-// probes a row twice on the primary-key path:
+// heads (13% of lineitem's rows in Q3), the bucket walk over the Bloom hits (~1%), the run length is computed for
+// hits only.  Three modes, none of which probes a row twice on the primary-key path:
 //   PROBE_STAGE  : pairs of warp tile t are written, compacted, at [t * JP_WTILE, ...) of staging buffers (a tile has
 //                  at most JP_WTILE matches when build keys are unique) and tile_cnt[t] = match count; a scan +
 //                  `join_compact_kernel` then move each tile's run to its final offset.
@@ -374,53 +379,77 @@ __device__ __forceinline__ void row_pred_vec(const RowPred& p, int64_t r0, bool*
 //   PROBE_WRITE  : pairs go straight to tile_cnt[t] (already scanned to offsets) + offset within tile.
 enum { PROBE_STAGE = 0, PROBE_COUNT = 1, PROBE_WRITE = 2 };
 constexpr int JP_WTILE = 32 * JP_ITEMS;
-template <int MODE, bool DUPS>
+// PRED: 0 = no inline predicate, 1 = exactly one Int32 / Date32 range term (every TPC-H date filter: its column pointer
+// and bounds live in registers across the tile loop), 2 = the general RowPred loop
+template <int MODE, bool DUPS, int PRED>
 __global__ void __launch_bounds__(JP_THREADS, 5)
-    join_probe32_kernel(const int32_t* __restrict__ key, RowPred pred, const uint8_t* __restrict__ mask, int64_t n,
-                        bool vec, const u64* __restrict__ slots, u64 bmask, const uint32_t* __restrict__ bloom,
-                        uint32_t wmask, const uint32_t* __restrict__ next, uint32_t* __restrict__ left_idx,
-                        uint32_t* __restrict__ right_idx, int64_t* tile_cnt) {
-  // run heads of the warp's tile in row order: key | (row within the tile | (run length - 1) << 8) << 32; rewritten in
-  // place by the hits of step (3): build row | the same info word
+    join_probe32_kernel(const int32_t* __restrict__ key, const __grid_constant__ RowPred pred,
+                        const uint8_t* __restrict__ mask, int64_t n, bool vec, const u64* __restrict__ slots, u64 bmask,
+                        const uint32_t* __restrict__ bloom, uint32_t wmask, const uint32_t* __restrict__ next,
+                        uint32_t* __restrict__ left_idx, uint32_t* __restrict__ right_idx, int64_t* tile_cnt) {
+  // run heads of the warp's tile in row order: key | (row within the tile) << 32; rewritten in place by the hits of
+  // step (3a): build row | the same position word
   __shared__ u64 s_ent[JP_TILE];
+  __shared__ unsigned s_bits[JP_THREADS];  // per lane: pass mask | continues mask << 8
   const int lane = threadIdx.x & 31;
   u64* went = s_ent + (threadIdx.x >> 5) * JP_WTILE;
+  unsigned* wbits = s_bits + (threadIdx.x & ~31);
   const int64_t n_tiles = (n + JP_WTILE - 1) / JP_WTILE;
   const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int32_t* const p1_col = PRED == 1 ? static_cast<const int32_t*>(pred.col[0]) : nullptr;
+  const int p1_lo = PRED == 1 ? pred.ilo[0] : 0;
+  const unsigned p1_w = PRED == 1 ? pred.iwidth[0] : 0u;
   for (int64_t tile = warp0; tile < n_tiles; tile += n_warps) {
     const int64_t r0 = tile * JP_WTILE + (int64_t)lane * JP_ITEMS;
     uint32_t k[JP_ITEMS];
-    bool pass[JP_ITEMS];
+    unsigned pm;  // bit j: row r0 + j takes part in the join
     if (vec && r0 + JP_ITEMS <= n) {
-      int4 v0 = ld_stream_i32x4(key + r0), v1 = ld_stream_i32x4(key + r0 + 4);
+      const int4 v0 = ld_stream_i32x4(key + r0), v1 = ld_stream_i32x4(key + r0 + 4);
+      int4 d0 = make_int4(0, 0, 0, 0), d1 = d0;
+      if (PRED == 1) {  // requested together with the keys: one round trip to HBM per tile
+        d0 = ld_stream_i32x4(p1_col + r0);
+        d1 = ld_stream_i32x4(p1_col + r0 + 4);
+      }
       k[0] = v0.x; k[1] = v0.y; k[2] = v0.z; k[3] = v0.w;
       k[4] = v1.x; k[5] = v1.y; k[6] = v1.z; k[7] = v1.w;
-      u64 m = mask ? __ldg(reinterpret_cast<const u64*>(mask + r0)) : 0x0101010101010101ull;
+      pm = 0xFFu;
+      if (mask) {
+        const u64 m = __ldg(reinterpret_cast<const u64*>(mask + r0));
+        pm = 0;
 #pragma unroll
-      for (int j = 0; j < JP_ITEMS; ++j) pass[j] = ((m >> (8 * j)) & 0xFFull) != 0;
-      row_pred_vec(pred, r0, pass);
+        for (int j = 0; j < JP_ITEMS; ++j) pm |= (((m >> (8 * j)) & 0xFFull) != 0 ? 1u : 0u) << j;
+      }
+      if (PRED == 1) {
+        if (!in_range_i32(d0.x, p1_lo, p1_w)) pm &= ~1u;
+        if (!in_range_i32(d0.y, p1_lo, p1_w)) pm &= ~2u;
+        if (!in_range_i32(d0.z, p1_lo, p1_w)) pm &= ~4u;
+        if (!in_range_i32(d0.w, p1_lo, p1_w)) pm &= ~8u;
+        if (!in_range_i32(d1.x, p1_lo, p1_w)) pm &= ~16u;
+        if (!in_range_i32(d1.y, p1_lo, p1_w)) pm &= ~32u;
+        if (!in_range_i32(d1.z, p1_lo, p1_w)) pm &= ~64u;
+        if (!in_range_i32(d1.w, p1_lo, p1_w)) pm &= ~128u;
+      } else if (PRED == 2) {
+        pm = row_pred_bits(pred, r0, pm);
+      }
     } else {
+      pm = 0;
 #pragma unroll
       for (int j = 0; j < JP_ITEMS; ++j) {
         bool in = r0 + j < n;
         k[j] = in ? (uint32_t)key[r0 + j] : 0u;
-        pass[j] = in && (!mask || mask[r0 + j]) && row_pred(pred, r0 + j);
+        if (in && (!mask || mask[r0 + j]) && row_pred(pred, r0 + j)) pm |= 1u << j;
       }
     }
-    // run heads and run lengths within the lane's 8 rows (runs do not continue across lanes: the first row of a lane
+    // bit j of `same`: row j repeats the key of row j - 1 (runs do not continue across lanes: the first row of a lane
     // is always a head, which costs one extra lookup per lane at most)
-    bool head[JP_ITEMS];
-    int len[JP_ITEMS];
-    head[0] = pass[0];
+    unsigned same = 0;
 #pragma unroll
-    for (int j = 1; j < JP_ITEMS; ++j) head[j] = pass[j] && !(pass[j - 1] && k[j] == k[j - 1]);
-    len[JP_ITEMS - 1] = 1;
-#pragma unroll
-    for (int j = JP_ITEMS - 2; j >= 0; --j) len[j] = (pass[j + 1] && !head[j + 1]) ? len[j + 1] + 1 : 1;
-    int nh = 0;
-#pragma unroll
-    for (int j = 0; j < JP_ITEMS; ++j) nh += head[j];
+    for (int j = 1; j < JP_ITEMS; ++j) same |= (k[j] == k[j - 1] ? 1u : 0u) << j;
+    const unsigned cont = pm & (pm << 1) & same;
+    const unsigned heads = pm & ~cont;
+    wbits[lane] = pm | (cont << 8);
+    const int nh = __popc(heads);
     int incl = nh;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -431,7 +460,7 @@ __global__ void __launch_bounds__(JP_THREADS, 5)
     int off = incl - nh;
 #pragma unroll
     for (int j = 0; j < JP_ITEMS; ++j)
-      if (head[j]) went[off++] = (u64)k[j] | ((u64)(uint32_t)((lane * JP_ITEMS + j) | ((len[j] - 1) << 8)) << 32);
+      if ((heads >> j) & 1u) went[off++] = (u64)k[j] | ((u64)(uint32_t)(lane * JP_ITEMS + j) << 32);
     __syncwarp();
     // (3a) Bloom word, then the bucket, for 32 heads at a time; the hits are compacted in place, in row order
     int n_hits = 0;
@@ -467,8 +496,10 @@ __global__ void __launch_bounds__(JP_THREADS, 5)
     for (int c0 = 0; c0 < n_hits; c0 += 32) {
       const bool active = c0 + lane < n_hits;
       const u64 e = active ? went[c0 + lane] : 0ull;
-      const uint32_t hd = (uint32_t)e, info = (uint32_t)(e >> 32);
-      const int run = (int)(info >> 8) + 1;
+      const uint32_t hd = (uint32_t)e, pos = (uint32_t)(e >> 32);
+      // run length: 1 + the rows after the head that continue its run (consecutive ones of the owner lane's mask)
+      const unsigned after = (wbits[pos >> 3] >> (8 + (pos & 7u) + 1));
+      const int run = active ? __ffs((int)~after) : 0;
       int cnt = 0;
       if (active) {
         if (DUPS) {
@@ -488,7 +519,7 @@ __global__ void __launch_bounds__(JP_THREADS, 5)
       const int chunk_total = __shfl_sync(0xffffffffu, inc2, 31);
       if (MODE != PROBE_COUNT && active) {
         int64_t o = base + done + (inc2 - cnt);
-        const uint32_t row = (uint32_t)(tile * JP_WTILE + (info & 0xFFu));
+        const uint32_t row = (uint32_t)(tile * JP_WTILE + pos);
         for (int i = 0; i < run; ++i) {  // probe-row major, chain order within a row
           uint32_t r = hd;
           do {
@@ -503,7 +534,7 @@ __global__ void __launch_bounds__(JP_THREADS, 5)
       done += chunk_total;
     }
     if (MODE != PROBE_WRITE && lane == 0) tile_cnt[tile] = done;
-    __syncwarp();  // the warp's slice is rewritten by its next tile
+    __syncwarp();  // the warp's slices are rewritten by its next tile
   }
 }
 
@@ -544,38 +575,45 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
   // persistent grid = exactly the co-resident CTAs, so the static tile striding has no ragged second wave
   static int per_sm = 0;
   if (!per_sm) {
-    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, join_probe32_kernel<PROBE_STAGE, false>, JP_THREADS, 0));
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, join_probe32_kernel<PROBE_STAGE, false, 2>, JP_THREADS, 0));
     if (per_sm < 1) per_sm = 1;
   }
+  const int pk = pred.n == 0 ? 0 : (pred.n == 1 && !pred.is_f64[0] ? 1 : 2);
+  auto launch = [&](auto mode, auto dups, uint32_t* li, uint32_t* ri, int grid_) {
+    constexpr int M = decltype(mode)::value;
+    constexpr bool D = decltype(dups)::value;
+    auto go = [&](auto kernel) {
+      kernel<<<grid_, JP_THREADS, 0, ctx->stream>>>(key, pred, mask, n, vec, t.slots->as<u64>(), t.cap / BUCKET - 1,
+                                                  t.bloom->as<uint32_t>(), (uint32_t)(t.bloom_words - 1),
+                                                  t.next->as<uint32_t>(), li, ri, tile_cnt);
+    };
+    if (pk == 0) go(join_probe32_kernel<M, D, 0>);
+    else if (pk == 1) go(join_probe32_kernel<M, D, 1>);
+    else go(join_probe32_kernel<M, D, 2>);
+    B2_LAUNCHED(ctx);
+  };
+  using std::integral_constant;
   int grid = grid_for(ctx, per_sm, n, JP_TILE);
   const u64* slots = t.slots->as<u64>();
   const uint32_t* next = t.next->as<uint32_t>();
   const uint32_t* bloom = t.bloom->as<uint32_t>();
   const uint32_t wmask = (uint32_t)(t.bloom_words - 1);
   if (t.dups_known && t.has_dups) {
-    join_probe32_kernel<PROBE_COUNT, true><<<grid, JP_THREADS, 0, ctx->stream>>>(key, pred, mask, n, vec, slots,
-                                                                               t.cap / BUCKET - 1, bloom, wmask, next, nullptr, nullptr, tile_cnt);
-    B2_LAUNCHED(ctx);
+    launch(integral_constant<int, PROBE_COUNT>{}, std::true_type{}, nullptr, nullptr, grid);
     scan_i64(ctx, tile_cnt, n_tiles);
     B2_READBACK(ctx, &total, tile_cnt + n_tiles, 8);
     if (total >= (int64_t)NIL) fail(B2_ERR_NOT_IMPLEMENTED, "join output beyond 2^32-2 rows in one batch");
     *left_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
     *right_idx = dev_alloc(ctx, (size_t)(total + 1) * 4);
-    if (total) {
-      join_probe32_kernel<PROBE_WRITE, true><<<grid, JP_THREADS, 0, ctx->stream>>>(
-          key, pred, mask, n, vec, slots, t.cap / BUCKET - 1, bloom, wmask, next, (*left_idx)->as<uint32_t>(),
-          (*right_idx)->as<uint32_t>(), tile_cnt);
-      B2_LAUNCHED(ctx);
-    }
+    if (total)
+      launch(integral_constant<int, PROBE_WRITE>{}, std::true_type{}, (*left_idx)->as<uint32_t>(),
+             (*right_idx)->as<uint32_t>(), grid);
     return total;
   }
   // primary-key build: one probe pass into tile-local staging runs, then scan + compaction of the runs
   auto stage_l = dev_alloc(ctx, (size_t)n_tiles * JP_WTILE * 4);
   auto stage_r = dev_alloc(ctx, (size_t)n_tiles * JP_WTILE * 4);
-  join_probe32_kernel<PROBE_STAGE, false><<<grid, JP_THREADS, 0, ctx->stream>>>(
-      key, pred, mask, n, vec, slots, t.cap / BUCKET - 1, bloom, wmask, next, stage_l->as<uint32_t>(),
-      stage_r->as<uint32_t>(), tile_cnt);
-  B2_LAUNCHED(ctx);
+  launch(integral_constant<int, PROBE_STAGE>{}, std::false_type{}, stage_l->as<uint32_t>(), stage_r->as<uint32_t>(), grid);
   scan_i64(ctx, tile_cnt, n_tiles);
   if (!t.dups_known) {
     int f = 0;

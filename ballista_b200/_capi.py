@@ -114,6 +114,7 @@ def lib():
         "b2_csv_decode": (i32, [vp, P(ArrowSchema), P(C.c_int), i32, C.c_char, i32, C.c_char_p, C.c_size_t, P(vp)]),
         "b2_plan_from_proto": (i32, [vp, C.c_char_p, C.c_size_t, P(vp), i32, P(vp)]),
         "b2_plan_proto_describe": (i32, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, P(i32)]),
+        "b2_jit_compile_check": (i32, [C.c_char_p, P(C.c_size_t)]),
         "b2_sort_create": (i32, [vp, vp, P(Expr), P(C.c_int), P(C.c_int), i32, P(vp)]),
         "b2_limit_create": (i32, [vp, vp, C.c_int64, i32, P(vp)]),
         "b2_hash_aggregate_create": (i32, [vp, vp, i32, P(Expr), i32, P(Agg), i32, P(ArrowSchema), P(vp)]),

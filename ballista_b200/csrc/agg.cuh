@@ -53,7 +53,7 @@ template <class Pred, class Keys, class Accs> struct FusedSrc {
   struct Rows {
     fx::Row r[ROWS_PER_THREAD];
   };
-  static std::string sig() { return "p:" + Pred::sig() + "|k:" + KT::sig() + "|a:" + AT::sig(); }
+  B2_SIG(return "p:" + Pred::sig() + "|k:" + KT::sig() + "|a:" + AT::sig();)
 
   // all global loads of a 4-row group are issued before any use (vector loads when the group is full)
   __device__ __forceinline__ static void load(const Params& p, int64_t r0, int64_t n, Rows& rows) {

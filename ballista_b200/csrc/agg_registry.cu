@@ -9,6 +9,7 @@
 #include "agg.h"
 #include "agg_kernels.cuh"
 #include "agg_tma.cuh"
+#include "jit.h"
 
 namespace b2 {
 
@@ -19,15 +20,15 @@ static int align_up(int x, int a) { return (x + a - 1) / a * a; }
 
 // shared-memory ring layout of agg_tma_kernel for one bound source; false when the TMA path cannot be used
 // (a column pointer that is not 16-byte aligned, e.g. a sliced view, or no room for two stages)
-template <class S> static bool build_tma_layout(const FusedParams& p, size_t static_smem, TmaLayout* lay) {
+static bool build_tma_layout_rt(const FusedParams& p, int nf, int ni, int ns, size_t static_smem, TmaLayout* lay) {
   memset(lay, 0, sizeof *lay);
   auto aligned = [](const void* q) { return ((uintptr_t)q & 15u) == 0; };
-  for (int c = 0; c < S::NF; ++c)
+  for (int c = 0; c < nf; ++c)
     if (!aligned(p.f[c])) return false;
-  for (int c = 0; c < S::NI; ++c)
+  for (int c = 0; c < ni; ++c)
     if (!aligned(p.i[c])) return false;
-  int off = TmaStage<S>::SC_OFF;
-  for (int c = 0; c < S::NS; ++c) {
+  int off = nf * TMA_TILE * 8 + ni * TMA_TILE * 4 + ns * TMA_SO_BYTES;  // == TmaStage<S>::SC_OFF
+  for (int c = 0; c < ns; ++c) {
     if (!aligned(p.soff[c]) || !aligned(p.schr[c])) return false;
     int cap = (int)(p.savg[c] * 1.5f * TMA_TILE) + 64;
     if (cap < 256) cap = 256;
@@ -39,11 +40,76 @@ template <class S> static bool build_tma_layout(const FusedParams& p, size_t sta
   }
   lay->stage_bytes = align_up(off > 0 ? off : 128, 128);
   int budget = 232448 - (int)static_smem - 256;
-  int ns = budget / lay->stage_bytes;
-  if (const char* e = getenv("B2_TMA_STAGES")) ns = std::min(ns, atoi(e));
-  if (ns > TMA_MAX_STAGES) ns = TMA_MAX_STAGES;
-  lay->n_stages = ns;
-  return ns >= 2;
+  int stages = budget / lay->stage_bytes;
+  if (const char* e = getenv("B2_TMA_STAGES")) stages = std::min(stages, atoi(e));
+  if (stages > TMA_MAX_STAGES) stages = TMA_MAX_STAGES;
+  lay->n_stages = stages;
+  return stages >= 2;
+}
+template <class S> static bool build_tma_layout(const FusedParams& p, size_t static_smem, TmaLayout* lay) {
+  static_assert(TmaStage<S>::SC_OFF == S::NF * TMA_TILE * 8 + S::NI * TMA_TILE * 4 + S::NS * TMA_SO_BYTES, "stage layout");
+  return build_tma_layout_rt(p, S::NF, S::NI, S::NS, static_smem, lay);
+}
+
+// launchers of a run-time compiled shape (jit.cu): the same four kernels make_launch<S> binds for a registry shape
+static AggLaunch make_launch_jit(Ctx* ctx, const FusedParams& prm, std::shared_ptr<JitKernels> jk, int nf, int ni, int ns,
+                                 int nacc, bool keyed) {
+  AggLaunch l;
+  l.na = nacc;
+  l.nc = 1;
+  l.keyed = keyed;
+  l.small = [ctx, prm, jk](int64_t n, TableRef tbl, int* status) {
+    int64_t tiles = (n + TILE_ROWS - 1) / TILE_ROWS;
+    int64_t cap = (int64_t)jk->per_sm_small * ctx->sm_count;
+    FusedParams p = prm;
+    void* args[] = {&p, &n, &tbl, &status};
+    ctx->prof_begin();
+    jit_launch(jk->small, (int)(tiles < cap ? tiles : cap), AGG_THREADS, 0, ctx->stream, args);
+    ctx->prof_end();
+    ctx->launches++;
+  };
+  l.global = [ctx, prm, jk](int64_t rb, int64_t re, int64_t n, TableRef tbl, int* status) {
+    int64_t tiles = (re - rb + TILE_ROWS - 1) / TILE_ROWS;
+    int64_t cap = (int64_t)jk->per_sm_global * ctx->sm_count;
+    FusedParams p = prm;
+    void* args[] = {&p, &rb, &re, &n, &tbl, &status};
+    ctx->prof_begin();
+    jit_launch(jk->global, (int)(tiles < cap ? tiles : cap), AGG_THREADS, 0, ctx->stream, args);
+    ctx->prof_end();
+    ctx->launches++;
+  };
+  auto tma = [&](void* fn, int static_smem, std::function<void(int64_t, TableRef, int*)>* out) {
+    TmaLayout lay;
+    if (!fn || !build_tma_layout_rt(prm, nf, ni, ns, (size_t)static_smem, &lay)) return false;
+    *out = [ctx, prm, lay, fn, jk](int64_t n, TableRef tbl, int* status) {
+      int64_t tiles = (n + TMA_TILE - 1) / TMA_TILE;
+      int grid = (int)(tiles < ctx->sm_count ? tiles : ctx->sm_count);
+      FusedParams p = prm;
+      TmaLayout ly = lay;
+      void* args[] = {&p, &ly, &n, &tbl, &status};
+      ctx->prof_begin();
+      jit_launch(fn, grid, TMA_THREADS, (size_t)ly.n_stages * ly.stage_bytes, ctx->stream, args);
+      ctx->prof_end();
+      ctx->launches++;
+    };
+    return true;
+  };
+  if (!getenv("B2_DISABLE_TMA")) {
+    std::function<void(int64_t, TableRef, int*)> narrow, wide;
+    bool have_narrow = jk->narrow_ok && prm.narrow_lits && !getenv("B2_DISABLE_NARROW") &&
+                       tma(jk->tma_narrow, jk->static_smem_narrow, &narrow);
+    bool have_wide = (!jk->narrow_ok || ns > 0 || !have_narrow) && tma(jk->tma_wide, jk->static_smem_wide, &wide);
+    if (have_narrow) {
+      l.small_wide = have_wide ? wide : l.small;
+      l.small = narrow;
+      l.tma = true;
+      l.narrow = true;
+    } else if (have_wide) {
+      l.small = wide;
+      l.tma = true;
+    }
+  }
+  return l;
 }
 
 template <class S> static AggLaunch make_launch(Ctx* ctx, const typename S::Params& prm) {
@@ -184,7 +250,17 @@ bool bind_fused_agg(Ctx* ctx, const ExprPtr& pred, const std::vector<ExprPtr>& g
   if (sig_out) *sig_out = sig;
   auto& reg = fused_registry();
   auto it = reg.find(sig);
-  if (it == reg.end()) return false;
+  std::shared_ptr<JitKernels> jk;
+  if (it == reg.end()) {
+    // not a pre-built shape: compile it (once per shape and process; the cubin is also cached on disk)
+    if (getenv("B2_DISABLE_JIT")) return false;
+    std::string why;
+    jk = jit_fused_kernels(sig, &why);
+    if (!jk) {
+      if (sig_out) *sig_out = sig + " [no fused kernel: " + why.substr(0, 200) + "]";
+      return false;
+    }
+  }
   if ((int)b.f64_cols.size() > MAX_F || (int)b.i32_cols.size() > MAX_I || (int)b.str_cols.size() > MAX_S ||
       (int)b.f64_lits.size() > MAX_LF || (int)b.i64_lits.size() > MAX_LI || (int)b.str_lits.size() > MAX_LS)
     return false;
@@ -206,7 +282,13 @@ bool bind_fused_agg(Ctx* ctx, const ExprPtr& pred, const std::vector<ExprPtr>& g
   for (size_t k = 0; k < b.f64_lits.size(); ++k) p.lits.f[k] = b.f64_lits[k];
   for (size_t k = 0; k < b.i64_lits.size(); ++k) p.lits.i[k] = b.i64_lits[k];
   for (size_t k = 0; k < b.str_lits.size(); ++k) p.lits.s[k] = pack_literal(b.str_lits[k]);
-  *out = it->second.bind(ctx, p);
+  if (jk) {
+    *out = make_launch_jit(ctx, p, jk, (int)b.f64_cols.size(), (int)b.i32_cols.size(), (int)b.str_cols.size(),
+                           (int)args.size(), !groups.empty());
+    if (sig_out) *sig_out = sig + (jk->compiled_now ? " {jit}" : " {jit,cached}");
+  } else {
+    *out = it->second.bind(ctx, p);
+  }
   return true;
 }
 

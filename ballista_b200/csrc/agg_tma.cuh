@@ -16,7 +16,9 @@
 // character window (sized on the host from the column's average string length); otherwise the consumers
 // read that tile's characters straight from global memory.
 #pragma once
+#ifndef __CUDACC_RTC__
 #include <type_traits>
+#endif
 
 #include "agg.cuh"
 

@@ -5,6 +5,7 @@
 #include <cstring>
 #include <new>
 
+#include "jit.h"
 #include "ops.h"
 
 using namespace b2;
@@ -229,6 +230,14 @@ int b2_plan_proto_describe(const uint8_t* buf, size_t len, char* out, size_t cap
     size_t n = t.size() < cap - 1 ? t.size() : cap - 1;
     memcpy(out, t.data(), n);
     out[n] = 0;
+  });
+}
+int b2_jit_compile_check(const char* signature, size_t* cubin_bytes) {
+  return guard([&] {
+    REQUIRE(signature && cubin_bytes, "null argument");
+    std::string why;
+    *cubin_bytes = jit_compile_check(signature, &why);
+    if (!*cubin_bytes) fail(B2_ERR_NOT_IMPLEMENTED, why);
   });
 }
 int b2_sort_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, const int* descending, const int* nulls_first,

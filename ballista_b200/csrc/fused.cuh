@@ -9,7 +9,9 @@
 // Arithmetic is IEEE Float64 with one rounding per operation (__dmul_rn/__dadd_rn: never contracted into
 // FMA), as DataFusion's column-at-a-time kernels compute it.
 #pragma once
+#ifndef __CUDACC_RTC__
 #include <string>
+#endif
 
 #include "table.cuh"
 
@@ -40,31 +42,31 @@ template <int K> struct F {  // Float64 column slot
   static constexpr int NF = K + 1, NI = 0, NS = 0, NLS = 0;
   static constexpr bool IS_STR = false;
   template <class R> __device__ static double eval(const R& r, const Lits&) { return r.f[K]; }
-  static std::string sig() { return "f" + std::to_string(K); }
+  B2_SIG(return "f" + std::to_string(K);)
 };
 template <int K> struct I {  // Int32 / Date32 column slot
   static constexpr int NF = 0, NI = K + 1, NS = 0, NLS = 0;
   static constexpr bool IS_STR = false;
   template <class R> __device__ static int32_t eval(const R& r, const Lits&) { return r.i[K]; }
-  static std::string sig() { return "i" + std::to_string(K); }
+  B2_SIG(return "i" + std::to_string(K);)
 };
 template <int K> struct S {  // Utf8 column slot
   static constexpr int NF = 0, NI = 0, NS = K + 1, NLS = 0;
   static constexpr bool IS_STR = true;
   template <class R> __device__ static StrValT<typename R::W> eval(const R& r, const Lits&) { return r.s[K]; }
-  static std::string sig() { return "s" + std::to_string(K); }
+  B2_SIG(return "s" + std::to_string(K);)
 };
 template <int K> struct LF {
   static constexpr int NF = 0, NI = 0, NS = 0, NLS = 0;
   static constexpr bool IS_STR = false;
   template <class R> __device__ static double eval(const R&, const Lits& l) { return l.f[K]; }
-  static std::string sig() { return "LF" + std::to_string(K); }
+  B2_SIG(return "LF" + std::to_string(K);)
 };
 template <int K> struct LI {
   static constexpr int NF = 0, NI = 0, NS = 0, NLS = 0;
   static constexpr bool IS_STR = false;
   template <class R> __device__ static int64_t eval(const R&, const Lits& l) { return l.i[K]; }
-  static std::string sig() { return "LI" + std::to_string(K); }
+  B2_SIG(return "LI" + std::to_string(K);)
 };
 template <int K> struct LS {
   static constexpr int NF = 0, NI = 0, NS = 0, NLS = K + 1;
@@ -72,13 +74,13 @@ template <int K> struct LS {
   template <class R> __device__ static StrValT<typename R::W> eval(const R&, const Lits& l) {
     return StrValT<typename R::W>{(typename R::W)l.s[K].bytes, l.s[K].len};
   }
-  static std::string sig() { return "LS" + std::to_string(K); }
+  B2_SIG(return "LS" + std::to_string(K);)
 };
 struct True {  // absent predicate
   static constexpr int NF = 0, NI = 0, NS = 0, NLS = 0;
   static constexpr bool IS_STR = false;
   template <class R> __device__ static bool eval(const R&, const Lits&) { return true; }
-  static std::string sig() { return "true"; }
+  B2_SIG(return "true";)
 };
 
 // ---- operators ----
@@ -99,7 +101,7 @@ template <class W> __device__ __forceinline__ bool str_eq(const StrValT<W>& a, c
       auto b = B::eval(r, l);                                                                 \
       return BODY;                                                                            \
     }                                                                                         \
-    static std::string sig() { return std::string(TEXT "(") + A::sig() + "," + B::sig() + ")"; } \
+    B2_SIG(return std::string(TEXT "(") + A::sig() + "," + B::sig() + ")";) \
   };
 B2_FX_BINARY(Add, "add", double, op_add(a, b))
 B2_FX_BINARY(Sub, "sub", double, op_sub(a, b))
@@ -121,13 +123,19 @@ template <class A> struct Not {
   static constexpr int NF = A::NF, NI = A::NI, NS = A::NS, NLS = A::NLS;
   static constexpr bool IS_STR = false;
   template <class R> __device__ static bool eval(const R& r, const Lits& l) { return !A::eval(r, l); }
-  static std::string sig() { return "not(" + A::sig() + ")"; }
+  B2_SIG(return "not(" + A::sig() + ")";)
+};
+template <class A> struct Neg {
+  static constexpr int NF = A::NF, NI = A::NI, NS = A::NS, NLS = A::NLS;
+  static constexpr bool IS_STR = false;
+  template <class R> __device__ static auto eval(const R& r, const Lits& l) -> decltype(A::eval(r, l)) { return -A::eval(r, l); }
+  B2_SIG(return "neg(" + A::sig() + ")";)
 };
 template <class A> struct ToF64 {
   static constexpr int NF = A::NF, NI = A::NI, NS = A::NS, NLS = A::NLS;
   static constexpr bool IS_STR = false;
   template <class R> __device__ static double eval(const R& r, const Lits& l) { return (double)A::eval(r, l); }
-  static std::string sig() { return "f64(" + A::sig() + ")"; }
+  B2_SIG(return "f64(" + A::sig() + ")";)
 };
 
 // ---- type lists ----
@@ -137,12 +145,12 @@ template <class... T> struct List {
 template <class L> struct ListTraits;
 template <> struct ListTraits<List<>> {
   static constexpr int NF = 0, NI = 0, NS = 0, NLS = 0;
-  static std::string sig() { return ""; }
+  B2_SIG(return "";)
 };
 template <class H, class... T> struct ListTraits<List<H, T...>> {
   using Rest = ListTraits<List<T...>>;
   static constexpr int NF = cmax(H::NF, Rest::NF), NI = cmax(H::NI, Rest::NI), NS = cmax(H::NS, Rest::NS), NLS = cmax(H::NLS, Rest::NLS);
-  static std::string sig() { return H::sig() + (sizeof...(T) ? "," + Rest::sig() : std::string()); }
+  B2_SIG(return H::sig() + (sizeof...(T) ? "," + Rest::sig() : std::string());)
 };
 
 // evaluate a list of Float64 expressions into out[]

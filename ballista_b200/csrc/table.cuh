@@ -2,10 +2,39 @@
 // 128-bit packed keys, the global open-addressing group table (128-bit CAS claim + red.add accumulate),
 // streaming loads, warp reductions.
 #pragma once
+#ifndef __CUDACC_RTC__
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #include <type_traits>
+#else
+// compiled at run time by NVRTC (jit.cu): no host headers; libcu++ supplies the few type traits used here
+#include <cuda/std/type_traits>
+typedef signed char int8_t;
+typedef unsigned char uint8_t;
+typedef short int16_t;
+typedef unsigned short uint16_t;
+typedef int int32_t;
+typedef unsigned int uint32_t;
+typedef long long int64_t;
+typedef unsigned long long uint64_t;
+typedef unsigned long long uintptr_t;
+namespace std {
+using cuda::std::conditional;
+using cuda::std::enable_if;
+using cuda::std::false_type;
+using cuda::std::integral_constant;
+using cuda::std::is_integral;
+using cuda::std::true_type;
+}  // namespace std
+#endif
+// sig(): the signature text of an expression template (host only; the registry is keyed on it)
+#ifdef __CUDACC_RTC__
+#define B2_SIG(...)
+#else
+#define B2_SIG(...) \
+  static std::string sig() { __VA_ARGS__ }
+#endif
 
 namespace b2 {
 

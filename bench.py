@@ -264,12 +264,13 @@ def oracle_scan_chunks(ctx, O, table_sf, r0, r1, columns, chunk_rows, fn):
     return checked
 
 
-def oracle_q1_partition(ctx, O, table_sf, r0, r1, threads, chunk_rows, columns):
+def oracle_q1_partition(ctx, O, table_sf, r0, r1, threads, chunk_rows, columns, date_lit=None):
     """-> ({(flag, status): [sum_qty, sum_base, sum_disc_price, sum_charge, sum_disc, count]}, generator rows checked)"""
     acc = {}
+    kw = {} if date_lit is None else {"date_lit": date_lit}
 
     def one(cols):
-        for r in O.q1(cols, n_partitions=threads):
+        for r in O.q1(cols, n_partitions=threads, **kw):
             a = acc.setdefault((r["l_returnflag"], r["l_linestatus"]), [0.0, 0.0, 0.0, 0.0, 0.0, 0])
             for k, nm in enumerate(("sum_qty", "sum_base_price", "sum_disc_price", "sum_charge")):
                 a[k] += r[nm]
@@ -774,6 +775,66 @@ def run_other_configs(args, env):
     out["q3"] = q3_local(sf, f"q3_sf{sf:g}")
     if world == 1 and args.q3_sf > sf:
         out[f"q3_sf{args.q3_sf:g}"] = q3_local(args.q3_sf, f"q3_sf{args.q3_sf:g}")
+    # ---- plan shapes the library has no pre-built kernel for: compiled at run time (NVRTC) into the same TMA-fed scan
+    # kernel.  (a) Q1 with `l_shipdate < d` instead of `<=`; (b) a disjunctive predicate, one key, other aggregates. ----
+    if world == 1:
+        from ballista_b200 import CoalesceBatchesExec, FilterExec, HashAggregateExec, avg, count, date, lit
+        from ballista_b200 import sum as sum_
+        n1 = nrows("lineitem", args.sf)
+        li1 = ctx.tpch("lineitem", args.sf, columns=tpch.Q1_COLUMNS)
+
+        def unseen(name, partial, make_final, bytes_per_row, check):
+            query = tpch.TwoStage(ctx, partial, make_final)
+            ms, launches, tab, t = timeit(query.run, steps=10, profile=True)
+            k_ms, k_n = t["kernel"]
+            path = partial.last_path()
+            assert path.startswith("fused:") and "[tma" in path and "{jit" in path, path
+            res = {"workload": name, "ms_per_step": ms, "step_ms": step_stats(t["per_step"]),
+                   "rows_per_s": n1 / (ms / 1e3), "frac_of_hbm_peak": n1 * bytes_per_row / (ms / 1e3) / 1e9 / peak,
+                   "scan_kernel": {"avg_launch_ms": k_ms / k_n, "GB_per_s": n1 * bytes_per_row / (k_ms / k_n / 1e3) / 1e9,
+                                   "frac_of_hbm_peak": n1 * bytes_per_row / (k_ms / k_n / 1e3) / 1e9 / peak},
+                   "algorithmic_bytes_per_row": bytes_per_row, "launches_per_step": launches, "path": path}
+            if O:
+                res["parity"] = check(tab.to_pylist())
+            return res
+        scan_a = tpch.scan(ctx, [[li1]])
+        part_a = HashAggregateExec("Partial", tpch._q1_groups(), tpch.q1_aggregates(),
+                                   CoalesceBatchesExec(FilterExec(col("l_shipdate") < date("1998-09-02"), scan_a)))
+
+        def check_a(rows_):
+            acc_, chk_ = oracle_q1_partition(ctx, O, args.sf, 0, n1, env.host_threads, args.parity_chunk_rows,
+                                             tpch.Q1_COLUMNS, date_lit=O.DATE_1998_09_02 - 1)  # x < d  ==  x <= d - 1
+            return parity_q1(f"q1_lt_sf{args.sf:g}", rows_, acc_, n1, chk_)
+        out["q1_lt_jit"] = unseen(f"TPC-H Q1 with l_shipdate < date (not <=), SF{args.sf:g}: a shape compiled at run time",
+                                  part_a, lambda s_: tpch.q1_final(s_, scan_a.schema()), Q1_BYTES_PER_ROW, check_a)
+        pred_b = col("l_discount").between(lit(0.02), lit(0.06)) | (col("l_quantity") < lit(10))
+        aggs_b = [sum_(col("l_quantity") * col("l_extendedprice")).alias("s"), avg(col("l_tax")).alias("t"), count().alias("n")]
+        scan_b = tpch.scan(ctx, [[li1]])
+        part_b = HashAggregateExec("Partial", [col("l_linestatus")], aggs_b, CoalesceBatchesExec(FilterExec(pred_b, scan_b)))
+        mk_b = lambda s_: HashAggregateExec("Final", [col("l_linestatus")], aggs_b, tpch.MergeExec(s_), input_schema=scan_b.schema())
+
+        def check_b(rows_):  # the column-at-a-time path (eval.cu + materialised source) over the same rows
+            os.environ["B2_DISABLE_FUSION"] = "1"
+            try:
+                p2 = HashAggregateExec("Partial", [col("l_linestatus")], aggs_b, CoalesceBatchesExec(FilterExec(pred_b, tpch.scan(ctx, [[li1]]))))
+                ref = tpch.run_two_stage(ctx, p2, mk_b).to_pylist()
+            finally:
+                del os.environ["B2_DISABLE_FUSION"]
+            got_ = {r_["l_linestatus"]: r_ for r_ in rows_}
+            want_ = {r_["l_linestatus"]: r_ for r_ in ref}
+            keys_eq = sorted(got_) == sorted(want_)
+            counts_eq = keys_eq and all(got_[k_]["n"] == want_[k_]["n"] for k_ in want_)
+            err_ = max(abs(got_[k_][c_] - want_[k_][c_]) / abs(want_[k_][c_]) for k_ in want_ for c_ in ("s", "t")) if keys_eq else 1.0
+            return {"config": f"unseen_shape_b_sf{args.sf:g}", "rows": int(n1), "keys_equal": bool(keys_eq),
+                    "counts_equal": bool(counts_eq), "max_rel_err": err_, "tolerance": 1e-9,
+                    "ok": bool(keys_eq and counts_eq and err_ <= 1e-9),
+                    "checker": "the library's own column-at-a-time path (B2_DISABLE_FUSION) over the same rows; the shape's "
+                               "semantics are checked against numpy in tests/test_gpu_jit.py"}
+        out["unseen_shape_b_jit"] = unseen("disjunctive predicate (l_discount BETWEEN .02 AND .06 OR l_quantity < 10), group by "
+                                           f"l_linestatus, SUM(qty*price) AVG(tax) COUNT(*), SF{args.sf:g}: compiled at run time",
+                                           part_b, mk_b, 37, check_b)
+        del li1, scan_a, scan_b, part_a, part_b
+
     # ---- Q5: six tables, five joins (one on a two-column key), group by n_name.  Orders / lineitem are row-range
     # partitions of ONE database (one per GPU); customer, supplier, nation and region are replicated, as the reference's
     # collect-left join reads its whole build side in every task.  An order's lines lie in its own partition, so every

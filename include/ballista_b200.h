@@ -194,6 +194,12 @@ int b2_plan_from_proto(b2_ctx* ctx, const uint8_t* buf, size_t len, b2_op* const
  * (NUL-terminated, truncated to `cap`) and the number of leaf nodes into *n_leaves.  For diagnostics and for
  * sizing the `leaves` array. */
 int b2_plan_proto_describe(const uint8_t* buf, size_t len, char* out, size_t cap, int* n_leaves);
+/* Run-time compiled scan kernels.  compile_expr accepts any expression (from_proto.rs:348-364); a HashAggregateExec whose
+ * (predicate, group keys, aggregate arguments) shape is not among the pre-built fused kernels is compiled for sm_100a on
+ * first use (NVRTC) and cached.  This entry point compiles the shape named by `signature` (the text b2_op_last_path shows
+ * after "fused:", e.g. "p:lt(i0,LI0)|k:s0|a:f0,mul(f0,f1)") WITHOUT loading it - it needs no device - and returns the
+ * size of the cubin in *cubin_bytes; B2_ERR_NOT_IMPLEMENTED when the shape is outside the fused vocabulary. */
+int b2_jit_compile_check(const char* signature, size_t* cubin_bytes);
 /* SortExec::try_new(Vec<PhysicalSortExpr{expr, SortOptions{descending, nulls_first}}>, input)  from_proto.rs:291-330.
  * Single input partition, one sorted output batch, stable.  `descending[i]` != 0 sorts expression i descending;
  * nulls_first is accepted for interface parity (columns on this path are non-null). */

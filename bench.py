@@ -532,6 +532,26 @@ def run_e2e(args, env):
             host_batches.append(rb.slice(o, args.e2e_batch_rows))
         rows_e2e += rb.num_rows
     h2d = rows_e2e * Q1_BYTES_PER_ROW + 8 * len(host_batches)  # Utf8 offsets carry one extra int32 per batch
+    # the ceiling of this leg: plain pinned host -> device copies issued by ALL ranks at the same time (same PCIe
+    # links, same host memory), no kernels
+    ceiling = None
+    try:
+        blk = torch.empty(256 << 20, dtype=torch.uint8).pin_memory()
+        dst = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        reps = 16
+        for _ in range(2):
+            dst.copy_(blk, non_blocking=True)
+        barrier(env)
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(reps):
+            dst.copy_(blk, non_blocking=True)
+        c1.record()
+        barrier(env)
+        ceiling = reps * blk.numel() / (env.cluster.max_over_ranks(env.dist, torch, c0.elapsed_time(c1), world) / 1e3) / 1e9
+        del blk, dst
+    except Exception:
+        pass
     t = time_steps(env, make_step(host_batches), args.e2e_steps, 1)
     table, _ = t["last"]
     ms = t["ms_total"]
@@ -542,6 +562,10 @@ def run_e2e(args, env):
             "d2h_bytes_per_step": int(d2h), "rows_per_gpu": rows_e2e, "steps": args.e2e_steps,
             "ms_per_step": ms / args.e2e_steps, "host_batch_rows": args.e2e_batch_rows,
             "h2d_GB_per_s_per_gpu": h2d / (ms / args.e2e_steps / 1e3) / 1e9,
+            "h2d_ceiling_GB_per_s_per_gpu": ceiling,
+            "frac_of_h2d_ceiling": (h2d / (ms / args.e2e_steps / 1e3) / 1e9 / ceiling) if ceiling else None,
+            "ceiling_note": "pinned 256 MiB host -> device copies issued by all ranks at once (CUDA events, max over ranks): "
+                            "what the PCIe links and the host memory deliver with no kernel running",
             "note": "host Arrow RecordBatches in cudaHostRegister'ed memory pushed through b2_memory_exec_add_batch; "
                     "H2D of all 7 columns + result D2H inside the timed region"
                     + ("" if frac == 1.0 else f"; bounded to {frac:.2f} of the partition by host RAM")}

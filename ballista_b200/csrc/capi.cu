@@ -456,7 +456,7 @@ int b2_comm_allgather_batch(b2_ctx* ctx, b2_batch* local, b2_batch** out) {
   return guard([&] {
     REQUIRE(ctx && local && local->b && out, "null argument");
     ctx->c.activate();
-    BatchPtr b = comm_allgather_batch(&ctx->c, *local->b);
+    BatchPtr b = comm_allgather_batch(&ctx->c, local->b, /*allow_lazy=*/true);
     auto* h = new b2_batch;
     h->b = b;
     *out = h;

@@ -176,11 +176,71 @@ __global__ void unpack_small_kernel(SmallArgs a, const char* recv) {
   }
 }
 
+// The same unpack when nothing was read back (the local batch was lazy): row / character prefixes are derived from the
+// gathered slot headers on the device, and the result's own header (Batch::lazy: status, rows, character totals) is
+// written for whoever consumes the gathered batch.  A slot that did not fit (-1) or whose sender must redo (-2) makes
+// the status non-zero: every rank sees the same headers, so every rank redoes the gather through the checked path.
+__global__ void unpack_small_lazy_kernel(SmallArgs a, const char* recv, int64_t* hdr_out) {
+  __shared__ int64_t row_prefix[SMALL_MAX_RANKS + 1];
+  __shared__ int64_t chr_prefix[SMALL_MAX_RANKS + 1];
+  __shared__ int bad;
+  const SmallCol& c = a.c[blockIdx.y];
+  if (threadIdx.x == 0) {
+    bad = 0;
+    row_prefix[0] = chr_prefix[0] = 0;
+    for (int r = 0; r < a.nr; ++r) {
+      const int64_t* h = reinterpret_cast<const int64_t*>(recv + (int64_t)r * a.stride);
+      if (h[0] < 0) bad = h[0] == -1 ? AGG_TOO_BIG : AGG_INPUT_FAILED;
+      row_prefix[r + 1] = row_prefix[r] + (h[0] > 0 ? h[0] : 0);
+      chr_prefix[r + 1] = chr_prefix[r] + (c.utf8 >= 0 ? h[1 + blockIdx.y] : 0);
+    }
+    if (blockIdx.y == 0) {
+      hdr_out[0] = bad;
+      hdr_out[1] = row_prefix[a.nr];
+    }
+    if (c.utf8 >= 0) hdr_out[2 + blockIdx.y] = chr_prefix[a.nr];
+  }
+  __syncthreads();
+  if (bad) return;
+  const int64_t total = row_prefix[a.nr];
+  for (int64_t i = threadIdx.x; i < total; i += blockDim.x) {
+    int r = 0;
+    while (row_prefix[r + 1] <= i) ++r;
+    int64_t j = i - row_prefix[r];
+    const char* base = recv + (int64_t)r * a.stride + c.val_off;
+    if (c.dst_valid) c.dst_valid[i] = (uint8_t)recv[(int64_t)r * a.stride + c.valid_off + j];
+    if (c.utf8 >= 0) {
+      const int32_t* lens = reinterpret_cast<const int32_t*>(base);
+      int64_t o = chr_prefix[r];
+      for (int64_t t = 0; t < j; ++t) o += lens[t];
+      static_cast<int32_t*>(c.dst)[i] = (int32_t)o;
+      if (i == total - 1) static_cast<int32_t*>(c.dst)[total] = (int32_t)chr_prefix[a.nr];
+    } else if (c.width == 8) {
+      static_cast<int64_t*>(c.dst)[i] = reinterpret_cast<const int64_t*>(base)[j];
+    } else if (c.width == 4) {
+      static_cast<int32_t*>(c.dst)[i] = reinterpret_cast<const int32_t*>(base)[j];
+    } else {
+      static_cast<char*>(c.dst)[i] = base[j];
+    }
+  }
+  if (c.utf8 >= 0) {
+    if (total == 0 && threadIdx.x == 0) static_cast<int32_t*>(c.dst)[0] = 0;
+    const int64_t tc = chr_prefix[a.nr];
+    for (int64_t k = threadIdx.x; k < tc; k += blockDim.x) {
+      int r = 0;
+      while (chr_prefix[r + 1] <= k) ++r;
+      c.dst_chars[k] = (uint8_t)recv[(int64_t)r * a.stride + c.chr_off + (k - chr_prefix[r])];
+    }
+  }
+}
+
 static BatchPtr allgather_general(Ctx* ctx, const Batch& local);
 
 // Returns nullptr when the schema is outside the small protocol or some rank's batch did not fit its slot; *retry is
 // set when some rank's lazy batch must be redone first (then every rank resolves and calls again).
-static BatchPtr allgather_small(Ctx* ctx, const Batch& local, bool* retry) {
+// `lazy_src`: the local batch is lazy (a speculative Partial result) and the caller can take a lazy result: nothing is
+// read back here either, the gathered batch carries its own device-side header.
+static BatchPtr allgather_small(Ctx* ctx, const Batch& local, bool* retry, const BatchPtr& lazy_src = nullptr) {
   *retry = false;
   const int nr = ctx->nranks;
   const size_t ncol = local.cols.size();
@@ -229,6 +289,41 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local, bool* retry) {
   B2_LAUNCHED(ctx);
   B2_NCCL(ncclAllGather(send->ptr, recv->ptr, (size_t)a.stride, ncclChar, ctx->comm->nccl, ctx->stream));
   ctx->bytes_sent += a.stride * (nr - 1);
+  if (lazy_src && local.lazy && ncol <= 24) {
+    const int64_t bound = (int64_t)nr * SMALL_ROWS;
+    auto out = std::make_shared<Batch>();
+    out->ctx = ctx;
+    out->schema = local.schema;
+    out->num_rows = -1;
+    for (size_t c = 0; c < ncol; ++c) {
+      Column o;
+      o.dtype = local.cols[c].dtype;
+      o.length = bound;
+      if (o.dtype == B2_UTF8) {
+        o.data = dev_alloc(ctx, (size_t)(bound + 1) * 4 + 16);
+        o.chars = dev_alloc(ctx, (size_t)nr * SMALL_CHARS + 16);
+        a.c[c].dst_chars = o.chars->as<uint8_t>();
+      } else {
+        o.data = dev_alloc(ctx, (size_t)bound * dtype_width(o.dtype) + 16);
+      }
+      a.c[c].dst = o.data->ptr;
+      o.valid = dev_alloc(ctx, (size_t)bound + 16);  // which ranks sent NULLs is not known on the host: always carried
+      a.c[c].dst_valid = o.valid->as<uint8_t>();
+      out->cols.push_back(std::move(o));
+    }
+    auto lz = std::make_shared<LazyRows>();
+    lz->hdr = dev_alloc_zero(ctx, (2 + 24) * 8);
+    lz->bound = bound;
+    unpack_small_lazy_kernel<<<dim3(1, (unsigned)ncol), 256, 0, ctx->stream>>>(a, recv->as<char>(), lz->hdr->as<int64_t>());
+    B2_LAUNCHED(ctx);
+    BatchPtr src = lazy_src;
+    lz->redo = [ctx, src](int) {  // collective: every rank saw the same slot headers and lands here together
+      resolve_batch(*src);
+      return comm_allgather_batch(ctx, src);
+    };
+    out->lazy = lz;
+    return out;
+  }
   // one strided readback: the header of every slot
   std::vector<int64_t> heads((size_t)nr * hdr_words);
   {
@@ -286,11 +381,13 @@ static BatchPtr allgather_small(Ctx* ctx, const Batch& local, bool* retry) {
   return out;
 }
 
-BatchPtr comm_allgather_batch(Ctx* ctx, Batch& local) {
+BatchPtr comm_allgather_batch(Ctx* ctx, const BatchPtr& local_ptr, bool allow_lazy) {
   if (!ctx->comm) fail(B2_ERR_INVALID_ARG, "no communicator (call b2_comm_init)");
+  Batch& local = *local_ptr;
   bool retry = false;
-  // a lazy batch is packed from its device-side header: the Partial -> Final hop adds no synchronisation of its own
-  if (BatchPtr b = allgather_small(ctx, local, &retry)) return b;  // carries validity
+  // a lazy batch is packed from its device-side header and (allow_lazy) unpacked without a readback: the
+  // Partial -> Final hop adds no synchronisation of its own
+  if (BatchPtr b = allgather_small(ctx, local, &retry, allow_lazy && local.lazy ? local_ptr : nullptr)) return b;  // carries validity
   if (local.lazy) resolve_batch(local);
   if (retry)
     if (BatchPtr b = allgather_small(ctx, local, &retry)) return b;

@@ -106,7 +106,8 @@ BufPtr radix_sort_order(Ctx* ctx, const std::vector<const u64*>& words, const st
 void comm_unique_id(void* id128);
 void comm_init(Ctx* ctx, int rank, int nranks, const void* id128);
 void comm_destroy(Ctx* ctx);
-BatchPtr comm_allgather_batch(Ctx* ctx, Batch& local);
+// allow_lazy: a lazy `local` (device-side row count) may yield a lazy result (nothing read back on the hop)
+BatchPtr comm_allgather_batch(Ctx* ctx, const BatchPtr& local, bool allow_lazy = false);
 // all-to-all of a destination-major permuted batch: slice d (counts[d] rows) goes to rank d
 BatchPtr comm_all_to_all(Ctx* ctx, const Batch& permuted, const std::vector<int64_t>& counts);
 // shuffle.cu: the same exchange over CUDA-IPC peer memory (columns moved into a peer-mapped arena by the split's

@@ -156,7 +156,7 @@ struct HashJoinExec : Op {
     }
     if (per_rank && !partitioned) {
       if (!ctx->comm) fail(B2_ERR_EXECUTION, "HashJoinExec: per-rank build partitions without a communicator");
-      left_batch = comm_allgather_batch(ctx, *left_batch);
+      left_batch = comm_allgather_batch(ctx, left_batch);
     }
   }
   // hash table over one side's batch (the collected left side, or - swapped - a small right batch)

@@ -136,7 +136,6 @@ int64_t join_probe(Ctx* ctx, const JoinTable& t, const Key128* pkeys, int64_t n,
 // gathered once, for matching rows only (late materialisation).
 // ------------------------------------------------------------------------------------------------------
 constexpr int BUCKET = 4;  // slots per bucket (one 32-byte sector)
-__device__ __forceinline__ u64 bucket_of(uint32_t k, u64 bmask) { return (u64)fmix32(k) & bmask; }
 __device__ __forceinline__ u64 ld_slot_volatile(const u64* p) {
   u64 v;
   asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
@@ -221,15 +220,22 @@ bool compile_row_pred(const ExprPtr& pred, const Batch& batch, RowPred* out) {
   return true;
 }
 
+// `perm` (optional): the rows to insert, already filtered and ordered by the top bits of their bucket (a 32-way split,
+// repartition.cu): consecutive threads then fill one slice of the table at a time and the inserts hit L2, where rows
+// in input order scatter 8-byte CAS operations over the whole table in HBM.
 __global__ void join_build32_kernel(const int32_t* __restrict__ key, RowPred pred, const uint8_t* __restrict__ mask,
-                                    int64_t n, u64* slots, u64 bmask, uint32_t* next, int* flags) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    if (mask && !mask[i]) continue;
-    if (!row_pred(pred, i)) continue;
+                                    const uint32_t* __restrict__ perm, int64_t n, u64* slots, u64 bmask, int bshift,
+                                    uint32_t* next, int* flags) {
+  int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = perm ? (int64_t)perm[j] : j;
+    if (!perm) {
+      if (mask && !mask[i]) continue;
+      if (!row_pred(pred, i)) continue;
+    }
     uint32_t k = (uint32_t)key[i];
     const uint32_t h = fmix32(k);
-    u64 b = (u64)h & bmask;
+    u64 b = (u64)(table_hash(h) >> bshift);
     u64 mine = ((u64)k << 32) | (uint32_t)i;
     bool placed = false;
     for (u64 probe = 0; probe <= bmask && !placed; ++probe) {
@@ -292,7 +298,22 @@ std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const RowP
   t->flags = dev_alloc_zero(ctx, 16);
   // size the table for the rows that pass the fused filter, so that a selective build side stays L2-resident
   int64_t n_in = n;
-  if ((mask || pred.n) && n > (1 << 18)) {
+  // Large build sides are first split 32 ways by the top bits of their table bucket (destination bytes, per-tile
+  // histogram, one scan, stable scatter of row ids: the hash-repartition kernels), which also counts the rows that pass
+  // the fused filter; the insert kernel then walks the permutation.
+  BufPtr perm;
+  // (measured on Q3 SF100, 14.7 M build rows into a 256 MB table: the pre-sorted build takes 1.14 ms + 0.2 ms of split
+  // against 0.72 ms for inserts in input order - the L2 atomics of one 8 MB slice serialise harder than CAS operations
+  // spread over HBM - so it stays an experiment behind B2_PARTITIONED_BUILD=1)
+  const bool big = n > (1 << 21) && getenv("B2_PARTITIONED_BUILD");
+  if (big) {
+    SplitState st = hash_split_begin(ctx, nullptr, key, n, 32, &pred, mask, nullptr, /*table_order=*/true);
+    std::vector<int64_t> counts;
+    hash_split_counts(ctx, st, &counts);
+    n_in = 0;
+    for (int64_t c : counts) n_in += c;
+    if (n_in > (1 << 21)) perm = hash_split_perm(ctx, st);  // a small surviving set builds an L2-resident table anyway
+  } else if ((mask || pred.n) && n > (1 << 18)) {
     pass_count_kernel<<<grid_for(ctx, 8, n, 1024), 256, 0, ctx->stream>>>(
         pred, mask, n, reinterpret_cast<unsigned long long*>(t->flags->as<char>() + 8));
     B2_LAUNCHED(ctx);
@@ -303,6 +324,9 @@ std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const RowP
   u64 cap = 64;  // slots; load factor <= 0.5, BUCKET slots per bucket
   while (cap < 2 * (u64)n_in + 16) cap <<= 1;
   t->cap = cap;
+  int lb = 0;
+  while ((1ull << lb) < cap / BUCKET) ++lb;
+  t->bshift = 32 - lb;
   t->slots = dev_alloc(ctx, cap * 8);
   t->next = dev_alloc(ctx, (size_t)(n + 1) * 4);
   B2_CUDA(cudaMemsetAsync(t->slots->ptr, 0xFF, cap * 8, ctx->stream));
@@ -315,9 +339,13 @@ std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const RowP
     bloom_build_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(key, pred, mask, n, t->bloom->as<uint32_t>(),
                                                                         (uint32_t)(words - 1));
     B2_LAUNCHED(ctx);
-    join_build32_kernel<<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(
-        key, pred, mask, n, t->slots->as<u64>(), cap / BUCKET - 1, t->next->as<uint32_t>(), t->flags->as<int>());
-    B2_LAUNCHED(ctx);
+    const int64_t work = perm ? n_in : n;
+    if (work) {
+      join_build32_kernel<<<grid_for(ctx, 8, work, 256), 256, 0, ctx->stream>>>(
+          key, pred, mask, perm ? perm->as<uint32_t>() : nullptr, work, t->slots->as<u64>(), cap / BUCKET - 1, t->bshift,
+          t->next->as<uint32_t>(), t->flags->as<int>());
+      B2_LAUNCHED(ctx);
+    }
   }
   t->dups_known = false;
   return t;
@@ -385,7 +413,7 @@ template <int MODE, bool DUPS, int PRED>
 __global__ void __launch_bounds__(JP_THREADS, 5)
     join_probe32_kernel(const int32_t* __restrict__ key, const __grid_constant__ RowPred pred,
                         const uint8_t* __restrict__ mask, int64_t n, bool vec, const u64* __restrict__ slots, u64 bmask,
-                        const uint32_t* __restrict__ bloom, uint32_t wmask, const uint32_t* __restrict__ next,
+                        int bshift, const uint32_t* __restrict__ bloom, uint32_t wmask, const uint32_t* __restrict__ next,
                         uint32_t* __restrict__ left_idx, uint32_t* __restrict__ right_idx, int64_t* tile_cnt) {
   // run heads of the warp's tile in row order: key | (row within the tile) << 32; rewritten in place by the hits of
   // step (3a): build row | the same position word
@@ -472,7 +500,7 @@ __global__ void __launch_bounds__(JP_THREADS, 5)
       const uint32_t word = c0 + lane < n_heads ? __ldg(bloom + (h & wmask)) : 0u;
       uint32_t hd = NIL;
       if ((word & bits) == bits) {  // lanes past the last head: word == 0, never true
-        u64 bb = (u64)h & bmask;
+        u64 bb = (u64)(table_hash(h) >> bshift);
         while (true) {
           const ulonglong2* bp = reinterpret_cast<const ulonglong2*>(slots + bb * BUCKET);
           const ulonglong2 x = __ldg(bp), y = __ldg(bp + 1);
@@ -584,7 +612,7 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
     constexpr bool D = decltype(dups)::value;
     auto go = [&](auto kernel) {
       kernel<<<grid_, JP_THREADS, 0, ctx->stream>>>(key, pred, mask, n, vec, t.slots->as<u64>(), t.cap / BUCKET - 1,
-                                                  t.bloom->as<uint32_t>(), (uint32_t)(t.bloom_words - 1),
+                                                  t.bshift, t.bloom->as<uint32_t>(), (uint32_t)(t.bloom_words - 1),
                                                   t.next->as<uint32_t>(), li, ri, tile_cnt);
     };
     if (pk == 0) go(join_probe32_kernel<M, D, 0>);

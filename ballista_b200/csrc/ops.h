@@ -45,6 +45,7 @@ struct JoinTable {
   bool k32 = false;
   BufPtr slots, flags, bloom;  // bloom: blocked Bloom filter over the build keys (32-bit words, 3 bits per key)
   u64 bloom_words = 0;
+  int bshift = 28;  // bucket = table_hash(fmix32(key)) >> bshift
   bool dups_known = false, has_dups = false;
 };
 // in-place exclusive scan of v[0..n) on the context's stream; v[n] = total (single CTA for short inputs, chunked above)
@@ -87,9 +88,10 @@ struct SplitState {
   int64_t n = 0, n_tiles = 0;
   int n_out = 0;
 };
+// table_order: split by the top bits of table_hash (the join table's bucket order) instead of the exchange's hash
 SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
                             const RowPred* pred = nullptr, const uint8_t* mask = nullptr,
-                            const SemiFilter* semi = nullptr);
+                            const SemiFilter* semi = nullptr, bool table_order = false);
 void hash_split_starts_device(Ctx* ctx, const SplitState& st, int64_t* out_dev);  // n_out + 1 slice starts
 void hash_split_counts(Ctx* ctx, const SplitState& st, std::vector<int64_t>* counts);
 BufPtr hash_split_perm(Ctx* ctx, const SplitState& st);

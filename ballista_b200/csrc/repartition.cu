@@ -53,7 +53,11 @@ constexpr uint8_t RP_DROPPED = 255;  // destination byte of a row the fused filt
 struct KeySrc {  // packed 16-byte keys, or a single Int32 / Date32 key column hashed as its packed form
   const Key128* k128;
   const int32_t* k32;
-  __device__ __forceinline__ uint32_t hash(int64_t i) const { return k128 ? part_hash(k128[i]) : part_hash((uint32_t)k32[i]); }
+  bool table_order;  // split by the join table's bucket order (join.cu's partitioned build), not for an exchange
+  __device__ __forceinline__ uint32_t hash(int64_t i) const {
+    const uint32_t h = k128 ? part_hash(k128[i]) : part_hash((uint32_t)k32[i]);
+    return table_order ? table_hash(h) : h;
+  }
 };
 
 // pass 1: destination byte per row + per-tile histogram, stored destination-major (hist[d * n_tiles + tile]) so
@@ -312,7 +316,7 @@ __global__ void __launch_bounds__(RP_THREADS)
 
 // ---- host side: phase 1 (destinations, histogram, scan: no host sync), then counts / permutation / column move ----
 SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
-                            const RowPred* pred, const uint8_t* mask, const SemiFilter* semi) {
+                            const RowPred* pred, const uint8_t* mask, const SemiFilter* semi, bool table_order) {
   if (n_out < 1 || n_out > RP_MAX_OUT) fail(B2_ERR_INVALID_ARG, "hash_split_begin supports 1..32 output partitions");
   if (n >= (1ll << 32) - 1) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
   SplitState st;
@@ -330,7 +334,7 @@ SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, 
     sa.stride = semi->stride;
     for (int d = 0; d < n_out; ++d) sa.wmask[d] = semi->wmask[d];
   }
-  rp_hist_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(KeySrc{keys, key32}, pred ? *pred : RowPred(), mask, sa, n, n_out,
+  rp_hist_kernel<<<grid, RP_THREADS, 0, ctx->stream>>>(KeySrc{keys, key32, table_order}, pred ? *pred : RowPred(), mask, sa, n, n_out,
                                                        st.dest->as<uint8_t>(), st.hist->as<int64_t>(), st.n_tiles);
   B2_LAUNCHED(ctx);
   scan_i64(ctx, st.hist->as<int64_t>(), st.n_tiles * n_out);

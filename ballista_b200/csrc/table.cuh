@@ -127,6 +127,11 @@ __host__ __device__ __forceinline__ uint32_t part_hash(const Key128& k) {
   return fmix32((uint32_t)k.lo ^ (uint32_t)(k.lo >> 32) * 0x85EBCA6Bu ^ (uint32_t)k.hi * 0xC2B2AE35u ^
                 (uint32_t)(k.hi >> 32) * 0x27D4EB2Fu);
 }
+// Bucket of the 32-bit-key join table: the TOP bits of a second multiplicative mix of the key's hash.  Top bits, so
+// that keys pre-sorted by the top bits of the same value fill the table slice by slice (join.cu builds large tables that
+// way: each slice stays in L2 while it is filled); a second mix, because after an exchange all keys of a rank share the
+// top bits of fmix32 itself (part_dest) and must still spread over the whole table.
+__host__ __device__ __forceinline__ uint32_t table_hash(uint32_t h) { return h * 0x9E3779B1u; }
 __host__ __device__ __forceinline__ int part_dest(uint32_t h, int n_out) { return (int)(((u64)h * (u64)(uint32_t)n_out) >> 32); }
 
 // ---- streaming (read-once) loads: bypass L1 allocation ----

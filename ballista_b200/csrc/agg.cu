@@ -447,17 +447,9 @@ BufPtr EmitPlan::run_lazy(const int* status_dev) {
 // small Final aggregate (see agg.h)
 // ------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) final_tiny_kernel(const __grid_constant__ TinyArgs a, TableRef t, int na_tbl, int nc_tbl, int* status) {
-  if (a.init) {  // the table arrives uninitialised
-    for (u64 i = threadIdx.x; i < t.cap; i += blockDim.x) {
-      t.keys[i] = Key128{KEY_EMPTY, KEY_EMPTY};
-      for (int x = 0; x < na_tbl; ++x) t.acc[(u64)x * t.cap + i] = 0.0;
-      for (int x = 0; x < nc_tbl; ++x) t.cnt[(u64)x * t.cap + i] = 0;
-    }
-    if (threadIdx.x == 0) *t.n_groups = 0;
-    __syncthreads();
-  }
   __shared__ int64_t s_rows[TINY_BATCHES];
   __shared__ int s_bad;
+  __shared__ unsigned long long s_cap;
   if (threadIdx.x == 0) {
     int bad = 0;
     int64_t total = 0;
@@ -474,8 +466,27 @@ __global__ void __launch_bounds__(1024) final_tiny_kernel(const __grid_constant_
     if (!bad && total > TINY_MAX_ROWS) bad = AGG_TOO_BIG;
     s_bad = bad;
     if (bad) atomicExch(status, bad);
+    // The table arrives uninitialised and only the part that is used gets initialised: with a single launch the
+    // hashed capacity is sized from the rows actually present (Q1: 4 rows -> 64 slots), the arrays keep their stride.
+    u64 cap = t.cap;
+    if (a.single) {
+      cap = t.cap < 64 ? t.cap : 64;
+      while (cap < t.cap && cap < 4 * (u64)(total > 0 ? total : 1)) cap <<= 1;
+    }
+    s_cap = cap;
   }
   __syncthreads();
+  const u64 stride = t.cap;  // acc[x * stride + slot], cnt[x * stride + slot]
+  t.cap = s_cap;
+  if (a.init) {
+    for (u64 i = threadIdx.x; i < t.cap; i += blockDim.x) {
+      t.keys[i] = Key128{KEY_EMPTY, KEY_EMPTY};
+      for (int x = 0; x < na_tbl; ++x) t.acc[(u64)x * stride + i] = 0.0;
+      for (int x = 0; x < nc_tbl; ++x) t.cnt[(u64)x * stride + i] = 0;
+    }
+    if (threadIdx.x == 0) *t.n_groups = 0;
+    __syncthreads();
+  }
   if (s_bad) return;
   int err = 0;
   for (int b = 0; b < a.nb; ++b) {
@@ -509,15 +520,15 @@ __global__ void __launch_bounds__(1024) final_tiny_kernel(const __grid_constant_
         const TinyCol& vc = tb.val[x];
         if (!vc.data) continue;
         const bool ok = !vc.valid || vc.valid[r];
-        if (ok) red_add_f64(&t.acc[(u64)x * t.cap + slot], ((const double*)vc.data)[r]);
-        if (a.vslot[x] >= 0 && ok) red_add_u64(&t.cnt[(u64)a.vslot[x] * t.cap + slot], 1ull);
+        if (ok) red_add_f64(&t.acc[(u64)x * stride + slot], ((const double*)vc.data)[r]);
+        if (a.vslot[x] >= 0 && ok) red_add_u64(&t.cnt[(u64)a.vslot[x] * stride + slot], 1ull);
       }
       for (int x = 0; x < a.nc; ++x) {
         const TinyCol& cc = tb.cnt[x];
         if (!cc.data) continue;
         const bool ok = !cc.valid || cc.valid[r];
-        if (ok) red_add_u64(&t.cnt[(u64)x * t.cap + slot], ((const u64*)cc.data)[r]);
-        if (a.cvslot[x] >= 0 && ok) red_add_u64(&t.cnt[(u64)a.cvslot[x] * t.cap + slot], 1ull);
+        if (ok) red_add_u64(&t.cnt[(u64)x * stride + slot], ((const u64*)cc.data)[r]);
+        if (a.cvslot[x] >= 0 && ok) red_add_u64(&t.cnt[(u64)a.cvslot[x] * stride + slot], 1ull);
       }
     }
   }

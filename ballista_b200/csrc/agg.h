@@ -164,6 +164,7 @@ struct TinyBatch {
 };
 struct TinyArgs {
   int nb, nkeys, na, nc, init;
+  int single;  // this launch holds every input batch: the hashed part of the table is sized from the rows present
   int part_dtype[8], part_off[8], part_bytes[8];
   int vslot[8];    // count slot that receives the number of non-NULL rows of value a, or -1
   int cvslot[12];  // likewise for an integer-sum column

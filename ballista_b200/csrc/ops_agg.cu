@@ -466,6 +466,7 @@ BatchPtr HashAggregateExec::run_final(int partition, bool speculate) {
       ta.na = n_acc;
       ta.nc = n_cnt;
       ta.init = b0 == 0;
+      ta.single = all.size() <= (size_t)TINY_BATCHES;
       for (size_t g = 0; g < ng; ++g) {
         ta.part_dtype[g] = layout.parts[g].dtype;
         ta.part_off[g] = layout.parts[g].byte_off;

@@ -144,7 +144,7 @@ struct HashJoinExec : Op {
                     lk == on_left && rk == on_right;
     }
     for (int p = 0; p < np; ++p) {
-      if (per_rank && p != partition) continue;
+      if (per_rank && p != ctx->rank) continue;  // partition r of an exchange lives on rank r
       StreamPtr s = l->execute(p);
       while (BatchPtr b = s->next())
         if (b->num_rows) all.push_back(b);

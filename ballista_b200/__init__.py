@@ -10,10 +10,11 @@ from .expr import Expr, AggExpr, col, lit, date, case, scalar_fn, sum, avg, coun
 from .plan import (Context, DeviceBatch, ExecutionPlan, RecordBatchStream, MemoryExec, FilterExec,
                    CoalesceBatchesExec, MergeExec, ProjectionExec, HashAggregateExec, HashJoinExec,
                    RepartitionExec, SortExec, GlobalLimitExec, LocalLimitExec, plan_from_proto, describe_plan_proto)
+from .parquet import ParquetFile, ParquetExec
 from . import tpch
 
 __all__ = ["BallistaError", "NotImplementedOnGpu", "Expr", "AggExpr", "col", "lit", "date", "case", "scalar_fn", "sum", "avg", "count",
            "Context", "DeviceBatch", "ExecutionPlan", "RecordBatchStream", "MemoryExec", "FilterExec",
            "CoalesceBatchesExec", "MergeExec", "ProjectionExec", "HashAggregateExec", "HashJoinExec",
            "RepartitionExec", "SortExec", "GlobalLimitExec", "LocalLimitExec", "plan_from_proto",
-           "describe_plan_proto", "tpch"]
+           "describe_plan_proto", "ParquetFile", "ParquetExec", "tpch"]

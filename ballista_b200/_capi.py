@@ -112,6 +112,9 @@ def lib():
         "b2_merge_create": (i32, [vp, vp, P(vp)]),
         "b2_projection_create": (i32, [vp, vp, P(Expr), i32, P(vp)]),
         "b2_csv_decode": (i32, [vp, P(ArrowSchema), P(C.c_int), i32, C.c_char, i32, C.c_char_p, C.c_size_t, P(vp)]),
+        "b2_parquet_describe": (i32, [vp, C.c_size_t, P(i64), P(i32), P(i32), C.c_char_p, C.c_size_t]),
+        "b2_parquet_schema": (i32, [vp, C.c_size_t, P(C.c_int), i32, P(ArrowSchema)]),
+        "b2_parquet_decode": (i32, [vp, vp, C.c_size_t, P(C.c_int), i32, i32, i32, P(vp)]),
         "b2_plan_from_proto": (i32, [vp, C.c_char_p, C.c_size_t, P(vp), i32, P(vp)]),
         "b2_plan_proto_describe": (i32, [C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, P(i32)]),
         "b2_jit_compile_check": (i32, [C.c_char_p, P(C.c_size_t)]),

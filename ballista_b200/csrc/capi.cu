@@ -7,6 +7,7 @@
 
 #include "jit.h"
 #include "ops.h"
+#include "parquet.h"
 
 using namespace b2;
 
@@ -212,6 +213,54 @@ int b2_csv_decode(b2_ctx* ctx, const struct ArrowSchema* file_schema, const int*
       for (size_t i = 0; i < fs.fields.size(); ++i) proj.push_back((int)i);
     auto* h = new b2_batch;
     h->b = csv_decode(&ctx->c, fs, proj, delimiter, has_header != 0, text, len);
+    *out = h;
+  });
+}
+int b2_parquet_describe(const uint8_t* file, size_t len, int64_t* num_rows, int* n_row_groups, int* n_columns,
+                        char* text, size_t cap) {
+  return guard([&] {
+    REQUIRE(file, "null argument");
+    pq::FileMeta m = pq::parse_footer(file, len);
+    if (num_rows) *num_rows = m.num_rows;
+    if (n_row_groups) *n_row_groups = (int)m.row_groups.size();
+    if (n_columns) *n_columns = (int)m.columns.size();
+    if (text && cap > 0) {
+      std::string t = pq::describe(m, file, len);
+      size_t n = t.size() < cap - 1 ? t.size() : cap - 1;
+      memcpy(text, t.data(), n);
+      text[n] = 0;
+    }
+  });
+}
+static std::vector<int> parquet_projection(const pq::FileMeta& m, const int* projection, int n_projection) {
+  std::vector<int> proj;
+  if (projection) proj.assign(projection, projection + n_projection);
+  else
+    for (size_t i = 0; i < m.columns.size(); ++i) proj.push_back((int)i);
+  return proj;
+}
+int b2_parquet_schema(const uint8_t* file, size_t len, const int* projection, int n_projection, struct ArrowSchema* out) {
+  return guard([&] {
+    REQUIRE(file && out && n_projection >= 0, "null argument");
+    pq::FileMeta m = pq::parse_footer(file, len);
+    schema_to_arrow(pq::arrow_schema(m, parquet_projection(m, projection, n_projection)), out);
+  });
+}
+int b2_parquet_decode(b2_ctx* ctx, const uint8_t* file, size_t len, const int* projection, int n_projection,
+                      int row_group_begin, int row_group_end, b2_batch** out) {
+  return guard([&] {
+    REQUIRE(ctx && file && out && n_projection >= 0, "null argument");
+    ctx->c.activate();
+    std::vector<int> proj;
+    if (projection) proj.assign(projection, projection + n_projection);
+    else proj = parquet_projection(pq::parse_footer(file, len), nullptr, 0);
+    auto* h = new b2_batch;
+    try {
+      h->b = parquet_decode(&ctx->c, file, len, proj, row_group_begin, row_group_end);
+    } catch (...) {
+      delete h;
+      throw;
+    }
     *out = h;
   });
 }

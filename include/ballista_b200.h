@@ -184,6 +184,24 @@ int b2_projection_create(b2_ctx* ctx, b2_op* input, const b2_expr* exprs, int n_
  * (YYYY-MM-DD) and Utf8 columns; malformed input is B2_ERR_ARROW with the line number. */
 int b2_csv_decode(b2_ctx* ctx, const struct ArrowSchema* file_schema, const int* projection, int n_projection,
                   char delimiter, int has_header, const char* text, size_t len, b2_batch** out);
+/* Column decode of the ParquetExec leaf (from_proto.rs:111-121: ParquetExec::try_from_files(filenames, projection, None,
+ * batch_size, num_partitions); the benchmark's `--format parquet`) on the GPU.  `file` = the `len` bytes of one whole
+ * Parquet file in host memory (an mmap is fine: only the footer, the page headers and the projected column chunks are
+ * touched).  Flat schemas; BOOLEAN, INT32 (Int32 / Date32), INT64 (Int64 / UInt64), DOUBLE and BYTE_ARRAY (Utf8)
+ * columns, REQUIRED or OPTIONAL; data pages V1 and V2; PLAIN, PLAIN_DICTIONARY / RLE_DICTIONARY (and RLE booleans);
+ * UNCOMPRESSED and SNAPPY.  Anything else is B2_ERR_NOT_IMPLEMENTED naming the feature, a malformed file B2_ERR_ARROW.
+ *   b2_parquet_describe: no device needed; *num_rows / *n_row_groups / *n_columns (each optional) and a text listing of
+ *                        columns, row groups, codecs, encodings and page counts into `text` (optional, NUL-terminated).
+ *   b2_parquet_schema:   Arrow schema of the projected columns (projection NULL = all), names and nullability as in
+ *                        the file (DataFusion's ParquetExec schema).
+ *   b2_parquet_decode:   row groups [row_group_begin, row_group_end) (end < 0 = to the last) of the projected columns
+ *                        as ONE batch in HBM; the file bytes may be released as soon as it returns. */
+int b2_parquet_describe(const uint8_t* file, size_t len, int64_t* num_rows, int* n_row_groups, int* n_columns,
+                        char* text, size_t cap);
+int b2_parquet_schema(const uint8_t* file, size_t len, const int* projection, int n_projection,
+                      struct ArrowSchema* out);
+int b2_parquet_decode(b2_ctx* ctx, const uint8_t* file, size_t len, const int* projection, int n_projection,
+                      int row_group_begin, int row_group_end, b2_batch** out);
 /* Wire compatibility: a serialized `PhysicalPlanNode` (rust/core/proto/ballista.proto:294-422, as the scheduler
  * stores it, rust/scheduler/src/state/mod.rs:149-162) decoded into the operator tree the way the executor does in
  * rust/core/src/serde/physical_plan/from_proto.rs:58-346.  Leaf nodes (CsvScan, ParquetScan, ShuffleReader,

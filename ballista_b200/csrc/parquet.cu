@@ -75,13 +75,18 @@ __device__ __forceinline__ uint32_t pq_le32(const uint8_t* p) {
 //     `offset` bytes, so lane i reads byte i mod offset).
 // Literals with an explicit length (> 60 bytes) end a batch and are moved by the whole warp; above 1 KB straight from
 // HBM to HBM in 16-byte pieces (incompressible pages are chains of 64 KB literals).
-constexpr uint32_t SN_RING = 4096, SN_WIN = 32768, SN_FLUSH = 2048, SN_LONG = 1024;
-constexpr int32_t SN_NEAR = SN_WIN - 2048 - 64;  // a batch writes < 2 KB: positions this close to its start are still in the window
+constexpr uint32_t SN_RING = 4096, SN_FLUSH = 2048, SN_LONG = 1024;
+// The window size is a template parameter: the standard compressor works in 64 KB blocks, so copies reach back up to
+// 64 KB; pages longer than SN_SMALL_PAGE get the 64 KB window (3 pages in flight per SM), the many short ones the 32 KB
+// window (6 per SM), launched side by side on two streams.
+constexpr uint32_t SN_WIN_SMALL = 32768, SN_WIN_LARGE = 65536, SN_SMALL_PAGE = 256 << 10;
+constexpr uint32_t SN_BATCH_SPAN = 2048 + 64;  // a batch writes < 2 KB: positions within WIN - this of its start are still in the window
 
 __device__ __forceinline__ uint4 sn_load16(const uint8_t* buf, uint32_t off, uint32_t buf_len) {
   return off + 16u <= buf_len ? *reinterpret_cast<const uint4*>(buf + off) : make_uint4(0, 0, 0, 0);
 }
 // window -> HBM for output positions [from, to); `out` is 16-byte aligned, so position i is aligned when i is
+template <uint32_t SN_WIN>
 __device__ __forceinline__ void sn_flush(const uint8_t* win, uint8_t* out, uint32_t from, uint32_t to, int lane) {
   uint32_t head = (from + 15u) & ~15u;
   if (head > to) head = to;
@@ -117,10 +122,12 @@ __device__ __forceinline__ void sn_copy_long(uint8_t* dst, const uint8_t* src, u
 }
 // output position p as seen from a batch that starts at `pos`: recent positions are in the window, older ones (and
 // everything before `win_from`, the end of the last literal that bypassed the window) have reached HBM
+template <uint32_t SN_WIN>
 __device__ __forceinline__ uint8_t sn_read(const uint8_t* win, const uint8_t* out, uint32_t p, uint32_t pos, uint32_t win_from) {
-  return (p >= win_from && (int32_t)(pos - p) <= SN_NEAR) ? win[p & (SN_WIN - 1)] : out[p];
+  return (p >= win_from && (int32_t)(pos - p) <= (int32_t)(SN_WIN - SN_BATCH_SPAN)) ? win[p & (SN_WIN - 1)] : out[p];
 }
 
+template <uint32_t SN_WIN>
 __global__ void __launch_bounds__(32)
 pq_snappy_kernel(uint8_t* buf, uint32_t buf_len, const PqPage* __restrict__ pages, const int* __restrict__ list, int* status) {
   extern __shared__ __align__(16) uint8_t sn_smem[];
@@ -165,39 +172,22 @@ pq_snappy_kernel(uint8_t* buf, uint32_t buf_len, const PqPage* __restrict__ page
     stage();
     if (pos - flushed >= SN_FLUSH) {
       const uint32_t to = pos & ~15u;
-      sn_flush(win, out, flushed, to, lane);
+      sn_flush<SN_WIN>(win, out, flushed, to, lane);
       flushed = to;
     }
     // every lane decodes the element that would start at its byte
     const uint32_t a = in + lane;
     const uint32_t t = ring[a & RM];
     const uint32_t b1 = ring[(a + 1) & RM], b2 = ring[(a + 2) & RM], b3 = ring[(a + 3) & RM], b4 = ring[(a + 4) & RM];
-    const uint32_t kind = t & 3;
-    uint32_t len, hdr, off = 0;
-    bool big = false;
-    if (kind == 0) {
-      len = (t >> 2) + 1;
-      hdr = 1;
-      if (len > 60) {  // explicit length, stored minus one in the next 1-4 bytes: kept that way until it is checked
-        big = true;
-        const uint32_t nb = len - 60;
-        len = b1 | b2 << 8 | b3 << 16 | b4 << 24;
-        if (nb < 4) len &= (1u << (8 * nb)) - 1u;
-        hdr = 1 + nb;
-      }
-    } else if (kind == 1) {
-      len = 4 + ((t >> 2) & 7);
-      off = (t >> 5) << 8 | b1;
-      hdr = 2;
-    } else if (kind == 2) {
-      len = (t >> 2) + 1;
-      off = b1 | b2 << 8;
-      hdr = 3;
-    } else {
-      len = (t >> 2) + 1;
-      off = b1 | b2 << 8 | b3 << 16 | b4 << 24;
-      hdr = 5;
-    }
+    // (no branches: the 32 lanes hold all four kinds of element)
+    const uint32_t kind = t & 3, t2 = t >> 2;
+    const uint32_t w4 = b1 | b2 << 8 | b3 << 16 | b4 << 24;
+    const bool lit = kind == 0;
+    const bool big = lit && t2 >= 60;  // explicit length, stored minus one in the next 1-4 bytes: kept that way until checked
+    const uint32_t nb = t2 - 59;
+    const uint32_t len = lit ? (big ? (nb < 4 ? w4 & ((1u << (8 * nb)) - 1u) : w4) : t2 + 1) : (kind == 1 ? 4 + (t2 & 7) : t2 + 1);
+    const uint32_t hdr = lit ? (big ? 1 + nb : 1) : (kind == 3 ? 5 : kind + 1);
+    const uint32_t off = lit ? 0 : (kind == 1 ? ((t >> 5) << 8 | b1) : (kind == 2 ? (w4 & 0xFFFFu) : w4));
     if (__shfl_sync(FULL, (int)big, 0)) {
       // a long literal at the head of the stream: the whole warp moves it
       uint32_t l = __shfl_sync(FULL, len, 0);
@@ -206,7 +196,7 @@ pq_snappy_kernel(uint8_t* buf, uint32_t buf_len, const PqPage* __restrict__ page
       l += 1;
       const uint32_t src = in + h;
       if (l > SN_LONG) {
-        sn_flush(win, out, flushed, pos, lane);
+        sn_flush<SN_WIN>(win, out, flushed, pos, lane);
         sn_copy_long(out + pos, buf + src, l, lane);
         flushed = win_from = pos + l;
       } else if (src + l <= staged) {
@@ -219,13 +209,14 @@ pq_snappy_kernel(uint8_t* buf, uint32_t buf_len, const PqPage* __restrict__ page
       __syncwarp();
       continue;
     }
-    // which lanes start an element: reachability from lane 0 over the "next element" links, by pointer doubling
+    // which lanes start an element: reachability from lane 0 over the "next element" links, by pointer doubling.
+    // An element takes at least 2 input bytes, so at most 15 links lie inside the 32 bytes: 4 rounds (1 + 2 + 4 + 8).
     const bool valid = a < in_end;
-    const uint32_t adv = hdr + (kind == 0 && !big ? len : 0);
+    const uint32_t adv = hdr + (lit && !big ? len : 0);
     uint32_t jump = valid && !big ? min(lane + adv, 32u) : 32u;
     uint32_t reach = 1;
 #pragma unroll
-    for (int r = 0; r < 5; ++r) {
+    for (int r = 0; r < 4; ++r) {
       reach |= __reduce_or_sync(FULL, ((reach >> lane) & 1u) && jump < 32u ? 1u << jump : 0u);
       const uint32_t j2 = __shfl_sync(FULL, jump, jump & 31u);
       jump = jump < 32u ? j2 : 32u;
@@ -248,36 +239,43 @@ pq_snappy_kernel(uint8_t* buf, uint32_t buf_len, const PqPage* __restrict__ page
     }
     const uint32_t tot = __shfl_sync(FULL, incl, 31);
     const uint32_t d0 = pos + incl - (is_elem ? len : 0u);  // this element's output position
-    const bool lit = kind == 0;
     const bool err = is_elem && (hdr > in_end - a || (lit ? len > in_end - a - hdr : (off == 0 || off > d0)));
     if (__any_sync(FULL, err) || tot > out_len - pos) return pq_fail(status, PQ_BAD_SNAPPY, pi);
     const uint32_t from = d0 - off;
-    // short elements that read nothing this batch writes: each by its own lane, all at once
-    const bool alone = is_elem && len <= 12 && (lit || from + min(len, off) <= pos);
+    // Short elements that read nothing this batch writes (and do not wrap in either ring): each by its own lane, all at
+    // once, up to 12 independent byte loads then stores.  Source as an offset into sn_smem: input ring or window.
+    const uint32_t dst_at = SN_RING + (d0 & WM);
+    const uint32_t src_at = lit ? ((a + hdr) & RM) : SN_RING + (from & WM);
+    const bool alone = is_elem && len <= 12 && dst_at + len <= SN_RING + SN_WIN &&
+                       (lit ? src_at + len <= SN_RING
+                            : (off >= len && from + len <= pos && from >= win_from &&
+                               pos - from <= SN_WIN - SN_BATCH_SPAN && src_at + len <= SN_RING + SN_WIN));
     if (alone) {
-      if (lit) {
-        const uint32_t s = a + hdr;
-        for (uint32_t i = 0; i < len; ++i) win[(d0 + i) & WM] = ring[(s + i) & RM];
-      } else {
-        for (uint32_t i = 0; i < len; ++i) win[(d0 + i) & WM] = sn_read(win, out, from + i, pos, win_from);
-      }
+      uint8_t v[12];
+#pragma unroll
+      for (int i = 0; i < 12; ++i)
+        if (i < (int)len) v[i] = sn_smem[src_at + i];
+#pragma unroll
+      for (int i = 0; i < 12; ++i)
+        if (i < (int)len) sn_smem[dst_at + i] = v[i];
     }
     __syncwarp();
     // the others in stream order, each by the whole warp
     uint32_t rest = __ballot_sync(FULL, is_elem && !alone);
+    const uint32_t meta = len | (lit ? 0x100u : 0u), what = lit ? a + hdr : off;
     while (rest) {
       const int e = __ffs(rest) - 1;
       rest &= rest - 1;
-      const uint32_t el = __shfl_sync(FULL, len, e), ed = __shfl_sync(FULL, d0, e);
-      if (__shfl_sync(FULL, (int)lit, e)) {
-        const uint32_t es = __shfl_sync(FULL, a + hdr, e);
-        for (uint32_t i = lane; i < el; i += 32) win[(ed + i) & WM] = ring[(es + i) & RM];
+      const uint32_t em = __shfl_sync(FULL, meta, e), ed = __shfl_sync(FULL, d0, e), ew = __shfl_sync(FULL, what, e);
+      const uint32_t el = em & 0xFFu;
+      if (em & 0x100u) {
+        for (uint32_t i = lane; i < el; i += 32) win[(ed + i) & WM] = ring[(ew + i) & RM];
       } else {
-        const uint32_t eo = __shfl_sync(FULL, off, e), ef = ed - eo;
-        if (eo >= el) {
-          for (uint32_t i = lane; i < el; i += 32) win[(ed + i) & WM] = sn_read(win, out, ef + i, pos, win_from);
+        const uint32_t ef = ed - ew;
+        if (ew >= el) {
+          for (uint32_t i = lane; i < el; i += 32) win[(ed + i) & WM] = sn_read<SN_WIN>(win, out, ef + i, pos, win_from);
         } else {
-          for (uint32_t i = lane; i < el; i += 32) win[(ed + i) & WM] = sn_read(win, out, ef + i % eo, pos, win_from);
+          for (uint32_t i = lane; i < el; i += 32) win[(ed + i) & WM] = sn_read<SN_WIN>(win, out, ef + i % ew, pos, win_from);
         }
       }
       __syncwarp();
@@ -286,7 +284,7 @@ pq_snappy_kernel(uint8_t* buf, uint32_t buf_len, const PqPage* __restrict__ page
     in += exit_rel;
   }
   __syncwarp();
-  sn_flush(win, out, flushed, pos, lane);
+  sn_flush<SN_WIN>(win, out, flushed, pos, lane);
   if (pos != out_len) pq_fail(status, PQ_BAD_SNAPPY, pi);
 }
 
@@ -812,9 +810,40 @@ BatchPtr parquet_decode(Ctx* ctx, const uint8_t* file, size_t len, const std::ve
   const int* l_dict = l_snappy + snappy_list.size();
   const int* l_data = l_dict + dict_list.size();
   if (!snappy_list.empty()) {
-    pq_snappy_kernel<<<(unsigned)snappy_list.size(), 32, SN_RING + SN_WIN, ctx->stream>>>(
-        buf->as<uint8_t>(), (uint32_t)(dev_bytes + 64) & ~15u, d_pages->as<PqPage>(), l_snappy, status);
-    B2_LAUNCHED(ctx);
+    // snappy_list is sorted by size: [0, n_large) use the 64 KB window on the main stream, the rest the 32 KB window on
+    // the second stream, both after the copies above and both before the decode below
+    size_t n_large = 0;
+    while (n_large < snappy_list.size() && pages[snappy_list[n_large]].data_len > SN_SMALL_PAGE) ++n_large;
+    const size_t n_small = snappy_list.size() - n_large;
+    const uint32_t buf_len = (uint32_t)(dev_bytes + 64) & ~15u;
+    static bool attr_set = false;
+    if (!attr_set) {
+      B2_CUDA(cudaFuncSetAttribute(pq_snappy_kernel<SN_WIN_LARGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SN_RING + SN_WIN_LARGE));
+      attr_set = true;
+    }
+    cudaEvent_t fork = nullptr, join = nullptr;
+    if (n_small && n_large) {
+      B2_CUDA(cudaEventCreateWithFlags(&fork, cudaEventDisableTiming));
+      B2_CUDA(cudaEventCreateWithFlags(&join, cudaEventDisableTiming));
+      B2_CUDA(cudaEventRecord(fork, ctx->stream));
+      B2_CUDA(cudaStreamWaitEvent(ctx->copy_stream, fork, 0));
+    }
+    if (n_large) {
+      pq_snappy_kernel<SN_WIN_LARGE><<<(unsigned)n_large, 32, SN_RING + SN_WIN_LARGE, ctx->stream>>>(
+          buf->as<uint8_t>(), buf_len, d_pages->as<PqPage>(), l_snappy, status);
+      B2_LAUNCHED(ctx);
+    }
+    if (n_small) {
+      pq_snappy_kernel<SN_WIN_SMALL><<<(unsigned)n_small, 32, SN_RING + SN_WIN_SMALL, n_large ? ctx->copy_stream : ctx->stream>>>(
+          buf->as<uint8_t>(), buf_len, d_pages->as<PqPage>(), l_snappy + n_large, status);
+      B2_LAUNCHED(ctx);
+    }
+    if (fork) {
+      B2_CUDA(cudaEventRecord(join, ctx->copy_stream));
+      B2_CUDA(cudaStreamWaitEvent(ctx->stream, join, 0));
+      cudaEventDestroy(fork);
+      cudaEventDestroy(join);
+    }
   }
   if (!dict_list.empty()) {
     pq_dict_kernel<<<(unsigned)dict_list.size(), PQ_THREADS, 0, ctx->stream>>>(

@@ -4,8 +4,8 @@ The reference builds this leaf as `ParquetExec::try_from_files(filenames, projec
 (rust/core/src/serde/physical_plan/from_proto.rs:111-121; message `ParquetScanExecNode { filename, projection,
 num_partitions, batch_size }`, rust/core/proto/ballista.proto:325-330).  DataFusion@46161d2 splits the file list into
 `num_partitions` contiguous chunks of ceil(n_files / num_partitions) files, one output partition per chunk; each file's
-row groups are read in order.  `ParquetExec` here keeps exactly that partitioning; one batch per row group instead of
-`batch_size`-row batches (the operators above take whole batches; CoalesceBatchesExec is a no-op on them).
+row groups are read in order.  `ParquetExec` here keeps exactly that partitioning; one batch per file (per ~3 GB of file)
+instead of `batch_size`-row batches (the operators above take whole batches; CoalesceBatchesExec is a no-op on them).
 """
 import ctypes as C
 import mmap
@@ -103,6 +103,20 @@ class ParquetFile:
         return DeviceBatch(ctx, h)
 
 
+def _read_batches(self, ctx, projection=None, max_bytes=3 << 30):
+    """The whole file as few DeviceBatches as the 4 GiB-per-call limit allows (normally one): the pages of all row
+    groups decode side by side, so the longest page chain is paid once per call, not once per row group."""
+    if self.num_row_groups == 0:
+        return [self.read(ctx, projection)]
+    per_group = max(self._len // max(self.num_row_groups, 1), 1)
+    step = max(int(max_bytes // per_group), 1)
+    return [self.read(ctx, projection, (g, min(g + step, self.num_row_groups)))
+            for g in range(0, self.num_row_groups, step)]
+
+
+ParquetFile.read_batches = _read_batches
+
+
 def split_files(filenames, n):
     """DataFusion's split_files: contiguous chunks of ceil(len / n) files."""
     filenames = list(filenames)
@@ -130,8 +144,7 @@ class ParquetExec(MemoryExec):
                 f = first if name == filenames[0] else ParquetFile(name)
                 if f.schema(projection) != schema:
                     raise K.BallistaError(f"Parquet file {name} has a different schema")
-                for g in range(f.num_row_groups):
-                    batches.append(f.read(ctx, projection, (g, g + 1)))
+                batches.extend(f.read_batches(ctx, projection))
             parts.append(batches)
         self.filenames, self.projection, self.batch_size = list(filenames), projection, batch_size
         super().__init__(ctx, schema, parts)

@@ -908,9 +908,65 @@ def run_other_configs(args, env):
     out["q5"] = q5_run(sf, f"q5_sf{sf:g}")
     if args.q3_sf > sf:
         out[f"q5_sf{args.q3_sf:g}"] = q5_run(args.q3_sf, f"q5_sf{args.q3_sf:g}")
+    if world == 1:
+        out["parquet_ingest"] = run_parquet_ingest(env, check=not args.no_parity)
     if world > 1:
         out.update(run_multi_gpu_configs(args, env, O, timeit))
     return out
+
+
+def run_parquet_ingest(env, sf=1.0, check=True):
+    """the ParquetExec leaf's column decode on the GPU.  A lineitem SF1 file written the way the reference's
+    `convert` command writes it (snappy pages, dictionary coding, the benchmark's REQUIRED columns; main.rs:233-252),
+    read into page-locked memory, decoded by b2_parquet_decode; pyarrow's reader on the same bytes is both the parity
+    check (every column bit-exact) and the CPU baseline."""
+    import io
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    import ballista_b200 as b2
+    ctx = env.ctx
+    table = pa.Table.from_batches([ctx.tpch("lineitem", sf).to_arrow()])
+    bio = io.BytesIO()
+    pq.write_table(table, bio, compression="snappy", use_dictionary=True)
+    data = bio.getvalue()
+    f = b2.ParquetFile(data, pinned_by=ctx)
+    times = []
+    for _ in range(6):
+        ctx.synchronize()
+        t0 = time.perf_counter()
+        dev = f.read(ctx)
+        ctx.synchronize()
+        times.append((time.perf_counter() - t0) * 1e3)
+        out_bytes = dev.num_bytes
+        got = dev.to_arrow() if check and len(times) == 1 else None
+        if got is not None:
+            first = got
+        del dev
+    times = sorted(times[1:])
+    cpu = {}
+    for threads in (False, True):
+        best = None
+        for _ in range(2):
+            t0 = time.perf_counter()
+            ref = pq.read_table(io.BytesIO(data), use_threads=threads)
+            dt = (time.perf_counter() - t0) * 1e3
+            best = dt if best is None or dt < best else best
+        cpu[threads] = best
+    res = {"workload": f"lineitem SF{sf:g} ({table.num_rows} rows x {table.num_columns} columns) as one Parquet file: snappy pages, "
+                       "dictionary coding, REQUIRED columns; file bytes in page-locked host memory -> columns in HBM",
+           "file_MB": len(data) / 1e6, "decoded_MB": out_bytes / 1e6, "ms_best": times[0], "ms_median": times[len(times) // 2],
+           "decoded_GB_per_s": out_bytes / (times[0] / 1e3) / 1e9,
+           "cpu_reader": {"what": "pyarrow.parquet.read_table on the same bytes (Arrow C++ reader)",
+                          "ms_1_thread": cpu[False], "ms_all_threads": cpu[True], "threads": os.cpu_count()}}
+    if check:
+        ref = ref.combine_chunks()
+        same = [first.column(i).equals(ref.column(i).chunk(0) if ref.column(i).num_chunks else pa.array([], ref.schema.field(i).type))
+                for i in range(ref.num_columns)]
+        res["parity"] = {"config": f"parquet_ingest_sf{sf:g}", "input_rows": int(table.num_rows), "columns": len(same),
+                         "keys_equal": bool(all(same)), "counts_equal": bool(first.num_rows == ref.num_rows), "max_rel_err": 0.0,
+                         "tolerance": 0.0, "ok": bool(all(same) and first.num_rows == ref.num_rows),
+                         "checker": "pyarrow.parquet reader on the same file bytes, every column Array.equals (bit-exact)"}
+    return res
 
 
 def run_multi_gpu_configs(args, env, O, timeit):

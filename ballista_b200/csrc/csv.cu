@@ -122,8 +122,8 @@ __device__ int csv_parse_field(const char* __restrict__ text, int64_t b, int64_t
   for (; i < e; ++i) {
     int dgt = text[i] - '0';
     if (dgt < 0 || dgt > 9) return CSV_BAD_NUMBER;
+    if (acc > ((1ull << 62) - 9) / 10) return CSV_BAD_NUMBER;  // checked before the multiply: 20-digit fields must not wrap
     acc = acc * 10 + (unsigned)dgt;
-    if (acc > (1ull << 62)) return CSV_BAD_NUMBER;
   }
   long long v = neg ? -(long long)acc : (long long)acc;
   if (dtype == B2_INT32) {

@@ -1,6 +1,6 @@
 """Throughput of the GPU .tbl decode (host text in, device columns out) beside pyarrow's multi-threaded CSV reader."""
 import io, sys, time, os
-sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..")); sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", "tests"))
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", "..")); sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", "..", "tests"))
 import pyarrow as pa, pyarrow.csv
 from test_gpu_csv import tbl_text, LINEITEM, arrow_read
 import ballista_b200 as b2

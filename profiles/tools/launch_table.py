@@ -1,4 +1,4 @@
-"""per-launch time + DRAM bytes of the last N launches of an ncu csv: python scratch/launch_table.py file.csv N"""
+"""per-launch time + DRAM bytes of the last N launches of an ncu csv: python profiles/tools/launch_table.py file.csv N"""
 import csv, sys
 lines = [l for l in open(sys.argv[1]) if not l.startswith('==')]
 by = {}

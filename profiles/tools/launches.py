@@ -1,4 +1,4 @@
-"""print the last N launches of an ncu gpu__time_duration launch list: python scratch/launches.py file.csv N"""
+"""print the last N launches of an ncu gpu__time_duration launch list: python profiles/tools/launches.py file.csv N"""
 import csv, sys
 lines = [l for l in open(sys.argv[1]) if not l.startswith('==')]
 L = [x for x in csv.DictReader(lines) if x.get('Metric Name') == 'gpu__time_duration.sum']

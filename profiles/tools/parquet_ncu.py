@@ -1,6 +1,6 @@
 """One decode of a pyarrow-default (snappy + dictionary) lineitem file, for an ncu launch list."""
 import io, os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import pyarrow as pa, pyarrow.parquet as pq
 import ballista_b200 as b2
 sf = float(sys.argv[1]) if len(sys.argv) > 1 else 1.0

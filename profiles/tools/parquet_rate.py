@@ -1,6 +1,6 @@
 """Parquet decode rate on the GPU against pyarrow's reader on the host: lineitem SF1 written by pyarrow."""
 import io, os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import pyarrow as pa, pyarrow.parquet as pq
 import ballista_b200 as b2
 

@@ -1,6 +1,6 @@
 """torchrun: per-stage wall time (synchronised after every stage) of the broadcast-join Q3 plan."""
 import os, sys, time, gc
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch, torch.distributed as dist
 import pyarrow as pa
 import ballista_b200 as b2

@@ -1,7 +1,7 @@
 """torchrun: time distributed Q3 over an SF<total> database (row-range partitions per rank), with the host trace of rank 0.
-usage: torchrun ... scratch/q3_dist_time.py <total_sf> <steps>"""
+usage: torchrun ... profiles/tools/q3_dist_time.py <total_sf> <steps>"""
 import os, sys, time, gc
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch, torch.distributed as dist
 import ballista_b200 as b2
 from ballista_b200 import MemoryExec, cluster, tpch

@@ -1,4 +1,4 @@
-"""group the SASS page of an ncu report into runs of equal execution count: python scratch/sass_blocks.py rep.ncu-rep [kernel_index]"""
+"""group the SASS page of an ncu report into runs of equal execution count: python profiles/tools/sass_blocks.py rep.ncu-rep [kernel_index]"""
 import sys, csv, subprocess
 from collections import Counter
 out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "source", "--csv"], capture_output=True, text=True).stdout

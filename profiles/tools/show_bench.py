@@ -1,4 +1,4 @@
-"""Compact view of a bench.py JSON line: python scratch/show_bench.py gpurun_out/bench_n1.json"""
+"""Compact view of a bench.py JSON line: python profiles/tools/show_bench.py gpurun_out/bench_n1.json"""
 import json, sys
 d = json.load(open(sys.argv[1]))
 print(f"N={d['n_gpus']} value={d['value']:.4g} {d['unit']}  ms/step={d['ms_per_step']:.3f} median={d['step_ms']['median_ms']:.3f} best={d['step_ms']['best_ms']:.3f} launches/step={d['gpu_launches']/d['steps']:.1f}")

@@ -1,14 +1,14 @@
 """Hash-repartition shuffle (BASELINE config 5): RepartitionExec(Hash(l_orderkey), N) over this rank's lineitem
 partition (l_orderkey, l_extendedprice, l_discount = 20 B/row), exchanged inside the box.
 
-    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 scratch/shuffle_bench.py [sf_per_gpu] [steps]
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 profiles/tools/shuffle_bench.py [sf_per_gpu] [steps]
 """
 import json
 import os
 import sys
 import time
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 import torch.distributed as dist
 

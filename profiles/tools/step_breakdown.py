@@ -1,6 +1,6 @@
 """Where a cached-plan Q6 / Q1 step spends its host time (wall clock per phase; the GPU runs asynchronously)."""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import ballista_b200 as b2
 from ballista_b200 import tpch, MemoryExec
 

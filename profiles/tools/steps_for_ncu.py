@@ -1,6 +1,6 @@
-"""A few steps of Q1 / Q6 / Q3 for an ncu launch list: python scratch/steps_for_ncu.py <sf> <steps>"""
+"""A few steps of Q1 / Q6 / Q3 for an ncu launch list: python profiles/tools/steps_for_ncu.py <sf> <steps>"""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import ballista_b200 as b2
 from ballista_b200 import tpch, MemoryExec
 ctx = b2.Context(0)

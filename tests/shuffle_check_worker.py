@@ -1,7 +1,7 @@
 """N-rank correctness check of the in-box shuffle (torchrun): the multiset of full rows is preserved bit-exactly,
 equal keys land on one rank, row order inside (source, destination) is kept.  Runs both exchange paths.
 
-    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 scratch/shuffle_check.py
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/shuffle_check_worker.py
 """
 import os
 import sys

@@ -147,6 +147,7 @@ def lib():
         "b2_comm_destroy": (i32, [vp]),
         "b2_comm_allgather_batch": (i32, [vp, vp, P(vp)]),
         "b2_comm_bytes_sent": (i64, [vp]),
+        "b2_hash_split_i32_static": (i32, [i32, vp, vp, i64, i32, vp, vp]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(L, name)  # AttributeError here = header/library mismatch: fail loudly

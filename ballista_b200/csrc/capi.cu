@@ -513,4 +513,11 @@ int b2_comm_allgather_batch(b2_ctx* ctx, b2_batch* local, b2_batch** out) {
 }
 int64_t b2_comm_bytes_sent(b2_ctx* ctx) { return ctx ? ctx->c.bytes_sent : 0; }
 
+int b2_hash_split_i32_static(int device, void* cuda_stream, const int32_t* keys, int64_t n_rows, int n_out,
+                             uint32_t* perm, int64_t* starts) {
+  return guard([&] {
+    hash_split_i32_static(device, static_cast<cudaStream_t>(cuda_stream), keys, n_rows, n_out, perm, starts);
+  });
+}
+
 }  // extern "C"

@@ -98,6 +98,11 @@ BufPtr hash_split_perm(Ctx* ctx, const SplitState& st);
 // moves fixed-width columns to dst[c] + base[c * n_out + d] + k * width[c] (k = rank inside destination d's slice)
 void hash_split_move(Ctx* ctx, const SplitState& st, int n_cols, const void* const* src, void* const* dst,
                      const int* width, const int64_t* base_dev, uint32_t* perm_or_null, int64_t n_live = -1);
+// allocation-free split of one Int32 / Date32 key column: scratch in a file-scope device array (repartition.cu), at most
+// hash_split_i32_static_max_rows() rows per call; perm = destination-major stable row ids, starts = n_out + 1 slice starts
+void hash_split_i32_static(int device, cudaStream_t stream, const int32_t* keys, int64_t n, int n_out, uint32_t* perm,
+                           int64_t* starts);
+int64_t hash_split_i32_static_max_rows();
 
 // SortExec support (repartition.cu): order-preserving 64-bit key words per sort column, stable LSD radix sort
 void sort_key_words(Ctx* ctx, const Column& c, bool descending, std::vector<BufPtr>* words, std::vector<int>* bits,

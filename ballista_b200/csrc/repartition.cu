@@ -4,6 +4,8 @@
 // single gather and each destination's rows are one contiguous slice (the send segment of the all-to-all).
 // Beyond 32 output partitions the permutation falls back to one compaction scan per destination.
 #include <cstring>
+#include <mutex>
+#include <string>
 
 #include "ops.h"
 #include "rowpred.cuh"
@@ -598,6 +600,83 @@ BatchPtr slice_batch(Ctx* ctx, const Batch& b, int64_t begin, int64_t end) {
     out->cols.push_back(std::move(o));
   }
   return out;
+}
+
+
+// ---- allocation-free hash split of one Int32 / Date32 key column (b2_hash_split_i32_static) ----
+// Same two passes as hash_split_begin + hash_split_perm, but the destination bytes and the per-tile histogram live in a
+// file-scope device array instead of stream-ordered allocations, so the call can sit inside a CUDA graph capture or a
+// serving loop that may not allocate.  Every GPU that loads the library holds the array (~4.5 MiB) until exit.  All calls
+// on one device share it: calls whose kernels overlap on the GPU (different streams) race; calls on one stream are fine.
+constexpr int64_t SPLIT_STATIC_MAX_ROWS = int64_t(1) << 22;
+constexpr int64_t SPLIT_STATIC_MAX_TILES = SPLIT_STATIC_MAX_ROWS / RP_TILE;
+struct SplitStaticScratch {
+  int64_t hist[RP_MAX_OUT * SPLIT_STATIC_MAX_TILES + 2];  // destination-major tile counts, scanned in place (+ total)
+  uint8_t dest[SPLIT_STATIC_MAX_ROWS + 16];               // destination byte per row
+};
+static __device__ __align__(256) unsigned char g_split_static[sizeof(SplitStaticScratch)];
+
+// The array's name is a host-side stand-in in host code: its device address is looked up once per device, with that
+// device current, and kept here.
+constexpr int SPLIT_STATIC_MAX_DEVICES = 64;
+static std::mutex g_split_static_mu;
+static SplitStaticScratch* g_split_static_ptr[SPLIT_STATIC_MAX_DEVICES];
+static int g_split_static_sms[SPLIT_STATIC_MAX_DEVICES];
+
+struct DeviceGuard {  // makes `device` current for the scope and restores the caller's device
+  int prev = -1;
+  explicit DeviceGuard(int device) {
+    B2_CUDA(cudaGetDevice(&prev));
+    if (prev != device) B2_CUDA(cudaSetDevice(device));
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+int64_t hash_split_i32_static_max_rows() { return SPLIT_STATIC_MAX_ROWS; }
+
+void hash_split_i32_static(int device, cudaStream_t stream, const int32_t* keys, int64_t n, int n_out, uint32_t* perm,
+                           int64_t* starts) {
+  if (device < 0 || device >= SPLIT_STATIC_MAX_DEVICES) fail(B2_ERR_INVALID_ARG, "b2_hash_split_i32_static: device out of range");
+  if (n_out < 1 || n_out > RP_MAX_OUT) fail(B2_ERR_INVALID_ARG, "b2_hash_split_i32_static supports 1..32 output partitions");
+  if (n < 0) fail(B2_ERR_INVALID_ARG, "b2_hash_split_i32_static: negative row count");
+  if (n > SPLIT_STATIC_MAX_ROWS)
+    fail(B2_ERR_INVALID_ARG, "b2_hash_split_i32_static: " + std::to_string(n) + " rows exceed the static scratch's maximum of " +
+                                 std::to_string(SPLIT_STATIC_MAX_ROWS) + " rows per call (split the batch, or use RepartitionExec)");
+  if (!starts || (n && (!keys || !perm))) fail(B2_ERR_INVALID_ARG, "b2_hash_split_i32_static: null pointer");
+  DeviceGuard on(device);
+  SplitStaticScratch* sc;
+  int sms;
+  {
+    std::lock_guard<std::mutex> lock(g_split_static_mu);
+    if (!g_split_static_ptr[device]) {
+      void* p = nullptr;
+      B2_CUDA(cudaGetSymbolAddress(&p, g_split_static));
+      int v = 0;
+      B2_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device));
+      g_split_static_sms[device] = v;
+      g_split_static_ptr[device] = static_cast<SplitStaticScratch*>(p);
+    }
+    sc = g_split_static_ptr[device];
+    sms = g_split_static_sms[device];
+  }
+  const int64_t n_tiles = (n + RP_TILE - 1) / RP_TILE;
+  // the array keeps the previous call's contents: the counts this call scans start at zero
+  B2_CUDA(cudaMemsetAsync(sc->hist, 0, (size_t)(n_tiles * n_out + 2) * 8, stream));
+  if (n) {
+    int64_t grid = std::min<int64_t>(n_tiles, (int64_t)sms * 8);
+    rp_hist_kernel<<<(unsigned)grid, RP_THREADS, 0, stream>>>(KeySrc{nullptr, keys, false}, RowPred(), nullptr,
+                                                             SemiArgs{nullptr, 0, {0}}, n, n_out, sc->dest, sc->hist, n_tiles);
+    B2_CUDA(cudaGetLastError());
+    scan_i64_kernel<<<1, SC_THREADS, 0, stream>>>(sc->hist, n_tiles * n_out);
+    B2_CUDA(cudaGetLastError());
+    rp_scatter_kernel<<<(unsigned)grid, RP_THREADS, 0, stream>>>(sc->dest, n, n_out, sc->hist, n_tiles, perm);
+    B2_CUDA(cudaGetLastError());
+  }
+  rp_starts_kernel<<<1, 64, 0, stream>>>(sc->hist, n_tiles, n_out, n, starts);
+  B2_CUDA(cudaGetLastError());
 }
 
 }  // namespace b2

@@ -290,6 +290,26 @@ int b2_comm_allgather_batch(b2_ctx* ctx, b2_batch* local, b2_batch** out);
 /* bytes this ctx sent over NVLink so far (shuffle roofline accounting) */
 int64_t b2_comm_bytes_sent(b2_ctx* ctx);
 
+/* ---- allocation-free entry point ----
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The hash split of RepartitionExec(Partitioning::Hash) over ONE Int32 / Date32 key column, with every intermediate
+ * (destination byte per row, per-tile histogram) in a file-scope device array of the library instead of an
+ * allocation: the call makes no cudaMalloc / cudaFree / allocating library call, creates no context object and does
+ * not synchronise; it enqueues a memset and four kernels on `cuda_stream` of `device`.
+ *   keys   [n_rows]      device, in : the key column's values
+ *   perm   [n_rows]      device, out: row ids, destination-major; inside a destination the input order is kept
+ *                                     (row perm[i] for starts[d] <= i < starts[d+1] goes to output partition d —
+ *                                     the same rows in the same order as b2_repartition_create's partition d)
+ *   starts [n_out + 1]   device, out: slice starts; starts[n_out] = n_rows
+ * Limits: 0 <= n_rows <= 4,194,304 (2^22) and 1 <= n_out <= 32; beyond either the call returns B2_ERR_INVALID_ARG
+ * and launches nothing.  The scratch array (about 4.5 MiB) is held by every GPU that loads the library until the
+ * process exits.  All calls on one device share it: calls that overlap on the GPU (different streams, or replays of
+ * two captured graphs at once) race and produce garbage; calls ordered on one stream are safe.  The first call on a
+ * device looks the array's device address up (cudaGetSymbolAddress): make that call outside a graph capture. */
+int b2_hash_split_i32_static(int device, void* cuda_stream, const int32_t* keys, int64_t n_rows, int n_out,
+                             uint32_t* perm, int64_t* starts);
+
 #ifdef __cplusplus
 }
 #endif

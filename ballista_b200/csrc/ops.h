@@ -98,6 +98,10 @@ BufPtr hash_split_perm(Ctx* ctx, const SplitState& st);
 // moves fixed-width columns to dst[c] + base[c * n_out + d] + k * width[c] (k = rank inside destination d's slice)
 void hash_split_move(Ctx* ctx, const SplitState& st, int n_cols, const void* const* src, void* const* dst,
                      const int* width, const int64_t* base_dev, uint32_t* perm_or_null, int64_t n_live = -1);
+// push form (the exchange's remote stores): addr_dev[c * n_out + d] = absolute address of this source's first element of
+// column c at destination d; a tile's values are staged destination-major in shared memory and written in whole runs
+void hash_split_push(Ctx* ctx, const SplitState& st, int n_cols, const void* const* src, const int* width,
+                     const int64_t* addr_dev, int64_t n_live = -1);
 // allocation-free split of one Int32 / Date32 key column: scratch in a file-scope device array (repartition.cu), at most
 // hash_split_i32_static_max_rows() rows per call; perm = destination-major stable row ids, starts = n_out + 1 slice starts
 void hash_split_i32_static(int device, cudaStream_t stream, const int32_t* keys, int64_t n, int n_out, uint32_t* perm,
@@ -120,7 +124,7 @@ BatchPtr comm_all_to_all(Ctx* ctx, const Batch& permuted, const std::vector<int6
 // shuffle.cu: the same exchange over CUDA-IPC peer memory (columns moved into a peer-mapped arena by the split's
 // second phase + one NVLink pull kernel).  Takes the unpermuted batch and phase 1 of its split.
 // nullptr = peer mapping unavailable.
-BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st);
+BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st, bool* pushed = nullptr);
 
 // ---- RecordBatchStream ----
 struct Stream {

@@ -536,9 +536,10 @@ struct RepartitionExec : Op {
       BatchPtr got;
       if (n_out <= 32) {
         SplitState st = split_begin(*local, pred);
-        got = comm_shuffle_p2p(ctx, *moved, st);
+        bool pushed = false;
+        got = comm_shuffle_p2p(ctx, *moved, st, &pushed);
         if (got) {
-          last_path = pred ? "nvlink-peer-pull+fused-filter" : "nvlink-peer-pull";
+          last_path = std::string(pushed ? "nvlink-peer-push" : "nvlink-peer-pull") + (pred ? "+fused-filter" : "");
         } else {
           std::vector<int64_t> counts;
           BufPtr perm = hash_split_perm(ctx, st);

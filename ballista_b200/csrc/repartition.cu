@@ -316,6 +316,126 @@ __global__ void __launch_bounds__(RP_THREADS)
   }
 }
 
+// pass 2-push for the PUSH exchange (shuffle.cu): the same stable destination-major positions, but every destination's
+// rows live in another GPU's memory, reached over NVLink.  A warp of `rp_move_kernel` stores 32 / n_out elements per
+// destination per instruction — fine for local HBM behind the L2, 32-byte packets on the wire.  Here a tile's values of
+// one column are first put in destination-major order in shared memory, then written out run by run with consecutive
+// lanes on consecutive addresses, so a destination receives whole 128-byte lines.  addr[c * n_out + d] is the absolute
+// address of this source's first element of column c in destination d's receive block.
+struct PushCols {
+  int n;
+  const char* src[8];
+  int width[8];
+  const int64_t* addr;  // device: [n][n_out]
+};
+__global__ void __launch_bounds__(RP_THREADS, 4)
+    rp_push_kernel(const uint8_t* __restrict__ dest, int64_t n, int n_out, const int64_t* __restrict__ off,
+                   int64_t n_tiles, PushCols pc) {
+  __shared__ uint32_t cnt[RP_ITEMS][RP_WARPS][RP_MAX_OUT];
+  __shared__ uint32_t tcount[RP_MAX_OUT], tstart[RP_MAX_OUT + 1];
+  __shared__ int64_t goff[RP_MAX_OUT];   // row offset of this tile's run inside my slice at destination d
+  __shared__ int64_t addr_s[8 * RP_MAX_OUT];
+  __shared__ uint8_t dst_of[RP_TILE];    // destination of the tile-local sorted position
+  __shared__ int64_t stage[RP_TILE];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < pc.n * n_out; i += RP_THREADS) addr_s[i] = pc.addr[i];
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    for (int i = threadIdx.x; i < RP_ITEMS * RP_WARPS * RP_MAX_OUT; i += RP_THREADS) (&cnt[0][0][0])[i] = 0;
+    __syncthreads();
+    int d[RP_ITEMS], rank[RP_ITEMS];
+#pragma unroll
+    for (int j = 0; j < RP_ITEMS; ++j) {
+      int64_t r = tile * RP_TILE + j * RP_THREADS + threadIdx.x;
+      d[j] = r < n ? (int)dest[r] : -1;
+      if (d[j] == RP_DROPPED) d[j] = -1;
+      unsigned peers = __match_any_sync(0xffffffffu, d[j]);
+      rank[j] = __popc(peers & ((1u << lane) - 1));
+      if (d[j] >= 0 && rank[j] == 0) cnt[j][warp][d[j]] = __popc(peers);
+    }
+    __syncthreads();
+    if (threadIdx.x < n_out) {  // per destination: exclusive scan over (j, warp), tile-local
+      uint32_t run = 0;
+      for (int j = 0; j < RP_ITEMS; ++j)
+        for (int w = 0; w < RP_WARPS; ++w) {
+          uint32_t c = cnt[j][w][threadIdx.x];
+          cnt[j][w][threadIdx.x] = run;
+          run += c;
+        }
+      tcount[threadIdx.x] = run;
+      goff[threadIdx.x] = off[(int64_t)threadIdx.x * n_tiles + tile] - off[(int64_t)threadIdx.x * n_tiles];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t run = 0;
+      for (int q = 0; q < n_out; ++q) {
+        tstart[q] = run;
+        run += tcount[q];
+      }
+      tstart[n_out] = run;
+    }
+    __syncthreads();
+    const uint32_t total = tstart[n_out];
+    if (total == 0) continue;  // uniform: every row of the tile was dropped by the fused filter
+    uint32_t lpos[RP_ITEMS];
+#pragma unroll
+    for (int j = 0; j < RP_ITEMS; ++j) {
+      lpos[j] = d[j] >= 0 ? tstart[d[j]] + cnt[j][warp][d[j]] + rank[j] : 0u;
+      if (d[j] >= 0) dst_of[lpos[j]] = (uint8_t)d[j];
+    }
+    for (int c = 0; c < pc.n; ++c) {
+      const int w = pc.width[c];
+      __syncthreads();  // dst_of written / the previous column's write-out has finished with `stage`
+      if (w == 8) {
+        int64_t v[RP_ITEMS];
+#pragma unroll
+        for (int j = 0; j < RP_ITEMS; ++j)
+          if (d[j] >= 0) v[j] = reinterpret_cast<const int64_t*>(pc.src[c])[tile * RP_TILE + j * RP_THREADS + threadIdx.x];
+#pragma unroll
+        for (int j = 0; j < RP_ITEMS; ++j)
+          if (d[j] >= 0) stage[lpos[j]] = v[j];
+        __syncthreads();
+        for (int q = 0; q < n_out; ++q) {  // run by run; a warp's 32 stores cover one aligned 256-byte span
+          const int64_t a0 = addr_s[c * n_out + q] + goff[q] * 8;
+          const int lead = (int)((a0 >> 3) & 31), cnt_q = (int)tcount[q];
+          for (int k = (int)threadIdx.x - lead; k < cnt_q; k += RP_THREADS)
+            if (k >= 0) *reinterpret_cast<int64_t*>(a0 + (int64_t)k * 8) = stage[tstart[q] + k];
+        }
+      } else if (w == 4) {
+        int32_t* stage4 = reinterpret_cast<int32_t*>(stage);
+        int32_t v[RP_ITEMS];
+#pragma unroll
+        for (int j = 0; j < RP_ITEMS; ++j)
+          if (d[j] >= 0) v[j] = reinterpret_cast<const int32_t*>(pc.src[c])[tile * RP_TILE + j * RP_THREADS + threadIdx.x];
+#pragma unroll
+        for (int j = 0; j < RP_ITEMS; ++j)
+          if (d[j] >= 0) stage4[lpos[j]] = v[j];
+        __syncthreads();
+        for (int q = 0; q < n_out; ++q) {  // a warp's 32 stores cover one aligned 128-byte line
+          const int64_t a0 = addr_s[c * n_out + q] + goff[q] * 4;
+          const int lead = (int)((a0 >> 2) & 31), cnt_q = (int)tcount[q];
+          for (int k = (int)threadIdx.x - lead; k < cnt_q; k += RP_THREADS)
+            if (k >= 0) *reinterpret_cast<int32_t*>(a0 + (int64_t)k * 4) = stage4[tstart[q] + k];
+        }
+      } else {
+        uint8_t* stage1 = reinterpret_cast<uint8_t*>(stage);
+#pragma unroll
+        for (int j = 0; j < RP_ITEMS; ++j)
+          if (d[j] >= 0)
+            for (int b = 0; b < w; ++b)
+              stage1[lpos[j] * w + b] = (uint8_t)pc.src[c][(tile * RP_TILE + j * RP_THREADS + threadIdx.x) * w + b];
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < total; i += RP_THREADS) {
+          const int q = dst_of[i];
+          uint8_t* to = reinterpret_cast<uint8_t*>(addr_s[c * n_out + q] + (goff[q] + (int64_t)(i - tstart[q])) * w);
+          for (int b = 0; b < w; ++b) to[b] = stage1[i * w + b];
+        }
+      }
+    }
+    __syncthreads();
+  }
+  __threadfence_system();  // the stores above cross NVLink: performed before the kernel (and the barrier behind it) ends
+}
+
 // ---- host side: phase 1 (destinations, histogram, scan: no host sync), then counts / permutation / column move ----
 SplitState hash_split_begin(Ctx* ctx, const Key128* keys, const int32_t* key32, int64_t n, int n_out,
                             const RowPred* pred, const uint8_t* mask, const SemiFilter* semi, bool table_order) {
@@ -390,6 +510,41 @@ void hash_split_move(Ctx* ctx, const SplitState& st, int n_cols, const void* con
   }
   rp_move_kernel<<<grid_for(ctx, 8, st.n, RP_TILE), RP_THREADS, 0, ctx->stream>>>(
       st.dest->as<uint8_t>(), st.n, st.n_out, st.hist->as<int64_t>(), st.n_tiles, mc, perm_or_null);
+  B2_LAUNCHED(ctx);
+}
+
+// the push form of hash_split_move: addr_dev[c * n_out + d] = absolute (possibly peer-mapped) address of this source's
+// first element of column c at destination d
+void hash_split_push(Ctx* ctx, const SplitState& st, int n_cols, const void* const* src, const int* width,
+                     const int64_t* addr_dev, int64_t n_live) {
+  if (st.n == 0) return;
+  if (n_cols > 8) fail(B2_ERR_EXECUTION, "internal: hash_split_push handles 8 columns per launch");
+  if (n_live >= 0 && n_live * 8 < st.n) {  // sparse survivors: one thread per surviving row, absolute addresses as bases
+    MoveCols mc;
+    memset(&mc, 0, sizeof mc);
+    mc.n = n_cols;
+    for (int c = 0; c < n_cols; ++c) {
+      mc.src[c] = static_cast<const char*>(src[c]);
+      mc.dst[c] = nullptr;
+      mc.width[c] = width[c];
+    }
+    mc.base = addr_dev;
+    rp_move_sparse_kernel<<<grid_for(ctx, 6, st.n, RP_TILE), RP_THREADS, 0, ctx->stream>>>(
+        st.dest->as<uint8_t>(), st.n, st.n_out, st.hist->as<int64_t>(), st.n_tiles, mc, nullptr);
+    B2_LAUNCHED(ctx);
+    return;
+  }
+  PushCols pc;
+  memset(&pc, 0, sizeof pc);
+  pc.n = n_cols;
+  for (int c = 0; c < n_cols; ++c) {
+    pc.src[c] = static_cast<const char*>(src[c]);
+    pc.width[c] = width[c];
+    if (width[c] > 8) fail(B2_ERR_EXECUTION, "internal: hash_split_push moves columns of at most 8 bytes per value");
+  }
+  pc.addr = addr_dev;
+  rp_push_kernel<<<grid_for(ctx, 4, st.n, RP_TILE), RP_THREADS, 0, ctx->stream>>>(
+      st.dest->as<uint8_t>(), st.n, st.n_out, st.hist->as<int64_t>(), st.n_tiles, pc);
   B2_LAUNCHED(ctx);
 }
 

@@ -16,6 +16,15 @@
 //      loads) directly into its final, contiguous output columns: no receive staging, no copy-out.
 // NCCL carries only the metadata all-gather and the barrier; when peer mapping is unavailable the grouped
 // ncclSend/ncclRecv path of comm.cu is used instead (B2_SHUFFLE=nccl forces it).
+//
+// PUSH form (the default when every moved column is fixed-width; B2_SHUFFLE=pull keeps the form above): steps 3-5
+// become ONE kernel.  Every rank owns a RECEIVE arena (comm.h) mapped by its peers and offers, in the metadata
+// message of step 2, the free span the exchange may land in.  After the all-gather every rank knows every
+// destination's total and where its own rows start there, so phase 2 of the split (`rp_push_kernel`) stores each
+// row's values straight into the destination's final column over NVLink, whole runs at a time; the barrier follows
+// and the output columns are windows of the receive block: no staging copy, no copy-out.  An offer that turns out too
+// small (all ranks see the same numbers) sends this one exchange down the pull form and grows the arena for the next.
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -37,6 +46,11 @@ void shuffle_arena_release(Ctx* ctx) {
   if (c->arena) cudaFree(c->arena);
   c->arena = nullptr;
   c->arena_cap = 0;
+  for (size_t r = 0; r < c->peer_recv.size(); ++r)
+    if ((int)r != ctx->rank)
+      for (auto& m : c->peer_recv[r]) cudaIpcCloseMemHandle(m.second);
+  c->peer_recv.clear();
+  c->recv_arenas.clear();  // each arena is freed with the last output block that still windows it
 }
 
 struct ArenaMsg {  // what every rank publishes in step A
@@ -121,6 +135,127 @@ static bool arena_map_peers(Ctx* ctx, const std::vector<ArenaMsg>& msgs, void* r
   }
   if (retired) cudaFree(retired);
   c->p2p_state = ok ? 1 : -1;
+  return ok;
+}
+
+// ---- push form: receive-arena offer, block layout, peer mappings ----
+struct PushMsg {  // rides in the metadata message behind ArenaMsg
+  int64_t ok;   // 1 = this rank offers [off, off + cap) of arena `gen` and wants the push form
+  int64_t gen;
+  int64_t off;
+  int64_t cap;
+  cudaIpcMemHandle_t handle;  // 64 bytes
+};
+static_assert(sizeof(PushMsg) == 96, "PushMsg is exchanged as 12 int64 words");
+constexpr size_t PUSH_MAX_ARENAS = 6;
+
+// layout of one destination's receive block holding `rows` rows: fixed-width columns in schema order (elided ones
+// take no room), each 256-byte aligned with slack behind it for the vector loads of the consumers
+static size_t push_layout(const Batch& like, int64_t rows, std::vector<size_t>* col_off) {
+  size_t off = 0;
+  col_off->assign(like.cols.size(), 0);
+  for (size_t c = 0; c < like.cols.size(); ++c) {
+    if (!like.cols[c].data) continue;
+    (*col_off)[c] = off;
+    off += align256((size_t)rows * dtype_width(like.cols[c].dtype) + 64);
+  }
+  return off ? off : 256;
+}
+static bool push_wanted(const Batch& local) {
+  const char* e = getenv("B2_SHUFFLE");
+  if (e && strcmp(e, "push") != 0) return false;  // "pull" / "nccl"
+  for (auto& c : local.cols)
+    if (c.data && (c.dtype == B2_UTF8 || dtype_width(c.dtype) == 0)) return false;
+  return true;
+}
+// picks (or allocates) the arena whose largest free span the coming exchange may land in
+static void push_offer(Ctx* ctx, size_t estimate, PushMsg* msg, std::shared_ptr<RecvArena>* arena) {
+  Comm* c = ctx->comm;
+  memset(msg, 0, sizeof *msg);
+  arena->reset();
+  if (c->push_state < 0) return;
+  size_t best_off = 0, best_len = 0;
+  for (auto& a : c->recv_arenas) {
+    size_t o, l;
+    a->largest(&o, &l);
+    if (l > best_len) {
+      best_off = o;
+      best_len = l;
+      *arena = a;
+    }
+  }
+  // grow on what was learned from an offer that was too small; the very first offer is sized from the local rows
+  const size_t want = c->recv_arenas.empty() ? std::max(estimate, c->recv_predict) : c->recv_predict;
+  if (best_len < want || c->recv_arenas.empty()) {
+    if (c->recv_arenas.size() >= PUSH_MAX_ARENAS) {
+      if (!*arena) return;
+    } else {
+      const char* fl = getenv("B2_PUSH_ARENA_MIN_MB");  // tests shrink the floor to reach the grow / too-small paths
+      size_t cap = align256(std::max<size_t>(want * 5 / 2, (size_t)(fl ? atoi(fl) : 256) << 20));
+      size_t free_b = 0, total_b = 0;
+      if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) cudaGetLastError();
+      if (cap > free_b / 3) cap = align256(free_b / 3);
+      void* p = nullptr;
+      if (cap >= want && cudaMalloc(&p, cap) == cudaSuccess) {
+        auto a = std::make_shared<RecvArena>();
+        a->base = p;
+        a->cap = cap;
+        a->gen = ((int64_t)(ctx->rank + 1) << 32) | ++c->recv_gen;
+        a->free_spans[0] = cap;
+        c->recv_arenas.push_back(a);
+        *arena = a;
+        best_off = 0;
+        best_len = cap;
+      } else {
+        cudaGetLastError();
+        if (!*arena) return;
+      }
+    }
+  }
+  if (cudaIpcGetMemHandle(&msg->handle, (*arena)->base) != cudaSuccess) {
+    cudaGetLastError();
+    arena->reset();
+    return;
+  }
+  msg->ok = 1;
+  msg->gen = (*arena)->gen;
+  msg->off = (int64_t)best_off;
+  msg->cap = (int64_t)best_len;
+}
+// maps the offered arenas not seen before.  Every rank sees the same offers, so "something new" is a global fact
+// and the vote below is entered by all ranks or by none.
+static bool push_map_peers(Ctx* ctx, const std::vector<PushMsg>& msgs, std::vector<char*>* base) {
+  Comm* c = ctx->comm;
+  const int nr = ctx->nranks, me = ctx->rank;
+  if (c->peer_recv.empty()) c->peer_recv.assign(nr, {});
+  base->assign(nr, nullptr);
+  bool ok = true, fresh = false;
+  for (int r = 0; r < nr; ++r) {
+    if (r == me) continue;
+    auto it = c->peer_recv[r].find(msgs[r].gen);
+    if (it != c->peer_recv[r].end()) {
+      (*base)[r] = static_cast<char*>(it->second);
+      continue;
+    }
+    fresh = true;
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, msgs[r].handle, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      ok = false;
+    } else {
+      c->peer_recv[r][msgs[r].gen] = p;
+      (*base)[r] = static_cast<char*>(p);
+    }
+  }
+  // has any rank offered an arena that was new to its peers?  (my own offer is new to them iff it is new to me)
+  bool mine_fresh = !c->recv_published[msgs[me].gen];
+  c->recv_published[msgs[me].gen] = true;
+  if (nr > 1 && (fresh || mine_fresh)) {
+    std::vector<int64_t> votes = allgather_counts(ctx, std::vector<int64_t>{ok ? 1 : 0});
+    for (int64_t v : votes) ok = ok && v;
+  }
+  if (!ok) c->push_state = -1;
   return ok;
 }
 
@@ -213,7 +348,8 @@ struct LensToOff {
 
 // Shuffle of `local` given phase 1 of its hash split (`st`, n_out == nranks).  Returns this rank's output
 // partition, or nullptr when peer mapping is unavailable (the caller then takes the NCCL send/recv path).
-BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
+BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st, bool* pushed) {
+  if (pushed) *pushed = false;
   require_no_nulls(local, "exchange over NVLink");
   if (!ctx->comm) fail(B2_ERR_INVALID_ARG, "no communicator (call b2_comm_init)");
   Comm* cm = ctx->comm;
@@ -260,9 +396,19 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
   ArenaMsg my_msg;
   void* retired = nullptr;
   arena_local(ctx, need, &my_msg, &retired);
-  const size_t AW = sizeof(ArenaMsg) / 8, L = AW + (size_t)(nr + 1) + (size_t)nr * ncol;
+  // the push form's offer: the free span of my receive arena this exchange may land in
+  PushMsg my_push;
+  std::shared_ptr<RecvArena> my_recv;
+  memset(&my_push, 0, sizeof my_push);
+  if (push_wanted(local)) {
+    std::vector<size_t> tmp;
+    size_t est = push_layout(local, n, &tmp);
+    push_offer(ctx, est + est / 4 + ((size_t)1 << 20), &my_push, &my_recv);
+  }
+  const size_t AW = (sizeof(ArenaMsg) + sizeof(PushMsg)) / 8, L = AW + (size_t)(nr + 1) + (size_t)nr * ncol;
   std::vector<int64_t> host_words(L, 0);
   memcpy(host_words.data(), &my_msg, sizeof my_msg);
+  memcpy(host_words.data() + sizeof(ArenaMsg) / 8, &my_push, sizeof my_push);
   for (int d = 0; d < nr; ++d)
     for (size_t c = 0; c < ncol; ++c)
       if (!chr_bounds[c].empty()) host_words[AW + nr + 1 + (size_t)d * ncol + c] = chr_bounds[c][d + 1] - chr_bounds[c][d];
@@ -306,6 +452,91 @@ BatchPtr comm_shuffle_p2p(Ctx* ctx, const Batch& local, const SplitState& st) {
   int64_t total = R[me][nr];
   if (total >= (1ll << 31) - 1) fail(B2_ERR_NOT_IMPLEMENTED, "received partition beyond 2^31-2 rows");
   char* arena = static_cast<char*>(cm->arena);
+
+  // ---- push form: every destination offered room for its total -> ONE kernel stores my rows into the final columns ----
+  {
+    std::vector<PushMsg> pm(nr);
+    bool fits = true;
+    for (int r = 0; r < nr; ++r) {
+      memcpy(&pm[r], all.data() + (size_t)r * L + sizeof(ArenaMsg) / 8, sizeof(PushMsg));
+      fits = fits && pm[r].ok;
+    }
+    std::vector<std::vector<size_t>> col_off(nr);
+    std::vector<size_t> block_need(nr, 0);
+    for (int d = 0; d < nr && fits; ++d) block_need[d] = push_layout(local, R[d][nr], &col_off[d]);
+    for (int d = 0; d < nr && fits; ++d)
+      if ((int64_t)block_need[d] > pm[d].cap) {
+        fits = false;  // every rank computes this from the same numbers: all of them take the pull form below
+        for (int q = 0; q < nr; ++q)
+          if (q == me && (int64_t)block_need[q] > pm[q].cap)
+            cm->recv_predict = std::max(cm->recv_predict, block_need[q] + block_need[q] / 4);
+      }
+    if (getenv("B2_PUSH_DEBUG"))
+      fprintf(stderr, "[push r%d] ok=%lld offer gen=%llx off=%lld cap=%lld need=%zu fits=%d arenas=%zu predict=%zu\n", me,
+              (long long)pm[me].ok, (long long)pm[me].gen, (long long)pm[me].off, (long long)pm[me].cap, block_need[me],
+              (int)fits, cm->recv_arenas.size(), cm->recv_predict);
+    std::vector<char*> pbase;
+    if (fits && push_map_peers(ctx, pm, &pbase)) {
+      const size_t boff = (size_t)pm[me].off, blen = align256(block_need[me]);
+      if (!my_recv || !my_recv->take(boff, blen)) fail(B2_ERR_EXECUTION, "internal: the offered receive span is gone");
+      pbase[me] = static_cast<char*>(my_recv->base);
+      // the block: returns its span to the arena when the last window of it is dropped
+      DevBuf* raw = new DevBuf(ctx, 0);
+      raw->ptr = pbase[me] + boff;
+      raw->bytes = blen;
+      std::shared_ptr<RecvArena> keep = my_recv;
+      BufPtr block(raw, [keep, boff, blen](DevBuf* b) {
+        keep->give(boff, blen);
+        b->ptr = nullptr;
+        delete b;
+      });
+      std::vector<const void*> src;
+      std::vector<int> width;
+      std::vector<int64_t> addr;
+      int64_t row_bytes = 0;
+      for (size_t c = 0; c < ncol; ++c) {
+        if (elided(c)) continue;
+        const int64_t w = (int64_t)dtype_width(local.cols[c].dtype);
+        row_bytes += w;
+        src.push_back(local.cols[c].data->ptr);
+        width.push_back((int)w);
+        for (int d = 0; d < nr; ++d)
+          addr.push_back((int64_t)(uintptr_t)(pbase[d] + pm[d].off + col_off[d][c]) + R[d][me] * w);
+      }
+      if (n && !src.empty()) {
+        auto daddr = dev_alloc(ctx, addr.size() * 8);
+        B2_CUDA(cudaMemcpyAsync(daddr->ptr, addr.data(), addr.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+        ctx->prof_begin();  // b2_ctx_set_profiling: CUDA events around the exchange kernel (bench.py's NVLink roofline)
+        for (size_t g = 0; g < src.size(); g += 8) {
+          int k = (int)std::min<size_t>(8, src.size() - g);
+          hash_split_push(ctx, st, k, src.data() + g, width.data() + g, daddr->as<int64_t>() + g * nr,
+                          all[(size_t)me * L + AW + nr]);
+        }
+        ctx->prof_end();
+      }
+      for (int d = 0; d < nr; ++d)
+        if (d != me) ctx->bytes_sent += cnt(me, d) * row_bytes;  // bytes crossing NVLink
+      pt.mark("shuffle 3p: push over NVLink");
+      {  // stream-ordered barrier: every rank's stores into my block have been performed
+        auto flag = dev_alloc_zero(ctx, 16);
+        B2_NCCL(ncclAllReduce(flag->ptr, flag->ptr, 1, ncclInt32, ncclSum, cm->nccl, ctx->stream));
+      }
+      pt.mark("shuffle 4p: barrier");
+      auto out = std::make_shared<Batch>();
+      out->ctx = ctx;
+      out->schema = local.schema;
+      out->num_rows = total;
+      for (size_t c = 0; c < ncol; ++c) {
+        Column o;
+        o.dtype = local.cols[c].dtype;
+        o.length = total;
+        if (!elided(c)) o.data = dev_view(block, col_off[me][c], (size_t)total * dtype_width(o.dtype) + 64);
+        out->cols.push_back(std::move(o));
+      }
+      if (pushed) *pushed = true;
+      return out;
+    }
+  }
 
   // ---- step 3: move my columns into my arena, destination-major, slices co-aligned with their receivers ----
   {

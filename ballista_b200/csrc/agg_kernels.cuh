@@ -166,10 +166,15 @@ __global__ void __launch_bounds__(AGG_THREADS)
 agg_global_kernel(const typename S::Params prm, int64_t row_begin, int64_t row_end, int64_t n, TableRef tbl,
                   int* status) {
   constexpr int NA = S::NACC, NC = S::NCNT;
+  // slots this CTA claimed in the current tile: listed in tbl.slot_list behind ONE reservation per tile
+  __shared__ uint32_t s_claim[TILE_ROWS];
+  __shared__ int s_nclaim, s_base;
   bool key_overflow = false;
   int64_t first_tile = row_begin / TILE_ROWS;
   int64_t end_tile = (row_end + TILE_ROWS - 1) / TILE_ROWS;
   for (int64_t tile = first_tile + blockIdx.x; tile < end_tile; tile += gridDim.x) {
+    if (threadIdx.x == 0) s_nclaim = 0;
+    __syncthreads();
     int64_t r0 = tile * TILE_ROWS + (int64_t)threadIdx.x * ROWS_PER_THREAD;
     typename S::Rows rows;
     if (r0 < n) S::load(prm, r0, n, rows);
@@ -181,11 +186,13 @@ agg_global_kernel(const typename S::Params prm, int64_t row_begin, int64_t row_e
     double run_v[NA ? NA : 1];
     u64 run_c[NC ? NC : 1];
     auto flush = [&]() {
-      u64 slot = table_upsert(tbl, run_key);
+      bool claimed;
+      u64 slot = table_upsert_quiet(tbl, run_key, &claimed);
       if (slot == ~0ull) {
         atomicExch(status, AGG_TABLE_FULL);
         return;
       }
+      if (claimed) s_claim[atomicAdd(&s_nclaim, 1)] = (uint32_t)slot;
 #pragma unroll
       for (int a = 0; a < NA; ++a) red_add_f64(&tbl.acc[(u64)a * tbl.cap + slot], run_v[a]);
 #pragma unroll
@@ -216,6 +223,15 @@ agg_global_kernel(const typename S::Params prm, int64_t row_begin, int64_t row_e
       for (int a = 0; a < NC; ++a) run_c[a] = c[a];
     }
     if (run_open) flush();
+    __syncthreads();
+    const int nclaim = s_nclaim;
+    if (nclaim) {  // uniform
+      if (threadIdx.x == 0) s_base = atomicAdd(tbl.n_groups, nclaim);
+      __syncthreads();
+      if (tbl.slot_list)
+        for (int i = threadIdx.x; i < nclaim; i += AGG_THREADS) tbl.slot_list[s_base + i] = s_claim[i];
+    }
+    __syncthreads();
   }
   if (key_overflow) atomicExch(status, AGG_KEY_TOO_WIDE);
 }

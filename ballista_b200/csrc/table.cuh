@@ -208,6 +208,30 @@ __device__ __forceinline__ u64 table_upsert(const TableRef& t, const Key128& key
   }
   return ~0ull;
 }
+// the same without the group counter and the slot list: *claimed = this call took an empty slot.  For callers that
+// count and list their claims themselves (agg_global_kernel stages a tile's claims in shared memory and reserves their
+// places in the list with ONE update of the counter: at a million groups the per-claim form spends its time queueing on
+// that one address in the L2).
+__device__ __forceinline__ u64 table_upsert_quiet(const TableRef& t, const Key128& key, bool* claimed) {
+  u64 mask = t.cap - 1;
+  u64 h = key_hash(key) & mask;
+  const Key128 empty{KEY_EMPTY, KEY_EMPTY};
+  *claimed = false;
+  for (u64 probe = 0; probe < t.cap; ++probe) {
+    Key128 cur = ld_key_volatile(&t.keys[h]);
+    if (key_eq(cur, key)) return h;
+    if (key_eq(cur, empty)) {
+      Key128 old = atomic_cas_key(&t.keys[h], empty, key);
+      if (key_eq(old, empty)) {
+        *claimed = true;
+        return h;
+      }
+      if (key_eq(old, key)) return h;
+    }
+    h = (h + 1) & mask;
+  }
+  return ~0ull;
+}
 // read-only lookup; ~0 when absent
 __device__ __forceinline__ u64 table_find(const Key128* keys, u64 cap, const Key128& key) {
   u64 mask = cap - 1;

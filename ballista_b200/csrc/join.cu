@@ -611,6 +611,12 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
     constexpr int M = decltype(mode)::value;
     constexpr bool D = decltype(dups)::value;
     auto go = [&](auto kernel) {
+      // persistent grid = the CTAs of THIS variant that are co-resident (the one-term predicate form needs fewer
+      // registers than the general one and fits more)
+      int fit = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fit, kernel, JP_THREADS, 0) != cudaSuccess) cudaGetLastError();
+      if (getenv("B2_PROBE_CTAS")) fit = atoi(getenv("B2_PROBE_CTAS"));
+      if (fit > 0) grid_ = grid_for(ctx, fit, n, JP_TILE);
       kernel<<<grid_, JP_THREADS, 0, ctx->stream>>>(key, pred, mask, n, vec, t.slots->as<u64>(), t.cap / BUCKET - 1,
                                                   t.bshift, t.bloom->as<uint32_t>(), (uint32_t)(t.bloom_words - 1),
                                                   t.next->as<uint32_t>(), li, ri, tile_cnt);

@@ -2,9 +2,11 @@
 // communicator attached the hash repartition IS the in-box shuffle).  SURVEY §8a rows F, G, H.
 // Constructed where from_proto.rs:253-276 and :133-164 construct the DataFusion operators.
 #include <cstdlib>
+#include <cstring>
 
 #include "comm.h"
 #include "ops.h"
+#include "scan.cuh"
 
 namespace b2 {
 
@@ -33,6 +35,41 @@ __global__ void mark_rows_kernel(const uint32_t* idx, int64_t m, uint8_t* flags)
   for (; i < m; i += (int64_t)gridDim.x * blockDim.x) flags[idx[i]] = 1;
 }
 
+// Several Int32 / Date32 key columns: the 32-bit table is built and probed on the FIRST pair only, and the candidate
+// pairs are then checked on the remaining pairs (equal values, neither side NULL) and compacted in pair order - the
+// same row set as one table over the packed key, without packing 16 bytes per row on either side.
+constexpr int JOIN_VERIFY_MAX = 4;
+struct VerifyIn {
+  const uint32_t* bi;
+  const uint32_t* pi;
+  int n;
+  const int32_t* bcol[JOIN_VERIFY_MAX];
+  const int32_t* pcol[JOIN_VERIFY_MAX];
+  const uint8_t* bval[JOIN_VERIFY_MAX];
+  const uint8_t* pval[JOIN_VERIFY_MAX];
+  __device__ __forceinline__ int operator()(int64_t i) const {
+    const uint32_t b = bi[i], p = pi[i];
+    for (int k = 0; k < n; ++k) {
+      if (bval[k] && !bval[k][b]) return 0;
+      if (pval[k] && !pval[k][p]) return 0;
+      if (__ldg(bcol[k] + b) != __ldg(pcol[k] + p)) return 0;
+    }
+    return 1;
+  }
+};
+struct PairOut {
+  const uint32_t* bi;
+  const uint32_t* pi;
+  uint32_t* bo;
+  uint32_t* po;
+  __device__ __forceinline__ void operator()(int64_t i, int v, int64_t pre) const {
+    if (v) {
+      bo[pre] = bi[i];
+      po[pre] = pi[i];
+    }
+  }
+};
+
 struct HashJoinExec : Op {
   std::vector<int> on_left, on_right;  // column indices
   int join_type = B2_JOIN_INNER;
@@ -41,7 +78,8 @@ struct HashJoinExec : Op {
   // partner, Right drops the left one instead (DataFusion's build_join_schema)
   std::vector<int> left_keep, right_keep;
   KeyLayout layout;
-  bool k32 = false;             // one Int32 / Date32 key per side: 8-byte-slot table, fused filters
+  bool k32 = false;             // Int32 / Date32 keys only: 8-byte-slot table on the first pair, fused filters;
+                                // further pairs are verified on the candidate pairs (verify_pairs)
   std::vector<char> need;       // output columns a parent will read (empty = all)
   // build side, collected once per version of the left subtree (the reference rebuilds it per task; result-neutral,
   // SURVEY App. C.10)
@@ -175,14 +213,40 @@ struct HashJoinExec : Op {
   void ensure_table() {
     if (!table) table = build_table(*left_batch, left_pred, on_left, 0x81, &left_keys);
   }
-  // pairs (row of `b`, build row) of one probe batch against `t`
-  int64_t probe_table(JoinTable& t, const Batch& b, const ExprPtr& pred, const std::vector<int>& on, int null_tag,
-                      BufPtr* build_idx, BufPtr* probe_idx) {
+  // keeps the candidate pairs whose remaining key columns agree (k32 with more than one key pair)
+  int64_t verify_pairs(const Batch& build_b, const std::vector<int>& build_on, const Batch& b,
+                       const std::vector<int>& on, int64_t m, BufPtr* build_idx, BufPtr* probe_idx) {
+    if (on.size() < 2 || m == 0) return m;
+    VerifyIn in;
+    memset(&in, 0, sizeof in);
+    in.bi = (*build_idx)->as<uint32_t>();
+    in.pi = (*probe_idx)->as<uint32_t>();
+    in.n = (int)on.size() - 1;
+    for (int k = 0; k < in.n; ++k) {
+      const Column& bc = build_b.cols[build_on[k + 1]];
+      const Column& pc = b.cols[on[k + 1]];
+      in.bcol[k] = bc.values<int32_t>();
+      in.pcol[k] = pc.values<int32_t>();
+      in.bval[k] = bc.validity();
+      in.pval[k] = pc.validity();
+    }
+    BufPtr bo = dev_alloc(ctx, (size_t)(m + 1) * 4), po = dev_alloc(ctx, (size_t)(m + 1) * 4);
+    int64_t kept = 0;
+    device_scan(ctx, in, m, PairOut{in.bi, in.pi, bo->as<uint32_t>(), po->as<uint32_t>()}, &kept);
+    *build_idx = bo;
+    *probe_idx = po;
+    return kept;
+  }
+  // pairs (row of `b`, build row) of one probe batch against `t` (built over `build_b` on `build_on`)
+  int64_t probe_table(JoinTable& t, const Batch& build_b, const std::vector<int>& build_on, const Batch& b,
+                      const ExprPtr& pred, const std::vector<int>& on, int null_tag, BufPtr* build_idx,
+                      BufPtr* probe_idx) {
     if (k32) {
       RowPred rp;
       Column mask = side_mask(pred, b, on[0], &rp);
-      return join_probe32(ctx, t, b.cols[on[0]].values<int32_t>(), rp, mask.data ? mask.values<uint8_t>() : nullptr,
-                          b.num_rows, build_idx, probe_idx);
+      int64_t m = join_probe32(ctx, t, b.cols[on[0]].values<int32_t>(), rp,
+                               mask.data ? mask.values<uint8_t>() : nullptr, b.num_rows, build_idx, probe_idx);
+      return verify_pairs(build_b, build_on, b, on, m, build_idx, probe_idx);
     }
     BufPtr pk = pack(b, on, null_tag);
     return join_probe(ctx, t, pk->as<Key128>(), b.num_rows, build_idx, probe_idx);
@@ -253,7 +317,7 @@ struct HashJoinExec : Op {
           first = nullptr;
           BufPtr keep, bi, pi;
           auto t = op->build_table(*r, pred, op->on_right, 0x82, &keep);
-          int64_t m = op->probe_table(*t, *op->left_batch, op->left_pred, op->on_left, 0x81, &bi, &pi);
+          int64_t m = op->probe_table(*t, *r, op->on_right, *op->left_batch, op->left_pred, op->on_left, 0x81, &bi, &pi);
           op->last_path += "/build-right";
           return assemble(r.get(), pi, bi, m, false, false);
         }
@@ -278,7 +342,7 @@ struct HashJoinExec : Op {
         return nullptr;
       }
       BufPtr li, ri;
-      int64_t m = op->probe_table(*op->table, *r, pred, op->on_right, 0x82, &li, &ri);
+      int64_t m = op->probe_table(*op->table, *op->left_batch, op->on_left, *r, pred, op->on_right, 0x82, &li, &ri);
       if (op->join_type == B2_JOIN_LEFT && op->left_batch->num_rows) {
         if (!left_matched) left_matched = dev_alloc_zero(ctx, (size_t)op->left_batch->num_rows + 16);
         if (m) {
@@ -351,7 +415,7 @@ struct HashJoinExec : Op {
     if (fuse_right()) r = peel_filter(r, &s->pred);
     s->in = r->execute(partition);
     last_path = std::string(k32 ? (fuse_left() || fuse_right() ? "k32:fused-filter" : "k32") : "key128") +
-                (partitioned ? "/partitioned" : "");
+                (k32 && on_left.size() > 1 ? "+verify" : "") + (partitioned ? "/partitioned" : "");
     return s;
   }
 };
@@ -379,7 +443,9 @@ OpPtr make_hash_join(Ctx* ctx, OpPtr left, OpPtr right, std::vector<std::string>
     kd.push_back(ta);
   }
   op->layout = make_key_layout(kd);
-  op->k32 = kd.size() == 1 && (kd[0] == B2_INT32 || kd[0] == B2_DATE32);
+  op->k32 = !kd.empty() && (int)kd.size() <= JOIN_VERIFY_MAX + 1 && !getenv("B2_DISABLE_K32_VERIFY");
+  for (int t : kd) op->k32 = op->k32 && (t == B2_INT32 || t == B2_DATE32);
+  if (kd.size() == 1) op->k32 = kd[0] == B2_INT32 || kd[0] == B2_DATE32;
   // output = left fields ++ right fields; an `on` column named like its partner appears once: Inner / Left keep the
   // left one, Right keeps the right one (A.3).  An outer join makes the null-extended side's fields nullable.
   auto is_dup = [&](const std::vector<int>& on_side, int c) {

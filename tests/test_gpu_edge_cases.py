@@ -172,9 +172,9 @@ def test_join_two_column_and_string_keys_general_path(ctx):
     p_supp = rng.integers(0, 600, npr).astype(np.int32)
     p_nat = rng.integers(0, 25, npr).astype(np.int32)
 
-    def check(left, right, on, lkey, rkey):
+    def check(left, right, on, lkey, rkey, expect="key128"):
         j = HashJoinExec(tpch.scan(ctx, [[left]]), tpch.scan(ctx, [[right.slice(0, 17_001), right.slice(17_001)]]), on)
-        assert "key128" in (j.collect_device(0) and j.last_path())
+        assert expect in (j.collect_device(0) and j.last_path()), j.last_path()
         t = j.collect(0)
         build = {}
         for i, k in enumerate(lkey):
@@ -186,8 +186,20 @@ def test_join_two_column_and_string_keys_general_path(ctx):
 
     left = rb(s_suppkey=b_supp, s_nationkey=b_nat, lrow=np.arange(nb, dtype=np.int64))
     right = rb(l_suppkey=p_supp, c_nationkey=p_nat, rrow=np.arange(npr, dtype=np.int64))
+    # all-Int32 key columns: 32-bit table on the first pair, the others verified on the candidate pairs ...
     check(left, right, [("s_suppkey", "l_suppkey"), ("s_nationkey", "c_nationkey")],
-          list(zip(b_supp.tolist(), b_nat.tolist())), list(zip(p_supp.tolist(), p_nat.tolist())))
+          list(zip(b_supp.tolist(), b_nat.tolist())), list(zip(p_supp.tolist(), p_nat.tolist())), expect="+verify")
+    # ... also with the low-cardinality column first (long chains on the table's key)
+    check(left, right, [("s_nationkey", "c_nationkey"), ("s_suppkey", "l_suppkey")],
+          list(zip(b_nat.tolist(), b_supp.tolist())), list(zip(p_nat.tolist(), p_supp.tolist())), expect="+verify")
+    # ... and the same join through the packed-key table
+    import os
+    os.environ["B2_DISABLE_K32_VERIFY"] = "1"
+    try:
+        check(left, right, [("s_suppkey", "l_suppkey"), ("s_nationkey", "c_nationkey")],
+              list(zip(b_supp.tolist(), b_nat.tolist())), list(zip(p_supp.tolist(), p_nat.tolist())))
+    finally:
+        del os.environ["B2_DISABLE_K32_VERIFY"]
     # Int64 key with values beyond 32 bits
     b64 = (b_supp.astype(np.int64) << 33) + b_nat
     p64 = (p_supp.astype(np.int64) << 33) + p_nat

@@ -223,6 +223,33 @@ def test_outer_joins_and_null_keys_match_oracle_and_acero(ctx, O, how, keytype):
     assert got.num_rows > 1000
 
 
+@pytest.mark.parametrize("how", ["Inner", "Left", "Right"])
+def test_two_int32_key_columns_with_nulls_match_oracle(ctx, O, how):
+    """Two Int32 key columns (32-bit table on the first, the second verified on the candidate pairs): NULLs in either
+    column never match, outer joins null-extend the rows left without a VERIFIED partner."""
+    rng = np.random.default_rng(33)
+    nl, nr = 2500, 6001
+    la, lb = rng.integers(0, 300, nl).astype(np.int32), rng.integers(0, 6, nl).astype(np.int32)
+    ra, rb_ = rng.integers(100, 400, nr).astype(np.int32), rng.integers(0, 6, nr).astype(np.int32)
+    lma, lmb = rng.random(nl) < 0.04, rng.random(nl) < 0.04
+    rma, rmb = rng.random(nr) < 0.04, rng.random(nr) < 0.04
+    left = rb(a=pa.array(la, mask=lma), b=pa.array(lb, mask=lmb), lv=np.arange(nl, dtype=np.int64))
+    right = rb(a2=pa.array(ra, mask=rma), b2=pa.array(rb_, mask=rmb), rv=np.arange(nr, dtype=np.int64))
+    got, j = join_table(ctx, left, right, [("a", "a2"), ("b", "b2")], how)
+    assert "k32" in j.last_path() and "+verify" in j.last_path(), j.last_path()
+    li, ri = O.hash_join_outer([la, lb], [ra, rb_], how, ~(lma | lmb), ~(rma | rmb))
+    lrows, rrows = left.to_pylist(), right.to_pylist()
+    nul_l, nul_r = {c: None for c in left.schema.names}, {c: None for c in right.schema.names}
+    want = []
+    for a, b in zip(li, ri):
+        row = dict(lrows[a] if a >= 0 else nul_l)
+        row.update(rrows[b] if b >= 0 else nul_r)
+        want.append(tuple(row[c] for c in got.schema.names))
+    key = lambda r: tuple((v is None, v) for v in r)
+    assert canon_rows(got) == sorted(want, key=key)
+    assert got.num_rows > 1000
+
+
 def test_right_join_drops_the_left_duplicate_key_column(ctx):
     left = rb(k=np.array([1, 2, 3], dtype=np.int32), a=np.array([1.0, 2.0, 3.0]))
     right = rb(k=np.array([2, 3, 4, 4], dtype=np.int32), b=np.array([20, 30, 40, 41], dtype=np.int64))

@@ -201,6 +201,8 @@ __global__ void scan_apply_kernel(In in, int64_t n, const int64_t* block_sums, O
   }
 }
 
+void scan_i64(Ctx* ctx, int64_t* v, int64_t n);  // repartition.cu: in-place exclusive scan, v[n] = total (chunked when large)
+
 // Runs the three launches.  Returns the device buffer of CTA sums; sums[nb] holds the grand total
 // (int64).  `total_host` (optional) receives it after a stream sync.
 template <class In, class Out>
@@ -210,8 +212,12 @@ BufPtr device_scan(Ctx* ctx, In in, int64_t n, Out out, int64_t* total_host) {
   if (n > 0) {
     scan_reduce_kernel<In><<<(unsigned)nb, SCAN_THREADS, 0, ctx->stream>>>(in, n, sums->as<int64_t>());
     B2_LAUNCHED(ctx);
-    scan_sums_kernel<<<1, SCAN_THREADS, 0, ctx->stream>>>(sums->as<int64_t>(), nb);
-    B2_LAUNCHED(ctx);
+    if (nb > 4 * SCAN_THREADS) {  // tens of thousands of CTA sums: the single small CTA walks them in ~nb / 256 rounds
+      scan_i64(ctx, sums->as<int64_t>(), nb);
+    } else {
+      scan_sums_kernel<<<1, SCAN_THREADS, 0, ctx->stream>>>(sums->as<int64_t>(), nb);
+      B2_LAUNCHED(ctx);
+    }
     scan_apply_kernel<In, Out><<<(unsigned)nb, SCAN_THREADS, 0, ctx->stream>>>(in, n, sums->as<int64_t>(), out);
     B2_LAUNCHED(ctx);
   }

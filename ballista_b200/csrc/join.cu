@@ -225,9 +225,23 @@ bool compile_row_pred(const ExprPtr& pred, const Batch& batch, RowPred* out) {
 // in input order scatter 8-byte CAS operations over the whole table in HBM.
 __global__ void join_build32_kernel(const int32_t* __restrict__ key, RowPred pred, const uint8_t* __restrict__ mask,
                                     const uint32_t* __restrict__ perm, int64_t n, u64* slots, u64 bmask, int bshift,
-                                    uint32_t* next, int* flags) {
+                                    uint32_t* next, int* flags, int ahead) {
   int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  for (; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; j < n; j += stride) {
+    // Experiment (B2_BUILD_AHEAD=k, off by default): request the bucket of the row this thread inserts k rounds from now
+    // into L2.  Measured on Q3 SF100 (14.7 M inserts into 256 MB): 0 -> 4.38 ms per step, 2 -> 4.64, 4 -> 4.63: the build
+    // is bound by the rate of random 32-byte sectors HBM sustains, not by the latency of one insert's chain.
+    {
+      const int64_t ja = j + ahead * stride;
+      if (ahead && ja < n) {
+        const int64_t ia = perm ? (int64_t)perm[ja] : ja;
+        if (perm || ((!mask || mask[ia]) && row_pred(pred, ia))) {
+          const u64 ba = (u64)(table_hash(fmix32((uint32_t)key[ia])) >> bshift);
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(slots + ba * BUCKET));
+        }
+      }
+    }
     const int64_t i = perm ? (int64_t)perm[j] : j;
     if (!perm) {
       if (mask && !mask[i]) continue;
@@ -343,7 +357,7 @@ std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const RowP
     if (work) {
       join_build32_kernel<<<grid_for(ctx, 8, work, 256), 256, 0, ctx->stream>>>(
           key, pred, mask, perm ? perm->as<uint32_t>() : nullptr, work, t->slots->as<u64>(), cap / BUCKET - 1, t->bshift,
-          t->next->as<uint32_t>(), t->flags->as<int>());
+          t->next->as<uint32_t>(), t->flags->as<int>(), getenv("B2_BUILD_AHEAD") ? atoi(getenv("B2_BUILD_AHEAD")) : 0);
       B2_LAUNCHED(ctx);
     }
   }

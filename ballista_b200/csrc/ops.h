@@ -15,6 +15,9 @@ namespace b2 {
 BufPtr mask_to_indices(Ctx* ctx, const uint8_t* mask, int64_t n, int64_t* count);        // take.cu
 // idx 0xFFFFFFFF = null-extended row (outer joins); pass null_extended when the index vector may hold such entries
 Column take_column(Ctx* ctx, const Column& c, const uint32_t* idx, int64_t m, bool null_extended = false);  // take.cu
+// the same for several columns through one index vector: fixed-width columns without NULLs share one launch
+std::vector<Column> take_columns(Ctx* ctx, const std::vector<const Column*>& cols, const uint32_t* idx, int64_t m,
+                                 bool null_extended = false);
 Column null_column(Ctx* ctx, int dtype, int64_t n);                                       // take.cu
 BatchPtr take_batch(Ctx* ctx, const Batch& b, const uint32_t* idx, int64_t m);            // take.cu
 BatchPtr concat_batches(Ctx* ctx, const Schema& schema, const std::vector<BatchPtr>& b);  // take.cu

@@ -273,19 +273,38 @@ struct HashJoinExec : Op {
         e.length = m;
         return e;
       };
+      // the columns of one side that a parent reads are gathered together (one launch per side for fixed-width data)
+      std::vector<const Column*> lsrc, rsrc;
+      std::vector<size_t> lpos, rpos;
       for (int c : op->left_keep) {
         const Column& col = op->left_batch->cols[c];
         if (!op->needed(oc)) o->cols.push_back(elided(col.dtype));
         else if (!li) o->cols.push_back(null_column(ctx, col.dtype, m));
-        else o->cols.push_back(take_column(ctx, col, li->as<uint32_t>(), m, null_left));
+        else {
+          lsrc.push_back(&col);
+          lpos.push_back(o->cols.size());
+          o->cols.push_back(Column());
+        }
         ++oc;
       }
       Schema rs = op->children[1]->schema();
       for (int c : op->right_keep) {
         if (!op->needed(oc)) o->cols.push_back(elided(rs.fields[c].dtype));
         else if (!ri) o->cols.push_back(null_column(ctx, rs.fields[c].dtype, m));
-        else o->cols.push_back(take_column(ctx, r->cols[c], ri->as<uint32_t>(), m, null_right));
+        else {
+          rsrc.push_back(&r->cols[c]);
+          rpos.push_back(o->cols.size());
+          o->cols.push_back(Column());
+        }
         ++oc;
+      }
+      if (!lsrc.empty()) {
+        std::vector<Column> g = take_columns(ctx, lsrc, li->as<uint32_t>(), m, null_left);
+        for (size_t k = 0; k < g.size(); ++k) o->cols[lpos[k]] = std::move(g[k]);
+      }
+      if (!rsrc.empty()) {
+        std::vector<Column> g = take_columns(ctx, rsrc, ri->as<uint32_t>(), m, null_right);
+        for (size_t k = 0; k < g.size(); ++k) o->cols[rpos[k]] = std::move(g[k]);
       }
       return o;
     }

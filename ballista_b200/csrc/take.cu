@@ -1,6 +1,8 @@
 // take.cu — selection vectors and gathers: mask -> ordered row indices (stream compaction), and
 // index-driven column gathers (`take`), the building blocks of FilterExec (arrow::compute::filter),
 // HashJoinExec output assembly and RepartitionExec (arrow::compute::take).  SURVEY §8a rows A, F, G.
+#include <cstring>
+
 #include "ops.h"
 #include "scan.cuh"
 
@@ -78,6 +80,70 @@ Column take_column(Ctx* ctx, const Column& c, const uint32_t* idx, int64_t m, bo
       case 8: gather_kernel<int64_t><<<grid, 256, 0, ctx->stream>>>(c.values<int64_t>(), idx, m, out.data->as<int64_t>()); break;
       default: fail(B2_ERR_NOT_IMPLEMENTED, "take on this type");
     }
+    B2_LAUNCHED(ctx);
+  }
+  return out;
+}
+
+// Several fixed-width columns gathered through ONE index vector in one launch (a join's output side): the index is read
+// once and every thread has one independent load per column in flight.
+struct GatherCols {
+  int n;
+  const char* in[8];
+  char* out[8];
+  int width[8];
+};
+__global__ void gather_multi_kernel(const __grid_constant__ GatherCols g, const uint32_t* __restrict__ idx, int64_t m) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < m; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t r = idx[i];
+    int64_t v[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+      if (c < g.n) {
+        if (g.width[c] == 8) v[c] = reinterpret_cast<const int64_t*>(g.in[c])[r];
+        else if (g.width[c] == 4) v[c] = reinterpret_cast<const int32_t*>(g.in[c])[r];
+        else v[c] = reinterpret_cast<const uint8_t*>(g.in[c])[r];
+      }
+#pragma unroll
+    for (int c = 0; c < 8; ++c)
+      if (c < g.n) {
+        if (g.width[c] == 8) reinterpret_cast<int64_t*>(g.out[c])[i] = v[c];
+        else if (g.width[c] == 4) reinterpret_cast<int32_t*>(g.out[c])[i] = (int32_t)v[c];
+        else reinterpret_cast<uint8_t*>(g.out[c])[i] = (uint8_t)v[c];
+      }
+  }
+}
+std::vector<Column> take_columns(Ctx* ctx, const std::vector<const Column*>& cols, const uint32_t* idx, int64_t m,
+                                 bool null_extended) {
+  std::vector<Column> out(cols.size());
+  std::vector<size_t> fused;
+  for (size_t k = 0; k < cols.size(); ++k) {
+    const Column& c = *cols[k];
+    const size_t w = c.dtype == B2_UTF8 ? 0 : dtype_width(c.dtype);
+    if (c.data && !c.valid && !null_extended && m && (w == 1 || w == 4 || w == 8)) fused.push_back(k);
+    else out[k] = take_column(ctx, c, idx, m, null_extended);
+  }
+  if (fused.size() == 1) {
+    out[fused[0]] = take_column(ctx, *cols[fused[0]], idx, m, null_extended);
+    fused.clear();
+  }
+  for (size_t g0 = 0; g0 < fused.size(); g0 += 8) {
+    GatherCols g;
+    memset(&g, 0, sizeof g);
+    g.n = (int)std::min<size_t>(8, fused.size() - g0);
+    for (int q = 0; q < g.n; ++q) {
+      const Column& c = *cols[fused[g0 + q]];
+      Column& o = out[fused[g0 + q]];
+      o.dtype = c.dtype;
+      o.length = m;
+      const size_t w = dtype_width(c.dtype);
+      o.data = dev_alloc(ctx, (size_t)m * w + 16);
+      g.in[q] = c.data->as<char>();
+      g.out[q] = o.data->as<char>();
+      g.width[q] = (int)w;
+    }
+    gather_multi_kernel<<<grid_for(ctx, 8, m, 256), 256, 0, ctx->stream>>>(g, idx, m);
     B2_LAUNCHED(ctx);
   }
   return out;

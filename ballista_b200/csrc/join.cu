@@ -424,7 +424,7 @@ constexpr int JP_WTILE = 32 * JP_ITEMS;
 // PRED: 0 = no inline predicate, 1 = exactly one Int32 / Date32 range term (every TPC-H date filter: its column pointer
 // and bounds live in registers across the tile loop), 2 = the general RowPred loop
 template <int MODE, bool DUPS, int PRED>
-__global__ void __launch_bounds__(JP_THREADS, 5)
+__global__ void __launch_bounds__(JP_THREADS, PRED == 2 ? 5 : 8)  // the two common forms fit 32 registers: 64 warps per SM
     join_probe32_kernel(const int32_t* __restrict__ key, const __grid_constant__ RowPred pred,
                         const uint8_t* __restrict__ mask, int64_t n, bool vec, const u64* __restrict__ slots, u64 bmask,
                         int bshift, const uint32_t* __restrict__ bloom, uint32_t wmask, const uint32_t* __restrict__ next,
@@ -598,8 +598,80 @@ __global__ void join_compact_kernel(const uint32_t* __restrict__ stage_l, const 
   }
 }
 
+// ---- several Int32 key columns: the table is keyed on the first pair, the others are checked on the candidate pairs ----
+__device__ __forceinline__ bool verify_pair(const JoinVerify& v, uint32_t b, uint32_t p) {
+  for (int k = 0; k < v.n; ++k) {
+    if (v.bval[k] && !v.bval[k][b]) return false;
+    if (v.pval[k] && !v.pval[k][p]) return false;
+    if (__ldg(v.bcol[k] + b) != __ldg(v.pcol[k] + p)) return false;
+  }
+  return true;
+}
+// primary-key path: one warp per tile checks the tile's staged pairs and compacts the survivors IN PLACE, in order,
+// before the tile counts are scanned - the scan and `join_compact_kernel` then only see verified pairs
+__global__ void join_verify_stage_kernel(uint32_t* __restrict__ stage_l, uint32_t* __restrict__ stage_r,
+                                         int64_t* __restrict__ tile_cnt, int64_t n_tiles,
+                                         const __grid_constant__ JoinVerify v) {
+  const int lane = threadIdx.x & 31;
+  int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t t = w; t < n_tiles; t += nw) {
+    const int c = (int)tile_cnt[t];
+    if (c == 0) continue;
+    const int64_t src = t * JP_WTILE;
+    int kept = 0;
+    for (int i0 = 0; i0 < c; i0 += 32) {
+      const int i = i0 + lane;
+      uint32_t b = 0, p = 0;
+      bool ok = false;
+      if (i < c) {
+        b = stage_l[src + i];
+        p = stage_r[src + i];
+        ok = verify_pair(v, b, p);
+      }
+      const unsigned m = __ballot_sync(0xffffffffu, ok);
+      if (ok) {  // destination index <= i: never ahead of a pair that is still to be read
+        const int o = kept + __popc(m & ((1u << lane) - 1u));
+        stage_l[src + o] = b;
+        stage_r[src + o] = p;
+      }
+      kept += __popc(m);
+    }
+    if (lane == 0) tile_cnt[t] = kept;
+  }
+}
+// chained (duplicate build keys) path: the written pairs are checked and compacted by one scan, in pair order
+struct VerifyIn {
+  const uint32_t* bi;
+  const uint32_t* pi;
+  JoinVerify v;
+  __device__ __forceinline__ int operator()(int64_t i) const { return verify_pair(v, bi[i], pi[i]) ? 1 : 0; }
+};
+struct PairOut {
+  const uint32_t* bi;
+  const uint32_t* pi;
+  uint32_t* bo;
+  uint32_t* po;
+  __device__ __forceinline__ void operator()(int64_t i, int v, int64_t pre) const {
+    if (v) {
+      bo[pre] = bi[i];
+      po[pre] = pi[i];
+    }
+  }
+};
+static int64_t verify_pairs_scan(Ctx* ctx, const JoinVerify& v, int64_t m, BufPtr* build_idx, BufPtr* probe_idx) {
+  if (m == 0) return 0;
+  VerifyIn in{(*build_idx)->as<uint32_t>(), (*probe_idx)->as<uint32_t>(), v};
+  BufPtr bo = dev_alloc(ctx, (size_t)(m + 1) * 4), po = dev_alloc(ctx, (size_t)(m + 1) * 4);
+  int64_t kept = 0;
+  device_scan(ctx, in, m, PairOut{in.bi, in.pi, bo->as<uint32_t>(), po->as<uint32_t>()}, &kept);
+  *build_idx = bo;
+  *probe_idx = po;
+  return kept;
+}
+
 int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& pred, const uint8_t* mask, int64_t n,
-                     BufPtr* left_idx, BufPtr* right_idx) {
+                     BufPtr* left_idx, BufPtr* right_idx, const JoinVerify* verify) {
   if (n >= (int64_t)NIL) fail(B2_ERR_NOT_IMPLEMENTED, "batches beyond 2^32-2 rows");
   // Whether any key occurs twice on the build side is learnt with the first probe's own readback: that probe runs
   // the primary-key path speculatively and is redone through the chain-walking path if the flag turns out set.
@@ -656,12 +728,17 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
     if (total)
       launch(integral_constant<int, PROBE_WRITE>{}, std::true_type{}, (*left_idx)->as<uint32_t>(),
              (*right_idx)->as<uint32_t>(), grid);
-    return total;
+    return verify ? verify_pairs_scan(ctx, *verify, total, left_idx, right_idx) : total;
   }
   // primary-key build: one probe pass into tile-local staging runs, then scan + compaction of the runs
   auto stage_l = dev_alloc(ctx, (size_t)n_tiles * JP_WTILE * 4);
   auto stage_r = dev_alloc(ctx, (size_t)n_tiles * JP_WTILE * 4);
   launch(integral_constant<int, PROBE_STAGE>{}, std::false_type{}, stage_l->as<uint32_t>(), stage_r->as<uint32_t>(), grid);
+  if (verify) {
+    join_verify_stage_kernel<<<grid_for(ctx, 8, n_tiles * 32, 256), 256, 0, ctx->stream>>>(
+        stage_l->as<uint32_t>(), stage_r->as<uint32_t>(), tile_cnt, n_tiles, *verify);
+    B2_LAUNCHED(ctx);
+  }
   scan_i64(ctx, tile_cnt, n_tiles);
   if (!t.dups_known) {
     int f = 0;
@@ -669,7 +746,7 @@ int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& 
     B2_READBACK(ctx, &total, tile_cnt + n_tiles, 8);
     t.dups_known = true;
     t.has_dups = f != 0;
-    if (t.has_dups) return join_probe32(ctx, t, key, pred, mask, n, left_idx, right_idx);  // speculation failed
+    if (t.has_dups) return join_probe32(ctx, t, key, pred, mask, n, left_idx, right_idx, verify);  // speculation failed
   } else {
     B2_READBACK(ctx, &total, tile_cnt + n_tiles, 8);
   }

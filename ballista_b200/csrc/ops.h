@@ -74,8 +74,18 @@ bool compile_row_pred(const ExprPtr& pred, const Batch& batch, RowPred* out);
 // uncompacted key column; row ids are those of the unfiltered batch
 std::shared_ptr<JoinTable> join_build32(Ctx* ctx, const int32_t* key, const RowPred& pred, const uint8_t* mask,
                                         int64_t n);
+// Further Int32 / Date32 key pairs of a join whose 32-bit table is keyed on the FIRST pair: a candidate pair (build row,
+// probe row) stays when every further pair agrees and neither side is NULL there (validity bytes, optional)
+constexpr int JOIN_VERIFY_MAX = 4;
+struct JoinVerify {
+  int n = 0;
+  const int32_t* bcol[JOIN_VERIFY_MAX];
+  const int32_t* pcol[JOIN_VERIFY_MAX];
+  const uint8_t* bval[JOIN_VERIFY_MAX];
+  const uint8_t* pval[JOIN_VERIFY_MAX];
+};
 int64_t join_probe32(Ctx* ctx, JoinTable& t, const int32_t* key, const RowPred& pred, const uint8_t* mask,
-                     int64_t n_probe, BufPtr* left_idx, BufPtr* right_idx);
+                     int64_t n_probe, BufPtr* left_idx, BufPtr* right_idx, const JoinVerify* verify = nullptr);
 
 // repartition.cu: rows -> destination partition by hash of packed key; returns the stable permutation
 // (destination-major) and fills counts[n_out]

@@ -35,41 +35,6 @@ __global__ void mark_rows_kernel(const uint32_t* idx, int64_t m, uint8_t* flags)
   for (; i < m; i += (int64_t)gridDim.x * blockDim.x) flags[idx[i]] = 1;
 }
 
-// Several Int32 / Date32 key columns: the 32-bit table is built and probed on the FIRST pair only, and the candidate
-// pairs are then checked on the remaining pairs (equal values, neither side NULL) and compacted in pair order - the
-// same row set as one table over the packed key, without packing 16 bytes per row on either side.
-constexpr int JOIN_VERIFY_MAX = 4;
-struct VerifyIn {
-  const uint32_t* bi;
-  const uint32_t* pi;
-  int n;
-  const int32_t* bcol[JOIN_VERIFY_MAX];
-  const int32_t* pcol[JOIN_VERIFY_MAX];
-  const uint8_t* bval[JOIN_VERIFY_MAX];
-  const uint8_t* pval[JOIN_VERIFY_MAX];
-  __device__ __forceinline__ int operator()(int64_t i) const {
-    const uint32_t b = bi[i], p = pi[i];
-    for (int k = 0; k < n; ++k) {
-      if (bval[k] && !bval[k][b]) return 0;
-      if (pval[k] && !pval[k][p]) return 0;
-      if (__ldg(bcol[k] + b) != __ldg(pcol[k] + p)) return 0;
-    }
-    return 1;
-  }
-};
-struct PairOut {
-  const uint32_t* bi;
-  const uint32_t* pi;
-  uint32_t* bo;
-  uint32_t* po;
-  __device__ __forceinline__ void operator()(int64_t i, int v, int64_t pre) const {
-    if (v) {
-      bo[pre] = bi[i];
-      po[pre] = pi[i];
-    }
-  }
-};
-
 struct HashJoinExec : Op {
   std::vector<int> on_left, on_right;  // column indices
   int join_type = B2_JOIN_INNER;
@@ -79,7 +44,7 @@ struct HashJoinExec : Op {
   std::vector<int> left_keep, right_keep;
   KeyLayout layout;
   bool k32 = false;             // Int32 / Date32 keys only: 8-byte-slot table on the first pair, fused filters;
-                                // further pairs are verified on the candidate pairs (verify_pairs)
+                                // further pairs are verified on the candidate pairs (JoinVerify)
   std::vector<char> need;       // output columns a parent will read (empty = all)
   // build side, collected once per version of the left subtree (the reference rebuilds it per task; result-neutral,
   // SURVEY App. C.10)
@@ -213,29 +178,21 @@ struct HashJoinExec : Op {
   void ensure_table() {
     if (!table) table = build_table(*left_batch, left_pred, on_left, 0x81, &left_keys);
   }
-  // keeps the candidate pairs whose remaining key columns agree (k32 with more than one key pair)
-  int64_t verify_pairs(const Batch& build_b, const std::vector<int>& build_on, const Batch& b,
-                       const std::vector<int>& on, int64_t m, BufPtr* build_idx, BufPtr* probe_idx) {
-    if (on.size() < 2 || m == 0) return m;
-    VerifyIn in;
-    memset(&in, 0, sizeof in);
-    in.bi = (*build_idx)->as<uint32_t>();
-    in.pi = (*probe_idx)->as<uint32_t>();
-    in.n = (int)on.size() - 1;
-    for (int k = 0; k < in.n; ++k) {
+  // the key pairs after the first (k32 with several key columns): checked on the candidate pairs inside join_probe32
+  static JoinVerify verify_of(const Batch& build_b, const std::vector<int>& build_on, const Batch& b,
+                              const std::vector<int>& on) {
+    JoinVerify v;
+    memset(&v, 0, sizeof v);
+    v.n = (int)on.size() - 1;
+    for (int k = 0; k < v.n; ++k) {
       const Column& bc = build_b.cols[build_on[k + 1]];
       const Column& pc = b.cols[on[k + 1]];
-      in.bcol[k] = bc.values<int32_t>();
-      in.pcol[k] = pc.values<int32_t>();
-      in.bval[k] = bc.validity();
-      in.pval[k] = pc.validity();
+      v.bcol[k] = bc.values<int32_t>();
+      v.pcol[k] = pc.values<int32_t>();
+      v.bval[k] = bc.validity();
+      v.pval[k] = pc.validity();
     }
-    BufPtr bo = dev_alloc(ctx, (size_t)(m + 1) * 4), po = dev_alloc(ctx, (size_t)(m + 1) * 4);
-    int64_t kept = 0;
-    device_scan(ctx, in, m, PairOut{in.bi, in.pi, bo->as<uint32_t>(), po->as<uint32_t>()}, &kept);
-    *build_idx = bo;
-    *probe_idx = po;
-    return kept;
+    return v;
   }
   // pairs (row of `b`, build row) of one probe batch against `t` (built over `build_b` on `build_on`)
   int64_t probe_table(JoinTable& t, const Batch& build_b, const std::vector<int>& build_on, const Batch& b,
@@ -244,9 +201,9 @@ struct HashJoinExec : Op {
     if (k32) {
       RowPred rp;
       Column mask = side_mask(pred, b, on[0], &rp);
-      int64_t m = join_probe32(ctx, t, b.cols[on[0]].values<int32_t>(), rp,
-                               mask.data ? mask.values<uint8_t>() : nullptr, b.num_rows, build_idx, probe_idx);
-      return verify_pairs(build_b, build_on, b, on, m, build_idx, probe_idx);
+      JoinVerify v = verify_of(build_b, build_on, b, on);
+      return join_probe32(ctx, t, b.cols[on[0]].values<int32_t>(), rp, mask.data ? mask.values<uint8_t>() : nullptr,
+                          b.num_rows, build_idx, probe_idx, v.n ? &v : nullptr);
     }
     BufPtr pk = pack(b, on, null_tag);
     return join_probe(ctx, t, pk->as<Key128>(), b.num_rows, build_idx, probe_idx);

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "core.h"
+#include "span_list.h"
 
 namespace b2 {
 
@@ -20,50 +21,13 @@ struct RecvArena {
   void* base = nullptr;
   size_t cap = 0;
   int64_t gen = 0;  // unique per (rank, arena): what the peers key their mappings on
-  std::mutex mu;
-  std::map<size_t, size_t> free_spans;  // offset -> length, coalesced
+  SpanList spans;   // free byte spans of [0, cap)
   ~RecvArena() {
     if (base) cudaFree(base);
   }
-  void largest(size_t* off, size_t* len) {
-    std::lock_guard<std::mutex> g(mu);
-    *off = 0;
-    *len = 0;
-    for (auto& s : free_spans)
-      if (s.second > *len) {
-        *off = s.first;
-        *len = s.second;
-      }
-  }
-  bool take(size_t off, size_t len) {  // [off, off + len) must lie at the start of a free span
-    std::lock_guard<std::mutex> g(mu);
-    auto it = free_spans.find(off);
-    if (it == free_spans.end() || it->second < len) return false;
-    size_t rest = it->second - len;
-    free_spans.erase(it);
-    if (rest) free_spans[off + len] = rest;
-    return true;
-  }
-  void give(size_t off, size_t len) {
-    std::lock_guard<std::mutex> g(mu);
-    auto nx = free_spans.lower_bound(off);
-    if (nx != free_spans.end() && off + len == nx->first) {
-      len += nx->second;
-      nx = free_spans.erase(nx);
-    }
-    if (nx != free_spans.begin()) {
-      auto pv = std::prev(nx);
-      if (pv->first + pv->second == off) {
-        pv->second += len;
-        return;
-      }
-    }
-    free_spans[off] = len;
-  }
-  bool idle() {
-    std::lock_guard<std::mutex> g(mu);
-    return free_spans.size() == 1 && free_spans.begin()->second == cap;
-  }
+  void largest(size_t* off, size_t* len) { spans.largest(off, len); }
+  bool take(size_t off, size_t len) { return spans.take(off, len); }
+  void give(size_t off, size_t len) { spans.give(off, len); }
 };
 
 struct Comm {

@@ -201,7 +201,7 @@ static void push_offer(Ctx* ctx, size_t estimate, PushMsg* msg, std::shared_ptr<
         a->base = p;
         a->cap = cap;
         a->gen = ((int64_t)(ctx->rank + 1) << 32) | ++c->recv_gen;
-        a->free_spans[0] = cap;
+        a->spans.reset(cap);
         c->recv_arenas.push_back(a);
         *arena = a;
         best_off = 0;

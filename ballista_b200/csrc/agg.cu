@@ -62,19 +62,38 @@ void reset_group_table(GroupTable& t) {
 }
 
 // walks the source's slot list (its claimed groups), not its whole capacity
-__global__ void table_merge_kernel(TableRef src, TableRef dst, int na, int nc, int* status) {
+// (256 threads per CTA; the groups a CTA claims in one round are listed behind ONE reservation of dst.n_groups, as in
+// agg_global_kernel: a regrow moves up to millions of groups, and a counter update per claim queues on one L2 address)
+__global__ void __launch_bounds__(256) table_merge_kernel(TableRef src, TableRef dst, int na, int nc, int* status) {
+  __shared__ uint32_t s_claim[256];
+  __shared__ int s_nclaim, s_base;
   const u64 ng = (u64)*src.n_groups;
-  u64 g = blockIdx.x * (u64)blockDim.x + threadIdx.x;
-  for (; g < ng; g += (u64)gridDim.x * blockDim.x) {
-    const u64 i = src.slot_list[g];
-    Key128 k = src.keys[i];
-    u64 slot = table_upsert(dst, k);
-    if (slot == ~0ull) {
-      atomicExch(status, AGG_TABLE_FULL);
-      continue;
+  for (u64 g0 = blockIdx.x * (u64)blockDim.x; g0 < ng; g0 += (u64)gridDim.x * blockDim.x) {  // uniform per CTA
+    if (threadIdx.x == 0) s_nclaim = 0;
+    __syncthreads();
+    const u64 g = g0 + threadIdx.x;
+    if (g < ng) {
+      const u64 i = src.slot_list[g];
+      Key128 k = src.keys[i];
+      bool claimed;
+      u64 slot = table_upsert_quiet(dst, k, &claimed);
+      if (slot == ~0ull) {
+        atomicExch(status, AGG_TABLE_FULL);
+      } else {
+        if (claimed) s_claim[atomicAdd(&s_nclaim, 1)] = (uint32_t)slot;
+        for (int a = 0; a < na; ++a) red_add_f64(&dst.acc[(u64)a * dst.cap + slot], src.acc[(u64)a * src.cap + i]);
+        for (int a = 0; a < nc; ++a) red_add_u64(&dst.cnt[(u64)a * dst.cap + slot], src.cnt[(u64)a * src.cap + i]);
+      }
     }
-    for (int a = 0; a < na; ++a) red_add_f64(&dst.acc[(u64)a * dst.cap + slot], src.acc[(u64)a * src.cap + i]);
-    for (int a = 0; a < nc; ++a) red_add_u64(&dst.cnt[(u64)a * dst.cap + slot], src.cnt[(u64)a * src.cap + i]);
+    __syncthreads();
+    const int nclaim = s_nclaim;
+    if (nclaim) {  // uniform
+      if (threadIdx.x == 0) s_base = atomicAdd(dst.n_groups, nclaim);
+      __syncthreads();
+      if (dst.slot_list)
+        for (int q = threadIdx.x; q < nclaim; q += blockDim.x) dst.slot_list[s_base + q] = s_claim[q];
+    }
+    __syncthreads();
   }
 }
 

@@ -143,3 +143,22 @@ def test_fused_high_cardinality_falls_back_to_global_table(ctx, O, n):
     rep, sums, counts = O.hash_aggregate([host["l_orderkey"]], [host["l_quantity"]])
     want = [{"l_orderkey": int(host["l_orderkey"][r]), "q[sum]": float(sums[g, 0])} for g, r in enumerate(rep)]
     assert_rows_match(got, want, ["l_orderkey"], approx=["q[sum]"])
+
+
+def test_high_cardinality_over_growing_batches_regrows_the_group_table(ctx, O):
+    """group by l_orderkey over batches of 4 k, 40 k and 260 k rows in ONE partition: the HBM group table is re-sized
+    between batches (table_merge_kernel moves the groups claimed so far, listing them behind one reservation per CTA
+    round) and every group must come out once with the sum over all batches."""
+    from ballista_b200 import HashAggregateExec, col, count, sum as sum_, tpch
+    sf, cuts = 0.1, [0, 4_000, 44_000, 304_000]
+    bs = [ctx.tpch("lineitem", sf, a, b, columns=["l_orderkey", "l_quantity"]) for a, b in zip(cuts, cuts[1:])]
+    partial = HashAggregateExec("Partial", [col("l_orderkey")],
+                                [sum_(col("l_quantity")).alias("q"), count(col("l_quantity")).alias("c")],
+                                tpch.scan(ctx, [bs]))
+    got = partial.collect().to_pylist()
+    host = O.gen_lineitem(sf, 0, cuts[-1])
+    rep, sums, counts = O.hash_aggregate([host["l_orderkey"]], [host["l_quantity"]])
+    want = [{"l_orderkey": int(host["l_orderkey"][r]), "q[sum]": float(sums[g, 0]), "c[count]": int(counts[g, 0])}
+            for g, r in enumerate(rep)]
+    assert len(got) == len(want) > 70_000
+    assert_rows_match(got, want, ["l_orderkey"], exact=["c[count]"], approx=["q[sum]"])

@@ -14,6 +14,7 @@
 #include <type_traits>
 
 #include "expr.h"
+#include "scan.cuh"
 #include "table.cuh"
 
 namespace b2 {
@@ -180,6 +181,48 @@ __global__ void str_case_kernel(const uint8_t* in, int64_t nbytes, bool upper, u
   }
   if (non_ascii) atomicOr(status, 4);
 }
+// trim / ltrim / rtrim (ScalarFunction TRIM / LTRIM / RTRIM).  The reference's DataFusion revision sits inside the
+// weeks in which these moved from Rust's str::trim* (every Unicode White_Space character) to the Postgres forms
+// (U+0020 only), and its source is not on disk.  Both agree whenever the character left at a trimmed edge is no kind
+// of white space, so: U+0020 is trimmed, and a row whose trimmed edge stops at U+0009..U+000D or at a byte >= 0x80
+// (possibly a non-ASCII White_Space code point) raises status bit 8 - refused, not guessed.
+__device__ __forceinline__ bool edge_in_doubt(uint8_t c) { return (c >= 0x09 && c <= 0x0D) || c >= 0x80; }
+__global__ void str_trim_kernel(const int32_t* off, const uint8_t* chr, const uint8_t* valid, int64_t n, bool left,
+                                bool right, int32_t* begin, int32_t* len, int* status) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  bool doubt = false;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int32_t b = off[i], e = off[i + 1];
+    const bool live = !valid || valid[i];
+    if (left) {
+      while (b < e && chr[b] == 0x20) ++b;
+      doubt |= live && b < e && edge_in_doubt(chr[b]);
+    }
+    if (right) {
+      while (e > b && chr[e - 1] == 0x20) --e;
+      doubt |= live && e > b && edge_in_doubt(chr[e - 1]);
+    }
+    begin[i] = b;
+    len[i] = e - b;
+  }
+  if (doubt) atomicOr(status, 8);
+}
+__global__ void str_copy_ranges_kernel(const uint8_t* in_chr, const int32_t* begin, const int32_t* out_off, int64_t n,
+                                       uint8_t* out_chr) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t b = begin[i], o = out_off[i], l = out_off[i + 1] - o;
+    for (int32_t q = 0; q < l; ++q) out_chr[o + q] = in_chr[b + q];
+  }
+}
+struct TrimOffOut {
+  int32_t* off;
+  int64_t n;
+  __device__ __forceinline__ void operator()(int64_t i, int v, int64_t pre) const {
+    off[i] = (int32_t)pre;
+    if (i == n - 1) off[n] = (int32_t)(pre + v);
+  }
+};
 // a Utf8 literal broadcast to a column (CASE branches, projections)
 __global__ void str_fill_kernel(const uint8_t* lit, int len, int64_t n, int32_t* off, uint8_t* chr) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -193,7 +236,7 @@ __global__ void str_fill_kernel(const uint8_t* lit, int len, int64_t n, int32_t*
 // ---- scalar functions on Float64 (ScalarFunction, ballista.proto:80-114) ----
 enum {
   FN_SQRT = 0, FN_SIN, FN_COS, FN_TAN, FN_ASIN, FN_ACOS, FN_ATAN, FN_EXP, FN_LOG, FN_LOG2, FN_LOG10, FN_FLOOR, FN_CEIL,
-  FN_ROUND, FN_TRUNC, FN_ABS, FN_SIGNUM, FN_OCTETLENGTH, FN_CONCAT, FN_LOWER, FN_UPPER
+  FN_ROUND, FN_TRUNC, FN_ABS, FN_SIGNUM, FN_OCTETLENGTH, FN_CONCAT, FN_LOWER, FN_UPPER, FN_TRIM, FN_LTRIM, FN_RTRIM
 };
 __global__ void math_kernel(int fn, const double* in, int64_t n, double* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -269,6 +312,8 @@ static void check_eval_status(Ctx* ctx, const BufPtr& st) {
   if (host & 1) fail(B2_ERR_EXECUTION, "Divide by zero");
   if (host & 2) fail(B2_ERR_EXECUTION, "integer overflow in division");
   if (host & 4) fail(B2_ERR_NOT_IMPLEMENTED, "lower() / upper() on non-ASCII text");
+  if (host & 8) fail(B2_ERR_NOT_IMPLEMENTED, "trim() of a string whose trimmed edge is a tab / line break or a non-ASCII character (the reference revision's "
+                   "white-space set is not known)");
 }
 
 template <class T>
@@ -609,6 +654,32 @@ static Column eval_scalar_fn(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
           c.chars->as<uint8_t>(), c.chars_len, e->op == FN_UPPER, out.chars->as<uint8_t>(), st->as<int>());
       B2_LAUNCHED(ctx);
       check_eval_status(ctx, st);
+    }
+    return out;
+  }
+  if (e->op == FN_TRIM || e->op == FN_LTRIM || e->op == FN_RTRIM) {
+    Column out = new_col(ctx, B2_UTF8, n);
+    out.valid = c.valid;
+    out.data = dev_alloc_zero(ctx, (size_t)(n + 1) * 4);
+    out.chars_len = 0;
+    out.chars = dev_alloc(ctx, 16);
+    if (n) {
+      BufPtr st = dev_alloc_zero(ctx, 16);
+      BufPtr begin = dev_alloc(ctx, (size_t)n * 4), len = dev_alloc(ctx, (size_t)n * 4);
+      str_trim_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), c.chars->as<uint8_t>(), c.validity(), n, e->op != FN_RTRIM,
+                                                    e->op != FN_LTRIM, begin->as<int32_t>(), len->as<int32_t>(),
+                                                    st->as<int>());
+      B2_LAUNCHED(ctx);
+      int64_t total = 0;
+      device_scan(ctx, I32In{len->as<int32_t>()}, n, TrimOffOut{out.data->as<int32_t>(), n}, &total);
+      check_eval_status(ctx, st);
+      out.chars_len = total;
+      out.chars = dev_alloc(ctx, (size_t)total + 16);
+      if (total) {
+        str_copy_ranges_kernel<<<grid, 256, 0, ctx->stream>>>(c.chars->as<uint8_t>(), begin->as<int32_t>(),
+                                                           out.data->as<int32_t>(), n, out.chars->as<uint8_t>());
+        B2_LAUNCHED(ctx);
+      }
     }
     return out;
   }

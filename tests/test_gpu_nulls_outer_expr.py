@@ -343,6 +343,35 @@ def test_like_utf8_ordering_and_scalar_functions(ctx):
     assert up["l"].to_pylist() == [w.lower() for w in ascii_rows["s"].to_pylist()]
 
 
+def test_trim_functions(ctx):
+    """trim / ltrim / rtrim (ScalarFunction TRIM / LTRIM / RTRIM, ballista.proto:101-103).  The reference's DataFusion
+    revision lies between Rust's str::trim* (all Unicode white space) and the Postgres forms (U+0020 only) and cannot be
+    read here: spaces are trimmed - where both agree - and a row whose trimmed edge is another white-space character, or
+    a non-ASCII one, is refused instead of guessed.  NULLs stay NULL."""
+    from ballista_b200 import NotImplementedOnGpu, col, scalar_fn
+    words = ["", " ", "  a", "a  ", "  a b  ", "x\ty", "no-space", "   ", " q ", "inner  space", " 7 ", "x" * 40 + "  ",
+             "  a\u00e9b  "]
+    rng = np.random.default_rng(5)
+    n = 4001
+    s = [words[i] for i in rng.integers(0, len(words), n)]
+    b = rb(s=pa.array(s, mask=rng.random(n) < 0.1))
+    got = project(ctx, b, [scalar_fn("trim", col("s")).alias("t"), scalar_fn("ltrim", col("s")).alias("l"),
+                           scalar_fn("rtrim", col("s")).alias("r")])
+    src = pa.Table.from_batches([b])["s"].to_pylist()
+    assert got["t"].to_pylist() == [None if v is None else v.strip(" ") for v in src]
+    assert got["l"].to_pylist() == [None if v is None else v.lstrip(" ") for v in src]
+    assert got["r"].to_pylist() == [None if v is None else v.rstrip(" ") for v in src]
+    # an edge that the two readings would treat differently: loud refusal (only on the side that is trimmed)
+    for bad in [" \tx", "x\n ", " \u00a0x "]:
+        with pytest.raises(NotImplementedOnGpu):
+            project(ctx, rb(s=pa.array([bad, "ok"])), [scalar_fn("trim", col("s")).alias("t")])
+    assert project(ctx, rb(s=pa.array(["\tx  "])), [scalar_fn("rtrim", col("s")).alias("r")])["r"].to_pylist() == ["\tx"]
+    # a NULL row's bytes are not looked at
+    nul = rb(s=pa.array(["\tz", " a "], mask=np.array([True, False])))
+    assert project(ctx, nul, [scalar_fn("trim", col("s")).alias("t")])["t"].to_pylist() == [None, "a"]
+    assert project(ctx, rb(s=pa.array([], pa.utf8())), [scalar_fn("trim", col("s")).alias("t")]).num_rows == 0
+
+
 def test_integer_division_by_zero_fails_and_casts(ctx):
     from ballista_b200 import BallistaError, col, lit
     from ballista_b200 import _capi as K

@@ -236,7 +236,8 @@ __global__ void str_fill_kernel(const uint8_t* lit, int len, int64_t n, int32_t*
 // ---- scalar functions on Float64 (ScalarFunction, ballista.proto:80-114) ----
 enum {
   FN_SQRT = 0, FN_SIN, FN_COS, FN_TAN, FN_ASIN, FN_ACOS, FN_ATAN, FN_EXP, FN_LOG, FN_LOG2, FN_LOG10, FN_FLOOR, FN_CEIL,
-  FN_ROUND, FN_TRUNC, FN_ABS, FN_SIGNUM, FN_OCTETLENGTH, FN_CONCAT, FN_LOWER, FN_UPPER, FN_TRIM, FN_LTRIM, FN_RTRIM
+  FN_ROUND, FN_TRUNC, FN_ABS, FN_SIGNUM, FN_OCTETLENGTH, FN_CONCAT, FN_LOWER, FN_UPPER, FN_TRIM, FN_LTRIM, FN_RTRIM,
+  FN_TOTIMESTAMP, FN_ARRAY, FN_NULLIF
 };
 __global__ void math_kernel(int fn, const double* in, int64_t n, double* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -623,10 +624,32 @@ static Column eval_case(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
   fail(B2_ERR_NOT_IMPLEMENTED, std::string("CASE producing ") + dtype_name(e->dtype));
 }
 
+// NULLIF(a, b): children = [a, a = b] (expr.cpp); out = (a = b holds) ? NULL : a
+template <class T> static Column nullif_typed(Ctx* ctx, const Column& a, const Column& cond, int dtype, int64_t n) {
+  Column out = new_col(ctx, dtype, n);
+  out.valid = dev_alloc(ctx, (size_t)n + 16);
+  if (n) {
+    select_kernel<T><<<grid_for(ctx, 8, n, 256), 256, 0, ctx->stream>>>(
+        cond.values<uint8_t>(), cond.validity(), Operand<T>{nullptr, T()}, nullptr, true, Operand<T>{a.values<T>(), T()},
+        a.validity(), false, n, out.data->as<T>(), out.valid->as<uint8_t>());
+    B2_LAUNCHED(ctx);
+  }
+  return out;
+}
+
 static Column eval_scalar_fn(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
   const int64_t n = batch.num_rows;
   const int grid = grid_for(ctx, 8, n, 256);
   Column c = eval_expr(ctx, e->ch[0], batch);
+  if (e->op == FN_NULLIF) {
+    Column cond = eval_expr(ctx, e->ch[1], batch);
+    switch (e->dtype) {
+      case B2_INT32: return nullif_typed<int32_t>(ctx, c, cond, e->dtype, n);
+      case B2_INT64: case B2_UINT64: return nullif_typed<int64_t>(ctx, c, cond, e->dtype, n);
+      case B2_FLOAT64: return nullif_typed<double>(ctx, c, cond, e->dtype, n);
+      default: return nullif_typed<uint8_t>(ctx, c, cond, e->dtype, n);
+    }
+  }
   if (e->op <= FN_SIGNUM) {
     Column out = new_col(ctx, B2_FLOAT64, n);
     out.valid = c.valid;

@@ -337,6 +337,26 @@ ExprPtr decode_expr(const b2_expr* ex, const Schema& input) {
         break;
       }
       case B2_EXPR_SCALAR_FN: {
+        if (n.op == 26 && n.nchildren == 2 && st.size() >= 2) {
+          // NULLIF(a, b) (DataFusion nullif_func: eq(a, b), then arrow's nullif): NULL where a = b holds, else a.  A NULL
+          // on either side makes the comparison NULL, which counts as "does not hold".  Same-typed arguments only (the
+          // reference's Uniform(2, ...) signature leaves such arguments as they are; mixed types would be coerced by
+          // rules that are not restated here).
+          ExprPtr b = pop(), a = pop();
+          const int t = a->dtype;
+          const bool ok_type = t == B2_INT32 || t == B2_INT64 || t == B2_UINT64 || t == B2_FLOAT64 || t == B2_BOOL || t == B2_UINT8;
+          if (!ok_type || b->dtype != t)
+            fail(B2_ERR_NOT_IMPLEMENTED, std::string("nullif over ") + dtype_name(a->dtype) + " and " + dtype_name(b->dtype) +
+                                             " (implemented: two arguments of one numeric or Boolean type)");
+          if (a->is_literal()) fail(B2_ERR_NOT_IMPLEMENTED, "nullif over a literal first argument");
+          auto e = std::make_shared<Expr>();
+          e->kind = B2_EXPR_SCALAR_FN;
+          e->op = n.op;
+          e->dtype = t;
+          e->ch = {a, make_binary(B2_OP_EQ, a, b)};
+          st.push_back(e);
+          break;
+        }
         if (n.nchildren != 1 || st.empty())
           fail(B2_ERR_NOT_IMPLEMENTED, "scalar function " + std::to_string(n.op) + " with " + std::to_string(n.nchildren) +
                                            " arguments");
@@ -360,7 +380,7 @@ ExprPtr decode_expr(const b2_expr* ex, const Schema& input) {
         } else {
           fail(B2_ERR_NOT_IMPLEMENTED, "scalar function " + std::to_string(n.op) +
                                            " (implemented: sqrt sin cos tan asin acos atan exp ln log2 log10 floor ceil "
-                                           "round trunc abs signum octet_length lower upper trim ltrim rtrim)");
+                                           "round trunc abs signum octet_length lower upper trim ltrim rtrim nullif)");
         }
         if (c->is_literal() && c->dtype != B2_FLOAT64) fail(B2_ERR_NOT_IMPLEMENTED, "scalar function over a literal");
         e->ch = {c};

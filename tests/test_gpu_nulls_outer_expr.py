@@ -372,6 +372,31 @@ def test_trim_functions(ctx):
     assert project(ctx, rb(s=pa.array([], pa.utf8())), [scalar_fn("trim", col("s")).alias("t")]).num_rows == 0
 
 
+def test_nullif(ctx):
+    """NULLIF(a, b) (ScalarFunction NULLIF, ballista.proto:106; DataFusion nullif_func = eq + arrow's nullif): NULL where
+    a = b holds, else a; a NULL on either side leaves a as it is.  Same-typed arguments only."""
+    from ballista_b200 import NotImplementedOnGpu, col, lit, scalar_fn
+    rng = np.random.default_rng(12)
+    n = 3001
+    a_i = rng.integers(0, 5, n).astype(np.int32)
+    b_i = rng.integers(0, 5, n).astype(np.int32)
+    a_f = rng.integers(0, 4, n).astype(np.float64) / 2
+    a_l = rng.integers(-2, 3, n).astype(np.int64) * 3_000_000_000
+    ma, mb = rng.random(n) < 0.1, rng.random(n) < 0.1
+    b = rb(ai=pa.array(a_i, mask=ma), bi=pa.array(b_i, mask=mb), af=pa.array(a_f, mask=ma), al=a_l)
+    got = project(ctx, b, [scalar_fn("nullif", col("ai"), col("bi")).alias("ii"),
+                           scalar_fn("nullif", col("af"), lit(0.5)).alias("f"),
+                           scalar_fn("nullif", col("al"), lit(3_000_000_000)).alias("l")])
+    t = pa.Table.from_batches([b])
+    ai, bi, af, al = (t[c].to_pylist() for c in ("ai", "bi", "af", "al"))
+    assert got["ii"].to_pylist() == [None if (x is not None and y is not None and x == y) else x for x, y in zip(ai, bi)]
+    assert got["f"].to_pylist() == [None if x == 0.5 else x for x in af]
+    assert got["l"].to_pylist() == [None if x == 3_000_000_000 else x for x in al]
+    assert got.schema.field("ii").type == pa.int32() and got.schema.field("l").type == pa.int64()
+    with pytest.raises(NotImplementedOnGpu):  # Int32 against an Int64 literal: the reference would coerce, not restated
+        project(ctx, b, [scalar_fn("nullif", col("ai"), lit(1)).alias("x")])
+
+
 def test_integer_division_by_zero_fails_and_casts(ctx):
     from ballista_b200 import BallistaError, col, lit
     from ballista_b200 import _capi as K

@@ -97,3 +97,54 @@ def test_empty_join_fixture(ctx, gold):
     j = HashJoinExec(tpch.scan(ctx, [[cust]]), tpch.scan(ctx, [[orders]]), [("c_custkey", "o_custkey")])
     out = j.collect()
     assert out.num_rows == 0 and out.schema.names == ["c_custkey", "c_mktsegment", "o_orderkey", "o_custkey"]
+
+
+def test_q3_partial_state_schema_and_two_partition_final(ctx, O, gold):
+    """The state schema the Partial stage of Q3 ships to the Final stage (group columns, then one `name[sum]` state per
+    SUM: SURVEY A.2), and a Final over the states of TWO Partial tasks (the fixture's two lineitem partitions joined
+    against the same orders) against the exact-arithmetic answer."""
+    import datetime
+    from ballista_b200 import CoalesceBatchesExec, HashAggregateExec, HashJoinExec, MemoryExec, tpch
+    orders = pa.RecordBatch.from_arrays(
+        [pa.array(np.array(gold["orders"][k], dtype=np.int32)) if k != "o_orderdate"
+         else pa.array(np.array(gold["orders"][k], dtype=np.int32)).cast(pa.date32()) for k in tpch.Q3_ORDERS_COLUMNS],
+        names=tpch.Q3_ORDERS_COLUMNS)
+    lparts = [[O.to_arrow(G.lineitem_columns(p, O.Utf8), ["l_orderkey", "l_linenumber", "l_extendedprice", "l_discount"])]
+              for p in gold["lineitem"]["partitions"]]
+    join = CoalesceBatchesExec(HashJoinExec(tpch.scan(ctx, [[orders]]), tpch.scan(ctx, lparts),
+                                            [("o_orderkey", "l_orderkey")]))
+    assert join.output_partitioning()[1] == 2  # the probe side's partitions
+    partial = HashAggregateExec("Partial", tpch.q3_groups(), tpch.q3_aggregates(), join)
+    ps = partial.schema()
+    assert ps.names == ["l_orderkey", "o_orderdate", "o_shippriority", "revenue[sum]"]
+    assert [str(ps.field(n).type) for n in ps.names] == ["int32", "date32[day]", "int32", "double"]
+    states = [s for p in range(2) for s in partial.collect_device(p)]
+    assert len(states) == 2
+    final = tpch.q3_final(MemoryExec(ctx, ps, [states]), join.schema())
+    rows = final.collect().to_pylist()
+    for r in rows:
+        r["o_orderdate"] = (r["o_orderdate"] - datetime.date(1970, 1, 1)).days
+    assert_rows_match(rows, gold["expected"]["q3_nofilter"], ["l_orderkey", "o_orderdate", "o_shippriority"],
+                      approx=["revenue"])
+
+
+@pytest.mark.parametrize("n_out", [2, 3])
+def test_repartition_fixture_keeps_arrival_order(ctx, O, gold, n_out):
+    """RepartitionExec(Hash(l_orderkey), n) over the fixture's two lineitem partitions: every input row comes out once;
+    an order's lines share one output partition; inside an output partition the rows appear in arrival order (input
+    partition 0 before 1, file order within each) - what the reference's per-input-batch `take` + channel send
+    produces for a single consumer draining the inputs in order."""
+    from ballista_b200 import RepartitionExec, col, tpch
+    names = ["l_orderkey", "l_linenumber", "l_extendedprice"]
+    parts = [[O.to_arrow(G.lineitem_columns(p, O.Utf8), names)] for p in gold["lineitem"]["partitions"]]
+    rep = RepartitionExec(tpch.scan(ctx, parts), "Hash", n_out, [col("l_orderkey")])
+    arrival = [(k, ln) for p in gold["lineitem"]["partitions"] for k, ln in zip(p["l_orderkey"], p["l_linenumber"])]
+    seen, owner = [], {}
+    for d in range(n_out):
+        t = rep.collect(d)
+        rows = list(zip(t["l_orderkey"].to_pylist(), t["l_linenumber"].to_pylist()))
+        for k, _ in rows:
+            assert owner.setdefault(k, d) == d
+        assert rows == [r for r in arrival if owner.get(r[0]) == d]  # a subsequence of the arrival order
+        seen += rows
+    assert sorted(seen) == sorted(arrival) and len(seen) == 20

@@ -611,10 +611,94 @@ static Column case_typed(Ctx* ctx, const ExprPtr& e, const Batch& batch, size_t 
   }
   return acc;
 }
+// CASE producing Utf8: the first WHEN whose condition holds (true and not NULL) picks its THEN string, else the ELSE
+// string, else NULL.  One pass picks the branch and its length per row, one scan makes the offsets, one pass copies.
+constexpr int CASE_STR_MAX = 8;
+struct CaseStrArgs {
+  int n_when;
+  bool has_else;
+  const uint8_t* cond[CASE_STR_MAX];
+  const uint8_t* cval[CASE_STR_MAX];
+  const int32_t* off[CASE_STR_MAX + 1];  // THEN strings, then the ELSE string
+  const uint8_t* chr[CASE_STR_MAX + 1];
+  const uint8_t* val[CASE_STR_MAX + 1];
+};
+__global__ void case_str_pick_kernel(const __grid_constant__ CaseStrArgs a, int64_t n, uint8_t* sel, int32_t* len,
+                                     uint8_t* out_valid) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int s = -1;
+    for (int k = 0; k < a.n_when && s < 0; ++k)
+      if (a.cond[k][i] != 0 && (!a.cval[k] || a.cval[k][i])) s = k;
+    if (s < 0 && a.has_else) s = a.n_when;
+    const bool v = s >= 0 && (!a.val[s] || a.val[s][i]);
+    sel[i] = v ? (uint8_t)s : (uint8_t)255;
+    len[i] = v ? a.off[s][i + 1] - a.off[s][i] : 0;
+    out_valid[i] = v;
+  }
+}
+__global__ void case_str_copy_kernel(const __grid_constant__ CaseStrArgs a, int64_t n, const uint8_t* sel,
+                                     const int32_t* out_off, uint8_t* out_chr) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int s = sel[i];
+    if (s == 255) continue;
+    const int32_t b = a.off[s][i], o = out_off[i], l = out_off[i + 1] - o;
+    for (int32_t q = 0; q < l; ++q) out_chr[o + q] = a.chr[s][b + q];
+  }
+}
+static Column case_utf8(Ctx* ctx, const ExprPtr& e, const Batch& batch, size_t n_when, bool has_else) {
+  const int64_t n = batch.num_rows;
+  if (n_when > (size_t)CASE_STR_MAX) fail(B2_ERR_NOT_IMPLEMENTED, "CASE producing Utf8 with more than 8 WHEN branches");
+  CaseStrArgs a;
+  memset(&a, 0, sizeof a);
+  a.n_when = (int)n_when;
+  a.has_else = has_else;
+  std::vector<Column> keep;  // conditions and branch strings (literals broadcast) stay alive until the kernels are queued
+  for (size_t k = 0; k < n_when; ++k) {
+    keep.push_back(eval_expr(ctx, e->ch[2 * k], batch));
+    a.cond[k] = keep.back().values<uint8_t>();
+    a.cval[k] = keep.back().validity();
+    keep.push_back(eval_expr(ctx, e->ch[2 * k + 1], batch));
+    a.off[k] = keep.back().values<int32_t>();
+    a.chr[k] = keep.back().chars->as<uint8_t>();
+    a.val[k] = keep.back().validity();
+  }
+  if (has_else) {
+    keep.push_back(eval_expr(ctx, e->ch.back(), batch));
+    a.off[n_when] = keep.back().values<int32_t>();
+    a.chr[n_when] = keep.back().chars->as<uint8_t>();
+    a.val[n_when] = keep.back().validity();
+  }
+  Column out;
+  out.dtype = B2_UTF8;
+  out.length = n;
+  out.data = dev_alloc_zero(ctx, (size_t)(n + 1) * 4);
+  out.chars = dev_alloc(ctx, 16);
+  out.chars_len = 0;
+  if (!n) return out;
+  out.valid = dev_alloc(ctx, (size_t)n + 16);
+  BufPtr sel = dev_alloc(ctx, (size_t)n + 16), len = dev_alloc(ctx, (size_t)n * 4);
+  const int grid = grid_for(ctx, 8, n, 256);
+  case_str_pick_kernel<<<grid, 256, 0, ctx->stream>>>(a, n, sel->as<uint8_t>(), len->as<int32_t>(), out.valid->as<uint8_t>());
+  B2_LAUNCHED(ctx);
+  int64_t total = 0;
+  device_scan(ctx, I32In{len->as<int32_t>()}, n, TrimOffOut{out.data->as<int32_t>(), n}, &total);
+  if (total >= (1ll << 31)) fail(B2_ERR_EXECUTION, "Utf8 column beyond 2 GiB after CASE");
+  out.chars_len = total;
+  out.chars = dev_alloc(ctx, (size_t)total + 16);
+  if (total) {
+    case_str_copy_kernel<<<grid, 256, 0, ctx->stream>>>(a, n, sel->as<uint8_t>(), out.data->as<int32_t>(), out.chars->as<uint8_t>());
+    B2_LAUNCHED(ctx);
+  }
+  return out;
+}
+
 static Column eval_case(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
   const bool has_base = e->op & 1, has_else = e->op & 2;
   (void)has_base;  // folded into the WHEN conditions at decode
   size_t n_when = (e->ch.size() - (has_else ? 1 : 0)) / 2;
+  if (e->dtype == B2_UTF8) return case_utf8(ctx, e, batch, n_when, has_else);
   switch (e->dtype) {
     case B2_INT32: case B2_DATE32: return case_typed<int32_t>(ctx, e, batch, 0, n_when, has_else);
     case B2_INT64: case B2_UINT64: return case_typed<int64_t>(ctx, e, batch, 0, n_when, has_else);

@@ -313,7 +313,6 @@ ExprPtr decode_expr(const b2_expr* ex, const Schema& input) {
         // result type: the common type of the THEN / ELSE values
         int t = 0;
         auto widen = [&](const ExprPtr& v) {
-          if (v->dtype == B2_UTF8) fail(B2_ERR_NOT_IMPLEMENTED, "CASE producing Utf8");
           if (!t) t = v->dtype;
           else if (t != v->dtype) {
             if (!is_num(t) || !is_num(v->dtype))
@@ -332,6 +331,7 @@ ExprPtr decode_expr(const b2_expr* ex, const Schema& input) {
           e->ch.push_back(make_cast(items[first + 2 * q + 1], t));
         }
         if (has_else) e->ch.push_back(make_cast(items.back(), t));
+        if (t == B2_UTF8 && pairs / 2 > 8) fail(B2_ERR_NOT_IMPLEMENTED, "CASE producing Utf8 with more than 8 WHEN branches");
         e->dtype = t;
         st.push_back(e);
         break;

@@ -309,6 +309,28 @@ def test_case_expressions(ctx):
     assert got.schema.field("hi").type == pa.int64() and got.schema.field("c3").type == pa.float64()
 
 
+def test_case_producing_strings(ctx):
+    """CASE whose THEN / ELSE values are Utf8 (literals and columns): first condition that holds (a NULL condition does
+    not), NULL when nothing fires and there is no ELSE, a NULL string in the chosen branch stays NULL."""
+    from ballista_b200 import case, col, lit
+    b = nullable_batch(4003, seed=9)
+    t = pa.Table.from_batches([b])
+    x, y, s = (t[c].to_pylist() for c in ("x", "y", "s"))
+    got = project(ctx, b, [
+        case([(col("x") < lit(25.0), lit("low")), (col("x") < lit(50.0), col("s"))], otherwise=lit("")).alias("a"),
+        case([(col("y") == lit(0), lit("zero")), (col("y") == lit(1), lit("one-and-a-bit longer"))]).alias("b"),
+        case([(lit(1), col("s"))], otherwise=lit("other"), base=col("y")).alias("c"),
+    ])
+    for i in range(b.num_rows):
+        a = "low" if (x[i] is not None and x[i] < 25.0) else (s[i] if (x[i] is not None and x[i] < 50.0) else "")
+        assert got["a"][i].as_py() == a, i
+        bb = "zero" if y[i] == 0 else ("one-and-a-bit longer" if y[i] == 1 else None)
+        assert got["b"][i].as_py() == bb, i
+        assert got["c"][i].as_py() == (s[i] if y[i] == 1 else "other"), i
+    assert got.schema.field("a").type == pa.utf8()
+    assert project(ctx, b.slice(0, 0), [case([(col("x") < lit(1.0), lit("q"))]).alias("e")]).num_rows == 0
+
+
 def test_like_utf8_ordering_and_scalar_functions(ctx):
     from ballista_b200 import FilterExec, col, lit, scalar_fn
     words = ["PROMO BRUSHED", "promo", "STANDARD POLISHED", "SMALL PROMO", "", "a%b", "häßlich", "MEDIUM", "x_y", "PRO"]

@@ -223,6 +223,84 @@ struct TrimOffOut {
     if (i == n - 1) off[n] = (int32_t)(pre + v);
   }
 };
+// md5(Utf8) -> 32 lower-case hex digits (ScalarFunction MD5; RFC 1321).  One thread per string: the message is
+// consumed in 64-byte blocks straight from the character buffer, the padded tail block(s) are assembled in registers.
+__device__ __forceinline__ uint32_t md5_rotl(uint32_t x, int c) { return (x << c) | (x >> (32 - c)); }
+__device__ void md5_block(uint32_t st[4], const uint32_t m[16]) {
+  const uint32_t K[64] = {
+      0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501, 0x698098d8,
+      0x8b44f7af, 0xffff5bb1, 0x895cd7be, 0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821, 0xf61e2562, 0xc040b340,
+      0x265e5a51, 0xe9b6c7aa, 0xd62f105d, 0x02441453, 0xd8a1e681, 0xe7d3fbc8, 0x21e1cde6, 0xc33707d6, 0xf4d50d87,
+      0x455a14ed, 0xa9e3e905, 0xfcefa3f8, 0x676f02d9, 0x8d2a4c8a, 0xfffa3942, 0x8771f681, 0x6d9d6122, 0xfde5380c,
+      0xa4beea44, 0x4bdecfa9, 0xf6bb4b60, 0xbebfbc70, 0x289b7ec6, 0xeaa127fa, 0xd4ef3085, 0x04881d05, 0xd9d4d039,
+      0xe6db99e5, 0x1fa27cf8, 0xc4ac5665, 0xf4292244, 0x432aff97, 0xab9423a7, 0xfc93a039, 0x655b59c3, 0x8f0ccc92,
+      0xffeff47d, 0x85845dd1, 0x6fa87e4f, 0xfe2ce6e0, 0xa3014314, 0x4e0811a1, 0xf7537e82, 0xbd3af235, 0x2ad7d2bb,
+      0xeb86d391};
+  const int R[64] = {7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 5, 9,  14, 20, 5, 9,
+                     14, 20, 5, 9,  14, 20, 5, 9,  14, 20, 4, 11, 16, 23, 4, 11, 16, 23, 4, 11, 16, 23,
+                     4, 11, 16, 23, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21};
+  uint32_t a = st[0], b = st[1], c = st[2], d = st[3];
+  for (int i = 0; i < 64; ++i) {
+    uint32_t f;
+    int g;
+    if (i < 16) { f = (b & c) | (~b & d); g = i; }
+    else if (i < 32) { f = (d & b) | (~d & c); g = (5 * i + 1) & 15; }
+    else if (i < 48) { f = b ^ c ^ d; g = (3 * i + 5) & 15; }
+    else { f = c ^ (b | ~d); g = (7 * i) & 15; }
+    const uint32_t t = d;
+    d = c;
+    c = b;
+    b = b + md5_rotl(a + f + K[i] + m[g], R[i]);
+    a = t;
+  }
+  st[0] += a; st[1] += b; st[2] += c; st[3] += d;
+}
+__global__ void md5_kernel(const int32_t* off, const uint8_t* chr, int64_t n, int32_t* out_off, uint8_t* out_chr) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint8_t* p = chr + off[i];
+    const uint32_t len = (uint32_t)(off[i + 1] - off[i]);
+    uint32_t st[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
+    uint32_t m[16];
+    uint32_t done = 0;
+    for (; done + 64 <= len; done += 64) {
+      for (int w = 0; w < 16; ++w)
+        m[w] = (uint32_t)p[done + 4 * w] | ((uint32_t)p[done + 4 * w + 1] << 8) | ((uint32_t)p[done + 4 * w + 2] << 16) |
+               ((uint32_t)p[done + 4 * w + 3] << 24);
+      md5_block(st, m);
+    }
+    // tail: the remaining bytes, 0x80, zeros, the bit length in the last 8 bytes of a block (a second block when the
+    // remainder is 56 bytes or more)
+    const uint32_t rem = len - done;
+    for (int blk = 0; blk < (rem >= 56 ? 2 : 1); ++blk) {
+      for (int w = 0; w < 16; ++w) {
+        uint32_t word = 0;
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t pos = (uint32_t)blk * 64 + 4 * w + q;  // byte position within the tail
+          uint32_t byte = 0;
+          if (pos < rem) byte = p[done + pos];
+          else if (pos == rem) byte = 0x80;
+          word |= byte << (8 * q);
+        }
+        m[w] = word;
+      }
+      if (blk == (rem >= 56 ? 1 : 0)) {
+        m[14] = len << 3;
+        m[15] = len >> 29;
+      }
+      md5_block(st, m);
+    }
+    out_off[i] = (int32_t)(i * 32);
+    if (i == n - 1) out_off[n] = (int32_t)(n * 32);
+    for (int w = 0; w < 4; ++w)
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t byte = (st[w] >> (8 * q)) & 0xFFu;
+        const char* hex = "0123456789abcdef";
+        out_chr[i * 32 + w * 8 + q * 2] = (uint8_t)hex[byte >> 4];
+        out_chr[i * 32 + w * 8 + q * 2 + 1] = (uint8_t)hex[byte & 15];
+      }
+  }
+}
 // a Utf8 literal broadcast to a column (CASE branches, projections)
 __global__ void str_fill_kernel(const uint8_t* lit, int len, int64_t n, int32_t* off, uint8_t* chr) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -237,7 +315,7 @@ __global__ void str_fill_kernel(const uint8_t* lit, int len, int64_t n, int32_t*
 enum {
   FN_SQRT = 0, FN_SIN, FN_COS, FN_TAN, FN_ASIN, FN_ACOS, FN_ATAN, FN_EXP, FN_LOG, FN_LOG2, FN_LOG10, FN_FLOOR, FN_CEIL,
   FN_ROUND, FN_TRUNC, FN_ABS, FN_SIGNUM, FN_OCTETLENGTH, FN_CONCAT, FN_LOWER, FN_UPPER, FN_TRIM, FN_LTRIM, FN_RTRIM,
-  FN_TOTIMESTAMP, FN_ARRAY, FN_NULLIF
+  FN_TOTIMESTAMP, FN_ARRAY, FN_NULLIF, FN_DATETRUNC, FN_MD5
 };
 __global__ void math_kernel(int fn, const double* in, int64_t n, double* out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -761,6 +839,22 @@ static Column eval_scalar_fn(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
           c.chars->as<uint8_t>(), c.chars_len, e->op == FN_UPPER, out.chars->as<uint8_t>(), st->as<int>());
       B2_LAUNCHED(ctx);
       check_eval_status(ctx, st);
+    }
+    return out;
+  }
+  if (e->op == FN_MD5) {
+    if (n * 32 >= (1ll << 31)) fail(B2_ERR_EXECUTION, "Utf8 column beyond 2 GiB after md5");
+    Column out;
+    out.dtype = B2_UTF8;
+    out.length = n;
+    out.valid = c.valid;  // md5(NULL) is NULL; the digest computed over a NULL row's bytes is never looked at
+    out.data = dev_alloc_zero(ctx, (size_t)(n + 1) * 4);
+    out.chars_len = n * 32;
+    out.chars = dev_alloc(ctx, (size_t)n * 32 + 16);
+    if (n) {
+      md5_kernel<<<grid, 256, 0, ctx->stream>>>(c.values<int32_t>(), c.chars->as<uint8_t>(), n, out.data->as<int32_t>(),
+                                               out.chars->as<uint8_t>());
+      B2_LAUNCHED(ctx);
     }
     return out;
   }

@@ -374,13 +374,16 @@ ExprPtr decode_expr(const b2_expr* ex, const Schema& input) {
         } else if (n.op == 19 || n.op == 20) {  // LOWER / UPPER
           if (c->dtype != B2_UTF8) fail(B2_ERR_EXECUTION, "lower / upper need a Utf8 argument");
           e->dtype = B2_UTF8;
+        } else if (n.op == 28) {  // MD5: Utf8 -> Utf8 (32 hex digits)
+          if (c->dtype != B2_UTF8) fail(B2_ERR_EXECUTION, "md5 needs a Utf8 argument");
+          e->dtype = B2_UTF8;
         } else if (n.op >= 21 && n.op <= 23) {  // TRIM / LTRIM / RTRIM
           if (c->dtype != B2_UTF8) fail(B2_ERR_EXECUTION, "trim / ltrim / rtrim need a Utf8 argument");
           e->dtype = B2_UTF8;
         } else {
           fail(B2_ERR_NOT_IMPLEMENTED, "scalar function " + std::to_string(n.op) +
                                            " (implemented: sqrt sin cos tan asin acos atan exp ln log2 log10 floor ceil "
-                                           "round trunc abs signum octet_length lower upper trim ltrim rtrim nullif)");
+                                           "round trunc abs signum octet_length lower upper trim ltrim rtrim nullif md5)");
         }
         if (c->is_literal() && c->dtype != B2_FLOAT64) fail(B2_ERR_NOT_IMPLEMENTED, "scalar function over a literal");
         e->ch = {c};

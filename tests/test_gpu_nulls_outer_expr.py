@@ -394,6 +394,21 @@ def test_trim_functions(ctx):
     assert project(ctx, rb(s=pa.array([], pa.utf8())), [scalar_fn("trim", col("s")).alias("t")]).num_rows == 0
 
 
+def test_md5(ctx):
+    """md5(Utf8) -> 32 lower-case hex digits (ScalarFunction MD5, ballista.proto:108), NULL for NULL; lengths around the
+    55 / 56 / 64-byte padding boundaries and multi-byte characters, against hashlib."""
+    import hashlib
+    from ballista_b200 import col, scalar_fn
+    vals = ["", "a", "abc", "message digest", "h\u00e4\u00dflich"] + ["x" * k for k in (54, 55, 56, 57, 63, 64, 65, 119, 120, 128, 1000)]
+    rng = np.random.default_rng(4)
+    s = [vals[i] for i in rng.integers(0, len(vals), 3001)]
+    b = rb(s=pa.array(s, mask=rng.random(len(s)) < 0.1))
+    got = project(ctx, b, [scalar_fn("md5", col("s")).alias("h")])["h"].to_pylist()
+    src = pa.Table.from_batches([b])["s"].to_pylist()
+    assert got == [None if v is None else hashlib.md5(v.encode()).hexdigest() for v in src]
+    assert hashlib.md5(b"").hexdigest() in got and got.count(None) > 100
+
+
 def test_nullif(ctx):
     """NULLIF(a, b) (ScalarFunction NULLIF, ballista.proto:106; DataFusion nullif_func = eq + arrow's nullif): NULL where
     a = b holds, else a; a NULL on either side leaves a as it is.  Same-typed arguments only."""

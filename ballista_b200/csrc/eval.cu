@@ -391,6 +391,8 @@ static void check_eval_status(Ctx* ctx, const BufPtr& st) {
   if (host & 1) fail(B2_ERR_EXECUTION, "Divide by zero");
   if (host & 2) fail(B2_ERR_EXECUTION, "integer overflow in division");
   if (host & 4) fail(B2_ERR_NOT_IMPLEMENTED, "lower() / upper() on non-ASCII text");
+  if (host & 16)
+    fail(B2_ERR_NOT_IMPLEMENTED, "concat() with a NULL argument (the reference revision's NULL rule for concat is not known)");
   if (host & 8) fail(B2_ERR_NOT_IMPLEMENTED, "trim() of a string whose trimmed edge is a tab / line break or a non-ASCII character (the reference revision's "
                    "white-space set is not known)");
 }
@@ -772,6 +774,75 @@ static Column case_utf8(Ctx* ctx, const ExprPtr& e, const Batch& batch, size_t n
   return out;
 }
 
+// CONCAT(s1, ..., sk), k <= 8.  The reference's DataFusion revision sits between "NULL if any argument is NULL" and the
+// Postgres rule "NULL arguments are skipped" and cannot be read here; both agree on rows without a NULL argument, so
+// those are concatenated and a row WITH a NULL argument raises status bit 16: refused, not guessed.
+struct ConcatArgs {
+  int n;
+  const int32_t* off[8];
+  const uint8_t* chr[8];
+  const uint8_t* val[8];
+};
+__global__ void concat_len_kernel(const __grid_constant__ ConcatArgs a, int64_t n, int32_t* len, int* status) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  bool null_arg = false;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int32_t l = 0;
+    for (int k = 0; k < a.n; ++k) {
+      null_arg |= a.val[k] && !a.val[k][i];
+      l += a.off[k][i + 1] - a.off[k][i];
+    }
+    len[i] = l;
+  }
+  if (null_arg) atomicOr(status, 16);
+}
+__global__ void concat_copy_kernel(const __grid_constant__ ConcatArgs a, int64_t n, const int32_t* out_off, uint8_t* out_chr) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int32_t o = out_off[i];
+    for (int k = 0; k < a.n; ++k) {
+      const int32_t b = a.off[k][i], l = a.off[k][i + 1] - b;
+      for (int32_t q = 0; q < l; ++q) out_chr[o + q] = a.chr[k][b + q];
+      o += l;
+    }
+  }
+}
+static Column eval_concat(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
+  const int64_t n = batch.num_rows;
+  ConcatArgs a;
+  memset(&a, 0, sizeof a);
+  a.n = (int)e->ch.size();
+  std::vector<Column> keep;
+  for (int k = 0; k < a.n; ++k) {
+    keep.push_back(eval_expr(ctx, e->ch[k], batch));
+    a.off[k] = keep.back().values<int32_t>();
+    a.chr[k] = keep.back().chars->as<uint8_t>();
+    a.val[k] = keep.back().validity();
+  }
+  Column out;
+  out.dtype = B2_UTF8;
+  out.length = n;
+  out.data = dev_alloc_zero(ctx, (size_t)(n + 1) * 4);
+  out.chars = dev_alloc(ctx, 16);
+  out.chars_len = 0;
+  if (!n) return out;
+  BufPtr st = dev_alloc_zero(ctx, 16), len = dev_alloc(ctx, (size_t)n * 4);
+  const int grid = grid_for(ctx, 8, n, 256);
+  concat_len_kernel<<<grid, 256, 0, ctx->stream>>>(a, n, len->as<int32_t>(), st->as<int>());
+  B2_LAUNCHED(ctx);
+  int64_t total = 0;
+  device_scan(ctx, I32In{len->as<int32_t>()}, n, TrimOffOut{out.data->as<int32_t>(), n}, &total);
+  check_eval_status(ctx, st);
+  if (total >= (1ll << 31)) fail(B2_ERR_EXECUTION, "Utf8 column beyond 2 GiB after concat");
+  out.chars_len = total;
+  out.chars = dev_alloc(ctx, (size_t)total + 16);
+  if (total) {
+    concat_copy_kernel<<<grid, 256, 0, ctx->stream>>>(a, n, out.data->as<int32_t>(), out.chars->as<uint8_t>());
+    B2_LAUNCHED(ctx);
+  }
+  return out;
+}
+
 static Column eval_case(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
   const bool has_base = e->op & 1, has_else = e->op & 2;
   (void)has_base;  // folded into the WHEN conditions at decode
@@ -802,6 +873,7 @@ template <class T> static Column nullif_typed(Ctx* ctx, const Column& a, const C
 static Column eval_scalar_fn(Ctx* ctx, const ExprPtr& e, const Batch& batch) {
   const int64_t n = batch.num_rows;
   const int grid = grid_for(ctx, 8, n, 256);
+  if (e->op == FN_CONCAT) return eval_concat(ctx, e, batch);
   Column c = eval_expr(ctx, e->ch[0], batch);
   if (e->op == FN_NULLIF) {
     Column cond = eval_expr(ctx, e->ch[1], batch);

@@ -357,6 +357,25 @@ ExprPtr decode_expr(const b2_expr* ex, const Schema& input) {
           st.push_back(e);
           break;
         }
+        if (n.op == 18 && n.nchildren >= 1 && n.nchildren <= 8 && (int)st.size() >= n.nchildren) {
+          // CONCAT(s1, s2, ...) over Utf8 arguments (the reference's Variadic(Utf8) signature would cast others to Utf8:
+          // not restated).  See eval.cu for the NULL rule.
+          std::vector<ExprPtr> args(n.nchildren);
+          for (int q = n.nchildren - 1; q >= 0; --q) args[q] = pop();
+          bool any_col = false;
+          for (auto& a : args) {
+            if (a->dtype != B2_UTF8) fail(B2_ERR_NOT_IMPLEMENTED, std::string("concat over a ") + dtype_name(a->dtype) + " argument");
+            any_col = any_col || !a->is_literal();
+          }
+          if (!any_col) fail(B2_ERR_NOT_IMPLEMENTED, "concat over literals only");
+          auto e = std::make_shared<Expr>();
+          e->kind = B2_EXPR_SCALAR_FN;
+          e->op = n.op;
+          e->dtype = B2_UTF8;
+          e->ch = args;
+          st.push_back(e);
+          break;
+        }
         if (n.nchildren != 1 || st.empty())
           fail(B2_ERR_NOT_IMPLEMENTED, "scalar function " + std::to_string(n.op) + " with " + std::to_string(n.nchildren) +
                                            " arguments");
@@ -383,7 +402,7 @@ ExprPtr decode_expr(const b2_expr* ex, const Schema& input) {
         } else {
           fail(B2_ERR_NOT_IMPLEMENTED, "scalar function " + std::to_string(n.op) +
                                            " (implemented: sqrt sin cos tan asin acos atan exp ln log2 log10 floor ceil "
-                                           "round trunc abs signum octet_length lower upper trim ltrim rtrim nullif md5)");
+                                           "round trunc abs signum octet_length lower upper trim ltrim rtrim nullif md5 concat)");
         }
         if (c->is_literal() && c->dtype != B2_FLOAT64) fail(B2_ERR_NOT_IMPLEMENTED, "scalar function over a literal");
         e->ch = {c};

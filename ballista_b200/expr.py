@@ -156,7 +156,7 @@ def case(when_then, otherwise=None, base=None):
 
 def scalar_fn(name, *args):
     """ScalarFunctionNode (ballista.proto:80-119): sqrt, sin, ..., floor, ceil, round, trunc, abs, signum,
-    octetlength, lower, upper, trim, ltrim, rtrim, nullif, md5."""
+    octetlength, lower, upper, trim, ltrim, rtrim, nullif, md5, concat."""
     return Expr(K.EXPR_SCALAR_FN, [a if isinstance(a, Expr) else lit(a) for a in args],
                 op=K.SCALAR_FUNCTIONS.index(name.lower()))
 

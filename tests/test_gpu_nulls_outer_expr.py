@@ -394,6 +394,27 @@ def test_trim_functions(ctx):
     assert project(ctx, rb(s=pa.array([], pa.utf8())), [scalar_fn("trim", col("s")).alias("t")]).num_rows == 0
 
 
+def test_concat(ctx):
+    """concat(s1, s2, ...) (ScalarFunction CONCAT, ballista.proto:98) over Utf8 columns and literals.  Rows without a NULL
+    argument are concatenated (every reading of the pinned DataFusion revision agrees on them); a NULL argument is
+    refused, because that revision's rule (NULL result, or the argument skipped) cannot be read here."""
+    from ballista_b200 import NotImplementedOnGpu, col, lit, scalar_fn
+    rng = np.random.default_rng(6)
+    words = np.array(["", "a", "PROMO", "h\u00e4\u00df", "x" * 33])
+    n = 3001
+    a, c = words[rng.integers(0, 5, n)], words[rng.integers(0, 5, n)]
+    b = rb(a=pa.array(a), c=pa.array(c))
+    got = project(ctx, b, [scalar_fn("concat", col("a"), lit("-"), col("c")).alias("j"),
+                           scalar_fn("concat", col("a")).alias("one")])
+    assert got["j"].to_pylist() == [f"{x}-{y}" for x, y in zip(a.tolist(), c.tolist())]
+    assert got["one"].to_pylist() == a.tolist()
+    withnull = rb(a=pa.array(a, mask=rng.random(n) < 0.01), c=pa.array(c))
+    with pytest.raises(NotImplementedOnGpu, match="NULL argument"):
+        project(ctx, withnull, [scalar_fn("concat", col("a"), col("c")).alias("j")])
+    with pytest.raises(NotImplementedOnGpu):
+        project(ctx, b, [scalar_fn("concat", lit("x"), lit("y")).alias("j")])
+
+
 def test_md5(ctx):
     """md5(Utf8) -> 32 lower-case hex digits (ScalarFunction MD5, ballista.proto:108), NULL for NULL; lengths around the
     55 / 56 / 64-byte padding boundaries and multi-byte characters, against hashlib."""

@@ -157,6 +157,26 @@ def between(x, lo, hi):
     return e
 
 
+def scalar_fn(fun, *args):
+    e = Expr()
+    e.scalar_function.fun = {"OCTETLENGTH": 17, "CONCAT": 18, "LOWER": 19, "UPPER": 20, "TRIM": 21, "LTRIM": 22, "RTRIM": 23,
+                             "NULLIF": 26, "MD5": 28}[fun]
+    for a in args:
+        e.scalar_function.expr.add().CopyFrom(a)
+    return e
+
+
+def case(when_then, otherwise=None):
+    e = Expr()
+    for w, t in when_then:
+        wt = e.case_.when_then_expr.add()
+        wt.when_expr.CopyFrom(w)
+        wt.then_expr.CopyFrom(t)
+    if otherwise is not None:
+        e.case_.else_expr.CopyFrom(otherwise)
+    return e
+
+
 def agg(fn, arg):
     e = Expr()
     e.aggregate_expr.aggr_function = {"MIN": 0, "MAX": 1, "SUM": 2, "AVG": 3, "COUNT": 4}[fn]
@@ -318,6 +338,22 @@ def build():
     rp.repartition.hash.partition_count = 4
     plans["lineitem_repartition_stage"] = {"plan": rp, "leaves": ["lineitem:" + ",".join(l_cols)],
                                            "nodes": ["RepartitionExec", "CoalesceBatchesExec", "FilterExec", "CsvScan"]}
+    # projection over customer with the string / NULL-producing vocabulary (ScalarFunctionNode, CaseNode)
+    pc_cols = ["c_custkey", "c_nationkey", "c_mktsegment"]
+    proj = Plan()
+    proj.projection.input.CopyFrom(csv_scan("customer", CUSTOMER, pc_cols))
+    for name, e in [("c_custkey", col("c_custkey")),
+                    ("seg", scalar_fn("TRIM", col("c_mktsegment"))),
+                    ("h", scalar_fn("MD5", col("c_mktsegment"))),
+                    ("tag", scalar_fn("CONCAT", col("c_mktsegment"), lit("#"), scalar_fn("LOWER", col("c_mktsegment")))),
+                    ("nk", scalar_fn("NULLIF", col("c_nationkey"), Expr(literal=Scalar(int32_value=3)))),
+                    ("cls", case([(binary("Eq", col("c_mktsegment"), lit("BUILDING")), lit("b")),
+                                  (binary("Lt", col("c_nationkey"), Expr(literal=Scalar(int32_value=5))), col("c_mktsegment"))],
+                                 lit("other")))]:
+        proj.projection.expr.add().CopyFrom(e)
+        proj.projection.expr_name.append(name)
+    plans["customer_projection_stage"] = {"plan": proj, "leaves": ["customer:" + ",".join(pc_cols)],
+                                          "nodes": ["ProjectionExec", "CsvScan"]}
     return plans
 
 

@@ -103,3 +103,26 @@ def test_repartition_stage_plan_and_leaf_checks(ctx):
     with pytest.raises(BallistaError):  # a source whose columns are not the ones the plan was built on
         plan_from_proto(ctx, plan_bytes("lineitem_repartition_stage"),
                         [tpch.scan(ctx, [[ctx.tpch("orders", sf, columns=tpch.Q3_ORDERS_COLUMNS)]])])
+
+
+@pytest.mark.gpu
+def test_projection_stage_with_string_functions_from_proto(ctx):
+    """A ProjectionExec whose expressions are ScalarFunctionNode / CaseNode messages (trim, md5, concat over lower,
+    nullif, a CASE with Utf8 branches) encoded by the protobuf runtime, decoded by proto.cpp and evaluated on the GPU."""
+    import hashlib
+    from ballista_b200 import plan_from_proto, tpch
+    spec = PLANS["customer_projection_stage"]["leaves"][0]
+    cu = _leaf_batches(ctx, 0.01, spec)
+    plan = plan_from_proto(ctx, plan_bytes("customer_projection_stage"), [tpch.scan(ctx, [[cu]])])
+    assert plan.schema().names == ["c_custkey", "seg", "h", "tag", "nk", "cls"]
+    got = plan.collect()
+    src = cu.to_arrow()
+    ck, nk, seg = (src.column(src.schema.get_field_index(c)).to_pylist() for c in ("c_custkey", "c_nationkey", "c_mktsegment"))
+    assert got.num_rows == len(ck) == 1500
+    assert got["c_custkey"].to_pylist() == ck
+    assert got["seg"].to_pylist() == [s.strip(" ") for s in seg]
+    assert got["h"].to_pylist() == [hashlib.md5(s.encode()).hexdigest() for s in seg]
+    assert got["tag"].to_pylist() == [s + "#" + s.lower() for s in seg]
+    assert got["nk"].to_pylist() == [None if n == 3 else n for n in nk]
+    assert got["cls"].to_pylist() == ["b" if s == "BUILDING" else (s if n < 5 else "other") for s, n in zip(seg, nk)]
+    assert any(v is None for v in got["nk"].to_pylist()) and "other" in got["cls"].to_pylist()

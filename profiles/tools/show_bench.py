@@ -12,6 +12,9 @@ for k, v in d.get("other_configs", {}).items():
     if "roofline" in v: extra += f" scan_frac={v['roofline']['frac_scan_only']:.3f}" + (f" scan+table={v['roofline'].get('frac_scan_plus_table', 0):.3f}" if 'frac_scan_plus_table' in v['roofline'] else "")
     if "frac_of_hbm_peak_per_gpu" in v: extra += f" frac_hbm={v['frac_of_hbm_peak_per_gpu']:.3f}"
     p = v.get("parity", {})
+    if not isinstance(v, dict) or "ms_per_step" not in v:  # legs with their own shape (parquet_ingest)
+        print(f"  {k:16s} {json.dumps(v)[:200]}")
+        continue
     print(f"  {k:16s} {v['ms_per_step']:.3f} ms (median {v['step_ms']['median_ms']:.3f}) launches={v.get('launches_per_step')} {extra} parity_ok={p.get('ok')} err={p.get('max_rel_err')}")
 for k in ("cpu_baseline", "cpu_baseline_b"):
     if d.get(k): print(f"  {k}: {d[k].get('value')}")

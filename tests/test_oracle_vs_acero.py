@@ -73,3 +73,24 @@ def test_generator_shape(O):
     # any row range is reproducible from the row index alone
     sub = O.gen_lineitem(sf, 1000, 77)
     assert np.array_equal(sub["l_extendedprice"], c["l_extendedprice"][1000:1077])
+
+
+@pytest.mark.parametrize("how", ["Inner", "Left", "Right"])
+def test_two_key_outer_joins_with_nulls_vs_acero(O, how):
+    """The oracle's outer-join restatement over TWO key columns with NULLs in either (the checker of the GPU's
+    Int32 multi-key join) against pyarrow's Acero join on the same data."""
+    rng = np.random.default_rng(41)
+    nl, nr = 1500, 4001
+    la, lb = rng.integers(0, 200, nl).astype(np.int32), rng.integers(0, 5, nl).astype(np.int32)
+    ra, rb = rng.integers(50, 250, nr).astype(np.int32), rng.integers(0, 5, nr).astype(np.int32)
+    lma, lmb = rng.random(nl) < 0.05, rng.random(nl) < 0.05
+    rma, rmb = rng.random(nr) < 0.05, rng.random(nr) < 0.05
+    li, ri = O.hash_join_outer([la, lb], [ra, rb], how, ~(lma | lmb), ~(rma | rmb))
+    left = pa.table({"a": pa.array(la, mask=lma), "b": pa.array(lb, mask=lmb), "lrow": np.arange(nl, dtype=np.int64)})
+    right = pa.table({"a2": pa.array(ra, mask=rma), "b2": pa.array(rb, mask=rmb), "rrow": np.arange(nr, dtype=np.int64)})
+    jt = {"Inner": "inner", "Left": "left outer", "Right": "right outer"}[how]
+    ac = left.join(right, keys=["a", "b"], right_keys=["a2", "b2"], join_type=jt, coalesce_keys=False)
+    want = sorted((-1 if l is None else l, -1 if r is None else r)
+                  for l, r in zip(ac["lrow"].to_pylist(), ac["rrow"].to_pylist()))
+    got = sorted(zip(li.tolist(), ri.tolist()))
+    assert got == want and len(got) > 500

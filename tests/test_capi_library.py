@@ -56,3 +56,18 @@ def test_product_does_not_import_the_oracle():
                 bad = re.findall(r"^\s*(?:from|import)\s+oracle|liboracle|#include\s+\"[^\"]*oracle|oracle_py|dlopen\([^)]*oracle",
                                  src, flags=re.M)
                 assert not bad, (os.path.join(dirpath, f), bad)
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/ballista_b200.h is the drop-in boundary: it must compile as C99 (what bindgen / cgo-style tools consume) and
+    as C++11, with no torch / CUDA type in any signature."""
+    import subprocess
+    src = tmp_path / "hdr.c"
+    src.write_text('#include "ballista_b200.h"\nint main(void) { return b2_version() != 0 ? 0 : 1; }\n')
+    inc = os.path.join(ROOT, "include")
+    for cmd in (["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-I", inc, str(src)],
+                ["g++", "-std=c++11", "-Wall", "-Werror", "-fsyntax-only", "-x", "c++", "-I", inc, str(src)]):
+        p = subprocess.run(cmd, capture_output=True, text=True)
+        assert p.returncode == 0, p.stderr
+    text = open(os.path.join(inc, "ballista_b200.h")).read()
+    assert "torch" not in text and "cudaStream_t" not in text and "#include <cuda" not in text

@@ -69,5 +69,5 @@ def test_header_is_plain_c(tmp_path):
                 ["g++", "-std=c++11", "-Wall", "-Werror", "-fsyntax-only", "-x", "c++", "-I", inc, str(src)]):
         p = subprocess.run(cmd, capture_output=True, text=True)
         assert p.returncode == 0, p.stderr
-    text = open(os.path.join(inc, "ballista_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", open(os.path.join(inc, "ballista_b200.h")).read(), flags=re.S)  # declarations only
     assert "torch" not in text and "cudaStream_t" not in text and "#include <cuda" not in text
